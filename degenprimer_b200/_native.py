@@ -1,0 +1,358 @@
+"""ctypes binding of include/degenprimer_b200.h.
+
+There is no fallback: if libdegenprimer_b200.so is missing, or no sm_100 GPU is
+usable, every entry point raises.  The library is loaded lazily so importing
+the package (and forking, as the reference's Manager processes do —
+BioUtils/Tools/UMP.py:83-91) never creates a CUDA context by itself.
+"""
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libdegenprimer_b200.so')
+
+DP_OK = 0
+DP_ERR_CUDA, DP_ERR_ARG, DP_ERR_ALPHABET, DP_ERR_LENGTH, DP_ERR_UNSUPPORTED = -1, -2, -3, -4, -5
+DP_ERR_IO, DP_ERR_NOMEM, DP_ERR_ABORTED, DP_ERR_STATE = -6, -7, -8, -9
+DP_MAX_PRIMER_LEN = 64
+DP_MAX_PRIMERS = 64
+DP_STRAND_FWD, DP_STRAND_REV, DP_STRAND_BOTH = 1, 2, 3
+DP_ALGO_AUTO, DP_ALGO_POPC, DP_ALGO_BITSLICE = 0, 1, 2
+
+LETTERS = 'ACTGRYSWKMBDHVN'      # letter index order of the ABI
+BASES = 'ACTG'                   # 2-bit plane code order
+
+
+class NativeError(RuntimeError):
+    def __init__(self, code, message):
+        RuntimeError.__init__(self, 'degenprimer_b200 native error %d: %s' % (code, message))
+        self.code = code
+        self.message = message
+
+
+class Aborted(Exception):
+    """The abort flag was raised; the facade turns this into `return None`."""
+
+
+class dp_template_info(C.Structure):
+    _fields_ = [('n_records', C.c_uint32), ('reserved', C.c_uint32),
+                ('total_bases', C.c_uint64), ('padded_bases', C.c_uint64),
+                ('n_exception_runs', C.c_uint64), ('device_bytes', C.c_uint64)]
+
+
+class dp_scan_stats(C.Structure):
+    _fields_ = [('windows', C.c_uint64), ('candidates', C.c_uint64), ('hits', C.c_uint64),
+                ('ms_scan', C.c_float), ('ms_total', C.c_float),
+                ('launches', C.c_uint32), ('algo', C.c_uint32)]
+
+
+class dp_dg_stats(C.Structure):
+    _fields_ = [('duplexes', C.c_uint64), ('dimers_tried', C.c_uint64), ('dimers_kept', C.c_uint64),
+                ('ms_kernel', C.c_float), ('ms_total', C.c_float),
+                ('launches', C.c_uint32), ('reserved', C.c_uint32)]
+
+
+class dp_nn_tables(C.Structure):
+    _fields_ = [('stack_dH', C.c_double * (4 * 4 * 15)), ('stack_dS', C.c_double * (4 * 4 * 15)),
+                ('rstack_dH', C.c_double * (4 * 4 * 15)), ('rstack_dS', C.c_double * (4 * 4 * 15)),
+                ('dangling_dH', C.c_double * (2 * 4 * 4 * 4)), ('dangling_dS', C.c_double * (2 * 4 * 4 * 4)),
+                ('loop_dS', C.c_double * 64),
+                ('ini_dH', C.c_double), ('ini_dS', C.c_double), ('ter_dH', C.c_double), ('ter_dS', C.c_double),
+                ('terminal_mismatch', C.c_double), ('dS_Na', C.c_double), ('R', C.c_double),
+                ('K0', C.c_double), ('T_DMSO', C.c_double)]
+
+
+class dp_conditions(C.Structure):
+    _fields_ = [('PCR_T', C.c_double), ('Na_eq_log', C.c_double), ('max_dimer_dG', C.c_double),
+                ('max_dG_for_K', C.c_double), ('DNA', C.c_double), ('DMSO', C.c_double)]
+
+
+HIT_DTYPE = np.dtype([('pos', '<u8'), ('record', '<u4'), ('primer', '<u2'),
+                      ('strand', 'u1'), ('score3', 'u1')], align=True)
+DIMER_DTYPE = np.dtype([('hit', '<u4'), ('variant', '<u4'), ('match_mask', '<u8'), ('dG', '<f8')],
+                       align=True)
+assert HIT_DTYPE.itemsize == 16 and DIMER_DTYPE.itemsize == 24
+
+_lib = None
+_lock = threading.Lock()
+
+
+def _declare(lib):
+    vp, cp, u32, u64, i32 = C.c_void_p, C.c_char_p, C.c_uint32, C.c_uint64, C.c_int
+    P = C.POINTER
+    sig = {
+        'dp_abi_version': (i32, []),
+        'dp_device_count': (i32, [P(i32)]),
+        'dp_create': (vp, [i32]),
+        'dp_create_error': (cp, []),
+        'dp_destroy': (None, [vp]),
+        'dp_last_error': (cp, [vp]),
+        'dp_free': (None, [vp]),
+        'dp_abort_requested': (i32, [vp, i32]),
+        'dp_device_info': (i32, [vp, C.c_char_p, P(i32), P(i32), P(i32), P(i32), P(u64)]),
+        'dp_template_from_records': (i32, [vp, u32, P(C.c_void_p), P(u64), P(vp)]),
+        'dp_template_from_ascii': (i32, [vp, C.c_void_p, u64, P(vp)]),
+        'dp_template_from_fasta': (i32, [vp, cp, P(vp)]),
+        'dp_template_free': (None, [vp]),
+        'dp_template_get_info': (i32, [vp, P(dp_template_info)]),
+        'dp_template_record': (i32, [vp, u32, P(u64), P(u64), P(cp), P(cp)]),
+        'dp_template_unpack': (i32, [vp, vp, u32, u64, u64, i32, C.c_void_p]),
+        'dp_scan': (i32, [vp, vp, u32, P(cp), P(C.c_int32), u64, u64, i32, i32,
+                          P(vp), P(u64), P(dp_scan_stats)]),
+        'dp_tables_load': (i32, [vp, P(dp_nn_tables)]),
+        'dp_duplex_dg': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p, C.c_void_p,
+                               C.c_void_p, P(dp_conditions), P(vp), P(u64), P(dp_dg_stats)]),
+        'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
+        'dp_dimer_dg': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                              C.c_void_p, C.c_void_p, C.c_void_p, P(dp_conditions), C.c_void_p]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    return sig
+
+
+EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
+           'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
+           'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
+           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_variant_tm dp_dimer_dg').split()
+
+
+def load():
+    """dlopen the library (no CUDA call is made).  Raises if it is missing."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError(
+                    'libdegenprimer_b200.so is not built (%s). Run `python -m degenprimer_b200.build`; '
+                    'there is no CPU fallback.' % LIB_PATH)
+            lib = C.CDLL(LIB_PATH)
+            _declare(lib)
+            if lib.dp_abi_version() != 1:
+                raise RuntimeError('libdegenprimer_b200.so has ABI %d, expected 1' % lib.dp_abi_version())
+            _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Template(object):
+    """A set of records resident in HBM (handle owned by this object)."""
+
+    def __init__(self, ctx, handle, keepalive=None):
+        self.ctx = ctx
+        self._h = handle
+        self._keep = keepalive
+        info = dp_template_info()
+        ctx._check(ctx.lib.dp_template_get_info(handle, C.byref(info)))
+        self.n_records = info.n_records
+        self.total_bases = info.total_bases
+        self.padded_bases = info.padded_bases
+        self.n_exception_runs = info.n_exception_runs
+        self.device_bytes = info.device_bytes
+        self.starts, self.lengths, self.ids, self.descriptions = [], [], [], []
+        s, n, i, d = C.c_uint64(), C.c_uint64(), C.c_char_p(), C.c_char_p()
+        for r in range(self.n_records):
+            ctx._check(ctx.lib.dp_template_record(handle, r, C.byref(s), C.byref(n), C.byref(i), C.byref(d)))
+            self.starts.append(s.value)
+            self.lengths.append(n.value)
+            self.ids.append(i.value.decode())
+            self.descriptions.append(d.value.decode())
+
+    def unpack(self, record=0, begin=0, n=None, reverse=False):
+        if n is None:
+            n = self.lengths[record] - begin
+        buf = C.create_string_buffer(max(1, n))
+        self.ctx._check(self.ctx.lib.dp_template_unpack(self.ctx._h, self._h, record, begin, n,
+                                                        1 if reverse else 0, buf))
+        return buf.raw[:n].decode('ascii')
+
+    def close(self):
+        if self._h is not None and self.ctx._h is not None:
+            self.ctx.lib.dp_template_free(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context(object):
+    """One CUDA context + stream on one device."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        h = self.lib.dp_create(int(device))
+        if not h:
+            raise NativeError(DP_ERR_CUDA, self.lib.dp_create_error().decode())
+        self._h = h
+        self.device = int(device)
+        self._tables_key = None
+
+    def close(self):
+        if self._h is not None:
+            self.lib.dp_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc == DP_OK:
+            return
+        msg = self.lib.dp_last_error(self._h).decode(errors='replace')
+        if rc == DP_ERR_ABORTED:
+            raise Aborted(msg)
+        if rc == DP_ERR_LENGTH:
+            raise ValueError('SearchEngine._find: template sequence should be longer or equal to primer '
+                             'sequence and both should be grater than zero. (%s)' % msg)
+        if rc == DP_ERR_ALPHABET:
+            raise KeyError(msg)
+        raise NativeError(rc, msg)
+
+    def abort(self, flag=True):
+        return self.lib.dp_abort_requested(self._h, 1 if flag else 0)
+
+    def device_info(self):
+        name = C.create_string_buffer(256)
+        sm, maj, mnr, khz = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        mem = C.c_uint64()
+        self._check(self.lib.dp_device_info(self._h, name, C.byref(sm), C.byref(maj), C.byref(mnr),
+                                            C.byref(khz), C.byref(mem)))
+        return dict(name=name.value.decode(), sm_count=sm.value, cc=(maj.value, mnr.value),
+                    clock_khz=khz.value, hbm_bytes=mem.value)
+
+    # ---- templates -------------------------------------------------------------
+    def template_from_sequences(self, seqs):
+        """seqs: list of bytes / str / (address, length) pairs."""
+        keep, ptrs, lens = [], [], []
+        for s in seqs:
+            if isinstance(s, tuple):
+                ptrs.append(int(s[0]))
+                lens.append(int(s[1]))
+                continue
+            if isinstance(s, str):
+                s = s.encode('latin-1')
+            elif not isinstance(s, bytes):
+                s = bytes(s)
+            keep.append(s)
+            ptrs.append(C.cast(C.c_char_p(s), C.c_void_p).value or 0)
+            lens.append(len(s))
+        n = len(ptrs)
+        arr = (C.c_void_p * max(1, n))(*ptrs)
+        ln = (C.c_uint64 * max(1, n))(*lens)
+        out = C.c_void_p()
+        self._check(self.lib.dp_template_from_records(self._h, n, arr, ln, C.byref(out)))
+        return Template(self, out.value)
+
+    def template_from_fasta(self, path):
+        out = C.c_void_p()
+        self._check(self.lib.dp_template_from_fasta(self._h, os.fsencode(path), C.byref(out)))
+        return Template(self, out.value)
+
+    # ---- scan ---------------------------------------------------------------------
+    def scan(self, template, masters, mismatches, seg_begin=0, seg_end=2 ** 64 - 1,
+             strands=DP_STRAND_BOTH, algo=DP_ALGO_AUTO):
+        """Returns (hits structured array, stats dict)."""
+        n = len(masters)
+        m = (C.c_char_p * n)(*[s.encode('ascii') if isinstance(s, str) else s for s in masters])
+        if isinstance(mismatches, int):
+            mismatches = [mismatches] * n
+        k = (C.c_int32 * n)(*[int(x) for x in mismatches])
+        hits, n_hits, st = C.c_void_p(), C.c_uint64(), dp_scan_stats()
+        self._check(self.lib.dp_scan(self._h, template._h, n, m, k, seg_begin, seg_end, strands, algo,
+                                     C.byref(hits), C.byref(n_hits), C.byref(st)))
+        try:
+            if n_hits.value:
+                buf = (C.c_char * (n_hits.value * HIT_DTYPE.itemsize)).from_address(hits.value)
+                arr = np.frombuffer(buf, dtype=HIT_DTYPE).copy()
+            else:
+                arr = np.zeros(0, dtype=HIT_DTYPE)
+        finally:
+            self.lib.dp_free(hits)
+        stats = {f: getattr(st, f) for f, _ in dp_scan_stats._fields_}
+        return arr, stats
+
+    # ---- thermodynamics ----------------------------------------------------------
+    def load_tables(self, tables, key=None):
+        if key is not None and key == self._tables_key:
+            return
+        self._check(self.lib.dp_tables_load(self._h, C.byref(tables)))
+        self._tables_key = key
+
+    def duplex_dg(self, template, hits, primer_lens, var_counts, var_offsets, variants, cond):
+        """hits: HIT_DTYPE array grouped by primer.  Returns (DIMER_DTYPE array, stats)."""
+        hits = np.ascontiguousarray(hits, dtype=HIT_DTYPE)
+        pl = np.ascontiguousarray(primer_lens, dtype=np.uint8)
+        vc = np.ascontiguousarray(var_counts, dtype=np.uint32)
+        vo = np.ascontiguousarray(var_offsets, dtype=np.uint64)
+        vb = variants if isinstance(variants, bytes) else variants.encode('ascii')
+        out, n_out, st = C.c_void_p(), C.c_uint64(), dp_dg_stats()
+        self._check(self.lib.dp_duplex_dg(self._h, template._h, _ptr(hits), len(hits), len(pl), _ptr(pl),
+                                          _ptr(vc), _ptr(vo), C.cast(C.c_char_p(vb), C.c_void_p),
+                                          C.byref(cond), C.byref(out), C.byref(n_out), C.byref(st)))
+        try:
+            if n_out.value:
+                buf = (C.c_char * (n_out.value * DIMER_DTYPE.itemsize)).from_address(out.value)
+                arr = np.frombuffer(buf, dtype=DIMER_DTYPE).copy()
+            else:
+                arr = np.zeros(0, dtype=DIMER_DTYPE)
+        finally:
+            self.lib.dp_free(out)
+        stats = {f: getattr(st, f) for f, _ in dp_dg_stats._fields_}
+        return arr, stats
+
+    def variant_tm(self, seqs, concentration, cond, conversion_degree=0.5):
+        n = len(seqs)
+        if n == 0:
+            return np.zeros(0)
+        L = len(seqs[0])
+        blob = ''.join(seqs).encode('ascii')
+        tm = np.zeros(n, dtype=np.float64)
+        self._check(self.lib.dp_variant_tm(self._h, n, L, C.cast(C.c_char_p(blob), C.c_void_p),
+                                           float(concentration), float(conversion_degree),
+                                           C.byref(cond), _ptr(tm)))
+        return tm
+
+    def dimer_dg(self, seqs1, seqs2, masks, offsets, cond):
+        n = len(seqs1)
+        s1 = ''.join(seqs1).encode('ascii')
+        s2 = ''.join(seqs2).encode('ascii')
+        l1 = np.array([len(s) for s in seqs1], dtype=np.uint8)
+        l2 = np.array([len(s) for s in seqs2], dtype=np.uint8)
+        o1 = np.concatenate(([0], np.cumsum(l1, dtype=np.uint64)[:-1])).astype(np.uint64)
+        o2 = np.concatenate(([0], np.cumsum(l2, dtype=np.uint64)[:-1])).astype(np.uint64)
+        mk = np.ascontiguousarray(masks, dtype=np.uint64)
+        of = np.ascontiguousarray(offsets, dtype=np.int32)
+        out = np.zeros(n, dtype=np.float64)
+        self._check(self.lib.dp_dimer_dg(self._h, n, C.cast(C.c_char_p(s1), C.c_void_p), _ptr(o1), _ptr(l1),
+                                         C.cast(C.c_char_p(s2), C.c_void_p), _ptr(o2), _ptr(l2),
+                                         _ptr(mk), _ptr(of), C.byref(cond), _ptr(out)))
+        return out
+
+
+_contexts = {}
+
+
+def context(device=None):
+    """Process-wide context per device, created on first use (after any fork)."""
+    if device is None:
+        device = int(os.environ.get('DEGENPRIMER_B200_DEVICE', os.environ.get('LOCAL_RANK', '0')))
+    key = (os.getpid(), device)
+    ctx = _contexts.get(key)
+    if ctx is None:
+        ctx = Context(device)
+        _contexts[key] = ctx
+    return ctx

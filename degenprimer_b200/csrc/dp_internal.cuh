@@ -1,0 +1,133 @@
+// Internal declarations shared by the translation units of libdegenprimer_b200.
+// Nothing in here is part of the ABI (include/degenprimer_b200.h is).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/degenprimer_b200.h"
+
+// ---- letters -----------------------------------------------------------------
+// 2-bit plane code: A=0 C=1 T=2 G=3  (hi = ASCII bit 2, lo = ASCII bit 1).
+// Letter index: A C T G R Y S W K M B D H V N  (0..14); 15 = not a DNA letter.
+#define DP_LETTERS "ACTGRYSWKMBDHVN"
+#define DP_NOT_A_LETTER 15
+
+// One maximal run of a single non-ACGT letter, in padded-concatenation coords.
+struct dp_exc_run {
+  uint64_t start;
+  uint64_t end;      // exclusive
+  uint32_t letter;   // letter index 4..14, or DP_NOT_A_LETTER for record padding
+  uint32_t pad;
+};
+
+struct dp_record {
+  uint64_t start;    // first base in the padded concatenation (multiple of 32)
+  uint64_t len;
+  std::string id;
+  std::string descr;
+};
+
+struct dp_template {
+  dp_ctx* ctx;
+  uint64_t n_words;            // plane words that hold record data
+  uint64_t n_words_alloc;      // + tail guard so kernels may read i+1, i+2, i+3
+  uint32_t* d_lo;
+  uint32_t* d_hi;
+  uint32_t* d_exc;
+  std::vector<dp_record> records;
+  uint64_t total_bases;
+  // record table on the device: start[r], len[r]
+  uint64_t* d_rec_start;
+  uint64_t* d_rec_len;
+  // exception runs, sorted by start (host + device)
+  std::vector<dp_exc_run> runs;
+  dp_exc_run* d_runs;
+  uint64_t device_bytes;
+};
+
+struct dp_ctx {
+  int device;
+  cudaStream_t stream;
+  cudaEvent_t ev0, ev1, ev2;
+  int sm_count;
+  int cc_major, cc_minor;
+  volatile int abort_flag;
+  bool tables_loaded;
+  dp_nn_tables* d_tables;      // device copy
+  // scan scratch
+  void* d_hits;                // raw hit records
+  uint64_t hits_cap;
+  unsigned long long* d_counters;   // [0]=hits [1]=candidates [2]=overflow ...
+  // pinned staging for uploads
+  char* h_stage[2];
+  char* d_stage[2];
+  cudaEvent_t stage_ev[2];
+  size_t stage_bytes;
+  std::string err;
+};
+
+int dp_set_error(dp_ctx* ctx, int code, const char* fmt, ...);
+
+#define DP_CUDA(ctx, call)                                                     \
+  do {                                                                         \
+    cudaError_t e__ = (call);                                                  \
+    if (e__ != cudaSuccess)                                                    \
+      return dp_set_error((ctx), DP_ERR_CUDA, "%s failed at %s:%d: %s", #call, \
+                          __FILE__, __LINE__, cudaGetErrorString(e__));        \
+  } while (0)
+
+// letter index of an ASCII byte (case-folded), DP_NOT_A_LETTER if foreign
+__host__ __device__ inline uint32_t dp_letter_of(unsigned char c) {
+  switch (c & 0xDF) {
+    case 'A': return 0;  case 'C': return 1;  case 'T': return 2;  case 'G': return 3;
+    case 'R': return 4;  case 'Y': return 5;  case 'S': return 6;  case 'W': return 7;
+    case 'K': return 8;  case 'M': return 9;  case 'B': return 10; case 'D': return 11;
+    case 'H': return 12; case 'V': return 13; case 'N': return 14;
+    default: return DP_NOT_A_LETTER;
+  }
+}
+
+// 4-bit base set of a letter: bit c set <=> plane code c is in the expansion
+// (DegenPrimer/SeqUtils.py:30-40).  A=1 C=2 T=4 G=8.
+__host__ __device__ inline uint32_t dp_letter_set(uint32_t letter) {
+  const uint32_t A = 1, C = 2, T = 4, G = 8;
+  switch (letter) {
+    case 0: return A;  case 1: return C;  case 2: return T;  case 3: return G;
+    case 4: return A | G;      // R
+    case 5: return C | T;      // Y
+    case 6: return G | C;      // S
+    case 7: return A | T;      // W
+    case 8: return G | T;      // K
+    case 9: return A | C;      // M
+    case 10: return C | G | T; // B
+    case 11: return A | G | T; // D
+    case 12: return A | C | T; // H
+    case 13: return A | C | G; // V
+    case 14: return A | C | G | T;
+    default: return 0;
+  }
+}
+
+// complement of a letter index (DegenPrimer/SecStructures.py:34-48)
+__host__ __device__ inline uint32_t dp_letter_complement(uint32_t l) {
+  // A C T G R Y S W K M B D H V N -> T G A C Y R S W M K V H D B N
+  const unsigned char m[16] = {2, 3, 0, 1, 5, 4, 6, 7, 9, 8, 13, 12, 11, 10, 14, 15};
+  return m[l & 15];
+}
+
+// deterministic 2-bit filler for non-ACGT positions, so that exception runs
+// look like random sequence to the prefilter instead of a homopolymer
+__host__ __device__ inline uint32_t dp_filler(uint64_t pos) {
+  uint64_t x = pos * 0x9E3779B97F4A7C15ull;
+  x ^= x >> 29;
+  x *= 0xBF58476D1CE4E5B9ull;
+  return (uint32_t)(x >> 62);
+}
+
+// host helpers implemented in dp_template.cu / dp_scan.cu
+int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
+                       const char* const* seqs, const uint64_t* lens);

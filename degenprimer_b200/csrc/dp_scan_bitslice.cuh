@@ -1,0 +1,285 @@
+// Scan kernel 2: bit-sliced prefilter over 32 windows at once + exact verify.
+//
+// Idea.  A window can only be a hit if a J-letter stretch of
+// the pattern ("anchor", chosen per pattern by the host) has at most K hard
+// mismatches, K = L - max(1, L-k).  That necessary condition is evaluated for
+// 32 consecutive windows per thread with word-wide logic only:
+//   * per plane word the thread builds the 4*J one-hot planes
+//       X_j[b] = (base at 32w+b+j == X),  X in A C T G, j < J
+//     (2 funnel shifts + 4 LOP3 per j) and parks them in its private column of
+//     shared memory;
+//   * a pattern is then just a list of NT plane slots (one per allowed base of
+//     each anchor letter, padded with an all-zero plane); the number of
+//     matching anchor positions is the bit-sliced sum of those planes (a
+//     carry-save adder tree of LOP3 full adders), and `alive` = sum >= J-K;
+//   * only alive windows (p ~ 4e-5 on random sequence) reach the exact
+//     thirds-weighted popcount verify.
+// Cost per (32 windows x pattern): NT LDS.32 + ~1.5*NT LOP3, no POPC, versus
+// 32 x (3 LOP3 + POPC + compare) for kernel 1.
+// Windows that touch a non-ACGT base are left to kernel 1 (only_exc mode).
+#pragma once
+#include <math.h>
+
+#include "dp_scan.cuh"
+
+#define DP_BS_THREADS 256
+#define DP_BS_MAX_K 4
+#define DP_BS_MAX_E 8
+#define DP_BS_MAX_TERMS (8 + 2 * DP_BS_MAX_K + DP_BS_MAX_E)
+
+struct dp_bs_pattern {
+  uint32_t term[DP_BS_MAX_TERMS];   // byte offset of the plane column
+  uint32_t anchor;                  // offset of the anchor inside the pattern
+  uint32_t pattern;                 // index into c_patterns
+};
+
+__constant__ dp_bs_pattern c_bs[DP_MAX_PATTERNS];
+
+struct dp_bitslice_plan {
+  int K, E;
+  uint32_t n;                       // patterns handled by the prefilter
+  uint64_t pmask[2];                // the same set as a bit mask over c_patterns
+  std::vector<dp_bs_pattern> pats;
+};
+
+// ---- bit-sliced population count of N one-bit planes ----------------------------
+template <int N>
+struct dp_level {
+  // Reduces N same-weight words to one; writes floor(N/2) next-weight carries.
+  __device__ __forceinline__ static uint32_t run(const uint32_t* in, uint32_t* c) {
+    if constexpr (N == 1) {
+      return in[0];
+    } else if constexpr (N == 2) {
+      c[0] = in[0] & in[1];
+      return in[0] ^ in[1];
+    } else {
+      constexpr int G = N / 3, R = N % 3;
+      uint32_t s[G + R];
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        uint32_t a = in[3 * g], b = in[3 * g + 1], d = in[3 * g + 2];
+        s[g] = a ^ b ^ d;
+        c[g] = (a & b) | (d & (a | b));
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) s[G + r] = in[3 * G + r];
+      return dp_level<G + R>::run(s, c + G);
+    }
+  }
+};
+
+// bits[] receives the binary count of the N planes; returns number of bits
+template <int N, int B>
+struct dp_count {
+  __device__ __forceinline__ static void run(const uint32_t* in, uint32_t* bits) {
+    if constexpr (N == 0) {
+      return;
+    } else {
+      uint32_t c[N / 2 + 1];
+      bits[B] = dp_level<N>::run(in, c);
+      dp_count<N / 2, B + 1>::run(c, bits);
+    }
+  }
+};
+
+__host__ __device__ constexpr int dp_bits_for(int n) { return n == 0 ? 0 : 1 + dp_bits_for(n / 2); }
+
+// word of windows whose plane count is >= THR
+template <int N, int THR>
+__device__ __forceinline__ uint32_t dp_count_ge(const uint32_t* in) {
+  constexpr int NB = dp_bits_for(N);
+  uint32_t bits[NB];
+  dp_count<N, 0>::run(in, bits);
+  uint32_t ge = 0u, eq = ~0u;
+#pragma unroll
+  for (int b = NB - 1; b >= 0; --b) {
+    if ((THR >> b) & 1) {
+      eq &= bits[b];
+    } else {
+      ge |= eq & bits[b];
+      eq &= ~bits[b];
+    }
+  }
+  return ge | eq;
+}
+
+template <int K, int E>
+__global__ void __launch_bounds__(DP_BS_THREADS, 3)
+dp_scan_bitslice_kernel(dp_scan_args A, uint32_t n_bs) {
+  constexpr int J = 8 + 2 * K;
+  constexpr int NT = J + E;
+  constexpr int THR = J - K;
+  extern __shared__ uint32_t dp_bs_smem[];
+  uint32_t* col = dp_bs_smem + threadIdx.x;
+  col[4 * J * DP_BS_THREADS] = 0u;               // the all-zero padding plane
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t w_end = A.word_end + 2;          // anchors sit up to 63 bases into the window
+  unsigned long long n_cand = 0;
+  for (uint64_t w = A.word_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < w_end; w += stride) {
+    const uint32_t h0 = __ldg(A.hi + w), h1 = __ldg(A.hi + w + 1);
+    const uint32_t l0 = __ldg(A.lo + w), l1 = __ldg(A.lo + w + 1);
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      const uint32_t hs = __funnelshift_r(h0, h1, j);
+      const uint32_t ls = __funnelshift_r(l0, l1, j);
+      col[(4 * j + 0) * DP_BS_THREADS] = ~hs & ~ls;   // A
+      col[(4 * j + 1) * DP_BS_THREADS] = ~hs & ls;    // C
+      col[(4 * j + 2) * DP_BS_THREADS] = hs & ~ls;    // T
+      col[(4 * j + 3) * DP_BS_THREADS] = hs & ls;     // G
+    }
+#pragma unroll 1
+    for (uint32_t p = 0; p < n_bs; ++p) {
+      const dp_bs_pattern& bp = c_bs[p];
+      uint32_t x[NT];
+#pragma unroll
+      for (int t = 0; t < NT; ++t)
+        x[t] = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(col) + bp.term[t]);
+      uint32_t alive = dp_count_ge<NT, THR>(x);
+      while (alive) {
+        const int b = __ffs(alive) - 1;
+        alive &= alive - 1;
+        ++n_cand;
+        const uint64_t q = w * 32 + b;
+        if (q < bp.anchor) continue;
+        const uint64_t g = q - bp.anchor;
+        if (g < A.seg_begin || g >= A.seg_end) continue;
+        const dp_pattern& P = c_patterns[bp.pattern];
+        const uint64_t wi = g >> 5;
+        const int sh = (int)(g & 31);
+        uint32_t whi[2], wlo[2], wex[2];
+        {
+          const uint32_t a0 = __ldg(A.hi + wi), a1 = __ldg(A.hi + wi + 1), a2 = __ldg(A.hi + wi + 2);
+          whi[0] = __funnelshift_r(a0, a1, sh); whi[1] = __funnelshift_r(a1, a2, sh);
+          const uint32_t b0 = __ldg(A.lo + wi), b1 = __ldg(A.lo + wi + 1), b2 = __ldg(A.lo + wi + 2);
+          wlo[0] = __funnelshift_r(b0, b1, sh); wlo[1] = __funnelshift_r(b1, b2, sh);
+          const uint32_t e0 = __ldg(A.exc + wi), e1 = __ldg(A.exc + wi + 1), e2 = __ldg(A.exc + wi + 2);
+          wex[0] = __funnelshift_r(e0, e1, sh); wex[1] = __funnelshift_r(e1, e2, sh);
+        }
+        if ((wex[0] & P.lmask[0]) | (wex[1] & P.lmask[1])) continue;   // kernel 1 (only_exc) owns it
+        const uint32_t s = dp_score3<2>(P, whi, wlo, wex);
+        if (s >= P.thr3) dp_emit_hit(A, g, bp.pattern, P.len, s);
+      }
+    }
+  }
+  if (n_cand) atomicAdd(&A.counters[1], n_cand);
+}
+
+// ---- host: anchor choice -----------------------------------------------------------
+// probability that a random ACGT stretch has <= K hard mismatches against the
+// J letters starting at `o` (match probability |set|/4 per position)
+static double dp_bs_alive_probability(const std::vector<uint8_t>& letters, int o, int J, int K) {
+  std::vector<double> d(K + 2, 0.0);   // d[m] = P(m mismatches so far), m = K+1 absorbs "more"
+  d[0] = 1.0;
+  for (int j = 0; j < J; ++j) {
+    double pm = __builtin_popcount(dp_letter_set(letters[o + j])) / 4.0;
+    for (int m = K + 1; m >= 0; --m) {
+      double stay = d[m] * pm;
+      double from = m > 0 ? d[m - 1] * (1.0 - pm) : 0.0;
+      if (m == K + 1) stay = d[m];   // absorbing
+      d[m] = stay + from;
+    }
+  }
+  double s = 0.0;
+  for (int m = 0; m <= K; ++m) s += d[m];
+  return s;
+}
+
+// Decides which patterns take the prefilter.  Returns false if none does.
+static bool dp_bitslice_make_plan(const std::vector<dp_pattern>& pats,
+                                  const std::vector<std::vector<uint8_t>>& letters,
+                                  dp_bitslice_plan& plan) {
+  plan.n = 0;
+  plan.pmask[0] = plan.pmask[1] = 0;
+  plan.pats.clear();
+  // K of each pattern; the launch takes the most frequent one
+  std::vector<int> Ks(pats.size());
+  int votes[DP_BS_MAX_K + 1] = {0};
+  for (size_t p = 0; p < pats.size(); ++p) {
+    int need = (pats[p].thr3 + 1) / 3;
+    Ks[p] = pats[p].len - need;
+    if (Ks[p] >= 0 && Ks[p] <= DP_BS_MAX_K && pats[p].len >= 8 + 2 * Ks[p]) ++votes[Ks[p]];
+  }
+  int K = -1, best = 0;
+  for (int k = 0; k <= DP_BS_MAX_K; ++k)
+    if (votes[k] > best) { best = votes[k]; K = k; }
+  if (K < 0) return false;
+  const int J = 8 + 2 * K;
+  int E = 0;
+  struct Choice { int o, terms; };
+  std::vector<Choice> choice(pats.size(), Choice{-1, 0});
+  for (size_t p = 0; p < pats.size(); ++p) {
+    if (Ks[p] != K || pats[p].len < J) continue;
+    const std::vector<uint8_t>& lt = letters[p];
+    double best_p = 2.0;
+    int best_o = -1, best_terms = 0;
+    for (int o = 0; o + J <= (int)pats[p].len; ++o) {
+      int terms = 0;
+      for (int j = 0; j < J; ++j) terms += __builtin_popcount(dp_letter_set(lt[o + j]));
+      if (terms > J + DP_BS_MAX_E) continue;
+      double pa = dp_bs_alive_probability(lt, o, J, K);
+      if (pa < best_p - 1e-15 || (fabs(pa - best_p) <= 1e-15 && terms < best_terms)) {
+        best_p = pa; best_o = o; best_terms = terms;
+      }
+    }
+    if (best_o < 0 || best_p > 2e-3) continue;   // too unselective: kernel 1 is cheaper
+    choice[p] = Choice{best_o, best_terms};
+    E = std::max(E, best_terms - J);
+  }
+  E = E == 0 ? 0 : E <= 2 ? 2 : E <= 4 ? 4 : 8;
+  const int NT = J + E;
+  for (size_t p = 0; p < pats.size(); ++p) {
+    if (choice[p].o < 0) continue;
+    dp_bs_pattern bp;
+    memset(&bp, 0, sizeof bp);
+    bp.anchor = (uint32_t)choice[p].o;
+    bp.pattern = (uint32_t)p;
+    int n = 0;
+    for (int j = 0; j < J; ++j) {
+      uint32_t set = dp_letter_set(letters[p][choice[p].o + j]);
+      for (int c = 0; c < 4; ++c)
+        if (set & (1u << c)) bp.term[n++] = (uint32_t)((4 * j + c) * DP_BS_THREADS * sizeof(uint32_t));
+    }
+    for (; n < NT; ++n) bp.term[n] = (uint32_t)(4 * J * DP_BS_THREADS * sizeof(uint32_t));
+    plan.pats.push_back(bp);
+    plan.pmask[p >> 6] |= 1ull << (p & 63);
+  }
+  plan.K = K;
+  plan.E = E;
+  plan.n = (uint32_t)plan.pats.size();
+  return plan.n > 0;
+}
+
+template <int K, int E>
+static int dp_bitslice_launch_one(dp_ctx* ctx, const dp_scan_args& A, uint32_t n_bs) {
+  constexpr int J = 8 + 2 * K;
+  const size_t smem = (size_t)(4 * J + 1) * DP_BS_THREADS * sizeof(uint32_t);
+  static bool configured = false;
+  if (!configured) {
+    DP_CUDA(ctx, cudaFuncSetAttribute(dp_scan_bitslice_kernel<K, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const uint64_t words = A.word_end + 2 - A.word_begin;
+  int per_sm = 1;
+  DP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_scan_bitslice_kernel<K, E>, DP_BS_THREADS, smem));
+  if (per_sm < 1) per_sm = 1;
+  unsigned blocks = (unsigned)std::min<uint64_t>((words + DP_BS_THREADS - 1) / DP_BS_THREADS,
+                                                 (uint64_t)ctx->sm_count * per_sm);
+  dp_scan_bitslice_kernel<K, E><<<blocks, DP_BS_THREADS, smem, ctx->stream>>>(A, n_bs);
+  DP_CUDA(ctx, cudaGetLastError());
+  return DP_OK;
+}
+
+static int dp_bitslice_launch(dp_ctx* ctx, const dp_scan_args& A, const dp_bitslice_plan& plan, uint32_t* launches) {
+  DP_CUDA(ctx, cudaMemcpyToSymbolAsync(c_bs, plan.pats.data(), plan.pats.size() * sizeof(dp_bs_pattern), 0,
+                                       cudaMemcpyHostToDevice, ctx->stream));
+  int rc = DP_ERR_ARG;
+#define DP_BS_CASE(KK, EE) \
+  if (plan.K == KK && plan.E == EE) rc = dp_bitslice_launch_one<KK, EE>(ctx, A, plan.n);
+#define DP_BS_ROW(KK) DP_BS_CASE(KK, 0) DP_BS_CASE(KK, 2) DP_BS_CASE(KK, 4) DP_BS_CASE(KK, 8)
+  DP_BS_ROW(0) DP_BS_ROW(1) DP_BS_ROW(2) DP_BS_ROW(3) DP_BS_ROW(4)
+#undef DP_BS_ROW
+#undef DP_BS_CASE
+  if (rc == DP_ERR_ARG) return dp_set_error(ctx, DP_ERR_STATE, "internal: no bit-slice kernel for K=%d E=%d", plan.K, plan.E);
+  if (rc == DP_OK) ++*launches;
+  return rc;
+}

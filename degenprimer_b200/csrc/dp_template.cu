@@ -1,0 +1,492 @@
+// Template loader: ASCII / FASTA -> three bit-planes resident in HBM.
+//
+// Replaces BioUtils/BioUtils/SeqUtils.py:103-271 (SeqView over SeqIO.index_db)
+// and the str()/upper()/reverse_complement() host copies of
+// DegenPrimer/SearchEngine.py:287-290,333-336.  The ASCII bytes are streamed to
+// the device through two pinned staging buffers (or straight from the caller's
+// buffer when that is already pinned) and packed there; the host never touches
+// a base twice.
+#include <algorithm>
+#include <stdlib.h>
+#include <string.h>
+
+#include "dp_internal.cuh"
+
+#define DP_PAD_BYTE 0xFFu
+#define DP_STAGE_BYTES (16u << 20)   // per staging buffer, multiple of 32
+#define DP_GUARD_WORDS 8             // readable plane words past the data
+
+// ---- pack kernel --------------------------------------------------------------
+// One thread packs 32 consecutive bases into one word of each plane.
+//   src        chunk of ASCII, src[0] is base 32*word0 of the padded layout
+//   n_valid    bytes of src that exist; everything after is padding
+//   prev_byte  the byte in front of src[0] (DP_PAD_BYTE at the very start)
+//   bounds     class-change list: entry = pos*16 + class, class 0 = ACGT,
+//              4..14 = IUPAC letter index, 15 = padding
+//   counters   [0] entries wanted (may exceed cap), [1] min position of a
+//              byte outside the alphabet (init UINT64_MAX)
+__device__ __forceinline__ uint32_t base_class(uint32_t c) {
+  if (c == DP_PAD_BYTE) return 15u;
+  uint32_t u = c & 0xDFu;
+  if (u == 'A' || u == 'C' || u == 'G' || u == 'T') return 0u;
+  uint32_t l = dp_letter_of((unsigned char)c);
+  return l == DP_NOT_A_LETTER ? 16u : l;   // 16 = foreign byte
+}
+
+__global__ void __launch_bounds__(256)
+dp_pack_kernel(const uint8_t* __restrict__ src, uint64_t n_valid, uint64_t n_words,
+               uint64_t word0, uint32_t prev_byte,
+               uint32_t* __restrict__ lo, uint32_t* __restrict__ hi, uint32_t* __restrict__ exc,
+               unsigned long long* __restrict__ bounds, uint64_t bounds_cap,
+               unsigned long long* __restrict__ counters) {
+  uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= n_words) return;
+  uint64_t i0 = w * 32;
+  uint32_t bytes[8];
+  if (i0 + 32 <= n_valid) {
+    const uint4* p = reinterpret_cast<const uint4*>(src + i0);
+    uint4 a = __ldg(p), b = __ldg(p + 1);
+    bytes[0] = a.x; bytes[1] = a.y; bytes[2] = a.z; bytes[3] = a.w;
+    bytes[4] = b.x; bytes[5] = b.y; bytes[6] = b.z; bytes[7] = b.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      uint32_t v = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint64_t idx = i0 + 4 * k + j;
+        uint32_t c = idx < n_valid ? src[idx] : DP_PAD_BYTE;
+        v |= c << (8 * j);
+      }
+      bytes[k] = v;
+    }
+  }
+  uint32_t pc = (i0 == 0) ? prev_byte : (i0 - 1 < n_valid ? (uint32_t)src[i0 - 1] : DP_PAD_BYTE);
+  uint32_t prev_cls = base_class(pc);
+  if (prev_cls == 16u) prev_cls = 15u;
+  uint32_t wl = 0, wh = 0, we = 0;
+  uint64_t g0 = (word0 + w) * 32;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int b = 4 * k + j;
+      uint32_t c = (bytes[k] >> (8 * j)) & 0xFFu;
+      uint32_t cls = base_class(c);
+      uint32_t code;
+      if (cls == 0u) {
+        code = (c >> 1) & 3u;
+      } else {
+        if (cls == 16u) {
+          atomicMin(&counters[1], (unsigned long long)(g0 + b));
+          cls = 15u;
+        }
+        code = dp_filler(g0 + b);
+        we |= 1u << b;
+      }
+      wl |= (code & 1u) << b;
+      wh |= (code >> 1) << b;
+      if (cls != prev_cls) {
+        unsigned long long slot = atomicAdd(&counters[0], 1ull);
+        if (slot < bounds_cap) bounds[slot] = (unsigned long long)(g0 + b) * 16ull + cls;
+        prev_cls = cls;
+      }
+    }
+  }
+  lo[word0 + w] = wl;
+  hi[word0 + w] = wh;
+  exc[word0 + w] = we;
+}
+
+__global__ void dp_fill_guard_kernel(uint32_t* lo, uint32_t* hi, uint32_t* exc, uint64_t from, uint64_t to) {
+  uint64_t w = from + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < to) { lo[w] = 0; hi[w] = 0; exc[w] = 0xFFFFFFFFu; }
+}
+
+// ---- unpack kernel ------------------------------------------------------------
+__device__ __forceinline__ uint32_t dp_run_letter(const dp_exc_run* runs, uint64_t n_runs, uint64_t g) {
+  uint64_t a = 0, b = n_runs;            // last run with start <= g
+  while (a < b) {
+    uint64_t m = (a + b) >> 1;
+    if (runs[m].start <= g) a = m + 1; else b = m;
+  }
+  if (a == 0) return 14u;
+  const dp_exc_run& r = runs[a - 1];
+  return g < r.end ? r.letter : 14u;
+}
+
+__global__ void dp_unpack_kernel(const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi,
+                                 const uint32_t* __restrict__ exc, const dp_exc_run* __restrict__ runs,
+                                 uint64_t n_runs, uint64_t rec_start, uint64_t rec_len,
+                                 uint64_t begin, uint64_t n, int reverse, char* __restrict__ out) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint64_t p = reverse ? rec_len - 1 - (begin + i) : begin + i;
+  uint64_t g = rec_start + p;
+  uint32_t w = (uint32_t)(g & 31);
+  uint64_t wi = g >> 5;
+  uint32_t letter;
+  if ((exc[wi] >> w) & 1u) letter = dp_run_letter(runs, n_runs, g);
+  else letter = ((hi[wi] >> w) & 1u) * 2u + ((lo[wi] >> w) & 1u);
+  if (reverse) letter = dp_letter_complement(letter);
+  out[i] = DP_LETTERS[letter];
+}
+
+// ---- host side ------------------------------------------------------------------
+static int ensure_stage(dp_ctx* ctx) {
+  if (ctx->stage_bytes) return DP_OK;
+  for (int i = 0; i < 2; ++i) {
+    DP_CUDA(ctx, cudaMallocHost(&ctx->h_stage[i], DP_STAGE_BYTES));
+    DP_CUDA(ctx, cudaMalloc(&ctx->d_stage[i], DP_STAGE_BYTES));
+    DP_CUDA(ctx, cudaEventCreateWithFlags(&ctx->stage_ev[i], cudaEventDisableTiming));
+  }
+  ctx->stage_bytes = DP_STAGE_BYTES;
+  return DP_OK;
+}
+
+static bool is_pinned(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost;
+}
+
+static void free_template_device(dp_template* t) {
+  if (t->d_lo) cudaFree(t->d_lo);
+  if (t->d_hi) cudaFree(t->d_hi);
+  if (t->d_exc) cudaFree(t->d_exc);
+  if (t->d_rec_start) cudaFree(t->d_rec_start);
+  if (t->d_rec_len) cudaFree(t->d_rec_len);
+  if (t->d_runs) cudaFree(t->d_runs);
+  t->d_lo = t->d_hi = t->d_exc = nullptr;
+  t->d_rec_start = t->d_rec_len = nullptr;
+  t->d_runs = nullptr;
+}
+
+// Streams the records of `t` (layout already decided: t->records[r].start/len)
+// to the device and packs them.  One attempt with a given boundary capacity.
+static int pack_once(dp_ctx* ctx, dp_template* t, const char* const* seqs, uint64_t bounds_cap,
+                     unsigned long long* d_bounds, unsigned long long* h_counters) {
+  const uint32_t n_records = (uint32_t)t->records.size();
+  unsigned long long init[2] = {0ull, ~0ull};
+  DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  int slot = 0;
+  bool slot_used[2] = {false, false};
+  // (a) pinned sources: copy straight from the caller's buffer, one record at a time
+  // (b) pageable sources: gather bytes at their padded offsets into a pinned chunk
+  uint64_t chunk_word0 = 0;       // padded word offset of the current gather chunk
+  size_t chunk_fill = 0;          // bytes placed so far (padded layout)
+  uint32_t chunk_prev = DP_PAD_BYTE;
+  char* hbuf = nullptr;
+  auto flush_gather = [&](void) -> int {
+    if (!chunk_fill) return DP_OK;
+    size_t n_bytes = (chunk_fill + 31) & ~(size_t)31;
+    memset(hbuf + chunk_fill, DP_PAD_BYTE, n_bytes - chunk_fill);
+    uint32_t last = (unsigned char)hbuf[n_bytes - 1];
+    DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage[slot], hbuf, n_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    uint64_t nw = n_bytes / 32;
+    dp_pack_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, ctx->stream>>>(
+        (const uint8_t*)ctx->d_stage[slot], n_bytes, nw, chunk_word0, chunk_prev,
+        t->d_lo, t->d_hi, t->d_exc, d_bounds, bounds_cap, ctx->d_counters);
+    DP_CUDA(ctx, cudaGetLastError());
+    DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
+    slot_used[slot] = true;
+    chunk_word0 += nw;
+    chunk_fill = 0;
+    chunk_prev = last;
+    slot ^= 1;
+    hbuf = nullptr;
+    return DP_OK;
+  };
+  auto acquire = [&](void) -> int {
+    if (slot_used[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[slot]));
+    hbuf = ctx->h_stage[slot];
+    return DP_OK;
+  };
+  for (uint32_t r = 0; r < n_records; ++r) {
+    if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+    const dp_record& rec = t->records[r];
+    const char* src = seqs[r];
+    uint64_t rec_words = (rec.len + 31) / 32;
+    if (rec.len >= (1u << 20) && is_pinned(src)) {
+      int rc = flush_gather();
+      if (rc) return rc;
+      // device-side chunks straight from the pinned source
+      uint64_t done = 0;
+      uint32_t prev = DP_PAD_BYTE;
+      while (done < rec.len) {
+        uint64_t n = std::min<uint64_t>(DP_STAGE_BYTES, rec.len - done);
+        if (slot_used[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[slot]));
+        DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage[slot], src + done, n, cudaMemcpyHostToDevice, ctx->stream));
+        uint64_t nw = (n + 31) / 32;
+        dp_pack_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, ctx->stream>>>(
+            (const uint8_t*)ctx->d_stage[slot], n, nw, rec.start / 32 + done / 32, prev,
+            t->d_lo, t->d_hi, t->d_exc, d_bounds, bounds_cap, ctx->d_counters);
+        DP_CUDA(ctx, cudaGetLastError());
+        DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
+        slot_used[slot] = true;
+        slot ^= 1;
+        prev = (unsigned char)src[done + n - 1];
+        done += n;
+      }
+      chunk_word0 = rec.start / 32 + rec_words;
+      chunk_prev = DP_PAD_BYTE;
+      continue;
+    }
+    // gather path
+    if (chunk_fill == 0) { chunk_word0 = rec.start / 32; }
+    uint64_t done = 0;
+    while (done < rec.len || (rec.len == 0 && done == 0)) {
+      if (!hbuf) { int rc = acquire(); if (rc) return rc; }
+      // position of the next byte inside the chunk (padded layout)
+      size_t at = (size_t)((rec.start + done) - chunk_word0 * 32);
+      if (at > chunk_fill) { memset(hbuf + chunk_fill, DP_PAD_BYTE, at - chunk_fill); chunk_fill = at; }
+      size_t room = DP_STAGE_BYTES - chunk_fill;
+      size_t n = (size_t)std::min<uint64_t>(room, rec.len - done);
+      memcpy(hbuf + chunk_fill, src + done, n);
+      chunk_fill += n;
+      done += n;
+      if (chunk_fill == DP_STAGE_BYTES) { int rc = flush_gather(); if (rc) return rc; }
+      if (rec.len == 0) break;
+    }
+  }
+  {
+    if (chunk_fill && !hbuf) return dp_set_error(ctx, DP_ERR_STATE, "internal: gather buffer lost");
+    int rc = flush_gather();
+    if (rc) return rc;
+  }
+  uint64_t guard_to = t->n_words_alloc;
+  uint64_t nguard = guard_to - t->n_words;
+  dp_fill_guard_kernel<<<(unsigned)((nguard + 255) / 256), 256, 0, ctx->stream>>>(t->d_lo, t->d_hi, t->d_exc, t->n_words, guard_to);
+  DP_CUDA(ctx, cudaGetLastError());
+  DP_CUDA(ctx, cudaMemcpyAsync(h_counters, ctx->d_counters, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return DP_OK;
+}
+
+int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
+                       const char* const* seqs, const uint64_t* lens) {
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = ensure_stage(ctx);
+  if (rc) return rc;
+  // layout: every record starts on a word boundary
+  uint64_t w = 0;
+  t->total_bases = 0;
+  for (uint32_t r = 0; r < n_records; ++r) {
+    t->records[r].start = w * 32;
+    t->records[r].len = lens[r];
+    w += (lens[r] + 31) / 32;
+    t->total_bases += lens[r];
+  }
+  t->n_words = w;
+  t->n_words_alloc = w + DP_GUARD_WORDS;
+  size_t plane_bytes = (size_t)t->n_words_alloc * sizeof(uint32_t);
+  DP_CUDA(ctx, cudaMalloc(&t->d_lo, plane_bytes));
+  DP_CUDA(ctx, cudaMalloc(&t->d_hi, plane_bytes));
+  DP_CUDA(ctx, cudaMalloc(&t->d_exc, plane_bytes));
+  t->device_bytes = 3 * plane_bytes;
+
+  uint64_t cap = std::max<uint64_t>(1u << 16, t->total_bases / 64);
+  std::vector<unsigned long long> bounds;
+  for (int attempt = 0;; ++attempt) {
+    unsigned long long* d_bounds = nullptr;
+    DP_CUDA(ctx, cudaMalloc(&d_bounds, cap * sizeof(unsigned long long)));
+    unsigned long long h_counters[2] = {0, 0};
+    rc = pack_once(ctx, t, seqs, cap, d_bounds, h_counters);
+    if (rc) { cudaFree(d_bounds); return rc; }
+    if (h_counters[1] != ~0ull) {
+      cudaFree(d_bounds);
+      uint64_t g = h_counters[1];
+      uint32_t r = 0;
+      while (r + 1 < n_records && t->records[r + 1].start <= g) ++r;
+      uint64_t off = g - t->records[r].start;
+      unsigned char c = off < lens[r] ? (unsigned char)seqs[r][off] : 0;
+      return dp_set_error(ctx, DP_ERR_ALPHABET, "record %u offset %llu: byte 0x%02x ('%c') is not an IUPAC DNA letter",
+                          r, (unsigned long long)off, c, (c >= 32 && c < 127) ? c : '?');
+    }
+    if (h_counters[0] > cap) {
+      if (attempt) { cudaFree(d_bounds); return dp_set_error(ctx, DP_ERR_STATE, "internal: boundary list overflow twice"); }
+      cudaFree(d_bounds);
+      cap = h_counters[0];
+      continue;
+    }
+    bounds.resize(h_counters[0]);
+    if (!bounds.empty())
+      DP_CUDA(ctx, cudaMemcpy(bounds.data(), d_bounds, bounds.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    cudaFree(d_bounds);
+    break;
+  }
+  std::sort(bounds.begin(), bounds.end());
+  bounds.push_back((unsigned long long)(t->n_words * 32) * 16ull);   // sentinel closes an open run
+  t->runs.clear();
+  for (size_t i = 0; i + 1 < bounds.size(); ++i) {
+    uint32_t cls = (uint32_t)(bounds[i] & 15ull);
+    if (cls == 0u || cls == 15u) continue;
+    dp_exc_run run;
+    run.start = bounds[i] >> 4;
+    run.end = bounds[i + 1] >> 4;
+    run.letter = cls;
+    run.pad = 0;
+    if (run.end > run.start) t->runs.push_back(run);
+  }
+  size_t nr = t->runs.size();
+  DP_CUDA(ctx, cudaMalloc(&t->d_runs, std::max<size_t>(1, nr) * sizeof(dp_exc_run)));
+  if (nr) DP_CUDA(ctx, cudaMemcpy(t->d_runs, t->runs.data(), nr * sizeof(dp_exc_run), cudaMemcpyHostToDevice));
+  std::vector<uint64_t> starts(n_records), rl(n_records);
+  for (uint32_t r = 0; r < n_records; ++r) { starts[r] = t->records[r].start; rl[r] = t->records[r].len; }
+  DP_CUDA(ctx, cudaMalloc(&t->d_rec_start, std::max<size_t>(1, n_records) * sizeof(uint64_t)));
+  DP_CUDA(ctx, cudaMalloc(&t->d_rec_len, std::max<size_t>(1, n_records) * sizeof(uint64_t)));
+  if (n_records) {
+    DP_CUDA(ctx, cudaMemcpy(t->d_rec_start, starts.data(), n_records * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    DP_CUDA(ctx, cudaMemcpy(t->d_rec_len, rl.data(), n_records * sizeof(uint64_t), cudaMemcpyHostToDevice));
+  }
+  t->device_bytes += nr * sizeof(dp_exc_run) + 2 * n_records * sizeof(uint64_t);
+  return DP_OK;
+}
+
+static dp_template* new_template(dp_ctx* ctx, uint32_t n_records) {
+  dp_template* t = new dp_template();
+  t->ctx = ctx;
+  t->n_words = t->n_words_alloc = 0;
+  t->d_lo = t->d_hi = t->d_exc = nullptr;
+  t->d_rec_start = t->d_rec_len = nullptr;
+  t->d_runs = nullptr;
+  t->total_bases = 0;
+  t->device_bytes = 0;
+  t->records.resize(n_records);
+  return t;
+}
+
+extern "C" {
+
+int dp_template_from_records(dp_ctx* ctx, uint32_t n_records, const char* const* seqs,
+                             const uint64_t* lens, dp_template** out) {
+  if (!ctx || !out || (n_records && (!seqs || !lens))) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *out = nullptr;
+  dp_template* t = new_template(ctx, n_records);
+  for (uint32_t r = 0; r < n_records; ++r) {
+    char name[32];
+    snprintf(name, sizeof name, "record_%u", r);
+    t->records[r].id = name;
+  }
+  int rc = dp_upload_and_pack(ctx, t, n_records, seqs, lens);
+  if (rc) { free_template_device(t); delete t; return rc; }
+  *out = t;
+  return DP_OK;
+}
+
+int dp_template_from_ascii(dp_ctx* ctx, const char* seq, uint64_t len, dp_template** out) {
+  const char* seqs[1] = {seq};
+  uint64_t lens[1] = {len};
+  return dp_template_from_records(ctx, 1, seqs, lens, out);
+}
+
+int dp_template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out) {
+  if (!ctx || !path || !out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *out = nullptr;
+  FILE* fh = fopen(path, "rb");
+  if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot open %s", path);
+  fseek(fh, 0, SEEK_END);
+  long fsize = ftell(fh);
+  fseek(fh, 0, SEEK_SET);
+  std::string data;
+  data.resize(fsize > 0 ? (size_t)fsize : 0);
+  if (fsize > 0 && fread(&data[0], 1, (size_t)fsize, fh) != (size_t)fsize) {
+    fclose(fh);
+    return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
+  }
+  fclose(fh);
+  struct Rec { std::string id, descr, seq; };
+  std::vector<Rec> recs;
+  size_t p = 0, n = data.size();
+  while (p < n) {
+    size_t eol = data.find('\n', p);
+    if (eol == std::string::npos) eol = n;
+    size_t end = eol;
+    while (end > p && (data[end - 1] == '\r' || data[end - 1] == ' ' || data[end - 1] == '\t')) --end;
+    if (end > p && data[p] == '>') {
+      Rec r;
+      r.descr = data.substr(p + 1, end - p - 1);
+      size_t sp = r.descr.find_first_of(" \t");
+      r.id = sp == std::string::npos ? r.descr : r.descr.substr(0, sp);
+      recs.push_back(r);
+    } else if (end > p && !recs.empty()) {
+      std::string& s = recs.back().seq;
+      for (size_t i = p; i < end; ++i) {
+        char c = data[i];
+        if (c != ' ' && c != '\t') s.push_back(c);
+      }
+    }
+    p = eol + 1;
+  }
+  data.clear();
+  data.shrink_to_fit();
+  if (recs.empty()) return dp_set_error(ctx, DP_ERR_IO, "no FASTA records in %s", path);
+  std::sort(recs.begin(), recs.end(), [](const Rec& a, const Rec& b) { return a.id < b.id; });
+  for (size_t i = 1; i < recs.size(); ++i)
+    if (recs[i].id == recs[i - 1].id) return dp_set_error(ctx, DP_ERR_ARG, "duplicate record id '%s' in %s", recs[i].id.c_str(), path);
+  uint32_t nr = (uint32_t)recs.size();
+  std::vector<const char*> seqs(nr);
+  std::vector<uint64_t> lens(nr);
+  dp_template* t = new_template(ctx, nr);
+  for (uint32_t r = 0; r < nr; ++r) {
+    seqs[r] = recs[r].seq.data();
+    lens[r] = recs[r].seq.size();
+    t->records[r].id = recs[r].id;
+    t->records[r].descr = recs[r].descr;
+  }
+  int rc = dp_upload_and_pack(ctx, t, nr, seqs.data(), lens.data());
+  if (rc) { free_template_device(t); delete t; return rc; }
+  *out = t;
+  return DP_OK;
+}
+
+void dp_template_free(dp_template* t) {
+  if (!t) return;
+  if (t->ctx) { cudaSetDevice(t->ctx->device); cudaStreamSynchronize(t->ctx->stream); }
+  free_template_device(t);
+  delete t;
+}
+
+int dp_template_get_info(const dp_template* t, dp_template_info* info) {
+  if (!t || !info) return DP_ERR_ARG;
+  info->n_records = (uint32_t)t->records.size();
+  info->reserved = 0;
+  info->total_bases = t->total_bases;
+  info->padded_bases = t->n_words * 32;
+  info->n_exception_runs = t->runs.size();
+  info->device_bytes = t->device_bytes;
+  return DP_OK;
+}
+
+int dp_template_record(const dp_template* t, uint32_t r, uint64_t* start, uint64_t* len,
+                       const char** id, const char** descr) {
+  if (!t || r >= t->records.size()) return DP_ERR_ARG;
+  const dp_record& rec = t->records[r];
+  if (start) *start = rec.start;
+  if (len) *len = rec.len;
+  if (id) *id = rec.id.c_str();
+  if (descr) *descr = rec.descr.c_str();
+  return DP_OK;
+}
+
+int dp_template_unpack(dp_ctx* ctx, const dp_template* t, uint32_t r, uint64_t begin, uint64_t n,
+                       int reverse, char* out) {
+  if (!ctx || !t || !out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (r >= t->records.size()) return dp_set_error(ctx, DP_ERR_ARG, "record %u out of range", r);
+  const dp_record& rec = t->records[r];
+  if (begin > rec.len || n > rec.len - begin) return dp_set_error(ctx, DP_ERR_ARG, "range outside record");
+  if (n == 0) return DP_OK;
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  char* d_out = nullptr;
+  DP_CUDA(ctx, cudaMalloc(&d_out, n));
+  dp_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(
+      t->d_lo, t->d_hi, t->d_exc, t->d_runs, t->runs.size(), rec.start, rec.len, begin, n, reverse, d_out);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, n, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d_out);
+  if (e != cudaSuccess) return dp_set_error(ctx, DP_ERR_CUDA, "unpack: %s", cudaGetErrorString(e));
+  return DP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,258 @@
+/* degenprimer_b200 — C ABI of the B200-native DegenPrimer hot path.
+ *
+ * The reference (allista/DegenPrimer, pure Python 2.7) has no FFI layer; the
+ * boundary it offers is the Python API of DegenPrimer/SearchEngine.py as called
+ * from DegenPrimer/PCR_ProductsFinder.py:36,74,88,100,118-120.  This header is
+ * the thin C-ABI the Python facade (degenprimer_b200/SearchEngine.py) binds with
+ * ctypes; every entry point names the reference code it replaces.
+ *
+ * Conventions
+ *   - every function returns DP_OK (0) or a negative DP_ERR_* code;
+ *     dp_last_error(ctx) holds the message of the last failure on that ctx.
+ *   - one dp_ctx per host thread; a ctx owns one CUDA stream and is NOT
+ *     re-entrant.  The CUDA context is created inside dp_create(), i.e. in the
+ *     calling process (never before a fork — SURVEY §7 "CUDA + Manager").
+ *   - result arrays returned through `T** out` are malloc()ed by the library
+ *     and released with dp_free().
+ *   - no torch / C++ types cross this boundary: plain pointers and sizes only.
+ *   - there is no CPU implementation behind these calls: without a usable
+ *     sm_100 device dp_create() fails.
+ *
+ * Base encoding in HBM: three bit-planes, one uint32 word per
+ * 32 bases each, bit b of word i = base 32*i+b.  hi = ASCII bit 2, lo = ASCII
+ * bit 1 (A=00 C=01 T=10 G=11, complement = flip hi); exc = 1 for every byte
+ * outside ACGT (IUPAC codes, record padding).  Exception letters live in a
+ * sorted run table.
+ */
+#ifndef DEGENPRIMER_B200_H
+#define DEGENPRIMER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DP_ABI_VERSION 1
+
+enum {
+  DP_OK = 0,
+  DP_ERR_CUDA = -1,        /* a CUDA runtime call failed / no usable device     */
+  DP_ERR_ARG = -2,         /* bad argument                                        */
+  DP_ERR_ALPHABET = -3,    /* byte outside the IUPAC DNA alphabet: the reference */
+                           /* raises KeyError in reverse_complement()            */
+                           /* (DegenPrimer/SecStructures.py:50-55)               */
+  DP_ERR_LENGTH = -4,      /* template shorter than primer / empty primer:       */
+                           /* ValueError of SearchEngine.py:232-238              */
+  DP_ERR_UNSUPPORTED = -5, /* primer longer than DP_MAX_PRIMER_LEN               */
+  DP_ERR_IO = -6,          /* cannot read a FASTA file                            */
+  DP_ERR_NOMEM = -7,
+  DP_ERR_ABORTED = -8,     /* abort flag was raised (reference returns None)     */
+  DP_ERR_STATE = -9        /* tables not loaded, template freed, ...             */
+};
+
+#define DP_MAX_PRIMER_LEN 64   /* configs use 18-35 nt                          */
+#define DP_MAX_PRIMERS    64   /* masters per dp_scan call (x2 strands)         */
+
+typedef struct dp_ctx dp_ctx;
+typedef struct dp_template dp_template;
+
+/* ---- context --------------------------------------------------------------- */
+int dp_abi_version(void);
+int dp_device_count(int* n);
+/* Creates the CUDA context on `device_ordinal`.  NULL on failure; the reason is
+ * returned by dp_create_error(). */
+dp_ctx* dp_create(int device_ordinal);
+const char* dp_create_error(void);
+void dp_destroy(dp_ctx* ctx);
+const char* dp_last_error(const dp_ctx* ctx);
+void dp_free(void* p);
+/* Cooperative abort (BioUtils/Tools/AbortableBase.py:16-35): once raised, the
+ * next kernel-launch boundary returns DP_ERR_ABORTED.  Returns previous flag. */
+int dp_abort_requested(dp_ctx* ctx, int flag);
+/* Device properties for the bench / roofline (name is a 256-byte buffer). */
+int dp_device_info(dp_ctx* ctx, char* name, int* sm_count, int* cc_major,
+                   int* cc_minor, int* clock_khz, uint64_t* hbm_bytes);
+
+/* ---- template loader: FASTA / ASCII -> bit-planes in HBM ---------------------
+ * Replaces BioUtils/BioUtils/SeqUtils.py:103-271 (SeqView over
+ * Bio.SeqIO.index_db) + the str(template.seq) / reverse_complement() copies of
+ * DegenPrimer/SearchEngine.py:287-290,333-336.  Input is case-folded like
+ * SeqView(upper=True) (DegenPrimer/iPCR_Base.py:47-52). */
+int dp_template_from_records(dp_ctx* ctx, uint32_t n_records,
+                             const char* const* seqs, const uint64_t* lens,
+                             dp_template** out);
+int dp_template_from_ascii(dp_ctx* ctx, const char* seq, uint64_t len,
+                           dp_template** out);
+/* Parses every record of a FASTA file; records are stored sorted by id, like
+ * SeqView._ids (BioUtils/BioUtils/SeqUtils.py:170). */
+int dp_template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out);
+void dp_template_free(dp_template* t);
+
+typedef struct dp_template_info {
+  uint32_t n_records;
+  uint32_t reserved;
+  uint64_t total_bases;      /* sum of record lengths                           */
+  uint64_t padded_bases;     /* 32 * number of plane words                      */
+  uint64_t n_exception_runs; /* maximal runs of one non-ACGT letter             */
+  uint64_t device_bytes;     /* HBM held by this template                       */
+} dp_template_info;
+int dp_template_get_info(const dp_template* t, dp_template_info* info);
+/* Record r: offset of its first base in the padded concatenation (multiple of
+ * 32), its length, its id / description (NUL-terminated, owned by `t`). */
+int dp_template_record(const dp_template* t, uint32_t r, uint64_t* start,
+                       uint64_t* len, const char** id, const char** descr);
+/* Decode bases [begin, begin+n) of record r back to upper-case ASCII
+ * (n bytes, no NUL).  reverse!=0 returns the same stretch of the
+ * reverse-complement strand, i.e. reverse_complement(record)[begin:begin+n]. */
+int dp_template_unpack(dp_ctx* ctx, const dp_template* t, uint32_t r,
+                       uint64_t begin, uint64_t n, int reverse, char* out);
+
+/* ---- scan: mismatch-tolerant annealing-site search ----------------------------
+ * Replaces SearchEngine._find / _find_mp / _find_in_slice / _find_in_chunk
+ * (DegenPrimer/SearchEngine.py:190-211,257-359): for every master primer and
+ * both strands, every window whose thirds-weighted score reaches
+ * 3*max(1, L-k)-1 (the integer form of `score >= max(1,L-k)-0.5`).
+ *
+ * A hit is reported in the coordinates the reference uses:
+ *   strand 0: pos = 0-based window start on the record (fwd_matches)
+ *   strand 1: pos = 0-based window start on reverse_complement(record)
+ *             (rev_matches) = record_len - L - forward_start
+ * Hits come back sorted by (primer, strand, record, pos).
+ */
+typedef struct dp_hit {
+  uint64_t pos;
+  uint32_t record;
+  uint16_t primer;   /* index into `masters`                                    */
+  uint8_t strand;    /* 0 forward, 1 reverse                                     */
+  uint8_t score3;    /* 3 * reference score (exact integer)                      */
+} dp_hit;
+
+enum { DP_STRAND_FWD = 1, DP_STRAND_REV = 2, DP_STRAND_BOTH = 3 };
+enum {
+  DP_ALGO_AUTO = 0,
+  DP_ALGO_POPC = 1,     /* per-window XOR/AND + popcount                        */
+  DP_ALGO_BITSLICE = 2  /* bit-sliced prefilter over 32 windows + exact verify  */
+};
+
+typedef struct dp_scan_stats {
+  uint64_t windows;        /* window x pattern pairs examined                    */
+  uint64_t candidates;     /* pairs that reached the exact verify stage          */
+  uint64_t hits;
+  float ms_scan;           /* CUDA-event time of the scan kernel(s)              */
+  float ms_total;          /* incl. hit download and sort                        */
+  uint32_t launches;       /* kernels launched by this call                      */
+  uint32_t algo;           /* DP_ALGO_* actually used                            */
+} dp_scan_stats;
+
+/* seg_begin/seg_end restrict window STARTS to [seg_begin, seg_end) of the
+ * padded concatenation (multi-GPU sharding); pass 0, UINT64_MAX for
+ * everything.  `stats` may be NULL. */
+int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
+            const char* const* masters, const int32_t* max_mismatches,
+            uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
+            dp_hit** hits, uint64_t* n_hits, dp_scan_stats* stats);
+
+/* ---- duplex thermodynamics ---------------------------------------------------
+ * Tables: DegenPrimer/UnifiedNN.py:208-246 + data/internal-NN.csv, loops.csv,
+ * dangling-ends.csv, flattened by the host (degenprimer_b200/UnifiedNN.py).
+ * 2-bit base index everywhere = the plane code: A=0 C=1 T=2 G=3.
+ * Letter index (15 letters): A C T G R Y S W K M B D H V N.
+ */
+typedef struct dp_nn_tables {
+  /* stack[x][y][w] = int_dPar_37(seq = X Y, rev = comp(X) W): dH, dS
+   * (DegenPrimer/TD_Functions.py:187-191).  x = primer[a], y = primer[a+1]
+   * (bases), w = letter of the 3'->5' complement strand under primer[a+1]
+   * (15 letters; ambiguous -> expansion average, UnifiedNN.py:231-245). */
+  double stack_dH[4][4][15];
+  double stack_dS[4][4][15];
+  /* rstack[x][y][w] = int_dPar_37(seq = comp(Y) W, rev = Y X): the right-hand
+   * stack of |x| and |xx| (DegenPrimer/TD_Functions.py:193-197).
+   * x = primer[b-1], y = primer[b], w = complement-strand letter under
+   * primer[b-1]. */
+  double rstack_dH[4][4][15];
+  double rstack_dS[4][4][15];
+  /* dangling ends (DegenPrimer/UnifiedNN.py:248-252): [kind][x][y][z],
+   * kind 0 = "XY/-Z", kind 1 = "XY/Z-"; NaN where the table has no row. */
+  double dangling_dH[2][4][4][4];
+  double dangling_dS[2][4][4][4];
+  /* internal_loop_dS_37 for a loop of n unpaired bases per strand, n=0..63
+   * (DegenPrimer/UnifiedNN.py:264-276,317-319). */
+  double loop_dS[64];
+  double ini_dH, ini_dS, ter_dH, ter_dS;
+  double terminal_mismatch;   /* -0.72, DegenPrimer/UnifiedNN.py:139            */
+  double dS_Na;               /* 0.368                                           */
+  double R;                   /* 1.9872                                          */
+  double K0;                  /* -273.15                                         */
+  double T_DMSO;              /* 0.75                                            */
+} dp_nn_tables;
+int dp_tables_load(dp_ctx* ctx, const dp_nn_tables* tables);
+
+/* PCR conditions read by the hot path (DegenPrimer/PCR_Parameters.py:66-97). */
+typedef struct dp_conditions {
+  double PCR_T;        /* Celsius                                                */
+  double Na_eq_log;    /* ln(Na + sqrt(14.4*(Mg-dNTP)))                          */
+  double max_dimer_dG; /* keep dimers with dG <= this (-3)                       */
+  double max_dG_for_K; /* largest dG whose exp(-1000 dG / (R (T-K0))) >= min_K,  */
+                       /* found by the host with the same libm exp()             */
+  double DNA;          /* mol/L, only for dp_variant_tm                          */
+  double DMSO;         /* %,    only for dp_variant_tm                           */
+} dp_conditions;
+
+/* One surviving dimer of one (site, variant) duplex — Dimer of
+ * DegenPrimer/SecStructures.py:58-192 after Duplex._recalculate :294-324. */
+typedef struct dp_dimer {
+  uint32_t hit;         /* index into the `hits` array passed in                */
+  uint32_t variant;     /* index into the primer's variant list                 */
+  uint64_t match_mask;  /* bit i = primer index i is paired (fwd_matches)       */
+  double dG;            /* kcal/mol at PCR_T                                    */
+} dp_dimer;
+
+typedef struct dp_dg_stats {
+  uint64_t duplexes;     /* (site, variant) pairs evaluated                      */
+  uint64_t dimers_tried; /* dimers whose dG was computed                         */
+  uint64_t dimers_kept;
+  float ms_kernel;
+  float ms_total;
+  uint32_t launches;
+  uint32_t reserved;
+} dp_dg_stats;
+
+/* Replaces SearchEngine._compile_duplexes_for_position + Duplex.__init__ /
+ * _recalculate + Dimer.from_sequences / alternatives + dimer_dG_corrected
+ * (DegenPrimer/SearchEngine.py:106-118, SecStructures.py:126-152,231-324,
+ * TD_Functions.py:124-206) for every hit x every unambiguous variant of the
+ * hit's primer.
+ *   variants: all variants of all primers, concatenated, variant v of primer p
+ *   is the primer_len[p] bytes at variants + var_offset[p] + v*primer_len[p];
+ *   var_count[p] variants each.
+ * Dimers come back grouped by (hit, variant) in input order, each group sorted
+ * by dG ascending, ties in the reference's construction order (stable sort,
+ * SecStructures.py:314). */
+int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hits,
+                 uint64_t n_hits, uint32_t n_primers, const uint8_t* primer_len,
+                 const uint32_t* var_count, const uint64_t* var_offset,
+                 const char* variants, const dp_conditions* cond,
+                 dp_dimer** dimers, uint64_t* n_dimers, dp_dg_stats* stats);
+
+/* Per-variant perfect-match Tr/Tm — TD_Functions.primer_template_Tr
+ * (DegenPrimer/TD_Functions.py:60-101) for `n` sequences of length `len`
+ * stored back to back; `concentration` is per variant (Primer.py:180-186),
+ * conversion_degree in (0,1): 0.5 gives Tm. */
+int dp_variant_tm(dp_ctx* ctx, uint32_t n, uint32_t len, const char* seqs,
+                  double concentration, double conversion_degree,
+                  const dp_conditions* cond, double* tm);
+
+/* dimer_dG_corrected for arbitrary dimers (offset != 0, unequal lengths:
+ * dangling ends reachable) — DegenPrimer/TD_Functions.py:124-206.
+ * Dimer i: seq1 = s1 + off1[i] (len1[i] bytes, 5'->3'), seq2 likewise,
+ * match_mask over seq1 indices, offset as in SecStructures.Dimer. */
+int dp_dimer_dg(dp_ctx* ctx, uint32_t n, const char* s1, const uint64_t* off1,
+                const uint8_t* len1, const char* s2, const uint64_t* off2,
+                const uint8_t* len2, const uint64_t* match_mask,
+                const int32_t* offset, const dp_conditions* cond, double* dG);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEGENPRIMER_B200_H */

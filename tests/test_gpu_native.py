@@ -1,0 +1,162 @@
+"""GPU parity of the C-ABI against the oracle (run on the B200 box: -m gpu)."""
+import numpy as np
+import pytest
+
+from oracle import search_o1 as o1
+from oracle import search_o2 as o2
+from oracle import conditions as ocond
+from oracle.primer import Primer as OPrimer, SeqRecord as OSeqRecord
+from oracle.sequtils import reverse_complement
+
+from tests.util import random_dna, plant_sites
+
+pytestmark = pytest.mark.gpu
+
+PRIMERS = ['ATATTCTACRACGGCTATCC', 'GAASGCRAAKATYGGGAAC',      # Test_SearchEngine.py:77-78
+           'ATARTCTYCGAMGGCTATCC', 'NAAGGYTTAGAKGCGGAAG']        # Test_Product.py:28-29
+
+
+def split_hits(hits, primer):
+    h = hits[hits['primer'] == primer]
+    return h[h['strand'] == 0]['pos'].astype(np.int64), h[h['strand'] == 1]['pos'].astype(np.int64)
+
+
+@pytest.mark.parametrize('algo', [1, 2])
+@pytest.mark.parametrize('k', [0, 1, 3, 6])
+def test_scan_matches_oracle(ctx, algo, k):
+    rng = np.random.default_rng(100 + k)
+    t = random_dna(rng, 60000)
+    t, _ = plant_sites(rng, t, PRIMERS, min(k, 4), 12)
+    tmpl = ctx.template_from_sequences([t])
+    assert tmpl.unpack() == t
+    assert tmpl.unpack(reverse=True) == reverse_complement(t)
+    hits, stats = ctx.scan(tmpl, PRIMERS, k, algo=algo)
+    total = 0
+    for i, m in enumerate(PRIMERS):
+        ref = o2.find(t, m, k)
+        f, r = split_hits(hits, i)
+        assert np.array_equal(f, ref[4]), (m, 'fwd')
+        assert np.array_equal(r, ref[5]), (m, 'rev')
+        total += len(f) + len(r)
+    assert total == len(hits) and total > 0
+
+
+@pytest.mark.parametrize('algo', [1, 2])
+def test_scan_with_iupac_template_and_fft_oracle(ctx, algo):
+    rng = np.random.default_rng(7)
+    t = random_dna(rng, 30000, 'ACGTNRYSWKMBDHV', p=[0.23] * 4 + [0.08 / 11] * 11)
+    t, _ = plant_sites(rng, t, PRIMERS[:2], 2, 10)
+    t = t[:5000] + 'N' * 300 + t[5300:]
+    tmpl = ctx.template_from_sequences([t])
+    assert tmpl.unpack() == t
+    assert tmpl.unpack(reverse=True) == reverse_complement(t)
+    for k in (2, 5, 12):
+        hits, _ = ctx.scan(tmpl, PRIMERS[:2], k, algo=algo)
+        for i, m in enumerate(PRIMERS[:2]):
+            ref = o1.find_serial(t, m, k)          # literal FFT restatement
+            f, r = split_hits(hits, i)
+            assert np.array_equal(f, ref[4]) and np.array_equal(r, ref[5]), (k, m)
+
+
+def test_multi_record_and_segments(ctx):
+    rng = np.random.default_rng(11)
+    recs = [random_dna(rng, n) for n in (3000, 64, 20, 4097, 19, 1)]
+    recs[0], _ = plant_sites(rng, recs[0], PRIMERS[:1], 1, 4)
+    recs[3], _ = plant_sites(rng, recs[3], PRIMERS[:1], 1, 4)
+    recs[2] = 'ATATTCTACAACGGCTATCC'                  # exactly one window
+    tmpl = ctx.template_from_sequences(recs)
+    assert tmpl.n_records == len(recs)
+    for r, s in enumerate(recs):
+        assert tmpl.unpack(r) == s
+    m = PRIMERS[0]
+    hits, _ = ctx.scan(tmpl, [m], 1)
+    for r, s in enumerate(recs):
+        h = hits[hits['record'] == r]
+        if len(s) < len(m):
+            assert len(h) == 0
+            continue
+        ref = o2.find(s, m, 1)
+        assert np.array_equal(h[h['strand'] == 0]['pos'].astype(np.int64), ref[4])
+        assert np.array_equal(h[h['strand'] == 1]['pos'].astype(np.int64), ref[5])
+    # sharding by window-start segment reproduces the whole
+    cut = tmpl.starts[3] + 2000
+    a, _ = ctx.scan(tmpl, [m], 1, 0, cut)
+    b, _ = ctx.scan(tmpl, [m], 1, cut, 2 ** 64 - 1)
+    both = np.sort(np.concatenate([a, b]), order=['primer', 'strand', 'record', 'pos'])
+    assert np.array_equal(both, hits)
+
+
+def test_errors(ctx):
+    with pytest.raises(KeyError):
+        ctx.template_from_sequences(['ACGTXACGT'])
+    tmpl = ctx.template_from_sequences(['ACGTACGT'])
+    with pytest.raises(ValueError):
+        ctx.scan(tmpl, ['ACGTACGTACGT'], 1)
+    with pytest.raises(ValueError):
+        ctx.scan(tmpl, [''], 1)
+
+
+def _oracle_dimers(t, master, k, cond):
+    ocond.PCR_P.set(cond)
+    p = OPrimer(OSeqRecord(master, id='p'), 1e-6)
+    m = o2.find(t, master, k)
+    res = o1.compile_duplexes(m[0], m[1], p, m[2], m[3], m[4], m[5], mp_order=True)
+    return p, m, res
+
+
+@pytest.mark.parametrize('master,k', [('GAASGCRAAKATYGGGAAC', 3), ('ATATTCTACRACGGCTATCC', 2),
+                                      ('NAAGGYTTAGAKGCGGAAG', 4)])
+def test_duplex_dg_matches_oracle(ctx, master, k):
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200.SeqUtils import unambiguous_sequences
+    rng = np.random.default_rng(5)
+    t = random_dna(rng, 20000, 'ACGTN', p=[0.2495] * 4 + [0.002])
+    t, _ = plant_sites(rng, t, [master], k, 20)
+    cond = dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=55.0)
+    p, m, ref = _oracle_dimers(t, master, k, cond)
+    tdf.PCR_P.set(cond)
+    tmpl = ctx.template_from_sequences([t])
+    hits, _ = ctx.scan(tmpl, [master], k)
+    variants = unambiguous_sequences(master)
+    L = len(master)
+    dimers, stats = ctx.duplex_dg(tmpl, hits, [L], [len(variants)], [0], ''.join(variants), tdf.conditions())
+    # oracle -> flat list of (strand, pos0, variant, mask, dG)
+    want = []
+    vid = {v: i for i, v in enumerate(variants)}
+    for strand, results in enumerate(ref):
+        for pos, dups in results:
+            for d in dups:
+                for dm in d.dimers:
+                    mask = sum(1 << i for i in dm.fwd_matches)
+                    want.append((strand, pos, vid[d.fwd_seq], mask, dm.dG))
+    got = []
+    T = len(t)
+    for d in dimers:
+        h = hits[d['hit']]
+        pos = int(h['pos']) + L if h['strand'] == 0 else T + 1 - (int(h['pos']) + L)
+        got.append((int(h['strand']), pos, int(d['variant']), int(d['match_mask']), float(d['dG'])))
+    assert len(got) == len(want) and len(got) > 0
+    key = lambda x: (x[0], x[1], x[2])
+    assert sorted(map(key, got)) == sorted(map(key, want))
+    # same grouping and the same in-group order (stable sort by dG)
+    got_s = sorted(range(len(got)), key=lambda i: (key(got[i]), i))
+    want_s = sorted(range(len(want)), key=lambda i: (key(want[i]), i))
+    for gi, wi in zip(got_s, want_s):
+        assert got[gi][:4] == want[wi][:4]
+        assert abs(got[gi][4] - want[wi][4]) <= 1e-9, (got[gi], want[wi])   # bar: 0.01 kcal/mol
+    assert max(abs(got[g][4] - want[w][4]) for g, w in zip(got_s, want_s)) == 0.0   # in fact bit-exact
+
+
+def test_variant_tm_matches_oracle(ctx):
+    from degenprimer_b200 import TD_Functions as tdf
+    cond = dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, DMSO=2.0, PCR_T=62.0)
+    ocond.PCR_P.set(cond)
+    tdf.PCR_P.set(cond)
+    p = OPrimer(OSeqRecord('ATARTCTYCGAMGGCNATKCAGGNCTGRGGA', id='p'), 1.5e-6)   # Test_Primer.py:30
+    assert p.calculate_Tms()
+    from oracle import thermo
+    want = np.array([thermo.primer_template_Tm(s, p.concentration) for s in p.str_sequences])
+    got = tdf.primer_template_Tms(p.str_sequences, p.concentration)
+    assert got.shape == want.shape
+    assert np.max(np.abs(got - want)) <= 0.05     # bar from BASELINE.json north_star
+    assert np.max(np.abs(got - want)) <= 1e-9
