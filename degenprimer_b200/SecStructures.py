@@ -1,0 +1,326 @@
+"""Dimer / Duplex result objects — host mirror of DegenPrimer/SecStructures.py:58-192,223-387.
+
+The scan path never builds these in bulk: the device returns structure-of-arrays
+dimer records (site, variant, match mask, dG) and `SiteDuplexes` materialises
+`Duplex` / `Dimer` objects only when a consumer touches them (PCR_Mixture,
+SinglePCR and the reports read `.dimers[i].K`, `.fwd_mismatch`, `.fwd_seq`, ...;
+SURVEY §8b).  Constructing a `Duplex` by hand still works and evaluates its
+dimers on the GPU through `TD_Functions.dimers_dG_corrected`.
+"""
+import numpy as np
+
+from . import TD_Functions as tdf
+from .SeqUtils import reverse_complement, rc_map   # noqa: F401  (rc_map re-exported like the reference)
+
+max_dimer_dG = tdf.max_dimer_dG      # -3 kcal/mol, SecStructures.py:30
+max_hairpin_dG = 3                   # SecStructures.py:31
+min_K = tdf.min_K                    # 100, SecStructures.py:32
+
+
+def mask_to_matches(mask):
+    mask = int(mask)
+    out = []
+    i = 0
+    while mask:
+        if mask & 1:
+            out.append(i)
+        mask >>= 1
+        i += 1
+    return tuple(out)
+
+
+class Dimer(object):
+    """Match-index structure of a dimer without bulges (SecStructures.py:58-192)."""
+    __slots__ = ['fwd_matches', 'offset', 'num_matches', 'conversion_degree', 'dG', 'K', 'fwd_mismatch']
+
+    def __init__(self, fwd_matches=None, offset=0):
+        if fwd_matches:
+            self.fwd_matches = tuple(sorted(fwd_matches))
+            self.offset = offset
+            self.num_matches = len(self.fwd_matches)
+        else:
+            self.fwd_matches = tuple()
+            self.offset = None
+            self.num_matches = 0
+        self.conversion_degree = None
+        self.dG = None
+        self.K = None
+        self.fwd_mismatch = None
+
+    def __hash__(self):
+        return hash((self.fwd_matches, self.offset))
+
+    def __eq__(self, other):
+        return hash(self) == hash(other)
+
+    def __ne__(self, other):
+        return hash(self) != hash(other)
+
+    def __bool__(self):
+        return self.num_matches > 0
+
+    def __getstate__(self):
+        return tuple(getattr(self, s) for s in self.__slots__)
+
+    def __setstate__(self, state):
+        for s, v in zip(self.__slots__, state):
+            setattr(self, s, v)
+
+    rev_matches = property(lambda self: np.array(self.fwd_matches) - self.offset)
+    fwd_min = property(lambda self: self.fwd_matches[0])
+    rev_min = property(lambda self: self.fwd_matches[0] - self.offset)
+    fwd_max = property(lambda self: self.fwd_matches[-1])
+    rev_max = property(lambda self: self.fwd_matches[-1] - self.offset)
+
+    @property
+    def alternatives(self):
+        """Every contiguous range of match runs except the full one, in the
+        reference's order (SecStructures.py:126-152)."""
+        if self.num_matches < 2:
+            return []
+        runs = [[self.fwd_matches[0]]]
+        for a, b in zip(self.fwd_matches, self.fwd_matches[1:]):
+            if b - a > 1:
+                runs.append([])
+            runs[-1].append(b)
+        last = len(runs) - 1
+        out = []
+        for l in range(last):
+            for r in range(last, l, -1):
+                out.append(Dimer([i for run in runs[l:r] for i in run], self.offset))
+            out.append(Dimer([i for run in runs[l + 1:] for i in run], self.offset))
+        return out
+
+    def add(self, fwd, rev):
+        if self.offset is None:
+            self.offset = fwd - rev
+        elif self.offset != fwd - rev:
+            raise ValueError('Dimer.add: fwd and rev indexes should be at the same distance as all '
+                             'other match pairs. Asymmetrical loops are not allowed.')
+        self.fwd_matches = tuple(sorted(self.fwd_matches + (fwd,)))
+        self.num_matches += 1
+
+    @classmethod
+    def from_sequences(cls, forward, revcomp, offset=0):
+        """Left-aligned (or offset) character comparison (SecStructures.py:173-191)."""
+        d = cls()
+        d.offset = offset
+        if offset > 0:
+            rng = range(offset, min(len(forward), len(revcomp) + offset))
+        else:
+            rng = range(0, min(len(forward) - offset, len(revcomp) + offset))
+        d.fwd_matches = tuple(i for i in rng if forward[i] == revcomp[i - offset])
+        d.num_matches = len(d.fwd_matches)
+        return d
+
+
+class Duplex(object):
+    """A DNA:DNA duplex and its stable dimers (SecStructures.py:223-387)."""
+    __slots__ = ['_fwd_sequence', '_rev_sequence', 'fwd_len', 'rev_len', 'name', '_dimers',
+                 '_nonzero', '_fwd_matches', '_fwd_mismatches', 'fwd_3_overhang']
+
+    def __init__(self, fwd_seq, rev_seq, name='', dimer=None, revcomp=False):
+        self.name = name
+        self.fwd_len = len(fwd_seq)
+        self.rev_len = len(rev_seq)
+        self._fwd_sequence = fwd_seq
+        self._rev_sequence = reverse_complement(rev_seq) if revcomp else rev_seq
+        if not dimer:
+            dimer = Dimer.from_sequences(fwd_seq, rev_seq if revcomp else reverse_complement(rev_seq))
+        self._dimers = [dimer] + dimer.alternatives
+        self._fwd_matches = []
+        self._fwd_mismatches = []
+        self.fwd_3_overhang = None
+        self._nonzero = False
+        self._recalculate()
+
+    @classmethod
+    def _from_device(cls, name, fwd_seq, window, masks, dGs, T):
+        """Build from the rows dp_duplex_dg returned for one (site, variant):
+        already filtered (dG <= -3, K >= 100) and stably sorted by dG."""
+        self = cls.__new__(cls)
+        self.name = name
+        self.fwd_len = self.rev_len = len(fwd_seq)
+        self._fwd_sequence = fwd_seq
+        self._rev_sequence = reverse_complement(window)
+        dimers = []
+        for mask, dG in zip(masks, dGs):
+            d = Dimer(mask_to_matches(mask), 0)
+            d.dG = float(dG)
+            d.K = tdf.equilibrium_constant(d.dG, T)
+            d.fwd_mismatch = d.fwd_max < self.fwd_len - 1
+            dimers.append(d)
+        self._dimers = tuple(dimers)
+        self._nonzero = bool(dimers)
+        self._fwd_matches = []
+        self._fwd_mismatches = []
+        self.fwd_3_overhang = None
+        self._index_3_ends()
+        return self
+
+    def _recalculate(self):
+        """SecStructures.py:294-324; dG of all candidate dimers in one launch."""
+        cand = [d for d in self._dimers if d]
+        kept = []
+        if cand:
+            dGs = tdf.dimers_dG_corrected(cand, [self._fwd_sequence] * len(cand),
+                                          [self._rev_sequence] * len(cand))
+            for d, g in zip(cand, dGs):
+                d.dG = float(g)
+                if d.dG > max_dimer_dG:
+                    continue
+                d.K = tdf.equilibrium_constant(d.dG, tdf.PCR_P.PCR_T)
+                if d.K < min_K:
+                    continue
+                d.fwd_mismatch = d.fwd_max < self.fwd_len - 1
+                kept.append(d)
+        self._nonzero = bool(kept)
+        if not self._nonzero:
+            self._dimers = tuple()
+            return
+        self._dimers = tuple(sorted(kept, key=lambda x: x.dG))
+        self._index_3_ends()
+
+    def _index_3_ends(self):
+        if not self._dimers:
+            return
+        fwd_tail = self.fwd_len - 1 - self._dimers[0].fwd_max
+        rev_tail = self.rev_len - 1 - self._dimers[0].rev_max
+        self.fwd_3_overhang = fwd_tail - rev_tail if fwd_tail > rev_tail else 0
+        for i, d in enumerate(self._dimers):
+            (self._fwd_mismatches if d.fwd_max < self.fwd_len - 1 else self._fwd_matches).append(i)
+
+    def __bool__(self):
+        return self._nonzero
+
+    def __hash__(self):
+        return hash((self._fwd_sequence, self._rev_sequence, self._dimers[0]))
+
+    def __eq__(self, other):
+        return hash(self) == hash(other)
+
+    def __ne__(self, other):
+        return hash(self) != hash(other)
+
+    def __getstate__(self):
+        return tuple(getattr(self, s) for s in self.__slots__)
+
+    def __setstate__(self, state):
+        for s, v in zip(self.__slots__, state):
+            setattr(self, s, v)
+
+    fwd_seq = property(lambda self: self._fwd_sequence)
+    rev_seq = property(lambda self: self._rev_sequence)
+    dimer = property(lambda self: self._dimers[0])
+    dimers = property(lambda self: self._dimers)
+    dG = property(lambda self: self._dimers[0].dG)
+    K = property(lambda self: self._dimers[0].K)
+    fwd_3_matches = property(lambda self: [self._dimers[i] for i in self._fwd_matches])
+    fwd_3_mismatches = property(lambda self: [self._dimers[i] for i in self._fwd_mismatches])
+    have_3_matches = property(lambda self: bool(self._fwd_matches))
+
+    def __str__(self):
+        s = '%d variants of annealing sorted by stability:\n' % len(self._dimers)
+        for i, d in enumerate(self._dimers):
+            s += '\n%d:\n' % (i + 1)
+            s += self.print_dimer(self._fwd_sequence, self._rev_sequence, d)
+            s += '\n'
+        return s + '\n'
+
+    __repr__ = __str__
+
+    def print_most_stable(self, include_fwd_3_mismatch=True):
+        s = ''
+        if not self._dimers:
+            return s
+        if not include_fwd_3_mismatch:
+            if self._fwd_matches:
+                return self.print_dimer(self._fwd_sequence, self._rev_sequence,
+                                        self._dimers[self._fwd_matches[0]])
+            s += "There's no annealing variant without 3' mismatches\n"
+        return s + self.print_dimer(self._fwd_sequence, self._rev_sequence, self._dimers[0])
+
+    @classmethod
+    def print_dimer(cls, fwd_sequence, rev_sequence, dimer):
+        """ASCII rendering, SecStructures.py:355-386."""
+        if not dimer:
+            return fwd_sequence + '\n' + rev_sequence[::-1] + '\n'
+        bars = [' '] * len(fwd_sequence)
+        for m in dimer.fwd_matches:
+            bars[m] = '|'
+        bars = ''.join(bars)
+        s = ''
+        if dimer.offset > 0:
+            s += "5' " + fwd_sequence + " 3'\n   " + bars + '\n'
+            s += ' ' * dimer.offset + "3' " + rev_sequence[::-1] + " 5'\n"
+        else:
+            pad = ' ' * abs(dimer.offset) if dimer.offset < 0 else ''
+            s += pad + "5' " + fwd_sequence + " 3'\n   " + pad + bars + '\n'
+            s += "3' " + rev_sequence[::-1] + " 5'\n"
+        if dimer.dG is not None:
+            s += 'dG(%.1fC) = %.2f kcal/mol\n' % (tdf.PCR_P.PCR_T, dimer.dG)
+        if dimer.conversion_degree is not None:
+            s += 'conversion degree = %.4f%%\n' % (dimer.conversion_degree * 100)
+        return s
+
+
+class DuplexTable(object):
+    """Structure-of-arrays result of one dp_duplex_dg call, shared by all sites."""
+
+    def __init__(self, dimers, windows, variants, names, T):
+        self.dimers = dimers        # DIMER_DTYPE rows grouped by (hit, variant)
+        self.windows = windows      # list: hit index -> window string (strand orientation)
+        self.variants = variants    # variant sequences of the primer
+        self.names = names          # variant ids
+        self.T = T                  # PCR_T the rows were computed at
+
+
+class SiteDuplexes(object):
+    """Tuple-like view of the duplexes at one annealing site (the second item of
+    the `(position, duplexes)` pairs of DegenPrimer/SearchEngine.py:106-118)."""
+    __slots__ = ['_table', '_hit', '_lo', '_hi', '_cache']
+
+    def __init__(self, table, hit, lo, hi):
+        self._table, self._hit, self._lo, self._hi = table, hit, lo, hi
+        self._cache = None
+
+    def _materialise(self):
+        if self._cache is None:
+            t = self._table
+            rows = t.dimers[self._lo:self._hi]
+            out = []
+            cut = np.flatnonzero(np.diff(rows['variant'])) + 1
+            for seg in np.split(np.arange(len(rows)), cut):
+                v = int(rows['variant'][seg[0]])
+                out.append(Duplex._from_device(t.names[v], t.variants[v], t.windows[self._hit],
+                                               rows['match_mask'][seg], rows['dG'][seg], t.T))
+            self._cache = tuple(out)
+        return self._cache
+
+    def __len__(self):
+        rows = self._table.dimers['variant'][self._lo:self._hi]
+        return int(np.count_nonzero(np.diff(rows)) + 1) if len(rows) else 0
+
+    def __bool__(self):
+        return self._hi > self._lo
+
+    def __iter__(self):
+        return iter(self._materialise())
+
+    def __getitem__(self, i):
+        return self._materialise()[i]
+
+    def __eq__(self, other):
+        return tuple(self) == tuple(other)
+
+    def __hash__(self):
+        return hash(tuple(self))
+
+    def __add__(self, other):
+        return tuple(self) + tuple(other)
+
+    def __repr__(self):
+        return repr(tuple(self))
+
+    def __reduce__(self):
+        return (tuple, (list(self._materialise()),))

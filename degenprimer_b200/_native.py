@@ -105,6 +105,7 @@ def _declare(lib):
         'dp_tables_load': (i32, [vp, P(dp_nn_tables)]),
         'dp_duplex_dg': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_void_p, P(dp_conditions), P(vp), P(u64), P(dp_dg_stats)]),
+        'dp_hit_windows': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p]),
         'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
         'dp_dimer_dg': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_void_p, P(dp_conditions), C.c_void_p]),
@@ -119,7 +120,7 @@ def _declare(lib):
 EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
-           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_variant_tm dp_dimer_dg').split()
+           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_hit_windows dp_variant_tm dp_dimer_dg').split()
 
 
 def load():
@@ -313,6 +314,18 @@ class Context(object):
             self.lib.dp_free(out)
         stats = {f: getattr(st, f) for f, _ in dp_dg_stats._fields_}
         return arr, stats
+
+    def hit_windows(self, template, hits, primer_lens):
+        """List of window strings, one per hit (strand orientation)."""
+        hits = np.ascontiguousarray(hits, dtype=HIT_DTYPE)
+        pl = np.ascontiguousarray(primer_lens, dtype=np.uint8)
+        out = np.zeros((len(hits), 64), dtype=np.uint8)
+        if len(hits):
+            self._check(self.lib.dp_hit_windows(self._h, template._h, _ptr(hits), len(hits), len(pl),
+                                                _ptr(pl), _ptr(out)))
+        lens = pl[hits['primer']] if len(hits) else []
+        raw = out.tobytes()
+        return [raw[64 * i:64 * i + int(n)].decode('ascii') for i, n in enumerate(lens)]
 
     def variant_tm(self, seqs, concentration, cond, conversion_degree=0.5):
         n = len(seqs)

@@ -405,6 +405,48 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
   return DP_OK;
 }
 
+extern "C" int dp_hit_windows(dp_ctx* ctx, const dp_template* t, const dp_hit* hits, uint64_t n_hits,
+                              uint32_t n_primers, const uint8_t* primer_len, char* out) {
+  if (!ctx || !t || (n_hits && (!hits || !out)) || !primer_len) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (n_hits == 0) return DP_OK;
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::vector<uint64_t> hit_g(n_hits);
+  std::vector<uint8_t> hit_len(n_hits), hit_strand(n_hits);
+  for (uint64_t h = 0; h < n_hits; ++h) {
+    const dp_hit& x = hits[h];
+    if (x.primer >= n_primers || x.record >= t->records.size())
+      return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: primer or record out of range", (unsigned long long)h);
+    const dp_record& rec = t->records[x.record];
+    uint32_t L = primer_len[x.primer];
+    if (L == 0 || L > DP_MAX_PRIMER_LEN || x.pos + L > rec.len)
+      return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: window outside its record", (unsigned long long)h);
+    hit_g[h] = rec.start + (x.strand ? rec.len - L - x.pos : x.pos);
+    hit_len[h] = (uint8_t)L;
+    hit_strand[h] = x.strand ? 1 : 0;
+  }
+  dev_buf<uint64_t> d_g;
+  dev_buf<uint8_t> d_len, d_strand, d_win;
+  DP_CUDA(ctx, d_g.alloc(n_hits));
+  DP_CUDA(ctx, d_len.alloc(n_hits));
+  DP_CUDA(ctx, d_strand.alloc(n_hits));
+  DP_CUDA(ctx, d_win.alloc(n_hits * DP_WIN));
+  cudaStream_t st = ctx->stream;
+  DP_CUDA(ctx, cudaMemcpyAsync(d_g.p, hit_g.data(), n_hits * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_len.p, hit_len.data(), n_hits, cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_strand.p, hit_strand.data(), n_hits, cudaMemcpyHostToDevice, st));
+  uint64_t n = n_hits * DP_WIN;
+  dp_dg_windows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+      t->d_lo, t->d_hi, t->d_exc, t->d_runs, t->runs.size(), d_g.p, d_len.p, d_strand.p, n_hits, d_win.p);
+  DP_CUDA(ctx, cudaGetLastError());
+  DP_CUDA(ctx, cudaMemcpyAsync(out, d_win.p, n, cudaMemcpyDeviceToHost, st));
+  DP_CUDA(ctx, cudaStreamSynchronize(st));
+  for (uint64_t i = 0; i < n; ++i) {
+    unsigned char l = (unsigned char)out[i];
+    out[i] = l < 15 ? DP_LETTERS[l] : 0;
+  }
+  return DP_OK;
+}
+
 extern "C" int dp_variant_tm(dp_ctx* ctx, uint32_t n, uint32_t len, const char* seqs, double concentration,
                              double conversion_degree, const dp_conditions* cond, double* tm) {
   if (!ctx || !seqs || !cond || !tm) return dp_set_error(ctx, DP_ERR_ARG, "null argument");

@@ -235,6 +235,13 @@ int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hits,
                  const char* variants, const dp_conditions* cond,
                  dp_dimer** dimers, uint64_t* n_dimers, dp_dg_stats* stats);
 
+/* The template window under every hit, as the reference's strand strings show
+ * it (fwd_seq[pos:pos+L] / rev_seq[pos:pos+L], DegenPrimer/SearchEngine.py:113):
+ * out receives n_hits rows of 64 bytes, upper-case ASCII, NUL padded. */
+int dp_hit_windows(dp_ctx* ctx, const dp_template* t, const dp_hit* hits,
+                   uint64_t n_hits, uint32_t n_primers, const uint8_t* primer_len,
+                   char* out);
+
 /* Per-variant perfect-match Tr/Tm — TD_Functions.primer_template_Tr
  * (DegenPrimer/TD_Functions.py:60-101) for `n` sequences of length `len`
  * stored back to back; `concentration` is per variant (Primer.py:180-186),
