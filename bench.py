@@ -1,0 +1,408 @@
+#!/usr/bin/env python3
+"""bench.py — the hot path's headline metric on B200 (contract: task brief ④).
+
+metric : template bp x primer-variants scanned per second (BASELINE.json), with the
+         dG stage run on every hit inside the same step.
+step   : one pass of the hot path over one resident template: dp_scan (all
+         primers, both strands) + dp_duplex_dg (every hit x every variant).
+N = 1  : BASELINE.json configs[1] — TP53 pair vs a synthetic 83,257,441 bp
+         chr17-sized template, k = 1 (`config2_tp53_chr17`).
+N > 1  : weak scaling — rank g holds segment g (83 Mbp + (L-1) halo) of an
+         N x 83 Mbp genome, scans it alone, and hit records are all-gathered
+         over NCCL every step (no collective in the scan itself).
+
+`python bench.py --gpus N --steps K --warmup W [--impl reference]`
+prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = 'template_bp_x_primer_variants_scanned_per_s'
+UNIT = 'bp*variants/s'
+WORKLOAD = 'config2_tp53_chr17'
+COND = dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=62.0)     # reference README.md:72-96
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--workload', default=WORKLOAD)
+    ap.add_argument('--scale', type=float, default=1.0, help='shrink the template (testing only)')
+    ap.add_argument('--algo', type=int, default=0, help='0 auto, 1 popcount, 2 bit-slice')
+    ap.add_argument('--cpu-sample-bp', type=int, default=12_000_000)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    return rank, world, local
+
+
+def variants_of(primers):
+    from degenprimer_b200.SeqUtils import unambiguous_sequences
+    return [unambiguous_sequences(p) for p in primers]
+
+
+# ---- clocks -------------------------------------------------------------------------
+class ClockSampler(object):
+    """nvidia-smi samples DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+         'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, device):
+        self.device = device
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix='.clocks.csv')
+            os.close(fd)
+            self.fh = open(self.path, 'w')
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.device), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=self.fh, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.fh.close()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        with open(self.path) as fh:
+            for line in fh:
+                f = [x.strip() for x in line.split(',')]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for name, v in zip(names, f[5:9]):
+                    if v.lower().startswith('active'):
+                        reasons.add(name)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm))
+        out['reasons'] = sorted(reasons)
+        return out
+
+
+# ---- CPU arm: the reference algorithm (oracle O1) on the host cores -------------------------
+def cpu_reference_pass(text, primers, k, workers):
+    """One pass of the reference's path (SearchEngine.find per primer: FFT scan
+    over multiprocessing slices, then Duplex compilation of every hit x variant).
+    Only bench.py's cpu_baseline / --impl reference legs call into oracle/."""
+    from oracle import conditions as ocond
+    from oracle import search_o1 as o1
+    from oracle.primer import Primer as OPrimer, SeqRecord as OSeqRecord
+    ocond.PCR_P.set(COND)
+    hits = dimers = 0
+    for i, master in enumerate(primers):
+        m = o1.find_mp(text, master, k, workers=workers)
+        p = OPrimer(OSeqRecord(master, id='p%d' % i), 1.5e-6)
+        res = o1.compile_duplexes(m[0], m[1], p, m[2], m[3], m[4], m[5], mp_order=True)
+        hits += len(m[4]) + len(m[5])
+        if res:
+            dimers += sum(len(d.dimers) for lst in res for _, dups in lst for d in dups)
+    return hits, dimers
+
+
+def make_cpu_sample(wl, sample_bp):
+    """A bounded prefix of the workload's template that still contains planted sites."""
+    rec = wl['records'][0]
+    n = min(len(rec), sample_bp)
+    arr = rec[:n].copy()
+    from degenprimer_b200.synthetic import plant_pairs
+    plant_pairs(np.random.default_rng(99), arr, wl['primers'], wl['k'], 8)
+    return arr.tobytes().decode()
+
+
+def cpu_baseline(wl, sample_bp, repeats=1):
+    cores = os.cpu_count() or 1
+    text = make_cpu_sample(wl, sample_bp)
+    n_var = sum(len(v) for v in variants_of(wl['primers']))
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        hits, dimers = cpu_reference_pass(text, wl['primers'], wl['k'], cores)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return dict(value=len(text) * n_var / best, unit=UNIT, cores=cores, kind='port',
+                sample='first %d bp of %s x %d primers, scan (scipy.fftpack, %d fork workers) + dG of %d hits; %.2f s'
+                       % (len(text), wl['name'], len(wl['primers']), cores, hits, best),
+                seconds=best, hits=hits, dimers=dimers)
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU algorithm for this path.  The
+    reference itself is Python 2.7 + Biopython and cannot run in this image
+    (no python2, no Bio), so its Python-3 restatement (oracle O1)
+    is what is timed; `kind` says so."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    from degenprimer_b200.synthetic import make_workload
+    wl = make_workload(args.workload, scale=min(args.scale, args.cpu_sample_bp / 83_257_441.0 * 1.01))
+    cores = os.cpu_count() or 1
+    text = make_cpu_sample(wl, args.cpu_sample_bp)
+    n_var = sum(len(v) for v in variants_of(wl['primers']))
+    for _ in range(args.warmup):
+        cpu_reference_pass(text[:min(len(text), 1_000_000)], wl['primers'], wl['k'], cores)
+    t0 = time.perf_counter()
+    hits = 0
+    for _ in range(args.steps):
+        hits, _d = cpu_reference_pass(text, wl['primers'], wl['k'], cores)
+    dt = (time.perf_counter() - t0) / max(1, args.steps)
+    value = len(text) * n_var / dt
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'complex128 FFT (reference) / u32 bitwise (ours)',
+        'data': 'synthetic',
+        'config': {'workload': args.workload, 'primers': wl['primers'], 'max_mismatches': wl['k'],
+                   'step_sample_bp': len(text), 'note': 'bounded sample per step; throughput is per bp so it is size independent'},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                         'sample': '%d bp x %d primers per step, %d hits' % (len(text), len(wl['primers']), hits)},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line))
+
+
+# ---- GPU arm -----------------------------------------------------------------------------------
+def run_ours(args):
+    rank, world, local = dist_env()
+    if world != args.gpus and world > 1:
+        raise SystemExit('WORLD_SIZE=%d but --gpus %d' % (world, args.gpus))
+    from degenprimer_b200.synthetic import make_workload
+    wl = make_workload(args.workload, scale=args.scale, seed_offset=1000 * rank)
+    primers, k = wl['primers'], wl['k']
+    var_lists = variants_of(primers)
+    n_var = sum(len(v) for v in var_lists)
+    bp = wl['bp']
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(wl, args.cpu_sample_bp)      # before CUDA is initialised (fork pool)
+
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    os.environ['DEGENPRIMER_B200_DEVICE'] = str(local)
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200 import _native as nat
+    from degenprimer_b200.distributed import all_gather_records, sort_hits
+    tdf.PCR_P.set(COND)
+    ctx = tdf._ctx()
+    info = ctx.device_info()
+    cond = tdf.conditions()
+
+    # inputs: pinned host ASCII (for e2e) and rotating resident copies (> L2) for the resident arm
+    host = [torch.from_numpy(r).pin_memory() for r in wl['records']]
+    srcs = [(h.data_ptr(), h.numel()) for h in host]
+    one = ctx.template_from_sequences(srcs)
+    plane_bytes = one.device_bytes
+    n_copies = max(2, int(np.ceil(1.5 * L2_BYTES / max(1, plane_bytes))))
+    n_copies = min(n_copies, 64)
+    copies = [one] + [ctx.template_from_sequences(srcs) for _ in range(n_copies - 1)]
+
+    lens = [len(p) for p in primers]
+    var_counts = [len(v) for v in var_lists]
+    var_offsets, blob, off = [], '', 0
+    for v, L in zip(var_lists, lens):
+        var_offsets.append(off)
+        blob += ''.join(v)
+        off += len(v) * L
+
+    def step(i):
+        t = copies[i % n_copies]
+        hits, st = ctx.scan(t, primers, k, algo=args.algo)
+        dimers, dst = ctx.duplex_dg(t, hits, lens, var_counts, var_offsets, blob, cond)
+        if world > 1:
+            hits = sort_hits(all_gather_records(hits))
+        return hits, dimers, st, dst
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for i in range(max(3, args.warmup)):
+        step(i)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    sync_all()
+    acc = dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, dimers=0, cand=0, windows=0)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        hits, dimers, st, dst = step(args.warmup + i)
+        acc['ms_main'] += st['ms_main']
+        acc['ms_scan'] += st['ms_scan']
+        acc['ms_dg'] += dst['ms_kernel']
+        acc['launches'] += st['launches'] + dst['launches']
+        acc['hits'] += len(hits)
+        acc['dimers'] += len(dimers)
+        acc['cand'] += st['candidates']
+        acc['windows'] = st['windows']
+    sync_all()
+    elapsed = time.perf_counter() - t0
+    if world > 1:
+        tt = torch.tensor([elapsed], dtype=torch.float64, device='cuda')
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        elapsed = float(tt.item())
+    K = max(1, args.steps)
+    ms_step = elapsed / K * 1e3
+    value = world * bp * n_var / (elapsed / K)
+
+    # ---- e2e: host ASCII in pinned memory -> reference-facing calls -> host results -------------
+    from degenprimer_b200.Primer import Primer
+    from degenprimer_b200.SearchEngine import SearchEngine
+    from degenprimer_b200.SeqUtils import Seq, SeqRecord
+    from degenprimer_b200.SeqView import ResidentRecord
+    from degenprimer_b200.WorkCounter import WorkCounter
+    gprimers = []
+    for i, p in enumerate(primers):
+        g = Primer(SeqRecord(Seq(p), id='primer%d' % i), 1.5e-6)
+        g.generate_components()
+        gprimers.append(g)
+    se = SearchEngine()
+
+    def e2e_step():
+        t = ctx.template_from_sequences(srcs)                 # H2D of the ASCII bytes + pack kernel
+        d2h = 0
+        for r in range(t.n_records):
+            rec = ResidentRecord(t, r)
+            for g in gprimers:
+                m = se.find_matches(WorkCounter(), rec, g, k)
+                d2h += 16 * (len(m[5]) + len(m[6]))
+                res = se.compile_duplexes_mp(WorkCounter(), *m)
+                d2h += 24 * int(se.last_stats['dg']['dimers_kept']) if res else 0
+        t.close()
+        return d2h
+
+    for _ in range(2):
+        e2e_step()
+    sync_all()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    d2h = 0
+    for _ in range(e2e_steps):
+        d2h = e2e_step()
+    sync_all()
+    e2e_elapsed = time.perf_counter() - t0
+    if world > 1:
+        tt = torch.tensor([e2e_elapsed], dtype=torch.float64, device='cuda')
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_elapsed = float(tt.item())
+    e2e_value = world * bp * n_var / (e2e_elapsed / e2e_steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel ----------------------------------------------------
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as fh:
+            peaks = json.load(fh)
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
+    peak_src = 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6.65 TB/s (B200_PROFILING.md)'
+    ms_main = acc['ms_main'] / K
+    algo_bytes = 0.25 * bp                      # 2 bits per template base, read once
+    achieved = algo_bytes / (ms_main * 1e-3) / 1e9 if ms_main > 0 else 0.0
+    roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s',
+                'frac': achieved / hbm_peak, 'traffic': None,
+                'kernel': 'dp_scan_bitslice_kernel' if st['algo'] == 2 else 'dp_scan_popc_kernel',
+                'ms_per_launch': ms_main, 'algorithmic_bytes_per_launch': algo_bytes,
+                'peak_source': peak_src}
+    # integer-pipe view (the path is integer/bitwise work; canonical op counts of SURVEY §8d)
+    lop3 = ctx.calibrate('lop3')
+    popc = ctx.calibrate('popc')
+    lds = ctx.calibrate('lds')
+    windows = float(acc['windows'])
+    a_win = 16.0
+    int_roofline = {
+        'bound': 'int32 ALU (LOP3) issue rate, measured by dp_calibrate on this GPU',
+        'peak_lop3_lane_ops_per_s': lop3, 'peak_popc_lane_ops_per_s': popc, 'peak_lds32_lane_ops_per_s': lds,
+        'windows_per_s': windows / (ms_main * 1e-3) if ms_main > 0 else 0.0,
+        'canonical_ops_per_window': a_win,
+        'frac_of_canonical_int_roof': (windows * a_win / (ms_main * 1e-3)) / lop3 if ms_main > 0 else 0.0,
+        'frac_of_canonical_popc_roof': (windows * 2.0 / (ms_main * 1e-3)) / popc if ms_main > 0 else 0.0,
+        'note': 'canonical = 16 int32 ops incl. 2 POPC per window (SURVEY 8d); the bit-sliced kernel '
+                'issues far fewer, so fractions above 1 mean "faster than the per-window popcount roof"',
+    }
+    line = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'u32 bitwise (scan) + f64 (dG)', 'data': 'synthetic',
+        'config': {'workload': args.workload, 'template_bp_per_gpu': bp, 'primers': primers,
+                   'variants': n_var, 'max_mismatches': k, 'records': len(wl['records']),
+                   'l2': 'rotating %d resident copies of the template planes (%.0f MB > 126 MB L2)'
+                         % (n_copies, n_copies * plane_bytes / 1e6),
+                   'timing': 'host wall clock around K synchronous steps; kernels by CUDA events on the launch stream',
+                   'gpu': info['name'], 'sms': info['sm_count'], 'scale': args.scale},
+        'hits_per_step': acc['hits'] / K, 'dimers_per_step': acc['dimers'] / K,
+        'candidates_per_step': acc['cand'] / K,
+        'ms_scan_kernels': acc['ms_scan'] / K, 'ms_dg_kernels': acc['ms_dg'] / K,
+        'dg_hits_per_s': (acc['hits'] / K) / (acc['ms_dg'] / K * 1e-3) if acc['ms_dg'] > 0 else None,
+        'gpu_launches': acc['launches'],
+        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': int(sum(n for _, n in srcs)),
+                'd2h_bytes_per_step': int(d2h), 'ms_per_step': e2e_elapsed / e2e_steps * 1e3,
+                'path': 'pinned host ASCII -> dp_template_from_records (H2D + pack) -> '
+                        'SearchEngine.find_matches + compile_duplexes_mp per primer -> host arrays'},
+        'roofline': roofline, 'int_roofline': int_roofline, 'clocks': clocks,
+    }
+    if cpu is not None:
+        line['cpu_baseline'] = cpu
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

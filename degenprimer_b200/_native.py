@@ -46,6 +46,7 @@ class dp_template_info(C.Structure):
 class dp_scan_stats(C.Structure):
     _fields_ = [('windows', C.c_uint64), ('candidates', C.c_uint64), ('hits', C.c_uint64),
                 ('ms_scan', C.c_float), ('ms_total', C.c_float),
+                ('ms_main', C.c_float), ('reserved', C.c_float),
                 ('launches', C.c_uint32), ('algo', C.c_uint32)]
 
 
@@ -106,6 +107,7 @@ def _declare(lib):
         'dp_duplex_dg': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_void_p, P(dp_conditions), P(vp), P(u64), P(dp_dg_stats)]),
         'dp_hit_windows': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p]),
+        'dp_calibrate': (i32, [vp, i32, i32, P(C.c_double), P(C.c_double)]),
         'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
         'dp_dimer_dg': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_void_p, P(dp_conditions), C.c_void_p]),
@@ -120,7 +122,7 @@ def _declare(lib):
 EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
-           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_hit_windows dp_variant_tm dp_dimer_dg').split()
+           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
 
 
 def load():
@@ -128,6 +130,9 @@ def load():
     global _lib
     with _lock:
         if _lib is None:
+            from .build import build_native, _stale
+            if _stale():              # sources newer than the .so: rebuild (seconds) or fail loudly
+                build_native()
             if not os.path.exists(LIB_PATH):
                 raise RuntimeError(
                     'libdegenprimer_b200.so is not built (%s). Run `python -m degenprimer_b200.build`; '
@@ -314,6 +319,13 @@ class Context(object):
             self.lib.dp_free(out)
         stats = {f: getattr(st, f) for f, _ in dp_dg_stats._fields_}
         return arr, stats
+
+    def calibrate(self, which, reps=5):
+        """Lane-ops/s of a pipe: 'lop3', 'popc' or 'lds'."""
+        idx = {'lop3': 0, 'popc': 1, 'lds': 2}[which]
+        rate, ms = C.c_double(), C.c_double()
+        self._check(self.lib.dp_calibrate(self._h, idx, reps, C.byref(rate), C.byref(ms)))
+        return rate.value
 
     def hit_windows(self, template, hits, primer_lens):
         """List of window strings, one per hit (strand orientation)."""

@@ -79,6 +79,7 @@ dp_ctx* dp_create(int device_ordinal) {
             cudaEventCreate(&ctx->ev0) == cudaSuccess &&
             cudaEventCreate(&ctx->ev1) == cudaSuccess &&
             cudaEventCreate(&ctx->ev2) == cudaSuccess &&
+            cudaEventCreate(&ctx->ev3) == cudaSuccess &&
             cudaMalloc(&ctx->d_counters, 16 * sizeof(unsigned long long)) == cudaSuccess &&
             cudaMalloc(&ctx->d_tables, sizeof(dp_nn_tables)) == cudaSuccess;
   if (!ok) {
@@ -104,6 +105,7 @@ void dp_destroy(dp_ctx* ctx) {
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaEventDestroy(ctx->ev2);
+  cudaEventDestroy(ctx->ev3);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

@@ -52,7 +52,7 @@ struct dp_template {
 struct dp_ctx {
   int device;
   cudaStream_t stream;
-  cudaEvent_t ev0, ev1, ev2;
+  cudaEvent_t ev0, ev1, ev2, ev3;
   int sm_count;
   int cc_major, cc_minor;
   volatile int abort_flag;

@@ -195,7 +195,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   const int NW = max_len > 32 ? 2 : 1;
   const uint64_t n_scan_words = A.word_end - A.word_begin;
   uint32_t launches = 0;
-  float ms_scan = 0.f;
+  float ms_scan = 0.f, ms_main = 0.f;
   unsigned long long h_counters[4] = {0, 0, 0, 0};
   uint64_t cap = std::max<uint64_t>(ctx->hits_cap, 1u << 20);
   for (int attempt = 0; attempt < 3; ++attempt) {
@@ -210,6 +210,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
       if (used_algo == DP_ALGO_BITSLICE) {
         rc = dp_bitslice_launch(ctx, A, plan, &launches);
         if (rc) return rc;
+        DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
         // windows touching non-ACGT bases, for the prefiltered patterns
         if (plan.pmask[0] | plan.pmask[1]) {
           if (NW == 1) dp_scan_popc_kernel<1><<<blocks, 256, 0, ctx->stream>>>(A, plan.pmask[0], plan.pmask[1], 1);
@@ -226,6 +227,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
         if (NW == 1) dp_scan_popc_kernel<1><<<blocks, 256, 0, ctx->stream>>>(A, pmask_all[0], pmask_all[1], 0);
         else dp_scan_popc_kernel<2><<<blocks, 256, 0, ctx->stream>>>(A, pmask_all[0], pmask_all[1], 0);
         ++launches;
+        DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
       }
       DP_CUDA(ctx, cudaGetLastError());
     }
@@ -235,6 +237,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ev_k0, ev_k1);
     ms_scan += ms;
+    if (n_scan_words) cudaEventElapsedTime(&ms_main, ev_k0, ctx->ev3);
     if (h_counters[0] <= ctx->hits_cap) break;
     cap = h_counters[0] + (h_counters[0] >> 3) + 1024;     // overflow: grow and rescan
     if (attempt == 2) return dp_set_error(ctx, DP_ERR_STATE, "internal: hit buffer overflow persists");
@@ -273,6 +276,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
     stats->candidates = h_counters[1];
     stats->hits = n;
     stats->ms_scan = ms_scan;
+    stats->ms_main = ms_main;
     cudaEventRecord(ev_k1, ctx->stream);
     cudaEventSynchronize(ev_k1);
     float ms_total = 0.f;

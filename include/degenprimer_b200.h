@@ -139,8 +139,11 @@ typedef struct dp_scan_stats {
   uint64_t windows;        /* window x pattern pairs examined                    */
   uint64_t candidates;     /* pairs that reached the exact verify stage          */
   uint64_t hits;
-  float ms_scan;           /* CUDA-event time of the scan kernel(s)              */
+  float ms_scan;           /* CUDA-event time of all scan kernels of the call    */
   float ms_total;          /* incl. hit download and sort                        */
+  float ms_main;           /* the dominant kernel alone (bit-slice, or popcount  */
+                           /* when that is the only one)                         */
+  float reserved;
   uint32_t launches;       /* kernels launched by this call                      */
   uint32_t algo;           /* DP_ALGO_* actually used                            */
 } dp_scan_stats;
@@ -258,6 +261,14 @@ int dp_dimer_dg(dp_ctx* ctx, uint32_t n, const char* s1, const uint64_t* off1,
                 const uint8_t* len1, const char* s2, const uint64_t* off2,
                 const uint8_t* len2, const uint64_t* match_mask,
                 const int32_t* offset, const dp_conditions* cond, double* dG);
+
+/* ---- roofline calibration -------------------------------------------------------
+ * Measured issue rate of the pipes the scan kernels live on (the
+ * integer roofline's denominators must be measured on the box).
+ * which: 0 = LOP3 (ALU pipe), 1 = POPC, 2 = conflict-free LDS.32.
+ * lane_ops_per_s = warp instructions x 32 per second over the whole chip. */
+int dp_calibrate(dp_ctx* ctx, int which, int reps, double* lane_ops_per_s,
+                 double* ms_best);
 
 #ifdef __cplusplus
 }
