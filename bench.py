@@ -237,27 +237,25 @@ def run_ours(args):
     n_copies = min(n_copies, 64)
     copies = [one] + [ctx.template_from_sequences(srcs) for _ in range(n_copies - 1)]
 
-    lens = [len(p) for p in primers]
-    var_counts = [len(v) for v in var_lists]
-    var_offsets, blob, off = [], '', 0
-    for v, L in zip(var_lists, lens):
-        var_offsets.append(off)
-        blob += ''.join(v)
-        off += len(v) * L
-
     def step(i):
+        # one pass of the hot path: scan of every primer over both strands + dG of every
+        # (hit, variant), one stream submission (dp_find), results back on the host
         t = copies[i % n_copies]
-        hits, st = ctx.scan(t, primers, k, algo=args.algo)
-        dimers, dst = ctx.duplex_dg(t, hits, lens, var_counts, var_offsets, blob, cond)
+        hits, dimers, st, dst = ctx.find(t, primers, k, var_lists, cond, algo=args.algo)
         if world > 1:
             hits = sort_hits(all_gather_records(hits))
         return hits, dimers, st, dst
 
     def sync_all():
+        ctx.synchronize()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
             torch.cuda.synchronize()
+
+    # CUDA events on the stream the kernels are launched on (the context's own stream)
+    kstream = torch.cuda.ExternalStream(ctx.stream, device=torch.device('cuda', local))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     for i in range(max(3, args.warmup)):
         step(i)
@@ -267,6 +265,7 @@ def run_ours(args):
     sync_all()
     acc = dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, dimers=0, cand=0, windows=0)
     t0 = time.perf_counter()
+    ev0.record(kstream)
     for i in range(args.steps):
         hits, dimers, st, dst = step(args.warmup + i)
         acc['ms_main'] += st['ms_main']
@@ -277,12 +276,14 @@ def run_ours(args):
         acc['dimers'] += len(dimers)
         acc['cand'] += st['candidates']
         acc['windows'] = st['windows']
+    ev1.record(kstream)
     sync_all()
-    elapsed = time.perf_counter() - t0
+    wall = time.perf_counter() - t0
+    elapsed = ev0.elapsed_time(ev1) * 1e-3        # device clock, first launch -> last result copy
     if world > 1:
-        tt = torch.tensor([elapsed], dtype=torch.float64, device='cuda')
+        tt = torch.tensor([elapsed, wall], dtype=torch.float64, device='cuda')
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        elapsed = float(tt.item())
+        elapsed, wall = float(tt[0].item()), float(tt[1].item())
     K = max(1, args.steps)
     ms_step = elapsed / K * 1e3
     value = world * bp * n_var / (elapsed / K)
@@ -306,10 +307,8 @@ def run_ours(args):
         for r in range(t.n_records):
             rec = ResidentRecord(t, r)
             for g in gprimers:
-                m = se.find_matches(WorkCounter(), rec, g, k)
-                d2h += 16 * (len(m[5]) + len(m[6]))
-                res = se.compile_duplexes_mp(WorkCounter(), *m)
-                d2h += 24 * int(se.last_stats['dg']['dimers_kept']) if res else 0
+                se.find_duplexes(WorkCounter(), rec, g, k)    # SearchEngine.find without the shelf file
+                d2h += 16 * int(se.last_stats['scan']['hits']) + 24 * int(se.last_stats['dg']['dimers_kept'])
         t.close()
         return d2h
 
@@ -376,7 +375,8 @@ def run_ours(args):
                    'variants': n_var, 'max_mismatches': k, 'records': len(wl['records']),
                    'l2': 'rotating %d resident copies of the template planes (%.0f MB > 126 MB L2)'
                          % (n_copies, n_copies * plane_bytes / 1e6),
-                   'timing': 'host wall clock around K synchronous steps; kernels by CUDA events on the launch stream',
+                   'timing': 'CUDA events on the context stream around K synchronous steps (max over ranks); '
+                             'wall clock %.4f ms/step' % (wall / K * 1e3),
                    'gpu': info['name'], 'sms': info['sm_count'], 'scale': args.scale},
         'hits_per_step': acc['hits'] / K, 'dimers_per_step': acc['dimers'] / K,
         'candidates_per_step': acc['cand'] / K,
@@ -386,7 +386,7 @@ def run_ours(args):
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': int(sum(n for _, n in srcs)),
                 'd2h_bytes_per_step': int(d2h), 'ms_per_step': e2e_elapsed / e2e_steps * 1e3,
                 'path': 'pinned host ASCII -> dp_template_from_records (H2D + pack) -> '
-                        'SearchEngine.find_matches + compile_duplexes_mp per primer -> host arrays'},
+                        'SearchEngine.find_duplexes (= find without the shelf file) per primer -> host arrays'},
         'roofline': roofline, 'int_roofline': int_roofline, 'clocks': clocks,
     }
     if cpu is not None:

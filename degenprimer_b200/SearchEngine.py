@@ -147,10 +147,23 @@ class SearchEngine(object):
         return fwd_seq, rev_seq, primer, t_len, p_len, fwd_matches, rev_matches
 
     # ---- duplex thermodynamics ------------------------------------------------------------
+    @staticmethod
+    def _site_results(tmpl, hits, dimers, primer, t_len, p_len, variants, names, T, n_f):
+        """(fwd_results, rev_results): lists of (position, SiteDuplexes) in hit order,
+        sites without a stable duplex dropped (DegenPrimer/SearchEngine.py:106-126).
+        hits: forward hits first (n_f of them), then reverse; dimers grouped by hit."""
+        table = _LazyWindowsTable(dimers, tmpl, hits, p_len, variants, names, T)
+        bounds = np.searchsorted(dimers['hit'], np.arange(len(hits) + 1))
+        pos = hits['pos'].astype(np.int64)
+        site_pos = np.where(hits['strand'] == 0, pos + p_len, t_len + 1 - (pos + p_len))
+        fwd_results, rev_results = [], []
+        for h in np.flatnonzero(bounds[1:] > bounds[:-1]):
+            item = (int(site_pos[h]), SiteDuplexes(table, int(h), int(bounds[h]), int(bounds[h + 1])))
+            (fwd_results if h < n_f else rev_results).append(item)
+        return fwd_results, rev_results
+
     def _compile(self, fwd_seq, rev_seq, primer, t_len, p_len, fwd_matches, rev_matches):
-        """Both strands in one dp_duplex_dg call.  Returns (fwd_results, rev_results),
-        each a list of (position, SiteDuplexes) in match order, sites without a
-        stable duplex dropped (DegenPrimer/SearchEngine.py:106-126)."""
+        """Both strands in one dp_duplex_dg call."""
         if isinstance(fwd_seq, StrandView):
             tmpl, rec = fwd_seq.template, fwd_seq.record
         else:
@@ -170,14 +183,38 @@ class SearchEngine(object):
             dimers, stats = tmpl.ctx.duplex_dg(tmpl, hits, [p_len], [len(variants)], [0],
                                                ''.join(variants), cond)
         self.last_stats['dg'] = stats
-        table = _LazyWindowsTable(dimers, tmpl, hits, p_len, variants, names, T)
-        bounds = np.searchsorted(dimers['hit'], np.arange(len(hits) + 1))
-        pos = hits['pos'].astype(np.int64)
-        site_pos = np.where(hits['strand'] == 0, pos + p_len, t_len + 1 - (pos + p_len))
-        fwd_results, rev_results = [], []
-        for h in np.flatnonzero(bounds[1:] > bounds[:-1]):
-            item = (int(site_pos[h]), SiteDuplexes(table, int(h), int(bounds[h]), int(bounds[h + 1])))
-            (fwd_results if h < n_f else rev_results).append(item)
+        return self._site_results(tmpl, hits, dimers, primer, t_len, p_len, variants, names, T, n_f)
+
+    def _find_fused(self, template, primer, mismatches):
+        """find_matches + compile_duplexes_mp as ONE stream submission (dp_find):
+        the hits never leave the device between the two stages."""
+        p_len, t_len = len(primer), len(template)
+        tmpl, rec = resident(template)
+        begin = tmpl.starts[rec]
+        end = begin + ((tmpl.lengths[rec] + 31) // 32) * 32
+        if tmpl.n_records == 1:
+            begin, end = 0, 2 ** 64 - 1
+        records = primer.seq_records
+        variants = [str(r.seq) for r in records]
+        names = [r.id for r in records]
+        with tdf.AcquireParameters():
+            cond = tdf.conditions()
+            T = tdf.PCR_P.PCR_T
+            hits, dimers, st, dst = tmpl.ctx.find(tmpl, [str(primer.master_sequence.seq)], int(mismatches),
+                                                  [variants], cond, begin, end)
+        self.last_stats['scan'] = st
+        self.last_stats['dg'] = dst
+        if len(hits) and not (hits['record'] == rec).all():
+            raise RuntimeError('internal: hits outside the scanned record')
+        if not len(hits):
+            return None
+        n_f = int(np.count_nonzero(hits['strand'] == 0))
+        fwd_results, rev_results = self._site_results(tmpl, hits, dimers, primer, t_len, p_len,
+                                                      variants, names, T, n_f)
+        if not fwd_results and not rev_results:
+            return None
+        fwd_results.sort(key=lambda x: x[0])
+        rev_results.sort(key=lambda x: x[0])
         return fwd_results, rev_results
 
     def compile_duplexes_mp(self, counter, fwd_seq, rev_seq, primer, t_len, p_len,
@@ -226,14 +263,27 @@ class SearchEngine(object):
         return fwd_results, rev_results
 
     # ---- compositions -------------------------------------------------------------------------
+    def find_duplexes(self, counter, template, primer, mismatches):
+        """find_matches + compile_duplexes_mp (what `find` puts on the shelf), fused on
+        the device; returns (fwd_results, rev_results) or None."""
+        p_len, t_len = len(primer), len(template)
+        self._check_length_inequality(t_len, p_len)
+        counter.set_subwork(2, (t_len, t_len * primer.num_components))
+        if self.aborted():
+            return None
+        try:
+            duplexes = self._find_fused(template, primer, mismatches)
+        except nat.Aborted:
+            return None
+        counter[0].done()
+        counter[1].done()
+        if self.aborted():
+            return None
+        return duplexes
+
     def find(self, counter, template, primer, mismatches):
         """DegenPrimer/SearchEngine.py:375-386."""
-        t_len = len(template)
-        counter.set_subwork(2, (t_len, t_len * primer.num_components))
-        matches = self.find_matches(counter[0], template, primer, mismatches)
-        if matches is None:
-            return None
-        duplexes = self.compile_duplexes_mp(counter[1], *matches)
+        duplexes = self.find_duplexes(counter, template, primer, mismatches)
         return to_shelf(duplexes) if duplexes else None
 
     def _batch_find(self, template, primer, p_len, mismatches):

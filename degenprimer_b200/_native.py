@@ -106,6 +106,11 @@ def _declare(lib):
         'dp_tables_load': (i32, [vp, P(dp_nn_tables)]),
         'dp_duplex_dg': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_void_p, P(dp_conditions), P(vp), P(u64), P(dp_dg_stats)]),
+        'dp_find': (i32, [vp, vp, u32, P(cp), P(C.c_int32), u64, u64, i32, i32, C.c_void_p, C.c_void_p,
+                          C.c_void_p, P(dp_conditions), P(vp), P(u64), P(vp), P(u64),
+                          P(dp_scan_stats), P(dp_dg_stats)]),
+        'dp_stream': (vp, [vp]),
+        'dp_synchronize': (i32, [vp]),
         'dp_hit_windows': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p]),
         'dp_calibrate': (i32, [vp, i32, i32, P(C.c_double), P(C.c_double)]),
         'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
@@ -122,7 +127,8 @@ def _declare(lib):
 EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
-           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
+           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_stream dp_synchronize '
+           'dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
 
 
 def load():
@@ -290,6 +296,48 @@ class Context(object):
             self.lib.dp_free(hits)
         stats = {f: getattr(st, f) for f, _ in dp_scan_stats._fields_}
         return arr, stats
+
+    def _take(self, ptr, n, dtype):
+        """Copy a malloc()ed result array into numpy and release it."""
+        try:
+            if n:
+                buf = (C.c_char * (n * dtype.itemsize)).from_address(ptr.value)
+                return np.frombuffer(buf, dtype=dtype).copy()
+            return np.zeros(0, dtype=dtype)
+        finally:
+            self.lib.dp_free(ptr)
+
+    def find(self, template, masters, mismatches, variants, cond, seg_begin=0, seg_end=2 ** 64 - 1,
+             strands=DP_STRAND_BOTH, algo=DP_ALGO_AUTO):
+        """Fused scan + duplex dG (dp_find).  variants: one list of unambiguous
+        sequences per master.  Returns (hits, dimers, scan stats, dG stats)."""
+        n = len(masters)
+        m = (C.c_char_p * n)(*[s.encode('ascii') if isinstance(s, str) else s for s in masters])
+        if isinstance(mismatches, int):
+            mismatches = [mismatches] * n
+        k = (C.c_int32 * n)(*[int(x) for x in mismatches])
+        vc = np.array([len(v) for v in variants], dtype=np.uint32)
+        lens = np.array([len(s) for s in masters], dtype=np.uint64)
+        vo = np.concatenate(([0], np.cumsum(vc.astype(np.uint64) * lens)[:-1])).astype(np.uint64)
+        vb = ''.join(''.join(v) for v in variants).encode('ascii')
+        hits, n_hits, dimers, n_dimers = C.c_void_p(), C.c_uint64(), C.c_void_p(), C.c_uint64()
+        st, dst = dp_scan_stats(), dp_dg_stats()
+        self._check(self.lib.dp_find(self._h, template._h, n, m, k, seg_begin, seg_end, strands, algo,
+                                     _ptr(vc), _ptr(vo), C.cast(C.c_char_p(vb), C.c_void_p), C.byref(cond),
+                                     C.byref(hits), C.byref(n_hits), C.byref(dimers), C.byref(n_dimers),
+                                     C.byref(st), C.byref(dst)))
+        h = self._take(hits, n_hits.value, HIT_DTYPE)
+        d = self._take(dimers, n_dimers.value, DIMER_DTYPE)
+        return (h, d, {f: getattr(st, f) for f, _ in dp_scan_stats._fields_},
+                {f: getattr(dst, f) for f, _ in dp_dg_stats._fields_})
+
+    @property
+    def stream(self):
+        """cudaStream_t of this context as an integer (for torch.cuda.ExternalStream)."""
+        return int(self.lib.dp_stream(self._h) or 0)
+
+    def synchronize(self):
+        self._check(self.lib.dp_synchronize(self._h))
 
     # ---- thermodynamics ----------------------------------------------------------
     def load_tables(self, tables, key=None):

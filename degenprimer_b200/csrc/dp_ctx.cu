@@ -18,6 +18,49 @@ int dp_set_error(dp_ctx* ctx, int code, const char* fmt, ...) {
   return code;
 }
 
+cudaError_t dp_pool_alloc(dp_ctx* ctx, void** p, size_t bytes) {
+  return cudaMallocFromPoolAsync(p, bytes ? bytes : 1, ctx->pool, ctx->stream);
+}
+
+void dp_pool_free(dp_ctx* ctx, void* p) {
+  if (p) cudaFreeAsync(p, ctx->stream);
+}
+
+// Grow-only workspace.  Growing synchronises the stream (rare: first calls and overflows).
+template <typename T>
+static int ws_grow(dp_ctx* ctx, T** p, uint64_t* cap, uint64_t want, const char* what) {
+  if (*cap >= want) return DP_OK;
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (*p) { cudaFree(*p); *p = nullptr; *cap = 0; }
+  cudaError_t e = cudaMalloc((void**)p, want * sizeof(T));
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return dp_set_error(ctx, DP_ERR_NOMEM, "out of device memory for %llu %s", (unsigned long long)want, what);
+  }
+  *cap = want;
+  return DP_OK;
+}
+
+int dp_ws_hits(dp_ctx* ctx, uint64_t cap) { return ws_grow(ctx, &ctx->d_hits, &ctx->hits_cap, cap, "hit records"); }
+int dp_ws_dir(dp_ctx* ctx, uint64_t cap) { return ws_grow(ctx, &ctx->d_dir, &ctx->dir_cap, cap, "duplex directory entries"); }
+int dp_ws_dimers(dp_ctx* ctx, uint64_t cap) { return ws_grow(ctx, &ctx->d_dimers, &ctx->dimers_cap, cap, "dimer records"); }
+int dp_ws_codes(dp_ctx* ctx, uint64_t cap) { return ws_grow(ctx, &ctx->d_codes, &ctx->codes_cap, cap, "variant bytes"); }
+
+int dp_ws_pinned(dp_ctx* ctx, size_t bytes) {
+  if (ctx->h_res_bytes >= bytes) return DP_OK;
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->h_res) { cudaFreeHost(ctx->h_res); ctx->h_res = nullptr; ctx->h_res_bytes = 0; }
+  size_t want = 1u << 20;
+  while (want < bytes) want <<= 1;
+  cudaError_t e = cudaMallocHost((void**)&ctx->h_res, want);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return dp_set_error(ctx, DP_ERR_NOMEM, "out of pinned host memory (%zu bytes)", want);
+  }
+  ctx->h_res_bytes = want;
+  return DP_OK;
+}
+
 extern "C" {
 
 int dp_abi_version(void) { return DP_ABI_VERSION; }
@@ -70,18 +113,39 @@ dp_ctx* dp_create(int device_ordinal) {
   ctx->abort_flag = 0;
   ctx->tables_loaded = false;
   ctx->d_tables = nullptr;
-  ctx->d_hits = nullptr;
-  ctx->hits_cap = 0;
+  ctx->pool = nullptr;
+  ctx->d_hits = nullptr;  ctx->hits_cap = 0;
+  ctx->d_dir = nullptr;   ctx->dir_cap = 0;
+  ctx->d_dimers = nullptr; ctx->dimers_cap = 0;
+  ctx->d_codes = nullptr; ctx->codes_cap = 0;
   ctx->d_counters = nullptr;
+  ctx->h_res = nullptr;   ctx->h_res_bytes = 0;
   ctx->stage_bytes = 0;
-  for (int i = 0; i < 2; ++i) { ctx->h_stage[i] = nullptr; ctx->d_stage[i] = nullptr; ctx->stage_ev[i] = nullptr; }
+  ctx->stream = ctx->copy_stream = nullptr;
+  for (int i = 0; i < 2; ++i) {
+    ctx->h_stage[i] = nullptr; ctx->d_stage[i] = nullptr;
+    ctx->stage_ev[i] = nullptr; ctx->stage_copied[i] = nullptr;
+  }
+  cudaMemPoolProps pp;
+  memset(&pp, 0, sizeof pp);
+  pp.allocType = cudaMemAllocationTypePinned;
+  pp.handleTypes = cudaMemHandleTypeNone;
+  pp.location.type = cudaMemLocationTypeDevice;
+  pp.location.id = device_ordinal;
+  unsigned long long keep = ~0ull;    // never hand memory back between calls
   bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
             cudaEventCreate(&ctx->ev0) == cudaSuccess &&
             cudaEventCreate(&ctx->ev1) == cudaSuccess &&
             cudaEventCreate(&ctx->ev2) == cudaSuccess &&
             cudaEventCreate(&ctx->ev3) == cudaSuccess &&
+            cudaEventCreate(&ctx->ev4) == cudaSuccess &&
+            cudaEventCreate(&ctx->ev5) == cudaSuccess &&
+            cudaMemPoolCreate(&ctx->pool, &pp) == cudaSuccess &&
+            cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep) == cudaSuccess &&
             cudaMalloc(&ctx->d_counters, 16 * sizeof(unsigned long long)) == cudaSuccess &&
-            cudaMalloc(&ctx->d_tables, sizeof(dp_nn_tables)) == cudaSuccess;
+            cudaMalloc(&ctx->d_tables, sizeof(dp_nn_tables)) == cudaSuccess &&
+            dp_ws_pinned(ctx, 1u << 20) == DP_OK;
   if (!ok) {
     dp_set_error(nullptr, DP_ERR_CUDA, "context resources: %s", cudaGetErrorString(cudaGetLastError()));
     delete ctx;
@@ -94,20 +158,38 @@ void dp_destroy(dp_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  cudaStreamSynchronize(ctx->copy_stream);
   for (int i = 0; i < 2; ++i) {
     if (ctx->h_stage[i]) cudaFreeHost(ctx->h_stage[i]);
     if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
     if (ctx->stage_ev[i]) cudaEventDestroy(ctx->stage_ev[i]);
+    if (ctx->stage_copied[i]) cudaEventDestroy(ctx->stage_copied[i]);
   }
   if (ctx->d_hits) cudaFree(ctx->d_hits);
+  if (ctx->d_dir) cudaFree(ctx->d_dir);
+  if (ctx->d_dimers) cudaFree(ctx->d_dimers);
+  if (ctx->d_codes) cudaFree(ctx->d_codes);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->d_tables) cudaFree(ctx->d_tables);
+  if (ctx->h_res) cudaFreeHost(ctx->h_res);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaEventDestroy(ctx->ev2);
   cudaEventDestroy(ctx->ev3);
+  cudaEventDestroy(ctx->ev4);
+  cudaEventDestroy(ctx->ev5);
+  if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
+  cudaStreamDestroy(ctx->copy_stream);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
+}
+
+void* dp_stream(dp_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int dp_synchronize(dp_ctx* ctx) {
+  if (!ctx) return DP_ERR_ARG;
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return DP_OK;
 }
 
 const char* dp_last_error(const dp_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }

@@ -95,7 +95,25 @@ __device__ double dp_dimer_dg_device(const dp_dg_args& A, const uint8_t* s, int 
   return bad ? nan : res;
 }
 
-// ---- window letters of every hit ------------------------------------------------
+// ---- window letters ----------------------------------------------------------------
+// letter index of padded position g (plane code, or the run's IUPAC letter)
+__device__ __forceinline__ uint32_t dp_letter_at(const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi,
+                                                 const uint32_t* __restrict__ exc, const dp_exc_run* __restrict__ runs,
+                                                 uint64_t n_runs, uint64_t g) {
+  const uint64_t wi = g >> 5;
+  const uint32_t b = (uint32_t)(g & 31);
+  if ((__ldg(exc + wi) >> b) & 1u) {
+    uint64_t lo_i = 0, hi_i = n_runs;
+    while (lo_i < hi_i) {
+      uint64_t mid = (lo_i + hi_i) >> 1;
+      if (runs[mid].start <= g) lo_i = mid + 1; else hi_i = mid;
+    }
+    if (lo_i) { const dp_exc_run& rr = runs[lo_i - 1]; if (g < rr.end) return rr.letter; }
+    return 14u;
+  }
+  return ((__ldg(hi + wi) >> b) & 1u) * 2u + ((__ldg(lo + wi) >> b) & 1u);
+}
+
 // win[h*64 + i] = letter index of window position i as the reference's
 // strand string shows it (reverse hits: reverse complement of the forward bases)
 __global__ void dp_dg_windows_kernel(const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi,
@@ -112,93 +130,177 @@ __global__ void dp_dg_windows_kernel(const uint32_t* __restrict__ lo, const uint
   if (i < L) {
     int strand = hit_strand[h];
     uint64_t g = hit_g[h] + (strand ? (uint64_t)(L - 1 - i) : (uint64_t)i);
-    uint64_t wi = g >> 5;
-    uint32_t b = (uint32_t)(g & 31);
-    uint32_t letter;
-    if ((exc[wi] >> b) & 1u) {
-      uint64_t lo_i = 0, hi_i = n_runs;
-      while (lo_i < hi_i) {
-        uint64_t mid = (lo_i + hi_i) >> 1;
-        if (runs[mid].start <= g) lo_i = mid + 1; else hi_i = mid;
-      }
-      letter = 14u;
-      if (lo_i) { const dp_exc_run& rr = runs[lo_i - 1]; if (g < rr.end) letter = rr.letter; }
-    } else {
-      letter = ((hi[wi] >> b) & 1u) * 2u + ((lo[wi] >> b) & 1u);
-    }
+    uint32_t letter = dp_letter_at(lo, hi, exc, runs, n_runs, g);
     out = (uint8_t)(strand ? dp_letter_complement(letter) : letter);
   }
   win[idx] = out;
 }
 
-// ---- per (hit, variant) duplex ----------------------------------------------------
-// pass 0: counts[pair] = surviving dimers;  pass 1: write them at out_off[pair]
-// in the reference's order [full, alternatives...] and stable-sort by dG.
-template <int PASS>
-__global__ void __launch_bounds__(128)
-dp_duplex_kernel(dp_dg_args A, const uint8_t* __restrict__ win, uint64_t hit0, uint64_t n_hits_p,
-                 uint32_t V, int L, const uint8_t* __restrict__ var_codes /* V x L */,
-                 uint64_t pair0, uint32_t* __restrict__ counts, const uint64_t* __restrict__ out_off,
-                 dp_dimer* __restrict__ out, unsigned long long* __restrict__ tried) {
-  uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n_hits_p * V) return;
-  const uint64_t h = hit0 + idx / V;
-  const uint32_t v = (uint32_t)(idx % V);
-  uint8_t s[DP_WIN], r[DP_WIN];
-  const uint8_t* wl = win + h * DP_WIN;
-  const uint8_t* vc = var_codes + (uint64_t)v * L;
-  uint64_t M = 0;
-  for (int i = 0; i < L; ++i) {
-    uint8_t w = wl[i];
-    s[i] = vc[i];
-    r[i] = (uint8_t)dp_letter_complement(w);        // rev_str = complement(window)
-    if (w == s[i]) M |= 1ull << i;                   // plain character equality
+// ---- per (hit, variant) duplex: the whole Duplex.__init__ / _recalculate in one pass ----
+// Grid-stride over the (hit, variant) pairs of the raw hits in `hits`; the pair
+// and hit counts are read from the device counters, so the kernel can be queued
+// right behind the scan without a host round trip.  Per pair:
+//   window letters from the planes -> match mask -> [full, alternatives...] in the
+//   reference's order -> dG of each -> filter -> stable order by dG -> one atomic
+//   reservation of the output range -> directory entry offset << 16 | count.
+struct dp_duplex_args {
+  dp_dg_args dg;
+  const uint32_t* lo;
+  const uint32_t* hi;
+  const uint32_t* exc;
+  const dp_exc_run* runs;
+  uint64_t n_runs;
+  const dp_raw_hit* hits;
+  uint64_t hits_cap;
+  const uint8_t* codes;
+  uint64_t* dir;
+  uint64_t dir_cap;
+  dp_raw_dimer* out;
+  uint64_t out_cap;
+  unsigned long long* counters;
+};
+
+#define DP_DUPLEX_THREADS 128
+#define DP_DUPLEX_KEEP 12      // survivors held in registers/local before the fallback re-run
+
+__global__ void __launch_bounds__(DP_DUPLEX_THREADS)
+dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant__ dp_dg_plan plan) {
+  const unsigned long long packed = A.counters[DP_C_HITS];
+  const uint64_t n_hits = (uint32_t)packed;
+  const uint64_t n_pairs = packed >> 32;
+  if (n_hits > A.hits_cap) return;                       // the host grows the buffer and rescans
+  if ((uint64_t)blockIdx.x * blockDim.x >= n_pairs) return;
+  // NN tables -> shared memory (10 KB), the per-thread work below is latency bound
+  __shared__ dp_nn_tables sT;
+  {
+    const uint64_t* src = reinterpret_cast<const uint64_t*>(A.dg.T);
+    uint64_t* dst = reinterpret_cast<uint64_t*>(&sT);
+    for (uint32_t i = threadIdx.x; i < sizeof(dp_nn_tables) / 8; i += blockDim.x) dst[i] = src[i];
   }
-  uint32_t kept = 0;
+  __syncthreads();
+  dp_dg_args G = A.dg;
+  G.T = &sT;
   unsigned long long n_tried = 0;
-  dp_dimer* dst = PASS ? out + out_off[pair0 + idx] : nullptr;
-  auto consider = [&](uint64_t sub) {
-    ++n_tried;
-    double dG = dp_dimer_dg_device(A, s, L, r, L, sub, 0);
-    if (dG > A.max_dimer_dG) return;        // SecStructures.py:302
-    if (!(dG <= A.max_dG_for_K)) return;    // K < min_K, SecStructures.py:303-304
-    if (PASS) {
-      dp_dimer d;
-      d.hit = (uint32_t)h; d.variant = v; d.match_mask = sub; d.dG = dG;
-      // stable insertion by dG (ties keep construction order)
-      uint32_t pos = kept;
-      while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
-      dst[pos] = d;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t pair = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; pair < n_pairs; pair += stride) {
+    // hit of this pair: last slot whose pair_base <= pair (pair_base is monotone in slot)
+    uint64_t a = 0, b = n_hits;
+    while (a < b) {
+      const uint64_t m = (a + b) >> 1;
+      if ((uint64_t)A.hits[m].pair_base <= pair) a = m + 1; else b = m;
     }
-    ++kept;
-  };
-  if (M) {
-    consider(M);
-    // Dimer.alternatives (SecStructures.py:126-152): split M into maximal runs
-    // of consecutive indices and emit every contiguous range of runs except
-    // the full one, in the reference's order: for each left cut l, first the
-    // right cuts from the far right inwards, then the next left cut.
-    const uint64_t S = M & ~(M << 1);      // first index of every run
-    const uint64_t Eb = M & ~(M >> 1);     // last index of every run
-    const uint64_t top_end = 1ull << (63 - __clzll((long long)Eb));
-    uint64_t sl = S;
-    while (sl & (sl - 1)) {                // at least one more run to the right
-      const int st = __ffsll((long long)sl) - 1;
-      const uint64_t lo_m = ~0ull << st;
-      uint64_t eh = Eb & lo_m & ~top_end;  // ends of runs l .. last-1
-      while (eh) {
-        const int e = 63 - __clzll((long long)eh);
-        eh &= ~(1ull << e);
-        const uint64_t hi_m = (2ull << e) - 1;   // e <= 62 here
-        consider(M & lo_m & hi_m);
+    const dp_raw_hit hit = A.hits[a - 1];
+    const uint32_t v = (uint32_t)(pair - hit.pair_base);
+    const int L = plan.pat_len[hit.pattern];
+    const int strand = plan.pat_strand[hit.pattern];
+    const uint32_t primer = plan.pat_primer[hit.pattern];
+    uint8_t s[DP_WIN], r[DP_WIN];
+    const uint8_t* vc = A.codes + plan.var_off[primer] + (uint64_t)v * L;
+    uint64_t M = 0;
+    for (int i = 0; i < L; ++i) {
+      const uint64_t g = hit.g + (strand ? (uint64_t)(L - 1 - i) : (uint64_t)i);
+      uint32_t w = dp_letter_at(A.lo, A.hi, A.exc, A.runs, A.n_runs, g);
+      if (strand) w = dp_letter_complement(w);
+      s[i] = vc[i];
+      r[i] = (uint8_t)dp_letter_complement(w);        // rev_str = complement(window)
+      if (w == s[i]) M |= 1ull << i;                   // plain character equality
+    }
+    // pass 0 keeps the first DP_DUPLEX_KEEP survivors sorted in local arrays; if there
+    // are more, pass 1 recomputes and inserts straight into the reserved output range
+    uint64_t kmask[DP_DUPLEX_KEEP];
+    double kdg[DP_DUPLEX_KEEP];
+    uint32_t kept = 0;
+    dp_raw_dimer* dst = nullptr;
+    auto consider = [&](uint64_t sub) {
+      if (!dst) ++n_tried;
+      const double dG = dp_dimer_dg_device(G, s, L, r, L, sub, 0);
+      if (dG > G.max_dimer_dG) return;        // SecStructures.py:302
+      if (!(dG <= G.max_dG_for_K)) return;    // K < min_K, SecStructures.py:303-304
+      if (dst) {
+        // stable insertion by dG (ties keep construction order)
+        uint32_t pos = kept;
+        while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
+        dst[pos].match_mask = sub;
+        dst[pos].dG = dG;
+      } else if (kept < DP_DUPLEX_KEEP) {
+        uint32_t pos = kept;
+        while (pos > 0 && kdg[pos - 1] > dG) { kdg[pos] = kdg[pos - 1]; kmask[pos] = kmask[pos - 1]; --pos; }
+        kdg[pos] = dG;
+        kmask[pos] = sub;
       }
-      sl &= sl - 1;
-      const int st2 = __ffsll((long long)sl) - 1;
-      consider(M & (~0ull << st2));
+      ++kept;
+    };
+    auto enumerate = [&]() {
+      if (!M) return;
+      consider(M);
+      // Dimer.alternatives (SecStructures.py:126-152): split M into maximal runs
+      // of consecutive indices and emit every contiguous range of runs except
+      // the full one, in the reference's order: for each left cut l, first the
+      // right cuts from the far right inwards, then the next left cut.
+      const uint64_t S = M & ~(M << 1);      // first index of every run
+      const uint64_t Eb = M & ~(M >> 1);     // last index of every run
+      const uint64_t top_end = 1ull << (63 - __clzll((long long)Eb));
+      uint64_t sl = S;
+      while (sl & (sl - 1)) {                // at least one more run to the right
+        const int st = __ffsll((long long)sl) - 1;
+        const uint64_t lo_m = ~0ull << st;
+        uint64_t eh = Eb & lo_m & ~top_end;  // ends of runs l .. last-1
+        while (eh) {
+          const int e = 63 - __clzll((long long)eh);
+          eh &= ~(1ull << e);
+          const uint64_t hi_m = (2ull << e) - 1;   // e <= 62 here
+          consider(M & lo_m & hi_m);
+        }
+        sl &= sl - 1;
+        const int st2 = __ffsll((long long)sl) - 1;
+        consider(M & (~0ull << st2));
+      }
+    };
+    enumerate();
+    uint64_t off = 0;
+    if (kept) {
+      off = atomicAdd(&A.counters[DP_C_DIMERS], (unsigned long long)kept);
+      if (off + kept <= A.out_cap) {
+        if (kept <= DP_DUPLEX_KEEP) {
+          for (uint32_t k = 0; k < kept; ++k) { A.out[off + k].match_mask = kmask[k]; A.out[off + k].dG = kdg[k]; }
+        } else {
+          dst = A.out + off;
+          kept = 0;
+          enumerate();
+        }
+      }
     }
+    if (pair < A.dir_cap) A.dir[pair] = (off << 16) | (uint64_t)kept;
   }
-  if (!PASS) counts[pair0 + idx] = kept;
-  if (!PASS && n_tried) atomicAdd(tried, n_tried);
+  if (n_tried) atomicAdd(&A.counters[DP_C_TRIED], n_tried);
+}
+
+int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches) {
+  dp_duplex_args A;
+  A.dg.T = ctx->d_tables;
+  A.dg.PCR_T = L.PCR_T;
+  A.dg.Na_eq_log = L.Na_eq_log;
+  A.dg.max_dimer_dG = L.max_dimer_dG;
+  A.dg.max_dG_for_K = L.max_dG_for_K;
+  A.lo = t->d_lo; A.hi = t->d_hi; A.exc = t->d_exc;
+  A.runs = t->d_runs;
+  A.n_runs = t->runs.size();
+  A.hits = ctx->d_hits;
+  A.hits_cap = ctx->hits_cap;
+  A.codes = ctx->d_codes;
+  A.dir = ctx->d_dir;
+  A.dir_cap = ctx->dir_cap;
+  A.out = ctx->d_dimers;
+  A.out_cap = ctx->dimers_cap;
+  A.counters = ctx->d_counters;
+  // pair count unknown on the host (fused call): a persistent grid, most blocks
+  // leave at once when there are few pairs
+  uint64_t blocks = (uint64_t)ctx->sm_count * 8;
+  if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_THREADS - 1) / DP_DUPLEX_THREADS);
+  dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, 0, ctx->stream>>>(A, L.plan);
+  DP_CUDA(ctx, cudaGetLastError());
+  ++*launches;
+  return DP_OK;
 }
 
 // ---- per-variant Tm — TD_Functions.py:60-101 -------------------------------------
@@ -242,11 +344,16 @@ __global__ void dp_dimer_dg_kernel(dp_dg_args A, uint32_t n, const uint8_t* __re
 }
 
 // ---- host ----------------------------------------------------------------------------
+// scratch from the context's stream-ordered pool (freed in stream order, no sync)
 template <typename T>
 struct dev_buf {
   T* p = nullptr;
-  ~dev_buf() { if (p) cudaFree(p); }
-  cudaError_t alloc(size_t n) { return cudaMalloc(&p, std::max<size_t>(1, n) * sizeof(T)); }
+  dp_ctx* owner = nullptr;
+  ~dev_buf() { if (p) dp_pool_free(owner, p); }
+  cudaError_t alloc(dp_ctx* ctx, size_t n) {
+    owner = ctx;
+    return dp_pool_alloc(ctx, (void**)&p, std::max<size_t>(1, n) * sizeof(T));
+  }
 };
 
 static int letters_of(dp_ctx* ctx, const char* src, size_t n, std::vector<uint8_t>& out, bool bases_only) {
@@ -271,140 +378,6 @@ static dp_dg_args make_args(dp_ctx* ctx, const dp_conditions* c) {
   return A;
 }
 
-extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hits, uint64_t n_hits,
-                            uint32_t n_primers, const uint8_t* primer_len, const uint32_t* var_count,
-                            const uint64_t* var_offset, const char* variants, const dp_conditions* cond,
-                            dp_dimer** dimers_out, uint64_t* n_dimers_out, dp_dg_stats* stats) {
-  if (!ctx || !t || !cond || !dimers_out || !n_dimers_out || (n_hits && !hits) ||
-      (n_primers && (!primer_len || !var_count || !var_offset || !variants)))
-    return dp_set_error(ctx, DP_ERR_ARG, "null argument");
-  *dimers_out = nullptr;
-  *n_dimers_out = 0;
-  if (stats) memset(stats, 0, sizeof *stats);
-  if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
-  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
-  if (n_hits == 0) { *dimers_out = (dp_dimer*)malloc(sizeof(dp_dimer)); return DP_OK; }
-  if (n_hits > 0xFFFFFFFFull) return dp_set_error(ctx, DP_ERR_ARG, "more than 2^32 hits in one call");
-  DP_CUDA(ctx, cudaSetDevice(ctx->device));
-  // hits must be grouped by primer (dp_scan returns them sorted that way)
-  std::vector<uint64_t> hit_g(n_hits);
-  std::vector<uint8_t> hit_len(n_hits), hit_strand(n_hits);
-  std::vector<uint64_t> pair0(n_hits + 1, 0);
-  struct Group { uint64_t h0, n; uint32_t primer; };
-  std::vector<Group> groups;
-  for (uint64_t h = 0; h < n_hits; ++h) {
-    const dp_hit& x = hits[h];
-    if (x.primer >= n_primers) return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: primer %u out of range", (unsigned long long)h, x.primer);
-    if (x.record >= t->records.size()) return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: record out of range", (unsigned long long)h);
-    const dp_record& rec = t->records[x.record];
-    uint32_t L = primer_len[x.primer];
-    if (L == 0 || L > DP_MAX_PRIMER_LEN || x.pos + L > rec.len)
-      return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: window outside its record", (unsigned long long)h);
-    uint64_t fwd = x.strand ? rec.len - L - x.pos : x.pos;
-    hit_g[h] = rec.start + fwd;
-    hit_len[h] = (uint8_t)L;
-    hit_strand[h] = x.strand ? 1 : 0;
-    pair0[h + 1] = pair0[h] + var_count[x.primer];
-    if (groups.empty() || groups.back().primer != x.primer) groups.push_back(Group{h, 1, x.primer});
-    else ++groups.back().n;
-  }
-  const uint64_t n_pairs = pair0[n_hits];
-  // variants -> plane codes
-  uint64_t var_bytes = 0;
-  for (uint32_t p = 0; p < n_primers; ++p)
-    var_bytes = std::max<uint64_t>(var_bytes, var_offset[p] + (uint64_t)var_count[p] * primer_len[p]);
-  std::vector<uint8_t> codes;
-  int rc = letters_of(ctx, variants, var_bytes, codes, true);
-  if (rc) return rc;
-
-  cudaStream_t st = ctx->stream;
-  dev_buf<uint64_t> d_g, d_off;
-  dev_buf<uint8_t> d_len, d_strand, d_win, d_codes;
-  dev_buf<uint32_t> d_counts;
-  dev_buf<unsigned long long> d_tried;
-  dev_buf<dp_dimer> d_out;
-  DP_CUDA(ctx, d_g.alloc(n_hits));
-  DP_CUDA(ctx, d_len.alloc(n_hits));
-  DP_CUDA(ctx, d_strand.alloc(n_hits));
-  DP_CUDA(ctx, d_win.alloc(n_hits * DP_WIN));
-  DP_CUDA(ctx, d_codes.alloc(var_bytes));
-  DP_CUDA(ctx, d_counts.alloc(n_pairs));
-  DP_CUDA(ctx, d_off.alloc(n_pairs + 1));
-  DP_CUDA(ctx, d_tried.alloc(1));
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
-  DP_CUDA(ctx, cudaMemcpyAsync(d_g.p, hit_g.data(), n_hits * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
-  DP_CUDA(ctx, cudaMemcpyAsync(d_len.p, hit_len.data(), n_hits, cudaMemcpyHostToDevice, st));
-  DP_CUDA(ctx, cudaMemcpyAsync(d_strand.p, hit_strand.data(), n_hits, cudaMemcpyHostToDevice, st));
-  DP_CUDA(ctx, cudaMemcpyAsync(d_codes.p, codes.data(), var_bytes, cudaMemcpyHostToDevice, st));
-  DP_CUDA(ctx, cudaMemsetAsync(d_tried.p, 0, sizeof(unsigned long long), st));
-  uint32_t launches = 0;
-  {
-    uint64_t n = n_hits * DP_WIN;
-    dp_dg_windows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
-        t->d_lo, t->d_hi, t->d_exc, t->d_runs, t->runs.size(), d_g.p, d_len.p, d_strand.p, n_hits, d_win.p);
-    DP_CUDA(ctx, cudaGetLastError());
-    ++launches;
-  }
-  dp_dg_args A = make_args(ctx, cond);
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
-  for (const Group& g : groups) {
-    uint32_t V = var_count[g.primer];
-    uint64_t n = g.n * V;
-    if (!n) continue;
-    dp_duplex_kernel<0><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
-        A, d_win.p, g.h0, g.n, V, primer_len[g.primer], d_codes.p + var_offset[g.primer], pair0[g.h0],
-        d_counts.p, nullptr, nullptr, d_tried.p);
-    DP_CUDA(ctx, cudaGetLastError());
-    ++launches;
-  }
-  std::vector<uint32_t> counts(n_pairs);
-  unsigned long long tried = 0;
-  if (n_pairs) DP_CUDA(ctx, cudaMemcpyAsync(counts.data(), d_counts.p, n_pairs * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-  DP_CUDA(ctx, cudaMemcpyAsync(&tried, d_tried.p, sizeof tried, cudaMemcpyDeviceToHost, st));
-  DP_CUDA(ctx, cudaStreamSynchronize(st));
-  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
-  std::vector<uint64_t> offs(n_pairs + 1, 0);
-  for (uint64_t i = 0; i < n_pairs; ++i) offs[i + 1] = offs[i] + counts[i];
-  const uint64_t n_out = offs[n_pairs];
-  dp_dimer* out = (dp_dimer*)malloc(std::max<uint64_t>(1, n_out) * sizeof(dp_dimer));
-  if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu dimers", (unsigned long long)n_out);
-  if (n_out) {
-    cudaError_t e = d_out.alloc(n_out);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off.p, offs.data(), (n_pairs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st);
-    for (const Group& g : groups) {
-      if (e != cudaSuccess) break;
-      uint32_t V = var_count[g.primer];
-      uint64_t n = g.n * V;
-      if (!n) continue;
-      dp_duplex_kernel<1><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(
-          A, d_win.p, g.h0, g.n, V, primer_len[g.primer], d_codes.p + var_offset[g.primer], pair0[g.h0],
-          nullptr, d_off.p, d_out.p, d_tried.p);
-      e = cudaGetLastError();
-      ++launches;
-    }
-    if (e == cudaSuccess) e = cudaEventRecord(ctx->ev2, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out.p, n_out * sizeof(dp_dimer), cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) { free(out); return dp_set_error(ctx, DP_ERR_CUDA, "duplex pass 2: %s", cudaGetErrorString(e)); }
-  } else {
-    DP_CUDA(ctx, cudaEventRecord(ctx->ev2, st));
-    DP_CUDA(ctx, cudaStreamSynchronize(st));
-  }
-  *dimers_out = out;
-  *n_dimers_out = n_out;
-  if (stats) {
-    stats->duplexes = n_pairs;
-    stats->dimers_tried = tried;
-    stats->dimers_kept = n_out;
-    cudaEventElapsedTime(&stats->ms_kernel, ctx->ev1, ctx->ev2);
-    cudaEventRecord(ctx->ev1, st);
-    cudaEventSynchronize(ctx->ev1);
-    cudaEventElapsedTime(&stats->ms_total, ctx->ev0, ctx->ev1);
-    stats->launches = launches;
-  }
-  return DP_OK;
-}
-
 extern "C" int dp_hit_windows(dp_ctx* ctx, const dp_template* t, const dp_hit* hits, uint64_t n_hits,
                               uint32_t n_primers, const uint8_t* primer_len, char* out) {
   if (!ctx || !t || (n_hits && (!hits || !out)) || !primer_len) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
@@ -426,10 +399,10 @@ extern "C" int dp_hit_windows(dp_ctx* ctx, const dp_template* t, const dp_hit* h
   }
   dev_buf<uint64_t> d_g;
   dev_buf<uint8_t> d_len, d_strand, d_win;
-  DP_CUDA(ctx, d_g.alloc(n_hits));
-  DP_CUDA(ctx, d_len.alloc(n_hits));
-  DP_CUDA(ctx, d_strand.alloc(n_hits));
-  DP_CUDA(ctx, d_win.alloc(n_hits * DP_WIN));
+  DP_CUDA(ctx, d_g.alloc(ctx, n_hits));
+  DP_CUDA(ctx, d_len.alloc(ctx, n_hits));
+  DP_CUDA(ctx, d_strand.alloc(ctx, n_hits));
+  DP_CUDA(ctx, d_win.alloc(ctx, n_hits * DP_WIN));
   cudaStream_t st = ctx->stream;
   DP_CUDA(ctx, cudaMemcpyAsync(d_g.p, hit_g.data(), n_hits * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
   DP_CUDA(ctx, cudaMemcpyAsync(d_len.p, hit_len.data(), n_hits, cudaMemcpyHostToDevice, st));
@@ -461,8 +434,8 @@ extern "C" int dp_variant_tm(dp_ctx* ctx, uint32_t n, uint32_t len, const char* 
   if (rc) return rc;
   dev_buf<uint8_t> d_codes;
   dev_buf<double> d_tm;
-  DP_CUDA(ctx, d_codes.alloc(codes.size()));
-  DP_CUDA(ctx, d_tm.alloc(n));
+  DP_CUDA(ctx, d_codes.alloc(ctx, codes.size()));
+  DP_CUDA(ctx, d_tm.alloc(ctx, n));
   DP_CUDA(ctx, cudaMemcpyAsync(d_codes.p, codes.data(), codes.size(), cudaMemcpyHostToDevice, ctx->stream));
   dp_variant_tm_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_tables, d_codes.p, n, len, concentration, conversion_degree,
                                                                   cond->DNA, cond->DMSO, cond->Na_eq_log, d_tm.p);
@@ -496,10 +469,10 @@ extern "C" int dp_dimer_dg(dp_ctx* ctx, uint32_t n, const char* s1, const uint64
   dev_buf<uint64_t> do1, do2, dm;
   dev_buf<int32_t> doff;
   dev_buf<double> dout;
-  DP_CUDA(ctx, d1.alloc(b1)); DP_CUDA(ctx, d2.alloc(b2));
-  DP_CUDA(ctx, dl1.alloc(n)); DP_CUDA(ctx, dl2.alloc(n));
-  DP_CUDA(ctx, do1.alloc(n)); DP_CUDA(ctx, do2.alloc(n));
-  DP_CUDA(ctx, dm.alloc(n)); DP_CUDA(ctx, doff.alloc(n)); DP_CUDA(ctx, dout.alloc(n));
+  DP_CUDA(ctx, d1.alloc(ctx, b1)); DP_CUDA(ctx, d2.alloc(ctx, b2));
+  DP_CUDA(ctx, dl1.alloc(ctx, n)); DP_CUDA(ctx, dl2.alloc(ctx, n));
+  DP_CUDA(ctx, do1.alloc(ctx, n)); DP_CUDA(ctx, do2.alloc(ctx, n));
+  DP_CUDA(ctx, dm.alloc(ctx, n)); DP_CUDA(ctx, doff.alloc(ctx, n)); DP_CUDA(ctx, dout.alloc(ctx, n));
   cudaStream_t st = ctx->stream;
   DP_CUDA(ctx, cudaMemcpyAsync(d1.p, c1.data(), b1, cudaMemcpyHostToDevice, st));
   DP_CUDA(ctx, cudaMemcpyAsync(d2.p, c2.data(), b2, cudaMemcpyHostToDevice, st));

@@ -49,23 +49,75 @@ struct dp_template {
   uint64_t device_bytes;
 };
 
+// raw hit as written by the scan kernels (padded-concatenation coordinates).
+// pair_base = number of (hit, variant) pairs of all earlier slots: slot and
+// pair_base come from ONE packed 64-bit atomic, so pair_base is monotone in slot.
+struct dp_raw_hit {
+  uint64_t g;          // forward window start in the padded concatenation
+  uint32_t record;
+  uint16_t pattern;
+  uint16_t score3;
+  uint32_t pair_base;
+  uint32_t reserved;
+};
+
+// one surviving dimer as written by the duplex kernel; (hit, variant) are
+// implied by the pair directory
+struct dp_raw_dimer {
+  uint64_t match_mask;
+  double dG;
+};
+
+// What the duplex kernel needs to know about the patterns/primers of a call
+// (kernel parameter, lives in the constant bank).
+#define DP_MAX_PATTERNS (2 * DP_MAX_PRIMERS)
+struct dp_dg_plan {
+  uint8_t pat_len[DP_MAX_PATTERNS];
+  uint8_t pat_strand[DP_MAX_PATTERNS];
+  uint8_t pat_primer[DP_MAX_PATTERNS];
+  uint32_t var_count[DP_MAX_PRIMERS];
+  uint32_t var_off[DP_MAX_PRIMERS];      // byte offset of the primer's variants in d_codes
+};
+
+// counters[] slots (device, 16 x u64)
+enum {
+  DP_C_HITS = 0,      // low 32 bits: hits wanted, high 32 bits: (hit, variant) pairs
+  DP_C_CAND = 1,      // windows that reached the exact verify
+  DP_C_DIMERS = 2,    // dimer slots wanted
+  DP_C_TRIED = 3,     // dimers whose dG was computed
+  DP_C_SATURATED = 4, // the packed hit counter came close to 2^32
+  DP_C_PACK0 = 8,     // pack kernel: boundary entries wanted
+  DP_C_PACK1 = 9      // pack kernel: first foreign byte
+};
+
 struct dp_ctx {
   int device;
   cudaStream_t stream;
-  cudaEvent_t ev0, ev1, ev2, ev3;
+  cudaStream_t copy_stream;    // H2D of template chunks (overlaps the pack kernel)
+  cudaEvent_t ev0, ev1, ev2, ev3, ev4, ev5;
   int sm_count;
   int cc_major, cc_minor;
   volatile int abort_flag;
   bool tables_loaded;
   dp_nn_tables* d_tables;      // device copy
-  // scan scratch
-  void* d_hits;                // raw hit records
+  cudaMemPool_t pool;          // stream-ordered pool: template planes, scratch
+  // grow-only workspace of the scan / duplex stages
+  dp_raw_hit* d_hits;
   uint64_t hits_cap;
-  unsigned long long* d_counters;   // [0]=hits [1]=candidates [2]=overflow ...
+  uint64_t* d_dir;             // per (hit, variant) pair: offset << 16 | count
+  uint64_t dir_cap;
+  dp_raw_dimer* d_dimers;
+  uint64_t dimers_cap;
+  uint8_t* d_codes;            // variant letters as plane codes
+  uint64_t codes_cap;
+  unsigned long long* d_counters;
+  char* h_res;                 // pinned staging for results
+  size_t h_res_bytes;
   // pinned staging for uploads
   char* h_stage[2];
   char* d_stage[2];
   cudaEvent_t stage_ev[2];
+  cudaEvent_t stage_copied[2];
   size_t stage_bytes;
   std::string err;
 };
@@ -131,3 +183,21 @@ __host__ __device__ inline uint32_t dp_filler(uint64_t pos) {
 // host helpers implemented in dp_template.cu / dp_scan.cu
 int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
                        const char* const* seqs, const uint64_t* lens);
+
+// stream-ordered allocation from the context's pool (no cudaMalloc on hot calls)
+cudaError_t dp_pool_alloc(dp_ctx* ctx, void** p, size_t bytes);
+void dp_pool_free(dp_ctx* ctx, void* p);
+// grow-only workspace; contents are lost when a buffer grows
+int dp_ws_hits(dp_ctx* ctx, uint64_t cap);
+int dp_ws_dir(dp_ctx* ctx, uint64_t cap);
+int dp_ws_dimers(dp_ctx* ctx, uint64_t cap);
+int dp_ws_codes(dp_ctx* ctx, uint64_t cap);
+int dp_ws_pinned(dp_ctx* ctx, size_t bytes);
+
+// duplex stage on the hits that sit in ctx->d_hits (dp_dg.cu).  n_pairs_hint = 0:
+// the pair count is only known on the device (fused dp_find).
+struct dp_dg_launch {
+  dp_dg_plan plan;
+  double PCR_T, Na_eq_log, max_dimer_dG, max_dG_for_K;
+};
+int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches);

@@ -1,4 +1,4 @@
-// Annealing-site scan (dp_scan): host driver + the per-window popcount kernel.
+// Annealing-site scan kernels + the host pipeline of dp_scan / dp_find / dp_duplex_dg.
 //
 // Replaces SearchEngine._find / _find_mp / _find_in_slice / _find_in_chunk
 // (DegenPrimer/SearchEngine.py:190-211,257-359).  The reference correlates
@@ -7,6 +7,13 @@
 // and a window is a hit iff score3 >= 3*max(1, L-k) - 1.  Both strands are
 // scanned from the forward planes: the reverse strand uses reverse-complemented
 // masks and reports pos_rev = T - L - pos_fwd.
+//
+// Pipeline of one call (no host round trip between the stages):
+//   memset counters -> bit-sliced prefilter kernel -> run-boundary kernel
+//   -> per-window kernel for patterns the prefilter cannot take
+//   [-> duplex kernel over (hit, variant) pairs, sizes read on the device]
+//   -> counters + a small speculative prefix of the results to pinned memory
+//   -> ONE stream synchronise (a second copy only when the results are large).
 #include <algorithm>
 #include <stdlib.h>
 #include <string.h>
@@ -15,13 +22,12 @@
 #include "dp_scan_bitslice.cuh"
 
 // ---- kernel 1: every window, XOR/AND-style mask select + popcount ---------------
-// One thread owns one plane word = 32 consecutive window starts.
-//   only_exc = 0 : all windows
-//   only_exc = 1 : only windows that touch a non-ACGT base (the bit-sliced
-//                  kernel skips exactly those)
-template <int NW>
+// One thread owns one plane word = 32 consecutive window starts; windows that
+// touch non-ACGT bases are scored here too (1/3 per unknown base).
+template <int NW, int NP>
 __global__ void __launch_bounds__(256)
-dp_scan_popc_kernel(dp_scan_args A, uint64_t pmask0, uint64_t pmask1, int only_exc) {
+dp_scan_popc_kernel(const __grid_constant__ dp_scan_args A, const __grid_constant__ dp_pattern_set<NP> PS,
+                    uint64_t pmask0, uint64_t pmask1) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t w = A.word_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < A.word_end; w += stride) {
     uint32_t H[NW + 1], Lw[NW + 1], E[NW + 1];
@@ -30,12 +36,6 @@ dp_scan_popc_kernel(dp_scan_args A, uint64_t pmask0, uint64_t pmask1, int only_e
       H[k] = __ldg(A.hi + w + k);
       Lw[k] = __ldg(A.lo + w + k);
       E[k] = __ldg(A.exc + w + k);
-    }
-    if (only_exc) {
-      uint32_t any = 0;
-#pragma unroll
-      for (int k = 0; k <= NW; ++k) any |= E[k];
-      if (!any) continue;
     }
     for (int b = 0; b < 32; ++b) {
       uint32_t whi[NW], wlo[NW], wex[NW];
@@ -49,17 +49,53 @@ dp_scan_popc_kernel(dp_scan_args A, uint64_t pmask0, uint64_t pmask1, int only_e
       for (uint32_t p = 0; p < A.n_patterns; ++p) {
         uint64_t bit = p < 64 ? (pmask0 >> p) & 1ull : (pmask1 >> (p - 64)) & 1ull;
         if (!bit) continue;
-        const dp_pattern& P = c_patterns[p];
-        if (only_exc) {
-          uint32_t touch = 0;
-#pragma unroll
-          for (int k = 0; k < NW; ++k) touch |= wex[k] & P.lmask[k];
-          if (!touch) continue;
-        }
+        const dp_pattern& P = PS.pat[p];
         uint32_t s = dp_score3<NW>(P, whi, wlo, wex);
-        if (s >= P.thr3) dp_emit_hit(A, g, p, P.len, s);
+        if (s >= P.thr3) dp_emit_hit(A, g, p, P.len, s, P.n_var);
       }
     }
+  }
+}
+
+// ---- kernel 3: windows that touch a non-ACGT base, for the prefiltered patterns ---
+// The bit-sliced kernel skips every window that contains an unknown base (1/3 of
+// a match is not a hard mismatch).  Those windows are enumerated from the sorted
+// exception-run table instead of re-reading the template: a window belongs to the
+// run that holds its FIRST unknown base, i.e. for run [start, end) with the
+// previous run ending at prev_end
+//   starts in [max(prev_end, start-(L-1)), start)  reach into the run from the left,
+//   starts in [max(start, end-e_max), end)         begin inside the run; a window
+//     with more than e_max = (3L - thr3)/2 unknown bases cannot reach thr3.
+// One thread per (run, candidate start); O(runs * L) work instead of O(T).
+template <int NP>
+__global__ void __launch_bounds__(128)
+dp_scan_runs_kernel(const __grid_constant__ dp_scan_args A, const __grid_constant__ dp_pattern_set<NP> PS,
+                    uint64_t pmask0, uint64_t pmask1, uint32_t left /* Lmax-1 */, uint32_t emax) {
+  const uint32_t span = left + emax;
+  const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t r = idx / span;
+  const uint32_t j = (uint32_t)(idx % span);
+  if (r >= A.n_runs) return;
+  const uint64_t start = A.runs[r].start, end = A.runs[r].end;
+  const uint64_t prev_end = r ? A.runs[r - 1].end : 0;
+  uint64_t g;
+  if (j < left) {
+    const uint64_t d = left - j;                 // 1 .. Lmax-1 bases in front of the run
+    if (start < d) return;
+    g = start - d;
+    if (g < prev_end) return;                    // an earlier run owns this window
+  } else {
+    const uint64_t d = emax - (j - left);        // 1 .. emax bases before the run's end
+    if (end - start < d) return;
+    g = end - d;
+  }
+  for (uint32_t p = 0; p < A.n_patterns; ++p) {
+    uint64_t bit = p < 64 ? (pmask0 >> p) & 1ull : (pmask1 >> (p - 64)) & 1ull;
+    if (!bit) continue;
+    const dp_pattern& P = PS.pat[p];
+    if (g < start && g + P.len <= start) continue;          // does not reach the run
+    if (g >= start && 2ull * min((unsigned long long)(end - g), (unsigned long long)P.len) > 3ull * P.len - P.thr3) continue;   // too many unknown bases
+    dp_verify_window(A, P, g, p, true);
   }
 }
 
@@ -82,7 +118,8 @@ static const int COMP_CODE[4] = {2, 3, 0, 1};   // A<->T, C<->G in plane codes
 
 // Builds the (primer, strand) patterns of one call.  Returns DP_OK or an error.
 static int build_patterns(dp_ctx* ctx, uint32_t n_primers, const char* const* masters,
-                          const int32_t* kmax, int strand_mask, std::vector<dp_pattern>& pats,
+                          const int32_t* kmax, int strand_mask, const uint32_t* var_count,
+                          std::vector<dp_pattern>& pats,
                           std::vector<std::vector<uint8_t>>& letters /* per pattern, window order */) {
   pats.clear();
   letters.clear();
@@ -110,6 +147,7 @@ static int build_patterns(dp_ctx* ctx, uint32_t n_primers, const char* const* ma
       P.thr3 = (uint16_t)(3 * need - 1);
       P.primer = (uint16_t)i;
       P.strand = (uint8_t)strand;
+      P.n_var = var_count ? var_count[i] : 1u;
       std::vector<uint8_t> wl(L);
       for (size_t j = 0; j < L; ++j) {
         // window position j on the forward planes
@@ -133,45 +171,35 @@ static int build_patterns(dp_ctx* ctx, uint32_t n_primers, const char* const* ma
   return DP_OK;
 }
 
-static int ensure_hits(dp_ctx* ctx, uint64_t cap) {
-  if (ctx->hits_cap >= cap) return DP_OK;
-  if (ctx->d_hits) { cudaFree(ctx->d_hits); ctx->d_hits = nullptr; ctx->hits_cap = 0; }
-  DP_CUDA(ctx, cudaMalloc(&ctx->d_hits, cap * sizeof(dp_raw_hit)));
-  ctx->hits_cap = cap;
-  return DP_OK;
-}
+// ---- host: one scan job -------------------------------------------------------------
+struct dp_scan_job {
+  std::vector<dp_pattern> pats;
+  std::vector<std::vector<uint8_t>> letters;
+  dp_bitslice_plan plan;
+  int used_algo;
+  int NW;
+  uint32_t max_len;
+  dp_scan_args A;
+  uint64_t pmask_all[2];
+};
 
-extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
-                       const char* const* masters, const int32_t* max_mismatches,
-                       uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
-                       dp_hit** hits_out, uint64_t* n_hits_out, dp_scan_stats* stats) {
-  if (!ctx || !t || !masters || !hits_out || !n_hits_out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
-  *hits_out = nullptr;
-  *n_hits_out = 0;
-  if (stats) memset(stats, 0, sizeof *stats);
+static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, const char* const* masters,
+                        const int32_t* max_mismatches, uint64_t seg_begin, uint64_t seg_end, int strand_mask,
+                        int algo, const uint32_t* var_count, dp_scan_job& J) {
   if (n_primers == 0 || n_primers > DP_MAX_PRIMERS)
     return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
   if (!(strand_mask & DP_STRAND_BOTH)) return dp_set_error(ctx, DP_ERR_ARG, "empty strand mask");
-  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
-  std::vector<dp_pattern> pats;
-  std::vector<std::vector<uint8_t>> letters;
-  int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, pats, letters);
+  int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.pats, J.letters);
   if (rc) return rc;
-  uint32_t max_len = 0;
-  for (auto& p : pats) max_len = std::max<uint32_t>(max_len, p.len);
-  if (t->records.size() == 1 && t->records[0].len < max_len)
+  J.max_len = 0;
+  for (auto& p : J.pats) J.max_len = std::max<uint32_t>(J.max_len, p.len);
+  if (t->records.size() == 1 && t->records[0].len < J.max_len)
     return dp_set_error(ctx, DP_ERR_LENGTH, "template (%llu) is shorter than the primer (%u)",
-                        (unsigned long long)t->records[0].len, max_len);
-  DP_CUDA(ctx, cudaSetDevice(ctx->device));
-  cudaEvent_t ev_begin = ctx->ev0, ev_k0 = ctx->ev1, ev_k1 = ctx->ev2;
-  DP_CUDA(ctx, cudaEventRecord(ev_begin, ctx->stream));
-  DP_CUDA(ctx, cudaMemcpyToSymbolAsync(c_patterns, pats.data(), pats.size() * sizeof(dp_pattern), 0,
-                                       cudaMemcpyHostToDevice, ctx->stream));
-  const uint32_t n_pat = (uint32_t)pats.size();
-  uint64_t pmask_all[2] = {0, 0};
-  for (uint32_t p = 0; p < n_pat; ++p) pmask_all[p >> 6] |= 1ull << (p & 63);
-
-  dp_scan_args A;
+                        (unsigned long long)t->records[0].len, J.max_len);
+  const uint32_t n_pat = (uint32_t)J.pats.size();
+  J.pmask_all[0] = J.pmask_all[1] = 0;
+  for (uint32_t p = 0; p < n_pat; ++p) J.pmask_all[p >> 6] |= 1ull << (p & 63);
+  dp_scan_args& A = J.A;
   A.lo = t->d_lo; A.hi = t->d_hi; A.exc = t->d_exc;
   A.rec_start = t->d_rec_start; A.rec_len = t->d_rec_len;
   A.n_records = (uint32_t)t->records.size();
@@ -183,107 +211,563 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   A.word_begin = seg_begin / 32;
   A.word_end = (seg_end + 31) / 32;
   A.counters = ctx->d_counters;
-
-  // plan: which patterns go through the bit-sliced prefilter
-  dp_bitslice_plan plan;
-  int used_algo = DP_ALGO_POPC;
+  A.runs = t->d_runs;
+  A.n_runs = t->runs.size();
+  J.used_algo = DP_ALGO_POPC;
   if (algo == DP_ALGO_AUTO || algo == DP_ALGO_BITSLICE) {
-    if (dp_bitslice_make_plan(pats, letters, plan)) used_algo = DP_ALGO_BITSLICE;
+    if (dp_bitslice_make_plan(J.pats, J.letters, J.plan)) J.used_algo = DP_ALGO_BITSLICE;
   } else if (algo != DP_ALGO_POPC) {
     return dp_set_error(ctx, DP_ERR_ARG, "unknown algo %d", algo);
   }
-  const int NW = max_len > 32 ? 2 : 1;
+  J.NW = J.max_len > 32 ? 2 : 1;
+  return DP_OK;
+}
+
+template <int NP>
+static void fill_set(dp_pattern_set<NP>& PS, const std::vector<dp_pattern>& pats) {
+  memset(&PS, 0, sizeof PS);
+  memcpy(PS.pat, pats.data(), pats.size() * sizeof(dp_pattern));
+}
+
+template <int NP>
+static int launch_popc(dp_ctx* ctx, const dp_scan_job& J, const uint64_t mask[2]) {
+  static thread_local dp_pattern_set<NP> PS;     // up to 12 KB: keep it off the stack
+  fill_set(PS, J.pats);
+  const uint64_t n_words = J.A.word_end - J.A.word_begin;
+  unsigned blocks = (unsigned)std::min<uint64_t>((n_words + 255) / 256, (uint64_t)ctx->sm_count * 8);
+  if (J.NW == 1) dp_scan_popc_kernel<1, NP><<<blocks, 256, 0, ctx->stream>>>(J.A, PS, mask[0], mask[1]);
+  else dp_scan_popc_kernel<2, NP><<<blocks, 256, 0, ctx->stream>>>(J.A, PS, mask[0], mask[1]);
+  DP_CUDA(ctx, cudaGetLastError());
+  return DP_OK;
+}
+
+template <int NP>
+static int launch_runs(dp_ctx* ctx, const dp_scan_job& J, const uint64_t mask[2], uint32_t left, uint32_t emax) {
+  static thread_local dp_pattern_set<NP> PS;
+  fill_set(PS, J.pats);
+  const uint64_t n = J.A.n_runs * (uint64_t)(left + emax);
+  dp_scan_runs_kernel<NP><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(J.A, PS, mask[0], mask[1], left, emax);
+  DP_CUDA(ctx, cudaGetLastError());
+  return DP_OK;
+}
+
+// Resets the counters and queues every scan kernel of the job.  Events: ev1 before the
+// first kernel, ev3 after the dominant one, ev2 after the last.
+static int scan_enqueue(dp_ctx* ctx, dp_scan_job& J, uint32_t* launches) {
+  dp_scan_args& A = J.A;
+  A.hits = ctx->d_hits;
+  A.hits_cap = ctx->hits_cap;
+  DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+  DP_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  const bool small = J.pats.size() <= DP_NP_SMALL;
   const uint64_t n_scan_words = A.word_end - A.word_begin;
-  uint32_t launches = 0;
-  float ms_scan = 0.f, ms_main = 0.f;
-  unsigned long long h_counters[4] = {0, 0, 0, 0};
-  uint64_t cap = std::max<uint64_t>(ctx->hits_cap, 1u << 20);
-  for (int attempt = 0; attempt < 3; ++attempt) {
-    rc = ensure_hits(ctx, cap);
-    if (rc) return rc;
-    A.hits = (dp_raw_hit*)ctx->d_hits;
-    A.hits_cap = ctx->hits_cap;
-    DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
-    DP_CUDA(ctx, cudaEventRecord(ev_k0, ctx->stream));
-    if (n_scan_words) {
-      unsigned blocks = (unsigned)std::min<uint64_t>((n_scan_words + 255) / 256, (uint64_t)ctx->sm_count * 8);
-      if (used_algo == DP_ALGO_BITSLICE) {
-        rc = dp_bitslice_launch(ctx, A, plan, &launches);
-        if (rc) return rc;
-        DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
+  int rc = DP_OK;
+  if (n_scan_words) {
+    if (J.used_algo == DP_ALGO_BITSLICE) {
+      rc = dp_bitslice_launch(ctx, A, J.pats, J.plan, launches);
+      if (rc) return rc;
+      DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
+      if (A.n_runs) {
         // windows touching non-ACGT bases, for the prefiltered patterns
-        if (plan.pmask[0] | plan.pmask[1]) {
-          if (NW == 1) dp_scan_popc_kernel<1><<<blocks, 256, 0, ctx->stream>>>(A, plan.pmask[0], plan.pmask[1], 1);
-          else dp_scan_popc_kernel<2><<<blocks, 256, 0, ctx->stream>>>(A, plan.pmask[0], plan.pmask[1], 1);
-          ++launches;
+        uint32_t left = 0, emax = 0;
+        for (size_t p = 0; p < J.pats.size(); ++p) {
+          if (!((J.plan.pmask[p >> 6] >> (p & 63)) & 1ull)) continue;
+          left = std::max<uint32_t>(left, J.pats[p].len - 1u);
+          emax = std::max<uint32_t>(emax, (3u * J.pats[p].len - J.pats[p].thr3) / 2u);
         }
-        uint64_t rest[2] = {pmask_all[0] & ~plan.pmask[0], pmask_all[1] & ~plan.pmask[1]};
-        if (rest[0] | rest[1]) {
-          if (NW == 1) dp_scan_popc_kernel<1><<<blocks, 256, 0, ctx->stream>>>(A, rest[0], rest[1], 0);
-          else dp_scan_popc_kernel<2><<<blocks, 256, 0, ctx->stream>>>(A, rest[0], rest[1], 0);
-          ++launches;
-        }
-      } else {
-        if (NW == 1) dp_scan_popc_kernel<1><<<blocks, 256, 0, ctx->stream>>>(A, pmask_all[0], pmask_all[1], 0);
-        else dp_scan_popc_kernel<2><<<blocks, 256, 0, ctx->stream>>>(A, pmask_all[0], pmask_all[1], 0);
-        ++launches;
-        DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
+        emax = std::max<uint32_t>(1u, std::min<uint32_t>(emax, J.max_len));
+        rc = small ? launch_runs<DP_NP_SMALL>(ctx, J, J.plan.pmask, left, emax)
+                   : launch_runs<DP_MAX_PATTERNS>(ctx, J, J.plan.pmask, left, emax);
+        if (rc) return rc;
+        ++*launches;
       }
-      DP_CUDA(ctx, cudaGetLastError());
+      uint64_t rest[2] = {J.pmask_all[0] & ~J.plan.pmask[0], J.pmask_all[1] & ~J.plan.pmask[1]};
+      if (rest[0] | rest[1]) {
+        rc = small ? launch_popc<DP_NP_SMALL>(ctx, J, rest) : launch_popc<DP_MAX_PATTERNS>(ctx, J, rest);
+        if (rc) return rc;
+        ++*launches;
+      }
+    } else {
+      rc = small ? launch_popc<DP_NP_SMALL>(ctx, J, J.pmask_all) : launch_popc<DP_MAX_PATTERNS>(ctx, J, J.pmask_all);
+      if (rc) return rc;
+      ++*launches;
+      DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
     }
-    DP_CUDA(ctx, cudaEventRecord(ev_k1, ctx->stream));
-    DP_CUDA(ctx, cudaMemcpyAsync(h_counters, ctx->d_counters, sizeof h_counters, cudaMemcpyDeviceToHost, ctx->stream));
-    DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, ev_k0, ev_k1);
-    ms_scan += ms;
-    if (n_scan_words) cudaEventElapsedTime(&ms_main, ev_k0, ctx->ev3);
-    if (h_counters[0] <= ctx->hits_cap) break;
-    cap = h_counters[0] + (h_counters[0] >> 3) + 1024;     // overflow: grow and rescan
-    if (attempt == 2) return dp_set_error(ctx, DP_ERR_STATE, "internal: hit buffer overflow persists");
-    if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  } else {
+    DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
   }
-  const uint64_t n = h_counters[0];
-  std::vector<dp_raw_hit> raw(n);
-  if (n) DP_CUDA(ctx, cudaMemcpy(raw.data(), ctx->d_hits, n * sizeof(dp_raw_hit), cudaMemcpyDeviceToHost));
+  DP_CUDA(ctx, cudaEventRecord(ctx->ev2, ctx->stream));
+  return DP_OK;
+}
+
+// ---- host: results ---------------------------------------------------------------------
+// Speculative prefix copied together with the counters, so that small results
+// (the common case) cost a single synchronise.
+#define DP_SPEC_HITS 1024u
+#define DP_SPEC_PAIRS 4096u
+#define DP_SPEC_DIMERS 2048u
+#define DP_RES_OFF_HITS 128u
+#define DP_RES_OFF_DIR (DP_RES_OFF_HITS + DP_SPEC_HITS * (unsigned)sizeof(dp_raw_hit))
+#define DP_RES_OFF_DIMERS (DP_RES_OFF_DIR + DP_SPEC_PAIRS * (unsigned)sizeof(uint64_t))
+#define DP_RES_SPEC_END (DP_RES_OFF_DIMERS + DP_SPEC_DIMERS * (unsigned)sizeof(dp_raw_dimer))
+
+struct dp_sizes {
+  uint64_t n_hits, n_pairs, n_dimers, tried, cand;
+  bool saturated;
+};
+
+static int fetch_sizes(dp_ctx* ctx, bool with_dg, dp_sizes& S) {
+  cudaStream_t st = ctx->stream;
+  DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res, ctx->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  const uint64_t nh = std::min<uint64_t>(DP_SPEC_HITS, ctx->hits_cap);
+  if (nh) DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + DP_RES_OFF_HITS, ctx->d_hits, nh * sizeof(dp_raw_hit), cudaMemcpyDeviceToHost, st));
+  if (with_dg) {
+    const uint64_t np = std::min<uint64_t>(DP_SPEC_PAIRS, ctx->dir_cap);
+    const uint64_t nd = std::min<uint64_t>(DP_SPEC_DIMERS, ctx->dimers_cap);
+    if (np) DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + DP_RES_OFF_DIR, ctx->d_dir, np * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+    if (nd) DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + DP_RES_OFF_DIMERS, ctx->d_dimers, nd * sizeof(dp_raw_dimer), cudaMemcpyDeviceToHost, st));
+  }
+  DP_CUDA(ctx, cudaEventRecord(ctx->ev5, st));
+  DP_CUDA(ctx, cudaStreamSynchronize(st));
+  const unsigned long long* c = (const unsigned long long*)ctx->h_res;
+  S.n_hits = (uint32_t)c[DP_C_HITS];
+  S.n_pairs = c[DP_C_HITS] >> 32;
+  S.cand = c[DP_C_CAND];
+  S.n_dimers = c[DP_C_DIMERS];
+  S.tried = c[DP_C_TRIED];
+  S.saturated = c[DP_C_SATURATED] != 0;
+  return DP_OK;
+}
+
+// Pointers to the complete raw results on the host (inside ctx->h_res, or inside
+// `big` when they do not fit the pinned buffer).
+struct dp_host_results {
+  const dp_raw_hit* hits;
+  const uint64_t* dir;
+  const dp_raw_dimer* dimers;
+  std::vector<char> big;
+};
+
+static int fetch_all(dp_ctx* ctx, bool with_dg, const dp_sizes& S, dp_host_results& R) {
+  const bool spec_ok = S.n_hits <= DP_SPEC_HITS && (!with_dg || (S.n_pairs <= DP_SPEC_PAIRS && S.n_dimers <= DP_SPEC_DIMERS));
+  if (spec_ok) {
+    R.hits = (const dp_raw_hit*)(ctx->h_res + DP_RES_OFF_HITS);
+    R.dir = (const uint64_t*)(ctx->h_res + DP_RES_OFF_DIR);
+    R.dimers = (const dp_raw_dimer*)(ctx->h_res + DP_RES_OFF_DIMERS);
+    return DP_OK;
+  }
+  const size_t b_hits = S.n_hits * sizeof(dp_raw_hit);
+  const size_t b_dir = with_dg ? S.n_pairs * sizeof(uint64_t) : 0;
+  const size_t b_dim = with_dg ? S.n_dimers * sizeof(dp_raw_dimer) : 0;
+  const size_t total = b_hits + b_dir + b_dim;
+  char* base;
+  if (total <= (256u << 20)) {
+    int rc = dp_ws_pinned(ctx, total);
+    if (rc) return rc;
+    base = ctx->h_res;
+  } else {
+    R.big.resize(total);
+    base = R.big.data();
+  }
+  cudaStream_t st = ctx->stream;
+  if (b_hits) DP_CUDA(ctx, cudaMemcpyAsync(base, ctx->d_hits, b_hits, cudaMemcpyDeviceToHost, st));
+  if (b_dir) DP_CUDA(ctx, cudaMemcpyAsync(base + b_hits, ctx->d_dir, b_dir, cudaMemcpyDeviceToHost, st));
+  if (b_dim) DP_CUDA(ctx, cudaMemcpyAsync(base + b_hits + b_dir, ctx->d_dimers, b_dim, cudaMemcpyDeviceToHost, st));
+  DP_CUDA(ctx, cudaStreamSynchronize(st));
+  R.hits = (const dp_raw_hit*)base;
+  R.dir = (const uint64_t*)(base + b_hits);
+  R.dimers = (const dp_raw_dimer*)(base + b_hits + b_dir);
+  return DP_OK;
+}
+
+// raw hits -> dp_hit in reference coordinates, sorted by (primer, strand, record, pos).
+// order[i] = raw slot of output hit i.
+static int hits_to_abi(dp_ctx* ctx, const dp_template* t, const dp_scan_job& J, const dp_raw_hit* raw,
+                       uint64_t n, dp_hit** out_p, std::vector<uint32_t>* order_p) {
   dp_hit* out = (dp_hit*)malloc(std::max<uint64_t>(1, n) * sizeof(dp_hit));
   if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu hits", (unsigned long long)n);
+  std::vector<dp_hit> tmp(n);
   for (uint64_t i = 0; i < n; ++i) {
     const dp_raw_hit& h = raw[i];
-    const dp_pattern& P = pats[h.pattern];
+    const dp_pattern& P = J.pats[h.pattern];
     const dp_record& rec = t->records[h.record];
     uint64_t off = h.g - rec.start;
-    out[i].pos = P.strand ? rec.len - P.len - off : off;
-    out[i].record = h.record;
-    out[i].primer = P.primer;
-    out[i].strand = P.strand;
-    out[i].score3 = (uint8_t)h.score3;
+    tmp[i].pos = P.strand ? rec.len - P.len - off : off;
+    tmp[i].record = h.record;
+    tmp[i].primer = P.primer;
+    tmp[i].strand = P.strand;
+    tmp[i].score3 = (uint8_t)h.score3;
   }
-  std::sort(out, out + n, [](const dp_hit& a, const dp_hit& b) {
+  std::vector<uint32_t> order(n);
+  for (uint64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+  std::sort(order.begin(), order.end(), [&tmp](uint32_t x, uint32_t y) {
+    const dp_hit& a = tmp[x];
+    const dp_hit& b = tmp[y];
     if (a.primer != b.primer) return a.primer < b.primer;
     if (a.strand != b.strand) return a.strand < b.strand;
     if (a.record != b.record) return a.record < b.record;
     return a.pos < b.pos;
   });
-  *hits_out = out;
-  *n_hits_out = n;
+  for (uint64_t i = 0; i < n; ++i) out[i] = tmp[order[i]];
+  *out_p = out;
+  if (order_p) order_p->swap(order);
+  return DP_OK;
+}
+
+// dimers grouped by (hit in `order`, variant); inside a group the device already
+// sorted by dG (stable).  var_of_hit(i) = number of variants of output hit i.
+template <typename VarCount>
+static int dimers_to_abi(dp_ctx* ctx, const dp_host_results& R, const dp_sizes& S, const std::vector<uint32_t>& order,
+                         VarCount var_of_hit, dp_dimer** out_p, uint64_t* n_out_p) {
+  dp_dimer* out = (dp_dimer*)malloc(std::max<uint64_t>(1, S.n_dimers) * sizeof(dp_dimer));
+  if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu dimers", (unsigned long long)S.n_dimers);
+  uint64_t w = 0;
+  for (size_t i = 0; i < order.size(); ++i) {
+    const dp_raw_hit& h = R.hits[order[i]];
+    const uint32_t V = var_of_hit(i);
+    for (uint32_t v = 0; v < V; ++v) {
+      const uint64_t e = R.dir[(uint64_t)h.pair_base + v];
+      const uint64_t off = e >> 16;
+      const uint32_t cnt = (uint32_t)(e & 0xFFFFu);
+      if (off + cnt > S.n_dimers || w + cnt > S.n_dimers) {
+        free(out);
+        return dp_set_error(ctx, DP_ERR_STATE, "internal: duplex directory is inconsistent");
+      }
+      for (uint32_t k = 0; k < cnt; ++k) {
+        out[w].hit = (uint32_t)i;
+        out[w].variant = v;
+        out[w].match_mask = R.dimers[off + k].match_mask;
+        out[w].dG = R.dimers[off + k].dG;
+        ++w;
+      }
+    }
+  }
+  *out_p = out;
+  *n_out_p = w;
+  return DP_OK;
+}
+
+static uint64_t count_windows(const dp_template* t, const dp_scan_job& J) {
+  uint64_t windows = 0;
+  for (auto& p : J.pats)
+    for (auto& rec : t->records)
+      if (rec.len >= p.len) windows += rec.len - p.len + 1;
+  return windows;
+}
+
+// variants -> plane codes on the device (skipped when the same blob is already there)
+static int upload_codes(dp_ctx* ctx, const char* variants, uint64_t n_bytes) {
+  static thread_local std::vector<uint8_t> last;      // what ctx->d_codes holds (one ctx per thread)
+  static thread_local dp_ctx* last_ctx = nullptr;
+  std::vector<uint8_t> codes(n_bytes);
+  for (uint64_t i = 0; i < n_bytes; ++i) {
+    uint32_t l = dp_letter_of((unsigned char)variants[i]);
+    if (l > 3)
+      return dp_set_error(ctx, DP_ERR_ALPHABET, "byte %llu ('%c') of the variants is not an unambiguous base",
+                          (unsigned long long)i, variants[i]);
+    codes[i] = (uint8_t)l;
+  }
+  if (last_ctx == ctx && last == codes && ctx->codes_cap >= n_bytes) return DP_OK;
+  int rc = dp_ws_codes(ctx, std::max<uint64_t>(n_bytes, 4096));
+  if (rc) return rc;
+  rc = dp_ws_pinned(ctx, DP_RES_SPEC_END + n_bytes);
+  if (rc) return rc;
+  // staged through pinned memory behind the result area; the stream is idle between calls
+  memcpy(ctx->h_res + DP_RES_SPEC_END, codes.data(), n_bytes);
+  DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_codes, ctx->h_res + DP_RES_SPEC_END, n_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  last.swap(codes);
+  last_ctx = ctx;
+  return DP_OK;
+}
+
+static int fill_dg_launch(dp_ctx* ctx, const dp_conditions* cond, dp_dg_launch& L) {
+  memset(&L.plan, 0, sizeof L.plan);
+  L.PCR_T = cond->PCR_T;
+  L.Na_eq_log = cond->Na_eq_log;
+  L.max_dimer_dG = cond->max_dimer_dG;
+  L.max_dG_for_K = cond->max_dG_for_K;
+  return DP_OK;
+}
+
+static void fill_scan_stats(dp_ctx* ctx, const dp_template* t, const dp_scan_job& J, const dp_sizes& S,
+                            float ms_scan, float ms_main, uint32_t launches, dp_scan_stats* stats) {
+  if (!stats) return;
+  stats->windows = count_windows(t, J);
+  stats->candidates = S.cand;
+  stats->hits = S.n_hits;
+  stats->ms_scan = ms_scan;
+  stats->ms_main = ms_main;
+  float ms_total = 0.f;
+  cudaEventElapsedTime(&ms_total, ctx->ev0, ctx->ev5);
+  stats->ms_total = ms_total;
+  stats->launches = launches;
+  stats->algo = (uint32_t)J.used_algo;
+}
+
+// scan [+ duplex] with overflow handling.  `dg` may be NULL (scan only).
+static int run_pipeline(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, const dp_dg_launch* dg,
+                        dp_sizes& S, dp_host_results& R, float* ms_scan, float* ms_main, float* ms_dg,
+                        uint32_t* scan_launches, uint32_t* dg_launches) {
+  int rc = dp_ws_hits(ctx, std::max<uint64_t>(ctx->hits_cap, 1u << 20));
+  if (rc) return rc;
+  if (dg) {
+    rc = dp_ws_dir(ctx, std::max<uint64_t>(ctx->dir_cap, 1u << 22));
+    if (rc) return rc;
+    rc = dp_ws_dimers(ctx, std::max<uint64_t>(ctx->dimers_cap, 1u << 22));
+    if (rc) return rc;
+  }
+  bool need_scan = true;
+  *ms_scan = *ms_main = *ms_dg = 0.f;
+  for (int attempt = 0;; ++attempt) {
+    if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+    if (attempt == 5) return dp_set_error(ctx, DP_ERR_STATE, "internal: result buffers keep overflowing");
+    if (need_scan) {
+      rc = scan_enqueue(ctx, J, scan_launches);
+      if (rc) return rc;
+    } else {
+      DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + DP_C_DIMERS, 0, 2 * sizeof(unsigned long long), ctx->stream));
+      DP_CUDA(ctx, cudaEventRecord(ctx->ev2, ctx->stream));
+    }
+    if (dg) {
+      rc = dp_dg_enqueue(ctx, t, *dg, 0, dg_launches);
+      if (rc) return rc;
+    }
+    DP_CUDA(ctx, cudaEventRecord(ctx->ev4, ctx->stream));
+    rc = fetch_sizes(ctx, dg != nullptr, S);
+    if (rc) return rc;
+    float ms = 0.f;
+    if (need_scan) {
+      cudaEventElapsedTime(&ms, ctx->ev1, ctx->ev2); *ms_scan += ms;
+      cudaEventElapsedTime(ms_main, ctx->ev1, ctx->ev3);
+    }
+    if (dg) { cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev4); *ms_dg += ms; }
+    if (S.saturated)
+      return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "more than 4e9 hits or duplexes in one call: lower max_mismatches or split the template");
+    if (need_scan && S.n_hits > ctx->hits_cap) {
+      rc = dp_ws_hits(ctx, S.n_hits + (S.n_hits >> 3) + 1024);
+      if (rc) return rc;
+      continue;
+    }
+    need_scan = false;
+    if (dg && (S.n_pairs > ctx->dir_cap || S.n_dimers > ctx->dimers_cap)) {
+      // (while the directory overflowed the dimer count is only a lower bound; the loop repeats)
+      if (S.n_pairs > ctx->dir_cap) { rc = dp_ws_dir(ctx, S.n_pairs + (S.n_pairs >> 3) + 1024); if (rc) return rc; }
+      if (S.n_dimers > ctx->dimers_cap) { rc = dp_ws_dimers(ctx, S.n_dimers + (S.n_dimers >> 2) + 1024); if (rc) return rc; }
+      continue;
+    }
+    break;
+  }
+  return fetch_all(ctx, dg != nullptr, S, R);
+}
+
+extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
+                       const char* const* masters, const int32_t* max_mismatches,
+                       uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
+                       dp_hit** hits_out, uint64_t* n_hits_out, dp_scan_stats* stats) {
+  if (!ctx || !t || !masters || !hits_out || !n_hits_out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *hits_out = nullptr;
+  *n_hits_out = 0;
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  dp_scan_job J;
+  int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, nullptr, J);
+  if (rc) return rc;
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  dp_sizes S;
+  dp_host_results R;
+  float ms_scan, ms_main, ms_dg;
+  uint32_t launches = 0, dg_launches = 0;
+  rc = run_pipeline(ctx, t, J, nullptr, S, R, &ms_scan, &ms_main, &ms_dg, &launches, &dg_launches);
+  if (rc) return rc;
+  rc = hits_to_abi(ctx, t, J, R.hits, S.n_hits, hits_out, nullptr);
+  if (rc) return rc;
+  *n_hits_out = S.n_hits;
+  fill_scan_stats(ctx, t, J, S, ms_scan, ms_main, launches, stats);
+  return DP_OK;
+}
+
+extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
+                       const char* const* masters, const int32_t* max_mismatches,
+                       uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
+                       const uint32_t* var_count, const uint64_t* var_offset, const char* variants,
+                       const dp_conditions* cond, dp_hit** hits_out, uint64_t* n_hits_out,
+                       dp_dimer** dimers_out, uint64_t* n_dimers_out,
+                       dp_scan_stats* stats, dp_dg_stats* dg_stats) {
+  if (!ctx || !t || !masters || !hits_out || !n_hits_out || !dimers_out || !n_dimers_out ||
+      !var_count || !var_offset || !variants || !cond)
+    return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *hits_out = nullptr; *n_hits_out = 0;
+  *dimers_out = nullptr; *n_dimers_out = 0;
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (dg_stats) memset(dg_stats, 0, sizeof *dg_stats);
+  if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
+  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  dp_scan_job J;
+  int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, var_count, J);
+  if (rc) return rc;
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  // variants of every primer, as plane codes
+  uint64_t var_bytes = 0;
+  for (uint32_t p = 0; p < n_primers; ++p) {
+    uint64_t L = strlen(masters[p]);
+    var_bytes = std::max<uint64_t>(var_bytes, var_offset[p] + (uint64_t)var_count[p] * L);
+    if (var_offset[p] + (uint64_t)var_count[p] * L > 0xFFFFFFFFull)
+      return dp_set_error(ctx, DP_ERR_ARG, "variant blob larger than 4 GB");
+  }
+  rc = upload_codes(ctx, variants, var_bytes);
+  if (rc) return rc;
+  dp_dg_launch DL;
+  fill_dg_launch(ctx, cond, DL);
+  for (size_t p = 0; p < J.pats.size(); ++p) {
+    DL.plan.pat_len[p] = (uint8_t)J.pats[p].len;
+    DL.plan.pat_strand[p] = J.pats[p].strand;
+    DL.plan.pat_primer[p] = (uint8_t)J.pats[p].primer;
+  }
+  for (uint32_t p = 0; p < n_primers; ++p) {
+    DL.plan.var_count[p] = var_count[p];
+    DL.plan.var_off[p] = (uint32_t)var_offset[p];
+  }
+  dp_sizes S;
+  dp_host_results R;
+  float ms_scan, ms_main, ms_dg;
+  uint32_t launches = 0, dg_launches = 0;
+  rc = run_pipeline(ctx, t, J, &DL, S, R, &ms_scan, &ms_main, &ms_dg, &launches, &dg_launches);
+  if (rc) return rc;
+  std::vector<uint32_t> order;
+  rc = hits_to_abi(ctx, t, J, R.hits, S.n_hits, hits_out, &order);
+  if (rc) return rc;
+  *n_hits_out = S.n_hits;
+  const dp_hit* hits = *hits_out;
+  rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return var_count[hits[i].primer]; }, dimers_out, n_dimers_out);
+  if (rc) { free(*hits_out); *hits_out = nullptr; *n_hits_out = 0; return rc; }
+  fill_scan_stats(ctx, t, J, S, ms_scan, ms_main, launches, stats);
+  if (dg_stats) {
+    dg_stats->duplexes = S.n_pairs;
+    dg_stats->dimers_tried = S.tried;
+    dg_stats->dimers_kept = *n_dimers_out;
+    dg_stats->ms_kernel = ms_dg;
+    cudaEventElapsedTime(&dg_stats->ms_total, ctx->ev2, ctx->ev5);
+    dg_stats->launches = dg_launches;
+  }
+  return DP_OK;
+}
+
+// Duplex stage alone, on hits handed back by the caller (the reference's optimiser
+// re-runs it per step under new conditions, DegenPrimer/PCR_Optimizer.py:162-169).
+extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hits, uint64_t n_hits,
+                            uint32_t n_primers, const uint8_t* primer_len, const uint32_t* var_count,
+                            const uint64_t* var_offset, const char* variants, const dp_conditions* cond,
+                            dp_dimer** dimers_out, uint64_t* n_dimers_out, dp_dg_stats* stats) {
+  if (!ctx || !t || !cond || !dimers_out || !n_dimers_out || (n_hits && !hits) ||
+      (n_primers && (!primer_len || !var_count || !var_offset || !variants)))
+    return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *dimers_out = nullptr;
+  *n_dimers_out = 0;
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
+  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  if (n_hits == 0) { *dimers_out = (dp_dimer*)malloc(sizeof(dp_dimer)); return DP_OK; }
+  if (n_hits > 0xF0000000ull) return dp_set_error(ctx, DP_ERR_ARG, "more than 4e9 hits in one call");
+  if (n_primers > DP_MAX_PRIMERS) return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  uint64_t var_bytes = 0;
+  for (uint32_t p = 0; p < n_primers; ++p) {
+    if (primer_len[p] == 0 || primer_len[p] > DP_MAX_PRIMER_LEN)
+      return dp_set_error(ctx, DP_ERR_ARG, "primer %u: length outside [1,%d]", p, DP_MAX_PRIMER_LEN);
+    var_bytes = std::max<uint64_t>(var_bytes, var_offset[p] + (uint64_t)var_count[p] * primer_len[p]);
+  }
+  if (var_bytes > 0xFFFFFFFFull) return dp_set_error(ctx, DP_ERR_ARG, "variant blob larger than 4 GB");
+  int rc = upload_codes(ctx, variants, var_bytes);
+  if (rc) return rc;
+  dp_dg_launch DL;
+  fill_dg_launch(ctx, cond, DL);
+  for (uint32_t p = 0; p < n_primers; ++p) {
+    for (int s = 0; s < 2; ++s) {
+      DL.plan.pat_len[2 * p + s] = primer_len[p];
+      DL.plan.pat_strand[2 * p + s] = (uint8_t)s;
+      DL.plan.pat_primer[2 * p + s] = (uint8_t)p;
+    }
+    DL.plan.var_count[p] = var_count[p];
+    DL.plan.var_off[p] = (uint32_t)var_offset[p];
+  }
+  // raw hits in the caller's order
+  rc = dp_ws_hits(ctx, std::max<uint64_t>(std::max<uint64_t>(ctx->hits_cap, 1u << 20), n_hits));
+  if (rc) return rc;
+  rc = dp_ws_pinned(ctx, DP_RES_SPEC_END + var_bytes + n_hits * sizeof(dp_raw_hit) + 64);
+  if (rc) return rc;
+  dp_raw_hit* raw = (dp_raw_hit*)(ctx->h_res + ((DP_RES_SPEC_END + var_bytes + 63) & ~(size_t)63));
+  uint64_t pairs = 0;
+  for (uint64_t h = 0; h < n_hits; ++h) {
+    const dp_hit& x = hits[h];
+    if (x.primer >= n_primers) return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: primer %u out of range", (unsigned long long)h, x.primer);
+    if (x.record >= t->records.size()) return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: record out of range", (unsigned long long)h);
+    const dp_record& rec = t->records[x.record];
+    const uint32_t L = primer_len[x.primer];
+    if (x.pos + L > rec.len) return dp_set_error(ctx, DP_ERR_ARG, "hit %llu: window outside its record", (unsigned long long)h);
+    raw[h].g = rec.start + (x.strand ? rec.len - L - x.pos : x.pos);
+    raw[h].record = x.record;
+    raw[h].pattern = (uint16_t)(2 * x.primer + (x.strand ? 1 : 0));
+    raw[h].score3 = x.score3;
+    raw[h].pair_base = (uint32_t)pairs;
+    raw[h].reserved = 0;
+    pairs += var_count[x.primer];
+    if (pairs > 0xF0000000ull) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "more than 4e9 (hit, variant) duplexes in one call");
+  }
+  rc = dp_ws_dir(ctx, std::max<uint64_t>(std::max<uint64_t>(ctx->dir_cap, 1u << 22), pairs));
+  if (rc) return rc;
+  rc = dp_ws_dimers(ctx, std::max<uint64_t>(ctx->dimers_cap, 1u << 22));
+  if (rc) return rc;
+  cudaStream_t st = ctx->stream;
+  unsigned long long* hc = (unsigned long long*)ctx->h_res + 8;     // behind the counter read-back area
+  for (int i = 0; i < 8; ++i) hc[i] = 0;
+  hc[DP_C_HITS] = n_hits | (pairs << 32);
+  DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_hits, raw, n_hits * sizeof(dp_raw_hit), cudaMemcpyHostToDevice, st));
+  dp_sizes S;
+  dp_host_results R;
+  float ms_dg = 0.f;
+  uint32_t launches = 0;
+  for (int attempt = 0;; ++attempt) {
+    if (attempt == 4) return dp_set_error(ctx, DP_ERR_STATE, "internal: dimer buffer keeps overflowing");
+    DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
+    DP_CUDA(ctx, cudaEventRecord(ctx->ev2, st));
+    rc = dp_dg_enqueue(ctx, t, DL, pairs, &launches);
+    if (rc) return rc;
+    DP_CUDA(ctx, cudaEventRecord(ctx->ev4, st));
+    // only directory + dimers are wanted back; the hit prefix copy is harmless
+    rc = fetch_sizes(ctx, true, S);
+    if (rc) return rc;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev4);
+    ms_dg += ms;
+    if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+    if (S.n_dimers > ctx->dimers_cap) {
+      rc = dp_ws_dimers(ctx, S.n_dimers + (S.n_dimers >> 3) + 1024);
+      if (rc) return rc;
+      continue;
+    }
+    break;
+  }
+  // the raw hits are still in pinned memory; fetch_all would overwrite them when it
+  // has to grow the buffer, so keep a private copy of what assembly needs
+  std::vector<dp_raw_hit> raw_copy(raw, raw + n_hits);
+  S.n_hits = 0;                          // nothing to copy back for the hits
+  rc = fetch_all(ctx, true, S, R);
+  if (rc) return rc;
+  R.hits = raw_copy.data();
+  std::vector<uint32_t> order(n_hits);
+  for (uint64_t i = 0; i < n_hits; ++i) order[i] = (uint32_t)i;
+  rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return var_count[hits[i].primer]; }, dimers_out, n_dimers_out);
+  if (rc) return rc;
   if (stats) {
-    uint64_t windows = 0;
-    for (auto& p : pats)
-      for (auto& rec : t->records)
-        if (rec.len >= p.len) windows += rec.len - p.len + 1;
-    stats->windows = windows;
-    stats->candidates = h_counters[1];
-    stats->hits = n;
-    stats->ms_scan = ms_scan;
-    stats->ms_main = ms_main;
-    cudaEventRecord(ev_k1, ctx->stream);
-    cudaEventSynchronize(ev_k1);
-    float ms_total = 0.f;
-    cudaEventElapsedTime(&ms_total, ev_begin, ev_k1);
-    stats->ms_total = ms_total;
+    stats->duplexes = pairs;
+    stats->dimers_tried = S.tried;
+    stats->dimers_kept = *n_dimers_out;
+    stats->ms_kernel = ms_dg;
+    cudaEventElapsedTime(&stats->ms_total, ctx->ev0, ctx->ev5);
     stats->launches = launches;
-    stats->algo = (uint32_t)used_algo;
   }
   return DP_OK;
 }

@@ -1,8 +1,6 @@
-// Scan: shared device structures (patterns in constant memory, exact verify).
+// Scan: shared device structures (patterns as kernel parameters, exact verify).
 #pragma once
 #include "dp_internal.cuh"
-
-#define DP_MAX_PATTERNS (2 * DP_MAX_PRIMERS)
 
 // One (primer, strand) pattern.  Masks are indexed by plane code (A C T G) and
 // cover primer positions 0..63 (two words, bit j = position j of the WINDOW on
@@ -17,14 +15,17 @@ struct dp_pattern {
   uint16_t primer;
   uint8_t strand;
   uint8_t has_half;
+  uint32_t n_var;      // unambiguous variants of the primer (duplex pairs per hit)
+  uint32_t reserved;
 };
 
-// raw hit as written by the kernels (padded-concatenation coordinates)
-struct dp_raw_hit {
-  uint64_t g;          // forward window start in the padded concatenation
-  uint32_t record;
-  uint16_t pattern;
-  uint16_t score3;
+// The patterns of a call travel as a __grid_constant__ kernel parameter (constant
+// bank 0, uniform LDC access, no symbol upload, nothing shared between contexts).
+// Two capacities so that the common 1-4 primer call ships < 1 KB per launch.
+#define DP_NP_SMALL 8
+template <int NP>
+struct dp_pattern_set {
+  dp_pattern pat[NP];
 };
 
 struct dp_scan_args {
@@ -42,11 +43,10 @@ struct dp_scan_args {
   uint64_t seg_end;
   dp_raw_hit* hits;
   uint64_t hits_cap;
-  unsigned long long* counters;   // [0] hits wanted, [1] candidates verified
+  unsigned long long* counters;   // DP_C_* slots
+  const dp_exc_run* runs;         // exception runs (sorted) for the run-boundary pass
+  uint64_t n_runs;
 };
-
-// defined once: this header is included by dp_scan.cu only
-__constant__ dp_pattern c_patterns[DP_MAX_PATTERNS];
 
 __device__ __forceinline__ uint32_t dp_mux4(uint32_t hi, uint32_t lo, uint32_t a, uint32_t c,
                                             uint32_t t, uint32_t g) {
@@ -86,15 +86,44 @@ __device__ __forceinline__ uint32_t dp_find_record(const uint64_t* rec_start, ui
 }
 
 __device__ __forceinline__ void dp_emit_hit(const dp_scan_args& A, uint64_t g, uint32_t pat,
-                                            uint32_t len, uint32_t score) {
+                                            uint32_t len, uint32_t score, uint32_t n_var) {
   if (g < A.seg_begin || g >= A.seg_end) return;
   uint32_t r = dp_find_record(A.rec_start, A.n_records, g);
   uint64_t off = g - A.rec_start[r];
   if (off + len > A.rec_len[r]) return;          // window runs past its record
-  unsigned long long slot = atomicAdd(&A.counters[0], 1ull);
+  // one packed atomic hands out the slot (low half) and the first (hit, variant)
+  // pair index (high half) together, so pair_base is monotone in slot
+  const unsigned long long seen = *(volatile unsigned long long*)&A.counters[DP_C_HITS];
+  if ((uint32_t)seen > 0xF0000000u || (seen >> 32) > 0xF0000000ull) {
+    A.counters[DP_C_SATURATED] = 1ull;
+    return;
+  }
+  const unsigned long long old = atomicAdd(&A.counters[DP_C_HITS], 1ull | ((unsigned long long)n_var << 32));
+  const uint32_t slot = (uint32_t)old;
   if (slot < A.hits_cap) {
     dp_raw_hit h;
     h.g = g; h.record = r; h.pattern = (uint16_t)pat; h.score3 = (uint16_t)score;
+    h.pair_base = (uint32_t)(old >> 32); h.reserved = 0;
     A.hits[slot] = h;
   }
+}
+
+// exact verify of window g against pattern P (index pat); with_exc = false leaves
+// windows that touch a non-ACGT base to the run-boundary pass
+__device__ __forceinline__ void dp_verify_window(const dp_scan_args& A, const dp_pattern& P, uint64_t g,
+                                                 uint32_t pat, bool with_exc) {
+  const uint64_t wi = g >> 5;
+  const int sh = (int)(g & 31);
+  uint32_t whi[2], wlo[2], wex[2];
+  {
+    const uint32_t a0 = __ldg(A.hi + wi), a1 = __ldg(A.hi + wi + 1), a2 = __ldg(A.hi + wi + 2);
+    whi[0] = __funnelshift_r(a0, a1, sh); whi[1] = __funnelshift_r(a1, a2, sh);
+    const uint32_t b0 = __ldg(A.lo + wi), b1 = __ldg(A.lo + wi + 1), b2 = __ldg(A.lo + wi + 2);
+    wlo[0] = __funnelshift_r(b0, b1, sh); wlo[1] = __funnelshift_r(b1, b2, sh);
+    const uint32_t e0 = __ldg(A.exc + wi), e1 = __ldg(A.exc + wi + 1), e2 = __ldg(A.exc + wi + 2);
+    wex[0] = __funnelshift_r(e0, e1, sh); wex[1] = __funnelshift_r(e1, e2, sh);
+  }
+  if (!with_exc && ((wex[0] & P.lmask[0]) | (wex[1] & P.lmask[1]))) return;
+  const uint32_t s = dp_score3<2>(P, whi, wlo, wex);
+  if (s >= P.thr3) dp_emit_hit(A, g, pat, P.len, s, P.n_var);
 }

@@ -33,7 +33,10 @@ struct dp_bs_pattern {
   uint32_t pattern;                 // index into c_patterns
 };
 
-__constant__ dp_bs_pattern c_bs[DP_MAX_PATTERNS];
+template <int NP>
+struct dp_bs_set {
+  dp_bs_pattern bs[NP];
+};
 
 struct dp_bitslice_plan {
   int K, E;
@@ -103,9 +106,10 @@ __device__ __forceinline__ uint32_t dp_count_ge(const uint32_t* in) {
   return ge | eq;
 }
 
-template <int K, int E>
+template <int K, int E, int NP>
 __global__ void __launch_bounds__(DP_BS_THREADS, 3)
-dp_scan_bitslice_kernel(dp_scan_args A, uint32_t n_bs) {
+dp_scan_bitslice_kernel(const __grid_constant__ dp_scan_args A, const __grid_constant__ dp_pattern_set<NP> PS,
+                        const __grid_constant__ dp_bs_set<NP> BS, uint32_t n_bs) {
   constexpr int J = 8 + 2 * K;
   constexpr int NT = J + E;
   constexpr int THR = J - K;
@@ -129,7 +133,7 @@ dp_scan_bitslice_kernel(dp_scan_args A, uint32_t n_bs) {
     }
 #pragma unroll 1
     for (uint32_t p = 0; p < n_bs; ++p) {
-      const dp_bs_pattern& bp = c_bs[p];
+      const dp_bs_pattern& bp = BS.bs[p];
       uint32_t x[NT];
 #pragma unroll
       for (int t = 0; t < NT; ++t)
@@ -143,25 +147,11 @@ dp_scan_bitslice_kernel(dp_scan_args A, uint32_t n_bs) {
         if (q < bp.anchor) continue;
         const uint64_t g = q - bp.anchor;
         if (g < A.seg_begin || g >= A.seg_end) continue;
-        const dp_pattern& P = c_patterns[bp.pattern];
-        const uint64_t wi = g >> 5;
-        const int sh = (int)(g & 31);
-        uint32_t whi[2], wlo[2], wex[2];
-        {
-          const uint32_t a0 = __ldg(A.hi + wi), a1 = __ldg(A.hi + wi + 1), a2 = __ldg(A.hi + wi + 2);
-          whi[0] = __funnelshift_r(a0, a1, sh); whi[1] = __funnelshift_r(a1, a2, sh);
-          const uint32_t b0 = __ldg(A.lo + wi), b1 = __ldg(A.lo + wi + 1), b2 = __ldg(A.lo + wi + 2);
-          wlo[0] = __funnelshift_r(b0, b1, sh); wlo[1] = __funnelshift_r(b1, b2, sh);
-          const uint32_t e0 = __ldg(A.exc + wi), e1 = __ldg(A.exc + wi + 1), e2 = __ldg(A.exc + wi + 2);
-          wex[0] = __funnelshift_r(e0, e1, sh); wex[1] = __funnelshift_r(e1, e2, sh);
-        }
-        if ((wex[0] & P.lmask[0]) | (wex[1] & P.lmask[1])) continue;   // kernel 1 (only_exc) owns it
-        const uint32_t s = dp_score3<2>(P, whi, wlo, wex);
-        if (s >= P.thr3) dp_emit_hit(A, g, bp.pattern, P.len, s);
+        dp_verify_window(A, PS.pat[bp.pattern], g, bp.pattern, false);
       }
     }
   }
-  if (n_cand) atomicAdd(&A.counters[1], n_cand);
+  if (n_cand) atomicAdd(&A.counters[DP_C_CAND], n_cand);
 }
 
 // ---- host: anchor choice -----------------------------------------------------------
@@ -249,32 +239,43 @@ static bool dp_bitslice_make_plan(const std::vector<dp_pattern>& pats,
   return plan.n > 0;
 }
 
-template <int K, int E>
-static int dp_bitslice_launch_one(dp_ctx* ctx, const dp_scan_args& A, uint32_t n_bs) {
+template <int K, int E, int NP>
+static int dp_bitslice_launch_one(dp_ctx* ctx, const dp_scan_args& A, const std::vector<dp_pattern>& pats,
+                                  const dp_bitslice_plan& plan) {
   constexpr int J = 8 + 2 * K;
   const size_t smem = (size_t)(4 * J + 1) * DP_BS_THREADS * sizeof(uint32_t);
-  static bool configured = false;
-  if (!configured) {
-    DP_CUDA(ctx, cudaFuncSetAttribute(dp_scan_bitslice_kernel<K, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+  static bool configured[16] = {false};      // per device
+  static int per_sm_cached[16] = {0};
+  const int dev = ctx->device & 15;
+  if (!configured[dev]) {
+    DP_CUDA(ctx, cudaFuncSetAttribute(dp_scan_bitslice_kernel<K, E, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    DP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_scan_bitslice_kernel<K, E, NP>, DP_BS_THREADS, smem));
+    per_sm_cached[dev] = per_sm < 1 ? 1 : per_sm;
+    configured[dev] = true;
   }
+  dp_pattern_set<NP> PS;
+  dp_bs_set<NP> BS;
+  memset(&PS, 0, sizeof PS);
+  memset(&BS, 0, sizeof BS);
+  memcpy(PS.pat, pats.data(), pats.size() * sizeof(dp_pattern));
+  memcpy(BS.bs, plan.pats.data(), plan.pats.size() * sizeof(dp_bs_pattern));
   const uint64_t words = A.word_end + 2 - A.word_begin;
-  int per_sm = 1;
-  DP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_scan_bitslice_kernel<K, E>, DP_BS_THREADS, smem));
-  if (per_sm < 1) per_sm = 1;
   unsigned blocks = (unsigned)std::min<uint64_t>((words + DP_BS_THREADS - 1) / DP_BS_THREADS,
-                                                 (uint64_t)ctx->sm_count * per_sm);
-  dp_scan_bitslice_kernel<K, E><<<blocks, DP_BS_THREADS, smem, ctx->stream>>>(A, n_bs);
+                                                 (uint64_t)ctx->sm_count * per_sm_cached[dev]);
+  dp_scan_bitslice_kernel<K, E, NP><<<blocks, DP_BS_THREADS, smem, ctx->stream>>>(A, PS, BS, plan.n);
   DP_CUDA(ctx, cudaGetLastError());
   return DP_OK;
 }
 
-static int dp_bitslice_launch(dp_ctx* ctx, const dp_scan_args& A, const dp_bitslice_plan& plan, uint32_t* launches) {
-  DP_CUDA(ctx, cudaMemcpyToSymbolAsync(c_bs, plan.pats.data(), plan.pats.size() * sizeof(dp_bs_pattern), 0,
-                                       cudaMemcpyHostToDevice, ctx->stream));
+static int dp_bitslice_launch(dp_ctx* ctx, const dp_scan_args& A, const std::vector<dp_pattern>& pats,
+                              const dp_bitslice_plan& plan, uint32_t* launches) {
   int rc = DP_ERR_ARG;
-#define DP_BS_CASE(KK, EE) \
-  if (plan.K == KK && plan.E == EE) rc = dp_bitslice_launch_one<KK, EE>(ctx, A, plan.n);
+  const bool small = pats.size() <= DP_NP_SMALL;
+#define DP_BS_CASE(KK, EE)                                                                        \
+  if (plan.K == KK && plan.E == EE)                                                               \
+    rc = small ? dp_bitslice_launch_one<KK, EE, DP_NP_SMALL>(ctx, A, pats, plan)                  \
+               : dp_bitslice_launch_one<KK, EE, DP_MAX_PATTERNS>(ctx, A, pats, plan);
 #define DP_BS_ROW(KK) DP_BS_CASE(KK, 0) DP_BS_CASE(KK, 2) DP_BS_CASE(KK, 4) DP_BS_CASE(KK, 8)
   DP_BS_ROW(0) DP_BS_ROW(1) DP_BS_ROW(2) DP_BS_ROW(3) DP_BS_ROW(4)
 #undef DP_BS_ROW

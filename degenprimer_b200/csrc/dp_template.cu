@@ -139,6 +139,7 @@ static int ensure_stage(dp_ctx* ctx) {
     DP_CUDA(ctx, cudaMallocHost(&ctx->h_stage[i], DP_STAGE_BYTES));
     DP_CUDA(ctx, cudaMalloc(&ctx->d_stage[i], DP_STAGE_BYTES));
     DP_CUDA(ctx, cudaEventCreateWithFlags(&ctx->stage_ev[i], cudaEventDisableTiming));
+    DP_CUDA(ctx, cudaEventCreateWithFlags(&ctx->stage_copied[i], cudaEventDisableTiming));
   }
   ctx->stage_bytes = DP_STAGE_BYTES;
   return DP_OK;
@@ -151,12 +152,14 @@ static bool is_pinned(const void* p) {
 }
 
 static void free_template_device(dp_template* t) {
-  if (t->d_lo) cudaFree(t->d_lo);
-  if (t->d_hi) cudaFree(t->d_hi);
-  if (t->d_exc) cudaFree(t->d_exc);
-  if (t->d_rec_start) cudaFree(t->d_rec_start);
-  if (t->d_rec_len) cudaFree(t->d_rec_len);
-  if (t->d_runs) cudaFree(t->d_runs);
+  // stream-ordered: safe while earlier kernels on ctx->stream still read the planes
+  dp_ctx* ctx = t->ctx;
+  dp_pool_free(ctx, t->d_lo);
+  dp_pool_free(ctx, t->d_hi);
+  dp_pool_free(ctx, t->d_exc);
+  dp_pool_free(ctx, t->d_rec_start);
+  dp_pool_free(ctx, t->d_rec_len);
+  dp_pool_free(ctx, t->d_runs);
   t->d_lo = t->d_hi = t->d_exc = nullptr;
   t->d_rec_start = t->d_rec_len = nullptr;
   t->d_runs = nullptr;
@@ -164,41 +167,56 @@ static void free_template_device(dp_template* t) {
 
 // Streams the records of `t` (layout already decided: t->records[r].start/len)
 // to the device and packs them.  One attempt with a given boundary capacity.
+// Chunks travel on ctx->copy_stream while the previous chunk is packed on
+// ctx->stream (two staging slots, events both ways); pinned sources are never
+// touched by the host.
 static int pack_once(dp_ctx* ctx, dp_template* t, const char* const* seqs, uint64_t bounds_cap,
                      unsigned long long* d_bounds, unsigned long long* h_counters) {
   const uint32_t n_records = (uint32_t)t->records.size();
   unsigned long long init[2] = {0ull, ~0ull};
-  DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  unsigned long long* d_cnt = ctx->d_counters + DP_C_PACK0;
+  DP_CUDA(ctx, cudaMemcpyAsync(d_cnt, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  // the copy stream must not overwrite a staging slot (or start) before what is
+  // already queued on the main stream has finished with it
+  DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[0], ctx->stream));
+  DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[1], ctx->stream));
   int slot = 0;
-  bool slot_used[2] = {false, false};
-  // (a) pinned sources: copy straight from the caller's buffer, one record at a time
-  // (b) pageable sources: gather bytes at their padded offsets into a pinned chunk
+  bool h_busy[2] = {false, false};   // h_stage[slot] has an H2D in flight
   uint64_t chunk_word0 = 0;       // padded word offset of the current gather chunk
   size_t chunk_fill = 0;          // bytes placed so far (padded layout)
   uint32_t chunk_prev = DP_PAD_BYTE;
   char* hbuf = nullptr;
+  // src (pinned host memory) -> d_stage[slot] -> planes
+  auto ship = [&](const char* src, uint64_t n_bytes, uint64_t word0, uint32_t prev, bool from_stage) -> int {
+    DP_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->stage_ev[slot], 0));
+    DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage[slot], src, n_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    DP_CUDA(ctx, cudaEventRecord(ctx->stage_copied[slot], ctx->copy_stream));
+    if (from_stage) h_busy[slot] = true;
+    DP_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->stage_copied[slot], 0));
+    uint64_t nw = (n_bytes + 31) / 32;
+    dp_pack_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, ctx->stream>>>(
+        (const uint8_t*)ctx->d_stage[slot], n_bytes, nw, word0, prev,
+        t->d_lo, t->d_hi, t->d_exc, d_bounds, bounds_cap, d_cnt);
+    DP_CUDA(ctx, cudaGetLastError());
+    DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
+    slot ^= 1;
+    return DP_OK;
+  };
   auto flush_gather = [&](void) -> int {
     if (!chunk_fill) return DP_OK;
     size_t n_bytes = (chunk_fill + 31) & ~(size_t)31;
     memset(hbuf + chunk_fill, DP_PAD_BYTE, n_bytes - chunk_fill);
     uint32_t last = (unsigned char)hbuf[n_bytes - 1];
-    DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage[slot], hbuf, n_bytes, cudaMemcpyHostToDevice, ctx->stream));
-    uint64_t nw = n_bytes / 32;
-    dp_pack_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, ctx->stream>>>(
-        (const uint8_t*)ctx->d_stage[slot], n_bytes, nw, chunk_word0, chunk_prev,
-        t->d_lo, t->d_hi, t->d_exc, d_bounds, bounds_cap, ctx->d_counters);
-    DP_CUDA(ctx, cudaGetLastError());
-    DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
-    slot_used[slot] = true;
-    chunk_word0 += nw;
+    int rc = ship(hbuf, n_bytes, chunk_word0, chunk_prev, true);
+    if (rc) return rc;
+    chunk_word0 += n_bytes / 32;
     chunk_fill = 0;
     chunk_prev = last;
-    slot ^= 1;
     hbuf = nullptr;
     return DP_OK;
   };
   auto acquire = [&](void) -> int {
-    if (slot_used[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[slot]));
+    if (h_busy[slot]) { DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_copied[slot])); h_busy[slot] = false; }
     hbuf = ctx->h_stage[slot];
     return DP_OK;
   };
@@ -210,21 +228,12 @@ static int pack_once(dp_ctx* ctx, dp_template* t, const char* const* seqs, uint6
     if (rec.len >= (1u << 20) && is_pinned(src)) {
       int rc = flush_gather();
       if (rc) return rc;
-      // device-side chunks straight from the pinned source
       uint64_t done = 0;
       uint32_t prev = DP_PAD_BYTE;
       while (done < rec.len) {
         uint64_t n = std::min<uint64_t>(DP_STAGE_BYTES, rec.len - done);
-        if (slot_used[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[slot]));
-        DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage[slot], src + done, n, cudaMemcpyHostToDevice, ctx->stream));
-        uint64_t nw = (n + 31) / 32;
-        dp_pack_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, ctx->stream>>>(
-            (const uint8_t*)ctx->d_stage[slot], n, nw, rec.start / 32 + done / 32, prev,
-            t->d_lo, t->d_hi, t->d_exc, d_bounds, bounds_cap, ctx->d_counters);
-        DP_CUDA(ctx, cudaGetLastError());
-        DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
-        slot_used[slot] = true;
-        slot ^= 1;
+        rc = ship(src + done, n, rec.start / 32 + done / 32, prev, false);
+        if (rc) return rc;
         prev = (unsigned char)src[done + n - 1];
         done += n;
       }
@@ -258,8 +267,9 @@ static int pack_once(dp_ctx* ctx, dp_template* t, const char* const* seqs, uint6
   uint64_t nguard = guard_to - t->n_words;
   dp_fill_guard_kernel<<<(unsigned)((nguard + 255) / 256), 256, 0, ctx->stream>>>(t->d_lo, t->d_hi, t->d_exc, t->n_words, guard_to);
   DP_CUDA(ctx, cudaGetLastError());
-  DP_CUDA(ctx, cudaMemcpyAsync(h_counters, ctx->d_counters, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+  DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res, d_cnt, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
   DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(h_counters, ctx->h_res, 2 * sizeof(unsigned long long));
   return DP_OK;
 }
 
@@ -280,21 +290,21 @@ int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
   t->n_words = w;
   t->n_words_alloc = w + DP_GUARD_WORDS;
   size_t plane_bytes = (size_t)t->n_words_alloc * sizeof(uint32_t);
-  DP_CUDA(ctx, cudaMalloc(&t->d_lo, plane_bytes));
-  DP_CUDA(ctx, cudaMalloc(&t->d_hi, plane_bytes));
-  DP_CUDA(ctx, cudaMalloc(&t->d_exc, plane_bytes));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_lo, plane_bytes));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_hi, plane_bytes));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_exc, plane_bytes));
   t->device_bytes = 3 * plane_bytes;
 
   uint64_t cap = std::max<uint64_t>(1u << 16, t->total_bases / 64);
   std::vector<unsigned long long> bounds;
   for (int attempt = 0;; ++attempt) {
     unsigned long long* d_bounds = nullptr;
-    DP_CUDA(ctx, cudaMalloc(&d_bounds, cap * sizeof(unsigned long long)));
+    DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&d_bounds, cap * sizeof(unsigned long long)));
     unsigned long long h_counters[2] = {0, 0};
     rc = pack_once(ctx, t, seqs, cap, d_bounds, h_counters);
-    if (rc) { cudaFree(d_bounds); return rc; }
+    if (rc) { dp_pool_free(ctx, d_bounds); return rc; }
     if (h_counters[1] != ~0ull) {
-      cudaFree(d_bounds);
+      dp_pool_free(ctx, d_bounds);
       uint64_t g = h_counters[1];
       uint32_t r = 0;
       while (r + 1 < n_records && t->records[r + 1].start <= g) ++r;
@@ -304,15 +314,15 @@ int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
                           r, (unsigned long long)off, c, (c >= 32 && c < 127) ? c : '?');
     }
     if (h_counters[0] > cap) {
-      if (attempt) { cudaFree(d_bounds); return dp_set_error(ctx, DP_ERR_STATE, "internal: boundary list overflow twice"); }
-      cudaFree(d_bounds);
+      if (attempt) { dp_pool_free(ctx, d_bounds); return dp_set_error(ctx, DP_ERR_STATE, "internal: boundary list overflow twice"); }
+      dp_pool_free(ctx, d_bounds);
       cap = h_counters[0];
       continue;
     }
     bounds.resize(h_counters[0]);
     if (!bounds.empty())
       DP_CUDA(ctx, cudaMemcpy(bounds.data(), d_bounds, bounds.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-    cudaFree(d_bounds);
+    dp_pool_free(ctx, d_bounds);
     break;
   }
   std::sort(bounds.begin(), bounds.end());
@@ -329,16 +339,17 @@ int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
     if (run.end > run.start) t->runs.push_back(run);
   }
   size_t nr = t->runs.size();
-  DP_CUDA(ctx, cudaMalloc(&t->d_runs, std::max<size_t>(1, nr) * sizeof(dp_exc_run)));
-  if (nr) DP_CUDA(ctx, cudaMemcpy(t->d_runs, t->runs.data(), nr * sizeof(dp_exc_run), cudaMemcpyHostToDevice));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_runs, std::max<size_t>(1, nr) * sizeof(dp_exc_run)));
   std::vector<uint64_t> starts(n_records), rl(n_records);
   for (uint32_t r = 0; r < n_records; ++r) { starts[r] = t->records[r].start; rl[r] = t->records[r].len; }
-  DP_CUDA(ctx, cudaMalloc(&t->d_rec_start, std::max<size_t>(1, n_records) * sizeof(uint64_t)));
-  DP_CUDA(ctx, cudaMalloc(&t->d_rec_len, std::max<size_t>(1, n_records) * sizeof(uint64_t)));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_rec_start, std::max<size_t>(1, n_records) * sizeof(uint64_t)));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_rec_len, std::max<size_t>(1, n_records) * sizeof(uint64_t)));
+  if (nr) DP_CUDA(ctx, cudaMemcpyAsync(t->d_runs, t->runs.data(), nr * sizeof(dp_exc_run), cudaMemcpyHostToDevice, ctx->stream));
   if (n_records) {
-    DP_CUDA(ctx, cudaMemcpy(t->d_rec_start, starts.data(), n_records * sizeof(uint64_t), cudaMemcpyHostToDevice));
-    DP_CUDA(ctx, cudaMemcpy(t->d_rec_len, rl.data(), n_records * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_start, starts.data(), n_records * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_len, rl.data(), n_records * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
   }
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));    // starts/rl/runs are pageable host memory
   t->device_bytes += nr * sizeof(dp_exc_run) + 2 * n_records * sizeof(uint64_t);
   return DP_OK;
 }
@@ -442,7 +453,7 @@ int dp_template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out) {
 
 void dp_template_free(dp_template* t) {
   if (!t) return;
-  if (t->ctx) { cudaSetDevice(t->ctx->device); cudaStreamSynchronize(t->ctx->stream); }
+  if (t->ctx) cudaSetDevice(t->ctx->device);
   free_template_device(t);
   delete t;
 }
@@ -478,13 +489,13 @@ int dp_template_unpack(dp_ctx* ctx, const dp_template* t, uint32_t r, uint64_t b
   if (n == 0) return DP_OK;
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
   char* d_out = nullptr;
-  DP_CUDA(ctx, cudaMalloc(&d_out, n));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&d_out, n));
   dp_unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(
       t->d_lo, t->d_hi, t->d_exc, t->d_runs, t->runs.size(), rec.start, rec.len, begin, n, reverse, d_out);
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, n, cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-  cudaFree(d_out);
+  dp_pool_free(ctx, d_out);
   if (e != cudaSuccess) return dp_set_error(ctx, DP_ERR_CUDA, "unpack: %s", cudaGetErrorString(e));
   return DP_OK;
 }

@@ -73,6 +73,11 @@ int dp_abort_requested(dp_ctx* ctx, int flag);
 /* Device properties for the bench / roofline (name is a 256-byte buffer). */
 int dp_device_info(dp_ctx* ctx, char* name, int* sm_count, int* cc_major,
                    int* cc_minor, int* clock_khz, uint64_t* hbm_bytes);
+/* The CUDA stream (cudaStream_t) every kernel and copy of this ctx is queued on:
+ * lets a caller bracket calls with its own CUDA events (bench.py wraps it in
+ * torch.cuda.ExternalStream).  dp_synchronize() waits for it. */
+void* dp_stream(dp_ctx* ctx);
+int dp_synchronize(dp_ctx* ctx);
 
 /* ---- template loader: FASTA / ASCII -> bit-planes in HBM ---------------------
  * Replaces BioUtils/BioUtils/SeqUtils.py:103-271 (SeqView over
@@ -202,6 +207,8 @@ typedef struct dp_conditions {
   double DMSO;         /* %,    only for dp_variant_tm                           */
 } dp_conditions;
 
+/* (dp_find, the fused scan + duplex call, is declared after dp_duplex_dg.) */
+
 /* One surviving dimer of one (site, variant) duplex — Dimer of
  * DegenPrimer/SecStructures.py:58-192 after Duplex._recalculate :294-324. */
 typedef struct dp_dimer {
@@ -237,6 +244,22 @@ int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hits,
                  const uint32_t* var_count, const uint64_t* var_offset,
                  const char* variants, const dp_conditions* cond,
                  dp_dimer** dimers, uint64_t* n_dimers, dp_dg_stats* stats);
+
+/* SearchEngine.find (DegenPrimer/SearchEngine.py:375-386) = find_matches +
+ * compile_duplexes_mp for every primer of the call, as ONE stream submission:
+ * scan kernels -> duplex kernel over every (hit, variant) pair (sizes stay on
+ * the device) -> one synchronise.  Same results as dp_scan followed by
+ * dp_duplex_dg: hits sorted by (primer, strand, record, pos); dimers grouped by
+ * (hit index in that order, variant), each group sorted by dG (stable).
+ * variants/var_count/var_offset as in dp_duplex_dg; primer lengths are those of
+ * `masters`. */
+int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
+            const char* const* masters, const int32_t* max_mismatches,
+            uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
+            const uint32_t* var_count, const uint64_t* var_offset,
+            const char* variants, const dp_conditions* cond,
+            dp_hit** hits, uint64_t* n_hits, dp_dimer** dimers, uint64_t* n_dimers,
+            dp_scan_stats* scan_stats, dp_dg_stats* dg_stats);
 
 /* The template window under every hit, as the reference's strand strings show
  * it (fwd_seq[pos:pos+L] / rev_seq[pos:pos+L], DegenPrimer/SearchEngine.py:113):

@@ -5,9 +5,10 @@ from degenprimer_b200.synthetic import make_workload
 from degenprimer_b200.SeqView import ResidentRecord
 from degenprimer_b200.SearchEngine import SearchEngine
 from degenprimer_b200.Primer import Primer
-from degenprimer_b200.SeqUtils import Seq, SeqRecord
+from degenprimer_b200.SeqUtils import Seq, SeqRecord, unambiguous_sequences
 from degenprimer_b200.WorkCounter import WorkCounter
 wl = make_workload('config2_tp53_chr17')
+tdf.PCR_P.set(dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=62.0))
 ctx = tdf._ctx()
 host = torch.from_numpy(wl['records'][0]).pin_memory()
 dev = torch.empty_like(host, device='cuda')
@@ -17,8 +18,8 @@ for _ in range(5): dev.copy_(host, non_blocking=True); torch.cuda.synchronize()
 dt=(time.perf_counter()-t0)/5
 print('torch pinned H2D: %.3f ms  %.1f GB/s' % (dt*1e3, host.numel()/dt/1e9))
 srcs=[(host.data_ptr(), host.numel())]
-def T(f, n=5):
-    f(); f()
+def T(f, n=10):
+    f(); f(); f()
     t0=time.perf_counter()
     for _ in range(n): r=f()
     return (time.perf_counter()-t0)/n*1e3, r
@@ -34,11 +35,13 @@ ms, m = T(lambda: se.find_matches(WorkCounter(), rec, gp[0], 1))
 print('find_matches: %.3f ms' % ms, se.last_stats['scan'])
 ms, r = T(lambda: se.compile_duplexes_mp(WorkCounter(), *m))
 print('compile_duplexes_mp: %.3f ms' % ms, se.last_stats['dg'])
+ms, r = T(lambda: se.find_duplexes(WorkCounter(), rec, gp[0], 1))
+print('find_duplexes (fused): %.3f ms' % ms, se.last_stats)
 ms, r = T(lambda: ctx.scan(t, wl['primers'], 1))
 print('ctx.scan both primers: %.3f ms' % ms, r[1])
 hits=r[0]
-from degenprimer_b200.SeqUtils import unambiguous_sequences
+var=[unambiguous_sequences(p) for p in wl['primers']]
 ms, r = T(lambda: ctx.duplex_dg(t, hits, [20,20],[1,1],[0,20], ''.join(wl['primers']), tdf.conditions()))
 print('ctx.duplex_dg: %.3f ms' % ms, r[1])
-ms, r = T(lambda: tdf.conditions())
-print('tdf.conditions(): %.3f ms' % ms)
+ms, r = T(lambda: ctx.find(t, wl['primers'], 1, var, tdf.conditions()))
+print('ctx.find fused: %.3f ms' % ms, r[2], r[3])

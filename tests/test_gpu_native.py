@@ -160,3 +160,103 @@ def test_variant_tm_matches_oracle(ctx):
     assert got.shape == want.shape
     assert np.max(np.abs(got - want)) <= 0.05     # bar from BASELINE.json north_star
     assert np.max(np.abs(got - want)) <= 1e-9
+
+
+def _two_stage(ctx, tmpl, primers, k, cond, **kw):
+    from degenprimer_b200.SeqUtils import unambiguous_sequences
+    hits, st = ctx.scan(tmpl, primers, k, **kw)
+    var = [unambiguous_sequences(m) for m in primers]
+    lens = [len(m) for m in primers]
+    offs, blob, off = [], '', 0
+    for v, L in zip(var, lens):
+        offs.append(off)
+        blob += ''.join(v)
+        off += len(v) * L
+    dimers, dst = ctx.duplex_dg(tmpl, hits, lens, [len(v) for v in var], offs, blob, cond)
+    return hits, dimers, var
+
+
+@pytest.mark.parametrize('k', [1, 3])
+def test_find_fused_equals_two_stage(ctx, k):
+    """dp_find (one stream submission) == dp_scan + dp_duplex_dg, on a multi-record
+    template with N runs and scattered IUPAC codes, primers with different V."""
+    from degenprimer_b200 import TD_Functions as tdf
+    rng = np.random.default_rng(21 + k)
+    recs = [random_dna(rng, n, 'ACGTNRY', p=[0.2485] * 4 + [0.002] * 3) for n in (30000, 500, 12000)]
+    recs[0], _ = plant_sites(rng, recs[0], PRIMERS, k, 10)
+    recs[2], _ = plant_sites(rng, recs[2], PRIMERS[:2], k, 6)
+    recs[0] = recs[0][:9000] + 'N' * 700 + recs[0][9700:]
+    cond = dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=52.0)
+    tdf.PCR_P.set(cond)
+    tmpl = ctx.template_from_sequences(recs)
+    hits, dimers, var = _two_stage(ctx, tmpl, PRIMERS, k, tdf.conditions())
+    fh, fd, st, dst = ctx.find(tmpl, PRIMERS, k, var, tdf.conditions())
+    assert np.array_equal(fh, hits)
+    assert np.array_equal(fd, dimers)
+    assert len(hits) > 20 and len(dimers) > 20
+    assert dst['duplexes'] == sum(len(var[int(h['primer'])]) for h in hits)
+    # one record only, through the segment arguments
+    b = tmpl.starts[2]
+    sh, sd, _, _ = ctx.find(tmpl, PRIMERS, k, var, tdf.conditions(), b, b + 12000)
+    sel = hits['record'] == 2
+    assert np.array_equal(sh, hits[sel])
+    assert len(sd) == int(np.isin(dimers['hit'], np.flatnonzero(sel)).sum())
+
+
+def test_large_results_and_buffer_growth(ctx):
+    """k = L: every window of both strands is a hit (threshold clamp max(1, L-k)), which
+    overflows the initial hit buffer (1 Mi records) and the speculative result prefix."""
+    from degenprimer_b200 import TD_Functions as tdf
+    rng = np.random.default_rng(33)
+    T = 600_000
+    t = random_dna(rng, T)
+    m = 'ACGTACGTACGTACGTAC'
+    L = len(m)
+    tmpl = ctx.template_from_sequences([t])
+    hits, st = ctx.scan(tmpl, [m], L)
+    # score >= 1 - 0.5: at least one matching position (or two unknown bases)
+    f, r = o2.find(t[:20000], m, L)[4:6]
+    n_f = int((hits['strand'] == 0).sum())
+    assert n_f > 500_000 and len(hits) > (1 << 20)
+    hf = hits[hits['strand'] == 0]['pos'].astype(np.int64)
+    assert np.array_equal(hf[hf <= 20000 - L], f)
+    assert np.all(np.diff(hf) > 0)
+    # fused call on the same data: > 2^20 pairs, dimers mostly filtered out
+    tdf.PCR_P.set(dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=30.0))
+    fh, fd, _, dst = ctx.find(tmpl, [m], L, [[m]], tdf.conditions())
+    assert np.array_equal(fh, hits)
+    assert dst['duplexes'] == len(hits)
+    sub = hits[:3000]
+    d2, _ = ctx.duplex_dg(tmpl, sub, [L], [1], [0], m, tdf.conditions())
+    assert np.array_equal(fd[fd['hit'] < 3000], d2)
+
+
+def test_run_boundary_windows(ctx):
+    """Windows that straddle the ends of N runs (1/3 per unknown base) against the
+    brute-force oracle: planted sites cut by runs of every short length."""
+    rng = np.random.default_rng(77)
+    m = PRIMERS[0]
+    L = len(m)
+    t = list(random_dna(rng, 40000))
+    site = 'ATATTCTACAACGGCTATCC'
+    at = 100
+    for run_len in range(1, 9):
+        for cut in (0, 3, L - run_len, L - 1):
+            t[at:at + L] = site
+            a = at + max(0, min(cut, L - 1))
+            t[a:a + run_len] = 'N' * run_len
+            at += 150
+    # adjacent runs of different letters and a run at the very start / end
+    t[at:at + L] = site
+    t[at + 5:at + 7] = 'RY'
+    t[0:2] = 'NN'
+    t[-3:] = 'NNN'
+    t = ''.join(t)
+    tmpl = ctx.template_from_sequences([t])
+    for k in (1, 2, 4):
+        ref = o2.find(t, m, k)
+        for algo in (1, 2):
+            hits, st = ctx.scan(tmpl, [m], k, algo=algo)
+            f, r = split_hits(hits, 0)
+            assert np.array_equal(f, ref[4]) and np.array_equal(r, ref[5]), (k, algo)
+        assert len(ref[4]) > 5
