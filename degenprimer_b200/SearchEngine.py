@@ -194,14 +194,11 @@ class SearchEngine(object):
         end = begin + ((tmpl.lengths[rec] + 31) // 32) * 32
         if tmpl.n_records == 1:
             begin, end = 0, 2 ** 64 - 1
-        records = primer.seq_records
-        variants = [str(r.seq) for r in records]
-        names = [r.id for r in records]
+        query, variants, names = _primer_query(primer, int(mismatches))
         with tdf.AcquireParameters():
             cond = tdf.conditions()
             T = tdf.PCR_P.PCR_T
-            hits, dimers, st, dst = tmpl.ctx.find(tmpl, [str(primer.master_sequence.seq)], int(mismatches),
-                                                  [variants], cond, begin, end)
+            hits, dimers, st, dst = tmpl.ctx.find(tmpl, query, cond=cond, seg_begin=begin, seg_end=end)
         self.last_stats['scan'] = st
         self.last_stats['dg'] = dst
         if len(hits) and not (hits['record'] == rec).all():
@@ -310,6 +307,25 @@ class SearchEngine(object):
                 results[result[0]] = result[1]
             counter.count()
         return results
+
+
+def _primer_query(primer, mismatches):
+    """(native Query, variant strings, variant names) of a primer, cached on the primer
+    object: the reference calls `find` once per template with the same Primer."""
+    cache = getattr(primer, '_dp_query_cache', None)
+    master = str(primer.master_sequence.seq)
+    key = (master, mismatches, primer.num_components)
+    if cache is not None and cache[0] == key:
+        return cache[1]
+    records = primer.seq_records
+    variants = [str(r.seq) for r in records]
+    names = [r.id for r in records]
+    value = (nat.Query([master], mismatches, [variants]), variants, names)
+    try:
+        primer._dp_query_cache = (key, value)
+    except AttributeError:          # a foreign Primer class with __slots__
+        pass
+    return value
 
 
 class _LazyWindowsTable(DuplexTable):

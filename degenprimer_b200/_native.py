@@ -43,14 +43,30 @@ class dp_template_info(C.Structure):
                 ('n_exception_runs', C.c_uint64), ('device_bytes', C.c_uint64)]
 
 
-class dp_scan_stats(C.Structure):
+class _Stats(C.Structure):
+    """ctypes struct that also reads like the dict the callers expect."""
+
+    def __getitem__(self, name):
+        return getattr(self, name)
+
+    def keys(self):
+        return [f for f, _ in self._fields_]
+
+    def as_dict(self):
+        return {f: getattr(self, f) for f, _ in self._fields_}
+
+    def __repr__(self):
+        return repr(self.as_dict())
+
+
+class dp_scan_stats(_Stats):
     _fields_ = [('windows', C.c_uint64), ('candidates', C.c_uint64), ('hits', C.c_uint64),
                 ('ms_scan', C.c_float), ('ms_total', C.c_float),
                 ('ms_main', C.c_float), ('reserved', C.c_float),
                 ('launches', C.c_uint32), ('algo', C.c_uint32)]
 
 
-class dp_dg_stats(C.Structure):
+class dp_dg_stats(_Stats):
     _fields_ = [('duplexes', C.c_uint64), ('dimers_tried', C.c_uint64), ('dimers_kept', C.c_uint64),
                 ('ms_kernel', C.c_float), ('ms_total', C.c_float),
                 ('launches', C.c_uint32), ('reserved', C.c_uint32)]
@@ -198,6 +214,29 @@ class Template(object):
             pass
 
 
+class Query(object):
+    """Masters, mismatch limits and unambiguous variants of a set of primers, laid out
+    for dp_find / dp_duplex_dg (variant v of primer p = len(p) bytes at
+    offset[p] + v*len(p) of one blob)."""
+
+    def __init__(self, masters, mismatches, variants):
+        n = len(masters)
+        self.n = n
+        self.masters = [s if isinstance(s, str) else s.decode('ascii') for s in masters]
+        self.m = (C.c_char_p * n)(*[s.encode('ascii') for s in self.masters])
+        if isinstance(mismatches, int):
+            mismatches = [mismatches] * n
+        self.k = (C.c_int32 * n)(*[int(x) for x in mismatches])
+        self.lens = np.array([len(s) for s in self.masters], dtype=np.uint8)
+        self.vc = np.array([len(v) for v in variants], dtype=np.uint32)
+        sizes = self.vc.astype(np.uint64) * self.lens.astype(np.uint64)
+        self.vo = np.concatenate(([0], np.cumsum(sizes)[:-1])).astype(np.uint64)
+        self.vb = ''.join(''.join(v) for v in variants).encode('ascii')
+        self.vc_p, self.vo_p = _ptr(self.vc), _ptr(self.vo)
+        self.vb_p = C.cast(C.c_char_p(self.vb), C.c_void_p)
+        self.n_variants = int(self.vc.sum())
+
+
 class Context(object):
     """One CUDA context + stream on one device."""
 
@@ -294,8 +333,7 @@ class Context(object):
                 arr = np.zeros(0, dtype=HIT_DTYPE)
         finally:
             self.lib.dp_free(hits)
-        stats = {f: getattr(st, f) for f, _ in dp_scan_stats._fields_}
-        return arr, stats
+        return arr, st
 
     def _take(self, ptr, n, dtype):
         """Copy a malloc()ed result array into numpy and release it."""
@@ -307,29 +345,26 @@ class Context(object):
         finally:
             self.lib.dp_free(ptr)
 
-    def find(self, template, masters, mismatches, variants, cond, seg_begin=0, seg_end=2 ** 64 - 1,
-             strands=DP_STRAND_BOTH, algo=DP_ALGO_AUTO):
-        """Fused scan + duplex dG (dp_find).  variants: one list of unambiguous
-        sequences per master.  Returns (hits, dimers, scan stats, dG stats)."""
-        n = len(masters)
-        m = (C.c_char_p * n)(*[s.encode('ascii') if isinstance(s, str) else s for s in masters])
-        if isinstance(mismatches, int):
-            mismatches = [mismatches] * n
-        k = (C.c_int32 * n)(*[int(x) for x in mismatches])
-        vc = np.array([len(v) for v in variants], dtype=np.uint32)
-        lens = np.array([len(s) for s in masters], dtype=np.uint64)
-        vo = np.concatenate(([0], np.cumsum(vc.astype(np.uint64) * lens)[:-1])).astype(np.uint64)
-        vb = ''.join(''.join(v) for v in variants).encode('ascii')
+    def prepare(self, masters, mismatches, variants):
+        """The primer side of dp_find as ready-made C arrays (build once, scan many
+        templates).  variants: one list of unambiguous sequences per master."""
+        return Query(masters, mismatches, variants)
+
+    def find(self, template, masters, mismatches=None, variants=None, cond=None, seg_begin=0,
+             seg_end=2 ** 64 - 1, strands=DP_STRAND_BOTH, algo=DP_ALGO_AUTO):
+        """Fused scan + duplex dG (dp_find).  `masters` is a Query from prepare(), or
+        the masters themselves together with `mismatches` and `variants`.
+        Returns (hits, dimers, scan stats, dG stats)."""
+        q = masters if isinstance(masters, Query) else Query(masters, mismatches, variants)
         hits, n_hits, dimers, n_dimers = C.c_void_p(), C.c_uint64(), C.c_void_p(), C.c_uint64()
         st, dst = dp_scan_stats(), dp_dg_stats()
-        self._check(self.lib.dp_find(self._h, template._h, n, m, k, seg_begin, seg_end, strands, algo,
-                                     _ptr(vc), _ptr(vo), C.cast(C.c_char_p(vb), C.c_void_p), C.byref(cond),
+        self._check(self.lib.dp_find(self._h, template._h, q.n, q.m, q.k, seg_begin, seg_end, strands, algo,
+                                     q.vc_p, q.vo_p, q.vb_p, C.byref(cond),
                                      C.byref(hits), C.byref(n_hits), C.byref(dimers), C.byref(n_dimers),
                                      C.byref(st), C.byref(dst)))
         h = self._take(hits, n_hits.value, HIT_DTYPE)
         d = self._take(dimers, n_dimers.value, DIMER_DTYPE)
-        return (h, d, {f: getattr(st, f) for f, _ in dp_scan_stats._fields_},
-                {f: getattr(dst, f) for f, _ in dp_dg_stats._fields_})
+        return h, d, st, dst
 
     @property
     def stream(self):
@@ -365,8 +400,7 @@ class Context(object):
                 arr = np.zeros(0, dtype=DIMER_DTYPE)
         finally:
             self.lib.dp_free(out)
-        stats = {f: getattr(st, f) for f, _ in dp_dg_stats._fields_}
-        return arr, stats
+        return arr, st
 
     def calibrate(self, which, reps=5):
         """Lane-ops/s of a pipe: 'lop3', 'popc' or 'lds'."""

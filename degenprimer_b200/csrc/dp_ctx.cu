@@ -119,6 +119,7 @@ dp_ctx* dp_create(int device_ordinal) {
   ctx->d_dimers = nullptr; ctx->dimers_cap = 0;
   ctx->d_codes = nullptr; ctx->codes_cap = 0;
   ctx->d_counters = nullptr;
+  ctx->counters_clean = false;
   ctx->h_res = nullptr;   ctx->h_res_bytes = 0;
   ctx->stage_bytes = 0;
   ctx->stream = ctx->copy_stream = nullptr;

@@ -160,18 +160,52 @@ struct dp_duplex_args {
   unsigned long long* counters;
 };
 
-#define DP_DUPLEX_THREADS 128
-#define DP_DUPLEX_KEEP 12      // survivors held in registers/local before the fallback re-run
+#define DP_DUPLEX_WARPS 4
+#define DP_DUPLEX_THREADS (32 * DP_DUPLEX_WARPS)
+#define DP_DUPLEX_LIST 128     // survivors one warp can rank in shared memory
 
+// per-warp scratch: the two strands of the duplex, its run table, surviving dimers
+struct dp_duplex_scratch {
+  uint8_t s[DP_WIN];
+  uint8_t r[DP_WIN];
+  uint8_t run_start[32];
+  uint8_t run_end[32];
+  double kdg[DP_DUPLEX_LIST];
+  uint64_t kmask[DP_DUPLEX_LIST];
+};
+
+// d-th dimer of [full, alternatives...] in the reference's construction order
+// (Dimer.alternatives, SecStructures.py:126-152): M split into n maximal runs of
+// consecutive indices; d = 0 is the full dimer; then for each left cut l = 0..n-2:
+// runs [l, r) for r = n-1 down to l+1, followed by runs [l+1, n).
+__device__ __forceinline__ uint64_t dp_nth_dimer(uint64_t M, int n, uint32_t d, const uint8_t* run_start,
+                                                 const uint8_t* run_end) {
+  if (d == 0) return M;
+  int l = 0;
+  uint32_t rem = d - 1;
+  while (rem >= (uint32_t)(n - l)) { rem -= (uint32_t)(n - l); ++l; }
+  int a, b;
+  if (rem < (uint32_t)(n - 1 - l)) { a = l; b = n - 2 - (int)rem; }
+  else { a = l + 1; b = n - 1; }
+  const uint64_t lo_m = ~0ull << run_start[a];
+  const uint64_t hi_m = (2ull << run_end[b]) - 1ull;     // run_end = 63 wraps to all ones
+  return M & lo_m & hi_m;
+}
+
+// One WARP per (hit, variant) pair: lanes read the window letters in parallel,
+// a ballot gives the match mask, then lane d evaluates the d-th dimer, the
+// survivors are ranked by dG (stable) in shared memory and written to one
+// atomically reserved output range.  Latency of a small call is one dimer
+// evaluation, not the sum over sites.
 __global__ void __launch_bounds__(DP_DUPLEX_THREADS)
 dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant__ dp_dg_plan plan) {
   const unsigned long long packed = A.counters[DP_C_HITS];
   const uint64_t n_hits = (uint32_t)packed;
   const uint64_t n_pairs = packed >> 32;
   if (n_hits > A.hits_cap) return;                       // the host grows the buffer and rescans
-  if ((uint64_t)blockIdx.x * blockDim.x >= n_pairs) return;
-  // NN tables -> shared memory (10 KB), the per-thread work below is latency bound
-  __shared__ dp_nn_tables sT;
+  if ((uint64_t)blockIdx.x * DP_DUPLEX_WARPS >= n_pairs) return;
+  __shared__ dp_nn_tables sT;                            // 10 KB: NN tables next to the lanes
+  __shared__ dp_duplex_scratch sW[DP_DUPLEX_WARPS];
   {
     const uint64_t* src = reinterpret_cast<const uint64_t*>(A.dg.T);
     uint64_t* dst = reinterpret_cast<uint64_t*>(&sT);
@@ -180,97 +214,117 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
   __syncthreads();
   dp_dg_args G = A.dg;
   G.T = &sT;
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  dp_duplex_scratch& W = sW[threadIdx.x >> 5];
   unsigned long long n_tried = 0;
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (uint64_t pair = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; pair < n_pairs; pair += stride) {
-    // hit of this pair: last slot whose pair_base <= pair (pair_base is monotone in slot)
-    uint64_t a = 0, b = n_hits;
-    while (a < b) {
-      const uint64_t m = (a + b) >> 1;
-      if ((uint64_t)A.hits[m].pair_base <= pair) a = m + 1; else b = m;
+  const uint64_t n_warps = (uint64_t)gridDim.x * DP_DUPLEX_WARPS;
+  for (uint64_t pair = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); pair < n_pairs; pair += n_warps) {
+    // hit of this pair: last slot whose pair_base <= pair (monotone in slot); 32-ary search
+    uint64_t lo = 0, hi = n_hits;
+    while (hi - lo > 1) {
+      const uint64_t step = (hi - lo + 31) / 32;
+      const uint64_t idx = lo + (uint64_t)(lane + 1) * step;
+      const bool ok = idx < hi && (uint64_t)A.hits[idx].pair_base <= pair;
+      const uint32_t c = __popc(__ballot_sync(0xFFFFFFFFu, ok));
+      lo += (uint64_t)c * step;
+      hi = min(hi, lo + step);
     }
-    const dp_raw_hit hit = A.hits[a - 1];
+    const dp_raw_hit hit = A.hits[lo];
     const uint32_t v = (uint32_t)(pair - hit.pair_base);
     const int L = plan.pat_len[hit.pattern];
     const int strand = plan.pat_strand[hit.pattern];
     const uint32_t primer = plan.pat_primer[hit.pattern];
-    uint8_t s[DP_WIN], r[DP_WIN];
     const uint8_t* vc = A.codes + plan.var_off[primer] + (uint64_t)v * L;
+    // the two strands: s = variant, r = complement(window) (3'->5'), match = plain equality
     uint64_t M = 0;
-    for (int i = 0; i < L; ++i) {
-      const uint64_t g = hit.g + (strand ? (uint64_t)(L - 1 - i) : (uint64_t)i);
-      uint32_t w = dp_letter_at(A.lo, A.hi, A.exc, A.runs, A.n_runs, g);
-      if (strand) w = dp_letter_complement(w);
-      s[i] = vc[i];
-      r[i] = (uint8_t)dp_letter_complement(w);        // rev_str = complement(window)
-      if (w == s[i]) M |= 1ull << i;                   // plain character equality
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int i = (int)lane + 32 * half;
+      bool match = false;
+      if (i < L) {
+        const uint64_t g = hit.g + (strand ? (uint64_t)(L - 1 - i) : (uint64_t)i);
+        uint32_t w = dp_letter_at(A.lo, A.hi, A.exc, A.runs, A.n_runs, g);
+        if (strand) w = dp_letter_complement(w);
+        const uint8_t sv = vc[i];
+        W.s[i] = sv;
+        W.r[i] = (uint8_t)dp_letter_complement(w);
+        match = (w == sv);
+      }
+      M |= (uint64_t)__ballot_sync(0xFFFFFFFFu, match) << (32 * half);
     }
-    // pass 0 keeps the first DP_DUPLEX_KEEP survivors sorted in local arrays; if there
-    // are more, pass 1 recomputes and inserts straight into the reserved output range
-    uint64_t kmask[DP_DUPLEX_KEEP];
-    double kdg[DP_DUPLEX_KEEP];
+    if (!M) {                                            // no dimer at all
+      if (lane == 0 && pair < A.dir_cap) A.dir[pair] = 0;
+      __syncwarp();
+      continue;
+    }
+    const uint64_t S = M & ~(M << 1);                    // first index of every run
+    const uint64_t Eb = M & ~(M >> 1);                   // last index of every run
+    const int n = __popcll(S);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int i = (int)lane + 32 * half;
+      const uint64_t below = (1ull << i) - 1ull;
+      if ((S >> i) & 1ull) W.run_start[__popcll(S & below)] = (uint8_t)i;
+      if ((Eb >> i) & 1ull) W.run_end[__popcll(Eb & below)] = (uint8_t)i;
+    }
+    __syncwarp();
+    const uint32_t n_dimers = (uint32_t)(n * (n + 1) / 2);
     uint32_t kept = 0;
-    dp_raw_dimer* dst = nullptr;
-    auto consider = [&](uint64_t sub) {
-      if (!dst) ++n_tried;
-      const double dG = dp_dimer_dg_device(G, s, L, r, L, sub, 0);
-      if (dG > G.max_dimer_dG) return;        // SecStructures.py:302
-      if (!(dG <= G.max_dG_for_K)) return;    // K < min_K, SecStructures.py:303-304
-      if (dst) {
-        // stable insertion by dG (ties keep construction order)
-        uint32_t pos = kept;
-        while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
-        dst[pos].match_mask = sub;
-        dst[pos].dG = dG;
-      } else if (kept < DP_DUPLEX_KEEP) {
-        uint32_t pos = kept;
-        while (pos > 0 && kdg[pos - 1] > dG) { kdg[pos] = kdg[pos - 1]; kmask[pos] = kmask[pos - 1]; --pos; }
-        kdg[pos] = dG;
-        kmask[pos] = sub;
+    for (uint32_t base = 0; base < n_dimers; base += 32) {
+      const uint32_t d = base + lane;
+      bool keep = false;
+      uint64_t sub = 0;
+      double dG = 0.0;
+      if (d < n_dimers) {
+        sub = dp_nth_dimer(M, n, d, W.run_start, W.run_end);
+        dG = dp_dimer_dg_device(G, W.s, L, W.r, L, sub, 0);
+        keep = !(dG > G.max_dimer_dG) && (dG <= G.max_dG_for_K);   // SecStructures.py:302-304
       }
-      ++kept;
-    };
-    auto enumerate = [&]() {
-      if (!M) return;
-      consider(M);
-      // Dimer.alternatives (SecStructures.py:126-152): split M into maximal runs
-      // of consecutive indices and emit every contiguous range of runs except
-      // the full one, in the reference's order: for each left cut l, first the
-      // right cuts from the far right inwards, then the next left cut.
-      const uint64_t S = M & ~(M << 1);      // first index of every run
-      const uint64_t Eb = M & ~(M >> 1);     // last index of every run
-      const uint64_t top_end = 1ull << (63 - __clzll((long long)Eb));
-      uint64_t sl = S;
-      while (sl & (sl - 1)) {                // at least one more run to the right
-        const int st = __ffsll((long long)sl) - 1;
-        const uint64_t lo_m = ~0ull << st;
-        uint64_t eh = Eb & lo_m & ~top_end;  // ends of runs l .. last-1
-        while (eh) {
-          const int e = 63 - __clzll((long long)eh);
-          eh &= ~(1ull << e);
-          const uint64_t hi_m = (2ull << e) - 1;   // e <= 62 here
-          consider(M & lo_m & hi_m);
-        }
-        sl &= sl - 1;
-        const int st2 = __ffsll((long long)sl) - 1;
-        consider(M & (~0ull << st2));
-      }
-    };
-    enumerate();
+      const uint32_t kb = __ballot_sync(0xFFFFFFFFu, keep);
+      const uint32_t pos = kept + __popc(kb & lt_mask);
+      if (keep && pos < DP_DUPLEX_LIST) { W.kdg[pos] = dG; W.kmask[pos] = sub; }
+      kept += __popc(kb);
+    }
+    if (lane == 0) n_tried += n_dimers;
+    __syncwarp();
     uint64_t off = 0;
     if (kept) {
-      off = atomicAdd(&A.counters[DP_C_DIMERS], (unsigned long long)kept);
+      if (lane == 0) off = atomicAdd(&A.counters[DP_C_DIMERS], (unsigned long long)kept);
+      off = __shfl_sync(0xFFFFFFFFu, off, 0);
       if (off + kept <= A.out_cap) {
-        if (kept <= DP_DUPLEX_KEEP) {
-          for (uint32_t k = 0; k < kept; ++k) { A.out[off + k].match_mask = kmask[k]; A.out[off + k].dG = kdg[k]; }
-        } else {
-          dst = A.out + off;
-          kept = 0;
-          enumerate();
+        if (kept <= DP_DUPLEX_LIST) {
+          // the list is in construction order; rank = stable position by dG
+          for (uint32_t e = lane; e < kept; e += 32) {
+            const double x = W.kdg[e];
+            uint32_t rank = 0;
+            for (uint32_t f = 0; f < kept; ++f) {
+              const double y = W.kdg[f];
+              rank += (y < x || (y == x && f < e)) ? 1u : 0u;
+            }
+            A.out[off + rank].match_mask = W.kmask[e];
+            A.out[off + rank].dG = x;
+          }
+        } else if (lane == 0) {
+          // more survivors than the list holds (>= 16 mismatch runs): one lane re-runs
+          // the enumeration and inserts straight into the reserved range
+          dp_raw_dimer* dst = A.out + off;
+          uint32_t m = 0;
+          for (uint32_t d = 0; d < n_dimers; ++d) {
+            const uint64_t sub = dp_nth_dimer(M, n, d, W.run_start, W.run_end);
+            const double dG = dp_dimer_dg_device(G, W.s, L, W.r, L, sub, 0);
+            if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) continue;
+            uint32_t pos = m;
+            while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
+            dst[pos].match_mask = sub;
+            dst[pos].dG = dG;
+            ++m;
+          }
         }
       }
     }
-    if (pair < A.dir_cap) A.dir[pair] = (off << 16) | (uint64_t)kept;
+    if (lane == 0 && pair < A.dir_cap) A.dir[pair] = (off << 16) | (uint64_t)kept;
+    __syncwarp();                                        // scratch is reused by the next pair
   }
   if (n_tried) atomicAdd(&A.counters[DP_C_TRIED], n_tried);
 }
@@ -296,7 +350,7 @@ int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint
   // pair count unknown on the host (fused call): a persistent grid, most blocks
   // leave at once when there are few pairs
   uint64_t blocks = (uint64_t)ctx->sm_count * 8;
-  if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_THREADS - 1) / DP_DUPLEX_THREADS);
+  if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS);
   dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, 0, ctx->stream>>>(A, L.plan);
   DP_CUDA(ctx, cudaGetLastError());
   ++*launches;

@@ -111,7 +111,8 @@ struct dp_ctx {
   uint8_t* d_codes;            // variant letters as plane codes
   uint64_t codes_cap;
   unsigned long long* d_counters;
-  char* h_res;                 // pinned staging for results
+  bool counters_clean;         // slots 0..7 are zero (the publish kernel leaves them so)
+  char* h_res;                 // pinned (device-visible) staging for results
   size_t h_res_bytes;
   // pinned staging for uploads
   char* h_stage[2];

@@ -15,6 +15,7 @@
 //   -> counters + a small speculative prefix of the results to pinned memory
 //   -> ONE stream synchronise (a second copy only when the results are large).
 #include <algorithm>
+#include <chrono>
 #include <stdlib.h>
 #include <string.h>
 
@@ -96,6 +97,44 @@ dp_scan_runs_kernel(const __grid_constant__ dp_scan_args A, const __grid_constan
     if (g < start && g + P.len <= start) continue;          // does not reach the run
     if (g >= start && 2ull * min((unsigned long long)(end - g), (unsigned long long)P.len) > 3ull * P.len - P.thr3) continue;   // too many unknown bases
     dp_verify_window(A, P, g, p, true);
+  }
+}
+
+// ---- kernel 4: publish -------------------------------------------------------------
+// Last kernel of a call: one block writes the counters and the first few result
+// records straight into pinned host memory (zero-copy over PCIe: a few KB) and
+// leaves the counters zeroed for the next call.  Replaces four small D2H copies
+// and a memset; the host only synchronises the stream and reads.
+struct dp_publish_args {
+  unsigned long long* counters;
+  const uint64_t* hits;        // dp_raw_hit = 3 words
+  const uint64_t* dir;
+  const uint64_t* dimers;      // dp_raw_dimer = 2 words
+  uint64_t hits_cap, dir_cap, dimers_cap;
+  uint64_t* h_counters;
+  uint64_t* h_hits;
+  uint64_t* h_dir;
+  uint64_t* h_dimers;
+  uint32_t spec_hits, spec_pairs, spec_dimers;
+  int with_dg;
+};
+
+__global__ void __launch_bounds__(1024)
+dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
+  __shared__ unsigned long long c[8];
+  if (threadIdx.x < 8) c[threadIdx.x] = P.counters[threadIdx.x];
+  __syncthreads();
+  const uint64_t n_hits = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), (uint64_t)P.spec_hits);
+  for (uint64_t i = threadIdx.x; i < n_hits * 3; i += blockDim.x) P.h_hits[i] = P.hits[i];
+  if (P.with_dg) {
+    const uint64_t n_pairs = min(min((uint64_t)(c[DP_C_HITS] >> 32), P.dir_cap), (uint64_t)P.spec_pairs);
+    const uint64_t n_dim = min(min((uint64_t)c[DP_C_DIMERS], P.dimers_cap), (uint64_t)P.spec_dimers);
+    for (uint64_t i = threadIdx.x; i < n_pairs; i += blockDim.x) P.h_dir[i] = P.dir[i];
+    for (uint64_t i = threadIdx.x; i < n_dim * 2; i += blockDim.x) P.h_dimers[i] = P.dimers[i];
+  }
+  if (threadIdx.x < 8) {
+    P.h_counters[threadIdx.x] = c[threadIdx.x];
+    P.counters[threadIdx.x] = 0ull;
   }
 }
 
@@ -183,27 +222,57 @@ struct dp_scan_job {
   uint64_t pmask_all[2];
 };
 
+// The primer side of a job (patterns, prefilter plan) depends only on the call's
+// primer arguments: the last one is kept per thread, because the reference calls
+// find() once per template with the same primers.
 static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, const char* const* masters,
                         const int32_t* max_mismatches, uint64_t seg_begin, uint64_t seg_end, int strand_mask,
                         int algo, const uint32_t* var_count, dp_scan_job& J) {
   if (n_primers == 0 || n_primers > DP_MAX_PRIMERS)
     return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
   if (!(strand_mask & DP_STRAND_BOTH)) return dp_set_error(ctx, DP_ERR_ARG, "empty strand mask");
-  int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.pats, J.letters);
-  if (rc) return rc;
-  J.max_len = 0;
-  for (auto& p : J.pats) J.max_len = std::max<uint32_t>(J.max_len, p.len);
+  if (algo != DP_ALGO_AUTO && algo != DP_ALGO_BITSLICE && algo != DP_ALGO_POPC)
+    return dp_set_error(ctx, DP_ERR_ARG, "unknown algo %d", algo);
+  static thread_local std::string cached_key;
+  static thread_local dp_scan_job cached;
+  std::string key;
+  key.reserve(64 * n_primers);
+  for (uint32_t i = 0; i < n_primers; ++i) {
+    key += masters[i] ? masters[i] : "";
+    key += '/';
+    key += std::to_string(max_mismatches ? max_mismatches[i] : 0);
+    key += '/';
+    key += std::to_string(var_count ? (long long)var_count[i] : -1ll);
+    key += ';';
+  }
+  key += std::to_string(strand_mask) + ',' + std::to_string(algo);
+  if (key == cached_key) {
+    J = cached;
+  } else {
+    int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.pats, J.letters);
+    if (rc) return rc;
+    J.max_len = 0;
+    for (auto& p : J.pats) J.max_len = std::max<uint32_t>(J.max_len, p.len);
+    const uint32_t n_pat = (uint32_t)J.pats.size();
+    J.pmask_all[0] = J.pmask_all[1] = 0;
+    for (uint32_t p = 0; p < n_pat; ++p) J.pmask_all[p >> 6] |= 1ull << (p & 63);
+    J.used_algo = DP_ALGO_POPC;
+    if (algo == DP_ALGO_AUTO || algo == DP_ALGO_BITSLICE) {
+      if (dp_bitslice_make_plan(J.pats, J.letters, J.plan)) J.used_algo = DP_ALGO_BITSLICE;
+    }
+    J.NW = J.max_len > 32 ? 2 : 1;
+    memset(&J.A, 0, sizeof J.A);
+    cached = J;
+    cached_key = key;
+  }
   if (t->records.size() == 1 && t->records[0].len < J.max_len)
     return dp_set_error(ctx, DP_ERR_LENGTH, "template (%llu) is shorter than the primer (%u)",
                         (unsigned long long)t->records[0].len, J.max_len);
-  const uint32_t n_pat = (uint32_t)J.pats.size();
-  J.pmask_all[0] = J.pmask_all[1] = 0;
-  for (uint32_t p = 0; p < n_pat; ++p) J.pmask_all[p >> 6] |= 1ull << (p & 63);
   dp_scan_args& A = J.A;
   A.lo = t->d_lo; A.hi = t->d_hi; A.exc = t->d_exc;
   A.rec_start = t->d_rec_start; A.rec_len = t->d_rec_len;
   A.n_records = (uint32_t)t->records.size();
-  A.n_patterns = n_pat;
+  A.n_patterns = (uint32_t)J.pats.size();
   A.n_words = t->n_words;
   if (seg_end > t->n_words * 32) seg_end = t->n_words * 32;
   if (seg_begin > seg_end) seg_begin = seg_end;
@@ -213,13 +282,6 @@ static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, c
   A.counters = ctx->d_counters;
   A.runs = t->d_runs;
   A.n_runs = t->runs.size();
-  J.used_algo = DP_ALGO_POPC;
-  if (algo == DP_ALGO_AUTO || algo == DP_ALGO_BITSLICE) {
-    if (dp_bitslice_make_plan(J.pats, J.letters, J.plan)) J.used_algo = DP_ALGO_BITSLICE;
-  } else if (algo != DP_ALGO_POPC) {
-    return dp_set_error(ctx, DP_ERR_ARG, "unknown algo %d", algo);
-  }
-  J.NW = J.max_len > 32 ? 2 : 1;
   return DP_OK;
 }
 
@@ -257,7 +319,9 @@ static int scan_enqueue(dp_ctx* ctx, dp_scan_job& J, uint32_t* launches) {
   dp_scan_args& A = J.A;
   A.hits = ctx->d_hits;
   A.hits_cap = ctx->hits_cap;
-  DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+  if (!ctx->counters_clean)
+    DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+  ctx->counters_clean = false;
   DP_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   const bool small = J.pats.size() <= DP_NP_SMALL;
   const uint64_t n_scan_words = A.word_end - A.word_begin;
@@ -318,17 +382,27 @@ struct dp_sizes {
 
 static int fetch_sizes(dp_ctx* ctx, bool with_dg, dp_sizes& S) {
   cudaStream_t st = ctx->stream;
-  DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res, ctx->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-  const uint64_t nh = std::min<uint64_t>(DP_SPEC_HITS, ctx->hits_cap);
-  if (nh) DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + DP_RES_OFF_HITS, ctx->d_hits, nh * sizeof(dp_raw_hit), cudaMemcpyDeviceToHost, st));
-  if (with_dg) {
-    const uint64_t np = std::min<uint64_t>(DP_SPEC_PAIRS, ctx->dir_cap);
-    const uint64_t nd = std::min<uint64_t>(DP_SPEC_DIMERS, ctx->dimers_cap);
-    if (np) DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + DP_RES_OFF_DIR, ctx->d_dir, np * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
-    if (nd) DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + DP_RES_OFF_DIMERS, ctx->d_dimers, nd * sizeof(dp_raw_dimer), cudaMemcpyDeviceToHost, st));
-  }
+  dp_publish_args P;
+  P.counters = ctx->d_counters;
+  P.hits = (const uint64_t*)ctx->d_hits;
+  P.dir = ctx->d_dir;
+  P.dimers = (const uint64_t*)ctx->d_dimers;
+  P.hits_cap = ctx->hits_cap;
+  P.dir_cap = ctx->dir_cap;
+  P.dimers_cap = ctx->dimers_cap;
+  P.h_counters = (uint64_t*)ctx->h_res;
+  P.h_hits = (uint64_t*)(ctx->h_res + DP_RES_OFF_HITS);
+  P.h_dir = (uint64_t*)(ctx->h_res + DP_RES_OFF_DIR);
+  P.h_dimers = (uint64_t*)(ctx->h_res + DP_RES_OFF_DIMERS);
+  P.spec_hits = DP_SPEC_HITS;
+  P.spec_pairs = DP_SPEC_PAIRS;
+  P.spec_dimers = DP_SPEC_DIMERS;
+  P.with_dg = with_dg ? 1 : 0;
+  dp_publish_kernel<<<1, 1024, 0, st>>>(P);
+  DP_CUDA(ctx, cudaGetLastError());
   DP_CUDA(ctx, cudaEventRecord(ctx->ev5, st));
   DP_CUDA(ctx, cudaStreamSynchronize(st));
+  ctx->counters_clean = true;
   const unsigned long long* c = (const unsigned long long*)ctx->h_res;
   S.n_hits = (uint32_t)c[DP_C_HITS];
   S.n_pairs = c[DP_C_HITS] >> 32;
@@ -525,7 +599,14 @@ static int run_pipeline(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, const
       rc = scan_enqueue(ctx, J, scan_launches);
       if (rc) return rc;
     } else {
-      DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + DP_C_DIMERS, 0, 2 * sizeof(unsigned long long), ctx->stream));
+      // duplex stage again on the hits that are still on the device: the publish kernel
+      // zeroed the counters, put the hit / pair counts back
+      unsigned long long* hc = (unsigned long long*)ctx->h_res + 8;
+      for (int i = 0; i < 8; ++i) hc[i] = 0;
+      hc[DP_C_HITS] = S.n_hits | (S.n_pairs << 32);
+      hc[DP_C_CAND] = S.cand;
+      DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, ctx->stream));
+      ctx->counters_clean = false;
       DP_CUDA(ctx, cudaEventRecord(ctx->ev2, ctx->stream));
     }
     if (dg) {
@@ -587,6 +668,10 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   return DP_OK;
 }
 
+static double now_us() {
+  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
                        const char* const* masters, const int32_t* max_mismatches,
                        uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
@@ -603,11 +688,14 @@ extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   if (dg_stats) memset(dg_stats, 0, sizeof *dg_stats);
   if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
   if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  static const bool trace = getenv("DP_TRACE") != nullptr;
+  const double t0 = trace ? now_us() : 0.0;
   dp_scan_job J;
   int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, var_count, J);
   if (rc) return rc;
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
   DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  const double t1 = trace ? now_us() : 0.0;
   // variants of every primer, as plane codes
   uint64_t var_bytes = 0;
   for (uint32_t p = 0; p < n_primers; ++p) {
@@ -633,8 +721,10 @@ extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   dp_host_results R;
   float ms_scan, ms_main, ms_dg;
   uint32_t launches = 0, dg_launches = 0;
+  const double t2 = trace ? now_us() : 0.0;
   rc = run_pipeline(ctx, t, J, &DL, S, R, &ms_scan, &ms_main, &ms_dg, &launches, &dg_launches);
   if (rc) return rc;
+  const double t3 = trace ? now_us() : 0.0;
   std::vector<uint32_t> order;
   rc = hits_to_abi(ctx, t, J, R.hits, S.n_hits, hits_out, &order);
   if (rc) return rc;
@@ -651,6 +741,9 @@ extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
     cudaEventElapsedTime(&dg_stats->ms_total, ctx->ev2, ctx->ev5);
     dg_stats->launches = dg_launches;
   }
+  if (trace)
+    fprintf(stderr, "dp_find trace: prepare %.1f us, codes+plan %.1f us, pipeline (enqueue+sync) %.1f us, post %.1f us\n",
+            t1 - t0, t2 - t1, t3 - t2, now_us() - t3);
   return DP_OK;
 }
 
@@ -732,6 +825,7 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
   for (int attempt = 0;; ++attempt) {
     if (attempt == 4) return dp_set_error(ctx, DP_ERR_STATE, "internal: dimer buffer keeps overflowing");
     DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
+    ctx->counters_clean = false;
     DP_CUDA(ctx, cudaEventRecord(ctx->ev2, st));
     rc = dp_dg_enqueue(ctx, t, DL, pairs, &launches);
     if (rc) return rc;

@@ -106,50 +106,78 @@ __device__ __forceinline__ uint32_t dp_count_ge(const uint32_t* in) {
   return ge | eq;
 }
 
+// one pattern against the 32 windows of the thread's current word
+template <int K, int E>
+__device__ __forceinline__ void dp_bs_pattern_step(const dp_scan_args& A, const dp_pattern& P, const dp_bs_pattern& bp,
+                                                   const uint32_t* col, uint64_t w, unsigned long long& n_cand) {
+  constexpr int J = 8 + 2 * K;
+  constexpr int NT = J + E;
+  constexpr int THR = J - K;
+  uint32_t x[NT];
+#pragma unroll
+  for (int t = 0; t < NT; ++t)
+    x[t] = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(col) + bp.term[t]);
+  uint32_t alive = dp_count_ge<NT, THR>(x);
+  while (alive) {
+    const int b = __ffs(alive) - 1;
+    alive &= alive - 1;
+    ++n_cand;
+    const uint64_t q = w * 32 + b;
+    if (q < bp.anchor) continue;
+    const uint64_t g = q - bp.anchor;
+    if (g < A.seg_begin || g >= A.seg_end) continue;
+    dp_verify_window(A, P, g, bp.pattern, false);
+  }
+}
+
 template <int K, int E, int NP>
 __global__ void __launch_bounds__(DP_BS_THREADS, 3)
 dp_scan_bitslice_kernel(const __grid_constant__ dp_scan_args A, const __grid_constant__ dp_pattern_set<NP> PS,
                         const __grid_constant__ dp_bs_set<NP> BS, uint32_t n_bs) {
   constexpr int J = 8 + 2 * K;
-  constexpr int NT = J + E;
-  constexpr int THR = J - K;
   extern __shared__ uint32_t dp_bs_smem[];
   uint32_t* col = dp_bs_smem + threadIdx.x;
   col[4 * J * DP_BS_THREADS] = 0u;               // the all-zero padding plane
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   const uint64_t w_end = A.word_end + 2;          // anchors sit up to 63 bases into the window
   unsigned long long n_cand = 0;
-  for (uint64_t w = A.word_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < w_end; w += stride) {
-    const uint32_t h0 = __ldg(A.hi + w), h1 = __ldg(A.hi + w + 1);
-    const uint32_t l0 = __ldg(A.lo + w), l1 = __ldg(A.lo + w + 1);
+  uint64_t w = A.word_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t h0 = 0, h1 = 0, l0 = 0, l1 = 0;
+  if (w < w_end) {
+    h0 = __ldg(A.hi + w); h1 = __ldg(A.hi + w + 1);
+    l0 = __ldg(A.lo + w); l1 = __ldg(A.lo + w + 1);
+  }
+  while (w < w_end) {
+    // the next word's planes are requested before this word is processed: HBM
+    // latency hides behind ~300 instructions of bit-sliced work
+    const uint64_t wn = w + stride;
+    uint32_t nh0 = 0, nh1 = 0, nl0 = 0, nl1 = 0;
+    if (wn < w_end) {
+      nh0 = __ldg(A.hi + wn); nh1 = __ldg(A.hi + wn + 1);
+      nl0 = __ldg(A.lo + wn); nl1 = __ldg(A.lo + wn + 1);
+    }
 #pragma unroll
     for (int j = 0; j < J; ++j) {
       const uint32_t hs = __funnelshift_r(h0, h1, j);
       const uint32_t ls = __funnelshift_r(l0, l1, j);
-      col[(4 * j + 0) * DP_BS_THREADS] = ~hs & ~ls;   // A
+      col[(4 * j + 0) * DP_BS_THREADS] = ~(hs | ls);  // A
       col[(4 * j + 1) * DP_BS_THREADS] = ~hs & ls;    // C
       col[(4 * j + 2) * DP_BS_THREADS] = hs & ~ls;    // T
       col[(4 * j + 3) * DP_BS_THREADS] = hs & ls;     // G
     }
-#pragma unroll 1
-    for (uint32_t p = 0; p < n_bs; ++p) {
-      const dp_bs_pattern& bp = BS.bs[p];
-      uint32_t x[NT];
+    if constexpr (NP <= DP_NP_SMALL) {
+      // few patterns: unrolled, so every plane offset is a kernel-parameter constant
+      // held in a uniform register (no per-word LDC + address add)
 #pragma unroll
-      for (int t = 0; t < NT; ++t)
-        x[t] = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(col) + bp.term[t]);
-      uint32_t alive = dp_count_ge<NT, THR>(x);
-      while (alive) {
-        const int b = __ffs(alive) - 1;
-        alive &= alive - 1;
-        ++n_cand;
-        const uint64_t q = w * 32 + b;
-        if (q < bp.anchor) continue;
-        const uint64_t g = q - bp.anchor;
-        if (g < A.seg_begin || g >= A.seg_end) continue;
-        dp_verify_window(A, PS.pat[bp.pattern], g, bp.pattern, false);
-      }
+      for (int p = 0; p < NP; ++p)
+        if (p < (int)n_bs) dp_bs_pattern_step<K, E>(A, PS.pat[BS.bs[p].pattern], BS.bs[p], col, w, n_cand);
+    } else {
+#pragma unroll 1
+      for (uint32_t p = 0; p < n_bs; ++p)
+        dp_bs_pattern_step<K, E>(A, PS.pat[BS.bs[p].pattern], BS.bs[p], col, w, n_cand);
     }
+    w = wn;
+    h0 = nh0; h1 = nh1; l0 = nl0; l1 = nl1;
   }
   if (n_cand) atomicAdd(&A.counters[DP_C_CAND], n_cand);
 }
