@@ -239,13 +239,22 @@ def run_ours(args):
 
     query = ctx.prepare(primers, k, var_lists)      # the primer side, laid out once
 
+    exch = None
+    if world > 1:
+        # the hit gather rides on the same stream submission: publish kernel -> ncclAllGather
+        # of fixed slots over NVLink -> D2H, all queued by the library before the host waits
+        from degenprimer_b200.distributed import HitExchange
+        exch = HitExchange(ctx, max_hits=1024)
+
     def step(i):
         # one pass of the hot path: scan of every primer over both strands + dG of every
         # (hit, variant), one stream submission (dp_find), results back on the host
         t = copies[i % n_copies]
         hits, dimers, st, dst = ctx.find(t, query, cond=cond, algo=args.algo)
-        if world > 1:
-            hits = sort_hits(all_gather_records(hits))
+        if exch is None:
+            return hits, dimers, st, dst
+        allh = exch.collect_hits()                      # rank g's segment = record g of the genome
+        hits = allh if allh is not None else sort_hits(all_gather_records(hits))
         return hits, dimers, st, dst
 
     def sync_all():

@@ -91,7 +91,10 @@ HIT_DTYPE = np.dtype([('pos', '<u8'), ('record', '<u4'), ('primer', '<u2'),
                       ('strand', 'u1'), ('score3', 'u1')], align=True)
 DIMER_DTYPE = np.dtype([('hit', '<u4'), ('variant', '<u4'), ('match_mask', '<u8'), ('dG', '<f8')],
                        align=True)
-assert HIT_DTYPE.itemsize == 16 and DIMER_DTYPE.itemsize == 24
+WIRE_DTYPE = np.dtype([('g', '<u8'), ('record', '<u4'), ('pattern', '<u2'), ('score3', '<u2'),
+                       ('pair_base', '<u4'), ('reserved', '<u4')], align=True)
+WIRE_HEADER_BYTES = 64
+assert HIT_DTYPE.itemsize == 16 and DIMER_DTYPE.itemsize == 24 and WIRE_DTYPE.itemsize == 24
 
 _lib = None
 _lock = threading.Lock()
@@ -125,6 +128,15 @@ def _declare(lib):
         'dp_find': (i32, [vp, vp, u32, P(cp), P(C.c_int32), u64, u64, i32, i32, C.c_void_p, C.c_void_p,
                           C.c_void_p, P(dp_conditions), P(vp), P(u64), P(vp), P(u64),
                           P(dp_scan_stats), P(dp_dg_stats)]),
+        'dp_find_begin': (i32, [vp, vp, u32, P(cp), P(C.c_int32), u64, u64, i32, i32, C.c_void_p, C.c_void_p,
+                                C.c_void_p, P(dp_conditions)]),
+        'dp_find_end': (i32, [vp, P(vp), P(u64), P(vp), P(u64), P(dp_scan_stats), P(dp_dg_stats)]),
+        'dp_set_wire': (i32, [vp, C.c_void_p, u64]),
+        'dp_comm_unique_id': (i32, [vp, C.c_char_p]),
+        'dp_comm_init': (i32, [vp, C.c_char_p, i32, i32, u32]),
+        'dp_comm_destroy': (i32, [vp]),
+        'dp_comm_gathered': (i32, [vp, P(vp), P(u64), P(i32)]),
+        'dp_comm_hits': (i32, [vp, P(vp), P(u64)]),
         'dp_stream': (vp, [vp]),
         'dp_synchronize': (i32, [vp]),
         'dp_hit_windows': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p]),
@@ -143,7 +155,8 @@ def _declare(lib):
 EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
-           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_stream dp_synchronize '
+           'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
+           'dp_set_wire dp_comm_unique_id dp_comm_init dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
 
 
@@ -365,6 +378,69 @@ class Context(object):
         h = self._take(hits, n_hits.value, HIT_DTYPE)
         d = self._take(dimers, n_dimers.value, DIMER_DTYPE)
         return h, d, st, dst
+
+    def find_begin(self, template, query, cond, seg_begin=0, seg_end=2 ** 64 - 1,
+                   strands=DP_STRAND_BOTH, algo=DP_ALGO_AUTO):
+        """First half of find(): every kernel is queued on `stream`, nothing is waited for."""
+        q = query
+        self._check(self.lib.dp_find_begin(self._h, template._h, q.n, q.m, q.k, seg_begin, seg_end, strands,
+                                           algo, q.vc_p, q.vo_p, q.vb_p, C.byref(cond)))
+
+    def find_end(self):
+        """Second half of find(): waits for the stream and returns (hits, dimers, stats, dG stats)."""
+        hits, n_hits, dimers, n_dimers = C.c_void_p(), C.c_uint64(), C.c_void_p(), C.c_uint64()
+        st, dst = dp_scan_stats(), dp_dg_stats()
+        self._check(self.lib.dp_find_end(self._h, C.byref(hits), C.byref(n_hits), C.byref(dimers),
+                                         C.byref(n_dimers), C.byref(st), C.byref(dst)))
+        h = self._take(hits, n_hits.value, HIT_DTYPE)
+        d = self._take(dimers, n_dimers.value, DIMER_DTYPE)
+        return h, d, st, dst
+
+    def set_wire(self, device_ptr, nbytes):
+        """Device buffer that receives {header, raw hits} of every call (multi-GPU gather)."""
+        self._check(self.lib.dp_set_wire(self._h, C.c_void_p(device_ptr or 0), int(nbytes)))
+
+    # ---- multi-GPU exchange (NCCL inside the library) ------------------------------
+    def comm_unique_id(self):
+        buf = C.create_string_buffer(128)
+        self._check(self.lib.dp_comm_unique_id(self._h, buf))
+        return buf.raw
+
+    def comm_init(self, unique_id, world, rank, max_hits=4096):
+        self._check(self.lib.dp_comm_init(self._h, unique_id, int(world), int(rank), int(max_hits)))
+        ptr, slot, w = C.c_void_p(), C.c_uint64(), C.c_int()
+        self._check(self.lib.dp_comm_gathered(self._h, C.byref(ptr), C.byref(slot), C.byref(w)))
+        self._gather_slot, self._gather_world, self._gather_max = slot.value, w.value, int(max_hits)
+        raw = (C.c_uint8 * (slot.value * w.value)).from_address(ptr.value)
+        self._gather_buf = np.frombuffer(raw, dtype=np.uint8)     # pinned memory owned by the library
+
+    def comm_destroy(self):
+        self._gather_buf = None
+        self._check(self.lib.dp_comm_destroy(self._h))
+
+    def gathered_hits(self):
+        """Hits of every rank for the call that just returned (one segment per rank:
+        record = sender rank, positions in that segment), sorted; None if a slot
+        overflowed or a rank holds a multi-record template."""
+        hits, n = C.c_void_p(), C.c_uint64()
+        rc = self.lib.dp_comm_hits(self._h, C.byref(hits), C.byref(n))
+        if rc == DP_ERR_UNSUPPORTED:
+            return None
+        self._check(rc)
+        return self._take(hits, n.value, HIT_DTYPE)
+
+    def gathered(self):
+        """(raw wire records of every rank for the call that just returned, in one
+        array; sender rank of every record), or None when some rank had more hits
+        than a slot holds."""
+        world, slot, cap = self._gather_world, self._gather_slot, self._gather_max
+        buf = self._gather_buf.reshape(world, slot)
+        counts = (buf[:, :8].copy().view(np.uint64)[:, 0] & np.uint64(0xFFFFFFFF)).astype(np.int64)
+        if int(counts.max()) > cap:
+            return None
+        recs = buf[:, WIRE_HEADER_BYTES:].view(WIRE_DTYPE)            # (world, cap) view of pinned memory
+        keep = np.arange(cap)[None, :] < counts[:, None]
+        return recs[keep], np.repeat(np.arange(world), counts)
 
     @property
     def stream(self):

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libdegenprimer_b200.so')
-SOURCES = ['dp_ctx.cu', 'dp_template.cu', 'dp_scan.cu', 'dp_dg.cu', 'dp_calib.cu']
+SOURCES = ['dp_ctx.cu', 'dp_template.cu', 'dp_scan.cu', 'dp_dg.cu', 'dp_comm.cu', 'dp_calib.cu']
 NVCC_FLAGS = ['-std=c++17', '-O3', '-gencode', 'arch=compute_100a,code=sm_100a',
               '-lineinfo', '-Xcompiler', '-fPIC']
 
@@ -55,7 +55,7 @@ def build_native(force=False, verbose=False):
             sys.stderr.write(out)
         objs.append(obj)
     tmp = LIB + '.tmp'
-    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs
+    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs + ['-ldl']
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode:
         raise RuntimeError('link failed:\n%s' % r.stdout.decode())

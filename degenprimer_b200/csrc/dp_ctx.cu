@@ -122,6 +122,15 @@ dp_ctx* dp_create(int device_ordinal) {
   ctx->counters_clean = false;
   ctx->h_res = nullptr;   ctx->h_res_bytes = 0;
   ctx->stage_bytes = 0;
+  ctx->pending = nullptr;
+  ctx->pending_free = nullptr;
+  ctx->wire = nullptr;
+  ctx->wire_bytes = 0;
+  ctx->comm = nullptr;
+  ctx->comm_world = ctx->comm_rank = 0;
+  ctx->d_wire_recv = nullptr;
+  ctx->h_wire_recv = nullptr;
+  ctx->wire_owned = false;
   ctx->stream = ctx->copy_stream = nullptr;
   for (int i = 0; i < 2; ++i) {
     ctx->h_stage[i] = nullptr; ctx->d_stage[i] = nullptr;
@@ -160,6 +169,7 @@ void dp_destroy(dp_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   cudaStreamSynchronize(ctx->copy_stream);
+  dp_comm_release(ctx);
   for (int i = 0; i < 2; ++i) {
     if (ctx->h_stage[i]) cudaFreeHost(ctx->h_stage[i]);
     if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
@@ -173,6 +183,7 @@ void dp_destroy(dp_ctx* ctx) {
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->d_tables) cudaFree(ctx->d_tables);
   if (ctx->h_res) cudaFreeHost(ctx->h_res);
+  if (ctx->pending && ctx->pending_free) ctx->pending_free(ctx->pending);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaEventDestroy(ctx->ev2);

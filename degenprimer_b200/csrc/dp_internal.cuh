@@ -120,6 +120,21 @@ struct dp_ctx {
   cudaEvent_t stage_ev[2];
   cudaEvent_t stage_copied[2];
   size_t stage_bytes;
+  // fused call in flight (dp_find_begin .. dp_find_end); owned by dp_scan.cu
+  void* pending;
+  void (*pending_free)(void*);
+  // optional device mirror of {counters, raw hits} written by the publish kernel
+  void* wire;
+  uint64_t wire_bytes;
+  // multi-GPU hit exchange (dp_comm.cu): NCCL communicator + receive buffers
+  void* comm;                  // ncclComm_t
+  int comm_world, comm_rank;
+  char* d_wire_recv;           // world x wire_bytes on the device
+  char* h_wire_recv;           // the same, pinned host memory
+  bool wire_owned;             // `wire` was allocated by dp_comm_init
+  dp_dg_plan last_plan;        // (length, strand, primer) of the patterns of the last scan
+  uint64_t last_rec0_len;      // its template: length of record 0 and record count
+  uint64_t last_n_records;
   std::string err;
 };
 
@@ -194,6 +209,10 @@ int dp_ws_dir(dp_ctx* ctx, uint64_t cap);
 int dp_ws_dimers(dp_ctx* ctx, uint64_t cap);
 int dp_ws_codes(dp_ctx* ctx, uint64_t cap);
 int dp_ws_pinned(dp_ctx* ctx, size_t bytes);
+
+// queues the all-gather of the wire buffer + its copy to the host (dp_comm.cu); no-op without a communicator
+int dp_comm_enqueue(dp_ctx* ctx);
+void dp_comm_release(dp_ctx* ctx);
 
 // duplex stage on the hits that sit in ctx->d_hits (dp_dg.cu).  n_pairs_hint = 0:
 // the pair count is only known on the device (fused dp_find).

@@ -15,7 +15,6 @@
 //   -> counters + a small speculative prefix of the results to pinned memory
 //   -> ONE stream synchronise (a second copy only when the results are large).
 #include <algorithm>
-#include <chrono>
 #include <stdlib.h>
 #include <string.h>
 
@@ -117,6 +116,9 @@ struct dp_publish_args {
   uint64_t* h_dimers;
   uint32_t spec_hits, spec_pairs, spec_dimers;
   int with_dg;
+  uint64_t* wire;              // optional device mirror {counters[8], raw hits...} for the multi-GPU gather
+  uint64_t wire_hits;          // raw hit records the mirror can hold
+  uint64_t rec0_len, n_records;   // sender's template, for receivers: header[5], header[6]
 };
 
 __global__ void __launch_bounds__(1024)
@@ -131,6 +133,12 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
     const uint64_t n_dim = min(min((uint64_t)c[DP_C_DIMERS], P.dimers_cap), (uint64_t)P.spec_dimers);
     for (uint64_t i = threadIdx.x; i < n_pairs; i += blockDim.x) P.h_dir[i] = P.dir[i];
     for (uint64_t i = threadIdx.x; i < n_dim * 2; i += blockDim.x) P.h_dimers[i] = P.dimers[i];
+  }
+  if (P.wire) {
+    const uint64_t n_wire = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), P.wire_hits);
+    for (uint64_t i = threadIdx.x; i < n_wire * 3; i += blockDim.x) P.wire[8 + i] = P.hits[i];
+    if (threadIdx.x < 8)
+      P.wire[threadIdx.x] = threadIdx.x == 5 ? P.rec0_len : threadIdx.x == 6 ? P.n_records : c[threadIdx.x];
   }
   if (threadIdx.x < 8) {
     P.h_counters[threadIdx.x] = c[threadIdx.x];
@@ -282,6 +290,8 @@ static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, c
   A.counters = ctx->d_counters;
   A.runs = t->d_runs;
   A.n_runs = t->runs.size();
+  ctx->last_rec0_len = t->records.empty() ? 0 : t->records[0].len;
+  ctx->last_n_records = t->records.size();
   return DP_OK;
 }
 
@@ -319,6 +329,11 @@ static int scan_enqueue(dp_ctx* ctx, dp_scan_job& J, uint32_t* launches) {
   dp_scan_args& A = J.A;
   A.hits = ctx->d_hits;
   A.hits_cap = ctx->hits_cap;
+  for (size_t p = 0; p < J.pats.size(); ++p) {
+    ctx->last_plan.pat_len[p] = (uint8_t)J.pats[p].len;
+    ctx->last_plan.pat_strand[p] = J.pats[p].strand;
+    ctx->last_plan.pat_primer[p] = (uint8_t)J.pats[p].primer;
+  }
   if (!ctx->counters_clean)
     DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
   ctx->counters_clean = false;
@@ -380,7 +395,7 @@ struct dp_sizes {
   bool saturated;
 };
 
-static int fetch_sizes(dp_ctx* ctx, bool with_dg, dp_sizes& S) {
+static int publish_enqueue(dp_ctx* ctx, bool with_dg) {
   cudaStream_t st = ctx->stream;
   dp_publish_args P;
   P.counters = ctx->d_counters;
@@ -398,10 +413,19 @@ static int fetch_sizes(dp_ctx* ctx, bool with_dg, dp_sizes& S) {
   P.spec_pairs = DP_SPEC_PAIRS;
   P.spec_dimers = DP_SPEC_DIMERS;
   P.with_dg = with_dg ? 1 : 0;
+  P.wire = (uint64_t*)ctx->wire;
+  P.wire_hits = ctx->wire_bytes >= 64 ? (ctx->wire_bytes - 64) / sizeof(dp_raw_hit) : 0;
+  if (ctx->wire_bytes < 64) P.wire = nullptr;
+  P.rec0_len = ctx->last_rec0_len;
+  P.n_records = ctx->last_n_records;
   dp_publish_kernel<<<1, 1024, 0, st>>>(P);
   DP_CUDA(ctx, cudaGetLastError());
   DP_CUDA(ctx, cudaEventRecord(ctx->ev5, st));
-  DP_CUDA(ctx, cudaStreamSynchronize(st));
+  return DP_OK;
+}
+
+static int read_sizes(dp_ctx* ctx, dp_sizes& S) {
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->counters_clean = true;
   const unsigned long long* c = (const unsigned long long*)ctx->h_res;
   S.n_hits = (uint32_t)c[DP_C_HITS];
@@ -411,6 +435,12 @@ static int fetch_sizes(dp_ctx* ctx, bool with_dg, dp_sizes& S) {
   S.tried = c[DP_C_TRIED];
   S.saturated = c[DP_C_SATURATED] != 0;
   return DP_OK;
+}
+
+static int fetch_sizes(dp_ctx* ctx, bool with_dg, dp_sizes& S) {
+  int rc = publish_enqueue(ctx, with_dg);
+  if (rc) return rc;
+  return read_sizes(ctx, S);
 }
 
 // Pointers to the complete raw results on the host (inside ctx->h_res, or inside
@@ -578,67 +608,100 @@ static void fill_scan_stats(dp_ctx* ctx, const dp_template* t, const dp_scan_job
   stats->algo = (uint32_t)J.used_algo;
 }
 
-// scan [+ duplex] with overflow handling.  `dg` may be NULL (scan only).
-static int run_pipeline(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, const dp_dg_launch* dg,
-                        dp_sizes& S, dp_host_results& R, float* ms_scan, float* ms_main, float* ms_dg,
-                        uint32_t* scan_launches, uint32_t* dg_launches) {
+// scan [+ duplex] with overflow handling, split so that a caller can queue its own
+// work (the multi-GPU hit gather) between the enqueue and the wait.
+struct dp_pipeline_state {
+  bool need_scan;
+  int attempt;
+  float ms_scan, ms_main, ms_dg;
+  uint32_t scan_launches, dg_launches;
+  dp_sizes S;                       // sizes of the previous attempt (duplex-only re-runs)
+  bool overflowed;                  // the first attempt did not fit: results were re-made after the wait
+};
+
+static int pipeline_reserve(dp_ctx* ctx, bool with_dg) {
   int rc = dp_ws_hits(ctx, std::max<uint64_t>(ctx->hits_cap, 1u << 20));
   if (rc) return rc;
-  if (dg) {
+  if (with_dg) {
     rc = dp_ws_dir(ctx, std::max<uint64_t>(ctx->dir_cap, 1u << 22));
     if (rc) return rc;
     rc = dp_ws_dimers(ctx, std::max<uint64_t>(ctx->dimers_cap, 1u << 22));
     if (rc) return rc;
   }
-  bool need_scan = true;
-  *ms_scan = *ms_main = *ms_dg = 0.f;
-  for (int attempt = 0;; ++attempt) {
-    if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
-    if (attempt == 5) return dp_set_error(ctx, DP_ERR_STATE, "internal: result buffers keep overflowing");
-    if (need_scan) {
-      rc = scan_enqueue(ctx, J, scan_launches);
-      if (rc) return rc;
-    } else {
-      // duplex stage again on the hits that are still on the device: the publish kernel
-      // zeroed the counters, put the hit / pair counts back
-      unsigned long long* hc = (unsigned long long*)ctx->h_res + 8;
-      for (int i = 0; i < 8; ++i) hc[i] = 0;
-      hc[DP_C_HITS] = S.n_hits | (S.n_pairs << 32);
-      hc[DP_C_CAND] = S.cand;
-      DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, ctx->stream));
-      ctx->counters_clean = false;
-      DP_CUDA(ctx, cudaEventRecord(ctx->ev2, ctx->stream));
-    }
-    if (dg) {
-      rc = dp_dg_enqueue(ctx, t, *dg, 0, dg_launches);
-      if (rc) return rc;
-    }
-    DP_CUDA(ctx, cudaEventRecord(ctx->ev4, ctx->stream));
-    rc = fetch_sizes(ctx, dg != nullptr, S);
+  return DP_OK;
+}
+
+// queues one attempt: scan kernels (or the restored counters), duplex kernel, publish
+static int pipeline_enqueue(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, const dp_dg_launch* dg,
+                            dp_pipeline_state& P) {
+  int rc;
+  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  if (P.need_scan) {
+    rc = scan_enqueue(ctx, J, &P.scan_launches);
+    if (rc) return rc;
+  } else {
+    // duplex stage again on the hits that are still on the device: the publish kernel
+    // zeroed the counters, put the hit / pair counts back
+    unsigned long long* hc = (unsigned long long*)ctx->h_res + 8;
+    for (int i = 0; i < 8; ++i) hc[i] = 0;
+    hc[DP_C_HITS] = P.S.n_hits | (P.S.n_pairs << 32);
+    hc[DP_C_CAND] = P.S.cand;
+    DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, ctx->stream));
+    ctx->counters_clean = false;
+    DP_CUDA(ctx, cudaEventRecord(ctx->ev2, ctx->stream));
+  }
+  if (dg) {
+    rc = dp_dg_enqueue(ctx, t, *dg, 0, &P.dg_launches);
+    if (rc) return rc;
+  }
+  DP_CUDA(ctx, cudaEventRecord(ctx->ev4, ctx->stream));
+  rc = publish_enqueue(ctx, dg != nullptr);
+  if (rc) return rc;
+  return dp_comm_enqueue(ctx);        // multi-GPU: all-gather of the wire mirror, same stream
+}
+
+// waits for the queued attempt; grows buffers and repeats while something overflowed
+static int pipeline_wait(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, const dp_dg_launch* dg,
+                         dp_pipeline_state& P, dp_sizes& S, dp_host_results& R) {
+  int rc;
+  for (;;) {
+    rc = read_sizes(ctx, S);
     if (rc) return rc;
     float ms = 0.f;
-    if (need_scan) {
-      cudaEventElapsedTime(&ms, ctx->ev1, ctx->ev2); *ms_scan += ms;
-      cudaEventElapsedTime(ms_main, ctx->ev1, ctx->ev3);
+    if (P.need_scan) {
+      cudaEventElapsedTime(&ms, ctx->ev1, ctx->ev2); P.ms_scan += ms;
+      cudaEventElapsedTime(&P.ms_main, ctx->ev1, ctx->ev3);
     }
-    if (dg) { cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev4); *ms_dg += ms; }
+    if (dg) { cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev4); P.ms_dg += ms; }
     if (S.saturated)
       return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "more than 4e9 hits or duplexes in one call: lower max_mismatches or split the template");
-    if (need_scan && S.n_hits > ctx->hits_cap) {
+    bool again = false;
+    if (P.need_scan && S.n_hits > ctx->hits_cap) {
       rc = dp_ws_hits(ctx, S.n_hits + (S.n_hits >> 3) + 1024);
       if (rc) return rc;
-      continue;
+      again = true;
+    } else {
+      P.need_scan = false;
+      if (dg && (S.n_pairs > ctx->dir_cap || S.n_dimers > ctx->dimers_cap)) {
+        // (while the directory overflowed the dimer count is only a lower bound; the loop repeats)
+        if (S.n_pairs > ctx->dir_cap) { rc = dp_ws_dir(ctx, S.n_pairs + (S.n_pairs >> 3) + 1024); if (rc) return rc; }
+        if (S.n_dimers > ctx->dimers_cap) { rc = dp_ws_dimers(ctx, S.n_dimers + (S.n_dimers >> 2) + 1024); if (rc) return rc; }
+        again = true;
+      }
     }
-    need_scan = false;
-    if (dg && (S.n_pairs > ctx->dir_cap || S.n_dimers > ctx->dimers_cap)) {
-      // (while the directory overflowed the dimer count is only a lower bound; the loop repeats)
-      if (S.n_pairs > ctx->dir_cap) { rc = dp_ws_dir(ctx, S.n_pairs + (S.n_pairs >> 3) + 1024); if (rc) return rc; }
-      if (S.n_dimers > ctx->dimers_cap) { rc = dp_ws_dimers(ctx, S.n_dimers + (S.n_dimers >> 2) + 1024); if (rc) return rc; }
-      continue;
-    }
-    break;
+    if (!again) break;
+    if (++P.attempt == 5) return dp_set_error(ctx, DP_ERR_STATE, "internal: result buffers keep overflowing");
+    P.overflowed = true;
+    P.S = S;
+    rc = pipeline_enqueue(ctx, t, J, dg, P);
+    if (rc) return rc;
   }
   return fetch_all(ctx, dg != nullptr, S, R);
+}
+
+static void pipeline_init(dp_pipeline_state& P) {
+  memset(&P, 0, sizeof P);
+  P.need_scan = true;
 }
 
 extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
@@ -657,45 +720,49 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   dp_sizes S;
   dp_host_results R;
-  float ms_scan, ms_main, ms_dg;
-  uint32_t launches = 0, dg_launches = 0;
-  rc = run_pipeline(ctx, t, J, nullptr, S, R, &ms_scan, &ms_main, &ms_dg, &launches, &dg_launches);
+  dp_pipeline_state P;
+  pipeline_init(P);
+  rc = pipeline_reserve(ctx, false);
+  if (rc) return rc;
+  rc = pipeline_enqueue(ctx, t, J, nullptr, P);
+  if (rc) return rc;
+  rc = pipeline_wait(ctx, t, J, nullptr, P, S, R);
   if (rc) return rc;
   rc = hits_to_abi(ctx, t, J, R.hits, S.n_hits, hits_out, nullptr);
   if (rc) return rc;
   *n_hits_out = S.n_hits;
-  fill_scan_stats(ctx, t, J, S, ms_scan, ms_main, launches, stats);
+  fill_scan_stats(ctx, t, J, S, P.ms_scan, P.ms_main, P.scan_launches, stats);
   return DP_OK;
 }
 
-static double now_us() {
-  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
-}
+// A fused call between its two halves (one per context; not re-entrant).
+struct dp_find_pending {
+  bool active = false;
+  const dp_template* t = nullptr;
+  dp_scan_job J;
+  dp_dg_launch DL;
+  dp_pipeline_state P;
+  std::vector<uint32_t> var_count;
+};
 
-extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
-                       const char* const* masters, const int32_t* max_mismatches,
-                       uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
-                       const uint32_t* var_count, const uint64_t* var_offset, const char* variants,
-                       const dp_conditions* cond, dp_hit** hits_out, uint64_t* n_hits_out,
-                       dp_dimer** dimers_out, uint64_t* n_dimers_out,
-                       dp_scan_stats* stats, dp_dg_stats* dg_stats) {
-  if (!ctx || !t || !masters || !hits_out || !n_hits_out || !dimers_out || !n_dimers_out ||
-      !var_count || !var_offset || !variants || !cond)
+static void pending_free(void* p) { delete (dp_find_pending*)p; }
+
+extern "C" int dp_find_begin(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
+                             const char* const* masters, const int32_t* max_mismatches,
+                             uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
+                             const uint32_t* var_count, const uint64_t* var_offset, const char* variants,
+                             const dp_conditions* cond) {
+  if (!ctx || !t || !masters || !var_count || !var_offset || !variants || !cond)
     return dp_set_error(ctx, DP_ERR_ARG, "null argument");
-  *hits_out = nullptr; *n_hits_out = 0;
-  *dimers_out = nullptr; *n_dimers_out = 0;
-  if (stats) memset(stats, 0, sizeof *stats);
-  if (dg_stats) memset(dg_stats, 0, sizeof *dg_stats);
   if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
   if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
-  static const bool trace = getenv("DP_TRACE") != nullptr;
-  const double t0 = trace ? now_us() : 0.0;
-  dp_scan_job J;
-  int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, var_count, J);
+  if (!ctx->pending) { ctx->pending = new dp_find_pending(); ctx->pending_free = pending_free; }
+  dp_find_pending& F = *(dp_find_pending*)ctx->pending;
+  if (F.active) return dp_set_error(ctx, DP_ERR_STATE, "dp_find_begin: the previous call was not finished with dp_find_end");
+  int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, var_count, F.J);
   if (rc) return rc;
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
   DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  const double t1 = trace ? now_us() : 0.0;
   // variants of every primer, as plane codes
   uint64_t var_bytes = 0;
   for (uint32_t p = 0; p < n_primers; ++p) {
@@ -706,44 +773,91 @@ extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   }
   rc = upload_codes(ctx, variants, var_bytes);
   if (rc) return rc;
-  dp_dg_launch DL;
-  fill_dg_launch(ctx, cond, DL);
-  for (size_t p = 0; p < J.pats.size(); ++p) {
-    DL.plan.pat_len[p] = (uint8_t)J.pats[p].len;
-    DL.plan.pat_strand[p] = J.pats[p].strand;
-    DL.plan.pat_primer[p] = (uint8_t)J.pats[p].primer;
+  fill_dg_launch(ctx, cond, F.DL);
+  for (size_t p = 0; p < F.J.pats.size(); ++p) {
+    F.DL.plan.pat_len[p] = (uint8_t)F.J.pats[p].len;
+    F.DL.plan.pat_strand[p] = F.J.pats[p].strand;
+    F.DL.plan.pat_primer[p] = (uint8_t)F.J.pats[p].primer;
   }
   for (uint32_t p = 0; p < n_primers; ++p) {
-    DL.plan.var_count[p] = var_count[p];
-    DL.plan.var_off[p] = (uint32_t)var_offset[p];
+    F.DL.plan.var_count[p] = var_count[p];
+    F.DL.plan.var_off[p] = (uint32_t)var_offset[p];
   }
+  F.var_count.assign(var_count, var_count + n_primers);
+  F.t = t;
+  pipeline_init(F.P);
+  rc = pipeline_reserve(ctx, true);
+  if (rc) return rc;
+  rc = pipeline_enqueue(ctx, t, F.J, &F.DL, F.P);
+  if (rc) return rc;
+  F.active = true;
+  return DP_OK;
+}
+
+extern "C" int dp_find_end(dp_ctx* ctx, dp_hit** hits_out, uint64_t* n_hits_out,
+                           dp_dimer** dimers_out, uint64_t* n_dimers_out,
+                           dp_scan_stats* stats, dp_dg_stats* dg_stats) {
+  if (!ctx || !hits_out || !n_hits_out || !dimers_out || !n_dimers_out)
+    return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *hits_out = nullptr; *n_hits_out = 0;
+  *dimers_out = nullptr; *n_dimers_out = 0;
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (dg_stats) memset(dg_stats, 0, sizeof *dg_stats);
+  dp_find_pending* Fp = (dp_find_pending*)ctx->pending;
+  if (!Fp || !Fp->active) return dp_set_error(ctx, DP_ERR_STATE, "dp_find_end without dp_find_begin");
+  dp_find_pending& F = *Fp;
+  F.active = false;
   dp_sizes S;
   dp_host_results R;
-  float ms_scan, ms_main, ms_dg;
-  uint32_t launches = 0, dg_launches = 0;
-  const double t2 = trace ? now_us() : 0.0;
-  rc = run_pipeline(ctx, t, J, &DL, S, R, &ms_scan, &ms_main, &ms_dg, &launches, &dg_launches);
+  int rc = pipeline_wait(ctx, F.t, F.J, &F.DL, F.P, S, R);
   if (rc) return rc;
-  const double t3 = trace ? now_us() : 0.0;
   std::vector<uint32_t> order;
-  rc = hits_to_abi(ctx, t, J, R.hits, S.n_hits, hits_out, &order);
+  rc = hits_to_abi(ctx, F.t, F.J, R.hits, S.n_hits, hits_out, &order);
   if (rc) return rc;
   *n_hits_out = S.n_hits;
   const dp_hit* hits = *hits_out;
-  rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return var_count[hits[i].primer]; }, dimers_out, n_dimers_out);
+  const std::vector<uint32_t>& vc = F.var_count;
+  rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return vc[hits[i].primer]; }, dimers_out, n_dimers_out);
   if (rc) { free(*hits_out); *hits_out = nullptr; *n_hits_out = 0; return rc; }
-  fill_scan_stats(ctx, t, J, S, ms_scan, ms_main, launches, stats);
+  fill_scan_stats(ctx, F.t, F.J, S, F.P.ms_scan, F.P.ms_main, F.P.scan_launches, stats);
+  if (stats) stats->reserved = F.P.overflowed ? 1.f : 0.f;     // the wire mirror of the first attempt is stale
   if (dg_stats) {
     dg_stats->duplexes = S.n_pairs;
     dg_stats->dimers_tried = S.tried;
     dg_stats->dimers_kept = *n_dimers_out;
-    dg_stats->ms_kernel = ms_dg;
+    dg_stats->ms_kernel = F.P.ms_dg;
     cudaEventElapsedTime(&dg_stats->ms_total, ctx->ev2, ctx->ev5);
-    dg_stats->launches = dg_launches;
+    dg_stats->launches = F.P.dg_launches;
   }
-  if (trace)
-    fprintf(stderr, "dp_find trace: prepare %.1f us, codes+plan %.1f us, pipeline (enqueue+sync) %.1f us, post %.1f us\n",
-            t1 - t0, t2 - t1, t3 - t2, now_us() - t3);
+  return DP_OK;
+}
+
+extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
+                       const char* const* masters, const int32_t* max_mismatches,
+                       uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
+                       const uint32_t* var_count, const uint64_t* var_offset, const char* variants,
+                       const dp_conditions* cond, dp_hit** hits_out, uint64_t* n_hits_out,
+                       dp_dimer** dimers_out, uint64_t* n_dimers_out,
+                       dp_scan_stats* stats, dp_dg_stats* dg_stats) {
+  if (!hits_out || !n_hits_out || !dimers_out || !n_dimers_out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *hits_out = nullptr; *n_hits_out = 0;
+  *dimers_out = nullptr; *n_dimers_out = 0;
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (dg_stats) memset(dg_stats, 0, sizeof *dg_stats);
+  int rc = dp_find_begin(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo,
+                         var_count, var_offset, variants, cond);
+  if (rc) return rc;
+  return dp_find_end(ctx, hits_out, n_hits_out, dimers_out, n_dimers_out, stats, dg_stats);
+}
+
+extern "C" int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes) {
+  if (!ctx) return DP_ERR_ARG;
+  if (device_ptr && bytes < 64 + sizeof(dp_raw_hit))
+    return dp_set_error(ctx, DP_ERR_ARG, "wire buffer must hold the 64-byte header and at least one 24-byte record");
+  if (((uintptr_t)device_ptr & 7u) != 0) return dp_set_error(ctx, DP_ERR_ARG, "wire buffer must be 8-byte aligned");
+  if (ctx->comm) return dp_set_error(ctx, DP_ERR_STATE, "the wire buffer is owned by the communicator (dp_comm_init)");
+  ctx->wire = device_ptr;
+  ctx->wire_bytes = device_ptr ? bytes : 0;
   return DP_OK;
 }
 

@@ -87,8 +87,70 @@ def all_gather_records(arr, group=None, device=None):
     return np.concatenate(parts)
 
 
+def wire_to_hits(raw, primer_lens, rec_starts, rec_lens, rec_index=None):
+    """Raw wire records (dp_wire_hit, include/degenprimer_b200.h) -> dp_hit records in
+    the senders' record coordinates.  pattern = 2*primer + strand.  rec_starts /
+    rec_lens are indexed by the record number of the wire record, or by rec_index
+    (e.g. the sender rank of every record, when each rank holds one segment)."""
+    out = np.zeros(len(raw), dtype=nat.HIT_DTYPE)
+    if not len(raw):
+        return out
+    primer = (raw['pattern'] >> 1).astype(np.int64)
+    strand = (raw['pattern'] & 1).astype(np.uint8)
+    L = np.asarray(primer_lens, dtype=np.int64)[primer]
+    rec = raw['record'].astype(np.int64) if rec_index is None else rec_index
+    off = raw['g'].astype(np.int64) - np.asarray(rec_starts, dtype=np.int64)[rec]
+    rl = np.asarray(rec_lens, dtype=np.int64)[rec]
+    out['pos'] = np.where(strand == 0, off, rl - L - off).astype(np.uint64)
+    out['record'] = raw['record']
+    out['primer'] = primer.astype(np.uint16)
+    out['strand'] = strand
+    out['score3'] = raw['score3'].astype(np.uint8)
+    return out
+
+
+class HitExchange(object):
+    """All-gather of the hits of every fused call, inside the call's own stream submission.
+
+    The library's publish kernel mirrors {header, raw hits} into a device slot; with a
+    communicator attached (dp_comm_init) every dp_find / dp_scan of the context ends
+    with ncclAllGather over NVLink + one copy to pinned host memory on the same
+    stream, so the exchange costs no extra host round trip.  torch.distributed is
+    only used to hand rank 0's NCCL unique id to the other ranks.  If any rank has
+    more hits than a slot holds, `collect` returns None and the caller falls back
+    to all_gather_records."""
+
+    def __init__(self, ctx, max_hits=1024, group=None):
+        import torch.distributed as dist
+        self.ctx = ctx
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        box = [ctx.comm_unique_id() if self.rank == 0 else None]
+        dist.broadcast_object_list(box, src=0, group=group)
+        ctx.comm_init(box[0], self.world, self.rank, max_hits)
+
+    def close(self):
+        self.ctx.comm_destroy()
+
+    def collect(self):
+        """(raw wire records, sender rank of each) of the call that just returned, or None."""
+        return self.ctx.gathered()
+
+    def collect_hits(self):
+        """Converted + sorted hits of every rank (record = sender rank), or None."""
+        return self.ctx.gathered_hits()
+
+
+def hit_keys(hits):
+    """Sort key of dp_scan's order (primer, strand, record, pos) as one uint64."""
+    return ((hits['primer'].astype(np.uint64) << np.uint64(57)) | (hits['strand'].astype(np.uint64) << np.uint64(56)) |
+            (hits['record'].astype(np.uint64) << np.uint64(40)) | hits['pos'].astype(np.uint64))
+
+
 def sort_hits(hits):
     """The order dp_scan uses: (primer, strand, record, pos)."""
+    if len(hits) and int(hits['pos'].max()) < (1 << 40) and int(hits['record'].max()) < (1 << 16):
+        return hits[np.argsort(hit_keys(hits), kind='stable')]
     return np.sort(hits, order=['primer', 'strand', 'record', 'pos'])
 
 
@@ -100,6 +162,7 @@ class ShardedTemplate(object):
         rank's slice is uploaded."""
         self.t_len = len(text)
         self.rank, self.world_size = rank, world_size
+        self.max_primer_len = max_primer_len
         self.base_begin, self.base_end, self.start_begin, self.start_end = \
             shard_bounds(self.t_len, world_size, rank, max_primer_len)
         piece = text[self.base_begin:self.base_end]
@@ -107,6 +170,35 @@ class ShardedTemplate(object):
             piece = piece.tobytes()
         self.template = ctx.template_from_sequences([piece])
         self.ctx = ctx
+
+    def find(self, query, cond, exchange=None, group=None):
+        """Fused scan + duplex dG of this rank's slice (window starts restricted to the
+        owned range on the device).  Returns (hits of the WHOLE template in
+        whole-template coordinates, sorted; this rank's dimers; this rank's local
+        hits the dimers index; stats, dG stats).  `exchange`: a HitExchange (NCCL
+        gather queued on the same stream); without it hits are gathered afterwards."""
+        lens = [len(m) for m in query.masters]
+        lo = self.start_begin - self.base_begin
+        hi = self.start_end - self.base_begin
+        local, dimers, st, dst = self.ctx.find(self.template, query, cond=cond, seg_begin=lo, seg_end=hi)
+        h = exchange.collect_hits() if exchange is not None else None
+        if h is not None:
+            sender = h['record'].astype(np.int64)
+            begins, sizes = self._all_bounds()
+            h['record'] = 0
+            hits = sort_hits(localize_hits(h, begins[sender], sizes[sender], self.t_len, lens))
+        else:
+            mine = localize_hits(local, self.base_begin, self.base_end - self.base_begin, self.t_len, lens)
+            hits = sort_hits(all_gather_records(mine, group))
+        return hits, dimers, local, st, dst
+
+    def _all_bounds(self):
+        if getattr(self, '_bounds', None) is None:
+            b = [shard_bounds(self.t_len, self.world_size, g, self.max_primer_len)[:2]
+                 for g in range(self.world_size)]
+            self._bounds = (np.array([x for x, _ in b], dtype=np.int64),
+                            np.array([y - x for x, y in b], dtype=np.int64))
+        return self._bounds
 
     def scan(self, masters, mismatches, gather=True, group=None):
         """Hits of the whole template in whole-template coordinates (every rank

@@ -261,6 +261,60 @@ int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
             dp_hit** hits, uint64_t* n_hits, dp_dimer** dimers, uint64_t* n_dimers,
             dp_scan_stats* scan_stats, dp_dg_stats* dg_stats);
 
+/* dp_find in two halves, so that a caller can queue its own work on dp_stream()
+ * behind the kernels and before the host waits (the multi-GPU hit gather: an NCCL
+ * all-gather of the wire buffer below).  dp_find == begin + end. */
+int dp_find_begin(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
+                  const char* const* masters, const int32_t* max_mismatches,
+                  uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
+                  const uint32_t* var_count, const uint64_t* var_offset,
+                  const char* variants, const dp_conditions* cond);
+int dp_find_end(dp_ctx* ctx, dp_hit** hits, uint64_t* n_hits, dp_dimer** dimers,
+                uint64_t* n_dimers, dp_scan_stats* scan_stats, dp_dg_stats* dg_stats);
+
+/* Device-side mirror of a call's hits for the multi-GPU exchange: when set, the
+ * last kernel of every dp_scan / dp_find writes
+ *     uint64 header[8]   header[0] = n_hits | n_pairs << 32 (n_hits may exceed
+ *                        what fits: then the mirror is truncated)
+ *     dp_wire_hit hit[]  unsorted, sender coordinates
+ * into `device_ptr` (caller-owned device memory, 8-byte aligned, `bytes` long).
+ * pattern = index of the (primer, strand) pair in call order (2*primer + strand
+ * with DP_STRAND_BOTH); g = forward window start in the sender's padded
+ * concatenation (record r starts at dp_template_record().start).
+ * Pass NULL to switch the mirror off. */
+typedef struct dp_wire_hit {
+  uint64_t g;
+  uint32_t record;
+  uint16_t pattern;
+  uint16_t score3;
+  uint32_t pair_base;
+  uint32_t reserved;
+} dp_wire_hit;
+int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes);
+
+/* NCCL exchange of the wire buffer over NVLink (the reference's
+ * counterpart is the pickling of slice results through multiprocessing Queues,
+ * BioUtils/Tools/Multiprocessing.py:201-211).  One process per GPU: rank 0 calls
+ * dp_comm_unique_id, the id is broadcast by the host side (torch.distributed),
+ * every rank calls dp_comm_init (collective).  From then on every dp_scan /
+ * dp_find of this ctx ends with ncclAllGather(wire slot) + a copy to pinned host
+ * memory on the same stream — all ranks must make the same sequence of calls.
+ * After the call returns, dp_comm_gathered() gives `world` slots of `slot_bytes`
+ * (layout of dp_set_wire), slot r = rank r's hits of that call.  A slot holds
+ * max_hits records; header[0] tells when a rank had more (then fall back to a
+ * host-side gather).  NCCL is loaded with dlopen("libnccl.so.2"). */
+int dp_comm_unique_id(dp_ctx* ctx, char id[128]);
+int dp_comm_init(dp_ctx* ctx, const char id[128], int world, int rank, uint32_t max_hits);
+int dp_comm_destroy(dp_ctx* ctx);
+int dp_comm_gathered(dp_ctx* ctx, const void** host_ptr, uint64_t* slot_bytes, int* world);
+/* The gathered hits of the call that just returned, converted: one segment (one
+ * record) per rank, hit.record = sender rank, hit.pos in that rank's segment
+ * coordinates (strand 1: on its reverse complement), sorted by (primer, strand,
+ * record, pos).  header[5] / header[6] of a slot carry the sender's record length
+ * and record count.  DP_ERR_UNSUPPORTED if a slot overflowed or a rank scanned a
+ * multi-record template (use dp_comm_gathered then). */
+int dp_comm_hits(dp_ctx* ctx, dp_hit** hits, uint64_t* n_hits);
+
 /* The template window under every hit, as the reference's strand strings show
  * it (fwd_seq[pos:pos+L] / rev_seq[pos:pos+L], DegenPrimer/SearchEngine.py:113):
  * out receives n_hits rows of 64 bytes, upper-case ASCII, NUL padded. */
