@@ -227,6 +227,20 @@ class Template(object):
             pass
 
 
+class _Owner(object):
+    """Releases a library-allocated result block when the numpy view over it dies."""
+    __slots__ = ('lib', 'ptr')
+
+    def __init__(self, lib, ptr):
+        self.lib, self.ptr = lib, ptr
+
+    def __del__(self):
+        try:
+            self.lib.dp_free(C.c_void_p(self.ptr))
+        except Exception:
+            pass
+
+
 class Query(object):
     """Masters, mismatch limits and unambiguous variants of a set of primers, laid out
     for dp_find / dp_duplex_dg (variant v of primer p = len(p) bytes at
@@ -338,25 +352,24 @@ class Context(object):
         hits, n_hits, st = C.c_void_p(), C.c_uint64(), dp_scan_stats()
         self._check(self.lib.dp_scan(self._h, template._h, n, m, k, seg_begin, seg_end, strands, algo,
                                      C.byref(hits), C.byref(n_hits), C.byref(st)))
-        try:
-            if n_hits.value:
-                buf = (C.c_char * (n_hits.value * HIT_DTYPE.itemsize)).from_address(hits.value)
-                arr = np.frombuffer(buf, dtype=HIT_DTYPE).copy()
-            else:
-                arr = np.zeros(0, dtype=HIT_DTYPE)
-        finally:
-            self.lib.dp_free(hits)
+        arr = self._take(hits, n_hits.value, HIT_DTYPE)
         return arr, st
 
     def _take(self, ptr, n, dtype):
-        """Copy a malloc()ed result array into numpy and release it."""
-        try:
-            if n:
-                buf = (C.c_char * (n * dtype.itemsize)).from_address(ptr.value)
-                return np.frombuffer(buf, dtype=dtype).copy()
-            return np.zeros(0, dtype=dtype)
-        finally:
-            self.lib.dp_free(ptr)
+        """A malloc()ed result array as numpy.  Small results are copied and released;
+        large ones are wrapped in place and released (dp_free) when the last view dies."""
+        nbytes = n * dtype.itemsize
+        if nbytes < (1 << 16):
+            try:
+                if n:
+                    buf = (C.c_char * nbytes).from_address(ptr.value)
+                    return np.frombuffer(buf, dtype=dtype).copy()
+                return np.zeros(0, dtype=dtype)
+            finally:
+                self.lib.dp_free(ptr)
+        buf = (C.c_char * nbytes).from_address(ptr.value)
+        buf._owner = _Owner(self.lib, ptr.value)          # numpy -> memoryview -> buf -> owner
+        return np.frombuffer(buf, dtype=dtype)
 
     def prepare(self, masters, mismatches, variants):
         """The primer side of dp_find as ready-made C arrays (build once, scan many
@@ -468,14 +481,7 @@ class Context(object):
         self._check(self.lib.dp_duplex_dg(self._h, template._h, _ptr(hits), len(hits), len(pl), _ptr(pl),
                                           _ptr(vc), _ptr(vo), C.cast(C.c_char_p(vb), C.c_void_p),
                                           C.byref(cond), C.byref(out), C.byref(n_out), C.byref(st)))
-        try:
-            if n_out.value:
-                buf = (C.c_char * (n_out.value * DIMER_DTYPE.itemsize)).from_address(out.value)
-                arr = np.frombuffer(buf, dtype=DIMER_DTYPE).copy()
-            else:
-                arr = np.zeros(0, dtype=DIMER_DTYPE)
-        finally:
-            self.lib.dp_free(out)
+        arr = self._take(out, n_out.value, DIMER_DTYPE)
         return arr, st
 
     def calibrate(self, which, reps=5):

@@ -160,7 +160,7 @@ int dp_comm_hits(dp_ctx* ctx, dp_hit** hits_out, uint64_t* n_out) {
                                        "dp_comm_hits handles one segment per rank", r, (unsigned long long)h[6]);
     total += n;
   }
-  dp_hit* out = (dp_hit*)malloc(std::max<uint64_t>(1, total) * sizeof(dp_hit));
+  dp_hit* out = (dp_hit*)dp_result_alloc(std::max<uint64_t>(1, total) * sizeof(dp_hit));
   if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu hits", (unsigned long long)total);
   uint64_t w = 0;
   for (int r = 0; r < ctx->comm_world; ++r) {

@@ -18,6 +18,65 @@ int dp_set_error(dp_ctx* ctx, int code, const char* fmt, ...) {
   return code;
 }
 
+// ---- host result blocks ---------------------------------------------------------
+// Large result arrays are recycled: a fresh malloc of tens of MB is an mmap whose
+// pages fault one by one while the results are copied in, which costs more than the
+// kernels that produced them.  dp_free() parks big blocks here (a few, process wide)
+// and the next call takes one that fits.
+#include <mutex>
+namespace {
+struct result_block { void* p; size_t bytes; };
+std::mutex g_blocks_mutex;
+result_block g_blocks[4] = {{nullptr, 0}, {nullptr, 0}, {nullptr, 0}, {nullptr, 0}};
+const size_t kBigBlock = 1u << 20;
+struct block_header { size_t bytes; size_t magic; };          // in front of every block
+const size_t kMagic = 0x44504253554C5453ull;
+}  // namespace
+
+void* dp_result_alloc(size_t bytes) {
+  if (bytes == 0) bytes = 1;
+  if (bytes >= kBigBlock) {
+    std::lock_guard<std::mutex> lock(g_blocks_mutex);
+    int best = -1;
+    for (int i = 0; i < 4; ++i)
+      if (g_blocks[i].p && g_blocks[i].bytes >= bytes && g_blocks[i].bytes <= 2 * bytes + kBigBlock &&
+          (best < 0 || g_blocks[i].bytes < g_blocks[best].bytes))
+        best = i;
+    if (best >= 0) {
+      void* p = g_blocks[best].p;
+      g_blocks[best].p = nullptr;
+      g_blocks[best].bytes = 0;
+      return (char*)p + sizeof(block_header);
+    }
+  }
+  block_header* h = (block_header*)malloc(sizeof(block_header) + bytes);
+  if (!h) return nullptr;
+  h->bytes = bytes;
+  h->magic = kMagic;
+  return (char*)h + sizeof(block_header);
+}
+
+void dp_result_free(void* p) {
+  if (!p) return;
+  block_header* h = (block_header*)((char*)p - sizeof(block_header));
+  if (h->magic != kMagic) { free(p); return; }               // not ours: plain malloc
+  if (h->bytes >= kBigBlock) {
+    std::lock_guard<std::mutex> lock(g_blocks_mutex);
+    int slot = -1;
+    for (int i = 0; i < 4; ++i) if (!g_blocks[i].p) { slot = i; break; }
+    if (slot < 0) {                                            // evict the smallest parked block
+      slot = 0;
+      for (int i = 1; i < 4; ++i) if (g_blocks[i].bytes < g_blocks[slot].bytes) slot = i;
+      if (g_blocks[slot].bytes >= h->bytes) { free(h); return; }
+      free(g_blocks[slot].p);
+    }
+    g_blocks[slot].p = h;
+    g_blocks[slot].bytes = h->bytes;
+    return;
+  }
+  free(h);
+}
+
 cudaError_t dp_pool_alloc(dp_ctx* ctx, void** p, size_t bytes) {
   return cudaMallocFromPoolAsync(p, bytes ? bytes : 1, ctx->pool, ctx->stream);
 }
@@ -206,7 +265,7 @@ int dp_synchronize(dp_ctx* ctx) {
 
 const char* dp_last_error(const dp_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
-void dp_free(void* p) { free(p); }
+void dp_free(void* p) { dp_result_free(p); }
 
 int dp_abort_requested(dp_ctx* ctx, int flag) {
   if (!ctx) return 0;

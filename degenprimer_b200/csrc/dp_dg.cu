@@ -329,6 +329,84 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
   if (n_tried) atomicAdd(&A.counters[DP_C_TRIED], n_tried);
 }
 
+// ---- large results: final dp_dimer records are laid out by the device -----------------
+// (a) dimers per hit slot, (b) after the host has sorted the hits and turned the
+// counts into output offsets: every pair's dimers copied to their final place with
+// (hit rank, variant) filled in.  One warp per hit slot, lanes over variants.
+struct dp_slot_info {
+  uint64_t final_off;   // first output record of this hit
+  uint32_t rank;        // index of the hit in the sorted hit list
+  uint32_t count;       // in: dimers of the hit (written by the count kernel)
+};
+
+__global__ void __launch_bounds__(128)
+dp_hit_count_kernel(const dp_raw_hit* __restrict__ hits, uint64_t n_hits, const uint64_t* __restrict__ dir,
+                    const __grid_constant__ dp_dg_plan plan, dp_slot_info* __restrict__ info) {
+  const uint64_t slot = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t lane = threadIdx.x & 31u;
+  if (slot >= n_hits) return;
+  const dp_raw_hit h = hits[slot];
+  const uint32_t V = plan.var_count[plan.pat_primer[h.pattern]];
+  uint32_t c = 0;
+  for (uint32_t v = lane; v < V; v += 32) c += (uint32_t)(dir[(uint64_t)h.pair_base + v] & 0xFFFFu);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+  if (lane == 0) info[slot].count = c;
+}
+
+__global__ void __launch_bounds__(128)
+dp_dimer_gather_kernel(const dp_raw_hit* __restrict__ hits, uint64_t n_hits, const uint64_t* __restrict__ dir,
+                       const dp_raw_dimer* __restrict__ raw, const __grid_constant__ dp_dg_plan plan,
+                       const dp_slot_info* __restrict__ info, dp_dimer* __restrict__ out) {
+  const uint64_t slot = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t lane = threadIdx.x & 31u;
+  if (slot >= n_hits) return;
+  const dp_raw_hit h = hits[slot];
+  const uint32_t V = plan.var_count[plan.pat_primer[h.pattern]];
+  const dp_slot_info si = info[slot];
+  uint64_t running = si.final_off;
+  for (uint32_t v0 = 0; v0 < V; v0 += 32) {
+    const uint32_t v = v0 + lane;
+    const uint64_t e = v < V ? dir[(uint64_t)h.pair_base + v] : 0ull;
+    const uint32_t c = (uint32_t)(e & 0xFFFFu);
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t x = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= (uint32_t)o) incl += x;
+    }
+    const uint64_t dest = running + incl - c;
+    const uint64_t src = e >> 16;
+    for (uint32_t k = 0; k < c; ++k) {
+      dp_dimer d;
+      d.hit = si.rank;
+      d.variant = v;
+      d.match_mask = raw[src + k].match_mask;
+      d.dG = raw[src + k].dG;
+      out[dest + k] = d;
+    }
+    running += __shfl_sync(0xFFFFFFFFu, incl, 31);
+  }
+}
+
+int dp_dg_hit_counts(dp_ctx* ctx, const dp_dg_plan& plan, uint64_t n_hits, void* d_info) {
+  if (!n_hits) return DP_OK;
+  const uint64_t threads = n_hits * 32;
+  dp_hit_count_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, ctx->stream>>>(
+      ctx->d_hits, n_hits, ctx->d_dir, plan, (dp_slot_info*)d_info);
+  DP_CUDA(ctx, cudaGetLastError());
+  return DP_OK;
+}
+
+int dp_dg_gather(dp_ctx* ctx, const dp_dg_plan& plan, uint64_t n_hits, const void* d_info, dp_dimer* d_out) {
+  if (!n_hits) return DP_OK;
+  const uint64_t threads = n_hits * 32;
+  dp_dimer_gather_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, ctx->stream>>>(
+      ctx->d_hits, n_hits, ctx->d_dir, ctx->d_dimers, plan, (const dp_slot_info*)d_info, d_out);
+  DP_CUDA(ctx, cudaGetLastError());
+  return DP_OK;
+}
+
 int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches) {
   dp_duplex_args A;
   A.dg.T = ctx->d_tables;

@@ -452,6 +452,10 @@ struct dp_host_results {
   std::vector<char> big;
 };
 
+static bool results_are_large(bool with_dg, const dp_sizes& S) {
+  return with_dg && (S.n_pairs > DP_SPEC_PAIRS || S.n_dimers > DP_SPEC_DIMERS);
+}
+
 static int fetch_all(dp_ctx* ctx, bool with_dg, const dp_sizes& S, dp_host_results& R) {
   const bool spec_ok = S.n_hits <= DP_SPEC_HITS && (!with_dg || (S.n_pairs <= DP_SPEC_PAIRS && S.n_dimers <= DP_SPEC_DIMERS));
   if (spec_ok) {
@@ -488,7 +492,7 @@ static int fetch_all(dp_ctx* ctx, bool with_dg, const dp_sizes& S, dp_host_resul
 // order[i] = raw slot of output hit i.
 static int hits_to_abi(dp_ctx* ctx, const dp_template* t, const dp_scan_job& J, const dp_raw_hit* raw,
                        uint64_t n, dp_hit** out_p, std::vector<uint32_t>* order_p) {
-  dp_hit* out = (dp_hit*)malloc(std::max<uint64_t>(1, n) * sizeof(dp_hit));
+  dp_hit* out = (dp_hit*)dp_result_alloc(std::max<uint64_t>(1, n) * sizeof(dp_hit));
   if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu hits", (unsigned long long)n);
   std::vector<dp_hit> tmp(n);
   for (uint64_t i = 0; i < n; ++i) {
@@ -523,7 +527,7 @@ static int hits_to_abi(dp_ctx* ctx, const dp_template* t, const dp_scan_job& J, 
 template <typename VarCount>
 static int dimers_to_abi(dp_ctx* ctx, const dp_host_results& R, const dp_sizes& S, const std::vector<uint32_t>& order,
                          VarCount var_of_hit, dp_dimer** out_p, uint64_t* n_out_p) {
-  dp_dimer* out = (dp_dimer*)malloc(std::max<uint64_t>(1, S.n_dimers) * sizeof(dp_dimer));
+  dp_dimer* out = (dp_dimer*)dp_result_alloc(std::max<uint64_t>(1, S.n_dimers) * sizeof(dp_dimer));
   if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu dimers", (unsigned long long)S.n_dimers);
   uint64_t w = 0;
   for (size_t i = 0; i < order.size(); ++i) {
@@ -534,7 +538,7 @@ static int dimers_to_abi(dp_ctx* ctx, const dp_host_results& R, const dp_sizes& 
       const uint64_t off = e >> 16;
       const uint32_t cnt = (uint32_t)(e & 0xFFFFu);
       if (off + cnt > S.n_dimers || w + cnt > S.n_dimers) {
-        free(out);
+        dp_result_free(out);
         return dp_set_error(ctx, DP_ERR_STATE, "internal: duplex directory is inconsistent");
       }
       for (uint32_t k = 0; k < cnt; ++k) {
@@ -548,6 +552,66 @@ static int dimers_to_abi(dp_ctx* ctx, const dp_host_results& R, const dp_sizes& 
   }
   *out_p = out;
   *n_out_p = w;
+  return DP_OK;
+}
+
+// Large results: the device counts the dimers of every hit, the host turns the counts
+// into output offsets in sorted-hit order, the device writes final dp_dimer records,
+// one copy brings them back.  order[i] = raw slot of output hit i.
+static int dimers_large(dp_ctx* ctx, const dp_dg_plan& plan, const std::vector<uint32_t>& order, const dp_sizes& S,
+                        dp_dimer** out_p, uint64_t* n_out_p) {
+  const uint64_t n = order.size();
+  cudaStream_t st = ctx->stream;
+  void* d_info = nullptr;
+  dp_dimer* d_final = nullptr;
+  DP_CUDA(ctx, dp_pool_alloc(ctx, &d_info, n * sizeof(dp_slot_info_host)));
+  int rc = dp_dg_hit_counts(ctx, plan, n, d_info);
+  if (rc == DP_OK) rc = dp_ws_pinned(ctx, n * sizeof(dp_slot_info_host));
+  if (rc) { dp_pool_free(ctx, d_info); return rc; }
+  dp_slot_info_host* h = (dp_slot_info_host*)ctx->h_res;
+  cudaError_t e = cudaMemcpyAsync(h, d_info, n * sizeof(dp_slot_info_host), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  uint64_t run = 0;
+  if (e == cudaSuccess) {
+    for (uint64_t i = 0; i < n; ++i) {
+      dp_slot_info_host& x = h[order[i]];
+      x.final_off = run;
+      x.rank = (uint32_t)i;
+      run += x.count;
+    }
+    if (run != S.n_dimers) {
+      dp_pool_free(ctx, d_info);
+      return dp_set_error(ctx, DP_ERR_STATE, "internal: per-hit dimer counts (%llu) disagree with the total (%llu)",
+                          (unsigned long long)run, (unsigned long long)S.n_dimers);
+    }
+    e = cudaMemcpyAsync(d_info, h, n * sizeof(dp_slot_info_host), cudaMemcpyHostToDevice, st);
+  }
+  if (e == cudaSuccess) e = dp_pool_alloc(ctx, (void**)&d_final, std::max<uint64_t>(1, run) * sizeof(dp_dimer));
+  dp_dimer* out = nullptr;
+  if (e == cudaSuccess) {
+    rc = dp_dg_gather(ctx, plan, n, d_info, d_final);
+    if (rc == DP_OK) {
+      out = (dp_dimer*)dp_result_alloc(std::max<uint64_t>(1, run) * sizeof(dp_dimer));
+      if (!out) rc = dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu dimers", (unsigned long long)run);
+    }
+    const size_t bytes = run * sizeof(dp_dimer);
+    if (rc == DP_OK && run && bytes <= (256u << 20)) {
+      // through pinned memory at PCIe speed, then one host memcpy into the (recycled) block
+      rc = dp_ws_pinned(ctx, bytes);
+      if (rc == DP_OK) e = cudaMemcpyAsync(ctx->h_res, d_final, bytes, cudaMemcpyDeviceToHost, st);
+      if (rc == DP_OK && e == cudaSuccess) e = cudaStreamSynchronize(st);
+      if (rc == DP_OK && e == cudaSuccess) memcpy(out, ctx->h_res, bytes);
+    } else if (rc == DP_OK && run) {
+      e = cudaMemcpyAsync(out, d_final, bytes, cudaMemcpyDeviceToHost, st);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    }
+  }
+  dp_pool_free(ctx, d_info);
+  dp_pool_free(ctx, d_final);
+  if (rc) { dp_result_free(out); return rc; }
+  if (e != cudaSuccess) { dp_result_free(out); return dp_set_error(ctx, DP_ERR_CUDA, "large-result gather: %s", cudaGetErrorString(e)); }
+  *out_p = out;
+  *n_out_p = run;
   return DP_OK;
 }
 
@@ -696,7 +760,8 @@ static int pipeline_wait(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, cons
     rc = pipeline_enqueue(ctx, t, J, dg, P);
     if (rc) return rc;
   }
-  return fetch_all(ctx, dg != nullptr, S, R);
+  // large duplex results are laid out by the device (dimers_large): only the hits come back here
+  return fetch_all(ctx, dg != nullptr && !results_are_large(true, S), S, R);
 }
 
 static void pipeline_init(dp_pipeline_state& P) {
@@ -817,8 +882,11 @@ extern "C" int dp_find_end(dp_ctx* ctx, dp_hit** hits_out, uint64_t* n_hits_out,
   *n_hits_out = S.n_hits;
   const dp_hit* hits = *hits_out;
   const std::vector<uint32_t>& vc = F.var_count;
-  rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return vc[hits[i].primer]; }, dimers_out, n_dimers_out);
-  if (rc) { free(*hits_out); *hits_out = nullptr; *n_hits_out = 0; return rc; }
+  if (results_are_large(true, S))
+    rc = dimers_large(ctx, F.DL.plan, order, S, dimers_out, n_dimers_out);
+  else
+    rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return vc[hits[i].primer]; }, dimers_out, n_dimers_out);
+  if (rc) { dp_result_free(*hits_out); *hits_out = nullptr; *n_hits_out = 0; return rc; }
   fill_scan_stats(ctx, F.t, F.J, S, F.P.ms_scan, F.P.ms_main, F.P.scan_launches, stats);
   if (stats) stats->reserved = F.P.overflowed ? 1.f : 0.f;     // the wire mirror of the first attempt is stale
   if (dg_stats) {
@@ -875,7 +943,7 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
   if (stats) memset(stats, 0, sizeof *stats);
   if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
   if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
-  if (n_hits == 0) { *dimers_out = (dp_dimer*)malloc(sizeof(dp_dimer)); return DP_OK; }
+  if (n_hits == 0) { *dimers_out = (dp_dimer*)dp_result_alloc(sizeof(dp_dimer)); return DP_OK; }
   if (n_hits > 0xF0000000ull) return dp_set_error(ctx, DP_ERR_ARG, "more than 4e9 hits in one call");
   if (n_primers > DP_MAX_PRIMERS) return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -958,16 +1026,19 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
     }
     break;
   }
-  // the raw hits are still in pinned memory; fetch_all would overwrite them when it
-  // has to grow the buffer, so keep a private copy of what assembly needs
-  std::vector<dp_raw_hit> raw_copy(raw, raw + n_hits);
-  S.n_hits = 0;                          // nothing to copy back for the hits
-  rc = fetch_all(ctx, true, S, R);
-  if (rc) return rc;
-  R.hits = raw_copy.data();
   std::vector<uint32_t> order(n_hits);
   for (uint64_t i = 0; i < n_hits; ++i) order[i] = (uint32_t)i;
-  rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return var_count[hits[i].primer]; }, dimers_out, n_dimers_out);
+  if (results_are_large(true, S)) {
+    rc = dimers_large(ctx, DL.plan, order, S, dimers_out, n_dimers_out);
+  } else {
+    // small: directory + dimers already sit in the published prefix; the raw hits are
+    // still in the pinned staging area behind it
+    S.n_hits = 0;
+    rc = fetch_all(ctx, true, S, R);
+    if (rc) return rc;
+    R.hits = raw;
+    rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return var_count[hits[i].primer]; }, dimers_out, n_dimers_out);
+  }
   if (rc) return rc;
   if (stats) {
     stats->duplexes = pairs;

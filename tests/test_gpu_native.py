@@ -260,3 +260,37 @@ def test_run_boundary_windows(ctx):
             f, r = split_hits(hits, 0)
             assert np.array_equal(f, ref[4]) and np.array_equal(r, ref[5]), (k, algo)
         assert len(ref[4]) > 5
+
+
+def test_large_duplex_results_device_layout(ctx):
+    """More (hit, variant) pairs / dimers than the published prefix holds: the final
+    dimer records are laid out by the device (count -> offsets -> gather).  Must equal
+    the small path run hit by hit, for dp_find and for dp_duplex_dg."""
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200.SeqUtils import unambiguous_sequences
+    rng = np.random.default_rng(91)
+    masters = ['ATARTCTYCGAMGGCNATKC', 'GAASGCRAAKATYGGGAAC']      # 64 and 16 variants
+    t = random_dna(rng, 120000, 'ACGTN', p=[0.2495] * 4 + [0.002])
+    t, _ = plant_sites(rng, t, masters, 3, 60)
+    tdf.PCR_P.set(dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=50.0))
+    cond = tdf.conditions()
+    tmpl = ctx.template_from_sequences([t])
+    var = [unambiguous_sequences(m) for m in masters]
+    hits, dimers, st, dst = ctx.find(tmpl, masters, 3, var, cond)
+    assert dst['duplexes'] > 4096 and len(dimers) > 2048          # the large path was taken
+    lens = [len(m) for m in masters]
+    offs = [0, len(var[0]) * lens[0]]
+    blob = ''.join(var[0]) + ''.join(var[1])
+    d2, _ = ctx.duplex_dg(tmpl, hits, lens, [len(v) for v in var], offs, blob, cond)
+    assert np.array_equal(d2, dimers)
+    # reference: small calls of 2 hits each (published-prefix path), indices shifted
+    parts = []
+    for a in range(0, len(hits), 2):
+        d, s = ctx.duplex_dg(tmpl, hits[a:a + 2], lens, [len(v) for v in var], offs, blob, cond)
+        assert s['duplexes'] <= 4096 and len(d) <= 2048
+        d = d.copy()
+        d['hit'] += a
+        parts.append(d)
+    want = np.concatenate(parts)
+    assert np.array_equal(want, dimers)
+    assert np.all(np.diff(dimers['hit'].astype(np.int64)) >= 0)
