@@ -357,9 +357,18 @@ def run_ours(args):
     ms_main = acc['ms_main'] / K
     algo_bytes = 0.25 * bp                      # 2 bits per template base, read once
     achieved = algo_bytes / (ms_main * 1e-3) / 1e9 if ms_main > 0 else 0.0
+    kernel = 'dp_scan_bitslice_kernel' if st['algo'] == 2 else 'dp_scan_popc_kernel'
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as fh:
+            entry = json.load(fh).get(args.workload, {}).get(kernel)
+        if entry and args.scale == 1.0:
+            traffic = entry['bytes_per_launch']
+    except Exception:
+        pass
     roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s',
-                'frac': achieved / hbm_peak, 'traffic': None,
-                'kernel': 'dp_scan_bitslice_kernel' if st['algo'] == 2 else 'dp_scan_popc_kernel',
+                'frac': achieved / hbm_peak, 'traffic': traffic,
+                'kernel': kernel,
                 'ms_per_launch': ms_main, 'algorithmic_bytes_per_launch': algo_bytes,
                 'peak_source': peak_src}
     # integer-pipe view (the path is integer/bitwise work; canonical op counts of SURVEY §8d)

@@ -33,16 +33,27 @@ struct dp_bs_pattern {
   uint32_t pattern;                 // index into c_patterns
 };
 
-template <int NP>
+// One launch group: up to NB patterns with the same K and the same number of plane
+// terms.  The group carries its own copy of the patterns (local index) next to the
+// prefilter entries; bs[i].pattern stays the index in the call's pattern list (that
+// is what a hit reports).
+#define DP_BS_GROUP_SMALL 8
+#define DP_BS_GROUP_LARGE 32
+template <int NB>
 struct dp_bs_set {
-  dp_bs_pattern bs[NP];
+  dp_bs_pattern bs[NB];
+  dp_pattern pat[NB];
+};
+
+struct dp_bitslice_group {
+  int K, E;
+  std::vector<dp_bs_pattern> pats;
 };
 
 struct dp_bitslice_plan {
-  int K, E;
   uint32_t n;                       // patterns handled by the prefilter
-  uint64_t pmask[2];                // the same set as a bit mask over c_patterns
-  std::vector<dp_bs_pattern> pats;
+  uint64_t pmask[2];                // the same set as a bit mask over the call's patterns
+  std::vector<dp_bitslice_group> groups;
 };
 
 // ---- bit-sliced population count of N one-bit planes ----------------------------
@@ -130,10 +141,13 @@ __device__ __forceinline__ void dp_bs_pattern_step(const dp_scan_args& A, const 
   }
 }
 
-template <int K, int E, int NP>
-__global__ void __launch_bounds__(DP_BS_THREADS, 3)
-dp_scan_bitslice_kernel(const __grid_constant__ dp_scan_args A, const __grid_constant__ dp_pattern_set<NP> PS,
-                        const __grid_constant__ dp_bs_set<NP> BS, uint32_t n_bs) {
+// resident CTAs per SM the register budget is tuned for: shared memory allows
+// 5 / 5 / 4 / 3 / 3 CTAs for K = 0..4 (4*(8+2K)+1 planes of 1 KB each)
+__host__ __device__ constexpr int dp_bs_min_blocks(int K) { return K <= 1 ? 5 : K == 2 ? 4 : 3; }
+
+template <int K, int E, int NB>
+__global__ void __launch_bounds__(DP_BS_THREADS, dp_bs_min_blocks(K))
+dp_scan_bitslice_kernel(const __grid_constant__ dp_scan_args A, const __grid_constant__ dp_bs_set<NB> BS, uint32_t n_bs) {
   constexpr int J = 8 + 2 * K;
   extern __shared__ uint32_t dp_bs_smem[];
   uint32_t* col = dp_bs_smem + threadIdx.x;
@@ -165,17 +179,11 @@ dp_scan_bitslice_kernel(const __grid_constant__ dp_scan_args A, const __grid_con
       col[(4 * j + 2) * DP_BS_THREADS] = hs & ~ls;    // T
       col[(4 * j + 3) * DP_BS_THREADS] = hs & ls;     // G
     }
-    if constexpr (NP <= DP_NP_SMALL) {
-      // few patterns: unrolled, so every plane offset is a kernel-parameter constant
-      // held in a uniform register (no per-word LDC + address add)
+    // unrolled over the group, so every plane offset is a kernel-parameter constant
+    // that reaches LDS through a uniform register (no per-word LDC + address add)
 #pragma unroll
-      for (int p = 0; p < NP; ++p)
-        if (p < (int)n_bs) dp_bs_pattern_step<K, E>(A, PS.pat[BS.bs[p].pattern], BS.bs[p], col, w, n_cand);
-    } else {
-#pragma unroll 1
-      for (uint32_t p = 0; p < n_bs; ++p)
-        dp_bs_pattern_step<K, E>(A, PS.pat[BS.bs[p].pattern], BS.bs[p], col, w, n_cand);
-    }
+    for (int p = 0; p < NB; ++p)
+      if (p < (int)n_bs) dp_bs_pattern_step<K, E>(A, BS.pat[p], BS.bs[p], col, w, n_cand);
     w = wn;
     h0 = nh0; h1 = nh1; l0 = nl0; l1 = nl1;
   }
@@ -202,31 +210,23 @@ static double dp_bs_alive_probability(const std::vector<uint8_t>& letters, int o
   return s;
 }
 
-// Decides which patterns take the prefilter.  Returns false if none does.
+// Decides which patterns take the prefilter and how they are grouped into launches.
+// Returns false if none does.
 static bool dp_bitslice_make_plan(const std::vector<dp_pattern>& pats,
                                   const std::vector<std::vector<uint8_t>>& letters,
                                   dp_bitslice_plan& plan) {
   plan.n = 0;
   plan.pmask[0] = plan.pmask[1] = 0;
-  plan.pats.clear();
-  // K of each pattern; the launch takes the most frequent one
-  std::vector<int> Ks(pats.size());
-  int votes[DP_BS_MAX_K + 1] = {0};
+  plan.groups.clear();
+  // (K, E class) -> prefilter entries
+  std::vector<dp_bs_pattern> bucket[DP_BS_MAX_K + 1][4];
+  static const int E_CLASS[4] = {0, 2, 4, 8};
   for (size_t p = 0; p < pats.size(); ++p) {
-    int need = (pats[p].thr3 + 1) / 3;
-    Ks[p] = pats[p].len - need;
-    if (Ks[p] >= 0 && Ks[p] <= DP_BS_MAX_K && pats[p].len >= 8 + 2 * Ks[p]) ++votes[Ks[p]];
-  }
-  int K = -1, best = 0;
-  for (int k = 0; k <= DP_BS_MAX_K; ++k)
-    if (votes[k] > best) { best = votes[k]; K = k; }
-  if (K < 0) return false;
-  const int J = 8 + 2 * K;
-  int E = 0;
-  struct Choice { int o, terms; };
-  std::vector<Choice> choice(pats.size(), Choice{-1, 0});
-  for (size_t p = 0; p < pats.size(); ++p) {
-    if (Ks[p] != K || pats[p].len < J) continue;
+    const int need = (pats[p].thr3 + 1) / 3;
+    const int K = pats[p].len - need;
+    if (K < 0 || K > DP_BS_MAX_K) continue;
+    const int J = 8 + 2 * K;
+    if ((int)pats[p].len < J) continue;
     const std::vector<uint8_t>& lt = letters[p];
     double best_p = 2.0;
     int best_o = -1, best_terms = 0;
@@ -240,75 +240,88 @@ static bool dp_bitslice_make_plan(const std::vector<dp_pattern>& pats,
       }
     }
     if (best_o < 0 || best_p > 2e-3) continue;   // too unselective: kernel 1 is cheaper
-    choice[p] = Choice{best_o, best_terms};
-    E = std::max(E, best_terms - J);
-  }
-  E = E == 0 ? 0 : E <= 2 ? 2 : E <= 4 ? 4 : 8;
-  const int NT = J + E;
-  for (size_t p = 0; p < pats.size(); ++p) {
-    if (choice[p].o < 0) continue;
+    const int extra = best_terms - J;
+    const int ec = extra == 0 ? 0 : extra <= 2 ? 1 : extra <= 4 ? 2 : 3;
+    const int NT = J + E_CLASS[ec];
     dp_bs_pattern bp;
     memset(&bp, 0, sizeof bp);
-    bp.anchor = (uint32_t)choice[p].o;
+    bp.anchor = (uint32_t)best_o;
     bp.pattern = (uint32_t)p;
     int n = 0;
     for (int j = 0; j < J; ++j) {
-      uint32_t set = dp_letter_set(letters[p][choice[p].o + j]);
+      uint32_t set = dp_letter_set(lt[best_o + j]);
       for (int c = 0; c < 4; ++c)
         if (set & (1u << c)) bp.term[n++] = (uint32_t)((4 * j + c) * DP_BS_THREADS * sizeof(uint32_t));
     }
-    for (; n < NT; ++n) bp.term[n] = (uint32_t)(4 * J * DP_BS_THREADS * sizeof(uint32_t));
-    plan.pats.push_back(bp);
+    for (; n < NT; ++n) bp.term[n] = (uint32_t)(4 * J * DP_BS_THREADS * sizeof(uint32_t));   // the all-zero plane
+    bucket[K][ec].push_back(bp);
     plan.pmask[p >> 6] |= 1ull << (p & 63);
+    ++plan.n;
   }
-  plan.K = K;
-  plan.E = E;
-  plan.n = (uint32_t)plan.pats.size();
+  // launches of at most DP_BS_GROUP_LARGE patterns, evenly filled (every launch rebuilds
+  // the planes of a word once, so fewer and fuller groups are cheaper)
+  for (int K = 0; K <= DP_BS_MAX_K; ++K)
+    for (int ec = 0; ec < 4; ++ec) {
+      const std::vector<dp_bs_pattern>& b = bucket[K][ec];
+      if (b.empty()) continue;
+      const size_t n_groups = (b.size() + DP_BS_GROUP_LARGE - 1) / DP_BS_GROUP_LARGE;
+      const size_t per = (b.size() + n_groups - 1) / n_groups;
+      for (size_t at = 0; at < b.size(); at += per) {
+        dp_bitslice_group g;
+        g.K = K;
+        g.E = E_CLASS[ec];
+        g.pats.assign(b.begin() + at, b.begin() + std::min(b.size(), at + per));
+        plan.groups.push_back(g);
+      }
+    }
   return plan.n > 0;
 }
 
-template <int K, int E, int NP>
+template <int K, int E, int NB>
 static int dp_bitslice_launch_one(dp_ctx* ctx, const dp_scan_args& A, const std::vector<dp_pattern>& pats,
-                                  const dp_bitslice_plan& plan) {
+                                  const dp_bitslice_group& g) {
   constexpr int J = 8 + 2 * K;
   const size_t smem = (size_t)(4 * J + 1) * DP_BS_THREADS * sizeof(uint32_t);
   static bool configured[16] = {false};      // per device
   static int per_sm_cached[16] = {0};
   const int dev = ctx->device & 15;
   if (!configured[dev]) {
-    DP_CUDA(ctx, cudaFuncSetAttribute(dp_scan_bitslice_kernel<K, E, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DP_CUDA(ctx, cudaFuncSetAttribute(dp_scan_bitslice_kernel<K, E, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 1;
-    DP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_scan_bitslice_kernel<K, E, NP>, DP_BS_THREADS, smem));
+    DP_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_scan_bitslice_kernel<K, E, NB>, DP_BS_THREADS, smem));
     per_sm_cached[dev] = per_sm < 1 ? 1 : per_sm;
     configured[dev] = true;
   }
-  dp_pattern_set<NP> PS;
-  dp_bs_set<NP> BS;
-  memset(&PS, 0, sizeof PS);
+  static thread_local dp_bs_set<NB> BS;
   memset(&BS, 0, sizeof BS);
-  memcpy(PS.pat, pats.data(), pats.size() * sizeof(dp_pattern));
-  memcpy(BS.bs, plan.pats.data(), plan.pats.size() * sizeof(dp_bs_pattern));
+  for (size_t i = 0; i < g.pats.size(); ++i) {
+    BS.bs[i] = g.pats[i];
+    BS.pat[i] = pats[g.pats[i].pattern];
+  }
   const uint64_t words = A.word_end + 2 - A.word_begin;
   unsigned blocks = (unsigned)std::min<uint64_t>((words + DP_BS_THREADS - 1) / DP_BS_THREADS,
                                                  (uint64_t)ctx->sm_count * per_sm_cached[dev]);
-  dp_scan_bitslice_kernel<K, E, NP><<<blocks, DP_BS_THREADS, smem, ctx->stream>>>(A, PS, BS, plan.n);
+  dp_scan_bitslice_kernel<K, E, NB><<<blocks, DP_BS_THREADS, smem, ctx->stream>>>(A, BS, (uint32_t)g.pats.size());
   DP_CUDA(ctx, cudaGetLastError());
   return DP_OK;
 }
 
 static int dp_bitslice_launch(dp_ctx* ctx, const dp_scan_args& A, const std::vector<dp_pattern>& pats,
                               const dp_bitslice_plan& plan, uint32_t* launches) {
-  int rc = DP_ERR_ARG;
-  const bool small = pats.size() <= DP_NP_SMALL;
+  for (const dp_bitslice_group& g : plan.groups) {
+    int rc = DP_ERR_ARG;
+    const bool small = g.pats.size() <= DP_BS_GROUP_SMALL;
 #define DP_BS_CASE(KK, EE)                                                                        \
-  if (plan.K == KK && plan.E == EE)                                                               \
-    rc = small ? dp_bitslice_launch_one<KK, EE, DP_NP_SMALL>(ctx, A, pats, plan)                  \
-               : dp_bitslice_launch_one<KK, EE, DP_MAX_PATTERNS>(ctx, A, pats, plan);
+    if (g.K == KK && g.E == EE)                                                                   \
+      rc = small ? dp_bitslice_launch_one<KK, EE, DP_BS_GROUP_SMALL>(ctx, A, pats, g)             \
+                 : dp_bitslice_launch_one<KK, EE, DP_BS_GROUP_LARGE>(ctx, A, pats, g);
 #define DP_BS_ROW(KK) DP_BS_CASE(KK, 0) DP_BS_CASE(KK, 2) DP_BS_CASE(KK, 4) DP_BS_CASE(KK, 8)
-  DP_BS_ROW(0) DP_BS_ROW(1) DP_BS_ROW(2) DP_BS_ROW(3) DP_BS_ROW(4)
+    DP_BS_ROW(0) DP_BS_ROW(1) DP_BS_ROW(2) DP_BS_ROW(3) DP_BS_ROW(4)
 #undef DP_BS_ROW
 #undef DP_BS_CASE
-  if (rc == DP_ERR_ARG) return dp_set_error(ctx, DP_ERR_STATE, "internal: no bit-slice kernel for K=%d E=%d", plan.K, plan.E);
-  if (rc == DP_OK) ++*launches;
-  return rc;
+    if (rc == DP_ERR_ARG) return dp_set_error(ctx, DP_ERR_STATE, "internal: no bit-slice kernel for K=%d E=%d", g.K, g.E);
+    if (rc) return rc;
+    ++*launches;
+  }
+  return DP_OK;
 }
