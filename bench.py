@@ -63,56 +63,57 @@ def variants_of(primers):
 
 # ---- clocks -------------------------------------------------------------------------
 class ClockSampler(object):
-    """nvidia-smi samples DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
-         'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
-         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md) through
+    NVML in a background thread (every 2 ms; the nvidia-smi CLI takes longer to start than the
+    timed region lasts)."""
+    REASONS = (('hw_slowdown', 0x8), ('hw_thermal_slowdown', 0x40), ('sw_thermal_slowdown', 0x20),
+               ('sw_power_cap', 0x4))
 
     def __init__(self, device):
         self.device = device
-        self.proc = None
-        self.path = None
+        self.thread = None
+        self.samples, self.maxes, self.bits = [], [], 0
+        self._stop = False
 
     def start(self):
+        import threading
         try:
-            fd, self.path = tempfile.mkstemp(suffix='.clocks.csv')
-            os.close(fd)
-            self.fh = open(self.path, 'w')
-            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.device), '--query-gpu=' + self.Q,
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
-                                         stdout=self.fh, stderr=subprocess.DEVNULL)
+            import pynvml
+            pynvml.nvmlInit()
+            visible = os.environ.get('CUDA_VISIBLE_DEVICES')
+            index = int(visible.split(',')[self.device]) if visible else self.device
+            self.nv = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
         except Exception:
-            self.proc = None
+            self.nv = None
+            return
+
+        def loop():
+            nv, h = self.nv, self.handle
+            while not self._stop:
+                try:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                    self.maxes.append(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+                    self.bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    try:
+                        self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                    except Exception:
+                        pass
+                time.sleep(0.002)
+        self.thread = threading.Thread(target=loop, daemon=True)
+        self.thread.start()
 
     def stop(self):
         out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
-        if self.proc is None:
+        if self.thread is None:
             return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        self.fh.close()
-        sm, mx, reasons = [], [], set()
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        with open(self.path) as fh:
-            for line in fh:
-                f = [x.strip() for x in line.split(',')]
-                if len(f) < 9:
-                    continue
-                try:
-                    sm.append(float(f[1]))
-                    mx.append(float(f[2]))
-                except ValueError:
-                    continue
-                for name, v in zip(names, f[5:9]):
-                    if v.lower().startswith('active'):
-                        reasons.add(name)
-        os.unlink(self.path)
-        if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm))
-        out['reasons'] = sorted(reasons)
+        self._stop = True
+        self.thread.join(timeout=2)
+        if self.samples:
+            out.update(sm_mhz=float(np.median(self.samples)), sm_max_mhz=float(max(self.maxes)) if self.maxes else None,
+                       samples=len(self.samples))
+        out['reasons'] = [name for name, bit in self.REASONS if self.bits & bit]
         return out
 
 
@@ -250,12 +251,15 @@ def run_ours(args):
         # one pass of the hot path: scan of every primer over both strands + dG of every
         # (hit, variant), one stream submission (dp_find), results back on the host
         t = copies[i % n_copies]
-        hits, dimers, st, dst = ctx.find(t, query, cond=cond, algo=args.algo)
-        if exch is None:
-            return hits, dimers, st, dst
-        allh = exch.collect_hits()                      # rank g's segment = record g of the genome
-        hits = allh if allh is not None else sort_hits(all_gather_records(hits))
-        return hits, dimers, st, dst
+        return ctx.find(t, query, cond=cond, algo=args.algo)
+
+    def gathered(age, own):
+        # hits of every rank for a step (rank g's segment = record g of the genome).  The
+        # exchange is double buffered on its own stream: step i's gather overlaps step i+1,
+        # so inside the loop it is collected one step late (age 1) and the last one after
+        # the loop (age 0) — every gather completes inside the timed region.
+        allh = exch.collect_hits(age)
+        return allh if allh is not None else sort_hits(all_gather_records(own))
 
     def sync_all():
         ctx.synchronize()
@@ -277,13 +281,21 @@ def run_ours(args):
     acc = dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, dimers=0, cand=0, windows=0)
     t0 = time.perf_counter()
     ev0.record(kstream)
+    n_gathered = 0
     for i in range(args.steps):
         hits, dimers, st, dst = step(args.warmup + i)
+        if exch is not None:
+            if i > 0:
+                n_gathered += len(gathered(1, hits))
+            if i == args.steps - 1:
+                n_gathered += len(gathered(0, hits))
+        else:
+            n_gathered += len(hits)
         acc['ms_main'] += st['ms_main']
         acc['ms_scan'] += st['ms_scan']
         acc['ms_dg'] += dst['ms_kernel']
         acc['launches'] += st['launches'] + dst['launches']
-        acc['hits'] += len(hits)
+        acc['hits'] = n_gathered
         acc['dimers'] += len(dimers)
         acc['cand'] += st['candidates']
         acc['windows'] = st['windows']

@@ -135,8 +135,8 @@ def _declare(lib):
         'dp_comm_unique_id': (i32, [vp, C.c_char_p]),
         'dp_comm_init': (i32, [vp, C.c_char_p, i32, i32, u32]),
         'dp_comm_destroy': (i32, [vp]),
-        'dp_comm_gathered': (i32, [vp, P(vp), P(u64), P(i32)]),
-        'dp_comm_hits': (i32, [vp, P(vp), P(u64)]),
+        'dp_comm_gathered': (i32, [vp, i32, P(vp), P(u64), P(i32)]),
+        'dp_comm_hits': (i32, [vp, i32, P(vp), P(u64)]),
         'dp_stream': (vp, [vp]),
         'dp_synchronize': (i32, [vp]),
         'dp_hit_windows': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p]),
@@ -421,33 +421,31 @@ class Context(object):
 
     def comm_init(self, unique_id, world, rank, max_hits=4096):
         self._check(self.lib.dp_comm_init(self._h, unique_id, int(world), int(rank), int(max_hits)))
-        ptr, slot, w = C.c_void_p(), C.c_uint64(), C.c_int()
-        self._check(self.lib.dp_comm_gathered(self._h, C.byref(ptr), C.byref(slot), C.byref(w)))
-        self._gather_slot, self._gather_world, self._gather_max = slot.value, w.value, int(max_hits)
-        raw = (C.c_uint8 * (slot.value * w.value)).from_address(ptr.value)
-        self._gather_buf = np.frombuffer(raw, dtype=np.uint8)     # pinned memory owned by the library
+        self._gather_world, self._gather_max = int(world), int(max_hits)
 
     def comm_destroy(self):
-        self._gather_buf = None
         self._check(self.lib.dp_comm_destroy(self._h))
 
-    def gathered_hits(self):
-        """Hits of every rank for the call that just returned (one segment per rank:
-        record = sender rank, positions in that segment), sorted; None if a slot
-        overflowed or a rank holds a multi-record template."""
+    def gathered_hits(self, age=0):
+        """Hits of every rank for a call (one segment per rank: record = sender rank,
+        positions in that segment), sorted.  age 0 = the call that just returned
+        (waits for its gather), age 1 = the call before (already there in a loop).
+        None if a slot overflowed or a rank holds a multi-record template."""
         hits, n = C.c_void_p(), C.c_uint64()
-        rc = self.lib.dp_comm_hits(self._h, C.byref(hits), C.byref(n))
+        rc = self.lib.dp_comm_hits(self._h, int(age), C.byref(hits), C.byref(n))
         if rc == DP_ERR_UNSUPPORTED:
             return None
         self._check(rc)
         return self._take(hits, n.value, HIT_DTYPE)
 
-    def gathered(self):
-        """(raw wire records of every rank for the call that just returned, in one
-        array; sender rank of every record), or None when some rank had more hits
-        than a slot holds."""
-        world, slot, cap = self._gather_world, self._gather_slot, self._gather_max
-        buf = self._gather_buf.reshape(world, slot)
+    def gathered(self, age=0):
+        """(raw wire records of every rank for a call, in one array; sender rank of
+        every record), or None when some rank had more hits than a slot holds."""
+        ptr, slot_b, w = C.c_void_p(), C.c_uint64(), C.c_int()
+        self._check(self.lib.dp_comm_gathered(self._h, int(age), C.byref(ptr), C.byref(slot_b), C.byref(w)))
+        world, slot, cap = w.value, slot_b.value, self._gather_max
+        raw = (C.c_uint8 * (slot * world)).from_address(ptr.value)
+        buf = np.frombuffer(raw, dtype=np.uint8).reshape(world, slot)
         counts = (buf[:, :8].copy().view(np.uint64)[:, 0] & np.uint64(0xFFFFFFFF)).astype(np.int64)
         if int(counts.max()) > cap:
             return None

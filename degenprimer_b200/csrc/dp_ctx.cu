@@ -187,8 +187,13 @@ dp_ctx* dp_create(int device_ordinal) {
   ctx->wire_bytes = 0;
   ctx->comm = nullptr;
   ctx->comm_world = ctx->comm_rank = 0;
-  ctx->d_wire_recv = nullptr;
-  ctx->h_wire_recv = nullptr;
+  ctx->comm_stream = nullptr;
+  ctx->wire_ready = nullptr;
+  ctx->comm_seq = 0;
+  for (int i = 0; i < 2; ++i) {
+    ctx->gather_done[i] = nullptr;
+    ctx->wire_slot[i] = ctx->d_wire_recv[i] = ctx->h_wire_recv[i] = nullptr;
+  }
   ctx->wire_owned = false;
   ctx->stream = ctx->copy_stream = nullptr;
   for (int i = 0; i < 2; ++i) {

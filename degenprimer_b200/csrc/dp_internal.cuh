@@ -129,8 +129,16 @@ struct dp_ctx {
   // multi-GPU hit exchange (dp_comm.cu): NCCL communicator + receive buffers
   void* comm;                  // ncclComm_t
   int comm_world, comm_rank;
-  char* d_wire_recv;           // world x wire_bytes on the device
-  char* h_wire_recv;           // the same, pinned host memory
+  // the exchange is double buffered and runs on its own stream, so that the gather of
+  // call i overlaps call i+1 and nobody waits for the slowest rank inside a call
+  cudaStream_t comm_stream;
+  cudaEvent_t wire_ready;      // main stream: the publish kernel has written the wire slot
+  cudaEvent_t gather_done[2];  // comm stream: slot's gather has landed in h_wire_recv[slot]
+  uint64_t comm_seq;           // calls gathered so far; call i uses slot i & 1
+  char* wire_slot[2];          // send slots (device)
+  char* d_wire_recv[2];        // world x wire_bytes on the device
+  char* h_wire_recv[2];        // the same, pinned host memory
+  dp_dg_plan comm_plan[2];     // (length, strand, primer) of the patterns of the call in each slot
   bool wire_owned;             // `wire` was allocated by dp_comm_init
   dp_dg_plan last_plan;        // (length, strand, primer) of the patterns of the last scan
   uint64_t last_rec0_len;      // its template: length of record 0 and record count
@@ -214,7 +222,10 @@ int dp_ws_dimers(dp_ctx* ctx, uint64_t cap);
 int dp_ws_codes(dp_ctx* ctx, uint64_t cap);
 int dp_ws_pinned(dp_ctx* ctx, size_t bytes);
 
-// queues the all-gather of the wire buffer + its copy to the host (dp_comm.cu); no-op without a communicator
+// dp_comm.cu; no-ops without a communicator.  prepare: before the publish kernel is queued
+// (selects the send slot, orders it behind the gather that last used it); enqueue: after it
+// (all-gather + copy to the host on the comm stream).
+int dp_comm_prepare(dp_ctx* ctx);
 int dp_comm_enqueue(dp_ctx* ctx);
 void dp_comm_release(dp_ctx* ctx);
 

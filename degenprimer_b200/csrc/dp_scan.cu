@@ -397,6 +397,8 @@ struct dp_sizes {
 
 static int publish_enqueue(dp_ctx* ctx, bool with_dg) {
   cudaStream_t st = ctx->stream;
+  int rc0 = dp_comm_prepare(ctx);
+  if (rc0) return rc0;
   dp_publish_args P;
   P.counters = ctx->d_counters;
   P.hits = (const uint64_t*)ctx->d_hits;

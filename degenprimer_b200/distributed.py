@@ -132,13 +132,14 @@ class HitExchange(object):
     def close(self):
         self.ctx.comm_destroy()
 
-    def collect(self):
-        """(raw wire records, sender rank of each) of the call that just returned, or None."""
-        return self.ctx.gathered()
+    def collect(self, age=0):
+        """(raw wire records, sender rank of each) of a call, or None.  age 0 = the call
+        that just returned, 1 = the one before it (its gather overlapped the last call)."""
+        return self.ctx.gathered(age)
 
-    def collect_hits(self):
+    def collect_hits(self, age=0):
         """Converted + sorted hits of every rank (record = sender rank), or None."""
-        return self.ctx.gathered_hits()
+        return self.ctx.gathered_hits(age)
 
 
 def hit_keys(hits):

@@ -297,23 +297,29 @@ int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes);
  * BioUtils/Tools/Multiprocessing.py:201-211).  One process per GPU: rank 0 calls
  * dp_comm_unique_id, the id is broadcast by the host side (torch.distributed),
  * every rank calls dp_comm_init (collective).  From then on every dp_scan /
- * dp_find of this ctx ends with ncclAllGather(wire slot) + a copy to pinned host
- * memory on the same stream — all ranks must make the same sequence of calls.
- * After the call returns, dp_comm_gathered() gives `world` slots of `slot_bytes`
- * (layout of dp_set_wire), slot r = rank r's hits of that call.  A slot holds
- * max_hits records; header[0] tells when a rank had more (then fall back to a
- * host-side gather).  NCCL is loaded with dlopen("libnccl.so.2"). */
+ * dp_find of this ctx is followed by ncclAllGather(wire slot) + a copy to pinned
+ * host memory — all ranks must make the same sequence of calls.  The exchange is
+ * double buffered and runs on its own high-priority stream behind an event, so the
+ * call itself returns as soon as this rank's own results are published; the
+ * gathered hits are fetched with `age`:
+ *   age 0  the call that just returned (waits for the slowest rank's gather),
+ *   age 1  the call before it: in a loop over many templates the gather of call
+ *          i overlaps call i+1 and costs nothing on the critical path.
+ * dp_comm_gathered() gives `world` slots of `slot_bytes` (layout of dp_set_wire),
+ * slot r = rank r's hits of that call.  A slot holds max_hits records; header[0]
+ * tells when a rank had more (then fall back to a host-side gather).
+ * NCCL is loaded with dlopen("libnccl.so.2"). */
 int dp_comm_unique_id(dp_ctx* ctx, char id[128]);
 int dp_comm_init(dp_ctx* ctx, const char id[128], int world, int rank, uint32_t max_hits);
 int dp_comm_destroy(dp_ctx* ctx);
-int dp_comm_gathered(dp_ctx* ctx, const void** host_ptr, uint64_t* slot_bytes, int* world);
-/* The gathered hits of the call that just returned, converted: one segment (one
+int dp_comm_gathered(dp_ctx* ctx, int age, const void** host_ptr, uint64_t* slot_bytes, int* world);
+/* The gathered hits of a call (age as above), converted: one segment (one
  * record) per rank, hit.record = sender rank, hit.pos in that rank's segment
  * coordinates (strand 1: on its reverse complement), sorted by (primer, strand,
  * record, pos).  header[5] / header[6] of a slot carry the sender's record length
  * and record count.  DP_ERR_UNSUPPORTED if a slot overflowed or a rank scanned a
  * multi-record template (use dp_comm_gathered then). */
-int dp_comm_hits(dp_ctx* ctx, dp_hit** hits, uint64_t* n_hits);
+int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits, uint64_t* n_hits);
 
 /* The template window under every hit, as the reference's strand strings show
  * it (fwd_seq[pos:pos+L] / rev_seq[pos:pos+L], DegenPrimer/SearchEngine.py:113):
