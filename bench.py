@@ -242,8 +242,8 @@ def run_ours(args):
 
     exch = None
     if world > 1:
-        # the hit gather rides on the same stream submission: publish kernel -> ncclAllGather
-        # of fixed slots over NVLink -> D2H, all queued by the library before the host waits
+        # the hit gather is the epilogue of the publish kernel: each rank stores its slot into
+        # every peer's receive buffer over NVLink (CUDA IPC peer memory), no collective launch
         from degenprimer_b200.distributed import HitExchange
         exch = HitExchange(ctx, max_hits=1024)
 
@@ -254,10 +254,11 @@ def run_ours(args):
         return ctx.find(t, query, cond=cond, algo=args.algo)
 
     def gathered(age, own):
-        # hits of every rank for a step (rank g's segment = record g of the genome).  The
-        # exchange is double buffered on its own stream: step i's gather overlaps step i+1,
-        # so inside the loop it is collected one step late (age 1) and the last one after
-        # the loop (age 0) — every gather completes inside the timed region.
+        # hits of every rank for a step (rank g's segment = record g of the genome).  Step
+        # i+1's publish kernel moves step i's slots to pinned host memory, so inside the loop
+        # step i-2 is collected while the GPU runs step i (age 2: its conversion and sort
+        # overlap the kernels), and the last two steps after the loop (ages 1 and 0) — every
+        # gather completes inside the timed region.
         allh = exch.collect_hits(age)
         return allh if allh is not None else sort_hits(all_gather_records(own))
 
@@ -282,14 +283,20 @@ def run_ours(args):
     t0 = time.perf_counter()
     ev0.record(kstream)
     n_gathered = 0
+    own = [None, None]                       # this rank's hits of the last two steps
     for i in range(args.steps):
-        hits, dimers, st, dst = step(args.warmup + i)
         if exch is not None:
-            if i > 0:
-                n_gathered += len(gathered(1, hits))
+            ctx.find_begin(copies[(args.warmup + i) % n_copies], query, cond, algo=args.algo)
+            if i >= 2:
+                n_gathered += len(gathered(2, own[0]))
+            hits, dimers, st, dst = ctx.find_end()
+            own = [own[1], hits]
             if i == args.steps - 1:
-                n_gathered += len(gathered(0, hits))
+                if i >= 1:
+                    n_gathered += len(gathered(1, own[0]))
+                n_gathered += len(gathered(0, own[1]))
         else:
+            hits, dimers, st, dst = step(args.warmup + i)
             n_gathered += len(hits)
         acc['ms_main'] += st['ms_main']
         acc['ms_scan'] += st['ms_scan']

@@ -132,8 +132,8 @@ def _declare(lib):
                                 C.c_void_p, P(dp_conditions)]),
         'dp_find_end': (i32, [vp, P(vp), P(u64), P(vp), P(u64), P(dp_scan_stats), P(dp_dg_stats)]),
         'dp_set_wire': (i32, [vp, C.c_void_p, u64]),
-        'dp_comm_unique_id': (i32, [vp, C.c_char_p]),
-        'dp_comm_init': (i32, [vp, C.c_char_p, i32, i32, u32]),
+        'dp_comm_export': (i32, [vp, i32, i32, u32, C.c_char_p]),
+        'dp_comm_attach': (i32, [vp, C.c_char_p]),
         'dp_comm_destroy': (i32, [vp]),
         'dp_comm_gathered': (i32, [vp, i32, P(vp), P(u64), P(i32)]),
         'dp_comm_hits': (i32, [vp, i32, P(vp), P(u64)]),
@@ -156,7 +156,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
-           'dp_set_wire dp_comm_unique_id dp_comm_init dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
+           'dp_set_wire dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
 
 
@@ -413,23 +413,29 @@ class Context(object):
         """Device buffer that receives {header, raw hits} of every call (multi-GPU gather)."""
         self._check(self.lib.dp_set_wire(self._h, C.c_void_p(device_ptr or 0), int(nbytes)))
 
-    # ---- multi-GPU exchange (NCCL inside the library) ------------------------------
-    def comm_unique_id(self):
+    # ---- multi-GPU exchange (peer-memory stores from the publish kernel) -----------
+    def comm_export(self, world, rank, max_hits=4096):
+        """Allocates this rank's receive buffers; returns their 128 bytes of IPC handles."""
         buf = C.create_string_buffer(128)
-        self._check(self.lib.dp_comm_unique_id(self._h, buf))
+        self._check(self.lib.dp_comm_export(self._h, int(world), int(rank), int(max_hits), buf))
+        self._gather_world, self._gather_max = int(world), int(max_hits)
         return buf.raw
 
-    def comm_init(self, unique_id, world, rank, max_hits=4096):
-        self._check(self.lib.dp_comm_init(self._h, unique_id, int(world), int(rank), int(max_hits)))
-        self._gather_world, self._gather_max = int(world), int(max_hits)
+    def comm_attach(self, all_handles):
+        """`all_handles`: the 128-byte blobs of comm_export of every rank, in rank order."""
+        blob = b''.join(all_handles)
+        if len(blob) != 128 * self._gather_world:
+            raise ValueError('expected %d handle blobs of 128 bytes' % self._gather_world)
+        self._check(self.lib.dp_comm_attach(self._h, blob))
 
     def comm_destroy(self):
         self._check(self.lib.dp_comm_destroy(self._h))
 
     def gathered_hits(self, age=0):
         """Hits of every rank for a call (one segment per rank: record = sender rank,
-        positions in that segment), sorted.  age 0 = the call that just returned
-        (waits for its gather), age 1 = the call before (already there in a loop).
+        positions in that segment), sorted.  age 0 = the newest call (waits for the
+        slowest rank), 1 = the call before (waits for this rank's stream), 2 = two calls
+        back (already on the host: collect it between find_begin and find_end).
         None if a slot overflowed or a rank holds a multi-record template."""
         hits, n = C.c_void_p(), C.c_uint64()
         rc = self.lib.dp_comm_hits(self._h, int(age), C.byref(hits), C.byref(n))

@@ -55,7 +55,7 @@ def build_native(force=False, verbose=False):
             sys.stderr.write(out)
         objs.append(obj)
     tmp = LIB + '.tmp'
-    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs + ['-ldl']
+    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode:
         raise RuntimeError('link failed:\n%s' % r.stdout.decode())

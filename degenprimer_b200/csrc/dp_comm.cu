@@ -1,187 +1,173 @@
-// Multi-GPU hit exchange: NCCL all-gather of the wire buffer, queued on the
-// context's stream right behind the publish kernel (one exchange step
-// at the end of the scan, KB-sized, latency bound).
+// Multi-GPU hit exchange over peer memory (one exchange step at the end
+// of the scan, KB-sized, latency bound).
 //
-// NCCL is bound at run time (dlopen of the libnccl.so.2 that torch ships and has
-// already loaded in a torchrun process), so the library itself has no link-time
-// dependency on it and single-GPU users never touch it.  Rank 0 makes the unique
-// id, the host side (degenprimer_b200/distributed.py) broadcasts it with
-// torch.distributed, every rank calls dp_comm_init.
+// Every rank owns two receive buffers (world slots each: 64-byte header + raw hits)
+// that its peers map through CUDA IPC.  The publish kernel of call c -- the last
+// kernel of the call anyway -- stores this rank's slot into receive buffer c&1 of
+// EVERY rank over NVLink and raises the slot's sequence word behind a system-scope
+// fence.  There is no separate collective launch: the gather is the epilogue of the
+// compute.  The same kernel first moves call c-1's slots (all ranks) from the local
+// receive buffer to pinned host memory, which is also the flow control: a rank
+// publishes call c only after it has seen every peer's call c-1, so peers are never
+// more than one call apart and a buffer is never overwritten before it was drained.
+//
+// The host side (degenprimer_b200/distributed.py) moves the IPC handles between the
+// ranks with torch.distributed; this file has no dependency on it or on NCCL.
 #include <algorithm>
-#include <dlfcn.h>
+#include <vector>
 #include <stdlib.h>
 #include <string.h>
 
 #include "dp_internal.cuh"
 
-typedef struct ncclComm* ncclComm_t;
-typedef struct { char internal[128]; } ncclUniqueId;
-typedef int ncclResult_t;
-enum { DP_NCCL_UINT8 = 1 };
-
-struct dp_nccl_api {
-  void* lib;
-  ncclResult_t (*GetUniqueId)(ncclUniqueId*);
-  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
-  ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t);
-  ncclResult_t (*CommDestroy)(ncclComm_t);
-  const char* (*GetErrorString)(ncclResult_t);
-};
-
-static dp_nccl_api* nccl_api(dp_ctx* ctx) {
-  static dp_nccl_api api;
-  static bool tried = false, ok = false;
-  if (!tried) {
-    tried = true;
-    const char* names[] = {"libnccl.so.2", "libnccl.so"};
-    for (const char* n : names) {
-      api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
-      if (api.lib) break;
-    }
-    if (api.lib) {
-      api.GetUniqueId = (ncclResult_t(*)(ncclUniqueId*))dlsym(api.lib, "ncclGetUniqueId");
-      api.CommInitRank = (ncclResult_t(*)(ncclComm_t*, int, ncclUniqueId, int))dlsym(api.lib, "ncclCommInitRank");
-      api.AllGather = (ncclResult_t(*)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t))dlsym(api.lib, "ncclAllGather");
-      api.CommDestroy = (ncclResult_t(*)(ncclComm_t))dlsym(api.lib, "ncclCommDestroy");
-      api.GetErrorString = (const char* (*)(ncclResult_t))dlsym(api.lib, "ncclGetErrorString");
-      ok = api.GetUniqueId && api.CommInitRank && api.AllGather && api.CommDestroy && api.GetErrorString;
-    }
-  }
-  if (!ok) {
-    dp_set_error(ctx, DP_ERR_STATE, "NCCL is not available: libnccl.so.2 could not be loaded (%s)",
-                 api.lib ? "symbols missing" : "dlopen failed; import torch first or set LD_LIBRARY_PATH");
-    return nullptr;
-  }
-  return &api;
-}
-
-#define DP_NCCL(ctx, api, call)                                                               \
-  do {                                                                                        \
-    ncclResult_t r__ = (call);                                                                \
-    if (r__ != 0)                                                                             \
-      return dp_set_error((ctx), DP_ERR_CUDA, "%s failed: %s", #call, (api)->GetErrorString(r__)); \
-  } while (0)
-
 void dp_comm_release(dp_ctx* ctx) {
-  if (!ctx) return;
-  if (ctx->comm_stream) cudaStreamSynchronize(ctx->comm_stream);
-  if (ctx->comm) {
-    dp_nccl_api* api = nccl_api(ctx);
-    if (api) api->CommDestroy((ncclComm_t)ctx->comm);
-    ctx->comm = nullptr;
+  if (!ctx->comm_world) return;
+  cudaStreamSynchronize(ctx->stream);
+  for (int b = 0; b < 2; ++b) {
+    for (int r = 0; r < ctx->comm_world; ++r) {
+      if (r != ctx->comm_rank && ctx->peer_mapped[b][r]) cudaIpcCloseMemHandle(ctx->peer_mapped[b][r]);
+      ctx->peer_mapped[b][r] = nullptr;
+    }
+    if (ctx->d_recv[b]) cudaFree(ctx->d_recv[b]);
+    if (ctx->d_peer[b]) cudaFree(ctx->d_peer[b]);
+    if (ctx->h_gather[b]) cudaFreeHost(ctx->h_gather[b]);
+    ctx->d_recv[b] = nullptr;
+    ctx->d_peer[b] = nullptr;
+    ctx->h_gather[b] = nullptr;
   }
-  for (int i = 0; i < 2; ++i) {
-    if (ctx->d_wire_recv[i]) { cudaFree(ctx->d_wire_recv[i]); ctx->d_wire_recv[i] = nullptr; }
-    if (ctx->h_wire_recv[i]) { cudaFreeHost(ctx->h_wire_recv[i]); ctx->h_wire_recv[i] = nullptr; }
-    if (ctx->wire_slot[i]) { cudaFree(ctx->wire_slot[i]); ctx->wire_slot[i] = nullptr; }
-    if (ctx->gather_done[i]) { cudaEventDestroy(ctx->gather_done[i]); ctx->gather_done[i] = nullptr; }
-  }
-  if (ctx->wire_ready) { cudaEventDestroy(ctx->wire_ready); ctx->wire_ready = nullptr; }
-  if (ctx->comm_stream) { cudaStreamDestroy(ctx->comm_stream); ctx->comm_stream = nullptr; }
-  if (ctx->wire_owned) { ctx->wire = nullptr; ctx->wire_bytes = 0; ctx->wire_owned = false; }
+  if (ctx->comm_err) cudaFreeHost(ctx->comm_err);
+  ctx->comm_err = nullptr;
   ctx->comm_world = ctx->comm_rank = 0;
+  ctx->comm_slot_bytes = 0;
   ctx->comm_seq = 0;
 }
 
-int dp_comm_prepare(dp_ctx* ctx) {
-  if (!ctx->comm) return DP_OK;
-  const int slot = (int)(ctx->comm_seq & 1);
-  ctx->wire = ctx->wire_slot[slot];
-  // the gather that used this slot two calls ago must have read it before it is rewritten
-  if (ctx->comm_seq >= 2) DP_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->gather_done[slot], 0));
-  return DP_OK;
+void dp_comm_fill(dp_ctx* ctx, dp_exchange_args* X) {
+  X->world = 0;
+  if (!ctx->comm_world || !ctx->d_peer[0]) return;
+  const uint64_t c = ctx->comm_seq;
+  X->world = ctx->comm_world;
+  X->rank = ctx->comm_rank;
+  X->seq = c;
+  X->slot_bytes = ctx->comm_slot_bytes;
+  X->slot_hits = (ctx->comm_slot_bytes - 64) / sizeof(dp_raw_hit);
+  X->peers = ctx->d_peer[c & 1];
+  X->recv_prev = ctx->d_recv[(c + 1) & 1];
+  X->h_prev = ctx->h_gather[(c + 1) & 1];
+  X->err = ctx->comm_err;
+  X->rec0_len = ctx->last_rec0_len;
+  X->n_records = ctx->last_n_records;
+  ctx->comm_plan[c & 3] = ctx->last_plan;
+  ctx->comm_seq = c + 1;
 }
 
-int dp_comm_enqueue(dp_ctx* ctx) {
-  if (!ctx->comm) return DP_OK;
-  dp_nccl_api* api = nccl_api(ctx);
-  if (!api) return DP_ERR_STATE;
-  const int slot = (int)(ctx->comm_seq & 1);
-  DP_CUDA(ctx, cudaEventRecord(ctx->wire_ready, ctx->stream));
-  DP_CUDA(ctx, cudaStreamWaitEvent(ctx->comm_stream, ctx->wire_ready, 0));
-  DP_NCCL(ctx, api, api->AllGather(ctx->wire_slot[slot], ctx->d_wire_recv[slot], ctx->wire_bytes, DP_NCCL_UINT8,
-                                   (ncclComm_t)ctx->comm, ctx->comm_stream));
-  DP_CUDA(ctx, cudaMemcpyAsync(ctx->h_wire_recv[slot], ctx->d_wire_recv[slot], (size_t)ctx->comm_world * ctx->wire_bytes,
-                               cudaMemcpyDeviceToHost, ctx->comm_stream));
-  DP_CUDA(ctx, cudaEventRecord(ctx->gather_done[slot], ctx->comm_stream));
-  ctx->comm_plan[slot] = ctx->last_plan;
-  ++ctx->comm_seq;
-  return DP_OK;
-}
-
-// slot of the call `age` calls ago (0 = the one that just returned); waits for its gather
-static int comm_slot(dp_ctx* ctx, int age, int* slot) {
-  if (!ctx->comm) return dp_set_error(ctx, DP_ERR_STATE, "no communicator: call dp_comm_init first");
-  if (age < 0 || age > 1 || ctx->comm_seq < (uint64_t)age + 1)
-    return dp_set_error(ctx, DP_ERR_ARG, "no gathered call of age %d (the exchange keeps the last two)", age);
-  *slot = (int)((ctx->comm_seq - 1 - (uint64_t)age) & 1);
-  DP_CUDA(ctx, cudaEventSynchronize(ctx->gather_done[*slot]));
+// Host buffer that holds the call made `age` calls ago.  With c = the last call queued:
+//   age 2  call c-2 was moved to the host by the publish kernel of call c-1, which has
+//          completed (calls do not overlap): nothing to wait for, call c may be in flight;
+//   age 1  call c-1 is moved by the publish kernel of call c: wait for the stream;
+//   age 0  call c is still in the device receive buffer: one small kernel waits for the
+//          slowest rank's slot and moves it.
+static int comm_collect(dp_ctx* ctx, int age, int* buf, uint64_t* call_out) {
+  if (!ctx->comm_world || !ctx->d_peer[0]) return dp_set_error(ctx, DP_ERR_STATE, "no exchange: call dp_comm_export and dp_comm_attach first");
+  if (age < 0 || age > 2 || ctx->comm_seq < (uint64_t)age + 1)
+    return dp_set_error(ctx, DP_ERR_ARG, "no gathered call of age %d (the exchange keeps the last three)", age);
+  const uint64_t call = ctx->comm_seq - 1 - (uint64_t)age;
+  const int b = (int)(call & 1);
+  if (age == 0) {
+    // the slots of the last call are still on the device (the next call would drain them)
+    dp_exchange_args X;
+    memset(&X, 0, sizeof X);
+    X.world = ctx->comm_world;
+    X.rank = ctx->comm_rank;
+    X.seq = call;
+    X.slot_bytes = ctx->comm_slot_bytes;
+    X.slot_hits = (ctx->comm_slot_bytes - 64) / sizeof(dp_raw_hit);
+    X.recv_prev = ctx->d_recv[b];
+    X.h_prev = ctx->h_gather[b];
+    X.err = ctx->comm_err;
+    dp_exchange_drain_launch(X, ctx->stream);
+    DP_CUDA(ctx, cudaGetLastError());
+  }
+  if (age < 2) DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (*(volatile unsigned long long*)ctx->comm_err)
+    return dp_set_error(ctx, DP_ERR_STATE, "exchange timed out waiting for a peer's call %llu: every rank must make the same calls",
+                        *(volatile unsigned long long*)ctx->comm_err - 1);
+  for (int r = 0; r < ctx->comm_world; ++r) {
+    const uint64_t* h = (const uint64_t*)(ctx->h_gather[b] + (size_t)r * ctx->comm_slot_bytes);
+    if (h[7] != call + 1)
+      return dp_set_error(ctx, DP_ERR_STATE, "exchange: slot of rank %d holds call %lld, expected %llu", r,
+                          (long long)h[7] - 1, (unsigned long long)call);
+  }
+  *buf = b;
+  *call_out = call;
   return DP_OK;
 }
 
 extern "C" {
 
-int dp_comm_unique_id(dp_ctx* ctx, char id[128]) {
-  if (!ctx || !id) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
-  dp_nccl_api* api = nccl_api(ctx);
-  if (!api) return DP_ERR_STATE;
-  ncclUniqueId u;
-  DP_NCCL(ctx, api, api->GetUniqueId(&u));
-  memcpy(id, u.internal, 128);
+int dp_comm_export(dp_ctx* ctx, int world, int rank, uint32_t max_hits, char handles[128]) {
+  if (!ctx || !handles) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (world < 1 || world > DP_MAX_RANKS || rank < 0 || rank >= world)
+    return dp_set_error(ctx, DP_ERR_ARG, "world %d / rank %d out of range (at most %d ranks)", world, rank, DP_MAX_RANKS);
+  if (sizeof(cudaIpcMemHandle_t) != 64) return dp_set_error(ctx, DP_ERR_STATE, "unexpected IPC handle size");
+  dp_comm_release(ctx);
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  const uint64_t slot = 64 + (uint64_t)std::max<uint32_t>(1, max_hits) * sizeof(dp_raw_hit);
+  ctx->comm_slot_bytes = slot;
+  ctx->comm_world = world;
+  ctx->comm_rank = rank;
+  ctx->comm_seq = 0;
+  for (int b = 0; b < 2; ++b) {
+    DP_CUDA(ctx, cudaMalloc(&ctx->d_recv[b], slot * world));
+    DP_CUDA(ctx, cudaMemset(ctx->d_recv[b], 0, slot * world));
+    DP_CUDA(ctx, cudaHostAlloc(&ctx->h_gather[b], slot * world, cudaHostAllocDefault));
+    memset(ctx->h_gather[b], 0, slot * world);
+    cudaIpcMemHandle_t h;
+    DP_CUDA(ctx, cudaIpcGetMemHandle(&h, ctx->d_recv[b]));
+    memcpy(handles + 64 * b, &h, 64);
+  }
+  DP_CUDA(ctx, cudaHostAlloc(&ctx->comm_err, sizeof(unsigned long long), cudaHostAllocDefault));
+  *ctx->comm_err = 0ull;
+  DP_CUDA(ctx, cudaDeviceSynchronize());
   return DP_OK;
 }
 
-int dp_comm_init(dp_ctx* ctx, const char id[128], int world, int rank, uint32_t max_hits) {
-  if (!ctx || !id) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
-  if (world < 1 || rank < 0 || rank >= world || max_hits == 0)
-    return dp_set_error(ctx, DP_ERR_ARG, "bad world/rank/max_hits");
-  dp_nccl_api* api = nccl_api(ctx);
-  if (!api) return DP_ERR_STATE;
+int dp_comm_attach(dp_ctx* ctx, const char* all_handles) {
+  if (!ctx || !all_handles) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (!ctx->comm_world || !ctx->d_recv[0]) return dp_set_error(ctx, DP_ERR_STATE, "dp_comm_export first");
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
-  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  dp_comm_release(ctx);
-  ncclUniqueId u;
-  memcpy(u.internal, id, 128);
-  ncclComm_t comm = nullptr;
-  DP_NCCL(ctx, api, api->CommInitRank(&comm, world, u, rank));
-  ctx->comm = comm;
-  ctx->comm_world = world;
-  ctx->comm_rank = rank;
-  const uint64_t slot = 64 + (uint64_t)max_hits * sizeof(dp_raw_hit);
-  int lo_prio = 0, hi_prio = 0;
-  DP_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
-  DP_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->comm_stream, cudaStreamNonBlocking, hi_prio));
-  DP_CUDA(ctx, cudaEventCreateWithFlags(&ctx->wire_ready, cudaEventDisableTiming));
-  for (int i = 0; i < 2; ++i) {
-    DP_CUDA(ctx, cudaEventCreateWithFlags(&ctx->gather_done[i], cudaEventDisableTiming));
-    DP_CUDA(ctx, cudaMalloc((void**)&ctx->wire_slot[i], slot));
-    DP_CUDA(ctx, cudaMemset(ctx->wire_slot[i], 0, slot));
-    DP_CUDA(ctx, cudaMalloc((void**)&ctx->d_wire_recv[i], (size_t)world * slot));
-    DP_CUDA(ctx, cudaMallocHost((void**)&ctx->h_wire_recv[i], (size_t)world * slot));
-    memset(ctx->h_wire_recv[i], 0, (size_t)world * slot);
+  for (int b = 0; b < 2; ++b) {
+    char* table[DP_MAX_RANKS];
+    for (int r = 0; r < ctx->comm_world; ++r) {
+      if (r == ctx->comm_rank) {
+        ctx->peer_mapped[b][r] = ctx->d_recv[b];
+      } else {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, all_handles + (size_t)r * 128 + 64 * b, 64);
+        DP_CUDA(ctx, cudaIpcOpenMemHandle(&ctx->peer_mapped[b][r], h, cudaIpcMemLazyEnablePeerAccess));
+      }
+      table[r] = (char*)ctx->peer_mapped[b][r];
+    }
+    DP_CUDA(ctx, cudaMalloc(&ctx->d_peer[b], sizeof(char*) * DP_MAX_RANKS));
+    DP_CUDA(ctx, cudaMemcpy(ctx->d_peer[b], table, sizeof(char*) * ctx->comm_world, cudaMemcpyHostToDevice));
   }
-  ctx->wire = ctx->wire_slot[0];
-  ctx->wire_owned = true;
-  ctx->wire_bytes = slot;
-  ctx->comm_seq = 0;
   return DP_OK;
 }
 
 int dp_comm_destroy(dp_ctx* ctx) {
   if (!ctx) return DP_ERR_ARG;
-  cudaSetDevice(ctx->device);
-  cudaStreamSynchronize(ctx->stream);
   dp_comm_release(ctx);
   return DP_OK;
 }
 
 int dp_comm_gathered(dp_ctx* ctx, int age, const void** host_ptr, uint64_t* slot_bytes, int* world) {
   if (!ctx || !host_ptr || !slot_bytes || !world) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
-  int slot = 0;
-  int rc = comm_slot(ctx, age, &slot);
+  int b = 0;
+  uint64_t call = 0;
+  int rc = comm_collect(ctx, age, &b, &call);
   if (rc) return rc;
-  *host_ptr = ctx->h_wire_recv[slot];
-  *slot_bytes = ctx->wire_bytes;
+  *host_ptr = ctx->h_gather[b];
+  *slot_bytes = ctx->comm_slot_bytes;
   *world = ctx->comm_world;
   return DP_OK;
 }
@@ -191,11 +177,12 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
   *hits_out = nullptr;
   *n_out = 0;
   int s = 0;
-  int rc = comm_slot(ctx, age, &s);
+  uint64_t call = 0;
+  int rc = comm_collect(ctx, age, &s, &call);
   if (rc) return rc;
-  const char* recv = ctx->h_wire_recv[s];
-  const dp_dg_plan& plan = ctx->comm_plan[s];
-  const uint64_t slot = ctx->wire_bytes;
+  const char* recv = ctx->h_gather[s];
+  const dp_dg_plan& plan = ctx->comm_plan[call & 3];
+  const uint64_t slot = ctx->comm_slot_bytes;
   const uint64_t cap = (slot - 64) / sizeof(dp_raw_hit);
   uint64_t total = 0;
   for (int r = 0; r < ctx->comm_world; ++r) {
@@ -209,29 +196,46 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
   }
   dp_hit* out = (dp_hit*)dp_result_alloc(std::max<uint64_t>(1, total) * sizeof(dp_hit));
   if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu hits", (unsigned long long)total);
-  uint64_t w = 0;
-  for (int r = 0; r < ctx->comm_world; ++r) {
+  // output order (primer, strand, record, pos): patterns are numbered in (primer, strand)
+  // order and record = sender rank, so a counting sort over (pattern, rank) buckets leaves
+  // only the positions inside a bucket to sort
+  const int W = ctx->comm_world;
+  static thread_local std::vector<uint64_t> bucket;
+  bucket.assign((size_t)DP_MAX_PATTERNS * W + 1, 0);
+  for (int r = 0; r < W; ++r) {
+    const char* base = recv + (size_t)r * slot;
+    const uint64_t n = (uint32_t)((const uint64_t*)base)[0];
+    const dp_raw_hit* raw = (const dp_raw_hit*)(base + 64);
+    for (uint64_t i = 0; i < n; ++i) {
+      if (raw[i].pattern >= DP_MAX_PATTERNS) return dp_result_free(out), dp_set_error(ctx, DP_ERR_STATE, "exchange: corrupt slot of rank %d", r);
+      ++bucket[(size_t)raw[i].pattern * W + r + 1];
+    }
+  }
+  for (size_t i = 1; i < bucket.size(); ++i) bucket[i] += bucket[i - 1];
+  for (int r = 0; r < W; ++r) {
     const char* base = recv + (size_t)r * slot;
     const uint64_t* h = (const uint64_t*)base;
     const uint64_t n = (uint32_t)h[0], rec_len = h[5];
     const dp_raw_hit* raw = (const dp_raw_hit*)(base + 64);
-    for (uint64_t i = 0; i < n; ++i, ++w) {
+    for (uint64_t i = 0; i < n; ++i) {
       const uint32_t pat = raw[i].pattern;
       const uint32_t L = plan.pat_len[pat];
       const uint32_t strand = plan.pat_strand[pat];
-      out[w].pos = strand ? rec_len - L - raw[i].g : raw[i].g;     // record 0 starts at padded position 0
-      out[w].record = (uint32_t)r;
-      out[w].primer = plan.pat_primer[pat];
-      out[w].strand = (uint8_t)strand;
-      out[w].score3 = (uint8_t)raw[i].score3;
+      dp_hit& o = out[bucket[(size_t)pat * W + r]++];
+      o.pos = strand ? rec_len - L - raw[i].g : raw[i].g;     // record 0 starts at padded position 0
+      o.record = (uint32_t)r;
+      o.primer = plan.pat_primer[pat];
+      o.strand = (uint8_t)strand;
+      o.score3 = (uint8_t)raw[i].score3;
     }
   }
-  std::sort(out, out + total, [](const dp_hit& a, const dp_hit& b) {
-    if (a.primer != b.primer) return a.primer < b.primer;
-    if (a.strand != b.strand) return a.strand < b.strand;
-    if (a.record != b.record) return a.record < b.record;
-    return a.pos < b.pos;
-  });
+  // bucket[j] now is the END of bucket j
+  uint64_t lo = 0;
+  for (size_t j = 0; j + 1 < bucket.size(); ++j) {
+    const uint64_t hi = bucket[j];
+    if (hi - lo > 1) std::sort(out + lo, out + hi, [](const dp_hit& a, const dp_hit& b) { return a.pos < b.pos; });
+    lo = hi;
+  }
   *hits_out = out;
   *n_out = total;
   return DP_OK;

@@ -185,15 +185,16 @@ dp_ctx* dp_create(int device_ordinal) {
   ctx->pending_free = nullptr;
   ctx->wire = nullptr;
   ctx->wire_bytes = 0;
-  ctx->comm = nullptr;
   ctx->comm_world = ctx->comm_rank = 0;
-  ctx->comm_stream = nullptr;
-  ctx->wire_ready = nullptr;
   ctx->comm_seq = 0;
   for (int i = 0; i < 2; ++i) {
-    ctx->gather_done[i] = nullptr;
-    ctx->wire_slot[i] = ctx->d_wire_recv[i] = ctx->h_wire_recv[i] = nullptr;
+    ctx->d_recv[i] = nullptr;
+    ctx->d_peer[i] = nullptr;
+    ctx->h_gather[i] = nullptr;
+    for (int r = 0; r < DP_MAX_RANKS; ++r) ctx->peer_mapped[i][r] = nullptr;
   }
+  ctx->comm_err = nullptr;
+  ctx->comm_slot_bytes = 0;
   ctx->wire_owned = false;
   ctx->stream = ctx->copy_stream = nullptr;
   for (int i = 0; i < 2; ++i) {

@@ -71,6 +71,7 @@ struct dp_raw_dimer {
 // What the duplex kernel needs to know about the patterns/primers of a call
 // (kernel parameter, lives in the constant bank).
 #define DP_MAX_PATTERNS (2 * DP_MAX_PRIMERS)
+#define DP_MAX_RANKS 16
 struct dp_dg_plan {
   uint8_t pat_len[DP_MAX_PATTERNS];
   uint8_t pat_strand[DP_MAX_PATTERNS];
@@ -126,20 +127,18 @@ struct dp_ctx {
   // optional device mirror of {counters, raw hits} written by the publish kernel
   void* wire;
   uint64_t wire_bytes;
-  // multi-GPU hit exchange (dp_comm.cu): NCCL communicator + receive buffers
-  void* comm;                  // ncclComm_t
-  int comm_world, comm_rank;
-  // the exchange is double buffered and runs on its own stream, so that the gather of
-  // call i overlaps call i+1 and nobody waits for the slowest rank inside a call
-  cudaStream_t comm_stream;
-  cudaEvent_t wire_ready;      // main stream: the publish kernel has written the wire slot
-  cudaEvent_t gather_done[2];  // comm stream: slot's gather has landed in h_wire_recv[slot]
-  uint64_t comm_seq;           // calls gathered so far; call i uses slot i & 1
-  char* wire_slot[2];          // send slots (device)
-  char* d_wire_recv[2];        // world x wire_bytes on the device
-  char* h_wire_recv[2];        // the same, pinned host memory
-  dp_dg_plan comm_plan[2];     // (length, strand, primer) of the patterns of the call in each slot
-  bool wire_owned;             // `wire` was allocated by dp_comm_init
+  // multi-GPU hit exchange (dp_comm.cu): the publish kernel stores this rank's wire slot
+  // straight into every peer's receive buffer over NVLink (CUDA IPC peer memory)
+  int comm_world, comm_rank;   // world == 0: no exchange attached
+  uint64_t comm_seq;           // calls exchanged so far; call c uses receive buffer c & 1
+  char* d_recv[2];             // this rank's receive buffers: world x wire_bytes each (cudaMalloc, IPC exported)
+  char** d_peer[2];            // device table: d_peer[b][r] = rank r's receive buffer b as seen from this GPU
+  void* peer_mapped[2][DP_MAX_RANKS];   // host copy of the table (what cudaIpcOpenMemHandle returned)
+  char* h_gather[2];           // pinned host copies of the receive buffers, written by the publish kernel
+  unsigned long long* comm_err;         // pinned host flag (device-visible): a wait for a peer timed out
+  uint64_t comm_slot_bytes;             // bytes per rank in a receive buffer: 64-byte header + raw hits
+  dp_dg_plan comm_plan[4];     // (length, strand, primer) of the patterns of the last calls (call & 3)
+  bool wire_owned;
   dp_dg_plan last_plan;        // (length, strand, primer) of the patterns of the last scan
   uint64_t last_rec0_len;      // its template: length of record 0 and record count
   uint64_t last_n_records;
@@ -222,12 +221,21 @@ int dp_ws_dimers(dp_ctx* ctx, uint64_t cap);
 int dp_ws_codes(dp_ctx* ctx, uint64_t cap);
 int dp_ws_pinned(dp_ctx* ctx, size_t bytes);
 
-// dp_comm.cu; no-ops without a communicator.  prepare: before the publish kernel is queued
-// (selects the send slot, orders it behind the gather that last used it); enqueue: after it
-// (all-gather + copy to the host on the comm stream).
-int dp_comm_prepare(dp_ctx* ctx);
-int dp_comm_enqueue(dp_ctx* ctx);
+// dp_comm.cu: what the publish kernel needs for the exchange (world == 0: none)
+struct dp_exchange_args {
+  int world, rank;
+  uint64_t seq;                // this call's sequence number c
+  uint64_t slot_bytes;         // bytes per rank in a receive buffer
+  uint64_t slot_hits;          // raw hit records a slot holds
+  char* const* peers;          // peers[r] = rank r's receive buffer (c & 1)
+  const char* recv_prev;       // this rank's receive buffer ((c-1) & 1): call c-1 of every rank
+  char* h_prev;                // pinned host copy of it
+  unsigned long long* err;
+  uint64_t rec0_len, n_records;
+};
+void dp_comm_fill(dp_ctx* ctx, dp_exchange_args* X);     // for the call being queued; advances the sequence
 void dp_comm_release(dp_ctx* ctx);
+void dp_exchange_drain_launch(const dp_exchange_args& X, cudaStream_t st);   // dp_scan.cu
 
 // duplex stage on the hits that sit in ctx->d_hits (dp_dg.cu).  n_pairs_hint = 0:
 // the pair count is only known on the device (fused dp_find).

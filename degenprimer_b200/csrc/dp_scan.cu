@@ -119,13 +119,86 @@ struct dp_publish_args {
   uint64_t* wire;              // optional device mirror {counters[8], raw hits...} for the multi-GPU gather
   uint64_t wire_hits;          // raw hit records the mirror can hold
   uint64_t rec0_len, n_records;   // sender's template, for receivers: header[5], header[6]
+  dp_exchange_args X;          // multi-GPU exchange over peer memory (world == 0: none)
 };
+
+// Exchange, flow control (call c >= 1): every rank's slot of call c-1 must have landed in
+// this rank's receive buffer (c-1)&1 -- header word 7 holds c once the slot is complete.
+// Peers run at most one call apart, so the poll normally succeeds at once; it gives up
+// after ~2 s and raises the error flag.  Returns false on a timeout (uniform over the block).
+__device__ bool dp_exchange_wait(const dp_exchange_args& X, uint64_t call) {
+  __shared__ int ok;
+  const uint64_t want = call + 1;
+  if (threadIdx.x == 0) ok = 1;
+  __syncthreads();
+  if ((int)threadIdx.x < X.world) {
+    const volatile uint64_t* flag = (const volatile uint64_t*)(X.recv_prev + threadIdx.x * X.slot_bytes) + 7;
+    unsigned long long t0 = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (*flag != want) {
+      __nanosleep(256);
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 2000000000ull) { ok = 0; break; }
+    }
+    __threadfence();               // the slot's words are read after its flag
+  }
+  __syncthreads();
+  if (!ok && threadIdx.x == 0) *X.err = want;
+  return ok != 0;
+}
+
+// the slots of a call that has landed: local receive buffer -> pinned host memory
+__device__ void dp_exchange_to_host(const dp_exchange_args& X) {
+  for (int r = 0; r < X.world; ++r) {
+    const volatile uint64_t* src = (const volatile uint64_t*)(X.recv_prev + r * X.slot_bytes);
+    uint64_t* dst = (uint64_t*)(X.h_prev + r * X.slot_bytes);
+    const uint64_t n = min((uint64_t)(uint32_t)src[DP_C_HITS], X.slot_hits);
+    for (uint64_t i = threadIdx.x; i < 8 + 3 * n; i += blockDim.x) dst[i] = src[i];
+  }
+}
+
+// standalone drain: brings the slots of the LAST call to the host (dp_comm_hits with age 0)
+__global__ void __launch_bounds__(1024)
+dp_exchange_drain_kernel(const __grid_constant__ dp_exchange_args X) {
+  if (dp_exchange_wait(X, X.seq)) dp_exchange_to_host(X);
+}
+
+void dp_exchange_drain_launch(const dp_exchange_args& X, cudaStream_t st) {
+  dp_exchange_drain_kernel<<<1, 1024, 0, st>>>(X);
+}
 
 __global__ void __launch_bounds__(1024)
 dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
   __shared__ unsigned long long c[8];
   if (threadIdx.x < 8) c[threadIdx.x] = P.counters[threadIdx.x];
   __syncthreads();
+  // multi-GPU exchange first: its stores travel over NVLink while the host copies below
+  // go out over PCIe, and the one system-scope fence then only waits for NVLink
+  bool landed = false;
+  if (P.X.world) {
+    // flow control: last call's slots of all ranks are here.  That also proves that every
+    // peer has consumed the buffer this call is about to overwrite (a peer moves call c-2
+    // to its host in the kernel that publishes call c-1).
+    landed = P.X.seq ? dp_exchange_wait(P.X, P.X.seq - 1) : false;
+    if (landed || !P.X.seq) {
+      // this rank's slot of call c goes into every rank's receive buffer c&1; header
+      // word 7 (= c+1) is stored last, behind the fence
+      const uint64_t n_wire = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), P.X.slot_hits);
+      for (int r = 0; r < P.X.world; ++r) {
+        uint64_t* dst = (uint64_t*)(P.X.peers[r] + (uint64_t)P.X.rank * P.X.slot_bytes);
+        for (uint64_t i = threadIdx.x; i < n_wire * 3; i += blockDim.x) dst[8 + i] = P.hits[i];
+        if (threadIdx.x < 7)
+          dst[threadIdx.x] = threadIdx.x == 5 ? P.X.rec0_len : threadIdx.x == 6 ? P.X.n_records : c[threadIdx.x];
+      }
+      __threadfence_system();
+      __syncthreads();
+      if ((int)threadIdx.x < P.X.world) {
+        volatile uint64_t* flag = (volatile uint64_t*)(P.X.peers[threadIdx.x] + (uint64_t)P.X.rank * P.X.slot_bytes) + 7;
+        *flag = P.X.seq + 1;
+      }
+    }
+  }
   const uint64_t n_hits = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), (uint64_t)P.spec_hits);
   for (uint64_t i = threadIdx.x; i < n_hits * 3; i += blockDim.x) P.h_hits[i] = P.hits[i];
   if (P.with_dg) {
@@ -140,6 +213,7 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
     if (threadIdx.x < 8)
       P.wire[threadIdx.x] = threadIdx.x == 5 ? P.rec0_len : threadIdx.x == 6 ? P.n_records : c[threadIdx.x];
   }
+  if (landed) dp_exchange_to_host(P.X);      // last call's slots of all ranks -> pinned host memory
   if (threadIdx.x < 8) {
     P.h_counters[threadIdx.x] = c[threadIdx.x];
     P.counters[threadIdx.x] = 0ull;
@@ -395,11 +469,11 @@ struct dp_sizes {
   bool saturated;
 };
 
-static int publish_enqueue(dp_ctx* ctx, bool with_dg) {
+static int publish_enqueue(dp_ctx* ctx, bool with_dg, bool exchange = false) {
   cudaStream_t st = ctx->stream;
-  int rc0 = dp_comm_prepare(ctx);
-  if (rc0) return rc0;
   dp_publish_args P;
+  P.X.world = 0;
+  if (exchange) dp_comm_fill(ctx, &P.X);
   P.counters = ctx->d_counters;
   P.hits = (const uint64_t*)ctx->d_hits;
   P.dir = ctx->d_dir;
@@ -721,9 +795,9 @@ static int pipeline_enqueue(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, c
     if (rc) return rc;
   }
   DP_CUDA(ctx, cudaEventRecord(ctx->ev4, ctx->stream));
-  rc = publish_enqueue(ctx, dg != nullptr);
-  if (rc) return rc;
-  return dp_comm_enqueue(ctx);        // multi-GPU: all-gather of the wire mirror, same stream
+  // multi-GPU: the first attempt of a call carries the exchange (a re-run after an overflow
+  // must not: every rank exchanges exactly once per call)
+  return publish_enqueue(ctx, dg != nullptr, !P.overflowed);
 }
 
 // waits for the queued attempt; grows buffers and repeats while something overflowed
@@ -925,7 +999,6 @@ extern "C" int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes) {
   if (device_ptr && bytes < 64 + sizeof(dp_raw_hit))
     return dp_set_error(ctx, DP_ERR_ARG, "wire buffer must hold the 64-byte header and at least one 24-byte record");
   if (((uintptr_t)device_ptr & 7u) != 0) return dp_set_error(ctx, DP_ERR_ARG, "wire buffer must be 8-byte aligned");
-  if (ctx->comm) return dp_set_error(ctx, DP_ERR_STATE, "the wire buffer is owned by the communicator (dp_comm_init)");
   ctx->wire = device_ptr;
   ctx->wire_bytes = device_ptr ? bytes : 0;
   return DP_OK;

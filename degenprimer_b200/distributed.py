@@ -110,31 +110,37 @@ def wire_to_hits(raw, primer_lens, rec_starts, rec_lens, rec_index=None):
 
 
 class HitExchange(object):
-    """All-gather of the hits of every fused call, inside the call's own stream submission.
+    """All-gather of the hits of every fused call, done by the call's own last kernel.
 
-    The library's publish kernel mirrors {header, raw hits} into a device slot; with a
-    communicator attached (dp_comm_init) every dp_find / dp_scan of the context ends
-    with ncclAllGather over NVLink + one copy to pinned host memory on the same
-    stream, so the exchange costs no extra host round trip.  torch.distributed is
-    only used to hand rank 0's NCCL unique id to the other ranks.  If any rank has
-    more hits than a slot holds, `collect` returns None and the caller falls back
-    to all_gather_records."""
+    Every rank owns two receive buffers that its peers map through CUDA IPC; the
+    library's publish kernel stores {header, raw hits} of a call straight into the
+    receive buffer of every rank over NVLink (no collective launch, no extra host
+    round trip) and moves the previous call's slots to pinned host memory.
+    torch.distributed only carries the IPC handles at set-up and the barrier at
+    tear-down.  If any rank has more hits than a slot holds, `collect` returns None
+    and the caller falls back to all_gather_records."""
 
     def __init__(self, ctx, max_hits=1024, group=None):
         import torch.distributed as dist
         self.ctx = ctx
+        self.group = group
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
-        box = [ctx.comm_unique_id() if self.rank == 0 else None]
-        dist.broadcast_object_list(box, src=0, group=group)
-        ctx.comm_init(box[0], self.world, self.rank, max_hits)
+        mine = ctx.comm_export(self.world, self.rank, max_hits)
+        blobs = [None] * self.world
+        dist.all_gather_object(blobs, mine, group=group)
+        ctx.comm_attach(blobs)
+        dist.barrier(group=group)        # nobody stores into a buffer that is not mapped yet
 
     def close(self):
+        import torch.distributed as dist
+        self.ctx.synchronize()
+        dist.barrier(group=self.group)   # peers may still be storing into this rank's buffers
         self.ctx.comm_destroy()
 
     def collect(self, age=0):
         """(raw wire records, sender rank of each) of a call, or None.  age 0 = the call
-        that just returned, 1 = the one before it (its gather overlapped the last call)."""
+        that just returned, 1 = the one before it (already on the host, costs nothing)."""
         return self.ctx.gathered(age)
 
     def collect_hits(self, age=0):

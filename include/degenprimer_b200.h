@@ -292,25 +292,34 @@ typedef struct dp_wire_hit {
 } dp_wire_hit;
 int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes);
 
-/* NCCL exchange of the wire buffer over NVLink (the reference's
- * counterpart is the pickling of slice results through multiprocessing Queues,
- * BioUtils/Tools/Multiprocessing.py:201-211).  One process per GPU: rank 0 calls
- * dp_comm_unique_id, the id is broadcast by the host side (torch.distributed),
- * every rank calls dp_comm_init (collective).  From then on every dp_scan /
- * dp_find of this ctx is followed by ncclAllGather(wire slot) + a copy to pinned
- * host memory — all ranks must make the same sequence of calls.  The exchange is
- * double buffered and runs on its own high-priority stream behind an event, so the
- * call itself returns as soon as this rank's own results are published; the
- * gathered hits are fetched with `age`:
- *   age 0  the call that just returned (waits for the slowest rank's gather),
- *   age 1  the call before it: in a loop over many templates the gather of call
- *          i overlaps call i+1 and costs nothing on the critical path.
- * dp_comm_gathered() gives `world` slots of `slot_bytes` (layout of dp_set_wire),
- * slot r = rank r's hits of that call.  A slot holds max_hits records; header[0]
- * tells when a rank had more (then fall back to a host-side gather).
- * NCCL is loaded with dlopen("libnccl.so.2"). */
-int dp_comm_unique_id(dp_ctx* ctx, char id[128]);
-int dp_comm_init(dp_ctx* ctx, const char id[128], int world, int rank, uint32_t max_hits);
+/* Hit exchange between the GPUs of one node over NVLink peer memory (SURVEY §8e;
+ * the reference's counterpart is the pickling of slice results through
+ * multiprocessing Queues, BioUtils/Tools/Multiprocessing.py:201-211).  One
+ * process per GPU.  Every rank calls dp_comm_export (allocates its two receive
+ * buffers, world slots of 64 + max_hits*24 bytes each, and returns their two
+ * 64-byte CUDA IPC handles); the host side moves the handles between the ranks
+ * (torch.distributed all_gather in degenprimer_b200/distributed.py) and every
+ * rank calls dp_comm_attach with world*128 bytes, rank-major.  From then on the
+ * publish kernel of every dp_find / dp_find_begin of this ctx -- the last kernel
+ * of the call -- stores this rank's slot (layout of dp_set_wire) into the
+ * receive buffer of every rank and raises its sequence word: the gather is the
+ * epilogue of the compute, there is no separate collective launch.  All ranks
+ * must make the same sequence of calls; ranks run at most one call apart (a call
+ * first waits, with a 2 s timeout, until every peer's previous call has landed).
+ * The gathered hits are fetched with `age`:
+ *   age 0  the call that just returned (one small kernel waits for the slowest
+ *          rank's slot),
+ *   age 1  the call before it: in pinned host memory once the last call's
+ *          kernels have finished (waits for the stream),
+ *   age 2  two calls back: in pinned host memory already, nothing is waited for
+ *          -- valid between dp_find_begin and dp_find_end of the newest call, so
+ *          the conversion overlaps the kernels of the call in flight.
+ * dp_comm_gathered() gives `world` slots of `slot_bytes`, slot r = rank r's hits
+ * of that call.  A slot holds max_hits records; header[0] tells when a rank had
+ * more (then fall back to a host-side gather).  dp_comm_destroy only after every
+ * rank has collected its last call (barrier on the host side). */
+int dp_comm_export(dp_ctx* ctx, int world, int rank, uint32_t max_hits, char handles[128]);
+int dp_comm_attach(dp_ctx* ctx, const char* all_handles);
 int dp_comm_destroy(dp_ctx* ctx);
 int dp_comm_gathered(dp_ctx* ctx, int age, const void** host_ptr, uint64_t* slot_bytes, int* world);
 /* The gathered hits of a call (age as above), converted: one segment (one

@@ -40,6 +40,16 @@ def _worker(rank, world, port, text, k, out_dir):
     ex = D.HitExchange(ctx, max_hits=512)
     hits, dimers, local, st, dst = sh.find(q, tdf.conditions(), exchange=ex)
     np.save(os.path.join(out_dir, 'fast%d.npy' % rank), hits)
+    # the exchange keeps three calls
+    for _ in range(3):
+        ctx.find(sh.template, q, cond=tdf.conditions())
+    older, newest = ex.collect_hits(1), ex.collect_hits(0)
+    ctx.find_begin(sh.template, q, tdf.conditions())
+    oldest = ex.collect_hits(2)          # on the host already: collected while the new call runs
+    ctx.find_end()
+    same = older is not None and newest is not None and np.array_equal(older, newest) and len(older) > 0
+    same = same and oldest is not None and np.array_equal(oldest, newest)
+    np.save(os.path.join(out_dir, 'ages%d.npy' % rank), np.array([int(same)]))
     ex.close()
     small = D.HitExchange(ctx, max_hits=1)               # forces the fallback gather
     hits2, _, _, _, _ = sh.find(q, tdf.conditions(), exchange=small)
@@ -70,6 +80,7 @@ def test_two_gpu_sharded_find(tmp_path, ctx):
     mp.spawn(_worker, args=(2, _free_port(), text, k, str(tmp_path)), nprocs=2, join=True)
     n_local = 0
     for r in range(2):
+        assert np.load(os.path.join(str(tmp_path), 'ages%d.npy' % r))[0] == 1
         for kind in ('fast', 'slow'):
             got = np.load(os.path.join(str(tmp_path), '%s%d.npy' % (kind, r)))
             assert np.array_equal(got['pos'], want['pos']) and np.array_equal(got['strand'], want['strand'])
