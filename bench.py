@@ -9,7 +9,7 @@ N = 1  : BASELINE.json configs[1] — TP53 pair vs a synthetic 83,257,441 bp
          chr17-sized template, k = 1 (`config2_tp53_chr17`).
 N > 1  : weak scaling — rank g holds segment g (83 Mbp + (L-1) halo) of an
          N x 83 Mbp genome, scans it alone, and hit records are all-gathered
-         over NCCL every step (no collective in the scan itself).
+         over NVLink peer memory every step (no collective in the scan itself).
 
 `python bench.py --gpus N --steps K --warmup W [--impl reference]`
 prints ONE JSON line on rank 0.
@@ -199,9 +199,32 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def bind_near_gpu(local):
+    """Pins this rank to the host cores NVML lists as local to its GPU, so that the pinned
+    staging memory of the e2e leg is first touched on the GPU's own NUMA node (8 ranks copy
+    83 MB per step each)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        visible = os.environ.get('CUDA_VISIBLE_DEVICES')
+        index = int(visible.split(',')[local]) if visible else local
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        n_words = (os.cpu_count() + 63) // 64
+        masks = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = {64 * w + b for w, m in enumerate(masks) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return 0
+
+
 # ---- GPU arm -----------------------------------------------------------------------------------
 def run_ours(args):
     rank, world, local = dist_env()
+    if world > 1:
+        bind_near_gpu(local)
     if world != args.gpus and world > 1:
         raise SystemExit('WORLD_SIZE=%d but --gpus %d' % (world, args.gpus))
     from degenprimer_b200.synthetic import make_workload

@@ -262,8 +262,8 @@ int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
             dp_scan_stats* scan_stats, dp_dg_stats* dg_stats);
 
 /* dp_find in two halves, so that a caller can queue its own work on dp_stream()
- * behind the kernels and before the host waits (the multi-GPU hit gather: an NCCL
- * all-gather of the wire buffer below).  dp_find == begin + end. */
+ * behind the kernels, or do host work (collecting the multi-GPU hit exchange of
+ * an earlier call, dp_comm_hits with age 2) before the host waits.  dp_find == begin + end. */
 int dp_find_begin(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
                   const char* const* masters, const int32_t* max_mismatches,
                   uint64_t seg_begin, uint64_t seg_end, int strand_mask, int algo,
