@@ -20,7 +20,7 @@ DP_ERR_IO, DP_ERR_NOMEM, DP_ERR_ABORTED, DP_ERR_STATE = -6, -7, -8, -9
 DP_MAX_PRIMER_LEN = 64
 DP_MAX_PRIMERS = 64
 DP_STRAND_FWD, DP_STRAND_REV, DP_STRAND_BOTH = 1, 2, 3
-DP_ALGO_AUTO, DP_ALGO_POPC, DP_ALGO_BITSLICE = 0, 1, 2
+DP_ALGO_AUTO, DP_ALGO_POPC, DP_ALGO_BITSLICE, DP_ALGO_JIT = 0, 1, 2, 3
 
 LETTERS = 'ACTGRYSWKMBDHVN'      # letter index order of the ABI
 BASES = 'ACTG'                   # 2-bit plane code order
@@ -132,6 +132,8 @@ def _declare(lib):
                                 C.c_void_p, P(dp_conditions)]),
         'dp_find_end': (i32, [vp, P(vp), P(u64), P(vp), P(u64), P(dp_scan_stats), P(dp_dg_stats)]),
         'dp_set_wire': (i32, [vp, C.c_void_p, u64]),
+        'dp_scan_prepare_kernels': (i32, [vp, u32, P(C.c_char_p), P(i32), i32]),
+        'dp_jit_selftest': (i32, [u32, P(C.c_char_p), P(i32), i32, C.c_char_p, C.c_char_p]),
         'dp_comm_export': (i32, [vp, i32, i32, u32, C.c_char_p]),
         'dp_comm_attach': (i32, [vp, C.c_char_p]),
         'dp_comm_destroy': (i32, [vp]),
@@ -156,7 +158,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
-           'dp_set_wire dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
+           'dp_set_wire dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
 
 
@@ -371,10 +373,25 @@ class Context(object):
         buf._owner = _Owner(self.lib, ptr.value)          # numpy -> memoryview -> buf -> owner
         return np.frombuffer(buf, dtype=dtype)
 
-    def prepare(self, masters, mismatches, variants):
+    def prepare(self, masters, mismatches, variants, jit=None, strands=DP_STRAND_BOTH):
         """The primer side of dp_find as ready-made C arrays (build once, scan many
-        templates).  variants: one list of unambiguous sequences per master."""
-        return Query(masters, mismatches, variants)
+        templates).  variants: one list of unambiguous sequences per master.
+        jit: also compile the scan kernel specialised for these primers
+        (dp_scan_prepare_kernels, ~0.3 s once per process and primer set; default on,
+        DEGENPRIMER_B200_JIT=0 turns it off).  Without NVRTC the generic kernel serves."""
+        q = Query(masters, mismatches, variants)
+        if jit is None:
+            jit = os.environ.get('DEGENPRIMER_B200_JIT', '1') != '0'
+        q.jit = False
+        if jit:
+            rc = self.lib.dp_scan_prepare_kernels(self._h, q.n, q.m, q.k, int(strands))
+            if rc == 0:
+                q.jit = True
+            elif rc != DP_ERR_STATE:
+                self._check(rc)
+            else:
+                q.jit_error = self.lib.dp_last_error(self._h).decode(errors='replace')
+        return q
 
     def find(self, template, masters, mismatches=None, variants=None, cond=None, seg_begin=0,
              seg_end=2 ** 64 - 1, strands=DP_STRAND_BOTH, algo=DP_ALGO_AUTO):

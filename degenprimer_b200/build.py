@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libdegenprimer_b200.so')
-SOURCES = ['dp_ctx.cu', 'dp_template.cu', 'dp_scan.cu', 'dp_dg.cu', 'dp_comm.cu', 'dp_calib.cu']
+SOURCES = ['dp_ctx.cu', 'dp_template.cu', 'dp_scan.cu', 'dp_dg.cu', 'dp_comm.cu', 'dp_jit.cu', 'dp_calib.cu']
 NVCC_FLAGS = ['-std=c++17', '-O3', '-gencode', 'arch=compute_100a,code=sm_100a',
               '-lineinfo', '-Xcompiler', '-fPIC']
 
@@ -33,6 +33,17 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def _embed_device_header(objdir):
+    """dp_device.cuh as a C++ raw string literal: the header of the run-time compiled kernels."""
+    text = open(os.path.join(CSRC, 'dp_device.cuh')).read()
+    assert ')DPJIT"' not in text
+    out = os.path.join(objdir, 'dp_jit_embed.inc')
+    body = 'R"DPJIT(' + text + ')DPJIT"\n'
+    if not os.path.exists(out) or open(out).read() != body:
+        with open(out, 'w') as f:
+            f.write(body)
+
+
 def build_native(force=False, verbose=False):
     """Compile every CUDA source into one shared library.  Returns its path."""
     if not force and not _stale():
@@ -40,6 +51,7 @@ def build_native(force=False, verbose=False):
     nvcc = _nvcc()
     objdir = os.path.join(HERE, 'build')
     os.makedirs(objdir, exist_ok=True)
+    _embed_device_header(objdir)
     procs = []
     for src in SOURCES:
         obj = os.path.join(objdir, src.replace('.cu', '.o'))
@@ -55,7 +67,7 @@ def build_native(force=False, verbose=False):
             sys.stderr.write(out)
         objs.append(obj)
     tmp = LIB + '.tmp'
-    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs
+    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs + ['-ldl']
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode:
         raise RuntimeError('link failed:\n%s' % r.stdout.decode())

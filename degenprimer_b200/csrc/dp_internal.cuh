@@ -9,20 +9,13 @@
 #include <vector>
 
 #include "../../include/degenprimer_b200.h"
+#include "dp_device.cuh"
 
 // ---- letters -----------------------------------------------------------------
 // 2-bit plane code: A=0 C=1 T=2 G=3  (hi = ASCII bit 2, lo = ASCII bit 1).
 // Letter index: A C T G R Y S W K M B D H V N  (0..14); 15 = not a DNA letter.
 #define DP_LETTERS "ACTGRYSWKMBDHVN"
 #define DP_NOT_A_LETTER 15
-
-// One maximal run of a single non-ACGT letter, in padded-concatenation coords.
-struct dp_exc_run {
-  uint64_t start;
-  uint64_t end;      // exclusive
-  uint32_t letter;   // letter index 4..14, or DP_NOT_A_LETTER for record padding
-  uint32_t pad;
-};
 
 struct dp_record {
   uint64_t start;    // first base in the padded concatenation (multiple of 32)
@@ -49,18 +42,6 @@ struct dp_template {
   uint64_t device_bytes;
 };
 
-// raw hit as written by the scan kernels (padded-concatenation coordinates).
-// pair_base = number of (hit, variant) pairs of all earlier slots: slot and
-// pair_base come from ONE packed 64-bit atomic, so pair_base is monotone in slot.
-struct dp_raw_hit {
-  uint64_t g;          // forward window start in the padded concatenation
-  uint32_t record;
-  uint16_t pattern;
-  uint16_t score3;
-  uint32_t pair_base;
-  uint32_t reserved;
-};
-
 // one surviving dimer as written by the duplex kernel; (hit, variant) are
 // implied by the pair directory
 struct dp_raw_dimer {
@@ -80,16 +61,6 @@ struct dp_dg_plan {
   uint32_t var_off[DP_MAX_PRIMERS];      // byte offset of the primer's variants in d_codes
 };
 
-// counters[] slots (device, 16 x u64)
-enum {
-  DP_C_HITS = 0,      // low 32 bits: hits wanted, high 32 bits: (hit, variant) pairs
-  DP_C_CAND = 1,      // windows that reached the exact verify
-  DP_C_DIMERS = 2,    // dimer slots wanted
-  DP_C_TRIED = 3,     // dimers whose dG was computed
-  DP_C_SATURATED = 4, // the packed hit counter came close to 2^32
-  DP_C_PACK0 = 8,     // pack kernel: boundary entries wanted
-  DP_C_PACK1 = 9      // pack kernel: first foreign byte
-};
 
 struct dp_ctx {
   int device;

@@ -20,6 +20,7 @@
 
 #include "dp_scan.cuh"
 #include "dp_scan_bitslice.cuh"
+#include "dp_jit.cuh"
 
 // ---- kernel 1: every window, XOR/AND-style mask select + popcount ---------------
 // One thread owns one plane word = 32 consecutive window starts; windows that
@@ -297,12 +298,64 @@ struct dp_scan_job {
   std::vector<dp_pattern> pats;
   std::vector<std::vector<uint8_t>> letters;
   dp_bitslice_plan plan;
+  std::vector<dp_jit_unit> jit;     // the same plan as run-time specialised kernels (dp_jit.cu)
+  bool jit_ready;                   // every unit has a compiled kernel
   int used_algo;
   int NW;
   uint32_t max_len;
   dp_scan_args A;
   uint64_t pmask_all[2];
 };
+
+// Finds (compile = false) or makes (compile = true) the specialised kernels of a job.
+static int jit_attach(dp_ctx* ctx, dp_scan_job& J, bool compile) {
+  J.jit_ready = !J.jit.empty();
+  for (dp_jit_unit& u : J.jit) {
+    if (!u.kernel || !u.kernel->fn) {
+      if (compile) {
+        int rc = dp_jit_compile(ctx, u.source, &u.kernel);
+        if (rc) {
+          J.jit_ready = false;
+          return rc;
+        }
+      } else {
+        u.kernel = dp_jit_lookup(u.source);
+      }
+    }
+    if (!u.kernel || !u.kernel->fn) J.jit_ready = false;
+  }
+  return DP_OK;
+}
+
+// patterns, prefilter plan and kernels of a call's primer arguments
+static int job_build(dp_ctx* ctx, uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
+                     int strand_mask, int algo, const uint32_t* var_count, dp_scan_job& J) {
+  int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.pats, J.letters);
+  if (rc) return rc;
+  J.max_len = 0;
+  for (auto& p : J.pats) J.max_len = std::max<uint32_t>(J.max_len, p.len);
+  const uint32_t n_pat = (uint32_t)J.pats.size();
+  J.pmask_all[0] = J.pmask_all[1] = 0;
+  for (uint32_t p = 0; p < n_pat; ++p) J.pmask_all[p >> 6] |= 1ull << (p & 63);
+  J.used_algo = DP_ALGO_POPC;
+  J.jit.clear();
+  J.jit_ready = false;
+  if (algo != DP_ALGO_POPC) {
+    if (dp_bitslice_make_plan(J.pats, J.letters, J.plan)) J.used_algo = DP_ALGO_BITSLICE;
+  }
+  if (J.used_algo == DP_ALGO_BITSLICE && algo != DP_ALGO_BITSLICE) {
+    std::vector<dp_jit_entry> entries;
+    for (const dp_bitslice_group& g : J.plan.groups)
+      for (const dp_bs_pattern& bp : g.pats) entries.push_back(dp_jit_entry{bp.pattern, bp.anchor, g.K});
+    std::sort(entries.begin(), entries.end(), [](const dp_jit_entry& a, const dp_jit_entry& b) { return a.pattern < b.pattern; });
+    dp_jit_make_units(J.pats, J.letters, entries, J.jit);
+    rc = jit_attach(ctx, J, algo == DP_ALGO_JIT);
+    if (rc) return rc;
+  }
+  J.NW = J.max_len > 32 ? 2 : 1;
+  memset(&J.A, 0, sizeof J.A);
+  return DP_OK;
+}
 
 // The primer side of a job (patterns, prefilter plan) depends only on the call's
 // primer arguments: the last one is kept per thread, because the reference calls
@@ -313,10 +366,8 @@ static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, c
   if (n_primers == 0 || n_primers > DP_MAX_PRIMERS)
     return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
   if (!(strand_mask & DP_STRAND_BOTH)) return dp_set_error(ctx, DP_ERR_ARG, "empty strand mask");
-  if (algo != DP_ALGO_AUTO && algo != DP_ALGO_BITSLICE && algo != DP_ALGO_POPC)
+  if (algo != DP_ALGO_AUTO && algo != DP_ALGO_BITSLICE && algo != DP_ALGO_POPC && algo != DP_ALGO_JIT)
     return dp_set_error(ctx, DP_ERR_ARG, "unknown algo %d", algo);
-  static thread_local std::string cached_key;
-  static thread_local dp_scan_job cached;
   std::string key;
   key.reserve(64 * n_primers);
   for (uint32_t i = 0; i < n_primers; ++i) {
@@ -328,24 +379,31 @@ static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, c
     key += ';';
   }
   key += std::to_string(strand_mask) + ',' + std::to_string(algo);
-  if (key == cached_key) {
-    J = cached;
+  // the last few jobs of this thread (the reference alternates between the primers of a pair)
+  struct cache_entry { std::string key; dp_scan_job job; uint64_t used; };
+  static thread_local std::vector<cache_entry> cache;
+  static thread_local uint64_t cache_clock = 0;
+  cache_entry* hit = nullptr;
+  for (cache_entry& e : cache)
+    if (e.key == key) hit = &e;
+  if (hit) {
+    if (!hit->job.jit_ready && !hit->job.jit.empty()) jit_attach(ctx, hit->job, false);   // prepared since?
+    hit->used = ++cache_clock;
+    J = hit->job;
   } else {
-    int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.pats, J.letters);
+    int rc = job_build(ctx, n_primers, masters, max_mismatches, strand_mask, algo, var_count, J);
     if (rc) return rc;
-    J.max_len = 0;
-    for (auto& p : J.pats) J.max_len = std::max<uint32_t>(J.max_len, p.len);
-    const uint32_t n_pat = (uint32_t)J.pats.size();
-    J.pmask_all[0] = J.pmask_all[1] = 0;
-    for (uint32_t p = 0; p < n_pat; ++p) J.pmask_all[p >> 6] |= 1ull << (p & 63);
-    J.used_algo = DP_ALGO_POPC;
-    if (algo == DP_ALGO_AUTO || algo == DP_ALGO_BITSLICE) {
-      if (dp_bitslice_make_plan(J.pats, J.letters, J.plan)) J.used_algo = DP_ALGO_BITSLICE;
+    if (cache.size() < 8) {
+      cache.push_back(cache_entry());
+      hit = &cache.back();
+    } else {
+      hit = &cache[0];
+      for (cache_entry& e : cache)
+        if (e.used < hit->used) hit = &e;
     }
-    J.NW = J.max_len > 32 ? 2 : 1;
-    memset(&J.A, 0, sizeof J.A);
-    cached = J;
-    cached_key = key;
+    hit->key = key;
+    hit->job = J;
+    hit->used = ++cache_clock;
   }
   if (t->records.size() == 1 && t->records[0].len < J.max_len)
     return dp_set_error(ctx, DP_ERR_LENGTH, "template (%llu) is shorter than the primer (%u)",
@@ -417,8 +475,16 @@ static int scan_enqueue(dp_ctx* ctx, dp_scan_job& J, uint32_t* launches) {
   int rc = DP_OK;
   if (n_scan_words) {
     if (J.used_algo == DP_ALGO_BITSLICE) {
-      rc = dp_bitslice_launch(ctx, A, J.pats, J.plan, launches);
-      if (rc) return rc;
+      if (J.jit_ready) {
+        for (const dp_jit_unit& u : J.jit) {
+          rc = dp_jit_launch(ctx, A, J.pats, u);
+          if (rc) return rc;
+          ++*launches;
+        }
+      } else {
+        rc = dp_bitslice_launch(ctx, A, J.pats, J.plan, launches);
+        if (rc) return rc;
+      }
       DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
       if (A.n_runs) {
         // windows touching non-ACGT bases, for the prefiltered patterns
@@ -745,7 +811,7 @@ static void fill_scan_stats(dp_ctx* ctx, const dp_template* t, const dp_scan_job
   cudaEventElapsedTime(&ms_total, ctx->ev0, ctx->ev5);
   stats->ms_total = ms_total;
   stats->launches = launches;
-  stats->algo = (uint32_t)J.used_algo;
+  stats->algo = (uint32_t)(J.used_algo == DP_ALGO_BITSLICE && J.jit_ready ? DP_ALGO_JIT : J.used_algo);
 }
 
 // scan [+ duplex] with overflow handling, split so that a caller can queue its own
@@ -992,6 +1058,47 @@ extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
                          var_count, var_offset, variants, cond);
   if (rc) return rc;
   return dp_find_end(ctx, hits_out, n_hits_out, dimers_out, n_dimers_out, stats, dg_stats);
+}
+
+extern "C" int dp_scan_prepare_kernels(dp_ctx* ctx, uint32_t n_primers, const char* const* masters,
+                                       const int32_t* max_mismatches, int strand_mask) {
+  if (!ctx || !masters) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (n_primers == 0 || n_primers > DP_MAX_PRIMERS)
+    return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
+  if (!(strand_mask & DP_STRAND_BOTH)) return dp_set_error(ctx, DP_ERR_ARG, "empty strand mask");
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  dp_scan_job J;
+  return job_build(ctx, n_primers, masters, max_mismatches, strand_mask, DP_ALGO_JIT, nullptr, J);
+}
+
+// Build check without a device: generates the specialised kernel source of a pattern set,
+// compiles it with NVRTC and (optionally) writes source / cubin of the first unit to files.
+// Returns the number of launch units, or a negative DP_ERR code (message via dp_last_error(NULL)).
+extern "C" int dp_jit_selftest(uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
+                               int strand_mask, const char* source_path, const char* cubin_path) {
+  dp_scan_job J;
+  int rc = build_patterns(nullptr, n_primers, masters, max_mismatches, strand_mask, nullptr, J.pats, J.letters);
+  if (rc) return rc;
+  if (!dp_bitslice_make_plan(J.pats, J.letters, J.plan)) return 0;
+  std::vector<dp_jit_entry> entries;
+  for (const dp_bitslice_group& g : J.plan.groups)
+    for (const dp_bs_pattern& bp : g.pats) entries.push_back(dp_jit_entry{bp.pattern, bp.anchor, g.K});
+  std::sort(entries.begin(), entries.end(), [](const dp_jit_entry& a, const dp_jit_entry& b) { return a.pattern < b.pattern; });
+  dp_jit_make_units(J.pats, J.letters, entries, J.jit);
+  for (size_t i = 0; i < J.jit.size(); ++i) {
+    std::string log;
+    std::string cubin = dp_jit_compile_only(J.jit[i].source, log);
+    if (i == 0 && source_path) {
+      FILE* f = fopen(source_path, "wb");
+      if (f) { fwrite(J.jit[i].source.data(), 1, J.jit[i].source.size(), f); fclose(f); }
+    }
+    if (cubin.empty()) return dp_set_error(nullptr, DP_ERR_STATE, "%s", log.c_str());
+    if (i == 0 && cubin_path) {
+      FILE* f = fopen(cubin_path, "wb");
+      if (f) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
+    }
+  }
+  return (int)J.jit.size();
 }
 
 extern "C" int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes) {

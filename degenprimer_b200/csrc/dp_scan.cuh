@@ -1,129 +1,4 @@
-// Scan: shared device structures (patterns as kernel parameters, exact verify).
+// Scan: shared device structures (patterns as kernel parameters, exact verify) live in
+// dp_device.cuh, which is also the header of the run-time compiled kernels (dp_jit.cu).
 #pragma once
 #include "dp_internal.cuh"
-
-// One (primer, strand) pattern.  Masks are indexed by plane code (A C T G) and
-// cover primer positions 0..63 (two words, bit j = position j of the WINDOW on
-// the forward strand; reverse-strand patterns are stored reverse-complemented).
-//   f: base scores 3/3 at this position,  h: base scores 2/3   
-struct dp_pattern {
-  uint32_t f[4][2];
-  uint32_t h[4][2];
-  uint32_t lmask[2];
-  uint16_t len;
-  uint16_t thr3;       // hit iff score3 >= thr3  (3*max(1,L-k)-1)
-  uint16_t primer;
-  uint8_t strand;
-  uint8_t has_half;
-  uint32_t n_var;      // unambiguous variants of the primer (duplex pairs per hit)
-  uint32_t reserved;
-};
-
-// The patterns of a call travel as a __grid_constant__ kernel parameter (constant
-// bank 0, uniform LDC access, no symbol upload, nothing shared between contexts).
-// Two capacities so that the common 1-4 primer call ships < 1 KB per launch.
-#define DP_NP_SMALL 8
-template <int NP>
-struct dp_pattern_set {
-  dp_pattern pat[NP];
-};
-
-struct dp_scan_args {
-  const uint32_t* lo;
-  const uint32_t* hi;
-  const uint32_t* exc;
-  const uint64_t* rec_start;
-  const uint64_t* rec_len;
-  uint32_t n_records;
-  uint32_t n_patterns;
-  uint64_t n_words;       // words holding record data
-  uint64_t word_begin;    // first word scanned
-  uint64_t word_end;
-  uint64_t seg_begin;     // window starts allowed in [seg_begin, seg_end)
-  uint64_t seg_end;
-  dp_raw_hit* hits;
-  uint64_t hits_cap;
-  unsigned long long* counters;   // DP_C_* slots
-  const dp_exc_run* runs;         // exception runs (sorted) for the run-boundary pass
-  uint64_t n_runs;
-};
-
-__device__ __forceinline__ uint32_t dp_mux4(uint32_t hi, uint32_t lo, uint32_t a, uint32_t c,
-                                            uint32_t t, uint32_t g) {
-  uint32_t u0 = (lo & c) | (~lo & a);    // hi = 0: A or C
-  uint32_t u1 = (lo & g) | (~lo & t);    // hi = 1: T or G
-  return (hi & u1) | (~hi & u0);
-}
-
-// exact thirds score of one window against one pattern; words 0/1 hold window
-// positions 0..31 / 32..63
-template <int NW>
-__device__ __forceinline__ uint32_t dp_score3(const dp_pattern& p, const uint32_t* whi,
-                                              const uint32_t* wlo, const uint32_t* wex) {
-  uint32_t s = 0;
-#pragma unroll
-  for (int k = 0; k < NW; ++k) {
-    uint32_t ok = ~wex[k];
-    uint32_t mf = dp_mux4(whi[k], wlo[k], p.f[0][k], p.f[1][k], p.f[2][k], p.f[3][k]) & ok;
-    s += 3u * __popc(mf);
-    if (p.has_half) {
-      uint32_t mh = dp_mux4(whi[k], wlo[k], p.h[0][k], p.h[1][k], p.h[2][k], p.h[3][k]) & ok;
-      s += 2u * __popc(mh);
-    }
-    s += __popc(wex[k] & p.lmask[k]);
-  }
-  return s;
-}
-
-// record that contains padded position g (records are word aligned, sorted)
-__device__ __forceinline__ uint32_t dp_find_record(const uint64_t* rec_start, uint32_t n, uint64_t g) {
-  uint32_t a = 0, b = n;
-  while (a < b) {
-    uint32_t m = (a + b) >> 1;
-    if (rec_start[m] <= g) a = m + 1; else b = m;
-  }
-  return a ? a - 1 : 0;
-}
-
-__device__ __forceinline__ void dp_emit_hit(const dp_scan_args& A, uint64_t g, uint32_t pat,
-                                            uint32_t len, uint32_t score, uint32_t n_var) {
-  if (g < A.seg_begin || g >= A.seg_end) return;
-  uint32_t r = dp_find_record(A.rec_start, A.n_records, g);
-  uint64_t off = g - A.rec_start[r];
-  if (off + len > A.rec_len[r]) return;          // window runs past its record
-  // one packed atomic hands out the slot (low half) and the first (hit, variant)
-  // pair index (high half) together, so pair_base is monotone in slot
-  const unsigned long long seen = *(volatile unsigned long long*)&A.counters[DP_C_HITS];
-  if ((uint32_t)seen > 0xF0000000u || (seen >> 32) > 0xF0000000ull) {
-    A.counters[DP_C_SATURATED] = 1ull;
-    return;
-  }
-  const unsigned long long old = atomicAdd(&A.counters[DP_C_HITS], 1ull | ((unsigned long long)n_var << 32));
-  const uint32_t slot = (uint32_t)old;
-  if (slot < A.hits_cap) {
-    dp_raw_hit h;
-    h.g = g; h.record = r; h.pattern = (uint16_t)pat; h.score3 = (uint16_t)score;
-    h.pair_base = (uint32_t)(old >> 32); h.reserved = 0;
-    A.hits[slot] = h;
-  }
-}
-
-// exact verify of window g against pattern P (index pat); with_exc = false leaves
-// windows that touch a non-ACGT base to the run-boundary pass
-__device__ __forceinline__ void dp_verify_window(const dp_scan_args& A, const dp_pattern& P, uint64_t g,
-                                                 uint32_t pat, bool with_exc) {
-  const uint64_t wi = g >> 5;
-  const int sh = (int)(g & 31);
-  uint32_t whi[2], wlo[2], wex[2];
-  {
-    const uint32_t a0 = __ldg(A.hi + wi), a1 = __ldg(A.hi + wi + 1), a2 = __ldg(A.hi + wi + 2);
-    whi[0] = __funnelshift_r(a0, a1, sh); whi[1] = __funnelshift_r(a1, a2, sh);
-    const uint32_t b0 = __ldg(A.lo + wi), b1 = __ldg(A.lo + wi + 1), b2 = __ldg(A.lo + wi + 2);
-    wlo[0] = __funnelshift_r(b0, b1, sh); wlo[1] = __funnelshift_r(b1, b2, sh);
-    const uint32_t e0 = __ldg(A.exc + wi), e1 = __ldg(A.exc + wi + 1), e2 = __ldg(A.exc + wi + 2);
-    wex[0] = __funnelshift_r(e0, e1, sh); wex[1] = __funnelshift_r(e1, e2, sh);
-  }
-  if (!with_exc && ((wex[0] & P.lmask[0]) | (wex[1] & P.lmask[1]))) return;
-  const uint32_t s = dp_score3<2>(P, whi, wlo, wex);
-  if (s >= P.thr3) dp_emit_hit(A, g, pat, P.len, s, P.n_var);
-}

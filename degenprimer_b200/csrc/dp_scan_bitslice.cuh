@@ -56,67 +56,6 @@ struct dp_bitslice_plan {
   std::vector<dp_bitslice_group> groups;
 };
 
-// ---- bit-sliced population count of N one-bit planes ----------------------------
-template <int N>
-struct dp_level {
-  // Reduces N same-weight words to one; writes floor(N/2) next-weight carries.
-  __device__ __forceinline__ static uint32_t run(const uint32_t* in, uint32_t* c) {
-    if constexpr (N == 1) {
-      return in[0];
-    } else if constexpr (N == 2) {
-      c[0] = in[0] & in[1];
-      return in[0] ^ in[1];
-    } else {
-      constexpr int G = N / 3, R = N % 3;
-      uint32_t s[G + R];
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        uint32_t a = in[3 * g], b = in[3 * g + 1], d = in[3 * g + 2];
-        s[g] = a ^ b ^ d;
-        c[g] = (a & b) | (d & (a | b));
-      }
-#pragma unroll
-      for (int r = 0; r < R; ++r) s[G + r] = in[3 * G + r];
-      return dp_level<G + R>::run(s, c + G);
-    }
-  }
-};
-
-// bits[] receives the binary count of the N planes; returns number of bits
-template <int N, int B>
-struct dp_count {
-  __device__ __forceinline__ static void run(const uint32_t* in, uint32_t* bits) {
-    if constexpr (N == 0) {
-      return;
-    } else {
-      uint32_t c[N / 2 + 1];
-      bits[B] = dp_level<N>::run(in, c);
-      dp_count<N / 2, B + 1>::run(c, bits);
-    }
-  }
-};
-
-__host__ __device__ constexpr int dp_bits_for(int n) { return n == 0 ? 0 : 1 + dp_bits_for(n / 2); }
-
-// word of windows whose plane count is >= THR
-template <int N, int THR>
-__device__ __forceinline__ uint32_t dp_count_ge(const uint32_t* in) {
-  constexpr int NB = dp_bits_for(N);
-  uint32_t bits[NB];
-  dp_count<N, 0>::run(in, bits);
-  uint32_t ge = 0u, eq = ~0u;
-#pragma unroll
-  for (int b = NB - 1; b >= 0; --b) {
-    if ((THR >> b) & 1) {
-      eq &= bits[b];
-    } else {
-      ge |= eq & bits[b];
-      eq &= ~bits[b];
-    }
-  }
-  return ge | eq;
-}
-
 // one pattern against the 32 windows of the thread's current word
 template <int K, int E>
 __device__ __forceinline__ void dp_bs_pattern_step(const dp_scan_args& A, const dp_pattern& P, const dp_bs_pattern& bp,

@@ -137,7 +137,11 @@ enum { DP_STRAND_FWD = 1, DP_STRAND_REV = 2, DP_STRAND_BOTH = 3 };
 enum {
   DP_ALGO_AUTO = 0,
   DP_ALGO_POPC = 1,     /* per-window XOR/AND + popcount                        */
-  DP_ALGO_BITSLICE = 2  /* bit-sliced prefilter over 32 windows + exact verify  */
+  DP_ALGO_BITSLICE = 2, /* bit-sliced prefilter over 32 windows + exact verify  */
+  DP_ALGO_JIT = 3       /* the same prefilter, compiled at run time (NVRTC) for
+                           this pattern set: compiles now if it has to.  AUTO
+                           uses such a kernel when dp_scan_prepare_kernels made
+                           one before, else the generic BITSLICE kernel        */
 };
 
 typedef struct dp_scan_stats {
@@ -152,6 +156,22 @@ typedef struct dp_scan_stats {
   uint32_t launches;       /* kernels launched by this call                      */
   uint32_t algo;           /* DP_ALGO_* actually used                            */
 } dp_scan_stats;
+
+/* Compiles (NVRTC, ~0.2-0.5 s once per process and pattern set) the scan kernel
+ * specialised for these primers; later dp_scan / dp_find calls with the same
+ * masters, mismatch limits and strand mask use it under DP_ALGO_AUTO.  Call it
+ * for a query that will be scanned more than once or over a large template.
+ * Fails (DP_ERR_STATE) if libnvrtc cannot be loaded or the compile fails -- the
+ * generic kernel then keeps serving DP_ALGO_AUTO; results are identical. */
+int dp_scan_prepare_kernels(dp_ctx* ctx, uint32_t n_primers, const char* const* masters,
+                            const int32_t* max_mismatches, int strand_mask);
+
+/* Build check that needs no device: generates the specialised kernel source for
+ * a primer set, compiles it with NVRTC and optionally writes the source / cubin
+ * of the first launch unit to files.  Returns the number of launch units (0: no
+ * pattern takes the prefilter) or a negative DP_ERR code (dp_last_error(NULL)). */
+int dp_jit_selftest(uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
+                    int strand_mask, const char* source_path, const char* cubin_path);
 
 /* seg_begin/seg_end restrict window STARTS to [seg_begin, seg_end) of the
  * padded concatenation (multi-GPU sharding); pass 0, UINT64_MAX for

@@ -21,7 +21,7 @@ def split_hits(hits, primer):
     return h[h['strand'] == 0]['pos'].astype(np.int64), h[h['strand'] == 1]['pos'].astype(np.int64)
 
 
-@pytest.mark.parametrize('algo', [1, 2])
+@pytest.mark.parametrize('algo', [1, 2, 3])
 @pytest.mark.parametrize('k', [0, 1, 3, 6])
 def test_scan_matches_oracle(ctx, algo, k):
     rng = np.random.default_rng(100 + k)
@@ -41,7 +41,7 @@ def test_scan_matches_oracle(ctx, algo, k):
     assert total == len(hits) and total > 0
 
 
-@pytest.mark.parametrize('algo', [1, 2])
+@pytest.mark.parametrize('algo', [1, 2, 3])
 def test_scan_with_iupac_template_and_fft_oracle(ctx, algo):
     rng = np.random.default_rng(7)
     t = random_dna(rng, 30000, 'ACGTNRYSWKMBDHV', p=[0.23] * 4 + [0.08 / 11] * 11)
@@ -255,7 +255,7 @@ def test_run_boundary_windows(ctx):
     tmpl = ctx.template_from_sequences([t])
     for k in (1, 2, 4):
         ref = o2.find(t, m, k)
-        for algo in (1, 2):
+        for algo in (1, 2, 3):
             hits, st = ctx.scan(tmpl, [m], k, algo=algo)
             f, r = split_hits(hits, 0)
             assert np.array_equal(f, ref[4]) and np.array_equal(r, ref[5]), (k, algo)
@@ -294,3 +294,37 @@ def test_large_duplex_results_device_layout(ctx):
     want = np.concatenate(parts)
     assert np.array_equal(want, dimers)
     assert np.all(np.diff(dimers['hit'].astype(np.int64)) >= 0)
+
+
+def test_jit_kernels_equal_generic(ctx):
+    """Run-time specialised scan kernels (NVRTC): same hits as the generic bit-slice kernel
+    and the popcount kernel for plain, degenerate and many-primer sets; prepare() makes
+    DP_ALGO_AUTO pick them up; candidate counts of the prefilter are identical."""
+    from degenprimer_b200 import _native as nat
+    from degenprimer_b200.SeqUtils import unambiguous_sequences
+    from degenprimer_b200.synthetic import multiplex_primers
+    rng = np.random.default_rng(123)
+    sets = [(PRIMERS, 1), (['AGRGTTYGATYMTGGYTYWG', 'KACGGYTAMCTTRTTAYGASTW'], 3),
+            (multiplex_primers(), 3), (['ATATTCTACAACGGCTATCCNNNNNNAGGTCA', 'GATTACAGATTACAGATTACA'], 4)]
+    for masters, k in sets:
+        t = random_dna(rng, 300000, 'ACGTN', p=[0.2495] * 4 + [0.002])
+        t, _ = plant_sites(rng, t, masters, min(k, 3), 6)
+        tmpl = ctx.template_from_sequences([t])
+        a, sa = ctx.scan(tmpl, masters, k, algo=nat.DP_ALGO_JIT)
+        b, sb = ctx.scan(tmpl, masters, k, algo=nat.DP_ALGO_BITSLICE)
+        c, sc = ctx.scan(tmpl, masters, k, algo=nat.DP_ALGO_POPC)
+        assert sa['algo'] == nat.DP_ALGO_JIT and sb['algo'] == nat.DP_ALGO_BITSLICE
+        assert np.array_equal(a, b) and np.array_equal(a, c) and len(a) > 0
+        assert sa['candidates'] == sb['candidates']
+        d, sd = ctx.scan(tmpl, masters, k)                       # compiled above: AUTO uses it
+        assert sd['algo'] == nat.DP_ALGO_JIT and np.array_equal(a, d)
+    # a set nobody prepared runs on the generic kernel under AUTO; prepare() switches it
+    fresh = ['TTGACCGATAGGCTAACGTA']
+    t = random_dna(rng, 50000)
+    tmpl = ctx.template_from_sequences([t])
+    _, s0 = ctx.scan(tmpl, fresh, 2)
+    assert s0['algo'] == nat.DP_ALGO_BITSLICE
+    q = ctx.prepare(fresh, 2, [unambiguous_sequences(m) for m in fresh], jit=True)
+    assert q.jit, getattr(q, 'jit_error', '')
+    _, s1 = ctx.scan(tmpl, fresh, 2)
+    assert s1['algo'] == nat.DP_ALGO_JIT

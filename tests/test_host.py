@@ -159,3 +159,25 @@ def test_search_engine_surface():
         se.SearchEngine._check_length_inequality(5, 10)
     with pytest.raises(ValueError):
         se.SearchEngine._check_length_inequality(5, 0)
+
+
+def test_specialised_scan_kernel_compiles_without_a_device(native_lib, tmp_path):
+    """dp_jit_selftest: source generation + NVRTC compile of the run-time specialised scan
+    kernel (sm_100a) for a plain pair, a degenerate pair and a 20-plex; the source has one
+    block per (primer, strand) pattern and no shared memory."""
+    lib = ctypes.CDLL(native_lib)
+    lib.dp_last_error.restype = ctypes.c_char_p
+    from degenprimer_b200.synthetic import TP53_F, TP53_R, P27F_D128, P1492R_D128, multiplex_primers
+    for masters, k, units in (([TP53_F, TP53_R], 1, 1), ([P27F_D128, P1492R_D128], 3, 1), (multiplex_primers(), 3, 1)):
+        arr = (ctypes.c_char_p * len(masters))(*[m.encode() for m in masters])
+        ks = (ctypes.c_int32 * len(masters))(*([k] * len(masters)))
+        src = str(tmp_path / 'unit.cu')
+        rc = lib.dp_jit_selftest(len(masters), arr, ks, 3, src.encode(), None)
+        if rc < 0 and b'libnvrtc' in lib.dp_last_error(None):
+            pytest.skip('NVRTC is not installed here')
+        assert rc == units, lib.dp_last_error(None)
+        text = open(src).read()
+        assert text.count('dp_count_ge<') == 2 * len(masters)
+        assert '__shared__' not in text
+    bad = (ctypes.c_char_p * 1)(b'ACGTZ')
+    assert lib.dp_jit_selftest(1, bad, (ctypes.c_int32 * 1)(0), 3, None, None) < 0
