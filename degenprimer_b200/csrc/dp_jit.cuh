@@ -6,6 +6,7 @@
 #include "dp_scan.cuh"
 
 #define DP_JIT_THREADS 256
+#define DP_JIT_AUTO_MAX_PATTERNS 16 // DP_ALGO_AUTO: larger sets stay on the generic kernel
 #define DP_JIT_MAX_PATTERNS 48     // per launch: bounds code size and the parameter block
 
 struct dp_jit_kernel {

@@ -329,7 +329,8 @@ static int jit_attach(dp_ctx* ctx, dp_scan_job& J, bool compile) {
 
 // patterns, prefilter plan and kernels of a call's primer arguments
 static int job_build(dp_ctx* ctx, uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
-                     int strand_mask, int algo, const uint32_t* var_count, dp_scan_job& J) {
+                     int strand_mask, int algo, const uint32_t* var_count, dp_scan_job& J,
+                     bool compile = false) {
   int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.pats, J.letters);
   if (rc) return rc;
   J.max_len = 0;
@@ -348,9 +349,14 @@ static int job_build(dp_ctx* ctx, uint32_t n_primers, const char* const* masters
     for (const dp_bitslice_group& g : J.plan.groups)
       for (const dp_bs_pattern& bp : g.pats) entries.push_back(dp_jit_entry{bp.pattern, bp.anchor, g.K});
     std::sort(entries.begin(), entries.end(), [](const dp_jit_entry& a, const dp_jit_entry& b) { return a.pattern < b.pattern; });
-    dp_jit_make_units(J.pats, J.letters, entries, J.jit);
-    rc = jit_attach(ctx, J, algo == DP_ALGO_JIT);
-    if (rc) return rc;
+    // with many patterns the generic kernel wins: it fetches a term's plane with an LDS,
+    // the specialised one computes it with a LOP3 on the integer pipe that bounds both
+    // (20-plex, K = 3: 13.7 ms against 15.3 ms), so AUTO leaves those to the generic kernel
+    if (algo == DP_ALGO_JIT || entries.size() <= DP_JIT_AUTO_MAX_PATTERNS) {
+      dp_jit_make_units(J.pats, J.letters, entries, J.jit);
+      rc = jit_attach(ctx, J, compile || algo == DP_ALGO_JIT);
+      if (rc) return rc;
+    }
   }
   J.NW = J.max_len > 32 ? 2 : 1;
   memset(&J.A, 0, sizeof J.A);
@@ -1068,7 +1074,7 @@ extern "C" int dp_scan_prepare_kernels(dp_ctx* ctx, uint32_t n_primers, const ch
   if (!(strand_mask & DP_STRAND_BOTH)) return dp_set_error(ctx, DP_ERR_ARG, "empty strand mask");
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
   dp_scan_job J;
-  return job_build(ctx, n_primers, masters, max_mismatches, strand_mask, DP_ALGO_JIT, nullptr, J);
+  return job_build(ctx, n_primers, masters, max_mismatches, strand_mask, DP_ALGO_AUTO, nullptr, J, true);
 }
 
 // Build check without a device: generates the specialised kernel source of a pattern set,

@@ -177,7 +177,8 @@ def test_specialised_scan_kernel_compiles_without_a_device(native_lib, tmp_path)
             pytest.skip('NVRTC is not installed here')
         assert rc == units, lib.dp_last_error(None)
         text = open(src).read()
-        assert text.count('dp_count_ge<') == 2 * len(masters)
+        assert text.count('dp_jit_alive(A, PS.pat') == 2 * len(masters)      # one prefilter per (primer, strand)
+        assert ('dp_count_ge<' in text) == (k == 3)                          # K <= 1: exact position sets, else adders
         assert '__shared__' not in text
     bad = (ctypes.c_char_p * 1)(b'ACGTZ')
     assert lib.dp_jit_selftest(1, bad, (ctypes.c_int32 * 1)(0), 3, None, None) < 0
