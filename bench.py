@@ -38,14 +38,16 @@ L2_BYTES = 126 * 1024 * 1024
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=20)
-    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--workload', default=WORKLOAD)
     ap.add_argument('--scale', type=float, default=1.0, help='shrink the template (testing only)')
     ap.add_argument('--algo', type=int, default=0, help='0 auto, 1 popcount, 2 bit-slice')
     ap.add_argument('--cpu-sample-bp', type=int, default=12_000_000)
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--in-flight', type=int, default=2,
+                    help='calls in flight on the GPU (one context per call); 1 = strictly sequential')
     return ap.parse_args()
 
 
@@ -261,85 +263,111 @@ def run_ours(args):
     n_copies = min(n_copies, 64)
     copies = [one] + [ctx.template_from_sequences(srcs) for _ in range(n_copies - 1)]
 
-    query = ctx.prepare(primers, k, var_lists)      # the primer side, laid out once
-
-    exch = None
+    # Lanes: contexts (own stream, own result buffers) on this GPU.  The resident arm keeps one
+    # call in flight per lane, so the host work of a call (queueing ~30 us, result conversion)
+    # overlaps the kernels of the other lane's call; templates are shared between the lanes.
+    n_lanes = max(1, args.in_flight)
+    lanes = [ctx] + [tdf.new_context(local) for _ in range(n_lanes - 1)]
+    queries = [c.prepare(primers, k, var_lists) for c in lanes]      # the primer side, laid out once
+    exchs = [None] * n_lanes
     if world > 1:
         # the hit gather is the epilogue of the publish kernel: each rank stores its slot into
         # every peer's receive buffer over NVLink (CUDA IPC peer memory), no collective launch
         from degenprimer_b200.distributed import HitExchange
-        exch = HitExchange(ctx, max_hits=1024)
+        exchs = [HitExchange(c, max_hits=1024) for c in lanes]
 
-    def step(i):
-        # one pass of the hot path: scan of every primer over both strands + dG of every
-        # (hit, variant), one stream submission (dp_find), results back on the host
-        t = copies[i % n_copies]
-        return ctx.find(t, query, cond=cond, algo=args.algo)
-
-    def gathered(age, own):
-        # hits of every rank for a step (rank g's segment = record g of the genome).  Step
-        # i+1's publish kernel moves step i's slots to pinned host memory, so inside the loop
-        # step i-2 is collected while the GPU runs step i (age 2: its conversion and sort
-        # overlap the kernels), and the last two steps after the loop (ages 1 and 0) — every
-        # gather completes inside the timed region.
-        allh = exch.collect_hits(age)
+    def gathered(lane, age, own):
+        # hits of every rank for a call of this lane (rank g's segment = record g of the genome).
+        # The publish kernel of the lane's next call moves a call's slots to pinned host memory,
+        # so inside the loop the call two back is collected while the newest one runs (age 2:
+        # conversion and sort overlap the kernels); the last two calls of a lane are collected
+        # after the loop (ages 1 and 0) — every gather completes inside the timed region.
+        allh = exchs[lane].collect_hits(age)
         return allh if allh is not None else sort_hits(all_gather_records(own))
 
     def sync_all():
-        ctx.synchronize()
+        for c in lanes:
+            c.synchronize()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
             torch.cuda.synchronize()
 
-    # CUDA events on the stream the kernels are launched on (the context's own stream)
+    # CUDA events on the stream the kernels are launched on (lane 0's stream; when the region
+    # ends every lane has been waited for, so the closing event is later than all work)
     kstream = torch.cuda.ExternalStream(ctx.stream, device=torch.device('cuda', local))
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
-    for i in range(max(3, args.warmup)):
-        step(i)
+    def timed_region(K, F, first_call):
+        """K steps with F calls in flight (F = 1: strictly one after the other).  A step = one
+        pass of the hot path: scan of every primer over both strands + dG of every (hit,
+        variant), one stream submission (dp_find), results back on the host."""
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        acc = dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, dimers=0, cand=0, windows=0, algo=0)
+        made = [0] * F                          # calls of this region queued on a lane
+        own = [[None, None] for _ in range(F)]  # a lane's own hits of its last two calls
+
+        def begin(i):
+            lane = i % F
+            lanes[lane].find_begin(copies[(first_call + i) % n_copies], queries[lane], cond, algo=args.algo)
+            made[lane] += 1
+
+        for c in lanes:
+            c.set_timing(F == 1)               # the ms_* stats are only read in the sequential region
+        sync_all()
+        t0 = time.perf_counter()
+        ev0.record(kstream)
+        for i in range(min(F - 1, K)):
+            begin(i)
+        for i in range(K):
+            if i + F - 1 < K:
+                begin(i + F - 1)
+            lane = i % F
+            if exchs[lane] is not None and made[lane] >= 3:
+                acc['hits'] += len(gathered(lane, 2, own[lane][0]))
+            hits, dimers, st, dst = lanes[lane].find_end()
+            own[lane] = [own[lane][1], hits]
+            if exchs[lane] is None:
+                acc['hits'] += len(hits)
+            acc['ms_main'] += st['ms_main']
+            acc['ms_scan'] += st['ms_scan']
+            acc['ms_dg'] += dst['ms_kernel']
+            acc['launches'] += st['launches'] + dst['launches']
+            acc['dimers'] += len(dimers)
+            acc['cand'] += st['candidates']
+            acc['windows'] = st['windows']
+            acc['algo'] = st['algo']
+        for lane in range(F):
+            if exchs[lane] is not None:
+                if made[lane] >= 2:
+                    acc['hits'] += len(gathered(lane, 1, own[lane][0]))
+                if made[lane] >= 1:
+                    acc['hits'] += len(gathered(lane, 0, own[lane][1]))
+        ev1.record(kstream)
+        sync_all()
+        wall = time.perf_counter() - t0
+        elapsed = ev0.elapsed_time(ev1) * 1e-3        # device clock, first launch -> last result on the host
+        if world > 1:
+            tt = torch.tensor([elapsed, wall], dtype=torch.float64, device='cuda')
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            elapsed, wall = float(tt[0].item()), float(tt[1].item())
+        return elapsed, wall, acc
+
+    K = max(1, args.steps)
+    W = max(3, args.warmup)
+    timed_region(W, n_lanes, 0)                     # warm-up, untimed
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    sync_all()
-    acc = dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, dimers=0, cand=0, windows=0)
-    t0 = time.perf_counter()
-    ev0.record(kstream)
-    n_gathered = 0
-    own = [None, None]                       # this rank's hits of the last two steps
-    for i in range(args.steps):
-        if exch is not None:
-            ctx.find_begin(copies[(args.warmup + i) % n_copies], query, cond, algo=args.algo)
-            if i >= 2:
-                n_gathered += len(gathered(2, own[0]))
-            hits, dimers, st, dst = ctx.find_end()
-            own = [own[1], hits]
-            if i == args.steps - 1:
-                if i >= 1:
-                    n_gathered += len(gathered(1, own[0]))
-                n_gathered += len(gathered(0, own[1]))
-        else:
-            hits, dimers, st, dst = step(args.warmup + i)
-            n_gathered += len(hits)
-        acc['ms_main'] += st['ms_main']
-        acc['ms_scan'] += st['ms_scan']
-        acc['ms_dg'] += dst['ms_kernel']
-        acc['launches'] += st['launches'] + dst['launches']
-        acc['hits'] = n_gathered
-        acc['dimers'] += len(dimers)
-        acc['cand'] += st['candidates']
-        acc['windows'] = st['windows']
-    ev1.record(kstream)
-    sync_all()
-    wall = time.perf_counter() - t0
-    elapsed = ev0.elapsed_time(ev1) * 1e-3        # device clock, first launch -> last result copy
-    if world > 1:
-        tt = torch.tensor([elapsed, wall], dtype=torch.float64, device='cuda')
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        elapsed, wall = float(tt[0].item()), float(tt[1].item())
-    K = max(1, args.steps)
+    # (1) the headline: K steps, n_lanes calls in flight
+    elapsed, wall, acc = timed_region(K, n_lanes, W)
     ms_step = elapsed / K * 1e3
     value = world * bp * n_var / (elapsed / K)
+    # (2) the same K steps strictly one after the other: per-call latency, and kernel durations
+    #     that are not stretched by the other lane's kernels (the roofline below uses these)
+    seq_elapsed, seq_wall, seq = timed_region(K, 1, W + K)
+    for ex in exchs:
+        if ex is not None:
+            ex.close()          # the e2e leg below runs the ranks independently
 
     # ---- e2e: host ASCII in pinned memory -> reference-facing calls -> host results -------------
     from degenprimer_b200.Primer import Primer
@@ -352,10 +380,15 @@ def run_ours(args):
         g = Primer(SeqRecord(Seq(p), id='primer%d' % i), 1.5e-6)
         g.generate_components()
         gprimers.append(g)
-    se = SearchEngine()
+    # one worker thread per lane, each with its own context and SearchEngine: while one worker's
+    # template is on its way over PCIe the other one's is being scanned (ctypes drops the GIL)
+    import threading
+    engines = [SearchEngine() for _ in lanes]
+    d2h_last = [0] * n_lanes
 
-    def e2e_step():
-        t = ctx.template_from_sequences(srcs)                 # H2D of the ASCII bytes + pack kernel
+    def e2e_step(lane):
+        c, se = lanes[lane], engines[lane]
+        t = c.template_from_sequences(srcs)                   # H2D of the ASCII bytes + pack kernel
         d2h = 0
         for r in range(t.n_records):
             rec = ResidentRecord(t, r)
@@ -363,18 +396,29 @@ def run_ours(args):
                 se.find_duplexes(WorkCounter(), rec, g, k)    # SearchEngine.find without the shelf file
                 d2h += 16 * int(se.last_stats['scan']['hits']) + 24 * int(se.last_stats['dg']['dimers_kept'])
         t.close()
-        return d2h
+        d2h_last[lane] = d2h
 
-    for _ in range(2):
-        e2e_step()
+    def e2e_run(n_steps):
+        def work(lane):
+            for i in range(lane, n_steps, n_lanes):
+                e2e_step(lane)
+        threads = [threading.Thread(target=work, args=(lane,)) for lane in range(1, n_lanes)]
+        for th in threads:
+            th.start()
+        work(0)
+        for th in threads:
+            th.join()
+
+    for lane in range(n_lanes):
+        e2e_step(lane)
+    e2e_run(2 * n_lanes)
     sync_all()
-    e2e_steps = max(3, min(args.steps, 10))
+    e2e_steps = max(4, min(args.steps, 10 * n_lanes))
     t0 = time.perf_counter()
-    d2h = 0
-    for _ in range(e2e_steps):
-        d2h = e2e_step()
+    e2e_run(e2e_steps)
     sync_all()
     e2e_elapsed = time.perf_counter() - t0
+    d2h = d2h_last[0]
     if world > 1:
         tt = torch.tensor([e2e_elapsed], dtype=torch.float64, device='cuda')
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -396,10 +440,10 @@ def run_ours(args):
         pass
     hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
     peak_src = 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6.65 TB/s (B200_PROFILING.md)'
-    ms_main = acc['ms_main'] / K
+    ms_main = seq['ms_main'] / K              # from the sequential region: not stretched by the other lane
     algo_bytes = 0.25 * bp                      # 2 bits per template base, read once
     achieved = algo_bytes / (ms_main * 1e-3) / 1e9 if ms_main > 0 else 0.0
-    kernel = 'dp_scan_bitslice_kernel' if st['algo'] == 2 else 'dp_scan_popc_kernel'
+    kernel = {2: 'dp_scan_bitslice_kernel', 3: 'dp_jit_scan'}.get(seq['algo'], 'dp_scan_popc_kernel')
     traffic = None
     try:
         with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as fh:
@@ -417,7 +461,7 @@ def run_ours(args):
     lop3 = ctx.calibrate('lop3')
     popc = ctx.calibrate('popc')
     lds = ctx.calibrate('lds')
-    windows = float(acc['windows'])
+    windows = float(seq['windows'])
     a_win = 16.0
     int_roofline = {
         'bound': 'int32 ALU (LOP3) issue rate, measured by dp_calibrate on this GPU',
@@ -437,16 +481,21 @@ def run_ours(args):
                    'variants': n_var, 'max_mismatches': k, 'records': len(wl['records']),
                    'l2': 'rotating %d resident copies of the template planes (%.0f MB > 126 MB L2)'
                          % (n_copies, n_copies * plane_bytes / 1e6),
-                   'timing': 'CUDA events on the context stream around K synchronous steps (max over ranks); '
-                             'wall clock %.4f ms/step' % (wall / K * 1e3),
+                   'calls_in_flight': n_lanes,
+                   'timing': 'CUDA events around K steps with %d calls in flight, one context each '
+                             '(max over ranks); wall clock %.4f ms/step' % (n_lanes, wall / K * 1e3),
                    'gpu': info['name'], 'sms': info['sm_count'], 'scale': args.scale},
         'hits_per_step': acc['hits'] / K, 'dimers_per_step': acc['dimers'] / K,
         'candidates_per_step': acc['cand'] / K,
-        'ms_scan_kernels': acc['ms_scan'] / K, 'ms_dg_kernels': acc['ms_dg'] / K,
-        'dg_hits_per_s': (acc['hits'] / K) / (acc['ms_dg'] / K * 1e-3) if acc['ms_dg'] > 0 else None,
+        'ms_scan_kernels': seq['ms_scan'] / K, 'ms_dg_kernels': seq['ms_dg'] / K,
+        'dg_hits_per_s': (seq['hits'] / K) / (seq['ms_dg'] / K * 1e-3) if seq['ms_dg'] > 0 else None,
         'gpu_launches': acc['launches'],
+        'sequential': {'ms_per_step': seq_elapsed / K * 1e3, 'value': world * bp * n_var / (seq_elapsed / K),
+                       'note': 'the same K steps with one call in flight (per-call latency); the kernel '
+                               'durations of the roofline are taken here'},
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': int(sum(n for _, n in srcs)),
                 'd2h_bytes_per_step': int(d2h), 'ms_per_step': e2e_elapsed / e2e_steps * 1e3,
+                'workers': n_lanes,
                 'path': 'pinned host ASCII -> dp_template_from_records (H2D + pack) -> '
                         'SearchEngine.find_duplexes (= find without the shelf file) per primer -> host arrays'},
         'roofline': roofline, 'int_roofline': int_roofline, 'clocks': clocks,
@@ -460,10 +509,16 @@ def run_ours(args):
 
 def main():
     args = parse_args()
+    # ONE JSON line on stdout: libraries that chat on fd 1 (NCCL prints its version there on
+    # some boxes) are sent to stderr for the duration of the run
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, 'w')
     if args.impl == 'reference':
         run_reference(args)
     else:
         run_ours(args)
+    sys.stdout.flush()
 
 
 if __name__ == '__main__':

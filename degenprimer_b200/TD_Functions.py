@@ -82,6 +82,15 @@ def _ctx():
     return ctx
 
 
+def new_context(device=None):
+    """A further native context on a device (own stream, workspaces and result buffers) with
+    the current NN tables loaded: one per call that is to be in flight on the GPU at the same
+    time, or one per worker thread.  Templates may be shared between the contexts of a device."""
+    ctx = nat.Context(nat.default_device() if device is None else device)
+    ctx.load_tables(UnifiedNN.device_tables(), key=UnifiedNN._version)
+    return ctx
+
+
 def primer_template_Tr(sequence, concentration, conversion_degree):
     """TD_Functions.py:60-98, two-state model, on the device."""
     if not (0 < conversion_degree < 1):

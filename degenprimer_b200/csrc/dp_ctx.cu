@@ -185,6 +185,7 @@ dp_ctx* dp_create(int device_ordinal) {
   ctx->pending_free = nullptr;
   ctx->wire = nullptr;
   ctx->wire_bytes = 0;
+  ctx->timing = true;
   ctx->comm_world = ctx->comm_rank = 0;
   ctx->comm_seq = 0;
   for (int i = 0; i < 2; ++i) {

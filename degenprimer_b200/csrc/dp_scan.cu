@@ -15,12 +15,24 @@
 //   -> counters + a small speculative prefix of the results to pinned memory
 //   -> ONE stream synchronise (a second copy only when the results are large).
 #include <algorithm>
+#include <memory>
 #include <stdlib.h>
 #include <string.h>
 
 #include "dp_scan.cuh"
 #include "dp_scan_bitslice.cuh"
 #include "dp_jit.cuh"
+
+// per-kernel timing of a call (six event records + four elapsed-time queries, ~15 us of
+// host time) can be switched off per context: dp_set_timing
+#define DP_EVENT(ctx, ev, st)                                         \
+  do {                                                                \
+    if ((ctx)->timing) DP_CUDA(ctx, cudaEventRecord((ctx)->ev, st));  \
+  } while (0)
+static inline void dp_elapsed(dp_ctx* ctx, float* ms, cudaEvent_t a, cudaEvent_t b) {
+  *ms = 0.f;
+  if (ctx->timing) cudaEventElapsedTime(ms, a, b);
+}
 
 // ---- kernel 1: every window, XOR/AND-style mask select + popcount ---------------
 // One thread owns one plane word = 32 consecutive window starts; windows that
@@ -294,11 +306,17 @@ static int build_patterns(dp_ctx* ctx, uint32_t n_primers, const char* const* ma
 }
 
 // ---- host: one scan job -------------------------------------------------------------
-struct dp_scan_job {
+// the part of a job that only depends on the primer arguments: shared between the cache and
+// the calls that use it (copying a job is then a few words, not vectors and source texts)
+struct dp_job_core {
   std::vector<dp_pattern> pats;
   std::vector<std::vector<uint8_t>> letters;
   dp_bitslice_plan plan;
   std::vector<dp_jit_unit> jit;     // the same plan as run-time specialised kernels (dp_jit.cu)
+};
+
+struct dp_scan_job {
+  std::shared_ptr<dp_job_core> core;
   bool jit_ready;                   // every unit has a compiled kernel
   int used_algo;
   int NW;
@@ -309,8 +327,8 @@ struct dp_scan_job {
 
 // Finds (compile = false) or makes (compile = true) the specialised kernels of a job.
 static int jit_attach(dp_ctx* ctx, dp_scan_job& J, bool compile) {
-  J.jit_ready = !J.jit.empty();
-  for (dp_jit_unit& u : J.jit) {
+  J.jit_ready = !J.core->jit.empty();
+  for (dp_jit_unit& u : J.core->jit) {
     if (!u.kernel || !u.kernel->fn) {
       if (compile) {
         int rc = dp_jit_compile(ctx, u.source, &u.kernel);
@@ -331,29 +349,30 @@ static int jit_attach(dp_ctx* ctx, dp_scan_job& J, bool compile) {
 static int job_build(dp_ctx* ctx, uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
                      int strand_mask, int algo, const uint32_t* var_count, dp_scan_job& J,
                      bool compile = false) {
-  int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.pats, J.letters);
+  J.core = std::make_shared<dp_job_core>();
+  int rc = build_patterns(ctx, n_primers, masters, max_mismatches, strand_mask, var_count, J.core->pats, J.core->letters);
   if (rc) return rc;
   J.max_len = 0;
-  for (auto& p : J.pats) J.max_len = std::max<uint32_t>(J.max_len, p.len);
-  const uint32_t n_pat = (uint32_t)J.pats.size();
+  for (auto& p : J.core->pats) J.max_len = std::max<uint32_t>(J.max_len, p.len);
+  const uint32_t n_pat = (uint32_t)J.core->pats.size();
   J.pmask_all[0] = J.pmask_all[1] = 0;
   for (uint32_t p = 0; p < n_pat; ++p) J.pmask_all[p >> 6] |= 1ull << (p & 63);
   J.used_algo = DP_ALGO_POPC;
-  J.jit.clear();
+  J.core->jit.clear();
   J.jit_ready = false;
   if (algo != DP_ALGO_POPC) {
-    if (dp_bitslice_make_plan(J.pats, J.letters, J.plan)) J.used_algo = DP_ALGO_BITSLICE;
+    if (dp_bitslice_make_plan(J.core->pats, J.core->letters, J.core->plan)) J.used_algo = DP_ALGO_BITSLICE;
   }
   if (J.used_algo == DP_ALGO_BITSLICE && algo != DP_ALGO_BITSLICE) {
     std::vector<dp_jit_entry> entries;
-    for (const dp_bitslice_group& g : J.plan.groups)
+    for (const dp_bitslice_group& g : J.core->plan.groups)
       for (const dp_bs_pattern& bp : g.pats) entries.push_back(dp_jit_entry{bp.pattern, bp.anchor, g.K});
     std::sort(entries.begin(), entries.end(), [](const dp_jit_entry& a, const dp_jit_entry& b) { return a.pattern < b.pattern; });
     // with many patterns the generic kernel wins: it fetches a term's plane with an LDS,
     // the specialised one computes it with a LOP3 on the integer pipe that bounds both
     // (20-plex, K = 3: 13.7 ms against 15.3 ms), so AUTO leaves those to the generic kernel
     if (algo == DP_ALGO_JIT || entries.size() <= DP_JIT_AUTO_MAX_PATTERNS) {
-      dp_jit_make_units(J.pats, J.letters, entries, J.jit);
+      dp_jit_make_units(J.core->pats, J.core->letters, entries, J.core->jit);
       rc = jit_attach(ctx, J, compile || algo == DP_ALGO_JIT);
       if (rc) return rc;
     }
@@ -393,7 +412,7 @@ static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, c
   for (cache_entry& e : cache)
     if (e.key == key) hit = &e;
   if (hit) {
-    if (!hit->job.jit_ready && !hit->job.jit.empty()) jit_attach(ctx, hit->job, false);   // prepared since?
+    if (!hit->job.jit_ready && !hit->job.core->jit.empty()) jit_attach(ctx, hit->job, false);   // prepared since?
     hit->used = ++cache_clock;
     J = hit->job;
   } else {
@@ -418,7 +437,7 @@ static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, c
   A.lo = t->d_lo; A.hi = t->d_hi; A.exc = t->d_exc;
   A.rec_start = t->d_rec_start; A.rec_len = t->d_rec_len;
   A.n_records = (uint32_t)t->records.size();
-  A.n_patterns = (uint32_t)J.pats.size();
+  A.n_patterns = (uint32_t)J.core->pats.size();
   A.n_words = t->n_words;
   if (seg_end > t->n_words * 32) seg_end = t->n_words * 32;
   if (seg_begin > seg_end) seg_begin = seg_end;
@@ -442,7 +461,7 @@ static void fill_set(dp_pattern_set<NP>& PS, const std::vector<dp_pattern>& pats
 template <int NP>
 static int launch_popc(dp_ctx* ctx, const dp_scan_job& J, const uint64_t mask[2]) {
   static thread_local dp_pattern_set<NP> PS;     // up to 12 KB: keep it off the stack
-  fill_set(PS, J.pats);
+  fill_set(PS, J.core->pats);
   const uint64_t n_words = J.A.word_end - J.A.word_begin;
   unsigned blocks = (unsigned)std::min<uint64_t>((n_words + 255) / 256, (uint64_t)ctx->sm_count * 8);
   if (J.NW == 1) dp_scan_popc_kernel<1, NP><<<blocks, 256, 0, ctx->stream>>>(J.A, PS, mask[0], mask[1]);
@@ -454,7 +473,7 @@ static int launch_popc(dp_ctx* ctx, const dp_scan_job& J, const uint64_t mask[2]
 template <int NP>
 static int launch_runs(dp_ctx* ctx, const dp_scan_job& J, const uint64_t mask[2], uint32_t left, uint32_t emax) {
   static thread_local dp_pattern_set<NP> PS;
-  fill_set(PS, J.pats);
+  fill_set(PS, J.core->pats);
   const uint64_t n = J.A.n_runs * (uint64_t)(left + emax);
   dp_scan_runs_kernel<NP><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(J.A, PS, mask[0], mask[1], left, emax);
   DP_CUDA(ctx, cudaGetLastError());
@@ -467,46 +486,46 @@ static int scan_enqueue(dp_ctx* ctx, dp_scan_job& J, uint32_t* launches) {
   dp_scan_args& A = J.A;
   A.hits = ctx->d_hits;
   A.hits_cap = ctx->hits_cap;
-  for (size_t p = 0; p < J.pats.size(); ++p) {
-    ctx->last_plan.pat_len[p] = (uint8_t)J.pats[p].len;
-    ctx->last_plan.pat_strand[p] = J.pats[p].strand;
-    ctx->last_plan.pat_primer[p] = (uint8_t)J.pats[p].primer;
+  for (size_t p = 0; p < J.core->pats.size(); ++p) {
+    ctx->last_plan.pat_len[p] = (uint8_t)J.core->pats[p].len;
+    ctx->last_plan.pat_strand[p] = J.core->pats[p].strand;
+    ctx->last_plan.pat_primer[p] = (uint8_t)J.core->pats[p].primer;
   }
   if (!ctx->counters_clean)
     DP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
   ctx->counters_clean = false;
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  const bool small = J.pats.size() <= DP_NP_SMALL;
+  DP_EVENT(ctx, ev1, ctx->stream);
+  const bool small = J.core->pats.size() <= DP_NP_SMALL;
   const uint64_t n_scan_words = A.word_end - A.word_begin;
   int rc = DP_OK;
   if (n_scan_words) {
     if (J.used_algo == DP_ALGO_BITSLICE) {
       if (J.jit_ready) {
-        for (const dp_jit_unit& u : J.jit) {
-          rc = dp_jit_launch(ctx, A, J.pats, u);
+        for (const dp_jit_unit& u : J.core->jit) {
+          rc = dp_jit_launch(ctx, A, J.core->pats, u);
           if (rc) return rc;
           ++*launches;
         }
       } else {
-        rc = dp_bitslice_launch(ctx, A, J.pats, J.plan, launches);
+        rc = dp_bitslice_launch(ctx, A, J.core->pats, J.core->plan, launches);
         if (rc) return rc;
       }
-      DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
+      DP_EVENT(ctx, ev3, ctx->stream);
       if (A.n_runs) {
         // windows touching non-ACGT bases, for the prefiltered patterns
         uint32_t left = 0, emax = 0;
-        for (size_t p = 0; p < J.pats.size(); ++p) {
-          if (!((J.plan.pmask[p >> 6] >> (p & 63)) & 1ull)) continue;
-          left = std::max<uint32_t>(left, J.pats[p].len - 1u);
-          emax = std::max<uint32_t>(emax, (3u * J.pats[p].len - J.pats[p].thr3) / 2u);
+        for (size_t p = 0; p < J.core->pats.size(); ++p) {
+          if (!((J.core->plan.pmask[p >> 6] >> (p & 63)) & 1ull)) continue;
+          left = std::max<uint32_t>(left, J.core->pats[p].len - 1u);
+          emax = std::max<uint32_t>(emax, (3u * J.core->pats[p].len - J.core->pats[p].thr3) / 2u);
         }
         emax = std::max<uint32_t>(1u, std::min<uint32_t>(emax, J.max_len));
-        rc = small ? launch_runs<DP_NP_SMALL>(ctx, J, J.plan.pmask, left, emax)
-                   : launch_runs<DP_MAX_PATTERNS>(ctx, J, J.plan.pmask, left, emax);
+        rc = small ? launch_runs<DP_NP_SMALL>(ctx, J, J.core->plan.pmask, left, emax)
+                   : launch_runs<DP_MAX_PATTERNS>(ctx, J, J.core->plan.pmask, left, emax);
         if (rc) return rc;
         ++*launches;
       }
-      uint64_t rest[2] = {J.pmask_all[0] & ~J.plan.pmask[0], J.pmask_all[1] & ~J.plan.pmask[1]};
+      uint64_t rest[2] = {J.pmask_all[0] & ~J.core->plan.pmask[0], J.pmask_all[1] & ~J.core->plan.pmask[1]};
       if (rest[0] | rest[1]) {
         rc = small ? launch_popc<DP_NP_SMALL>(ctx, J, rest) : launch_popc<DP_MAX_PATTERNS>(ctx, J, rest);
         if (rc) return rc;
@@ -516,12 +535,12 @@ static int scan_enqueue(dp_ctx* ctx, dp_scan_job& J, uint32_t* launches) {
       rc = small ? launch_popc<DP_NP_SMALL>(ctx, J, J.pmask_all) : launch_popc<DP_MAX_PATTERNS>(ctx, J, J.pmask_all);
       if (rc) return rc;
       ++*launches;
-      DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
+      DP_EVENT(ctx, ev3, ctx->stream);
     }
   } else {
-    DP_CUDA(ctx, cudaEventRecord(ctx->ev3, ctx->stream));
+    DP_EVENT(ctx, ev3, ctx->stream);
   }
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev2, ctx->stream));
+  DP_EVENT(ctx, ev2, ctx->stream);
   return DP_OK;
 }
 
@@ -568,7 +587,7 @@ static int publish_enqueue(dp_ctx* ctx, bool with_dg, bool exchange = false) {
   P.n_records = ctx->last_n_records;
   dp_publish_kernel<<<1, 1024, 0, st>>>(P);
   DP_CUDA(ctx, cudaGetLastError());
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev5, st));
+  DP_EVENT(ctx, ev5, st);
   return DP_OK;
 }
 
@@ -645,7 +664,7 @@ static int hits_to_abi(dp_ctx* ctx, const dp_template* t, const dp_scan_job& J, 
   std::vector<dp_hit> tmp(n);
   for (uint64_t i = 0; i < n; ++i) {
     const dp_raw_hit& h = raw[i];
-    const dp_pattern& P = J.pats[h.pattern];
+    const dp_pattern& P = J.core->pats[h.pattern];
     const dp_record& rec = t->records[h.record];
     uint64_t off = h.g - rec.start;
     tmp[i].pos = P.strand ? rec.len - P.len - off : off;
@@ -765,7 +784,7 @@ static int dimers_large(dp_ctx* ctx, const dp_dg_plan& plan, const std::vector<u
 
 static uint64_t count_windows(const dp_template* t, const dp_scan_job& J) {
   uint64_t windows = 0;
-  for (auto& p : J.pats)
+  for (auto& p : J.core->pats)
     for (auto& rec : t->records)
       if (rec.len >= p.len) windows += rec.len - p.len + 1;
   return windows;
@@ -814,7 +833,7 @@ static void fill_scan_stats(dp_ctx* ctx, const dp_template* t, const dp_scan_job
   stats->ms_scan = ms_scan;
   stats->ms_main = ms_main;
   float ms_total = 0.f;
-  cudaEventElapsedTime(&ms_total, ctx->ev0, ctx->ev5);
+  dp_elapsed(ctx, &ms_total, ctx->ev0, ctx->ev5);
   stats->ms_total = ms_total;
   stats->launches = launches;
   stats->algo = (uint32_t)(J.used_algo == DP_ALGO_BITSLICE && J.jit_ready ? DP_ALGO_JIT : J.used_algo);
@@ -860,13 +879,13 @@ static int pipeline_enqueue(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, c
     hc[DP_C_CAND] = P.S.cand;
     DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, ctx->stream));
     ctx->counters_clean = false;
-    DP_CUDA(ctx, cudaEventRecord(ctx->ev2, ctx->stream));
+    DP_EVENT(ctx, ev2, ctx->stream);
   }
   if (dg) {
     rc = dp_dg_enqueue(ctx, t, *dg, 0, &P.dg_launches);
     if (rc) return rc;
   }
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev4, ctx->stream));
+  DP_EVENT(ctx, ev4, ctx->stream);
   // multi-GPU: the first attempt of a call carries the exchange (a re-run after an overflow
   // must not: every rank exchanges exactly once per call)
   return publish_enqueue(ctx, dg != nullptr, !P.overflowed);
@@ -881,10 +900,10 @@ static int pipeline_wait(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, cons
     if (rc) return rc;
     float ms = 0.f;
     if (P.need_scan) {
-      cudaEventElapsedTime(&ms, ctx->ev1, ctx->ev2); P.ms_scan += ms;
-      cudaEventElapsedTime(&P.ms_main, ctx->ev1, ctx->ev3);
+      dp_elapsed(ctx, &ms, ctx->ev1, ctx->ev2); P.ms_scan += ms;
+      dp_elapsed(ctx, &P.ms_main, ctx->ev1, ctx->ev3);
     }
-    if (dg) { cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev4); P.ms_dg += ms; }
+    if (dg) { dp_elapsed(ctx, &ms, ctx->ev2, ctx->ev4); P.ms_dg += ms; }
     if (S.saturated)
       return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "more than 4e9 hits or duplexes in one call: lower max_mismatches or split the template");
     bool again = false;
@@ -930,7 +949,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, nullptr, J);
   if (rc) return rc;
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  DP_EVENT(ctx, ev0, ctx->stream);
   dp_sizes S;
   dp_host_results R;
   dp_pipeline_state P;
@@ -975,7 +994,7 @@ extern "C" int dp_find_begin(dp_ctx* ctx, const dp_template* t, uint32_t n_prime
   int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, var_count, F.J);
   if (rc) return rc;
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  DP_EVENT(ctx, ev0, ctx->stream);
   // variants of every primer, as plane codes
   uint64_t var_bytes = 0;
   for (uint32_t p = 0; p < n_primers; ++p) {
@@ -987,10 +1006,10 @@ extern "C" int dp_find_begin(dp_ctx* ctx, const dp_template* t, uint32_t n_prime
   rc = upload_codes(ctx, variants, var_bytes);
   if (rc) return rc;
   fill_dg_launch(ctx, cond, F.DL);
-  for (size_t p = 0; p < F.J.pats.size(); ++p) {
-    F.DL.plan.pat_len[p] = (uint8_t)F.J.pats[p].len;
-    F.DL.plan.pat_strand[p] = F.J.pats[p].strand;
-    F.DL.plan.pat_primer[p] = (uint8_t)F.J.pats[p].primer;
+  for (size_t p = 0; p < F.J.core->pats.size(); ++p) {
+    F.DL.plan.pat_len[p] = (uint8_t)F.J.core->pats[p].len;
+    F.DL.plan.pat_strand[p] = F.J.core->pats[p].strand;
+    F.DL.plan.pat_primer[p] = (uint8_t)F.J.core->pats[p].primer;
   }
   for (uint32_t p = 0; p < n_primers; ++p) {
     F.DL.plan.var_count[p] = var_count[p];
@@ -1042,7 +1061,7 @@ extern "C" int dp_find_end(dp_ctx* ctx, dp_hit** hits_out, uint64_t* n_hits_out,
     dg_stats->dimers_tried = S.tried;
     dg_stats->dimers_kept = *n_dimers_out;
     dg_stats->ms_kernel = F.P.ms_dg;
-    cudaEventElapsedTime(&dg_stats->ms_total, ctx->ev2, ctx->ev5);
+    dp_elapsed(ctx, &dg_stats->ms_total, ctx->ev2, ctx->ev5);
     dg_stats->launches = F.P.dg_launches;
   }
   return DP_OK;
@@ -1066,6 +1085,12 @@ extern "C" int dp_find(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   return dp_find_end(ctx, hits_out, n_hits_out, dimers_out, n_dimers_out, stats, dg_stats);
 }
 
+extern "C" int dp_set_timing(dp_ctx* ctx, int on) {
+  if (!ctx) return DP_ERR_ARG;
+  ctx->timing = on != 0;
+  return DP_OK;
+}
+
 extern "C" int dp_scan_prepare_kernels(dp_ctx* ctx, uint32_t n_primers, const char* const* masters,
                                        const int32_t* max_mismatches, int strand_mask) {
   if (!ctx || !masters) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
@@ -1083,20 +1108,21 @@ extern "C" int dp_scan_prepare_kernels(dp_ctx* ctx, uint32_t n_primers, const ch
 extern "C" int dp_jit_selftest(uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
                                int strand_mask, const char* source_path, const char* cubin_path) {
   dp_scan_job J;
-  int rc = build_patterns(nullptr, n_primers, masters, max_mismatches, strand_mask, nullptr, J.pats, J.letters);
+  J.core = std::make_shared<dp_job_core>();
+  int rc = build_patterns(nullptr, n_primers, masters, max_mismatches, strand_mask, nullptr, J.core->pats, J.core->letters);
   if (rc) return rc;
-  if (!dp_bitslice_make_plan(J.pats, J.letters, J.plan)) return 0;
+  if (!dp_bitslice_make_plan(J.core->pats, J.core->letters, J.core->plan)) return 0;
   std::vector<dp_jit_entry> entries;
-  for (const dp_bitslice_group& g : J.plan.groups)
+  for (const dp_bitslice_group& g : J.core->plan.groups)
     for (const dp_bs_pattern& bp : g.pats) entries.push_back(dp_jit_entry{bp.pattern, bp.anchor, g.K});
   std::sort(entries.begin(), entries.end(), [](const dp_jit_entry& a, const dp_jit_entry& b) { return a.pattern < b.pattern; });
-  dp_jit_make_units(J.pats, J.letters, entries, J.jit);
-  for (size_t i = 0; i < J.jit.size(); ++i) {
+  dp_jit_make_units(J.core->pats, J.core->letters, entries, J.core->jit);
+  for (size_t i = 0; i < J.core->jit.size(); ++i) {
     std::string log;
-    std::string cubin = dp_jit_compile_only(J.jit[i].source, log);
+    std::string cubin = dp_jit_compile_only(J.core->jit[i].source, log);
     if (i == 0 && source_path) {
       FILE* f = fopen(source_path, "wb");
-      if (f) { fwrite(J.jit[i].source.data(), 1, J.jit[i].source.size(), f); fclose(f); }
+      if (f) { fwrite(J.core->jit[i].source.data(), 1, J.core->jit[i].source.size(), f); fclose(f); }
     }
     if (cubin.empty()) return dp_set_error(nullptr, DP_ERR_STATE, "%s", log.c_str());
     if (i == 0 && cubin_path) {
@@ -1104,7 +1130,7 @@ extern "C" int dp_jit_selftest(uint32_t n_primers, const char* const* masters, c
       if (f) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
     }
   }
-  return (int)J.jit.size();
+  return (int)J.core->jit.size();
 }
 
 extern "C" int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes) {
@@ -1135,7 +1161,7 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
   if (n_hits > 0xF0000000ull) return dp_set_error(ctx, DP_ERR_ARG, "more than 4e9 hits in one call");
   if (n_primers > DP_MAX_PRIMERS) return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
-  DP_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  DP_EVENT(ctx, ev0, ctx->stream);
   uint64_t var_bytes = 0;
   for (uint32_t p = 0; p < n_primers; ++p) {
     if (primer_len[p] == 0 || primer_len[p] > DP_MAX_PRIMER_LEN)
@@ -1196,15 +1222,15 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
     if (attempt == 4) return dp_set_error(ctx, DP_ERR_STATE, "internal: dimer buffer keeps overflowing");
     DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
     ctx->counters_clean = false;
-    DP_CUDA(ctx, cudaEventRecord(ctx->ev2, st));
+    DP_EVENT(ctx, ev2, st);
     rc = dp_dg_enqueue(ctx, t, DL, pairs, &launches);
     if (rc) return rc;
-    DP_CUDA(ctx, cudaEventRecord(ctx->ev4, st));
+    DP_EVENT(ctx, ev4, st);
     // only directory + dimers are wanted back; the hit prefix copy is harmless
     rc = fetch_sizes(ctx, true, S);
     if (rc) return rc;
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev4);
+    dp_elapsed(ctx, &ms, ctx->ev2, ctx->ev4);
     ms_dg += ms;
     if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
     if (S.n_dimers > ctx->dimers_cap) {
@@ -1233,7 +1259,7 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
     stats->dimers_tried = S.tried;
     stats->dimers_kept = *n_dimers_out;
     stats->ms_kernel = ms_dg;
-    cudaEventElapsedTime(&stats->ms_total, ctx->ev0, ctx->ev5);
+    dp_elapsed(ctx, &stats->ms_total, ctx->ev0, ctx->ev5);
     stats->launches = launches;
   }
   return DP_OK;

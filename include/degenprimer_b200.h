@@ -157,6 +157,11 @@ typedef struct dp_scan_stats {
   uint32_t algo;           /* DP_ALGO_* actually used                            */
 } dp_scan_stats;
 
+/* Per-kernel timing of every call (the ms_* fields of the stats: six CUDA event
+ * records and four elapsed-time queries, ~15 us of host time per call).  On by
+ * default; a throughput loop that does not read the ms_* fields switches it off. */
+int dp_set_timing(dp_ctx* ctx, int on);
+
 /* Compiles (NVRTC, ~0.2-0.5 s once per process and pattern set) the scan kernel
  * specialised for these primers; later dp_scan / dp_find calls with the same
  * masters, mismatch limits and strand mask use it under DP_ALGO_AUTO.  Call it
