@@ -46,7 +46,9 @@ def parse_args():
     ap.add_argument('--algo', type=int, default=0, help='0 auto, 1 popcount, 2 bit-slice')
     ap.add_argument('--cpu-sample-bp', type=int, default=12_000_000)
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--in-flight', type=int, default=2,
+    ap.add_argument('--no-jit', action='store_true', help='generic scan kernel instead of the run-time specialised one')
+    ap.add_argument('--host-threads', type=int, default=2, help='host threads that queue and collect the calls')
+    ap.add_argument('--in-flight', type=int, default=4,
                     help='calls in flight on the GPU (one context per call); 1 = strictly sequential')
     return ap.parse_args()
 
@@ -268,7 +270,9 @@ def run_ours(args):
     # overlaps the kernels of the other lane's call; templates are shared between the lanes.
     n_lanes = max(1, args.in_flight)
     lanes = [ctx] + [tdf.new_context(local) for _ in range(n_lanes - 1)]
-    queries = [c.prepare(primers, k, var_lists) for c in lanes]      # the primer side, laid out once
+    # the primer side, laid out once; a throughput loop over one query is what the run-time
+    # specialised scan kernel is for (compiled here, ~0.3 s, outside every timed region)
+    queries = [c.prepare(primers, k, var_lists, jit=not args.no_jit) for c in lanes]
     exchs = [None] * n_lanes
     if world > 1:
         # the hit gather is the epilogue of the publish kernel: each rank stores its slot into
@@ -297,35 +301,31 @@ def run_ours(args):
     # ends every lane has been waited for, so the closing event is later than all work)
     kstream = torch.cuda.ExternalStream(ctx.stream, device=torch.device('cuda', local))
 
-    def timed_region(K, F, first_call):
-        """K steps with F calls in flight (F = 1: strictly one after the other).  A step = one
-        pass of the hot path: scan of every primer over both strands + dG of every (hit,
-        variant), one stream submission (dp_find), results back on the host."""
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        acc = dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, dimers=0, cand=0, windows=0, algo=0)
+    def drive(my, n_steps, first_call, acc):
+        """n_steps steps on the lanes `my` (indices), one call in flight per lane, from one
+        host thread.  A step = one pass of the hot path: scan of every primer over both
+        strands + dG of every (hit, variant), one stream submission (dp_find), results back
+        on the host."""
+        F = len(my)
         made = [0] * F                          # calls of this region queued on a lane
         own = [[None, None] for _ in range(F)]  # a lane's own hits of its last two calls
 
         def begin(i):
-            lane = i % F
-            lanes[lane].find_begin(copies[(first_call + i) % n_copies], queries[lane], cond, algo=args.algo)
-            made[lane] += 1
+            j = i % F
+            lanes[my[j]].find_begin(copies[(first_call + i) % n_copies], queries[my[j]], cond, algo=args.algo)
+            made[j] += 1
 
-        for c in lanes:
-            c.set_timing(F == 1)               # the ms_* stats are only read in the sequential region
-        sync_all()
-        t0 = time.perf_counter()
-        ev0.record(kstream)
-        for i in range(min(F - 1, K)):
+        for i in range(min(F - 1, n_steps)):
             begin(i)
-        for i in range(K):
-            if i + F - 1 < K:
+        for i in range(n_steps):
+            if i + F - 1 < n_steps:
                 begin(i + F - 1)
-            lane = i % F
-            if exchs[lane] is not None and made[lane] >= 3:
-                acc['hits'] += len(gathered(lane, 2, own[lane][0]))
+            j = i % F
+            lane = my[j]
+            if exchs[lane] is not None and made[j] >= 3:
+                acc['hits'] += len(gathered(lane, 2, own[j][0]))
             hits, dimers, st, dst = lanes[lane].find_end()
-            own[lane] = [own[lane][1], hits]
+            own[j] = [own[j][1], hits]
             if exchs[lane] is None:
                 acc['hits'] += len(hits)
             acc['ms_main'] += st['ms_main']
@@ -336,13 +336,48 @@ def run_ours(args):
             acc['cand'] += st['candidates']
             acc['windows'] = st['windows']
             acc['algo'] = st['algo']
-        for lane in range(F):
+        for j in range(F):
+            lane = my[j]
             if exchs[lane] is not None:
-                if made[lane] >= 2:
-                    acc['hits'] += len(gathered(lane, 1, own[lane][0]))
-                if made[lane] >= 1:
-                    acc['hits'] += len(gathered(lane, 0, own[lane][1]))
+                if made[j] >= 2:
+                    acc['hits'] += len(gathered(lane, 1, own[j][0]))
+                if made[j] >= 1:
+                    acc['hits'] += len(gathered(lane, 0, own[j][1]))
+
+    def timed_region(K, F, T, first_call):
+        """K steps with F calls in flight (one per lane), queued and collected by T host threads
+        (F = T = 1: strictly one call after the other on the main thread).  Step i of the
+        region belongs to thread i % T, so every rank makes the same calls on the same lane."""
+        import threading
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        T = max(1, min(T, F))
+        accs = [dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, dimers=0, cand=0, windows=0, algo=0)
+                for _ in range(T)]
+        shares = [K // T + (1 if t < K % T else 0) for t in range(T)]
+        firsts = [first_call + sum(shares[:t]) for t in range(T)]
+        groups = [list(range(t, F, T)) for t in range(T)]
+        for c in lanes:
+            c.set_timing(F == 1)               # the ms_* stats are only read in the sequential region
+        errors = []
+
+        def work(t):
+            try:
+                drive(groups[t], shares[t], firsts[t], accs[t])
+            except BaseException as e:          # noqa: surfaced on the main thread below
+                errors.append(e)
+
+        sync_all()
+        t0 = time.perf_counter()
+        ev0.record(kstream)
+        threads = [threading.Thread(target=work, args=(t,)) for t in range(1, T)]
+        for th in threads:
+            th.start()
+        work(0)
+        for th in threads:
+            th.join()
         ev1.record(kstream)
+        if errors:
+            raise errors[0]
         sync_all()
         wall = time.perf_counter() - t0
         elapsed = ev0.elapsed_time(ev1) * 1e-3        # device clock, first launch -> last result on the host
@@ -350,21 +385,26 @@ def run_ours(args):
             tt = torch.tensor([elapsed, wall], dtype=torch.float64, device='cuda')
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             elapsed, wall = float(tt[0].item()), float(tt[1].item())
+        acc = accs[0]
+        for o in accs[1:]:
+            for key in ('ms_main', 'ms_scan', 'ms_dg', 'launches', 'hits', 'dimers', 'cand'):
+                acc[key] += o[key]
         return elapsed, wall, acc
 
     K = max(1, args.steps)
     W = max(3, args.warmup)
-    timed_region(W, n_lanes, 0)                     # warm-up, untimed
+    n_threads = max(1, min(args.host_threads, n_lanes))
+    timed_region(max(W, 3 * n_lanes), n_lanes, n_threads, 0)      # warm-up, untimed (every lane, every thread)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     # (1) the headline: K steps, n_lanes calls in flight
-    elapsed, wall, acc = timed_region(K, n_lanes, W)
+    elapsed, wall, acc = timed_region(K, n_lanes, n_threads, W)
     ms_step = elapsed / K * 1e3
     value = world * bp * n_var / (elapsed / K)
     # (2) the same K steps strictly one after the other: per-call latency, and kernel durations
     #     that are not stretched by the other lane's kernels (the roofline below uses these)
-    seq_elapsed, seq_wall, seq = timed_region(K, 1, W + K)
+    seq_elapsed, seq_wall, seq = timed_region(K, 1, 1, W + K)
     for ex in exchs:
         if ex is not None:
             ex.close()          # the e2e leg below runs the ranks independently
@@ -380,11 +420,13 @@ def run_ours(args):
         g = Primer(SeqRecord(Seq(p), id='primer%d' % i), 1.5e-6)
         g.generate_components()
         gprimers.append(g)
-    # one worker thread per lane, each with its own context and SearchEngine: while one worker's
-    # template is on its way over PCIe the other one's is being scanned (ctypes drops the GIL)
+    # two worker threads, each with its own context and SearchEngine: while one worker's
+    # template is on its way over PCIe the other one's is being scanned (ctypes drops the GIL);
+    # the leg is PCIe bound (83 MB per step), more workers do not help
     import threading
-    engines = [SearchEngine() for _ in lanes]
-    d2h_last = [0] * n_lanes
+    n_workers = min(2, n_lanes)
+    engines = [SearchEngine() for _ in range(n_workers)]
+    d2h_last = [0] * n_workers
 
     def e2e_step(lane):
         c, se = lanes[lane], engines[lane]
@@ -399,21 +441,28 @@ def run_ours(args):
         d2h_last[lane] = d2h
 
     def e2e_run(n_steps):
+        errors = []
+
         def work(lane):
-            for i in range(lane, n_steps, n_lanes):
-                e2e_step(lane)
-        threads = [threading.Thread(target=work, args=(lane,)) for lane in range(1, n_lanes)]
+            try:
+                for i in range(lane, n_steps, n_workers):
+                    e2e_step(lane)
+            except BaseException as e:          # noqa: surfaced on the main thread below
+                errors.append(e)
+        threads = [threading.Thread(target=work, args=(lane,)) for lane in range(1, n_workers)]
         for th in threads:
             th.start()
         work(0)
         for th in threads:
             th.join()
+        if errors:
+            raise errors[0]
 
-    for lane in range(n_lanes):
+    for lane in range(n_workers):
         e2e_step(lane)
-    e2e_run(2 * n_lanes)
+    e2e_run(2 * n_workers)
     sync_all()
-    e2e_steps = max(4, min(args.steps, 10 * n_lanes))
+    e2e_steps = max(4, min(args.steps, 10 * n_workers))
     t0 = time.perf_counter()
     e2e_run(e2e_steps)
     sync_all()
@@ -481,9 +530,9 @@ def run_ours(args):
                    'variants': n_var, 'max_mismatches': k, 'records': len(wl['records']),
                    'l2': 'rotating %d resident copies of the template planes (%.0f MB > 126 MB L2)'
                          % (n_copies, n_copies * plane_bytes / 1e6),
-                   'calls_in_flight': n_lanes,
-                   'timing': 'CUDA events around K steps with %d calls in flight, one context each '
-                             '(max over ranks); wall clock %.4f ms/step' % (n_lanes, wall / K * 1e3),
+                   'calls_in_flight': n_lanes, 'host_threads': n_threads,
+                   'timing': 'CUDA events around K steps with %d calls in flight (one context each, %d host '
+                             'threads; max over ranks); wall clock %.4f ms/step' % (n_lanes, n_threads, wall / K * 1e3),
                    'gpu': info['name'], 'sms': info['sm_count'], 'scale': args.scale},
         'hits_per_step': acc['hits'] / K, 'dimers_per_step': acc['dimers'] / K,
         'candidates_per_step': acc['cand'] / K,
@@ -495,7 +544,7 @@ def run_ours(args):
                                'durations of the roofline are taken here'},
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': int(sum(n for _, n in srcs)),
                 'd2h_bytes_per_step': int(d2h), 'ms_per_step': e2e_elapsed / e2e_steps * 1e3,
-                'workers': n_lanes,
+                'workers': n_workers,
                 'path': 'pinned host ASCII -> dp_template_from_records (H2D + pack) -> '
                         'SearchEngine.find_duplexes (= find without the shelf file) per primer -> host arrays'},
         'roofline': roofline, 'int_roofline': int_roofline, 'clocks': clocks,

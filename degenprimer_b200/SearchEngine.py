@@ -177,11 +177,11 @@ class SearchEngine(object):
         records = primer.seq_records
         variants = [str(r.seq) for r in records]
         names = [r.id for r in records]
-        with tdf.AcquireParameters():
+        with tdf.AcquireParameters():       # the snapshot is the by-value conditions block
             cond = tdf.conditions()
             T = tdf.PCR_P.PCR_T
-            dimers, stats = tmpl.ctx.duplex_dg(tmpl, hits, [p_len], [len(variants)], [0],
-                                               ''.join(variants), cond)
+        dimers, stats = tmpl.ctx.duplex_dg(tmpl, hits, [p_len], [len(variants)], [0],
+                                           ''.join(variants), cond)
         self.last_stats['dg'] = stats
         return self._site_results(tmpl, hits, dimers, primer, t_len, p_len, variants, names, T, n_f)
 
@@ -195,10 +195,10 @@ class SearchEngine(object):
         if tmpl.n_records == 1:
             begin, end = 0, 2 ** 64 - 1
         query, variants, names = _primer_query(primer, int(mismatches))
-        with tdf.AcquireParameters():
+        with tdf.AcquireParameters():       # the snapshot is the by-value conditions block
             cond = tdf.conditions()
             T = tdf.PCR_P.PCR_T
-            hits, dimers, st, dst = tmpl.ctx.find(tmpl, query, cond=cond, seg_begin=begin, seg_end=end)
+        hits, dimers, st, dst = tmpl.ctx.find(tmpl, query, cond=cond, seg_begin=begin, seg_end=end)
         self.last_stats['scan'] = st
         self.last_stats['dg'] = dst
         if len(hits) and not (hits['record'] == rec).all():

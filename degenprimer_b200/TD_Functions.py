@@ -7,6 +7,7 @@ Host mirror of DegenPrimer/TD_Functions.py: module globals `NN`, `PCR_P`,
 Every dG / Tm is evaluated by kernels in csrc/dp_dg.cu through the C-ABI; the
 two closed-form scalar helpers at the bottom are one `exp` / one `sqrt`.
 """
+import threading
 from contextlib import contextmanager
 from copy import deepcopy
 from math import exp, nextafter, sqrt, inf, log
@@ -23,16 +24,22 @@ max_dimer_dG = -3      # DegenPrimer/SecStructures.py:30
 min_K = 100            # DegenPrimer/SecStructures.py:32
 
 
+_acquire_lock = threading.RLock()
+
+
 @contextmanager
 def AcquireParameters():
-    """Work on a private snapshot of PCR_P (TD_Functions.py:50-58)."""
+    """Work on a private snapshot of PCR_P (TD_Functions.py:50-58).  The reference runs one
+    process per worker; here worker threads share the module, so other threads wait while
+    one holds the snapshot (nesting in one thread still asserts, as in the reference)."""
     global _PCR_P, PCR_P
-    assert _PCR_P is None, 'TD_Functions: PCR parameters are already acquired.'
-    try:
-        _PCR_P, PCR_P = PCR_P, deepcopy(PCR_P)
-        yield
-    finally:
-        PCR_P, _PCR_P = _PCR_P, None
+    with _acquire_lock:
+        assert _PCR_P is None, 'TD_Functions: PCR parameters are already acquired.'
+        try:
+            _PCR_P, PCR_P = PCR_P, deepcopy(PCR_P)
+            yield
+        finally:
+            PCR_P, _PCR_P = _PCR_P, None
 
 
 def equilibrium_constant(dG_T, T):

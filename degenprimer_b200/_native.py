@@ -377,11 +377,13 @@ class Context(object):
         """The primer side of dp_find as ready-made C arrays (build once, scan many
         templates).  variants: one list of unambiguous sequences per master.
         jit: also compile the scan kernel specialised for these primers
-        (dp_scan_prepare_kernels, ~0.3 s once per process and primer set; default on,
-        DEGENPRIMER_B200_JIT=0 turns it off).  Without NVRTC the generic kernel serves."""
+        (dp_scan_prepare_kernels, ~0.3 s once per process and primer set).  It pays for
+        a query that is scanned thousands of times or over Gbp templates (a screening
+        loop); default off, DEGENPRIMER_B200_JIT=1 turns it on for every prepare().
+        Without NVRTC the generic kernel serves."""
         q = Query(masters, mismatches, variants)
         if jit is None:
-            jit = os.environ.get('DEGENPRIMER_B200_JIT', '1') != '0'
+            jit = os.environ.get('DEGENPRIMER_B200_JIT', '0') == '1'
         q.jit = False
         if jit:
             rc = self.lib.dp_scan_prepare_kernels(self._h, q.n, q.m, q.k, int(strands))

@@ -188,6 +188,10 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
   for (int r = 0; r < ctx->comm_world; ++r) {
     const uint64_t* h = (const uint64_t*)(recv + (size_t)r * slot);
     const uint64_t n = (uint32_t)h[0];
+    // the GPU wrote these lines over PCIe, so none is in a CPU cache: ask for all of them
+    // now, the misses then overlap instead of being taken one by one in the loops below
+    for (uint64_t off = 64; off < 64 + std::min(n, cap) * sizeof(dp_raw_hit); off += 64)
+      __builtin_prefetch((const char*)h + off);
     if (n > cap) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "rank %d had %llu hits, a slot holds %llu", r,
                                      (unsigned long long)n, (unsigned long long)cap);
     if (h[6] != 1) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "rank %d scanned a template of %llu records; "

@@ -629,6 +629,12 @@ static int fetch_all(dp_ctx* ctx, bool with_dg, const dp_sizes& S, dp_host_resul
     R.hits = (const dp_raw_hit*)(ctx->h_res + DP_RES_OFF_HITS);
     R.dir = (const uint64_t*)(ctx->h_res + DP_RES_OFF_DIR);
     R.dimers = (const dp_raw_dimer*)(ctx->h_res + DP_RES_OFF_DIMERS);
+    // written by the GPU over PCIe: no line is in a CPU cache, let the misses overlap
+    for (size_t off = 0; off < S.n_hits * sizeof(dp_raw_hit); off += 64) __builtin_prefetch((const char*)R.hits + off);
+    if (with_dg) {
+      for (size_t off = 0; off < S.n_pairs * sizeof(uint64_t); off += 64) __builtin_prefetch((const char*)R.dir + off);
+      for (size_t off = 0; off < S.n_dimers * sizeof(dp_raw_dimer); off += 64) __builtin_prefetch((const char*)R.dimers + off);
+    }
     return DP_OK;
   }
   const size_t b_hits = S.n_hits * sizeof(dp_raw_hit);

@@ -32,6 +32,7 @@ def main():
     ap.add_argument('--v16', action='store_true', help='config 5: the V=16 version of the 35-mer')
     ap.add_argument('--algo', type=int, default=0)
     ap.add_argument('--check-popc', action='store_true')
+    ap.add_argument('--no-jit', action='store_true')
     ap.add_argument('--check-oracle-mbp', type=float, default=0.0)
     args = ap.parse_args()
 
@@ -58,7 +59,7 @@ def main():
     t0 = time.perf_counter()
     tmpl = ctx.template_from_sequences(srcs)
     t_up = time.perf_counter() - t0
-    q = ctx.prepare(primers, k, var)
+    q = ctx.prepare(primers, k, var, jit=not args.no_jit)
     ctx.find(tmpl, q, cond=cond, algo=args.algo)
     ctx.find(tmpl, q, cond=cond, algo=args.algo)
     ms = []
