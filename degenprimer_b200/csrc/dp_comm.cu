@@ -31,6 +31,8 @@ void dp_comm_release(dp_ctx* ctx) {
     if (ctx->d_recv[b]) cudaFree(ctx->d_recv[b]);
     if (ctx->d_peer[b]) cudaFree(ctx->d_peer[b]);
     if (ctx->h_gather[b]) cudaFreeHost(ctx->h_gather[b]);
+    if (ctx->h_sorted[b]) cudaFreeHost(ctx->h_sorted[b]);
+    ctx->h_sorted[b] = nullptr;
     ctx->d_recv[b] = nullptr;
     ctx->d_peer[b] = nullptr;
     ctx->h_gather[b] = nullptr;
@@ -40,6 +42,14 @@ void dp_comm_release(dp_ctx* ctx) {
   ctx->comm_world = ctx->comm_rank = 0;
   ctx->comm_slot_bytes = 0;
   ctx->comm_seq = 0;
+}
+
+// (length, strand, primer) of the patterns of `call`, for the kernel that converts its hits
+static void fill_plan(dp_ctx* ctx, dp_exchange_args* X, uint64_t call) {
+  const dp_dg_plan& plan = ctx->comm_plan[call & 3];
+  memcpy(X->prev_len, plan.pat_len, DP_MAX_PATTERNS);
+  memcpy(X->prev_strand, plan.pat_strand, DP_MAX_PATTERNS);
+  memcpy(X->prev_primer, plan.pat_primer, DP_MAX_PATTERNS);
 }
 
 void dp_comm_fill(dp_ctx* ctx, dp_exchange_args* X) {
@@ -54,6 +64,8 @@ void dp_comm_fill(dp_ctx* ctx, dp_exchange_args* X) {
   X->peers = ctx->d_peer[c & 1];
   X->recv_prev = ctx->d_recv[(c + 1) & 1];
   X->h_prev = ctx->h_gather[(c + 1) & 1];
+  X->h_sorted = ctx->h_sorted[(c + 1) & 1];
+  if (c) fill_plan(ctx, X, c - 1);
   X->err = ctx->comm_err;
   X->rec0_len = ctx->last_rec0_len;
   X->n_records = ctx->last_n_records;
@@ -84,6 +96,8 @@ static int comm_collect(dp_ctx* ctx, int age, int* buf, uint64_t* call_out) {
     X.slot_hits = (ctx->comm_slot_bytes - 64) / sizeof(dp_raw_hit);
     X.recv_prev = ctx->d_recv[b];
     X.h_prev = ctx->h_gather[b];
+    X.h_sorted = ctx->h_sorted[b];
+    fill_plan(ctx, &X, call);
     X.err = ctx->comm_err;
     dp_exchange_drain_launch(X, ctx->stream);
     DP_CUDA(ctx, cudaGetLastError());
@@ -122,6 +136,8 @@ int dp_comm_export(dp_ctx* ctx, int world, int rank, uint32_t max_hits, char han
     DP_CUDA(ctx, cudaMemset(ctx->d_recv[b], 0, slot * world));
     DP_CUDA(ctx, cudaHostAlloc(&ctx->h_gather[b], slot * world, cudaHostAllocDefault));
     memset(ctx->h_gather[b], 0, slot * world);
+    DP_CUDA(ctx, cudaHostAlloc(&ctx->h_sorted[b], 32 + DP_EXCHANGE_SORT_MAX * sizeof(dp_hit), cudaHostAllocDefault));
+    memset(ctx->h_sorted[b], 0, 32);
     cudaIpcMemHandle_t h;
     DP_CUDA(ctx, cudaIpcGetMemHandle(&h, ctx->d_recv[b]));
     memcpy(handles + 64 * b, &h, 64);
@@ -180,6 +196,19 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
   uint64_t call = 0;
   int rc = comm_collect(ctx, age, &s, &call);
   if (rc) return rc;
+  // the kernel that brought the slots to the host has converted and sorted them already
+  // (one segment per rank, not too many hits): just take its array
+  const uint64_t* sorted = ctx->h_sorted[s];
+  const char* force = getenv("DEGENPRIMER_B200_EXCHANGE_SORT");      // "host": test hook for the path below
+  if (sorted[1] == 1 && sorted[2] == call + 1 && sorted[0] <= DP_EXCHANGE_SORT_MAX && !(force && force[0] == 'h')) {
+    const uint64_t n = sorted[0];
+    dp_hit* out = (dp_hit*)dp_result_alloc(std::max<uint64_t>(1, n) * sizeof(dp_hit));
+    if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu hits", (unsigned long long)n);
+    memcpy(out, sorted + 4, n * sizeof(dp_hit));
+    *hits_out = out;
+    *n_out = n;
+    return DP_OK;
+  }
   const char* recv = ctx->h_gather[s];
   const dp_dg_plan& plan = ctx->comm_plan[call & 3];
   const uint64_t slot = ctx->comm_slot_bytes;

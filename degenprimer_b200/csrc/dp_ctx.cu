@@ -192,6 +192,7 @@ dp_ctx* dp_create(int device_ordinal) {
     ctx->d_recv[i] = nullptr;
     ctx->d_peer[i] = nullptr;
     ctx->h_gather[i] = nullptr;
+    ctx->h_sorted[i] = nullptr;
     for (int r = 0; r < DP_MAX_RANKS; ++r) ctx->peer_mapped[i][r] = nullptr;
   }
   ctx->comm_err = nullptr;

@@ -107,6 +107,7 @@ struct dp_ctx {
   char** d_peer[2];            // device table: d_peer[b][r] = rank r's receive buffer b as seen from this GPU
   void* peer_mapped[2][DP_MAX_RANKS];   // host copy of the table (what cudaIpcOpenMemHandle returned)
   char* h_gather[2];           // pinned host copies of the receive buffers, written by the publish kernel
+  uint64_t* h_sorted[2];       // the same calls converted to dp_hit and sorted by the kernel (32-byte header first)
   unsigned long long* comm_err;         // pinned host flag (device-visible): a wait for a peer timed out
   uint64_t comm_slot_bytes;             // bytes per rank in a receive buffer: 64-byte header + raw hits
   dp_dg_plan comm_plan[4];     // (length, strand, primer) of the patterns of the last calls (call & 3)
@@ -204,7 +205,12 @@ struct dp_exchange_args {
   char* h_prev;                // pinned host copy of it
   unsigned long long* err;
   uint64_t rec0_len, n_records;
+  // converted + sorted copy of the landed call (dp_exchange_to_host): header {n, valid, seq, 0}
+  // then dp_hit records; (length, strand, primer) of that call's patterns
+  uint64_t* h_sorted;
+  uint8_t prev_len[DP_MAX_PATTERNS], prev_strand[DP_MAX_PATTERNS], prev_primer[DP_MAX_PATTERNS];
 };
+#define DP_EXCHANGE_SORT_MAX 2048     // hits of all ranks the publish kernel converts and sorts itself
 void dp_comm_fill(dp_ctx* ctx, dp_exchange_args* X);     // for the call being queued; advances the sequence
 void dp_comm_release(dp_ctx* ctx);
 void dp_exchange_drain_launch(const dp_exchange_args& X, cudaStream_t st);   // dp_scan.cu

@@ -161,20 +161,75 @@ __device__ bool dp_exchange_wait(const dp_exchange_args& X, uint64_t call) {
   return ok != 0;
 }
 
-// the slots of a call that has landed: local receive buffer -> pinned host memory
-__device__ void dp_exchange_to_host(const dp_exchange_args& X) {
+// The slots of a call that has landed: local receive buffer -> pinned host memory, raw, and
+// (one segment per rank, at most DP_EXCHANGE_SORT_MAX hits in all) also as the final result:
+// dp_hit records in reference coordinates, sorted by (primer, strand, record = sender, pos).
+// Every rank needs the hits of all ranks, so this conversion is N times the work of a rank's
+// own hits; done here it costs a few microseconds of one block instead of host time per call.
+__device__ void dp_exchange_to_host(const dp_exchange_args& X, uint64_t call) {
+  __shared__ uint64_t keys[DP_EXCHANGE_SORT_MAX];
+  __shared__ uint32_t first[DP_MAX_RANKS + 1];
+  __shared__ int sortable;
   for (int r = 0; r < X.world; ++r) {
     const volatile uint64_t* src = (const volatile uint64_t*)(X.recv_prev + r * X.slot_bytes);
     uint64_t* dst = (uint64_t*)(X.h_prev + r * X.slot_bytes);
     const uint64_t n = min((uint64_t)(uint32_t)src[DP_C_HITS], X.slot_hits);
     for (uint64_t i = threadIdx.x; i < 8 + 3 * n; i += blockDim.x) dst[i] = src[i];
   }
+  if (threadIdx.x == 0) {
+    uint32_t total = 0;
+    int ok = 1;
+    for (int r = 0; r < X.world; ++r) {
+      const volatile uint64_t* h = (const volatile uint64_t*)(X.recv_prev + r * X.slot_bytes);
+      const uint64_t n = (uint32_t)h[DP_C_HITS];
+      if (n > X.slot_hits || h[6] != 1) ok = 0;
+      first[r] = total;
+      total += (uint32_t)min(n, X.slot_hits);
+    }
+    first[X.world] = total;
+    sortable = ok && total <= DP_EXCHANGE_SORT_MAX;
+  }
+  __syncthreads();
+  if (!sortable) {
+    if (threadIdx.x == 0) { X.h_sorted[1] = 0; X.h_sorted[2] = call + 1; }
+    return;
+  }
+  const uint32_t total = first[X.world];
+  // at most two records per thread
+  uint64_t key[2] = {0, 0}, pos[2] = {0, 0};
+  uint32_t meta[2] = {0, 0};
+  for (int e = 0; e < 2; ++e) {
+    const uint32_t i = threadIdx.x + e * blockDim.x;
+    if (i >= total) break;
+    int r = 0;
+    while (i >= first[r + 1]) ++r;
+    const volatile uint64_t* h = (const volatile uint64_t*)(X.recv_prev + r * X.slot_bytes);
+    const uint64_t g = h[8 + 3 * (i - first[r])], w1 = h[8 + 3 * (i - first[r]) + 1];
+    const uint32_t pat = (uint32_t)(w1 >> 32) & 0xFFFFu, score3 = (uint32_t)(w1 >> 48);
+    const uint32_t strand = X.prev_strand[pat & (DP_MAX_PATTERNS - 1)];
+    pos[e] = strand ? h[5] - X.prev_len[pat & (DP_MAX_PATTERNS - 1)] - g : g;   // record 0 starts at padded position 0
+    key[e] = ((uint64_t)pat << 56) | ((uint64_t)r << 48) | (pos[e] & 0xFFFFFFFFFFFFull);
+    meta[e] = (uint32_t)r | ((uint32_t)X.prev_primer[pat & (DP_MAX_PATTERNS - 1)] << 8) | (strand << 16) | ((score3 & 0xFFu) << 17);
+    keys[i] = key[e];
+  }
+  __syncthreads();
+  for (int e = 0; e < 2; ++e) {
+    const uint32_t i = threadIdx.x + e * blockDim.x;
+    if (i >= total) break;
+    uint32_t rank = 0;
+    for (uint32_t j = 0; j < total; ++j) rank += keys[j] < key[e];       // keys are distinct
+    // dp_hit {pos u64; record u32; primer u16; strand u8; score3 u8}
+    X.h_sorted[4 + 2 * rank] = pos[e];
+    X.h_sorted[4 + 2 * rank + 1] = (uint64_t)(meta[e] & 0xFFu) | ((uint64_t)((meta[e] >> 8) & 0xFFu) << 32) |
+                                   ((uint64_t)((meta[e] >> 16) & 1u) << 48) | ((uint64_t)(meta[e] >> 17) << 56);
+  }
+  if (threadIdx.x == 0) { X.h_sorted[0] = total; X.h_sorted[1] = 1; X.h_sorted[2] = call + 1; }
 }
 
 // standalone drain: brings the slots of the LAST call to the host (dp_comm_hits with age 0)
 __global__ void __launch_bounds__(1024)
 dp_exchange_drain_kernel(const __grid_constant__ dp_exchange_args X) {
-  if (dp_exchange_wait(X, X.seq)) dp_exchange_to_host(X);
+  if (dp_exchange_wait(X, X.seq)) dp_exchange_to_host(X, X.seq);
 }
 
 void dp_exchange_drain_launch(const dp_exchange_args& X, cudaStream_t st) {
@@ -226,7 +281,7 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
     if (threadIdx.x < 8)
       P.wire[threadIdx.x] = threadIdx.x == 5 ? P.rec0_len : threadIdx.x == 6 ? P.n_records : c[threadIdx.x];
   }
-  if (landed) dp_exchange_to_host(P.X);      // last call's slots of all ranks -> pinned host memory
+  if (landed) dp_exchange_to_host(P.X, P.X.seq - 1);      // last call's slots of all ranks -> pinned host memory
   if (threadIdx.x < 8) {
     P.h_counters[threadIdx.x] = c[threadIdx.x];
     P.counters[threadIdx.x] = 0ull;

@@ -14,7 +14,8 @@ tdf.PCR_P.set(dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=62.0))
 ctx = tdf._ctx(); cond = tdf.conditions()
 t = ctx.template_from_sequences([wl['records'][0].tobytes()])
 var=[unambiguous_sequences(p) for p in wl['primers']]
-q = ctx.prepare(wl['primers'], 1, var)
+KK=int(os.environ.get('KK','1'))
+q = ctx.prepare(wl['primers'], KK, var)
 ex = HitExchange(ctx, max_hits=1024)
 lib=ctx.lib
 N=300

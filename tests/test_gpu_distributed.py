@@ -49,6 +49,11 @@ def _worker(rank, world, port, text, k, out_dir):
     ctx.find_end()
     same = older is not None and newest is not None and np.array_equal(older, newest) and len(older) > 0
     same = same and oldest is not None and np.array_equal(oldest, newest)
+    # the kernel-side conversion + sort of the gathered hits against the host-side one
+    os.environ['DEGENPRIMER_B200_EXCHANGE_SORT'] = 'host'
+    by_host = ex.collect_hits(0)
+    del os.environ['DEGENPRIMER_B200_EXCHANGE_SORT']
+    same = same and by_host is not None and np.array_equal(by_host, newest)
     np.save(os.path.join(out_dir, 'ages%d.npy' % rank), np.array([int(same)]))
     ex.close()
     small = D.HitExchange(ctx, max_hits=1)               # forces the fallback gather
