@@ -241,29 +241,24 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
   __shared__ unsigned long long c[8];
   if (threadIdx.x < 8) c[threadIdx.x] = P.counters[threadIdx.x];
   __syncthreads();
-  // multi-GPU exchange first: its stores travel over NVLink while the host copies below
-  // go out over PCIe, and the one system-scope fence then only waits for NVLink
-  bool landed = false;
+  // multi-GPU exchange: the slot's stores travel over NVLink while the host copies below go
+  // out over PCIe; the sequence words that publish the slot are stored at the very end
+  bool landed = false, sent = false;
   if (P.X.world) {
     // flow control: last call's slots of all ranks are here.  That also proves that every
-    // peer has consumed the buffer this call is about to overwrite (a peer moves call c-2
-    // to its host in the kernel that publishes call c-1).
+    // peer has consumed the buffer this call is about to overwrite: a peer raises the
+    // sequence word of its call c-1 only after it has moved call c-2 out of that buffer
+    // (end of this kernel).
     landed = P.X.seq ? dp_exchange_wait(P.X, P.X.seq - 1) : false;
-    if (landed || !P.X.seq) {
-      // this rank's slot of call c goes into every rank's receive buffer c&1; header
-      // word 7 (= c+1) is stored last, behind the fence
+    sent = landed || !P.X.seq;
+    if (sent) {
+      // this rank's slot of call c goes into every rank's receive buffer c&1
       const uint64_t n_wire = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), P.X.slot_hits);
       for (int r = 0; r < P.X.world; ++r) {
         uint64_t* dst = (uint64_t*)(P.X.peers[r] + (uint64_t)P.X.rank * P.X.slot_bytes);
         for (uint64_t i = threadIdx.x; i < n_wire * 3; i += blockDim.x) dst[8 + i] = P.hits[i];
         if (threadIdx.x < 7)
           dst[threadIdx.x] = threadIdx.x == 5 ? P.X.rec0_len : threadIdx.x == 6 ? P.X.n_records : c[threadIdx.x];
-      }
-      __threadfence_system();
-      __syncthreads();
-      if ((int)threadIdx.x < P.X.world) {
-        volatile uint64_t* flag = (volatile uint64_t*)(P.X.peers[threadIdx.x] + (uint64_t)P.X.rank * P.X.slot_bytes) + 7;
-        *flag = P.X.seq + 1;
       }
     }
   }
@@ -285,6 +280,17 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
   if (threadIdx.x < 8) {
     P.h_counters[threadIdx.x] = c[threadIdx.x];
     P.counters[threadIdx.x] = 0ull;
+  }
+  if (sent) {
+    // header word 7 (= c+1) publishes the slot to a peer.  It must come after this rank's
+    // reads of receive buffer (c-1)&1 above: the peer's next call overwrites that buffer as
+    // soon as it sees the word.  The fence orders those reads and the slot's stores before it.
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < P.X.world) {
+      volatile uint64_t* flag = (volatile uint64_t*)(P.X.peers[threadIdx.x] + (uint64_t)P.X.rank * P.X.slot_bytes) + 7;
+      *flag = P.X.seq + 1;
+    }
   }
 }
 
