@@ -133,6 +133,7 @@ def _declare(lib):
         'dp_find_end': (i32, [vp, P(vp), P(u64), P(vp), P(u64), P(dp_scan_stats), P(dp_dg_stats)]),
         'dp_set_wire': (i32, [vp, C.c_void_p, u64]),
         'dp_set_timing': (i32, [vp, i32]),
+        'dp_find_again': (i32, [vp, vp, P(vp), P(u64), vp]),
         'dp_scan_prepare_kernels': (i32, [vp, u32, P(C.c_char_p), P(i32), i32]),
         'dp_jit_selftest': (i32, [u32, P(C.c_char_p), P(i32), i32, C.c_char_p, C.c_char_p]),
         'dp_comm_export': (i32, [vp, i32, i32, u32, C.c_char_p]),
@@ -159,7 +160,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
-           'dp_set_wire dp_set_timing dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
+           'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
 
 
@@ -427,6 +428,15 @@ class Context(object):
         h = self._take(hits, n_hits.value, HIT_DTYPE)
         d = self._take(dimers, n_dimers.value, DIMER_DTYPE)
         return h, d, st, dst
+
+    def find_again(self, cond):
+        """The duplex stage of the last find() of this context under other conditions: the hits
+        stay on the device, `dimers['hit']` indexes the hits that find() returned.
+        Returns (dimers, dG stats)."""
+        dimers, n_dimers = C.c_void_p(), C.c_uint64()
+        dst = dp_dg_stats()
+        self._check(self.lib.dp_find_again(self._h, C.byref(cond), C.byref(dimers), C.byref(n_dimers), C.byref(dst)))
+        return self._take(dimers, n_dimers.value, DIMER_DTYPE), dst
 
     def set_timing(self, on):
         """Per-kernel CUDA-event timing of every call (ms_* stats); off saves ~15 us of host time."""

@@ -100,6 +100,7 @@ struct dp_ctx {
   uint64_t wire_bytes;
   // multi-GPU hit exchange (dp_comm.cu): the publish kernel stores this rank's wire slot
   // straight into every peer's receive buffer over NVLink (CUDA IPC peer memory)
+  std::vector<uint8_t> codes_shadow;   // host copy of what d_codes holds (variants of the last dp_find)
   bool timing;                 // per-kernel CUDA-event timing of every call (dp_set_timing)
   int comm_world, comm_rank;   // world == 0: no exchange attached
   uint64_t comm_seq;           // calls exchanged so far; call c uses receive buffer c & 1

@@ -29,6 +29,8 @@
   do {                                                                \
     if ((ctx)->timing) DP_CUDA(ctx, cudaEventRecord((ctx)->ev, st));  \
   } while (0)
+static void drop_resident(dp_ctx* ctx);      // the hits of the last dp_find leave the device (dp_find_again)
+
 static inline void dp_elapsed(dp_ctx* ctx, float* ms, cudaEvent_t a, cudaEvent_t b) {
   *ms = 0.f;
   if (ctx->timing) cudaEventElapsedTime(ms, a, b);
@@ -859,9 +861,9 @@ static uint64_t count_windows(const dp_template* t, const dp_scan_job& J) {
 
 // variants -> plane codes on the device (skipped when the same blob is already there)
 static int upload_codes(dp_ctx* ctx, const char* variants, uint64_t n_bytes) {
-  static thread_local std::vector<uint8_t> last;      // what ctx->d_codes holds (one ctx per thread)
-  static thread_local dp_ctx* last_ctx = nullptr;
-  std::vector<uint8_t> codes(n_bytes);
+  std::vector<uint8_t>& last = ctx->codes_shadow;     // what ctx->d_codes holds
+  static thread_local std::vector<uint8_t> codes;
+  codes.resize(n_bytes);
   for (uint64_t i = 0; i < n_bytes; ++i) {
     uint32_t l = dp_letter_of((unsigned char)variants[i]);
     if (l > 3)
@@ -869,7 +871,8 @@ static int upload_codes(dp_ctx* ctx, const char* variants, uint64_t n_bytes) {
                           (unsigned long long)i, variants[i]);
     codes[i] = (uint8_t)l;
   }
-  if (last_ctx == ctx && last == codes && ctx->codes_cap >= n_bytes) return DP_OK;
+  if (last == codes && ctx->codes_cap >= n_bytes && !last.empty()) return DP_OK;
+  drop_resident(ctx);
   int rc = dp_ws_codes(ctx, std::max<uint64_t>(n_bytes, 4096));
   if (rc) return rc;
   rc = dp_ws_pinned(ctx, DP_RES_SPEC_END + n_bytes);
@@ -877,8 +880,7 @@ static int upload_codes(dp_ctx* ctx, const char* variants, uint64_t n_bytes) {
   // staged through pinned memory behind the result area; the stream is idle between calls
   memcpy(ctx->h_res + DP_RES_SPEC_END, codes.data(), n_bytes);
   DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_codes, ctx->h_res + DP_RES_SPEC_END, n_bytes, cudaMemcpyHostToDevice, ctx->stream));
-  last.swap(codes);
-  last_ctx = ctx;
+  last = codes;
   return DP_OK;
 }
 
@@ -915,6 +917,7 @@ struct dp_pipeline_state {
   uint32_t scan_launches, dg_launches;
   dp_sizes S;                       // sizes of the previous attempt (duplex-only re-runs)
   bool overflowed;                  // the first attempt did not fit: results were re-made after the wait
+  bool no_exchange;                 // dp_find_again: a duplex-only call is not part of the multi-GPU exchange
 };
 
 static int pipeline_reserve(dp_ctx* ctx, bool with_dg) {
@@ -955,7 +958,7 @@ static int pipeline_enqueue(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, c
   DP_EVENT(ctx, ev4, ctx->stream);
   // multi-GPU: the first attempt of a call carries the exchange (a re-run after an overflow
   // must not: every rank exchanges exactly once per call)
-  return publish_enqueue(ctx, dg != nullptr, !P.overflowed);
+  return publish_enqueue(ctx, dg != nullptr, !P.overflowed && !P.no_exchange);
 }
 
 // waits for the queued attempt; grows buffers and repeats while something overflowed
@@ -1012,6 +1015,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
   *n_hits_out = 0;
   if (stats) memset(stats, 0, sizeof *stats);
   if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  drop_resident(ctx);
   dp_scan_job J;
   int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, nullptr, J);
   if (rc) return rc;
@@ -1042,7 +1046,17 @@ struct dp_find_pending {
   dp_dg_launch DL;
   dp_pipeline_state P;
   std::vector<uint32_t> var_count;
+  // after a successful dp_find_end the hits are still on the device (dp_find_again)
+  bool resident = false;
+  dp_sizes S;                         // sizes of the finished call
+  std::vector<uint32_t> order;        // raw slot of output hit i
+  std::vector<uint16_t> primer_of;    // primer of output hit i
 };
+
+// any other call on the context overwrites the hit workspace
+static void drop_resident(dp_ctx* ctx) {
+  if (ctx->pending) ((dp_find_pending*)ctx->pending)->resident = false;
+}
 
 static void pending_free(void* p) { delete (dp_find_pending*)p; }
 
@@ -1058,6 +1072,7 @@ extern "C" int dp_find_begin(dp_ctx* ctx, const dp_template* t, uint32_t n_prime
   if (!ctx->pending) { ctx->pending = new dp_find_pending(); ctx->pending_free = pending_free; }
   dp_find_pending& F = *(dp_find_pending*)ctx->pending;
   if (F.active) return dp_set_error(ctx, DP_ERR_STATE, "dp_find_begin: the previous call was not finished with dp_find_end");
+  F.resident = false;
   int rc = scan_prepare(ctx, t, n_primers, masters, max_mismatches, seg_begin, seg_end, strand_mask, algo, var_count, F.J);
   if (rc) return rc;
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -1121,8 +1136,66 @@ extern "C" int dp_find_end(dp_ctx* ctx, dp_hit** hits_out, uint64_t* n_hits_out,
   else
     rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return vc[hits[i].primer]; }, dimers_out, n_dimers_out);
   if (rc) { dp_result_free(*hits_out); *hits_out = nullptr; *n_hits_out = 0; return rc; }
+  F.S = S;
+  F.order.swap(order);
+  F.primer_of.resize(S.n_hits);
+  for (uint64_t i = 0; i < S.n_hits; ++i) F.primer_of[i] = hits[i].primer;
+  F.resident = true;
   fill_scan_stats(ctx, F.t, F.J, S, F.P.ms_scan, F.P.ms_main, F.P.scan_launches, stats);
   if (stats) stats->reserved = F.P.overflowed ? 1.f : 0.f;     // the wire mirror of the first attempt is stale
+  if (dg_stats) {
+    dg_stats->duplexes = S.n_pairs;
+    dg_stats->dimers_tried = S.tried;
+    dg_stats->dimers_kept = *n_dimers_out;
+    dg_stats->ms_kernel = F.P.ms_dg;
+    dp_elapsed(ctx, &dg_stats->ms_total, ctx->ev2, ctx->ev5);
+    dg_stats->launches = F.P.dg_launches;
+  }
+  return DP_OK;
+}
+
+// The duplex stage of the last dp_find of this context again, under other conditions: the
+// hits are still on the device, nothing is scanned or uploaded (the optimiser's inner loop,
+// DegenPrimer/PCR_Optimizer.py:162-214 re-evaluates every duplex for each trial point).
+extern "C" int dp_find_again(dp_ctx* ctx, const dp_conditions* cond, dp_dimer** dimers_out, uint64_t* n_dimers_out,
+                             dp_dg_stats* dg_stats) {
+  if (!ctx || !cond || !dimers_out || !n_dimers_out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *dimers_out = nullptr; *n_dimers_out = 0;
+  if (dg_stats) memset(dg_stats, 0, sizeof *dg_stats);
+  dp_find_pending* Fp = (dp_find_pending*)ctx->pending;
+  if (!Fp || Fp->active || !Fp->resident)
+    return dp_set_error(ctx, DP_ERR_STATE, "dp_find_again: the hits of the last dp_find are not on the device any more "
+                                           "(another call used the context, or there was none)");
+  if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
+  dp_find_pending& F = *Fp;
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  F.DL.PCR_T = cond->PCR_T;
+  F.DL.Na_eq_log = cond->Na_eq_log;
+  F.DL.max_dimer_dG = cond->max_dimer_dG;
+  F.DL.max_dG_for_K = cond->max_dG_for_K;
+  pipeline_init(F.P);
+  F.P.need_scan = false;
+  F.P.no_exchange = true;
+  F.P.S = F.S;
+  F.resident = false;                   // until this call has succeeded
+  DP_EVENT(ctx, ev0, ctx->stream);
+  int rc = pipeline_enqueue(ctx, F.t, F.J, &F.DL, F.P);
+  if (rc) return rc;
+  dp_sizes S;
+  dp_host_results R;
+  rc = pipeline_wait(ctx, F.t, F.J, &F.DL, F.P, S, R);
+  if (rc) return rc;
+  if (S.n_hits != F.S.n_hits || S.n_pairs != F.S.n_pairs)
+    return dp_set_error(ctx, DP_ERR_STATE, "internal: resident hits changed between dp_find and dp_find_again");
+  const std::vector<uint16_t>& primer_of = F.primer_of;
+  const std::vector<uint32_t>& vc = F.var_count;
+  if (results_are_large(true, S))
+    rc = dimers_large(ctx, F.DL.plan, F.order, S, dimers_out, n_dimers_out);
+  else
+    rc = dimers_to_abi(ctx, R, S, F.order, [&](size_t i) { return vc[primer_of[i]]; }, dimers_out, n_dimers_out);
+  if (rc) return rc;
+  F.S = S;
+  F.resident = true;
   if (dg_stats) {
     dg_stats->duplexes = S.n_pairs;
     dg_stats->dimers_tried = S.tried;
@@ -1225,6 +1298,7 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
   if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
   if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
   if (n_hits == 0) { *dimers_out = (dp_dimer*)dp_result_alloc(sizeof(dp_dimer)); return DP_OK; }
+  drop_resident(ctx);
   if (n_hits > 0xF0000000ull) return dp_set_error(ctx, DP_ERR_ARG, "more than 4e9 hits in one call");
   if (n_primers > DP_MAX_PRIMERS) return dp_set_error(ctx, DP_ERR_ARG, "n_primers must be in [1,%d]", DP_MAX_PRIMERS);
   DP_CUDA(ctx, cudaSetDevice(ctx->device));

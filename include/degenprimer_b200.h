@@ -355,6 +355,16 @@ int dp_comm_gathered(dp_ctx* ctx, int age, const void** host_ptr, uint64_t* slot
  * multi-record template (use dp_comm_gathered then). */
 int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits, uint64_t* n_hits);
 
+/* The duplex stage of the LAST dp_find / dp_find_end of this context again under
+ * other conditions (the optimiser's inner loop, DegenPrimer/PCR_Optimizer.py:
+ * 162-214 and PCR_ProductsFinder.matches_to_mixture :67-81, re-evaluates every
+ * duplex for each trial point): the hits are still on the device, nothing is
+ * scanned or uploaded.  dimers[].hit indexes the hit array that dp_find returned.
+ * The template of that call must still exist.  DP_ERR_STATE if another call has
+ * used the context since (dp_scan, dp_duplex_dg, another dp_find_begin). */
+int dp_find_again(dp_ctx* ctx, const dp_conditions* cond, dp_dimer** dimers, uint64_t* n_dimers,
+                  dp_dg_stats* dg_stats);
+
 /* The template window under every hit, as the reference's strand strings show
  * it (fwd_seq[pos:pos+L] / rev_seq[pos:pos+L], DegenPrimer/SearchEngine.py:113):
  * out receives n_hits rows of 64 bytes, upper-case ASCII, NUL padded. */

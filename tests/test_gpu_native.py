@@ -328,3 +328,39 @@ def test_jit_kernels_equal_generic(ctx):
     assert q.jit, getattr(q, 'jit_error', '')
     _, s1 = ctx.scan(tmpl, fresh, 2)
     assert s1['algo'] == nat.DP_ALGO_JIT
+
+
+def test_find_again_under_new_conditions(ctx):
+    """dp_find_again: the duplex stage of the last find() under other PCR conditions, hits
+    still on the device, equals a fresh find() under those conditions — for a result that
+    fits the published prefix and for one laid out by the device — and refuses to run once
+    another call has used the context."""
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200 import _native as nat
+    from degenprimer_b200.SeqUtils import unambiguous_sequences
+    rng = np.random.default_rng(404)
+    first = dict(Na=50e-3, Mg=3e-3, dNTP=0.35e-3, DNA=1e-9, PCR_T=52.0)
+    second = dict(Na=120e-3, Mg=1.5e-3, dNTP=0.2e-3, DNA=1e-9, PCR_T=64.0)
+    for masters, k, n_sites in ((PRIMERS[:2], 2, 12), (['ATARTCTYCGAMGGCNATKC', 'GAASGCRAAKATYGGGAAC'], 3, 60)):
+        t = random_dna(rng, 150000, 'ACGTN', p=[0.2495] * 4 + [0.002])
+        t, _ = plant_sites(rng, t, masters, min(k, 3), n_sites)
+        tmpl = ctx.template_from_sequences([t])
+        var = [unambiguous_sequences(m) for m in masters]
+        q = ctx.prepare(masters, k, var)
+        tdf.PCR_P.set(first)
+        c1 = tdf.conditions()
+        hits, d1, _, _ = ctx.find(tmpl, q, cond=c1)
+        tdf.PCR_P.set(second)
+        c2 = tdf.conditions()
+        again, dst = ctx.find_again(c2)
+        hits2, d2, _, dst2 = ctx.find(tmpl, q, cond=c2)
+        assert np.array_equal(hits, hits2) and len(hits) > 10
+        assert np.array_equal(again, d2) and dst['duplexes'] == dst2['duplexes']
+        assert not np.array_equal(d1, d2)                         # the conditions matter
+        back, _ = ctx.find_again(c1)                              # and back: same records as the first call
+        assert np.array_equal(back, d1)
+        ctx.scan(tmpl, masters, k)                                # another call takes the hit workspace
+        with pytest.raises(nat.NativeError) as err:
+            ctx.find_again(c2)
+        assert err.value.code == nat.DP_ERR_STATE
+    tdf.PCR_P.set(first)
