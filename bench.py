@@ -44,7 +44,8 @@ def parse_args():
     ap.add_argument('--workload', default=WORKLOAD)
     ap.add_argument('--scale', type=float, default=1.0, help='shrink the template (testing only)')
     ap.add_argument('--algo', type=int, default=0, help='0 auto, 1 popcount, 2 bit-slice')
-    ap.add_argument('--cpu-sample-bp', type=int, default=12_000_000)
+    ap.add_argument('--cpu-sample-bp', type=int, default=83_257_441,
+                    help='template prefix the cpu_baseline leg of the GPU arm times (about 12 s on 16 cores)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-jit', action='store_true', help='generic scan kernel instead of the run-time specialised one')
     ap.add_argument('--host-threads', type=int, default=2, help='host threads that queue and collect the calls')
@@ -176,10 +177,19 @@ def run_reference(args):
     if rank != 0:
         return
     from degenprimer_b200.synthetic import make_workload
-    wl = make_workload(args.workload, scale=min(args.scale, args.cpu_sample_bp / 83_257_441.0 * 1.01))
+    wl = make_workload(args.workload, scale=args.scale)
     cores = os.cpu_count() or 1
-    text = make_cpu_sample(wl, args.cpu_sample_bp)
     n_var = sum(len(v) for v in variants_of(wl['primers']))
+    # the per-step sample is sized so that the whole run (K timed steps) takes about 2.5 minutes
+    # on this host, between 1 Mbp and the whole template; throughput is per bp
+    probe = make_cpu_sample(wl, 2_000_000)
+    cpu_reference_pass(probe[:500_000], wl['primers'], wl['k'], cores)        # fork pool, imports
+    t0 = time.perf_counter()
+    cpu_reference_pass(probe, wl['primers'], wl['k'], cores)
+    s_per_bp = (time.perf_counter() - t0) / max(1, len(probe))
+    budget = min(15.0, max(0.25, 150.0 / max(1, args.steps)))
+    sample_bp = int(min(wl['bp'], max(1_000_000, budget / s_per_bp)))
+    text = make_cpu_sample(wl, sample_bp)
     for _ in range(args.warmup):
         cpu_reference_pass(text[:min(len(text), 1_000_000)], wl['primers'], wl['k'], cores)
     t0 = time.perf_counter()
@@ -538,7 +548,7 @@ def run_ours(args):
         'candidates_per_step': acc['cand'] / K,
         'ms_scan_kernels': seq['ms_scan'] / K, 'ms_dg_kernels': seq['ms_dg'] / K,
         'dg_hits_per_s': (seq['hits'] / K) / (seq['ms_dg'] / K * 1e-3) if seq['ms_dg'] > 0 else None,
-        'gpu_launches': acc['launches'],
+        'gpu_launches': acc['launches'] + K,          # scan kernels + duplex kernel + the publish kernel of every step
         'sequential': {'ms_per_step': seq_elapsed / K * 1e3, 'value': world * bp * n_var / (seq_elapsed / K),
                        'note': 'the same K steps with one call in flight (per-call latency); the kernel '
                                'durations of the roofline are taken here'},
