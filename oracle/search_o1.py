@@ -82,7 +82,7 @@ def calculate_chunk_size(t_len, p_len, max_chunk=MAX_CHUNK):
 def check_length_inequality(t_len, p_len):
     """SearchEngine.py:232-238."""
     if t_len < p_len or p_len == 0:
-        raise ValueError('template sequence should be longer or equal to primer '
+        raise ValueError('SearchEngine._find: template sequence should be longer or equal to primer '
                          'sequence and both should be grater than zero.')
 
 

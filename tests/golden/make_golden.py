@@ -1,8 +1,8 @@
 #!/usr/bin/env python3
 """Generate tests/golden/*.json from the oracle (O1, the literal FFT restatement).
 
-The reference ships no golden vectors for this path and cannot run in this
-image (oracle/README.md: parity unpinned), so these fixtures freeze the ORACLE:
+The reference ships no golden vectors for this path; these fixtures freeze the ORACLE
+(the reference's own outputs are recorded by make_reference_golden.py next to this file):
 they catch regressions in oracle/ and give the GPU tests fixed inputs with
 recorded outputs.  Inputs reuse the sequences of the reference's own smoke
 tests (Tests/DegenPrimer_Tests/Test_SearchEngine.py:77-78, Test_Product.py:28-29,

@@ -1,0 +1,104 @@
+"""oracle/refshim.py: the Python-2 -> 3 rewrites, and (only where /root/reference exists, i.e. in the
+build container) a live re-run of the reference that must reproduce committed fixtures."""
+import gzip
+import json
+import os
+import signal
+import subprocess
+import sys
+
+import pytest
+
+from oracle import refshim
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_text_rewrites():
+    src = '\n'.join([
+        "from Queue import Empty",
+        "from collections import Sequence, Sized",
+        "def f(x):",
+        "    try: return x.next()",
+        "    except ValueError, e:",
+        "        print 'bad %s' \\",
+        "            % e  ",
+        "        print e #note",
+        "    if x: print 'a', 'b',",
+        "    print",
+        "    print >>sys.stderr, 'x'",
+        "    g = lambda(c): c/2",
+        "    for k, v in x.iteritems(): pass",
+        "    exec 'y = 1' in d",
+        "    return g"])
+    out = refshim.py2_text_to_py3(src)
+    compile(out, '<t>', 'exec')
+    assert 'from queue import Empty' in out and 'from collections.abc import Sequence, Sized' in out
+    assert 'except ValueError as e:' in out and "print(e) #note" in out
+    assert "print('a', 'b', end=' ')" in out and 'print()' in out and "print('x', file=sys.stderr)" in out
+    assert 'lambda c:' in out and '.items()' in out and "exec('y = 1', d)" in out and '.__next__()' in out
+
+
+def test_py2_semantics():
+    ns = dict(refshim._NAMES)
+    code = refshim.compile_py2('\n'.join([
+        "class M(type):",
+        "    def __new__(cls, name, bases, attrs):",
+        "        attrs['tagged'] = True",
+        "        return super(M, cls).__new__(cls, name, bases, attrs)",
+        "class A(object):",
+        "    __metaclass__ = M",
+        "    def __init__(self, n): self.n = n",
+        "    def __nonzero__(self): return self.n > 0",
+        "a = 7/2; b = 7/2.0; c = 9; c /= 2; d = -7/2",
+        "e = map(lambda x: x/2, range(4)); f = zip('ab', 'cd')",
+        "t = {'x': 1, 'y': 2}",
+        "for k in t.keys(): t[k+k] = 0",
+        "z = (bool(A(0)), bool(A(1)), A.tagged)"]), '<t>')
+    exec(code, ns)
+    assert (ns['a'], ns['b'], ns['c'], ns['d']) == (3, 3.5, 4, -4)
+    assert ns['e'] == [0, 0, 1, 1] and ns['f'] == [('a', 'c'), ('b', 'd')]
+    assert sorted(ns['t']) == ['x', 'xx', 'y', 'yy'] and ns['z'] == (False, True, True)
+
+
+_LIVE = r'''
+import gzip, json, sys, warnings
+warnings.simplefilter('ignore')
+sys.path.insert(0, %(root)r)
+from oracle import refshim
+ns = refshim.load()
+sys.path.insert(0, %(root)r + '/tests/golden')
+import make_reference_golden as gen
+from multiprocessing import Event
+with gzip.open(%(root)r + '/tests/golden/reference_golden.json.gz', 'rt') as fh:
+    ref = json.load(fh)
+eng = ns.SearchEngine.SearchEngine(Event()); WC = ns.WorkCounter.WorkCounter
+def primer(m): return ns.Primer.Primer(ns.SeqRecord(ns.Seq(m), id='P'), 1e-6, True)
+case = ref['scan'][3]
+for m, want in case['primers'].items():
+    r = eng._find(WC(), ns.SeqRecord(ns.Seq(case['template']), id='T'), primer(m), len(case['template']), len(m), case['k'])
+    assert r[5].tolist() == want['fwd'] and r[6].tolist() == want['rev'], m
+case = ref['duplex'][1]
+ns.tdf.PCR_P.set(ref['conds'][case['cond']])
+r = eng._find(WC(), ns.SeqRecord(ns.Seq(case['template']), id='T'), primer(case['master']), len(case['template']), len(case['master']), case['k'])
+got = json.loads(json.dumps(gen.dump_results(eng.compile_duplexes(WC(), *r))))
+assert got == case['serial']
+print('LIVE-OK')
+'''
+
+
+@pytest.mark.skipif(not refshim.available(), reason='reference sources only exist in the build container')
+def test_live_reference_reproduces_fixtures():
+    proc = subprocess.Popen([sys.executable, '-c', _LIVE % {'root': ROOT}], stdout=subprocess.PIPE,
+                            stderr=subprocess.STDOUT, start_new_session=True)
+    try:
+        out, _ = proc.communicate(timeout=180)
+    except subprocess.TimeoutExpired:
+        os.killpg(proc.pid, signal.SIGKILL)
+        raise
+    finally:
+        try:
+            os.killpg(proc.pid, signal.SIGKILL)      # the reference's manager process ignores SIGTERM
+        except ProcessLookupError:
+            pass
+    assert b'LIVE-OK' in out, out.decode(errors='replace')[-2000:]
