@@ -324,3 +324,87 @@ class SiteDuplexes(object):
 
     def __reduce__(self):
         return (tuple, (list(self._materialise()),))
+
+
+# ---------------------------------------------------------------------------------------------
+# self- and cross-dimers of primer variants.
+class DimerSet(object):
+    """What SecStructures._find_dimers leaves behind for ONE sequence pair
+    (DegenPrimer/SecStructures.py:609-668): `dimers` — the most stable structure of every
+    relative position with dG < max_dimer_dG, de-duplicated by the reference's structure key,
+    in the reference's scan order; `fronts` — for self-dimers, the full (un-trimmed) dimer of every position
+    that has at least one match, first of each structure key (the reference's hairpin seeds, :643-645);
+    the 3'-dimer counter and the most stable 3' dimer (:660-667)."""
+    __slots__ = ['seq1', 'seq2', 'dimers', 'fronts', 'n_3prim_dimers', 'min_3prim_dimer', 'min_3prim_dimer_dG']
+
+    def __init__(self, seq1, seq2):
+        self.seq1, self.seq2 = seq1, seq2
+        self.dimers, self.fronts = [], []
+        self.n_3prim_dimers = 0
+        self.min_3prim_dimer = None
+        self.min_3prim_dimer_dG = None
+
+    def __bool__(self):
+        return bool(self.dimers)
+
+    def __len__(self):
+        return len(self.dimers)
+
+
+def structure_key(dimer):
+    """The tuple inside SecStructures._structure_hash (:597-605): `fwd_matches + rev_matches` adds a
+    tuple to a numpy array, i.e. ELEMENT-WISE — the key is (2*f - offset for f in fwd_matches)."""
+    return tuple(2 * f - dimer.offset for f in dimer.fwd_matches)
+
+
+def find_dimers_batch(seqs, pairs, return_ms=False):
+    """SecStructures._find_dimers for many sequence pairs in ONE kernel launch (dp_find_dimers:
+    one warp per (pair, relative position); [dimer] + alternatives evaluated by the lanes).
+
+    seqs: list of str / Seq (5'->3', <= 64 nt); pairs: iterable of (i, j) indices into seqs
+    (i == j or equal sequences: self-dimers).  Returns a list of DimerSet, one per pair."""
+    strs = [str(s).upper() for s in seqs]
+    pairs = np.asarray(list(pairs), dtype=np.uint32).reshape(-1, 2)
+    rec, ms = tdf._ctx().find_dimers(strs, pairs, tdf.conditions())
+    if np.isnan(rec['best_dG']).any():
+        raise ValueError('UnifiedNN.int_dPar_37: sequence is not in the database')
+    out = []
+    la = np.array([len(s) for s in strs], dtype=np.int64)
+    has_full = rec['full_mask'] != 0
+    for p, (i, j) in enumerate(pairs):
+        ds = DimerSet(strs[i], strs[j])
+        fwd_len = int(la[i])
+        seen, seen_fronts = set(), set()
+        self_pair = strs[i] == strs[j]
+        for f in np.nonzero(has_full[p])[0]:
+            f = int(f)
+            offset = max(0, fwd_len - f - 1) - max(0, f - fwd_len + 1)
+            r = rec[p, f]
+            if self_pair:
+                full = Dimer(mask_to_matches(r['full_mask']), offset)
+                if structure_key(full) not in seen_fronts:                    # SecStructures.py:643-645
+                    seen_fronts.add(structure_key(full))
+                    ds.fronts.append(full)
+            if not r['best_mask']:
+                continue
+            d = Dimer(mask_to_matches(r['best_mask']), offset)
+            d.dG = float(r['best_dG'])
+            key = structure_key(d)
+            if key in seen:
+                continue
+            seen.add(key)
+            ds.dimers.append(d)
+            if d.fwd_matches[-1] > fwd_len - 4 or d.rev_min < 3:          # SecStructures.py:660-667
+                ds.n_3prim_dimers += 1
+                if ds.min_3prim_dimer_dG is None or ds.min_3prim_dimer_dG > d.dG:
+                    ds.min_3prim_dimer_dG = d.dG
+                    ds.min_3prim_dimer = d
+        out.append(ds)
+    return (out, ms) if return_ms else out
+
+
+def find_dimers(seq1, seq2=None):
+    """One pair: cross-dimers of seq1 and seq2, or self-dimers of seq1 (SecStructures.py:576-588)."""
+    if seq2 is None or str(seq1) == str(seq2):
+        return find_dimers_batch([seq1], [(0, 0)])[0]
+    return find_dimers_batch([seq1, seq2], [(0, 1)])[0]

@@ -94,7 +94,9 @@ DIMER_DTYPE = np.dtype([('hit', '<u4'), ('variant', '<u4'), ('match_mask', '<u8'
 WIRE_DTYPE = np.dtype([('g', '<u8'), ('record', '<u4'), ('pattern', '<u2'), ('score3', '<u2'),
                        ('pair_base', '<u4'), ('reserved', '<u4')], align=True)
 WIRE_HEADER_BYTES = 64
+FRONT_DIMER_DTYPE = np.dtype([('full_mask', '<u8'), ('best_mask', '<u8'), ('best_dG', '<f8')], align=True)
 assert HIT_DTYPE.itemsize == 16 and DIMER_DTYPE.itemsize == 24 and WIRE_DTYPE.itemsize == 24
+assert FRONT_DIMER_DTYPE.itemsize == 24
 
 _lib = None
 _lock = threading.Lock()
@@ -148,6 +150,8 @@ def _declare(lib):
         'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
         'dp_dimer_dg': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_void_p, P(dp_conditions), C.c_void_p]),
+        'dp_find_dimers': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, u32, C.c_void_p, C.c_void_p,
+                                 P(dp_conditions), u32, C.c_void_p, P(C.c_float)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -161,7 +165,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
            'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
-           'dp_hit_windows dp_variant_tm dp_dimer_dg dp_calibrate').split()
+           'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_calibrate').split()
 
 
 def load():
@@ -567,6 +571,27 @@ class Context(object):
                                          C.cast(C.c_char_p(s2), C.c_void_p), _ptr(o2), _ptr(l2),
                                          _ptr(mk), _ptr(of), C.byref(cond), _ptr(out)))
         return out
+
+
+    def find_dimers(self, seqs, pairs, cond):
+        """dp_find_dimers: `seqs` list of str, `pairs` (n, 2) indices into it.  Returns
+        (records[n_pairs, stride] of FRONT_DIMER_DTYPE, kernel ms)."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.uint32).reshape(-1, 2)
+        n_pairs = len(pairs)
+        ln = np.array([len(s) for s in seqs], dtype=np.uint8)
+        if any(len(s) > 64 for s in seqs):
+            raise ValueError('sequences longer than 64 nt are not supported by dp_find_dimers')
+        off = np.concatenate(([0], np.cumsum(ln, dtype=np.uint64)[:-1])).astype(np.uint64)
+        blob = ''.join(seqs).encode('ascii')
+        a = np.ascontiguousarray(pairs[:, 0])
+        b = np.ascontiguousarray(pairs[:, 1])
+        stride = int((ln[a].astype(np.int64) + ln[b].astype(np.int64) - 1).max()) if n_pairs else 1
+        out = np.zeros((n_pairs, stride), dtype=FRONT_DIMER_DTYPE)
+        ms = C.c_float(0.0)
+        self._check(self.lib.dp_find_dimers(self._h, len(seqs), C.cast(C.c_char_p(blob), C.c_void_p), _ptr(off),
+                                            _ptr(ln), n_pairs, _ptr(a), _ptr(b), C.byref(cond), stride,
+                                            _ptr(out), C.byref(ms)))
+        return out, float(ms.value)
 
 
 _contexts = {}

@@ -475,6 +475,119 @@ __global__ void dp_dimer_dg_kernel(dp_dg_args A, uint32_t n, const uint8_t* __re
   out[i] = dp_dimer_dg_device(A, s, sl, r, rl, mask[i], offset[i]);
 }
 
+// ---- self / cross dimers of primer pairs -------------------------------
+// SecStructures._find_dimers, DegenPrimer/SecStructures.py:609-668: slide seq2 (as its reverse
+// complement) along seq1; at every relative position ("front", fwd_len+rev_len-1 of them) the
+// matching letters form a Dimer; of [dimer] + dimer.alternatives the one with the lowest
+// dimer_dG_corrected below max_dimer_dG is kept (first one wins a tie).  One WARP per
+// (pair, front): lanes compare letters (ballot -> match mask), build the run table, then lane d
+// evaluates the d-th candidate; a shuffle reduction picks the minimum (dG, d).
+struct dp_fd_scratch {
+  uint8_t s[DP_WIN];
+  uint8_t r[DP_WIN];
+  uint8_t run_start[32];
+  uint8_t run_end[32];
+};
+
+__global__ void __launch_bounds__(DP_DUPLEX_THREADS)
+dp_find_dimers_kernel(dp_dg_args A, const uint8_t* __restrict__ codes, const uint64_t* __restrict__ seq_off,
+                      const uint8_t* __restrict__ seq_len, const uint32_t* __restrict__ pair_a,
+                      const uint32_t* __restrict__ pair_b, uint32_t n_pairs, uint32_t stride,
+                      dp_front_dimer* __restrict__ out) {
+  __shared__ dp_nn_tables sT;
+  __shared__ dp_fd_scratch sW[DP_DUPLEX_WARPS];
+  {
+    const uint64_t* src = reinterpret_cast<const uint64_t*>(A.T);
+    uint64_t* dst = reinterpret_cast<uint64_t*>(&sT);
+    for (uint32_t i = threadIdx.x; i < sizeof(dp_nn_tables) / 8; i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  dp_dg_args G = A;
+  G.T = &sT;
+  const uint32_t lane = threadIdx.x & 31u;
+  dp_fd_scratch& W = sW[threadIdx.x >> 5];
+  const uint64_t n_items = (uint64_t)n_pairs * stride;
+  const uint64_t n_warps = (uint64_t)gridDim.x * DP_DUPLEX_WARPS;
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  for (uint64_t item = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); item < n_items; item += n_warps) {
+    const uint32_t pair = (uint32_t)(item / stride);
+    const int front = (int)(item % stride);
+    const uint32_t ia = pair_a[pair], ib = pair_b[pair];
+    const int la = seq_len[ia], lb = seq_len[ib];
+    dp_front_dimer res;
+    res.full_mask = 0; res.best_mask = 0; res.best_dG = 0.0;
+    if (front >= la + lb - 1) {                          // padding of the dense [pair][front] layout
+      if (lane == 0) out[item] = res;
+      continue;
+    }
+    __syncwarp();                                        // previous item's readers are done
+    const uint8_t* ca = codes + seq_off[ia];
+    const uint8_t* cb = codes + seq_off[ib];
+    for (int i = (int)lane; i < la; i += 32) W.s[i] = ca[i];
+    for (int i = (int)lane; i < lb; i += 32) W.r[i] = cb[lb - 1 - i];      // seq2 reversed: 3'->5'
+    __syncwarp();
+    // margins — SecStructures.py:620-636 (fwd_right may exceed fwd_len; zip() cuts at the shorter range)
+    const int fwd_left = la - front - 1 > 0 ? la - front - 1 : 0;
+    int fwd_right = la;
+    if (front >= lb) fwd_right -= front - lb - 1;
+    const int rev_left = front >= la ? front - la + 1 : 0;
+    const int rev_right = front >= lb ? lb : front + 1;
+    const int cnt = min(fwd_right - fwd_left, rev_right - rev_left);
+    const int off = fwd_left - rev_left;
+    uint64_t M = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int i = (int)lane + 32 * half;
+      bool match = false;
+      if (i < cnt) match = W.s[fwd_left + i] == (uint8_t)dp_letter_complement(W.r[rev_left + i]);
+      const uint64_t b = (uint64_t)__ballot_sync(0xFFFFFFFFu, match) << (32 * half);
+      M |= b;
+    }
+    M <<= fwd_left;                                      // bit = seq1 index (fwd_left + cnt <= 64)
+    if (!M) {
+      if (lane == 0) out[item] = res;
+      continue;
+    }
+    const uint64_t S = M & ~(M << 1);
+    const uint64_t Eb = M & ~(M >> 1);
+    const int n = __popcll(S);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int i = (int)lane + 32 * half;
+      const uint64_t below = (1ull << i) - 1ull;
+      if ((S >> i) & 1ull) W.run_start[__popcll(S & below)] = (uint8_t)i;
+      if ((Eb >> i) & 1ull) W.run_end[__popcll(Eb & below)] = (uint8_t)i;
+    }
+    __syncwarp();
+    const uint32_t n_dimers = (uint32_t)(n * (n + 1) / 2);
+    double best = G.max_dimer_dG;                        // `if min_dG > dimer.dG` — strict
+    uint32_t best_d = 0xFFFFFFFFu;
+    bool bad = false;
+    for (uint32_t d = lane; d < n_dimers; d += 32) {
+      const uint64_t sub = dp_nth_dimer(M, n, d, W.run_start, W.run_end);
+      const double dG = dp_dimer_dg_device(G, W.s, la, W.r, lb, sub, off);
+      if (dG != dG) bad = true;
+      if (best > dG) { best = dG; best_d = d; }
+    }
+#pragma unroll
+    for (int sh = 16; sh > 0; sh >>= 1) {
+      const double ob = __shfl_xor_sync(0xFFFFFFFFu, best, sh);
+      const uint32_t od = __shfl_xor_sync(0xFFFFFFFFu, best_d, sh);
+      if (ob < best || (ob == best && od < best_d)) { best = ob; best_d = od; }
+    }
+    bad = __any_sync(0xFFFFFFFFu, bad);
+    if (lane == 0) {
+      res.full_mask = M;
+      if (bad) { res.best_mask = 0; res.best_dG = nan; }        // the reference raises (unknown NN key)
+      else if (best_d != 0xFFFFFFFFu) {
+        res.best_mask = dp_nth_dimer(M, n, best_d, W.run_start, W.run_end);
+        res.best_dG = best;
+      }
+      out[item] = res;
+    }
+  }
+}
+
 // ---- host ----------------------------------------------------------------------------
 // scratch from the context's stream-ordered pool (freed in stream order, no sync)
 template <typename T>
@@ -619,5 +732,67 @@ extern "C" int dp_dimer_dg(dp_ctx* ctx, uint32_t n, const char* s1, const uint64
   DP_CUDA(ctx, cudaGetLastError());
   DP_CUDA(ctx, cudaMemcpyAsync(dG, dout.p, n * sizeof(double), cudaMemcpyDeviceToHost, st));
   DP_CUDA(ctx, cudaStreamSynchronize(st));
+  return DP_OK;
+}
+
+extern "C" int dp_find_dimers(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, const uint64_t* off, const uint8_t* len,
+                              uint32_t n_pairs, const uint32_t* pair_a, const uint32_t* pair_b,
+                              const dp_conditions* cond, uint32_t stride, dp_front_dimer* out, float* ms_kernel) {
+  if (!ctx || !seqs || !off || !len || !cond || (n_pairs && (!pair_a || !pair_b || !out)))
+    return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
+  if (ms_kernel) *ms_kernel = 0.f;
+  if (n_pairs == 0) return DP_OK;
+  uint64_t bytes = 0;
+  for (uint32_t i = 0; i < n_seqs; ++i) {
+    if (len[i] == 0 || len[i] > DP_WIN)
+      return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "sequence %u: length outside [1,%d]", i, DP_WIN);
+    bytes = std::max<uint64_t>(bytes, off[i] + len[i]);
+  }
+  uint32_t need = 0;
+  for (uint32_t p = 0; p < n_pairs; ++p) {
+    if (pair_a[p] >= n_seqs || pair_b[p] >= n_seqs)
+      return dp_set_error(ctx, DP_ERR_ARG, "pair %u: sequence index out of range", p);
+    need = std::max<uint32_t>(need, (uint32_t)len[pair_a[p]] + len[pair_b[p]] - 1);
+  }
+  if (stride < need) return dp_set_error(ctx, DP_ERR_ARG, "stride %u is smaller than the %u fronts of the longest pair", stride, need);
+  if ((uint64_t)n_pairs * stride > (1ull << 31))
+    return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "more than 2^31 (pair, front) items in one call");
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::vector<uint8_t> codes;
+  int rc = letters_of(ctx, seqs, bytes, codes, false);
+  if (rc) return rc;
+  const uint64_t n_items = (uint64_t)n_pairs * stride;
+  dev_buf<uint8_t> d_codes, d_len;
+  dev_buf<uint64_t> d_off;
+  dev_buf<uint32_t> d_a, d_b;
+  dev_buf<dp_front_dimer> d_out;
+  DP_CUDA(ctx, d_codes.alloc(ctx, bytes)); DP_CUDA(ctx, d_len.alloc(ctx, n_seqs)); DP_CUDA(ctx, d_off.alloc(ctx, n_seqs));
+  DP_CUDA(ctx, d_a.alloc(ctx, n_pairs)); DP_CUDA(ctx, d_b.alloc(ctx, n_pairs)); DP_CUDA(ctx, d_out.alloc(ctx, n_items));
+  cudaStream_t st = ctx->stream;
+  DP_CUDA(ctx, cudaMemcpyAsync(d_codes.p, codes.data(), bytes, cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_len.p, len, n_seqs, cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_off.p, off, n_seqs * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_a.p, pair_a, n_pairs * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_b.p, pair_b, n_pairs * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (ms_kernel) {
+    DP_CUDA(ctx, cudaEventCreate(&e0));
+    DP_CUDA(ctx, cudaEventCreate(&e1));
+    DP_CUDA(ctx, cudaEventRecord(e0, st));
+  }
+  // one warp per (pair, front), grid-stride; 16 resident blocks of 4 warps per SM
+  const uint64_t blocks_needed = (n_items + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS;
+  const unsigned grid = (unsigned)std::min<uint64_t>(blocks_needed, (uint64_t)ctx->sm_count * 16);
+  dp_dg_args A = make_args(ctx, cond);
+  dp_find_dimers_kernel<<<grid, DP_DUPLEX_THREADS, 0, st>>>(A, d_codes.p, d_off.p, d_len.p, d_a.p, d_b.p, n_pairs, stride, d_out.p);
+  cudaError_t le = cudaGetLastError();
+  if (ms_kernel && le == cudaSuccess) le = cudaEventRecord(e1, st);
+  if (le == cudaSuccess) le = cudaMemcpyAsync(out, d_out.p, n_items * sizeof(dp_front_dimer), cudaMemcpyDeviceToHost, st);
+  if (le == cudaSuccess) le = cudaStreamSynchronize(st);
+  if (ms_kernel && le == cudaSuccess) le = cudaEventElapsedTime(ms_kernel, e0, e1);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  DP_CUDA(ctx, le);
   return DP_OK;
 }

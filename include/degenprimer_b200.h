@@ -389,6 +389,29 @@ int dp_dimer_dg(dp_ctx* ctx, uint32_t n, const char* s1, const uint64_t* off1,
                 const uint8_t* len2, const uint64_t* match_mask,
                 const int32_t* offset, const dp_conditions* cond, double* dG);
 
+/* SURVEY §8(f) N3 — primer self- and cross-dimers: SecStructures._find_dimers
+ * (DegenPrimer/SecStructures.py:609-668) for a batch of sequence pairs.
+ * Sequence i = seqs + off[i], len[i] <= 64 IUPAC letters, 5'->3'.  For pair p =
+ * (pair_a[p], pair_b[p]) and every front f in [0, len_a + len_b - 1) — seq2's reverse
+ * complement slid along seq1, Dimer.offset = max(0, len_a-f-1) - max(0, f-len_a+1) —
+ * out[p*stride + f] holds the matching seq1 indices (full_mask; 0 = no match at this
+ * front) and, of [dimer] + dimer.alternatives, the structure with the lowest
+ * dimer_dG_corrected strictly below cond->max_dimer_dG (best_mask, best_dG; best_mask = 0
+ * when none; best_dG = NaN where the reference raises for an unknown NN key).  Entries
+ * f >= len_a + len_b - 1 are zero.  stride >= the largest front count of the batch.
+ * The de-duplication by structure hash and the 3'-dimer counters of the reference are a
+ * few dictionary operations per pair and stay with the caller (SecStructures.find_dimers).
+ * ms_kernel (optional): device time of the kernel by CUDA events. */
+typedef struct dp_front_dimer {
+  uint64_t full_mask;
+  uint64_t best_mask;
+  double best_dG;
+} dp_front_dimer;
+int dp_find_dimers(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, const uint64_t* off,
+                   const uint8_t* len, uint32_t n_pairs, const uint32_t* pair_a,
+                   const uint32_t* pair_b, const dp_conditions* cond, uint32_t stride,
+                   dp_front_dimer* out, float* ms_kernel);
+
 /* ---- roofline calibration -------------------------------------------------------
  * Measured issue rate of the pipes the scan kernels live on (the
  * integer roofline's denominators must be measured on the box).

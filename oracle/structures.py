@@ -223,3 +223,56 @@ class Duplex(object):
         return out + '\n'
 
     __repr__ = __str__
+
+
+def structure_key(dimer):
+    """The tuple hashed by SecStructures._structure_hash (DP/SecStructures.py:597-605):
+    `struct.fwd_matches + struct.rev_matches` is tuple + numpy array, i.e. an ELEMENT-WISE sum."""
+    return tuple(2 * f - dimer.offset for f in dimer.fwd_matches)
+
+
+def find_dimers(seq1, seq2, max_dimer_dG=-3):
+    """SecStructures._find_dimers, DP/SecStructures.py:609-668.
+
+    Returns (dimers, fronts, n_3prim, min_3prim_dG): the most stable structure of every relative
+    position with dG < max_dimer_dG (insertion order, de-duplicated by structure_key), the full dimer
+    of every position with at least one match (first of each structure_key: the hairpin seeds), and the 3'-dimer bookkeeping of :660-667.
+    """
+    from . import thermo
+    fwd_str = str(seq1)
+    rev_str = reverse_complement(str(seq2))
+    fwd_len, rev_len = len(fwd_str), len(rev_str)
+    dimers, fronts, seen, seen_fronts = [], [], set(), set()
+    n_3prim, min_3prim_dG = 0, None
+    for front in range(fwd_len + rev_len - 1):
+        fwd_left = max(fwd_len - front - 1, 0)
+        fwd_right = fwd_len
+        if front >= rev_len:
+            fwd_right -= front - rev_len - 1
+        rev_left = front - fwd_len + 1 if front >= fwd_len else 0
+        rev_right = rev_len if front >= rev_len else front + 1
+        matches = [f for f, r in zip(range(fwd_left, fwd_right), range(rev_left, rev_right))
+                   if fwd_str[f] == rev_str[r]]
+        if not matches:
+            continue
+        dimer = Dimer(matches, fwd_left - rev_left)
+        if structure_key(dimer) not in seen_fronts:          # :643-645 (the reference does this for self-dimers only)
+            seen_fronts.add(structure_key(dimer))
+            fronts.append(dimer)
+        min_dG, best = max_dimer_dG, None
+        for d in [dimer] + dimer.alternatives:
+            d.dG = thermo.dimer_dG_corrected(d, fwd_str, str(seq2))
+            if min_dG > d.dG:
+                min_dG, best = d.dG, d
+        if best is None:
+            continue
+        key = structure_key(best)
+        if key in seen:
+            continue
+        seen.add(key)
+        dimers.append(best)
+        if best.fwd_matches[-1] > fwd_len - 4 or best.rev_min < 3:
+            n_3prim += 1
+            if min_3prim_dG is None or min_3prim_dG > min_dG:
+                min_3prim_dG = min_dG
+    return dimers, fronts, n_3prim, min_3prim_dG
