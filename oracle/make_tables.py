@@ -5,7 +5,7 @@ TEST INFRASTRUCTURE ONLY (see oracle/README.md).
 
 Reads the TAB-separated, '"'-quoted csv files the reference installs to
 share/degen_primer (reference data/internal-NN.csv, data/dangling-ends.csv,
-data/loops.csv; parsed like DegenPrimer/UnifiedNN.py:163-199) and writes them
+data/loops.csv, data/3-4-hairpin-loops.csv; parsed like DegenPrimer/UnifiedNN.py:163-199) and writes them
 as one JSON document in this repo's own layout.  The JSON travels to the GPU
 box; /root/reference does not.
 
@@ -29,6 +29,7 @@ def main():
     nn = read_table(os.path.join(src, 'internal-NN.csv'))
     ends = read_table(os.path.join(src, 'dangling-ends.csv'))
     loops = read_table(os.path.join(src, 'loops.csv'))
+    tri_tetra = read_table(os.path.join(src, '3-4-hairpin-loops.csv'))
     doc = {
         'source': 'allista/DegenPrimer data/*.csv (SantaLucia & Hicks 2004)',
         'units': {'dH': 'kcal/mol', 'dS': 'cal/(K*mol)', 'dG': 'kcal/mol at 37C'},
@@ -37,6 +38,8 @@ def main():
         'dangling': {k: [v['dH'], v['dS'], v['dG']] for k, v in ends.items()},
         # loop size -> [internal dG37, hairpin dG37]
         'loops': {k: [v['internal'], v['hairpin']] for k, v in loops.items()},
+        # closing pair + loop letters of special tri-/tetra-loops -> [dH, dG37 bonus]
+        'tri_tetra_hairpin_loops': {k: [v['dH'], v['dG']] for k, v in tri_tetra.items()},
     }
     out = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'tables.json')
     with open(out, 'w') as fh:

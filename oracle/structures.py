@@ -276,3 +276,60 @@ def find_dimers(seq1, seq2, max_dimer_dG=-3):
             if min_3prim_dG is None or min_3prim_dG > min_dG:
                 min_3prim_dG = min_dG
     return dimers, fronts, n_3prim, min_3prim_dG
+
+
+class Hairpin(object):
+    """DP/SecStructures.py:194-220."""
+    __slots__ = ['fwd_matches', 'rev_matches', 'conversion_degree', 'dG', 'K']
+
+    def __init__(self, fwd_matches, rev_matches):
+        if len(fwd_matches) != len(rev_matches):
+            raise ValueError('number of forward matches should equal that of reverse matches.')
+        self.fwd_matches = tuple(sorted(fwd_matches))
+        self.rev_matches = tuple(sorted(rev_matches, reverse=True))
+        self.conversion_degree = None
+        self.dG = None
+        self.K = None
+
+
+def trim_hairpin_seed(fwd_matches):
+    """The while loop of SecStructures._find_hairpins (:684-690): both sets start as the self-dimer's
+    fwd_matches; pairs are dropped from the middle until the stem ends are >= 4 apart (3 unpaired bases)."""
+    fwd, rev = set(fwd_matches), set(fwd_matches)
+    while (rev and fwd) and (min(rev) < max(fwd) or min(rev) - max(fwd) < 4):
+        fwd.remove(max(fwd))
+        rev.remove(min(rev))
+    return fwd, rev
+
+
+def find_hairpins(seeds, seq, max_hairpin_dG=3):
+    """SecStructures._find_hairpins, DP/SecStructures.py:676-716.  seeds: the full self-dimers of
+    find_dimers (`fronts`).  Returns (hairpins, n_3prim, min_3prim_dG)."""
+    from . import thermo
+    seq = str(seq)
+    seq_len = len(seq)
+    hairpins, seen = [], set()
+    n_3prim, min_3prim_dG = 0, None
+    for seed in seeds:
+        fwd, rev = trim_hairpin_seed(seed.fwd_matches)
+        if not fwd:
+            continue
+        dimer = Dimer(fwd, min(fwd) - (seq_len - 1 - max(rev)))
+        min_dG, best = max_hairpin_dG, None
+        for d in [dimer] + dimer.alternatives:
+            h = Hairpin(d.fwd_matches, set(seq_len - 1 - (m - d.offset) for m in d.fwd_matches))
+            h.dG = thermo.hairpin_dG_corrected(h, seq)
+            if min_dG > h.dG:
+                min_dG, best = h.dG, h
+        if best is None:
+            continue
+        key = best.fwd_matches + best.rev_matches          # _structure_hash: tuple + tuple = concatenation
+        if key in seen:
+            continue
+        seen.add(key)
+        hairpins.append(best)
+        if best.rev_matches[0] > seq_len - 4:
+            n_3prim += 1
+            if min_3prim_dG is None or min_3prim_dG > min_dG:
+                min_3prim_dG = min_dG
+    return hairpins, n_3prim, min_3prim_dG

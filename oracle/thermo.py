@@ -116,3 +116,49 @@ def dimer_dG_corrected(dimer, seq1, seq2):
 def equilibrium_constant(dG_T, T):
     """TD_Functions.py:279-283."""
     return exp(-1000 * dG_T / (nn.R * (T - nn.K0)))
+
+
+def hairpin_dG_corrected(hairpin, seq):
+    """TD_Functions.py:209-276.  hairpin.fwd_matches ascending, hairpin.rev_matches descending,
+    fwd_matches[i] pairs with rev_matches[i]."""
+    fm, rm = hairpin.fwd_matches, hairpin.rev_matches
+    s = str(seq)
+    s_len = len(s)
+    dG = 0
+    dH = nn.INI.dH
+    dS = nn.INI.dS
+    f0, r0 = fm[0], rm[0]
+    if f0 == 0 and r0 < s_len - 1:                 # 3' dangling (:228-232)
+        p = nn.end_dPar_37(s[r0] + s[r0 + 1], s[0] + '-')
+        dH += p.dH
+        dS += p.dS
+    elif f0 > 0 and r0 == s_len - 1:               # 5' dangling (:233-237)
+        p = nn.end_dPar_37(s[f0 - 1] + s[f0], '-' + s[-1])
+        dH += p.dH
+        dS += p.dS
+    elif f0 > 0 and r0 < s_len - 1:                # terminal mismatch
+        dG += nn.TERMINAL_MISMATCH
+    elif f0 == 0 and r0 == s_len - 1:              # blunt
+        if s[0] in 'AT':
+            dH += nn.TER.dH
+            dS += nn.TER.dS
+    for i in range(len(fm) - 1):                   # :246-267
+        a, b = fm[i], fm[i + 1]
+        ra, rb = rm[i], rm[i + 1]
+        gap = b - a
+        if gap < 4:
+            p = nn.int_dPar_37(s[a:a + 2], s[ra - 1:ra + 1][::-1])
+            dH += p.dH
+            dS += p.dS
+            if gap > 1:
+                p = nn.int_dPar_37(s[rb:rb + 2], s[b - 1:b + 1][::-1])
+                dH += p.dH
+                dS += p.dS
+        else:
+            dS += nn.internal_loop_dS_37(s[a:b + 1])
+    f1 = fm[-1]
+    hp = s[f1:rm[-1] + 1]                          # :269-272
+    dH += nn.hairpin_loop_dH_37(hp)
+    dS += nn.hairpin_loop_dS_37(hp)
+    dS += nn.DS_NA * (f1 - f0) * cond.PCR_P.Na_eq_log
+    return dG + dH - (cond.PCR_P.PCR_T - nn.K0) * dS / 1000.0

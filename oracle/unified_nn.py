@@ -44,10 +44,11 @@ def _load():
         stacks[k[::-1]] = stacks[k]
     dangling = {k: Pars(*v) for k, v in doc['dangling'].items()}
     loops = {int(k): {'internal': v[0], 'hairpin': v[1]} for k, v in doc['loops'].items()}
-    return stacks, dangling, loops
+    tri_tetra = {k: {'dH': v[0], 'dG': v[1]} for k, v in doc['tri_tetra_hairpin_loops'].items()}
+    return stacks, dangling, loops, tri_tetra
 
 
-STACKS, DANGLING, LOOPS = _load()
+STACKS, DANGLING, LOOPS, TRI_TETRA = _load()
 INI = STACKS['ini']
 TER = STACKS['ter']
 SYM = STACKS['sym']
@@ -108,3 +109,40 @@ def internal_loop_dG_37(length):
 def internal_loop_dS_37(seq):
     """UnifiedNN.py:317-319 — depends on len(seq) only."""
     return internal_loop_dG_37(len(seq) - 2) * IK37
+
+
+def hairpin_loop_dG_37(seq):
+    """UnifiedNN.py:279-307; seq includes the closing pair (the >30 warning print is dropped)."""
+    length = len(seq) - 2
+    if length in LOOPS:
+        g = LOOPS[length]['hairpin']
+        if length == 3:
+            if seq in TRI_TETRA:
+                g += TRI_TETRA[seq]['dG']
+            if seq[0] in 'AT':
+                g += 0.5
+        elif length == 4:
+            if seq in TRI_TETRA:
+                g += TRI_TETRA[seq]['dG']
+            g += TERMINAL_MISMATCH
+        else:
+            g += TERMINAL_MISMATCH
+        return g
+    g = _extrapolate_loop_dG_37(length, 'hairpin')
+    g += TERMINAL_MISMATCH
+    return g
+
+
+def hairpin_loop_dH_37(seq):
+    """UnifiedNN.py:310-315."""
+    if len(seq) - 2 > 4:
+        return 0
+    try:
+        return TRI_TETRA[seq]['dH']
+    except KeyError:
+        return 0
+
+
+def hairpin_loop_dS_37(seq):
+    """UnifiedNN.py:321-325."""
+    return (hairpin_loop_dG_37(seq) - hairpin_loop_dH_37(seq)) * IK37

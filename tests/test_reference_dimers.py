@@ -96,3 +96,19 @@ def test_gpu_find_dimers_equals_oracle_on_random_pairs():
             assert [(d.fwd_matches, d.offset) for d in ds.fronts] == [(d.fwd_matches, d.offset) for d in fronts]
         total += len(dimers)
     assert total > 100
+
+
+def test_oracle_find_hairpins_equals_reference():
+    from oracle.structures import find_hairpins as o_find_hairpins
+    n = 0
+    for case in REF['cases']:
+        if 'hairpins' not in case:
+            continue
+        ocond.PCR_P.set(REF['conds'][case['cond']])
+        seq = SEQS[case['a']]
+        _, fronts, _, _ = o_find_dimers(seq, seq)
+        hairpins, n3, _ = o_find_hairpins(fronts, seq)
+        assert [[list(h.fwd_matches), list(h.rev_matches), h.dG] for h in hairpins] == case['hairpins']
+        assert n3 == case['n_3prim_hairpins']
+        n += len(hairpins)
+    assert n > 50
