@@ -327,14 +327,50 @@ class SiteDuplexes(object):
 
 
 # ---------------------------------------------------------------------------------------------
-# self- and cross-dimers of primer variants.
+# self-dimers, cross-dimers and hairpins of primer variants
+# (DegenPrimer/SecStructures.py:389-716).  Two kernels: dp_find_dimers (one warp per sequence pair and
+# relative position) and dp_find_hairpins (one warp per hairpin seed).
+class Hairpin(object):
+    """Stem of a hairpin (SecStructures.py:194-220): fwd_matches ascending, rev_matches descending,
+    fwd_matches[i] pairs with rev_matches[i]."""
+    __slots__ = ['fwd_matches', 'rev_matches', 'conversion_degree', 'dG', 'K']
+
+    def __init__(self, fwd_matches, rev_matches):
+        if len(fwd_matches) != len(rev_matches):
+            raise ValueError('SecStructures.Dimer: number of forward matches should equal that of reverse matches.')
+        self.fwd_matches = tuple(sorted(fwd_matches))
+        self.rev_matches = tuple(sorted(rev_matches, reverse=True))
+        self.conversion_degree = None
+        self.dG = None
+        self.K = None
+
+    def __getstate__(self):
+        return tuple(getattr(self, s) for s in self.__slots__)
+
+    def __setstate__(self, state):
+        for s, v in zip(self.__slots__, state):
+            setattr(self, s, v)
+
+
+class Reaction(object):
+    """The four fields of Equilibrium.Reaction (DegenPrimer/Equilibrium.py:33-62) that
+    SecStructures.compose_reactions fills; Equilibrium itself is out of scope."""
+    __slots__ = ['constant', 'Ai', 'Bi', 'type']
+
+    def __init__(self, K, Ai, Bi, r_type):
+        self.constant, self.Ai, self.Bi, self.type = K, Ai, Bi, r_type
+
+    def __str__(self):
+        return '[K=%f; Ai: %s; Bi: %s; type: %s]' % (self.constant, str(self.Ai), str(self.Bi), self.type)
+
+
 class DimerSet(object):
     """What SecStructures._find_dimers leaves behind for ONE sequence pair
     (DegenPrimer/SecStructures.py:609-668): `dimers` — the most stable structure of every
     relative position with dG < max_dimer_dG, de-duplicated by the reference's structure key,
-    in the reference's scan order; `fronts` — for self-dimers, the full (un-trimmed) dimer of every position
-    that has at least one match, first of each structure key (the reference's hairpin seeds, :643-645);
-    the 3'-dimer counter and the most stable 3' dimer (:660-667)."""
+    in the reference's scan order; `fronts` — for self-dimers, the full (un-trimmed) dimer of every
+    position that has at least one match, first of each structure key (the reference's hairpin
+    seeds, :643-645); the 3'-dimer counter and the most stable 3' dimer (:660-667)."""
     __slots__ = ['seq1', 'seq2', 'dimers', 'fronts', 'n_3prim_dimers', 'min_3prim_dimer', 'min_3prim_dimer_dG']
 
     def __init__(self, seq1, seq2):
@@ -349,6 +385,24 @@ class DimerSet(object):
 
     def __len__(self):
         return len(self.dimers)
+
+
+class HairpinSet(object):
+    """What SecStructures._find_hairpins leaves behind for one sequence (:676-716)."""
+    __slots__ = ['seq', 'hairpins', 'n_3prim_hairpins', 'min_3prim_hairpin', 'min_3prim_hairpin_dG']
+
+    def __init__(self, seq):
+        self.seq = seq
+        self.hairpins = []
+        self.n_3prim_hairpins = 0
+        self.min_3prim_hairpin = None
+        self.min_3prim_hairpin_dG = None
+
+    def __bool__(self):
+        return bool(self.hairpins)
+
+    def __len__(self):
+        return len(self.hairpins)
 
 
 def structure_key(dimer):
@@ -368,38 +422,41 @@ def find_dimers_batch(seqs, pairs, return_ms=False):
     rec, ms = tdf._ctx().find_dimers(strs, pairs, tdf.conditions())
     if np.isnan(rec['best_dG']).any():
         raise ValueError('UnifiedNN.int_dPar_37: sequence is not in the database')
-    out = []
     la = np.array([len(s) for s in strs], dtype=np.int64)
-    has_full = rec['full_mask'] != 0
-    for p, (i, j) in enumerate(pairs):
-        ds = DimerSet(strs[i], strs[j])
-        fwd_len = int(la[i])
-        seen, seen_fronts = set(), set()
-        self_pair = strs[i] == strs[j]
-        for f in np.nonzero(has_full[p])[0]:
-            f = int(f)
-            offset = max(0, fwd_len - f - 1) - max(0, f - fwd_len + 1)
-            r = rec[p, f]
-            if self_pair:
-                full = Dimer(mask_to_matches(r['full_mask']), offset)
-                if structure_key(full) not in seen_fronts:                    # SecStructures.py:643-645
-                    seen_fronts.add(structure_key(full))
-                    ds.fronts.append(full)
-            if not r['best_mask']:
-                continue
-            d = Dimer(mask_to_matches(r['best_mask']), offset)
-            d.dG = float(r['best_dG'])
-            key = structure_key(d)
-            if key in seen:
-                continue
-            seen.add(key)
-            ds.dimers.append(d)
-            if d.fwd_matches[-1] > fwd_len - 4 or d.rev_min < 3:          # SecStructures.py:660-667
-                ds.n_3prim_dimers += 1
-                if ds.min_3prim_dimer_dG is None or ds.min_3prim_dimer_dG > d.dG:
-                    ds.min_3prim_dimer_dG = d.dG
-                    ds.min_3prim_dimer = d
-        out.append(ds)
+    out = [DimerSet(strs[i], strs[j]) for i, j in pairs]
+    is_self = np.array([strs[i] == strs[j] for i, j in pairs], dtype=bool) if len(pairs) else np.zeros(0, bool)
+    # only the entries that lead to an object are visited: stable structures, and the seeds of self pairs
+    want = (rec['best_mask'] != 0) | ((rec['full_mask'] != 0) & is_self[:, None])
+    pp, ff = np.nonzero(want)                                # row-major: pair by pair, fronts ascending
+    fwd_len = la[pairs[pp, 0]] if len(pp) else np.zeros(0, np.int64)
+    offsets = np.maximum(0, fwd_len - ff - 1) - np.maximum(0, ff - fwd_len + 1)
+    full, best, dGs = rec['full_mask'][pp, ff], rec['best_mask'][pp, ff], rec['best_dG'][pp, ff]
+    seen, seen_fronts, last = None, None, -1
+    for p, offset, fm, bm, dG, flen in zip(pp.tolist(), offsets.tolist(), full.tolist(), best.tolist(),
+                                           dGs.tolist(), fwd_len.tolist()):
+        if p != last:
+            seen, seen_fronts, last = set(), set(), p
+        ds = out[p]
+        if is_self[p]:
+            seed = Dimer(mask_to_matches(fm), offset)
+            key = structure_key(seed)
+            if key not in seen_fronts:                                        # SecStructures.py:643-645
+                seen_fronts.add(key)
+                ds.fronts.append(seed)
+        if not bm:
+            continue
+        d = Dimer(mask_to_matches(bm), offset)
+        d.dG = dG
+        key = structure_key(d)
+        if key in seen:
+            continue
+        seen.add(key)
+        ds.dimers.append(d)
+        if d.fwd_matches[-1] > flen - 4 or d.rev_min < 3:                     # SecStructures.py:660-667
+            ds.n_3prim_dimers += 1
+            if ds.min_3prim_dimer_dG is None or ds.min_3prim_dimer_dG > d.dG:
+                ds.min_3prim_dimer_dG = d.dG
+                ds.min_3prim_dimer = d
     return (out, ms) if return_ms else out
 
 
@@ -408,3 +465,185 @@ def find_dimers(seq1, seq2=None):
     if seq2 is None or str(seq1) == str(seq2):
         return find_dimers_batch([seq1], [(0, 0)])[0]
     return find_dimers_batch([seq1, seq2], [(0, 1)])[0]
+
+
+def trim_hairpin_seed(fwd_matches):
+    """The while loop of SecStructures._find_hairpins (:684-690) on the sorted match list m: after t
+    rounds the 5' arm is m[:k-t] and the 3' arm m[t:]; pairs are dropped from the middle until the arms
+    neither cross nor come closer than 4 (3 unpaired bases).  Returns (fwd arm, rev arm)."""
+    m = sorted(fwd_matches)
+    k, t = len(m), 0
+    while t < k and (m[t] < m[k - 1 - t] or m[t] - m[k - 1 - t] < 4):
+        t += 1
+    return m[:k - t], m[t:]
+
+
+def find_hairpins_batch(dimer_sets, return_ms=False):
+    """SecStructures._find_hairpins for the self-dimer seeds (`DimerSet.fronts`) of many sequences in
+    ONE kernel launch (dp_find_hairpins: one warp per seed).  Returns a list of HairpinSet."""
+    seqs = [ds.seq1 for ds in dimer_sets]
+    seed_seq, seed_mask, seed_off = [], [], []
+    for si, ds in enumerate(dimer_sets):
+        L = len(ds.seq1)
+        for seed in ds.fronts:
+            fwd, rev = trim_hairpin_seed(seed.fwd_matches)
+            if not fwd:
+                continue
+            m = 0
+            for f in fwd:
+                m |= 1 << f
+            seed_seq.append(si)
+            seed_mask.append(m)
+            seed_off.append(fwd[0] - (L - 1 - rev[-1]))                       # SecStructures.py:695
+    out = [HairpinSet(s) for s in seqs]
+    ms = 0.0
+    if seed_seq:
+        rec, ms = tdf._ctx_with_hairpin_tables().find_hairpins(seqs, seed_seq, seed_mask, seed_off, tdf.conditions(),
+                                                               max_hairpin_dG)
+        if np.isnan(rec['best_dG']).any():
+            raise ValueError('UnifiedNN.int_dPar_37: sequence is not in the database')
+        seen, last = None, -1
+        for si, off, bm, dG in zip(seed_seq, seed_off, rec['best_mask'].tolist(), rec['best_dG'].tolist()):
+            if si != last:
+                seen, last = set(), si
+            if not bm:
+                continue
+            hs = out[si]
+            L = len(hs.seq)
+            fm = mask_to_matches(bm)
+            h = Hairpin(fm, [L - 1 - (f - off) for f in fm])
+            h.dG = dG
+            key = h.fwd_matches + h.rev_matches                               # _structure_hash: concatenation
+            if key in seen:
+                continue
+            seen.add(key)
+            hs.hairpins.append(h)
+            if h.rev_matches[0] > L - 4:                                      # SecStructures.py:707-713
+                hs.n_3prim_hairpins += 1
+                if hs.min_3prim_hairpin_dG is None or hs.min_3prim_hairpin_dG > dG:
+                    hs.min_3prim_hairpin_dG = dG
+                    hs.min_3prim_hairpin = h
+    return (out, ms) if return_ms else out
+
+
+class SecStructures(object):
+    """Self-dimers and hairpins of one sequence, or cross-dimers of two
+    (DegenPrimer/SecStructures.py:389-605): same constructor, same attributes and query methods;
+    the report formatting (`_format_*`, :720-871) stays with the reference's reporters.
+    `SecStructures.batch(records, pairs)` builds many of them from two kernel launches."""
+
+    def __init__(self, seq_rec1, seq_rec2=None, _dimer_set=None, _hairpin_set=None):
+        self._seq_rec1 = seq_rec1
+        self._seq1 = seq_rec1.seq
+        if seq_rec2 and str(seq_rec1.seq) != str(seq_rec2.seq):
+            self._seq_rec2 = seq_rec2
+            self._seq2 = seq_rec2.seq
+        else:
+            self._seq_rec2 = None
+            self._seq2 = None
+        if _dimer_set is None:
+            _dimer_set = find_dimers(str(self._seq1), None if self._seq2 is None else str(self._seq2))
+        if self._seq2 is None and _hairpin_set is None:
+            _hairpin_set = find_hairpins_batch([_dimer_set])[0]
+        self._fill(_dimer_set, _hairpin_set)
+
+    def _fill(self, ds, hs):
+        dimers = dict((self._structure_hash(d), d) for d in ds.dimers)
+        self._3prim_dimers = ds.n_3prim_dimers
+        self._min_3prim_dimer_dG = ds.min_3prim_dimer_dG
+        self._min_3prim_dimer = ds.min_3prim_dimer
+        self._3prim_hairpins = 0
+        self._min_3prim_hairpin_dG = None
+        self._min_3prim_hairpin = None
+        if self._seq2 is not None:
+            self._seq1_dimers = None
+            self._seq1_hairpins = None
+            self._cross_dimers = dimers
+        else:
+            self._seq1_dimers = dimers
+            self._seq1_hairpins = dict((self._structure_hash(h), h) for h in hs.hairpins)
+            self._cross_dimers = None
+            self._3prim_hairpins = hs.n_3prim_hairpins
+            self._min_3prim_hairpin_dG = hs.min_3prim_hairpin_dG
+            self._min_3prim_hairpin = hs.min_3prim_hairpin
+
+    @classmethod
+    def batch(cls, records, pairs):
+        """[SecStructures(records[i], records[j]) for i, j in pairs] (i == j: self structures) with one
+        dp_find_dimers and one dp_find_hairpins launch for all of them (AllSecStructures.py:90-121)."""
+        pairs = [(int(i), int(j)) for i, j in pairs]
+        sets = find_dimers_batch([str(r.seq) for r in records], pairs)
+        selfs = [k for k, (i, j) in enumerate(pairs) if str(records[i].seq) == str(records[j].seq)]
+        hsets = dict(zip(selfs, find_hairpins_batch([sets[k] for k in selfs])))
+        return [cls(records[i], records[j], _dimer_set=sets[k], _hairpin_set=hsets.get(k))
+                for k, (i, j) in enumerate(pairs)]
+
+    def _structure_hash(self, struct):
+        rev = struct.rev_matches
+        key = struct.fwd_matches + rev if isinstance(rev, tuple) else structure_key(struct)
+        if not self._seq_rec2:
+            return hash((str(self._seq1), tuple(key)))
+        return hash((str(self._seq1), str(self._seq2), tuple(key)))
+
+    def __bool__(self):
+        if self._seq2 and self._cross_dimers:
+            return True
+        return bool(self._seq1_dimers or self._seq1_hairpins)
+
+    def __contains__(self, s_hash):
+        if not self._seq_rec2:
+            return s_hash in self._seq1_dimers or s_hash in self._seq1_hairpins
+        return s_hash in self._cross_dimers
+
+    def compose_reactions(self):
+        """SecStructures.py:439-466."""
+        reactions = dict()
+        T = tdf.PCR_P.PCR_T
+        if not self._seq_rec2:
+            for h, D in (self._seq1_dimers or {}).items():
+                reactions[h] = Reaction(tdf.equilibrium_constant(D.dG, T), str(self._seq1), None, '2A')
+            for h, H in (self._seq1_hairpins or {}).items():
+                reactions[h] = Reaction(tdf.equilibrium_constant(H.dG, T), str(self._seq1), None, 'A')
+        else:
+            for h, D in (self._cross_dimers or {}).items():
+                reactions[h] = Reaction(tdf.equilibrium_constant(D.dG, T), str(self._seq1), str(self._seq2), 'AB')
+        return reactions
+
+    def set_conversion_degree(self, s_hash, r):
+        """SecStructures.py:469-482."""
+        if not self._seq_rec2:
+            for table in (self._seq1_dimers, self._seq1_hairpins):
+                if s_hash in table:
+                    table[s_hash].conversion_degree = r
+                    return True
+        elif s_hash in self._cross_dimers:
+            self._cross_dimers[s_hash].conversion_degree = r
+            return True
+
+    def max_conversion_degree(self):
+        if self._seq_rec2 and self._cross_dimers:
+            return max(s.conversion_degree for s in self._cross_dimers.values())
+        CG = 0
+        if self._seq1_dimers:
+            CG += max(s.conversion_degree for s in self._seq1_dimers.values())
+        if self._seq1_hairpins:
+            CG += max(s.conversion_degree for s in self._seq1_hairpins.values())
+        return CG if CG else None
+
+    def dimerMin_dG(self):
+        if self._seq_rec2 and self._cross_dimers:
+            return min(s.dG for s in self._cross_dimers.values())
+        if self._seq1_dimers:
+            return min(s.dG for s in self._seq1_dimers.values())
+        return None
+
+    def dimerMin_3prim_dG(self):
+        return self._min_3prim_dimer_dG if self._min_3prim_dimer_dG else None
+
+    def hairpinMin_dG(self):
+        if self._seq_rec2 or not self._seq1_hairpins:
+            return None
+        return min(s.dG for s in self._seq1_hairpins.values())
+
+    def hairpinMin_3prim_dG(self):
+        return self._min_3prim_hairpin_dG if self._min_3prim_hairpin_dG else None

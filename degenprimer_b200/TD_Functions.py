@@ -89,6 +89,12 @@ def _ctx():
     return ctx
 
 
+def _ctx_with_hairpin_tables():
+    ctx = _ctx()
+    ctx.load_hairpin_tables(UnifiedNN.hairpin_device_tables(), key=UnifiedNN._version)
+    return ctx
+
+
 def new_context(device=None):
     """A further native context on a device (own stream, workspaces and result buffers) with
     the current NN tables loaded: one per call that is to be in flight on the GPU at the same

@@ -54,6 +54,7 @@ class UnifiedNN(object):
     internal_NN = None
     dangling_ends = None
     loops = None
+    tri_tetra_hairpin_loops = None
     ter = Pars()
     ini = Pars()
     sym = Pars()
@@ -82,13 +83,17 @@ class UnifiedNN(object):
             stacks = {k: Pars(*v) for k, v in nn_data.STACKS.items()}
             ends = {k: Pars(*v) for k, v in nn_data.DANGLING_ENDS.items()}
             loops = {k: Loops(*v) for k, v in nn_data.LOOPS.items()}
+            tri_tetra = {k: Pars(dH=v[0], dG=v[1]) for k, v in nn_data.TRI_TETRA_HAIRPIN_LOOPS.items()}
         else:
             stacks = {k: Pars(**v) for k, v in cls._read_csv(os.path.join(directory, 'internal-NN.csv')).items()}
             ends = {k: Pars(**v) for k, v in cls._read_csv(os.path.join(directory, 'dangling-ends.csv')).items()}
             loops = {int(k): Loops(**v) for k, v in cls._read_csv(os.path.join(directory, 'loops.csv')).items()}
+            tri_tetra = {k: Pars(**v) for k, v in
+                         cls._read_csv(os.path.join(directory, '3-4-hairpin-loops.csv')).items()}
         for k in list(stacks):            # UnifiedNN.py:214-215
             stacks[k[::-1]] = stacks[k]
         cls.internal_NN, cls.dangling_ends, cls.loops = stacks, ends, loops
+        cls.tri_tetra_hairpin_loops = tri_tetra
         cls.ter = stacks.get('ter', Pars())
         cls.ini = stacks.get('ini', Pars())
         cls.sym = stacks.get('sym', Pars())
@@ -151,7 +156,72 @@ class UnifiedNN(object):
     def dG_T(cls, dH, dS, temperature):
         return dH - (temperature - cls.K0) * dS / 1000.0
 
+    @classmethod
+    def hairpin_loop_dG_37(cls, seq):
+        """UnifiedNN.py:279-307; seq includes the closing pair."""
+        length = len(seq) - 2
+        if length in cls.loops:
+            loop_dG = cls.loops[length].hairpin
+            if length == 3:
+                if seq in cls.tri_tetra_hairpin_loops:
+                    loop_dG += cls.tri_tetra_hairpin_loops[seq].dG
+                if seq[0] in 'AT':
+                    loop_dG += 0.5
+            elif length == 4:
+                if seq in cls.tri_tetra_hairpin_loops:
+                    loop_dG += cls.tri_tetra_hairpin_loops[seq].dG
+                loop_dG += cls.Terminal_mismatch_mean
+            else:
+                loop_dG += cls.Terminal_mismatch_mean
+            return loop_dG
+        return cls._extrapolate_loop_dG_37(length, 'hairpin') + cls.Terminal_mismatch_mean
+
+    @classmethod
+    def hairpin_loop_dH_37(cls, seq):
+        """UnifiedNN.py:310-315."""
+        if len(seq) - 2 > 4:
+            return 0
+        try:
+            return cls.tri_tetra_hairpin_loops[seq].dH
+        except KeyError:
+            return 0
+
+    @classmethod
+    def hairpin_loop_dS_37(cls, seq):
+        return (cls.hairpin_loop_dG_37(seq) - cls.hairpin_loop_dH_37(seq)) * cls.iK37
+
     # ---- device block --------------------------------------------------------------
+    @classmethod
+    def hairpin_device_tables(cls):
+        """dp_hairpin_tables filled exactly as dp_hairpin_dg_device indexes it."""
+        if not cls._inited:
+            cls.load_tables()
+        t = nat.dp_hairpin_tables()
+        nan = float('nan')
+        for n in range(64):
+            if n < 3:
+                t.loop_dG[n] = nan
+            elif n in cls.loops:
+                t.loop_dG[n] = cls.loops[n].hairpin
+            else:
+                t.loop_dG[n] = cls._extrapolate_loop_dG_37(n, 'hairpin')
+        for i in range(1024):
+            t.tri_dH[i] = t.tri_dG[i] = nan
+        for i in range(4096):
+            t.tetra_dH[i] = t.tetra_dG[i] = nan
+        for key, p in cls.tri_tetra_hairpin_loops.items():
+            idx = 0
+            for c in key:
+                idx = idx * 4 + nat.BASES.index(c)
+            if len(key) == 5:
+                t.tri_dH[idx], t.tri_dG[idx] = p.dH, p.dG
+            elif len(key) == 6:
+                t.tetra_dH[idx], t.tetra_dG[idx] = p.dH, p.dG
+            else:
+                raise ValueError('3-4-hairpin-loops: key %r is neither a tri- nor a tetra-loop' % key)
+        t.iK37 = cls.iK37
+        return t
+
     @classmethod
     def device_tables(cls):
         """dp_nn_tables filled exactly as the kernels index it."""

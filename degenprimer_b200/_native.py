@@ -82,6 +82,11 @@ class dp_nn_tables(C.Structure):
                 ('K0', C.c_double), ('T_DMSO', C.c_double)]
 
 
+class dp_hairpin_tables(C.Structure):
+    _fields_ = [('loop_dG', C.c_double * 64), ('tri_dH', C.c_double * 1024), ('tri_dG', C.c_double * 1024),
+                ('tetra_dH', C.c_double * 4096), ('tetra_dG', C.c_double * 4096), ('iK37', C.c_double)]
+
+
 class dp_conditions(C.Structure):
     _fields_ = [('PCR_T', C.c_double), ('Na_eq_log', C.c_double), ('max_dimer_dG', C.c_double),
                 ('max_dG_for_K', C.c_double), ('DNA', C.c_double), ('DMSO', C.c_double)]
@@ -94,6 +99,7 @@ DIMER_DTYPE = np.dtype([('hit', '<u4'), ('variant', '<u4'), ('match_mask', '<u8'
 WIRE_DTYPE = np.dtype([('g', '<u8'), ('record', '<u4'), ('pattern', '<u2'), ('score3', '<u2'),
                        ('pair_base', '<u4'), ('reserved', '<u4')], align=True)
 WIRE_HEADER_BYTES = 64
+BEST_STRUCTURE_DTYPE = np.dtype([('best_mask', '<u8'), ('best_dG', '<f8')], align=True)
 FRONT_DIMER_DTYPE = np.dtype([('full_mask', '<u8'), ('best_mask', '<u8'), ('best_dG', '<f8')], align=True)
 assert HIT_DTYPE.itemsize == 16 and DIMER_DTYPE.itemsize == 24 and WIRE_DTYPE.itemsize == 24
 assert FRONT_DIMER_DTYPE.itemsize == 24
@@ -150,6 +156,9 @@ def _declare(lib):
         'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
         'dp_dimer_dg': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_void_p, P(dp_conditions), C.c_void_p]),
+        'dp_hairpin_tables_load': (i32, [vp, P(dp_hairpin_tables)]),
+        'dp_find_hairpins': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, u32, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, P(dp_conditions), C.c_double, C.c_void_p, P(C.c_float)]),
         'dp_find_dimers': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, u32, C.c_void_p, C.c_void_p,
                                  P(dp_conditions), u32, C.c_void_p, P(C.c_float)]),
     }
@@ -165,7 +174,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
            'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
-           'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_calibrate').split()
+           'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
 
 
 def load():
@@ -572,6 +581,29 @@ class Context(object):
                                          _ptr(mk), _ptr(of), C.byref(cond), _ptr(out)))
         return out
 
+
+    def load_hairpin_tables(self, tables, key=None):
+        if key is not None and key == getattr(self, '_hp_tables_key', None):
+            return
+        self._check(self.lib.dp_hairpin_tables_load(self._h, C.byref(tables)))
+        self._hp_tables_key = key
+
+    def find_hairpins(self, seqs, seed_seq, seed_mask, seed_offset, cond, max_hairpin_dG):
+        """dp_find_hairpins: returns (BEST_STRUCTURE_DTYPE[n_seeds], kernel ms)."""
+        ln = np.array([len(s) for s in seqs], dtype=np.uint8)
+        if any(len(s) > 64 for s in seqs):
+            raise ValueError('sequences longer than 64 nt are not supported by dp_find_hairpins')
+        off = np.concatenate(([0], np.cumsum(ln, dtype=np.uint64)[:-1])).astype(np.uint64)
+        blob = ''.join(seqs).encode('ascii')
+        sq = np.ascontiguousarray(seed_seq, dtype=np.uint32)
+        mk = np.ascontiguousarray(seed_mask, dtype=np.uint64)
+        so = np.ascontiguousarray(seed_offset, dtype=np.int32)
+        out = np.zeros(len(sq), dtype=BEST_STRUCTURE_DTYPE)
+        ms = C.c_float(0.0)
+        self._check(self.lib.dp_find_hairpins(self._h, len(seqs), C.cast(C.c_char_p(blob), C.c_void_p), _ptr(off),
+                                              _ptr(ln), len(sq), _ptr(sq), _ptr(mk), _ptr(so), C.byref(cond),
+                                              float(max_hairpin_dG), _ptr(out), C.byref(ms)))
+        return out, float(ms.value)
 
     def find_dimers(self, seqs, pairs, cond):
         """dp_find_dimers: `seqs` list of str, `pairs` (n, 2) indices into it.  Returns

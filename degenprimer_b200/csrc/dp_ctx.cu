@@ -172,6 +172,8 @@ dp_ctx* dp_create(int device_ordinal) {
   ctx->abort_flag = 0;
   ctx->tables_loaded = false;
   ctx->d_tables = nullptr;
+  ctx->d_hp_tables = nullptr;
+  ctx->hp_tables_loaded = false;
   ctx->pool = nullptr;
   ctx->d_hits = nullptr;  ctx->hits_cap = 0;
   ctx->d_dir = nullptr;   ctx->dir_cap = 0;
@@ -249,6 +251,7 @@ void dp_destroy(dp_ctx* ctx) {
   if (ctx->d_codes) cudaFree(ctx->d_codes);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->d_tables) cudaFree(ctx->d_tables);
+  if (ctx->d_hp_tables) cudaFree(ctx->d_hp_tables);
   if (ctx->h_res) cudaFreeHost(ctx->h_res);
   if (ctx->pending && ctx->pending_free) ctx->pending_free(ctx->pending);
   cudaEventDestroy(ctx->ev0);

@@ -588,6 +588,166 @@ dp_find_dimers_kernel(dp_dg_args A, const uint8_t* __restrict__ codes, const uin
   }
 }
 
+// ---- hairpins of one primer ---------------------------------------------
+// hairpin_dG_corrected, DegenPrimer/TD_Functions.py:209-276, with UnifiedNN.hairpin_loop_dG/dH/dS_37
+// (DegenPrimer/UnifiedNN.py:279-325).  s: the sequence (letter codes, 5'->3'), mask: stem positions
+// of the 5' arm, off: Dimer.offset of the self-dimer the hairpin folds from — position f pairs with
+// L-1-(f-off).  NaN where the reference would raise.
+__device__ double dp_hairpin_dg_device(const dp_dg_args& A, const dp_hairpin_tables* __restrict__ H,
+                                       const uint8_t* s, int L, uint64_t mask, int off) {
+  const dp_nn_tables& T = *A.T;
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  if (!mask) return nan;
+  const int f0 = __ffsll((long long)mask) - 1;
+  const int f1 = 63 - __clzll((long long)mask);
+  const int r0 = L - 1 - (f0 - off);
+  const int r1 = L - 1 - (f1 - off);
+  if (r0 < 0 || r0 >= L || r1 <= f1) return nan;
+  double dG = 0.0, dH = T.ini_dH, dS = T.ini_dS;
+  bool bad = false;
+  // open end of the stem — TD_Functions.py:227-244
+  if (f0 == 0 && r0 < L - 1) {
+    uint32_t x = s[r0], y = s[r0 + 1], z = s[0];
+    if (x > 3 || y > 3 || z > 3) bad = true;
+    else { dH = f64_add(dH, T.dangling_dH[1][x][y][z]); dS = f64_add(dS, T.dangling_dS[1][x][y][z]); }
+  } else if (f0 > 0 && r0 == L - 1) {
+    uint32_t x = s[f0 - 1], y = s[f0], z = s[L - 1];
+    if (x > 3 || y > 3 || z > 3) bad = true;
+    else { dH = f64_add(dH, T.dangling_dH[0][x][y][z]); dS = f64_add(dS, T.dangling_dS[0][x][y][z]); }
+  } else if (f0 > 0 && r0 < L - 1) {
+    dG = f64_add(dG, T.terminal_mismatch);
+  } else {
+    if (s[0] == 0 || s[0] == 2) { dH = f64_add(dH, T.ter_dH); dS = f64_add(dS, T.ter_dS); }
+  }
+  // stacks, |x|, |xx| and internal loops — TD_Functions.py:246-267
+  uint64_t m = mask & (mask - 1);
+  int a = f0;
+  while (m) {
+    const int b = __ffsll((long long)m) - 1;
+    m &= m - 1;
+    const int gap = b - a;
+    const int ra = L - 1 - (a - off), rb = L - 1 - (b - off);
+    if (gap < 4) {
+      uint32_t x = s[a], y = s[a + 1], z = s[ra], w = s[ra - 1];
+      if (x > 3 || y > 3 || w > 14 || z != dp_letter_complement(x)) bad = true;
+      else { dH = f64_add(dH, T.stack_dH[x][y][w]); dS = f64_add(dS, T.stack_dS[x][y][w]); }
+      if (gap > 1) {
+        uint32_t x2 = s[b - 1], y2 = s[b], z2 = s[rb], w2 = s[rb + 1];
+        if (x2 > 3 || y2 > 3 || w2 > 14 || z2 != dp_letter_complement(y2)) bad = true;
+        else { dH = f64_add(dH, T.rstack_dH[x2][y2][w2]); dS = f64_add(dS, T.rstack_dS[x2][y2][w2]); }
+      }
+    } else {
+      dS = f64_add(dS, T.loop_dS[gap - 1]);
+    }
+    a = b;
+  }
+  // the loop: hp = s[f1 .. r1], n unpaired bases — UnifiedNN.py:279-325
+  const int n = r1 - f1 - 1;
+  double loop_dH = 0.0, loop_dG = H->loop_dG[n < 63 ? n : 63];
+  double sp_dH = nan, sp_dG = nan;                  // special tri-/tetra-loop row, if any
+  if (n == 3 || n == 4) {
+    uint32_t idx = 0;
+    bool plain = true;
+    for (int i = f1; i <= r1; ++i) { plain &= s[i] <= 3; idx = idx * 4 + (s[i] & 3u); }
+    if (plain) {
+      sp_dH = n == 3 ? H->tri_dH[idx] : H->tetra_dH[idx];
+      sp_dG = n == 3 ? H->tri_dG[idx] : H->tetra_dG[idx];
+    }
+  }
+  if (n == 3) {
+    if (sp_dG == sp_dG) loop_dG = f64_add(loop_dG, sp_dG);
+    if (s[f1] == 0 || s[f1] == 2) loop_dG = f64_add(loop_dG, 0.5);      // AT-closing penalty
+  } else if (n == 4) {
+    if (sp_dG == sp_dG) loop_dG = f64_add(loop_dG, sp_dG);
+    loop_dG = f64_add(loop_dG, T.terminal_mismatch);
+  } else {
+    loop_dG = f64_add(loop_dG, T.terminal_mismatch);
+  }
+  if (sp_dH == sp_dH) loop_dH = sp_dH;
+  dH = f64_add(dH, loop_dH);
+  dS = f64_add(dS, f64_mul(f64_add(loop_dG, -loop_dH), H->iK37));
+  dS = f64_add(dS, f64_mul(f64_mul(T.dS_Na, (double)(f1 - f0)), A.Na_eq_log));
+  const double tds = __ddiv_rn(f64_mul(f64_add(A.PCR_T, -T.K0), dS), 1000.0);
+  const double res = f64_add(f64_add(dG, dH), -tds);
+  return bad ? nan : res;
+}
+
+// SecStructures._find_hairpins, DegenPrimer/SecStructures.py:676-716, the part after the seed has been
+// trimmed (a few set operations, done by the caller): of [stem] + stem.alternatives the hairpin with
+// the lowest dG strictly below max_hairpin_dG.  One WARP per seed, lane d evaluates candidate d.
+__global__ void __launch_bounds__(DP_DUPLEX_THREADS)
+dp_find_hairpins_kernel(dp_dg_args A, const dp_hairpin_tables* __restrict__ H, double max_hairpin_dG,
+                        const uint8_t* __restrict__ codes, const uint64_t* __restrict__ seq_off,
+                        const uint8_t* __restrict__ seq_len, const uint32_t* __restrict__ seed_seq,
+                        const uint64_t* __restrict__ seed_mask, const int32_t* __restrict__ seed_offset,
+                        uint32_t n_seeds, dp_best_structure* __restrict__ out) {
+  __shared__ dp_nn_tables sT;
+  __shared__ dp_fd_scratch sW[DP_DUPLEX_WARPS];
+  {
+    const uint64_t* src = reinterpret_cast<const uint64_t*>(A.T);
+    uint64_t* dst = reinterpret_cast<uint64_t*>(&sT);
+    for (uint32_t i = threadIdx.x; i < sizeof(dp_nn_tables) / 8; i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  dp_dg_args G = A;
+  G.T = &sT;
+  const uint32_t lane = threadIdx.x & 31u;
+  dp_fd_scratch& W = sW[threadIdx.x >> 5];
+  const uint32_t n_warps = gridDim.x * DP_DUPLEX_WARPS;
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  for (uint32_t seed = blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); seed < n_seeds; seed += n_warps) {
+    const uint32_t si = seed_seq[seed];
+    const int L = seq_len[si];
+    const uint64_t M = seed_mask[seed];
+    const int off = seed_offset[seed];
+    dp_best_structure res;
+    res.best_mask = 0; res.best_dG = 0.0;
+    __syncwarp();
+    if (!M) {
+      if (lane == 0) out[seed] = res;
+      continue;
+    }
+    const uint8_t* cs = codes + seq_off[si];
+    for (int i = (int)lane; i < L; i += 32) W.s[i] = cs[i];
+    const uint64_t S = M & ~(M << 1);
+    const uint64_t Eb = M & ~(M >> 1);
+    const int n = __popcll(S);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int i = (int)lane + 32 * half;
+      const uint64_t below = (1ull << i) - 1ull;
+      if ((S >> i) & 1ull) W.run_start[__popcll(S & below)] = (uint8_t)i;
+      if ((Eb >> i) & 1ull) W.run_end[__popcll(Eb & below)] = (uint8_t)i;
+    }
+    __syncwarp();
+    const uint32_t n_cand = (uint32_t)(n * (n + 1) / 2);
+    double best = max_hairpin_dG;
+    uint32_t best_d = 0xFFFFFFFFu;
+    bool bad = false;
+    for (uint32_t d = lane; d < n_cand; d += 32) {
+      const uint64_t sub = dp_nth_dimer(M, n, d, W.run_start, W.run_end);
+      const double dG = dp_hairpin_dg_device(G, H, W.s, L, sub, off);
+      if (dG != dG) bad = true;
+      if (best > dG) { best = dG; best_d = d; }
+    }
+#pragma unroll
+    for (int sh = 16; sh > 0; sh >>= 1) {
+      const double ob = __shfl_xor_sync(0xFFFFFFFFu, best, sh);
+      const uint32_t od = __shfl_xor_sync(0xFFFFFFFFu, best_d, sh);
+      if (ob < best || (ob == best && od < best_d)) { best = ob; best_d = od; }
+    }
+    bad = __any_sync(0xFFFFFFFFu, bad);
+    if (lane == 0) {
+      if (bad) res.best_dG = nan;
+      else if (best_d != 0xFFFFFFFFu) {
+        res.best_mask = dp_nth_dimer(M, n, best_d, W.run_start, W.run_end);
+        res.best_dG = best;
+      }
+      out[seed] = res;
+    }
+  }
+}
+
 // ---- host ----------------------------------------------------------------------------
 // scratch from the context's stream-ordered pool (freed in stream order, no sync)
 template <typename T>
@@ -789,6 +949,86 @@ extern "C" int dp_find_dimers(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, co
   cudaError_t le = cudaGetLastError();
   if (ms_kernel && le == cudaSuccess) le = cudaEventRecord(e1, st);
   if (le == cudaSuccess) le = cudaMemcpyAsync(out, d_out.p, n_items * sizeof(dp_front_dimer), cudaMemcpyDeviceToHost, st);
+  if (le == cudaSuccess) le = cudaStreamSynchronize(st);
+  if (ms_kernel && le == cudaSuccess) le = cudaEventElapsedTime(ms_kernel, e0, e1);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  DP_CUDA(ctx, le);
+  return DP_OK;
+}
+
+extern "C" int dp_hairpin_tables_load(dp_ctx* ctx, const dp_hairpin_tables* tables) {
+  if (!ctx || !tables) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->d_hp_tables) DP_CUDA(ctx, cudaMalloc(&ctx->d_hp_tables, sizeof(dp_hairpin_tables)));
+  DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_hp_tables, tables, sizeof(dp_hairpin_tables), cudaMemcpyHostToDevice, ctx->stream));
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->hp_tables_loaded = true;
+  return DP_OK;
+}
+
+extern "C" int dp_find_hairpins(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, const uint64_t* off, const uint8_t* len,
+                                uint32_t n_seeds, const uint32_t* seed_seq, const uint64_t* seed_mask,
+                                const int32_t* seed_offset, const dp_conditions* cond, double max_hairpin_dG,
+                                dp_best_structure* out, float* ms_kernel) {
+  if (!ctx || !seqs || !off || !len || !cond || (n_seeds && (!seed_seq || !seed_mask || !seed_offset || !out)))
+    return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (!ctx->tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_tables_load() has not been called");
+  if (!ctx->hp_tables_loaded) return dp_set_error(ctx, DP_ERR_STATE, "dp_hairpin_tables_load() has not been called");
+  if (ms_kernel) *ms_kernel = 0.f;
+  if (n_seeds == 0) return DP_OK;
+  uint64_t bytes = 0;
+  for (uint32_t i = 0; i < n_seqs; ++i) {
+    if (len[i] == 0 || len[i] > DP_WIN)
+      return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "sequence %u: length outside [1,%d]", i, DP_WIN);
+    bytes = std::max<uint64_t>(bytes, off[i] + len[i]);
+  }
+  for (uint32_t k = 0; k < n_seeds; ++k) {
+    if (seed_seq[k] >= n_seqs) return dp_set_error(ctx, DP_ERR_ARG, "seed %u: sequence index out of range", k);
+    const int L = len[seed_seq[k]];
+    const uint64_t m = seed_mask[k];
+    if (L < 64 && (m >> L)) return dp_set_error(ctx, DP_ERR_ARG, "seed %u: stem position beyond the sequence", k);
+    if (m) {
+      // every stem position f must pair with L-1-(f-offset) 3' of the whole 5' arm, >= 3 bases apart
+      const int f0 = __builtin_ctzll(m), f1 = 63 - __builtin_clzll(m);
+      const int r0 = L - 1 - (f0 - seed_offset[k]), r1 = L - 1 - (f1 - seed_offset[k]);
+      if (r0 < 0 || r0 >= L || r1 - f1 < 4)
+        return dp_set_error(ctx, DP_ERR_ARG, "seed %u: stem arms overlap or leave fewer than 3 loop bases", k);
+    }
+  }
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::vector<uint8_t> codes;
+  int rc = letters_of(ctx, seqs, bytes, codes, false);
+  if (rc) return rc;
+  dev_buf<uint8_t> d_codes, d_len;
+  dev_buf<uint64_t> d_off, d_mask;
+  dev_buf<uint32_t> d_seq;
+  dev_buf<int32_t> d_so;
+  dev_buf<dp_best_structure> d_out;
+  DP_CUDA(ctx, d_codes.alloc(ctx, bytes)); DP_CUDA(ctx, d_len.alloc(ctx, n_seqs)); DP_CUDA(ctx, d_off.alloc(ctx, n_seqs));
+  DP_CUDA(ctx, d_seq.alloc(ctx, n_seeds)); DP_CUDA(ctx, d_mask.alloc(ctx, n_seeds)); DP_CUDA(ctx, d_so.alloc(ctx, n_seeds));
+  DP_CUDA(ctx, d_out.alloc(ctx, n_seeds));
+  cudaStream_t st = ctx->stream;
+  DP_CUDA(ctx, cudaMemcpyAsync(d_codes.p, codes.data(), bytes, cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_len.p, len, n_seqs, cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_off.p, off, n_seqs * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_seq.p, seed_seq, n_seeds * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_mask.p, seed_mask, n_seeds * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  DP_CUDA(ctx, cudaMemcpyAsync(d_so.p, seed_offset, n_seeds * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (ms_kernel) {
+    DP_CUDA(ctx, cudaEventCreate(&e0));
+    DP_CUDA(ctx, cudaEventCreate(&e1));
+    DP_CUDA(ctx, cudaEventRecord(e0, st));
+  }
+  const uint64_t blocks_needed = ((uint64_t)n_seeds + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS;
+  const unsigned grid = (unsigned)std::min<uint64_t>(blocks_needed, (uint64_t)ctx->sm_count * 16);
+  dp_dg_args A = make_args(ctx, cond);
+  dp_find_hairpins_kernel<<<grid, DP_DUPLEX_THREADS, 0, st>>>(A, ctx->d_hp_tables, max_hairpin_dG, d_codes.p, d_off.p, d_len.p,
+                                                              d_seq.p, d_mask.p, d_so.p, n_seeds, d_out.p);
+  cudaError_t le = cudaGetLastError();
+  if (ms_kernel && le == cudaSuccess) le = cudaEventRecord(e1, st);
+  if (le == cudaSuccess) le = cudaMemcpyAsync(out, d_out.p, (size_t)n_seeds * sizeof(dp_best_structure), cudaMemcpyDeviceToHost, st);
   if (le == cudaSuccess) le = cudaStreamSynchronize(st);
   if (ms_kernel && le == cudaSuccess) le = cudaEventElapsedTime(ms_kernel, e0, e1);
   if (e0) cudaEventDestroy(e0);

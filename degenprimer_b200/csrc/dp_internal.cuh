@@ -72,6 +72,8 @@ struct dp_ctx {
   volatile int abort_flag;
   bool tables_loaded;
   dp_nn_tables* d_tables;      // device copy
+  bool hp_tables_loaded;
+  dp_hairpin_tables* d_hp_tables;   // hairpin-loop tables (global memory, 81 KB), allocated on first load
   cudaMemPool_t pool;          // stream-ordered pool: template planes, scratch
   // grow-only workspace of the scan / duplex stages
   dp_raw_hit* d_hits;

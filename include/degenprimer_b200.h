@@ -412,6 +412,39 @@ int dp_find_dimers(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, const uint64_
                    const uint32_t* pair_b, const dp_conditions* cond, uint32_t stride,
                    dp_front_dimer* out, float* ms_kernel);
 
+/* SURVEY §8(f) N3 — hairpins of a primer: SecStructures._find_hairpins
+ * (DegenPrimer/SecStructures.py:676-716) with hairpin_dG_corrected
+ * (DegenPrimer/TD_Functions.py:209-276) and UnifiedNN.hairpin_loop_dG/dH/dS_37
+ * (DegenPrimer/UnifiedNN.py:279-325).  Tables: data/loops.csv (hairpin column) and
+ * data/3-4-hairpin-loops.csv, flattened by the host (degenprimer_b200/UnifiedNN.py). */
+typedef struct dp_hairpin_tables {
+  /* loops[n].hairpin, or its extrapolation (UnifiedNN.py:254-261), n = unpaired bases
+   * (index 63 also serves longer loops); NaN for n < 3 */
+  double loop_dG[64];
+  /* special tri-/tetra-loops, key = closing pair + loop letters (5 / 6 bases) read as a
+   * base-4 number, first letter most significant, A=0 C=1 T=2 G=3; NaN = no row */
+  double tri_dH[1024], tri_dG[1024];
+  double tetra_dH[4096], tetra_dG[4096];
+  double iK37;                /* -1000 / 310.15, UnifiedNN.py:135 */
+} dp_hairpin_tables;
+int dp_hairpin_tables_load(dp_ctx* ctx, const dp_hairpin_tables* tables);
+
+typedef struct dp_best_structure {
+  uint64_t best_mask;         /* 0 = nothing below the threshold */
+  double best_dG;             /* NaN where the reference raises */
+} dp_best_structure;
+/* Seed k: sequence seed_seq[k] (index into seqs/off/len as for dp_find_dimers), stem
+ * positions of the 5' arm seed_mask[k] and Dimer.offset seed_offset[k] of the symmetric
+ * self-dimer it folds from — position f pairs with len-1-(f-offset); the caller has
+ * already dropped the innermost pairs until >= 3 bases are left in the loop
+ * (SecStructures.py:684-690).  out[k]: of [stem] + stem.alternatives the hairpin with the
+ * lowest dG strictly below max_hairpin_dG (3 kcal/mol in the reference). */
+int dp_find_hairpins(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, const uint64_t* off,
+                     const uint8_t* len, uint32_t n_seeds, const uint32_t* seed_seq,
+                     const uint64_t* seed_mask, const int32_t* seed_offset,
+                     const dp_conditions* cond, double max_hairpin_dG,
+                     dp_best_structure* out, float* ms_kernel);
+
 /* ---- roofline calibration -------------------------------------------------------
  * Measured issue rate of the pipes the scan kernels live on (the
  * integer roofline's denominators must be measured on the box).

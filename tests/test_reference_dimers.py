@@ -112,3 +112,78 @@ def test_oracle_find_hairpins_equals_reference():
         assert n3 == case['n_3prim_hairpins']
         n += len(hairpins)
     assert n > 50
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('cname', sorted(REF['conds']))
+def test_gpu_hairpins_and_secstructures_equal_reference(cname):
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200.SecStructures import SecStructures, find_dimers_batch, find_hairpins_batch
+    from degenprimer_b200.SeqUtils import SeqRecord, Seq
+    tdf.PCR_P.set(REF['conds'][cname])
+    cases = [c for c in REF['cases'] if c['cond'] == cname]
+    selfs = [c for c in cases if 'hairpins' in c]
+    sets = find_dimers_batch(SEQS, [(c['a'], c['a']) for c in selfs])
+    hsets = find_hairpins_batch(sets)                                       # one launch for all seeds
+    n = 0
+    for c, hs in zip(selfs, hsets):
+        assert [[list(h.fwd_matches), list(h.rev_matches)] for h in hs.hairpins] == [x[:2] for x in c['hairpins']]
+        for h, (_, _, dG) in zip(hs.hairpins, c['hairpins']):
+            assert abs(h.dG - dG) <= 0.01 and abs(h.dG - dG) < 1e-9
+        assert hs.n_3prim_hairpins == c['n_3prim_hairpins']
+        n += len(hs.hairpins)
+    assert n == sum(len(c['hairpins']) for c in selfs) > 10
+    # the drop-in class, one by one and batched
+    recs = [SeqRecord(Seq(s), id='s%d' % i) for i, s in enumerate(SEQS)]
+    some = [c for c in cases if c['dimers'] or c.get('hairpins')][:12] + cases[:4]
+    objs = SecStructures.batch(recs, [(c['a'], c['b']) for c in some])
+    objs += [SecStructures(recs[c['a']], None if c['a'] == c['b'] else recs[c['b']]) for c in some[:5]]
+    for c, o in zip(some + some[:5], objs):
+        d = o._seq1_dimers if c['a'] == c['b'] else o._cross_dimers
+        assert len(d) == len(c['dimers']) and o._3prim_dimers == c['n_3prim']
+        assert sorted(x.dG for x in d.values()) == pytest.approx(sorted(x[2] for x in c['dimers']), abs=1e-9)
+        want_min = min((x[2] for x in c['dimers']), default=None)
+        assert (o.dimerMin_dG() is None) == (want_min is None)
+        if want_min is not None:
+            assert abs(o.dimerMin_dG() - want_min) < 1e-9
+        if c['a'] == c['b']:
+            assert len(o._seq1_hairpins) == len(c['hairpins']) and o._3prim_hairpins == c['n_3prim_hairpins']
+            want_h = min((x[2] for x in c['hairpins']), default=None)
+            assert (o.hairpinMin_dG() is None) == (want_h is None)
+            if want_h is not None:
+                assert abs(o.hairpinMin_dG() - want_h) < 1e-9
+            assert bool(o) == bool(c['dimers'] or c['hairpins'])
+            assert all(h in o for h in o.compose_reactions())
+        else:
+            assert o.hairpinMin_dG() is None and bool(o) == bool(c['dimers'])
+
+
+@pytest.mark.gpu
+def test_gpu_find_hairpins_equals_oracle_on_random_sequences():
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200.SecStructures import find_dimers_batch, find_hairpins_batch
+    from oracle.structures import find_hairpins as o_find_hairpins
+    from oracle.sequtils import reverse_complement
+    cond = dict(Na=50e-3, Mg=3e-3, dNTP=0.3e-3, DNA=1e-10, DMSO=0.0, PCR_T=30.0)
+    tdf.PCR_P.set(cond)
+    ocond.PCR_P.set(cond)
+    rng = np.random.default_rng(11)
+    seqs = []
+    for n in rng.integers(8, 65, size=60):
+        n = int(n)
+        stem = ''.join(rng.choice(list('ACGT'), size=int(rng.integers(3, max(4, n // 2 - 2)))))
+        loop = ''.join(rng.choice(list('ACGT'), size=int(rng.integers(3, 8))))
+        tail = ''.join(rng.choice(list('ACGT'), size=64))
+        s = (tail[:int(rng.integers(0, 4))] + stem + loop + reverse_complement(stem) + tail)[:n]
+        seqs.append(s)
+    sets = find_dimers_batch(seqs, [(i, i) for i in range(len(seqs))])
+    hsets = find_hairpins_batch(sets)
+    total = 0
+    for s, hs in zip(seqs, hsets):
+        _, fronts, _, _ = o_find_dimers(s, s)
+        hairpins, n3, _ = o_find_hairpins(fronts, s)
+        assert [(h.fwd_matches, h.rev_matches) for h in hs.hairpins] == [(h.fwd_matches, h.rev_matches) for h in hairpins]
+        assert all(abs(x.dG - y.dG) < 1e-9 for x, y in zip(hs.hairpins, hairpins))
+        assert hs.n_3prim_hairpins == n3
+        total += len(hairpins)
+    assert total > 40
