@@ -43,6 +43,14 @@ def main():
     t0 = time.perf_counter()
     sets = find_dimers_batch(seqs, pairs)
     ms_objects = (time.perf_counter() - t0) * 1e3
+    # hairpins of every variant: seeds = the self-dimers' full structures
+    from degenprimer_b200.SecStructures import find_hairpins_batch
+    self_sets = [sets[k] for k in range(len(pairs)) if pairs[k][0] == pairs[k][1]]
+    find_hairpins_batch(self_sets)                                                # warm-up, table upload
+    t0 = time.perf_counter()
+    hsets, ms_hp = find_hairpins_batch(self_sets, return_ms=True)
+    ms_hp_objects = (time.perf_counter() - t0) * 1e3
+    n_seeds = sum(len(ds.fronts) for ds in self_sets)
     n_fronts = len(pairs) * (2 * L - 1)
     # candidates evaluated: n_runs*(n_runs+1)/2 per front
     full = rec['full_mask']
@@ -74,6 +82,9 @@ def main():
         'ms_with_python_objects': ms_objects,
         'pairs_per_s': len(pairs) / (k * 1e-3), 'dimer_dG_per_s': n_eval / (k * 1e-3),
         'stable_dimers': int(sum(len(s) for s in sets)),
+        'hairpins': {'kernel': 'dp_find_hairpins_kernel', 'sequences': len(self_sets), 'seeds': n_seeds,
+                     'ms_kernel': ms_hp, 'ms_with_python_objects': ms_hp_objects,
+                     'stable_hairpins': int(sum(len(h) for h in hsets))},
         'cpu_oracle': {'pairs': int(len(sample)), 'seconds': cpu_s, 'pairs_per_s': len(sample) / cpu_s, 'cores': 1,
                        'kind': 'port', 'equal_to_gpu': bool(same)},
         'speedup_kernel_vs_cpu_core': (len(pairs) / (k * 1e-3)) / (len(sample) / cpu_s)}))
