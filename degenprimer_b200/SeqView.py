@@ -144,8 +144,17 @@ class SeqView(object):
             raise NotImplementedError('only FASTA templates are packed on the device; GenBank/EMBL '
                                       'input is listed under "next" (SURVEY §8f N4)')
         ctx = nat.context(device)
-        for f in valid:
-            t = ctx.template_from_fasta(f)
+        for i, f in enumerate(valid):
+            # `dbname` is the reference's on-disk index (SeqIO.index_db, BioUtils/SeqUtils.py:160-172);
+            # here it names the packed-template cache: used when it is newer than the
+            # FASTA file, (re)written otherwise.
+            cache = None if not dbname else (dbname if len(valid) == 1 else '%s.%d' % (dbname, i))
+            if cache and os.path.isfile(cache) and os.path.getmtime(cache) >= os.path.getmtime(f):
+                t = ctx.template_load(cache)
+            else:
+                t = ctx.template_from_fasta(f)
+                if cache:
+                    t.save(cache)
             self._templates.append(t)
             for r, rid in enumerate(t.ids):
                 if rid in self._where:
@@ -154,6 +163,30 @@ class SeqView(object):
         self._ids = tuple(sorted(self._where))
         self.master = True
         return bool(self)
+
+    def load_packed(self, paths, device=None):
+        """Packed-template files written by `save_packed` / `load(..., dbname=...)`: the planes go
+        straight to HBM, nothing is parsed (dp_template_load)."""
+        if isinstance(paths, (str, bytes)):
+            paths = [paths]
+        self.close()
+        ctx = nat.context(device)
+        for f in paths:
+            t = ctx.template_load(f)
+            self._templates.append(t)
+            for r, rid in enumerate(t.ids):
+                if rid in self._where:
+                    raise ValueError("Duplicate key '%s'" % rid)
+                self._where[rid] = (t, r)
+        self._ids = tuple(sorted(self._where))
+        self.master = True
+        return bool(self)
+
+    def save_packed(self, path):
+        """Write the resident templates as packed files; returns the list of paths
+        (`path` for one template, `path.0`, `path.1`, ... for several)."""
+        one = len(self._templates) == 1
+        return [t.save(path if one else '%s.%d' % (path, i)) for i, t in enumerate(self._templates)]
 
     @classmethod
     def safe_load(cls, files):

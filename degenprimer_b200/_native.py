@@ -124,6 +124,8 @@ def _declare(lib):
         'dp_template_from_records': (i32, [vp, u32, P(C.c_void_p), P(u64), P(vp)]),
         'dp_template_from_ascii': (i32, [vp, C.c_void_p, u64, P(vp)]),
         'dp_template_from_fasta': (i32, [vp, cp, P(vp)]),
+        'dp_template_save': (i32, [vp, vp, cp]),
+        'dp_template_load': (i32, [vp, cp, P(vp)]),
         'dp_template_free': (None, [vp]),
         'dp_template_get_info': (i32, [vp, P(dp_template_info)]),
         'dp_template_record': (i32, [vp, u32, P(u64), P(u64), P(cp), P(cp)]),
@@ -171,7 +173,7 @@ def _declare(lib):
 
 EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
-           'dp_template_from_fasta dp_template_free dp_template_get_info dp_template_record '
+           'dp_template_from_fasta dp_template_save dp_template_load dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
            'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
@@ -231,6 +233,11 @@ class Template(object):
         self.ctx._check(self.ctx.lib.dp_template_unpack(self.ctx._h, self._h, record, begin, n,
                                                         1 if reverse else 0, buf))
         return buf.raw[:n].decode('ascii')
+
+    def save(self, path):
+        """dp_template_save: planes + run table + record table as they sit in HBM."""
+        self.ctx._check(self.ctx.lib.dp_template_save(self.ctx._h, self._h, os.fsencode(path)))
+        return path
 
     def close(self):
         if self._h is not None and self.ctx._h is not None:
@@ -355,6 +362,12 @@ class Context(object):
     def template_from_fasta(self, path):
         out = C.c_void_p()
         self._check(self.lib.dp_template_from_fasta(self._h, os.fsencode(path), C.byref(out)))
+        return Template(self, out.value)
+
+    def template_load(self, path):
+        """dp_template_load: a packed template written by Template.save."""
+        out = C.c_void_p()
+        self._check(self.lib.dp_template_load(self._h, os.fsencode(path), C.byref(out)))
         return Template(self, out.value)
 
     # ---- scan ---------------------------------------------------------------------
@@ -624,6 +637,59 @@ class Context(object):
                                             _ptr(ln), n_pairs, _ptr(a), _ptr(b), C.byref(cond), stride,
                                             _ptr(out), C.byref(ms)))
         return out, float(ms.value)
+
+
+PACK_MAGIC = b'DPB200PK'
+PACK_HEADER = np.dtype([('magic', 'S8'), ('version', '<u4'), ('n_records', '<u4'), ('n_words', '<u8'),
+                        ('n_words_alloc', '<u8'), ('total_bases', '<u8'), ('n_runs', '<u8'),
+                        ('names_bytes', '<u8'), ('checksum', '<u8')])
+PACK_RECORD = np.dtype([('start', '<u8'), ('len', '<u8'), ('id_len', '<u4'), ('descr_len', '<u4')])
+PACK_RUN = np.dtype([('start', '<u8'), ('end', '<u8'), ('letter', '<u4'), ('pad', '<u4')])
+assert PACK_HEADER.itemsize == 64 and PACK_RECORD.itemsize == 24 and PACK_RUN.itemsize == 24
+
+
+def pack_checksum(*chunks):
+    """The checksum of a packed-template file (dp_pack_mix in csrc/dp_template.cu): the six sections
+    (record table, names, run table, plane lo, plane hi, plane exc) are mixed one after the other, 8 bytes at a
+    time, the last word of a section zero-padded."""
+    mask = (1 << 64) - 1
+    h = 0xCBF29CE484222325
+    for chunk in chunks:
+        b = bytes(chunk)
+        for i in range(0, len(b), 8):
+            w = int.from_bytes(b[i:i + 8].ljust(8, b'\0'), 'little')
+            h = ((h ^ w) * 0x100000001B3) & mask
+            h ^= h >> 29
+    return h
+
+
+def packed_info(path):
+    """Header and record table of a packed-template file, read on the host (no GPU): a dict with
+    n_records, total_bases, n_runs, records = [(id, description, start, len)], expected_bytes, bytes."""
+    size = os.path.getsize(path)
+    with open(path, 'rb') as fh:
+        raw = fh.read(64)
+        if len(raw) < 64:
+            raise ValueError('%s: shorter than a packed-template header' % path)
+        h = np.frombuffer(raw, dtype=PACK_HEADER)[0]
+        if bytes(h['magic']) != PACK_MAGIC:
+            raise ValueError('%s: not a packed template (bad magic)' % path)
+        if int(h['version']) != 1:
+            raise ValueError('%s: packed-template version %d, expected 1' % (path, int(h['version'])))
+        n = int(h['n_records'])
+        recs = np.frombuffer(fh.read(24 * n), dtype=PACK_RECORD)
+        names = fh.read(int(h['names_bytes']))
+    want = 64 + 24 * n + int(h['names_bytes']) + 24 * int(h['n_runs']) + 12 * int(h['n_words_alloc'])
+    out, p = [], 0
+    for r in recs:
+        rid = names[p:p + int(r['id_len'])].decode()
+        p += int(r['id_len'])
+        descr = names[p:p + int(r['descr_len'])].decode()
+        p += int(r['descr_len'])
+        out.append((rid, descr, int(r['start']), int(r['len'])))
+    return {'n_records': n, 'total_bases': int(h['total_bases']), 'n_words': int(h['n_words']),
+            'n_runs': int(h['n_runs']), 'checksum': int(h['checksum']), 'records': out,
+            'expected_bytes': want, 'bytes': size}
 
 
 _contexts = {}

@@ -501,3 +501,207 @@ int dp_template_unpack(dp_ctx* ctx, const dp_template* t, uint32_t r, uint64_t b
 }
 
 }  // extern "C"
+
+// ---- on-disk packed template ---------------------------------------------
+// Replaces the SQLite index the reference builds for every run (SeqIO.index_db into a temp
+// file, BioUtils/SeqUtils.py:140-172) and the parse + pack of the FASTA text: the three
+// bit-planes, the exception-run table and the record table exactly as they sit in HBM.
+//   header  64 B : magic "DPB200PK", u32 version, u32 n_records, u64 n_words, u64 n_words_alloc,
+//                  u64 total_bases, u64 n_runs, u64 names_bytes, u64 checksum (of all that follows)
+//   records      : n_records x {u64 start, u64 len, u32 id_len, u32 descr_len}
+//   names        : id and description bytes of every record, back to back
+//   runs         : n_runs x dp_exc_run {u64 start, u64 end, u32 letter, u32 pad}
+//   planes       : lo, hi, exc — n_words_alloc little-endian u32 each (tail guard included)
+// 0.375 B/bp instead of >= 1 B/bp of text, nothing to parse, and the load is one H2D stream.
+#define DP_PACK_MAGIC "DPB200PK"
+#define DP_PACK_VERSION 1u
+
+struct dp_pack_header {
+  char magic[8];
+  uint32_t version;
+  uint32_t n_records;
+  uint64_t n_words;
+  uint64_t n_words_alloc;
+  uint64_t total_bases;
+  uint64_t n_runs;
+  uint64_t names_bytes;
+  uint64_t checksum;
+};
+static_assert(sizeof(dp_pack_header) == 64, "packed-template header is 64 bytes");
+
+struct dp_pack_record {
+  uint64_t start, len;
+  uint32_t id_len, descr_len;
+};
+
+// word-wise FNV-1a style mix (8 bytes per step); `n` need not be a multiple of 8
+static uint64_t dp_pack_mix(uint64_t h, const void* data, size_t n) {
+  const unsigned char* p = (const unsigned char*)data;
+  size_t i = 0;
+  for (; i + 8 <= n; i += 8) {
+    uint64_t w;
+    memcpy(&w, p + i, 8);
+    h = (h ^ w) * 0x100000001B3ull;
+    h ^= h >> 29;
+  }
+  uint64_t w = 0;
+  if (i < n) { memcpy(&w, p + i, n - i); h = (h ^ w) * 0x100000001B3ull; h ^= h >> 29; }
+  return h;
+}
+#define DP_PACK_SEED 0xCBF29CE484222325ull
+
+extern "C" int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* path) {
+  if (!ctx || !t || !path) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  const uint32_t nrec = (uint32_t)t->records.size();
+  std::vector<dp_pack_record> recs(nrec);
+  std::string names;
+  for (uint32_t r = 0; r < nrec; ++r) {
+    const dp_record& x = t->records[r];
+    recs[r].start = x.start;
+    recs[r].len = x.len;
+    recs[r].id_len = (uint32_t)x.id.size();
+    recs[r].descr_len = (uint32_t)x.descr.size();
+    names += x.id;
+    names += x.descr;
+  }
+  const size_t plane_words = (size_t)t->n_words_alloc;
+  std::vector<uint32_t> planes(3 * plane_words);
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  DP_CUDA(ctx, cudaMemcpy(planes.data(), t->d_lo, plane_words * 4, cudaMemcpyDeviceToHost));
+  DP_CUDA(ctx, cudaMemcpy(planes.data() + plane_words, t->d_hi, plane_words * 4, cudaMemcpyDeviceToHost));
+  DP_CUDA(ctx, cudaMemcpy(planes.data() + 2 * plane_words, t->d_exc, plane_words * 4, cudaMemcpyDeviceToHost));
+  dp_pack_header h;
+  memset(&h, 0, sizeof h);
+  memcpy(h.magic, DP_PACK_MAGIC, 8);
+  h.version = DP_PACK_VERSION;
+  h.n_records = nrec;
+  h.n_words = t->n_words;
+  h.n_words_alloc = t->n_words_alloc;
+  h.total_bases = t->total_bases;
+  h.n_runs = t->runs.size();
+  h.names_bytes = names.size();
+  uint64_t c = DP_PACK_SEED;
+  c = dp_pack_mix(c, recs.data(), recs.size() * sizeof(dp_pack_record));
+  c = dp_pack_mix(c, names.data(), names.size());
+  c = dp_pack_mix(c, t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
+  for (int pl = 0; pl < 3; ++pl) c = dp_pack_mix(c, planes.data() + pl * plane_words, plane_words * 4);   // one section per plane
+  h.checksum = c;
+  std::string tmp = std::string(path) + ".tmp";
+  FILE* fh = fopen(tmp.c_str(), "wb");
+  if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot create %s", tmp.c_str());
+  bool ok = fwrite(&h, sizeof h, 1, fh) == 1;
+  ok = ok && (recs.empty() || fwrite(recs.data(), sizeof(dp_pack_record), recs.size(), fh) == recs.size());
+  ok = ok && (names.empty() || fwrite(names.data(), 1, names.size(), fh) == names.size());
+  ok = ok && (t->runs.empty() || fwrite(t->runs.data(), sizeof(dp_exc_run), t->runs.size(), fh) == t->runs.size());
+  ok = ok && fwrite(planes.data(), 4, planes.size(), fh) == planes.size();
+  ok = (fclose(fh) == 0) && ok;
+  if (!ok || rename(tmp.c_str(), path) != 0) {
+    remove(tmp.c_str());
+    return dp_set_error(ctx, DP_ERR_IO, "cannot write %s", path);
+  }
+  return DP_OK;
+}
+
+extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out) {
+  if (!ctx || !path || !out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *out = nullptr;
+  FILE* fh = fopen(path, "rb");
+  if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot open %s", path);
+  struct closer { FILE* f; ~closer() { if (f) fclose(f); } } guard{fh};
+  dp_pack_header h;
+  if (fread(&h, sizeof h, 1, fh) != 1) return dp_set_error(ctx, DP_ERR_IO, "%s: shorter than a packed-template header", path);
+  if (memcmp(h.magic, DP_PACK_MAGIC, 8) != 0) return dp_set_error(ctx, DP_ERR_IO, "%s: not a packed template (bad magic)", path);
+  if (h.version != DP_PACK_VERSION) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "%s: packed-template version %u, expected %u", path, h.version, DP_PACK_VERSION);
+  if (h.n_words_alloc != h.n_words + DP_GUARD_WORDS || h.total_bases > h.n_words * 32)
+    return dp_set_error(ctx, DP_ERR_IO, "%s: inconsistent header", path);
+  fseek(fh, 0, SEEK_END);
+  const uint64_t fsize = (uint64_t)ftell(fh);
+  const uint64_t want = sizeof h + (uint64_t)h.n_records * sizeof(dp_pack_record) + h.names_bytes +
+                        h.n_runs * sizeof(dp_exc_run) + 3ull * h.n_words_alloc * 4ull;
+  if (fsize != want) return dp_set_error(ctx, DP_ERR_IO, "%s: %llu bytes, header says %llu (truncated?)", path,
+                                         (unsigned long long)fsize, (unsigned long long)want);
+  fseek(fh, sizeof h, SEEK_SET);
+  std::vector<dp_pack_record> recs(h.n_records);
+  std::string names((size_t)h.names_bytes, '\0');
+  dp_template* t = new_template(ctx, h.n_records);
+  struct dropper {     // error paths: no copy may still be writing into planes that go back to the pool
+    dp_template* t;
+    ~dropper() { if (t) { cudaStreamSynchronize(t->ctx->copy_stream); free_template_device(t); delete t; } }
+  } drop{t};
+  t->runs.resize((size_t)h.n_runs);
+  if ((h.n_records && fread(recs.data(), sizeof(dp_pack_record), recs.size(), fh) != recs.size()) ||
+      (h.names_bytes && fread(&names[0], 1, names.size(), fh) != names.size()) ||
+      (h.n_runs && fread(t->runs.data(), sizeof(dp_exc_run), t->runs.size(), fh) != t->runs.size()))
+    return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
+  uint64_t c = DP_PACK_SEED;
+  c = dp_pack_mix(c, recs.data(), recs.size() * sizeof(dp_pack_record));
+  c = dp_pack_mix(c, names.data(), names.size());
+  c = dp_pack_mix(c, t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
+  size_t np = 0;
+  uint64_t prev_end = 0;
+  for (uint32_t r = 0; r < h.n_records; ++r) {
+    const dp_pack_record& x = recs[r];
+    if ((x.start & 31) || x.start < prev_end || x.start + x.len > h.n_words * 32 || np + x.id_len + x.descr_len > names.size())
+      return dp_set_error(ctx, DP_ERR_IO, "%s: record table is inconsistent at record %u", path, r);
+    prev_end = x.start + x.len;
+    t->records[r].start = x.start;
+    t->records[r].len = x.len;
+    t->records[r].id = names.substr(np, x.id_len);
+    np += x.id_len;
+    t->records[r].descr = names.substr(np, x.descr_len);
+    np += x.descr_len;
+  }
+  for (size_t i = 0; i < t->runs.size(); ++i)
+    if (t->runs[i].end <= t->runs[i].start || t->runs[i].end > h.n_words * 32 || (i && t->runs[i].start < t->runs[i - 1].end))
+      return dp_set_error(ctx, DP_ERR_IO, "%s: exception-run table is inconsistent at run %zu", path, i);
+  t->n_words = h.n_words;
+  t->n_words_alloc = h.n_words_alloc;
+  t->total_bases = h.total_bases;
+  DP_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = ensure_stage(ctx);
+  if (rc) return rc;
+  const size_t plane_bytes = (size_t)h.n_words_alloc * 4;
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_lo, plane_bytes));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_hi, plane_bytes));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_exc, plane_bytes));
+  // the planes were allocated in ctx->stream order; the copies run on copy_stream behind an event
+  DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[0], ctx->stream));
+  DP_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->stage_ev[0], 0));
+  uint32_t* dst[3] = {t->d_lo, t->d_hi, t->d_exc};
+  bool slot_busy[2] = {false, false};
+  int slot = 0;
+  for (int pl = 0; pl < 3; ++pl) {
+    size_t done = 0;
+    while (done < plane_bytes) {
+      const size_t n = std::min<size_t>(DP_STAGE_BYTES, plane_bytes - done);
+      if (slot_busy[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_copied[slot]));   // pinned slot free again
+      if (fread(ctx->h_stage[slot], 1, n, fh) != n) return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
+      c = dp_pack_mix(c, ctx->h_stage[slot], n);
+      DP_CUDA(ctx, cudaMemcpyAsync((char*)dst[pl] + done, ctx->h_stage[slot], n, cudaMemcpyHostToDevice, ctx->copy_stream));
+      DP_CUDA(ctx, cudaEventRecord(ctx->stage_copied[slot], ctx->copy_stream));
+      slot_busy[slot] = true;
+      slot ^= 1;
+      done += n;
+    }
+  }
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  if (c != h.checksum) return dp_set_error(ctx, DP_ERR_IO, "%s: checksum mismatch (file is corrupt)", path);
+  const size_t nr = t->runs.size();
+  const uint32_t nrec = h.n_records;
+  std::vector<uint64_t> starts(nrec), rl(nrec);
+  for (uint32_t r = 0; r < nrec; ++r) { starts[r] = t->records[r].start; rl[r] = t->records[r].len; }
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_runs, std::max<size_t>(1, nr) * sizeof(dp_exc_run)));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_rec_start, std::max<size_t>(1, nrec) * sizeof(uint64_t)));
+  DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_rec_len, std::max<size_t>(1, nrec) * sizeof(uint64_t)));
+  if (nr) DP_CUDA(ctx, cudaMemcpyAsync(t->d_runs, t->runs.data(), nr * sizeof(dp_exc_run), cudaMemcpyHostToDevice, ctx->stream));
+  if (nrec) {
+    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_start, starts.data(), nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_len, rl.data(), nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  t->device_bytes = 3 * plane_bytes + nr * sizeof(dp_exc_run) + 2 * nrec * sizeof(uint64_t);
+  drop.t = nullptr;
+  *out = t;
+  return DP_OK;
+}

@@ -94,6 +94,21 @@ int dp_template_from_ascii(dp_ctx* ctx, const char* seq, uint64_t len,
 int dp_template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out);
 void dp_template_free(dp_template* t);
 
+/* SURVEY §8(f) N4 — on-disk packed template.  Replaces the SQLite index the reference
+ * builds on every run (SeqIO.index_db into a temp file, BioUtils/SeqUtils.py:140-172)
+ * together with parsing and packing the text: the file holds the three bit-planes, the
+ * exception-run table and the record table (ids, descriptions) exactly as they sit in
+ * HBM — 0.375 B/bp, nothing to parse, one H2D stream through pinned staging.
+ * Layout (little endian): 64-byte header {magic "DPB200PK", u32 version = 1,
+ * u32 n_records, u64 n_words, u64 n_words_alloc, u64 total_bases, u64 n_runs,
+ * u64 names_bytes, u64 checksum of the six sections after the header}; n_records x
+ * {u64 start, u64 len, u32 id_len, u32 descr_len}; the id and description bytes;
+ * n_runs x {u64 start, u64 end, u32 letter, u32 pad}; planes lo, hi, exc of
+ * n_words_alloc u32 each.  dp_template_load checks magic, version, sizes, the tables'
+ * consistency and the checksum (DP_ERR_IO / DP_ERR_UNSUPPORTED otherwise). */
+int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* path);
+int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out);
+
 typedef struct dp_template_info {
   uint32_t n_records;
   uint32_t reserved;
