@@ -649,18 +649,25 @@ assert PACK_HEADER.itemsize == 64 and PACK_RECORD.itemsize == 24 and PACK_RUN.it
 
 
 def pack_checksum(*chunks):
-    """The checksum of a packed-template file (dp_pack_mix in csrc/dp_template.cu): the six sections
-    (record table, names, run table, plane lo, plane hi, plane exc) are mixed one after the other, 8 bytes at a
-    time, the last word of a section zero-padded."""
+    """The checksum of a packed-template file (dp_pack_sum in csrc/dp_template.cu): the six sections
+    (record table, names, run table, plane lo, plane hi, plane exc), each zero-padded to a multiple of 8
+    bytes, form one sequence of little-endian 64-bit words; word i goes to lane i & 3 (h_l starts at
+    SEED + l; h = (h ^ w) * P; h ^= h >> 29) and the four lanes are folded at the end."""
     mask = (1 << 64) - 1
-    h = 0xCBF29CE484222325
+    prime = 0x100000001B3
+    hs = [(0xCBF29CE484222325 + lane) & mask for lane in range(4)]
+    i = 0
     for chunk in chunks:
         b = bytes(chunk)
-        for i in range(0, len(b), 8):
-            w = int.from_bytes(b[i:i + 8].ljust(8, b'\0'), 'little')
-            h = ((h ^ w) * 0x100000001B3) & mask
-            h ^= h >> 29
-    return h
+        for k in range(0, len(b), 8):
+            w = int.from_bytes(b[k:k + 8].ljust(8, b'\0'), 'little')
+            h = ((hs[i & 3] ^ w) * prime) & mask
+            hs[i & 3] = h ^ (h >> 29)
+            i += 1
+    r = hs[0]
+    for lane in range(1, 4):
+        r = ((r * prime) & mask) ^ hs[lane]
+    return r
 
 
 def packed_info(path):
@@ -674,8 +681,8 @@ def packed_info(path):
         h = np.frombuffer(raw, dtype=PACK_HEADER)[0]
         if bytes(h['magic']) != PACK_MAGIC:
             raise ValueError('%s: not a packed template (bad magic)' % path)
-        if int(h['version']) != 1:
-            raise ValueError('%s: packed-template version %d, expected 1' % (path, int(h['version'])))
+        if int(h['version']) != 2:
+            raise ValueError('%s: packed-template version %d, expected 2' % (path, int(h['version'])))
         n = int(h['n_records'])
         recs = np.frombuffer(fh.read(24 * n), dtype=PACK_RECORD)
         names = fh.read(int(h['names_bytes']))

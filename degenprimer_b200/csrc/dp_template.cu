@@ -514,7 +514,7 @@ int dp_template_unpack(dp_ctx* ctx, const dp_template* t, uint32_t r, uint64_t b
 //   planes       : lo, hi, exc — n_words_alloc little-endian u32 each (tail guard included)
 // 0.375 B/bp instead of >= 1 B/bp of text, nothing to parse, and the load is one H2D stream.
 #define DP_PACK_MAGIC "DPB200PK"
-#define DP_PACK_VERSION 1u
+#define DP_PACK_VERSION 2u
 
 struct dp_pack_header {
   char magic[8];
@@ -534,21 +534,35 @@ struct dp_pack_record {
   uint32_t id_len, descr_len;
 };
 
-// word-wise FNV-1a style mix (8 bytes per step); `n` need not be a multiple of 8
-static uint64_t dp_pack_mix(uint64_t h, const void* data, size_t n) {
-  const unsigned char* p = (const unsigned char*)data;
-  size_t i = 0;
-  for (; i + 8 <= n; i += 8) {
-    uint64_t w;
-    memcpy(&w, p + i, 8);
-    h = (h ^ w) * 0x100000001B3ull;
-    h ^= h >> 29;
-  }
-  uint64_t w = 0;
-  if (i < n) { memcpy(&w, p + i, n - i); h = (h ^ w) * 0x100000001B3ull; h ^= h >> 29; }
-  return h;
-}
+// Checksum: the six sections after the header, each zero-padded to a multiple of 8 bytes, read as
+// one sequence of little-endian 64-bit words w[0..N); lane l = i & 3 takes the words i == l (mod 4)
+// (four independent multiply chains, so the sum runs at memory speed instead of at the latency of
+// one multiply per word); h_l starts at SEED + l, h = (h ^ w) * P, h ^= h >> 29; the lanes are
+// folded at the end.  Only the last call of a section may pass n that is not a multiple of 8.
 #define DP_PACK_SEED 0xCBF29CE484222325ull
+#define DP_PACK_PRIME 0x100000001B3ull
+struct dp_pack_sum {
+  uint64_t h[4];
+  uint64_t i;      // words taken so far
+  dp_pack_sum() : i(0) { for (int l = 0; l < 4; ++l) h[l] = DP_PACK_SEED + (uint64_t)l; }
+  static inline uint64_t step(uint64_t h, uint64_t w) { h = (h ^ w) * DP_PACK_PRIME; return h ^ (h >> 29); }
+  void mix(const void* data, size_t n) {
+    const unsigned char* p = (const unsigned char*)data;
+    size_t k = 0;
+    while ((i & 3) && k + 8 <= n) { uint64_t w; memcpy(&w, p + k, 8); h[i & 3] = step(h[i & 3], w); ++i; k += 8; }
+    uint64_t a = h[0], b = h[1], c = h[2], d = h[3];
+    for (; k + 32 <= n; k += 32) {
+      uint64_t w[4];
+      memcpy(w, p + k, 32);
+      a = step(a, w[0]); b = step(b, w[1]); c = step(c, w[2]); d = step(d, w[3]);
+      i += 4;
+    }
+    h[0] = a; h[1] = b; h[2] = c; h[3] = d;
+    for (; k + 8 <= n; k += 8) { uint64_t w; memcpy(&w, p + k, 8); h[i & 3] = step(h[i & 3], w); ++i; }
+    if (k < n) { uint64_t w = 0; memcpy(&w, p + k, n - k); h[i & 3] = step(h[i & 3], w); ++i; }
+  }
+  uint64_t value() const { uint64_t r = h[0]; for (int l = 1; l < 4; ++l) r = (r * DP_PACK_PRIME) ^ h[l]; return r; }
+};
 
 extern "C" int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* path) {
   if (!ctx || !t || !path) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
@@ -581,12 +595,12 @@ extern "C" int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* p
   h.total_bases = t->total_bases;
   h.n_runs = t->runs.size();
   h.names_bytes = names.size();
-  uint64_t c = DP_PACK_SEED;
-  c = dp_pack_mix(c, recs.data(), recs.size() * sizeof(dp_pack_record));
-  c = dp_pack_mix(c, names.data(), names.size());
-  c = dp_pack_mix(c, t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
-  for (int pl = 0; pl < 3; ++pl) c = dp_pack_mix(c, planes.data() + pl * plane_words, plane_words * 4);   // one section per plane
-  h.checksum = c;
+  dp_pack_sum c;
+  c.mix(recs.data(), recs.size() * sizeof(dp_pack_record));
+  c.mix(names.data(), names.size());
+  c.mix(t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
+  for (int pl = 0; pl < 3; ++pl) c.mix(planes.data() + pl * plane_words, plane_words * 4);   // one section per plane
+  h.checksum = c.value();
   std::string tmp = std::string(path) + ".tmp";
   FILE* fh = fopen(tmp.c_str(), "wb");
   if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot create %s", tmp.c_str());
@@ -634,10 +648,10 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
       (h.names_bytes && fread(&names[0], 1, names.size(), fh) != names.size()) ||
       (h.n_runs && fread(t->runs.data(), sizeof(dp_exc_run), t->runs.size(), fh) != t->runs.size()))
     return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
-  uint64_t c = DP_PACK_SEED;
-  c = dp_pack_mix(c, recs.data(), recs.size() * sizeof(dp_pack_record));
-  c = dp_pack_mix(c, names.data(), names.size());
-  c = dp_pack_mix(c, t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
+  dp_pack_sum c;
+  c.mix(recs.data(), recs.size() * sizeof(dp_pack_record));
+  c.mix(names.data(), names.size());
+  c.mix(t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
   size_t np = 0;
   uint64_t prev_end = 0;
   for (uint32_t r = 0; r < h.n_records; ++r) {
@@ -677,7 +691,7 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
       const size_t n = std::min<size_t>(DP_STAGE_BYTES, plane_bytes - done);
       if (slot_busy[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_copied[slot]));   // pinned slot free again
       if (fread(ctx->h_stage[slot], 1, n, fh) != n) return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
-      c = dp_pack_mix(c, ctx->h_stage[slot], n);
+      c.mix(ctx->h_stage[slot], n);              // DP_STAGE_BYTES is a multiple of 32: only a plane's last chunk has a tail
       DP_CUDA(ctx, cudaMemcpyAsync((char*)dst[pl] + done, ctx->h_stage[slot], n, cudaMemcpyHostToDevice, ctx->copy_stream));
       DP_CUDA(ctx, cudaEventRecord(ctx->stage_copied[slot], ctx->copy_stream));
       slot_busy[slot] = true;
@@ -686,7 +700,7 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
     }
   }
   DP_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
-  if (c != h.checksum) return dp_set_error(ctx, DP_ERR_IO, "%s: checksum mismatch (file is corrupt)", path);
+  if (c.value() != h.checksum) return dp_set_error(ctx, DP_ERR_IO, "%s: checksum mismatch (file is corrupt)", path);
   const size_t nr = t->runs.size();
   const uint32_t nrec = h.n_records;
   std::vector<uint64_t> starts(nrec), rl(nrec);

@@ -99,9 +99,10 @@ void dp_template_free(dp_template* t);
  * together with parsing and packing the text: the file holds the three bit-planes, the
  * exception-run table and the record table (ids, descriptions) exactly as they sit in
  * HBM — 0.375 B/bp, nothing to parse, one H2D stream through pinned staging.
- * Layout (little endian): 64-byte header {magic "DPB200PK", u32 version = 1,
+ * Layout (little endian): 64-byte header {magic "DPB200PK", u32 version = 2,
  * u32 n_records, u64 n_words, u64 n_words_alloc, u64 total_bases, u64 n_runs,
- * u64 names_bytes, u64 checksum of the six sections after the header}; n_records x
+ * u64 names_bytes, u64 checksum of the six sections after the header (four interleaved
+ * multiply-xor lanes over their 64-bit words, see dp_pack_sum)}; n_records x
  * {u64 start, u64 len, u32 id_len, u32 descr_len}; the id and description bytes;
  * n_runs x {u64 start, u64 end, u32 letter, u32 pad}; planes lo, hi, exc of
  * n_words_alloc u32 each.  dp_template_load checks magic, version, sizes, the tables'

@@ -26,7 +26,7 @@ def _write_packed(path, records, n_runs=2, corrupt=None):
         runs[i] = (10 * i + 3, 10 * i + 7, 14, 0)
     planes = np.arange(3 * (n_words + guard), dtype='<u4') * np.uint32(2654435761)
     h = np.zeros(1, dtype=nat.PACK_HEADER)
-    h['magic'], h['version'], h['n_records'] = nat.PACK_MAGIC, 1, len(records)
+    h['magic'], h['version'], h['n_records'] = nat.PACK_MAGIC, 2, len(records)
     h['n_words'], h['n_words_alloc'] = n_words, n_words + guard
     h['total_bases'], h['n_runs'], h['names_bytes'] = sum(r[2] for r in records), n_runs, len(names)
     pb = planes.tobytes()
