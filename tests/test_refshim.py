@@ -83,6 +83,14 @@ ns.tdf.PCR_P.set(ref['conds'][case['cond']])
 r = eng._find(WC(), ns.SeqRecord(ns.Seq(case['template']), id='T'), primer(case['master']), len(case['template']), len(case['master']), case['k'])
 got = json.loads(json.dumps(gen.dump_results(eng.compile_duplexes(WC(), *r))))
 assert got == case['serial']
+# two defects of the reference that the replacement does not reproduce (DESIGN.md section 2), seen live:
+SE = ns.SearchEngine.SearchEngine
+assert SE._calculate_chunk_size(32, 32) - 32 == 0          # chunk_stride 0: `_find` never advances `pos`
+import numpy as np
+T = 1040472                                                # last slice shorter than a whole number of chunks
+t = ''.join(np.random.default_rng(1).choice(list('ACGT'), size=T))
+r = eng._find_mp(WC(), ns.SeqRecord(ns.Seq(t), id='T'), primer('ATATTCTACGACGGCTATCC'), T, 20, 1)
+assert r is None                                           # broadcast ValueError in the collector -> abort -> None
 print('LIVE-OK')
 '''
 
