@@ -1,4 +1,4 @@
-"""Template loader: FASTA files -> records resident in HBM as 2-bit planes.
+"""Template loader: FASTA / GenBank / EMBL files, or a packed cache -> records resident in HBM as 2-bit planes.
 
 Keeps the container interface of BioUtils/BioUtils/SeqUtils.py:103-271
 (`SeqView`: `load`, `load_dir`, `keys`, `__getitem__` by index / id / slice,
@@ -15,6 +15,82 @@ from .SeqUtils import Seq
 
 _FASTA = re.compile(r'.*\.f(asta|as|a|aa|fn|rn|na)$')     # SeqLoader schemas, SeqUtils.py:30-35
 _OTHER = re.compile(r'.*\.(gb|gbk|embl)$')
+
+
+def parse_genbank(path):
+    """Records of a GenBank flat file as (id, description, sequence): id = VERSION (accession.version) if
+    present, else the first ACCESSION, else the LOCUS name — the order Bio.SeqIO's 'gb' parser uses, which
+    the reference reads these files with (BioUtils/SeqUtils.py:30-35,160-172); description = DEFINITION
+    joined to one line; sequence = the ORIGIN block without digits and blanks."""
+    out, cur, field = [], None, None
+    with open(path) as fh:
+        for line in fh:
+            key = line[:12].strip()
+            if line.startswith('LOCUS'):
+                parts = line.split()
+                cur = {'locus': parts[1] if len(parts) > 1 else '', 'acc': '', 'ver': '', 'def': [], 'seq': []}
+                field = None
+            elif cur is None:
+                continue
+            elif line.startswith('//'):
+                rid = cur['ver'] or cur['acc'] or cur['locus']
+                out.append((rid, ' '.join(cur['def']), ''.join(cur['seq'])))
+                cur, field = None, None
+            elif field == 'ORIGIN':
+                cur['seq'].append(''.join(c for c in line if c.isalpha() or c == '*'))
+            elif key == 'DEFINITION':
+                cur['def'].append(line[12:].strip())
+                field = 'DEFINITION'
+            elif key == 'ACCESSION':
+                cur['acc'] = (line[12:].split() or [''])[0]
+                field = None
+            elif key == 'VERSION':
+                cur['ver'] = (line[12:].split() or [''])[0]
+                field = None
+            elif key == 'ORIGIN':
+                field = 'ORIGIN'
+            elif key == '' and field == 'DEFINITION' and line[:12].strip() == '':
+                cur['def'].append(line.strip())
+            elif key:
+                field = None
+    if cur is not None:
+        raise ValueError('%s: GenBank record %s is not terminated by //' % (path, cur['locus']))
+    return out
+
+
+def parse_embl(path):
+    """Records of an EMBL flat file as (id, description, sequence): id = first AC accession plus the
+    sequence version of the ID line (SV n) when there is one, else the ID name; description = DE lines
+    joined; sequence = the lines after SQ without digits and blanks."""
+    out, cur, in_seq = [], None, False
+    with open(path) as fh:
+        for line in fh:
+            tag = line[:2]
+            if tag == 'ID':
+                fields = [f.strip() for f in line[5:].split(';')]
+                sv = next((f[3:].strip() for f in fields if f.startswith('SV ')), '')
+                cur = {'name': fields[0].split()[0] if fields and fields[0] else '', 'sv': sv, 'acc': '', 'de': [],
+                       'seq': []}
+                in_seq = False
+            elif cur is None:
+                continue
+            elif tag == '//':
+                rid = cur['acc'] or cur['name']
+                if cur['acc'] and cur['sv']:
+                    rid = '%s.%s' % (cur['acc'], cur['sv'])
+                out.append((rid, ' '.join(cur['de']), ''.join(cur['seq'])))
+                cur, in_seq = None, False
+            elif in_seq:
+                cur['seq'].append(''.join(c for c in line if c.isalpha() or c == '*'))
+            elif tag == 'AC' and not cur['acc']:
+                cur['acc'] = line[5:].split(';')[0].strip()
+            elif tag == 'DE':
+                cur['de'].append(line[5:].strip())
+            elif tag == 'SQ':
+                in_seq = True
+    if cur is not None:
+        raise ValueError('%s: EMBL record %s is not terminated by //' % (path, cur['name']))
+    return out
 
 
 class StrandView(object):
@@ -140,9 +216,7 @@ class SeqView(object):
         if len(schemas) != 1:
             raise ValueError('All files should be of the same type, but %d types found: %s'
                              % (len(schemas), ', '.join(sorted(schemas))))
-        if schemas != {'fasta'}:
-            raise NotImplementedError('only FASTA templates are packed on the device; GenBank/EMBL '
-                                      'input is listed under "next" (SURVEY §8f N4)')
+        schema = next(iter(schemas))
         ctx = nat.context(device)
         for i, f in enumerate(valid):
             # `dbname` is the reference's on-disk index (SeqIO.index_db, BioUtils/SeqUtils.py:160-172);
@@ -152,7 +226,17 @@ class SeqView(object):
             if cache and os.path.isfile(cache) and os.path.getmtime(cache) >= os.path.getmtime(f):
                 t = ctx.template_load(cache)
             else:
-                t = ctx.template_from_fasta(f)
+                if schema == 'fasta':
+                    t = ctx.template_from_fasta(f)
+                else:                       # GenBank / EMBL: parsed on the host, packed on the device
+                    recs = sorted(parse_genbank(f) if schema == 'gb' else parse_embl(f))
+                    if not recs:
+                        raise ValueError('no %s records in %s' % (schema, f))
+                    for (a, _, _), (b, _, _) in zip(recs, recs[1:]):
+                        if a == b:
+                            raise ValueError("Duplicate key '%s'" % a)
+                    t = ctx.template_from_sequences([r[2] for r in recs])
+                    t.set_record_names([r[0] for r in recs], [r[1] for r in recs])
                 if cache:
                     t.save(cache)
             self._templates.append(t)

@@ -124,6 +124,7 @@ def _declare(lib):
         'dp_template_from_records': (i32, [vp, u32, P(C.c_void_p), P(u64), P(vp)]),
         'dp_template_from_ascii': (i32, [vp, C.c_void_p, u64, P(vp)]),
         'dp_template_from_fasta': (i32, [vp, cp, P(vp)]),
+        'dp_template_set_record_name': (i32, [vp, u32, cp, cp]),
         'dp_template_save': (i32, [vp, vp, cp]),
         'dp_template_load': (i32, [vp, cp, P(vp)]),
         'dp_template_free': (None, [vp]),
@@ -173,7 +174,7 @@ def _declare(lib):
 
 EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
-           'dp_template_from_fasta dp_template_save dp_template_load dp_template_free dp_template_get_info dp_template_record '
+           'dp_template_from_fasta dp_template_set_record_name dp_template_save dp_template_load dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
            'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
@@ -233,6 +234,12 @@ class Template(object):
         self.ctx._check(self.ctx.lib.dp_template_unpack(self.ctx._h, self._h, record, begin, n,
                                                         1 if reverse else 0, buf))
         return buf.raw[:n].decode('ascii')
+
+    def set_record_names(self, ids, descriptions):
+        """Name the records (dp_template_set_record_name): for loaders of formats other than FASTA."""
+        for r, (rid, descr) in enumerate(zip(ids, descriptions)):
+            self.ctx._check(self.ctx.lib.dp_template_set_record_name(self._h, r, rid.encode(), descr.encode()))
+        self.ids, self.descriptions = list(ids), list(descriptions)
 
     def save(self, path):
         """dp_template_save: planes + run table + record table as they sit in HBM."""

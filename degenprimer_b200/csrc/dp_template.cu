@@ -719,3 +719,12 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
   *out = t;
   return DP_OK;
 }
+
+// id / description of a record (records made by dp_template_from_records are named record_<r>):
+// what a GenBank / EMBL loader calls after it has handed the sequences over.  Host-side only.
+extern "C" int dp_template_set_record_name(dp_template* t, uint32_t r, const char* id, const char* descr) {
+  if (!t || r >= t->records.size() || !id) return DP_ERR_ARG;
+  t->records[r].id = id;
+  t->records[r].descr = descr ? descr : "";
+  return DP_OK;
+}

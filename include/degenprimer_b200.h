@@ -107,6 +107,9 @@ void dp_template_free(dp_template* t);
  * n_runs x {u64 start, u64 end, u32 letter, u32 pad}; planes lo, hi, exc of
  * n_words_alloc u32 each.  dp_template_load checks magic, version, sizes, the tables'
  * consistency and the checksum (DP_ERR_IO / DP_ERR_UNSUPPORTED otherwise). */
+/* id / description of record r (dp_template_from_records names them record_<r>); host-side,
+ * used by loaders of formats other than FASTA (GenBank, EMBL) before dp_template_save. */
+int dp_template_set_record_name(dp_template* t, uint32_t r, const char* id, const char* descr);
 int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* path);
 int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out);
 

@@ -145,3 +145,83 @@ def test_packed_template_round_trip(tmp_path):
     os.utime(cache, (1, 1))
     d = SeqView(upper=True)
     assert d.load(fa, dbname=cache) and os.path.getmtime(cache) > 1 and hits(d) == want
+
+
+GENBANK = '''LOCUS       SCU49845     120 bp    DNA             PLN       21-JUN-1999
+DEFINITION  Saccharomyces cerevisiae TCP1-beta gene, partial cds, and Axl2p
+            (AXL2) and Rev7p (REV7) genes, complete cds.
+ACCESSION   U49845 X00001
+VERSION     U49845.1  GI:1293613
+KEYWORDS    .
+FEATURES             Location/Qualifiers
+     source          1..120
+                     /organism="Saccharomyces cerevisiae"
+ORIGIN
+        1 gatcctccat atacaacggt atctccacct caggtttaga tctcaacaac ggaaccattg
+       61 ccgacatgag acagttaggt atcgtcgaga gttacaagct aaaacgagca gtagtcagct
+//
+LOCUS       NOVERSION     10 bp    DNA
+DEFINITION  second record.
+ACCESSION   AB000002
+ORIGIN
+        1 acgtnnryac
+//
+'''
+
+EMBL = '''ID   X56734; SV 1; linear; mRNA; STD; PLN; 70 BP.
+XX
+AC   X56734; S46826;
+XX
+DE   Trifolium repens mRNA for non-cyanogenic beta-glucosidase
+DE   second line
+XX
+SQ   Sequence 70 BP; 19 A; 16 C; 17 G; 18 T; 0 other;
+     aaacaaacca aatatggatt ttattgtagc catatttgct ctgtttgtta ttagctcatt        60
+     cacaattact                                                               70
+//
+ID   NOAC_NAME; linear; DNA; 8 BP.
+DE   no accession
+SQ   Sequence 8 BP;
+     acgtacgn         8
+//
+'''
+
+
+def test_genbank_and_embl_parsers(tmp_path):
+    from degenprimer_b200.SeqView import SeqView, parse_embl, parse_genbank
+    gb, em = tmp_path / 'x.gb', tmp_path / 'x.embl'
+    gb.write_text(GENBANK)
+    em.write_text(EMBL)
+    recs = parse_genbank(str(gb))
+    assert [(r[0], len(r[2])) for r in recs] == [('U49845.1', 120), ('AB000002', 10)]
+    assert recs[0][1] == ('Saccharomyces cerevisiae TCP1-beta gene, partial cds, and Axl2p (AXL2) and Rev7p (REV7) '
+                          'genes, complete cds.')
+    assert recs[0][2].startswith('gatcctccat') and recs[0][2].endswith('gtagtcagct') and recs[1][2] == 'acgtnnryac'
+    recs = parse_embl(str(em))
+    assert [(r[0], len(r[2])) for r in recs] == [('X56734.1', 70), ('NOAC_NAME', 8)]
+    assert recs[0][1] == 'Trifolium repens mRNA for non-cyanogenic beta-glucosidase second line'
+    assert recs[0][2].endswith('cacaattact') and recs[1][2] == 'acgtacgn'
+    (tmp_path / 'broken.gb').write_text(GENBANK.rsplit('//', 1)[0])
+    with pytest.raises(ValueError, match='not terminated'):
+        parse_genbank(str(tmp_path / 'broken.gb'))
+    assert SeqView.guess_schema('a.gbk') == 'gb' and SeqView.guess_schema('a.embl') == 'embl'
+
+
+@pytest.mark.gpu
+def test_genbank_embl_load_and_cache(tmp_path):
+    from degenprimer_b200.SeqView import SeqView
+    gb, em = tmp_path / 'x.gb', tmp_path / 'x.embl'
+    gb.write_text(GENBANK)
+    em.write_text(EMBL)
+    v = SeqView(upper=True)
+    assert v.load(str(gb), dbname=str(tmp_path / 'gb.dpk'))
+    assert v.keys() == ('AB000002', 'U49845.1') and str(v['AB000002'].seq) == 'ACGTNNRYAC'
+    assert str(v['U49845.1'].seq).startswith('GATCCTCCAT') and len(v['U49845.1']) == 120
+    assert v['U49845.1'].description.startswith('Saccharomyces cerevisiae TCP1-beta')
+    info = nat.packed_info(str(tmp_path / 'gb.dpk'))
+    assert [r[0] for r in info['records']] == ['AB000002', 'U49845.1']           # names travel with the cache
+    w = SeqView(upper=True)
+    assert w.load_packed(str(tmp_path / 'gb.dpk')) and w.keys() == v.keys()
+    assert str(w['U49845.1'].seq) == str(v['U49845.1'].seq) and w['AB000002'].description == 'second record.'
+    e = SeqView(upper=True)
+    assert e.load(str(em)) and e.keys() == ('NOAC_NAME', 'X56734.1') and str(e['NOAC_NAME'].seq) == 'ACGTACGN'
