@@ -1,0 +1,178 @@
+"""PCR_Mixture / MixtureFactory — host mirror of DegenPrimer/PCR_Mixture.py:29-249.
+
+The step right after the hot path: annealing sites of both strands (the `(position, duplexes)` lists
+SearchEngine.compile_duplexes[_mp] returns) are split into sites that can prime a product and sites
+that cannot, and forward / reverse sites are paired into products of [min_amplicon, max_amplicon].
+This is host code on purpose: the pairing loop of the reference carries state from one forward site
+to the next (see `create_PCR_mixture`), so its exact result is a sequential walk over two sorted lists
+— microseconds of work for the site counts the scan produces — and everything else is object
+bookkeeping that PCR_Simulation reads (`reaction_id, annealings, templates, products`).
+"""
+from . import tmpStorage
+from .Product import Product, Region
+
+
+class PCR_Mixture(object):
+    """All annealings, template regions and products of one target sequence (PCR_Mixture.py:29-107)."""
+    __slots__ = ['reaction_id', 'annealings', 'templates', 'products']
+
+    def __init__(self, reaction_id):
+        self.reaction_id = reaction_id
+        self.annealings = []            # (duplexes, template Region) of every site that takes part
+        self.templates = [[], []]       # [reverse strand, forward strand]: merged template regions
+        self.products = dict()          # hash(Product) -> Product
+
+    def _compact_templates(self, strand):
+        """Merge overlapping regions of a start-sorted list, in place on the Region objects (:62-69) —
+        the same objects sit in `annealings`, which therefore see the merged extent too."""
+        regions = self.templates[strand]
+        merged = [regions[0]]
+        for r in regions:
+            if r.overlaps(merged[-1]):
+                merged[-1] += r
+            else:
+                merged.append(r)
+        self.templates[strand] = merged
+
+    def add_annealing(self, duplexes, template):
+        self.annealings.append((duplexes, template))
+        strand = template.forward
+        self.templates[strand].append(template)
+        self.templates[strand].sort(key=lambda x: x.start)
+        self._compact_templates(strand)
+
+    def add_annealings(self, annealings):
+        self.annealings.extend(annealings)
+        before = (len(self.templates[0]), len(self.templates[1]))
+        for _dups, template in annealings:
+            self.templates[template.forward].append(template)
+        for strand in (1, 0):
+            if len(self.templates[strand]) > before[strand]:
+                self.templates[strand].sort(key=lambda x: x.start)
+                self._compact_templates(strand)
+
+    def add_product(self, start, end, fwd_duplexes, rev_duplexes):
+        """start, end: 1-based positions of the first and last base of the product (:72-92)."""
+        new = Product(self.reaction_id, start, end, fwd_duplexes, rev_duplexes)
+        key = hash(new)
+        if key in self.products:
+            self.products[key] += new
+        else:
+            self.products[key] = new
+
+    def save(self):
+        """Temp-file hand-off like the reference's tmpDict (:95-106); read back with `load_mixture`."""
+        return tmpStorage.to_shelf(self)
+
+    def __getstate__(self):
+        return tuple(getattr(self, s) for s in self.__slots__)
+
+    def __setstate__(self, state):
+        for s, v in zip(self.__slots__, state):
+            setattr(self, s, v)
+
+
+def load_mixture(path):
+    """What ShelvedMixture(path) gives in the reference (:110-131): the saved mixture, read-only by convention."""
+    return tmpStorage.from_shelf(path)
+
+
+ShelvedMixture = load_mixture
+
+
+class MixtureFactory(object):
+    """PCR_Mixture.py:134-249: same constructor arguments, `_sort_annealings`, `create_PCR_mixture`."""
+
+    def __init__(self, abort_event, primers, min_amplicon, max_amplicon, with_exonuclease=False,
+                 include_side_annealings=False):
+        self._abort_event = abort_event
+        self._primers = primers
+        self._min_amplicon = min_amplicon
+        self._max_amplicon = max_amplicon
+        self._with_exonuclease = with_exonuclease
+        self._include_side_annealings = include_side_annealings
+
+    def aborted(self):
+        return self._abort_event is not None and self._abort_event.is_set()
+
+    @staticmethod
+    def _add_side_annealings(mixture, sorted_annealings):
+        mixture.add_annealings(tuple((d, t) for _p, d, t in sorted_annealings))
+
+    def _sort_annealings(self, hit, strand, annealings, good, bad):
+        """Split every site's duplexes into those that can be extended (3' end annealed, or any when the
+        polymerase has 3'-5' exonuclease activity) and those that cannot (:161-191).  `position` is the
+        3' end of the primer: the site spans [pos-L+1, pos] on the forward strand, [pos, pos+L-1] on the reverse."""
+        for pos, duplexes in annealings:
+            length = duplexes[0].fwd_len
+            if strand:
+                template = Region(hit, pos - length + 1, pos, strand)
+            else:
+                template = Region(hit, pos, pos + length - 1, strand)
+            good_here, bad_here = (pos, [], template), (pos, [], template)
+            for duplex in duplexes:
+                if not any(duplex.fwd_seq in primer for primer in self._primers):
+                    continue                                  # no such primer in this system
+                if self._with_exonuclease or duplex.have_3_matches:
+                    good_here[1].append(duplex)
+                else:
+                    bad_here[1].append(duplex)
+            if good_here[1]:
+                good[strand].append(good_here)
+            if bad_here[1]:
+                bad.append(bad_here)
+
+    def create_PCR_mixture(self, counter, hit, fwd_annealings, rev_annealings):
+        """Pair forward and reverse sites into products (:194-249).  Returns a PCR_Mixture, or None when
+        there is no product.
+
+        The inner loop is kept as the reference has it, including what looks like two slips, because
+        the products it reports depend on them:
+          * `rev_start = rev_pi` stores an index into the SLICED list `good[0][rev_start:]`, so the
+            window start can move backwards;
+          * a pair shorter than min_amplicon `break`s the scan of reverse sites for this forward site
+            just like a pair longer than max_amplicon does;
+          * `added_positions[0]` remembers reverse sites by that same relative index.
+        """
+        if not fwd_annealings or not rev_annealings:
+            counter.done()
+            return None
+        counter.set_work(3 if self._include_side_annealings else 2)
+        hit = str(hit)
+        mixture = PCR_Mixture(hit)
+        good = ([], [])                  # [reverse, forward]
+        bad = []
+        self._sort_annealings(hit, 1, fwd_annealings, good, bad)
+        self._sort_annealings(hit, 0, rev_annealings, good, bad)
+        good[1].sort(key=lambda x: x[0])
+        good[0].sort(key=lambda x: x[0])
+        counter.count()
+        products_added = False
+        added = (set(), set())
+        rev_start = 0
+        for fwd_pi, (fwd_pos, fwd_dups, fwd_templ) in enumerate(good[1]):
+            start = fwd_pos + 1
+            for rev_pi, (rev_pos, rev_dups, rev_templ) in enumerate(good[0][rev_start:]):
+                end = rev_pos - 1
+                if start >= end:
+                    rev_start = rev_pi
+                    continue
+                if not self._min_amplicon <= end - start + 1 <= self._max_amplicon:
+                    break
+                mixture.add_product(start, end, fwd_dups, rev_dups)
+                if fwd_pi not in added[1]:
+                    mixture.add_annealing(fwd_dups, fwd_templ)
+                    added[1].add(fwd_pi)
+                if rev_pi not in added[0]:
+                    mixture.add_annealing(rev_dups, rev_templ)
+                    added[0].add(rev_pi)
+                products_added = True
+        counter.count()
+        if not products_added:
+            return None
+        if self._include_side_annealings:
+            self._add_side_annealings(mixture, [a for i, a in enumerate(good[1]) if i not in added[1]])
+            self._add_side_annealings(mixture, [a for i, a in enumerate(good[0]) if i not in added[0]])
+            self._add_side_annealings(mixture, bad)
+            counter.count()
+        return mixture

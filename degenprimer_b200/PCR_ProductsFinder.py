@@ -1,0 +1,126 @@
+"""PCR_ProductsFinder — host mirror of DegenPrimer/PCR_ProductsFinder.py:31-141: the caller of the hot
+path.  For every primer of the system it runs the scan + duplex stage (SearchEngine, i.e. the CUDA path)
+on a template, pools the annealing sites of all primers and pairs them into products (MixtureFactory).
+Same constructor and method names, argument order and return values (paths of saved mixtures, `None`
+when aborted or when nothing was found); the reference's Manager wrappers (:144-168) are not needed — there
+is no process fan-out to coordinate, the GPU grid is the fan-out.
+"""
+from .PCR_Mixture import MixtureFactory
+from .SearchEngine import SearchEngine
+from .SeqUtils import pretty_rec_name
+from .WorkCounter import WorkCounter
+from .tmpStorage import cleanup_files, from_shelf
+
+
+class PCR_ProductsFinder(MixtureFactory):
+    def __init__(self, abort_event, *args, **kwargs):
+        MixtureFactory.__init__(self, abort_event, *args, **kwargs)
+        self._searcher = SearchEngine(self._abort_event)
+        self._p_weights = [p.num_components for p in self._primers]
+        self._pw_sum = sum(self._p_weights)
+        self._num_p = len(self._primers)
+
+    @property
+    def searcher(self):
+        return self._searcher
+
+    @staticmethod
+    def _combine_annealings(*annealings_list):
+        """Pool the (fwd_results, rev_results) pairs of several primers (:57-65)."""
+        fwd, rev = [], []
+        for ann in annealings_list:
+            if ann[0]:
+                fwd.extend(ann[0])
+            if ann[1]:
+                rev.extend(ann[1])
+        return fwd, rev
+
+    @staticmethod
+    def _extract_annealings(*paths):
+        """The same for results that were handed over as temp files (:45-55)."""
+        fwd, rev = [], []
+        for path in paths:
+            ann = from_shelf(path)
+            if not ann:
+                continue
+            if ann[0]:
+                fwd.extend(ann[0])
+            if ann[1]:
+                rev.extend(ann[1])
+        return fwd, rev
+
+    def find_matches(self, counter, template, mismatches):
+        """Scan only: one 7-tuple per primer (:83-92)."""
+        all_matches = []
+        counter.set_subwork(self._num_p, self._p_weights)
+        for i, primer in enumerate(self._primers):
+            if self.aborted():
+                return None
+            matches = self._searcher.find_matches(counter[i], template, primer, mismatches)
+            if matches is None:
+                return None
+            all_matches.append(matches)
+        return all_matches
+
+    def matches_to_mixture(self, counter, tname, matches_list):
+        """Duplex stage + pairing for matches found earlier — the optimiser's inner loop (:67-81)."""
+        all_annealings = []
+        weights = [len(m) for m in matches_list]
+        counter.set_subwork(len(matches_list) + 1, weights + [0.01 * sum(weights)])
+        for i, matches in enumerate(matches_list):
+            if self.aborted():
+                return None
+            annealings = self._searcher.compile_duplexes_mp(counter[i], *matches)
+            if annealings is None:
+                return None
+            all_annealings.append(annealings)
+        mixture = self.create_PCR_mixture(counter[-1], tname, *self._combine_annealings(*all_annealings))
+        counter.done()
+        return mixture.save()          # like the reference, this raises when no product was found
+
+    def find(self, counter, template, mismatches):
+        """{template name: path of the saved mixture}, or None (:94-112)."""
+        all_annealings = []
+        counter.set_subwork(self._num_p + 1, self._p_weights + [0.01 * self._pw_sum])
+        for i, primer in enumerate(self._primers):
+            if self.aborted():
+                return None
+            annealings = self._searcher.find(counter[i], template, primer, mismatches)
+            if annealings is None:
+                continue
+            all_annealings.append(annealings)
+        if not all_annealings:
+            return None
+        tname = pretty_rec_name(template)
+        mixture = self.create_PCR_mixture(counter[-1], tname, *self._extract_annealings(*all_annealings))
+        cleanup_files(all_annealings)
+        counter.done()
+        if not mixture:
+            return None
+        return {tname: mixture.save()}
+
+    def batch_find(self, counter, templates, mismatches, **kwargs):
+        """Many short templates: {template name: path}, or None when nothing was found (:114-141)."""
+        results = dict()
+        counter.set_subwork(1)
+        counter[0].set_work(max(1, len(templates)))
+        for template in templates:
+            if self.aborted():
+                return None
+            search_results = []
+            for primer in self._primers:
+                matches = self._searcher.find_matches(WorkCounter(), template, primer, mismatches)
+                if not matches:
+                    continue
+                duplexes = self._searcher.compile_duplexes(WorkCounter(), *matches)
+                if duplexes:
+                    search_results.append(duplexes)
+            counter[0].count()
+            if not search_results:
+                continue
+            fwd, rev = self._combine_annealings(*search_results)
+            tname = pretty_rec_name(template)
+            mixture = self.create_PCR_mixture(WorkCounter(), tname, fwd, rev)
+            if mixture:
+                results[tname] = mixture.save()
+        return results or None

@@ -1,0 +1,195 @@
+"""Region / Product — host mirror of DegenPrimer/Product.py:30-215.
+
+Plain host objects: a PCR product is a template region bounded by the 3' ends of the forward and
+reverse primers that produce it, plus the sets of annealed primers (Duplex objects) on either side.
+PCR_Simulation and the reporters of the reference read `start, end, name, quantity, cycles,
+fwd_primers, rev_primers, fwd_template, rev_template, fwd_ids, rev_ids, pretty_print()`.
+"""
+from copy import deepcopy
+from math import log
+
+TEXT_WIDTH = 80      # BioUtils/Tools/Text.py:16
+
+
+def hr(text='', symbol='-', width=TEXT_WIDTH):
+    """Centered horizontal rule for short captions (BioUtils/Tools/Text.py:22-26)."""
+    return (' %s ' % text).center(width, symbol) + '\n\n'
+
+
+def format_concentration(quantity, unit='M'):
+    """TD_Functions.format_concentration = Text.format_quantity(c, 'M') (BioUtils/Tools/Text.py:125-139)."""
+    if quantity is None or quantity < 0:
+        return 'N/A  %s' % unit
+    if quantity == 0:
+        return '0.0  %s' % unit
+    mag = -log(quantity, 10)
+    for top, scale, prefix in ((0, 1, ' '), (3, 1e3, 'm'), (6, 1e6, 'u'), (9, 1e9, 'n'), (12, 1e12, 'p'),
+                               (15, 1e15, 'f')):
+        if mag < top:
+            return '%.1f %s%s' % (quantity * scale, prefix, unit)
+    return '%.1f a%s' % (quantity * 1e18, unit)
+
+
+class Region(object):
+    """A stretch [start, end] (1-based, inclusive) of one strand of a named sequence (Product.py:30-86)."""
+    __slots__ = ['name', 'start', 'end', 'forward']
+
+    def __init__(self, name, start, end, forward):
+        if start < 1 or end < 1:
+            raise ValueError('Region: start and end of a sequence region should be grater than 1.')
+        if start > end:
+            raise ValueError("Region: start of a sequence region should be less than it's end")
+        self.name, self.start, self.end, self.forward = name, start, end, forward
+
+    def pretty_print(self, with_name=True):
+        rep = 'target: %s\n' % self.name if with_name else ''
+        rep += 'strand: %s\n' % ('forward' if self.forward else 'reverse')
+        rep += 'start:  %d\n' % self.start
+        rep += 'end:    %d\n' % self.end
+        rep += 'length: %d\n' % len(self)
+        return rep
+
+    def __str__(self):
+        return self.pretty_print()
+
+    def __len__(self):
+        return self.end - self.start + 1
+
+    def __hash__(self):
+        return hash((self.name, self.start, self.end, self.forward))
+
+    def __eq__(self, other):
+        return hash(self) == hash(other)
+
+    def __ne__(self, other):
+        return hash(self) != hash(other)
+
+    def __iadd__(self, other):
+        """Grow to the union with a region of the same sequence and strand (:71-77)."""
+        if self.name == other.name and self.forward == other.forward:
+            self.start = min(self.start, other.start)
+            self.end = max(self.end, other.end)
+        return self
+
+    def overlaps(self, other):
+        """:79-86.  The reference's expression is `same_name and same_strand and start_inside or end_inside`:
+        the second alternative does not look at name or strand.  Kept as it is."""
+        return ((self.name == other.name and self.forward == other.forward
+                 and self.start <= other.start <= self.end)
+                or self.start <= other.end <= self.end)
+
+    def __getstate__(self):
+        return tuple(getattr(self, s) for s in Region.__slots__)
+
+    def __setstate__(self, state):
+        for s, v in zip(Region.__slots__, state):
+            setattr(self, s, v)
+
+
+class Product(Region):
+    """One PCR product (Product.py:89-215)."""
+    __slots__ = ['quantity', 'cycles', 'fwd_primers', 'rev_primers', '_fwd_margin', '_rev_margin',
+                 'fwd_template', 'rev_template']
+
+    def __init__(self, template_name, start, end, fwd_primers=(), rev_primers=()):
+        Region.__init__(self, template_name, start, end, forward=True)
+        self.quantity = 0
+        self.cycles = 0
+        self.fwd_primers = set()
+        self.rev_primers = set()
+        self._fwd_margin = max(self.start - 1, 1)
+        self._rev_margin = self.end + 1
+        self.fwd_template = Region(template_name, self._fwd_margin, self._fwd_margin, forward=True)
+        self.rev_template = Region(template_name, self._rev_margin, self._rev_margin, forward=False)
+        for p in fwd_primers:
+            self.add_fwd_primer(p)
+        for p in rev_primers:
+            self.add_rev_primer(p)
+
+    def add_fwd_primer(self, primer):
+        """The annealing site of a forward primer ends right before the product (:201-207)."""
+        if primer in self.fwd_primers:
+            return
+        self.fwd_primers.add(primer)
+        self.fwd_template += Region(self.name, max(self.start - primer.fwd_len, 1), max(self.start - 1, 1),
+                                    forward=True)
+
+    def add_rev_primer(self, primer):
+        if primer in self.rev_primers:
+            return
+        self.rev_primers.add(primer)
+        self.rev_template += Region(self.name, self.end + 1, self.end + primer.fwd_len, forward=False)
+
+    def __iadd__(self, other):
+        """Merge a product found again (:165-186): the wider end wins its side, equal ends pool primers."""
+        if self.name != other.name or self.forward != other.forward:
+            return self
+        if self.start > other.start:
+            self.start = other.start
+            self._fwd_margin = other._fwd_margin
+            self.fwd_template = deepcopy(other.fwd_template)
+            self.fwd_primers = deepcopy(other.fwd_primers)
+        elif self.start == other.start:
+            for p in other.fwd_primers:
+                self.add_fwd_primer(p)
+        if self.end < other.end:
+            self.end = other.end
+            self._rev_margin = other._rev_margin
+            self.rev_template = deepcopy(other.rev_template)
+            self.rev_primers = deepcopy(other.rev_primers)
+        elif self.end == other.end:
+            for p in other.rev_primers:
+                self.add_rev_primer(p)
+        return self
+
+    # Region defines __eq__, so the hash has to be named again for the subclass
+    __hash__ = Region.__hash__
+
+    @property
+    def fwd_ids(self):
+        return sorted(p.name for p in self.fwd_primers)
+
+    @property
+    def rev_ids(self):
+        return sorted(p.name for p in self.rev_primers)
+
+    @staticmethod
+    def _rep_primers(primers, tostr=repr):
+        return ''.join('%s:\n%s\n' % (p.name, tostr(p)) for p in sorted(primers, key=lambda x: x.name))
+
+    def pretty_print(self, with_name=True, include_fwd_3_mismatch=True):
+        rep = Region.pretty_print(self, with_name=with_name)
+        rep += '\n'
+        rep += 'concentration:    %s\n' % format_concentration(self.quantity)
+        rep += 'number of cycles: %d\n' % self.cycles
+        rep += '\n'
+        rep += hr(' forward annealing site ')
+        rep += self.fwd_template.pretty_print(with_name=False)
+        rep += '\n'
+        rep += hr(' reverse annealing site ')
+        rep += self.rev_template.pretty_print(with_name=False)
+        rep += '\n'
+        rep += hr(' forward primers ')
+        rep += self._rep_primers(self.fwd_primers, lambda p: p.print_most_stable(include_fwd_3_mismatch))
+        rep += '\n'
+        rep += hr(' reverse primers ')
+        rep += self._rep_primers(self.rev_primers, lambda p: p.print_most_stable(include_fwd_3_mismatch))
+        return rep
+
+    def __str__(self):
+        rep = Region.pretty_print(self)
+        rep += 'concentration:    %s\n' % format_concentration(self.quantity)
+        rep += 'number of cycles: %d\n' % self.cycles
+        rep += '\nforward annealing site:\n' + str(self.fwd_template)
+        rep += '\nreverse annealing site:\n' + str(self.rev_template)
+        rep += '\nforward primers:\n' + self._rep_primers(self.fwd_primers)
+        rep += '\nreverse primers:\n' + self._rep_primers(self.rev_primers)
+        return rep
+
+    def __getstate__(self):
+        return Region.__getstate__(self) + tuple(getattr(self, s) for s in Product.__slots__)
+
+    def __setstate__(self, state):
+        Region.__setstate__(self, state[:4])
+        for s, v in zip(Product.__slots__, state[4:]):
+            setattr(self, s, v)
