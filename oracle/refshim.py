@@ -6,10 +6,11 @@ Python-2.7-only and needs Biopython 1.66; this image has neither `python2`,
 anyway: a meta-path finder reads every `DegenPrimer.*` / `BioUtils.*` source
 file WHERE IT LIES under /root/reference (nothing is copied into this repo),
 rewrites Python-2 syntax in memory, and restores Python-2 semantics with an AST
-pass before compiling.  `tests/golden/make_reference_golden.py` uses it to record
-the reference's own outputs (hit positions, duplexes, dimers, dG, K, Tm) as
-committed fixtures; `tests/test_reference_golden.py` pins the oracle (and the
-CUDA path) to them.  Nothing under degenprimer_b200/ may import this file, and it
+pass before compiling.  `tests/golden/make_reference_golden.py` (scan, duplexes, dG, K,
+Tm), `make_reference_dimers.py` (SecStructures: self-/cross-dimers, hairpins) and
+`make_reference_mixture.py` (MixtureFactory: products) use it to record the reference's
+own outputs as committed fixtures; `tests/test_reference_*.py` pin the oracle, the host
+mirrors and the CUDA path to them.  Nothing under degenprimer_b200/ may import this file, and it
 cannot run on the GPU box (/root/reference does not exist there).
 
 What is rewritten (the complete list; everything else is the reference's code):
@@ -226,10 +227,13 @@ class _Py2Semantics(ast.NodeTransformer):
 
 
 def _py2div(a, b):
+    """Python-2 `/`: floor division when both operands are integers (bool and numpy integer scalars
+    included), true division otherwise.  Integer numpy ARRAYS would also floor-divide under Python 2;
+    the path never divides one (its arrays are float / complex), so that case is not emulated."""
     import numbers
     import numpy as np
-    if (isinstance(a, (numbers.Integral, np.integer)) and not isinstance(a, bool) or isinstance(a, bool)) \
-            and isinstance(b, (numbers.Integral, np.integer, bool)):
+    ints = (numbers.Integral, np.integer)
+    if isinstance(a, ints) and isinstance(b, ints):
         return a // b
     return a / b
 
