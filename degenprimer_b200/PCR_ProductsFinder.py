@@ -25,29 +25,24 @@ class PCR_ProductsFinder(MixtureFactory):
         return self._searcher
 
     @staticmethod
-    def _combine_annealings(*annealings_list):
-        """Pool the (fwd_results, rev_results) pairs of several primers (:57-65)."""
-        fwd, rev = [], []
-        for ann in annealings_list:
-            if ann[0]:
-                fwd.extend(ann[0])
-            if ann[1]:
-                rev.extend(ann[1])
-        return fwd, rev
+    def _pool(results):
+        """One forward and one reverse list out of the (fwd_results, rev_results) pairs of several primers."""
+        pooled = ([], [])
+        for pair in results:
+            for strand in (0, 1):
+                if pair and pair[strand]:
+                    pooled[strand].extend(pair[strand])
+        return pooled
 
-    @staticmethod
-    def _extract_annealings(*paths):
-        """The same for results that were handed over as temp files (:45-55)."""
-        fwd, rev = [], []
-        for path in paths:
-            ann = from_shelf(path)
-            if not ann:
-                continue
-            if ann[0]:
-                fwd.extend(ann[0])
-            if ann[1]:
-                rev.extend(ann[1])
-        return fwd, rev
+    @classmethod
+    def _combine_annealings(cls, *annealings_list):
+        """Results held in memory (PCR_ProductsFinder.py:57-65)."""
+        return cls._pool(annealings_list)
+
+    @classmethod
+    def _extract_annealings(cls, *paths):
+        """Results handed over as temp files (:45-55); an empty store contributes nothing."""
+        return cls._pool(from_shelf(path) for path in paths)
 
     def find_matches(self, counter, template, mismatches):
         """Scan only: one 7-tuple per primer (:83-92)."""

@@ -42,12 +42,10 @@ class Region(object):
         self.name, self.start, self.end, self.forward = name, start, end, forward
 
     def pretty_print(self, with_name=True):
-        rep = 'target: %s\n' % self.name if with_name else ''
-        rep += 'strand: %s\n' % ('forward' if self.forward else 'reverse')
-        rep += 'start:  %d\n' % self.start
-        rep += 'end:    %d\n' % self.end
-        rep += 'length: %d\n' % len(self)
-        return rep
+        rows = [('target', self.name)] if with_name else []
+        rows += [('strand', 'forward' if self.forward else 'reverse'), ('start', '%d' % self.start),
+                 ('end', '%d' % self.end), ('length', '%d' % len(self))]
+        return ''.join('%-8s%s\n' % (k + ':', v) for k, v in rows)
 
     def __str__(self):
         return self.pretty_print()
@@ -121,23 +119,20 @@ class Product(Region):
         self.rev_template += Region(self.name, self.end + 1, self.end + primer.fwd_len, forward=False)
 
     def __iadd__(self, other):
-        """Merge a product found again (:165-186): the wider end wins its side, equal ends pool primers."""
-        if self.name != other.name or self.forward != other.forward:
+        """Merge a product found again (:165-186): on either side the wider end replaces margin, template
+        and primers (deep copies), an equal end pools the primers."""
+        if (self.name, self.forward) != (other.name, other.forward):
             return self
-        if self.start > other.start:
-            self.start = other.start
-            self._fwd_margin = other._fwd_margin
-            self.fwd_template = deepcopy(other.fwd_template)
-            self.fwd_primers = deepcopy(other.fwd_primers)
-        elif self.start == other.start:
+        if other.start < self.start:
+            self.start, self._fwd_margin = other.start, other._fwd_margin
+            self.fwd_template, self.fwd_primers = deepcopy(other.fwd_template), deepcopy(other.fwd_primers)
+        elif other.start == self.start:
             for p in other.fwd_primers:
                 self.add_fwd_primer(p)
-        if self.end < other.end:
-            self.end = other.end
-            self._rev_margin = other._rev_margin
-            self.rev_template = deepcopy(other.rev_template)
-            self.rev_primers = deepcopy(other.rev_primers)
-        elif self.end == other.end:
+        if other.end > self.end:
+            self.end, self._rev_margin = other.end, other._rev_margin
+            self.rev_template, self.rev_primers = deepcopy(other.rev_template), deepcopy(other.rev_primers)
+        elif other.end == self.end:
             for p in other.rev_primers:
                 self.add_rev_primer(p)
         return self
@@ -157,34 +152,29 @@ class Product(Region):
     def _rep_primers(primers, tostr=repr):
         return ''.join('%s:\n%s\n' % (p.name, tostr(p)) for p in sorted(primers, key=lambda x: x.name))
 
+    def _status_lines(self):
+        return ('concentration:    %s\n' % format_concentration(self.quantity)
+                + 'number of cycles: %d\n' % self.cycles)
+
     def pretty_print(self, with_name=True, include_fwd_3_mismatch=True):
-        rep = Region.pretty_print(self, with_name=with_name)
-        rep += '\n'
-        rep += 'concentration:    %s\n' % format_concentration(self.quantity)
-        rep += 'number of cycles: %d\n' % self.cycles
-        rep += '\n'
-        rep += hr(' forward annealing site ')
-        rep += self.fwd_template.pretty_print(with_name=False)
-        rep += '\n'
-        rep += hr(' reverse annealing site ')
-        rep += self.rev_template.pretty_print(with_name=False)
-        rep += '\n'
-        rep += hr(' forward primers ')
-        rep += self._rep_primers(self.fwd_primers, lambda p: p.print_most_stable(include_fwd_3_mismatch))
-        rep += '\n'
-        rep += hr(' reverse primers ')
-        rep += self._rep_primers(self.rev_primers, lambda p: p.print_most_stable(include_fwd_3_mismatch))
-        return rep
+        """Report layout of Product.py:128-147: region, status, both annealing sites, both primer lists."""
+        def show(duplex):
+            return duplex.print_most_stable(include_fwd_3_mismatch)
+        parts = [Region.pretty_print(self, with_name=with_name), self._status_lines()]
+        for caption, site in ((' forward annealing site ', self.fwd_template),
+                              (' reverse annealing site ', self.rev_template)):
+            parts.append(hr(caption) + site.pretty_print(with_name=False))
+        for caption, primers in ((' forward primers ', self.fwd_primers), (' reverse primers ', self.rev_primers)):
+            parts.append(hr(caption) + self._rep_primers(primers, show))
+        return '\n'.join(parts)
 
     def __str__(self):
-        rep = Region.pretty_print(self)
-        rep += 'concentration:    %s\n' % format_concentration(self.quantity)
-        rep += 'number of cycles: %d\n' % self.cycles
-        rep += '\nforward annealing site:\n' + str(self.fwd_template)
-        rep += '\nreverse annealing site:\n' + str(self.rev_template)
-        rep += '\nforward primers:\n' + self._rep_primers(self.fwd_primers)
-        rep += '\nreverse primers:\n' + self._rep_primers(self.rev_primers)
-        return rep
+        """Plain layout of Product.py:149-162."""
+        return ''.join((Region.pretty_print(self), self._status_lines(),
+                        '\nforward annealing site:\n', str(self.fwd_template),
+                        '\nreverse annealing site:\n', str(self.rev_template),
+                        '\nforward primers:\n', self._rep_primers(self.fwd_primers),
+                        '\nreverse primers:\n', self._rep_primers(self.rev_primers)))
 
     def __getstate__(self):
         return Region.__getstate__(self) + tuple(getattr(self, s) for s in Product.__slots__)

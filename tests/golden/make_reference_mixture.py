@@ -35,6 +35,18 @@ CASES = [
 ]
 
 
+class StubDuplex(object):
+    """What Product reads of a Duplex: name, fwd_len, print_most_stable(), repr."""
+    def __init__(self, name, n):
+        self.name, self.fwd_len = name, n
+
+    def print_most_stable(self, include_fwd_3_mismatch=True):
+        return 'duplex %s %s\n' % (self.name, include_fwd_3_mismatch)
+
+    def __repr__(self):
+        return 'rep %s' % self.name
+
+
 def main():
     ns = refshim.load()
     import DegenPrimer.PCR_Mixture as pm
@@ -76,6 +88,13 @@ def main():
                 'annealings': [[region(tpl), [d.name for d in dups]] for dups, tpl in mix.annealings]}
         gold['cases'].append(case)
         print(cond, n_sites, None if mix is None else (len(mix.products), len(mix.annealings)), flush=True)
+    # report text of Product / Region with stand-in duplexes (DP/Product.py:54-66,128-162)
+    import DegenPrimer.Product as rp
+    a = rp.Product('t seq', 101, 300, [StubDuplex('P_1', 20), StubDuplex('P_2', 25)], [StubDuplex('R_1', 18)])
+    a.quantity, a.cycles = 2.5e-7, 12
+    gold['texts'] = {'str': str(a), 'pretty': a.pretty_print(), 'pretty_no_name_no_3': a.pretty_print(False, False),
+                     'region': str(rp.Region('x', 3, 9, False)), 'fwd_ids': a.fwd_ids,
+                     'fwd_template': [a.fwd_template.start, a.fwd_template.end]}
     out = os.path.join(HERE, 'reference_mixture.json.gz')
     with open(out, 'wb') as raw, gzip.GzipFile(fileobj=raw, mode='wb', mtime=0, filename='') as fh:
         fh.write(json.dumps(gold, separators=(',', ':'), default=lambda o: o.item()).encode())

@@ -249,3 +249,14 @@ def test_products_finder_composition(idx):
     ev.set()
     ppf._abort_event = ev
     assert ppf.find(WorkCounter(), rec, case['k']) is None and ppf.find_matches(WorkCounter(), rec, case['k']) is None
+
+
+def test_product_text_equals_reference():
+    from tests.golden.make_reference_mixture import StubDuplex
+    want = REF['texts']
+    a = Product('t seq', 101, 300, [StubDuplex('P_1', 20), StubDuplex('P_2', 25)], [StubDuplex('R_1', 18)])
+    a.quantity, a.cycles = 2.5e-7, 12
+    assert str(a) == want['str'] and a.pretty_print() == want['pretty']
+    assert a.pretty_print(False, False) == want['pretty_no_name_no_3']
+    assert str(Region('x', 3, 9, False)) == want['region'] and a.fwd_ids == want['fwd_ids']
+    assert [a.fwd_template.start, a.fwd_template.end] == want['fwd_template']
