@@ -25,6 +25,15 @@ def segments(t_len, world_size):
     return out
 
 
+def shard_pairs(n_pairs, world_size, rank):
+    """[begin, end) of the sequence pairs rank `rank` evaluates in a sharded `find_dimers_batch` /
+    `SecStructures.batch`: pairs are independent, so the shards are contiguous, differ by
+    at most one pair and need no exchange but the final gather of the (small) result records."""
+    base, extra = divmod(n_pairs, world_size)
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
 def shard_bounds(t_len, world_size, rank, max_primer_len):
     """(base_begin, base_end, start_begin, start_end) of this rank's slice."""
     b, e = segments(t_len, world_size)[rank]

@@ -80,3 +80,45 @@ def test_segments_cover_and_align():
             assert seg[0][0] == 0 and seg[-1][1] == T
             assert all(a[1] == b[0] for a, b in zip(seg, seg[1:]))
             assert all(b % 32 == 0 for b, _ in seg if b < T)
+
+
+def _pairs_worker(rank, world, port, seqs, pairs, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from degenprimer_b200 import distributed as D
+    from oracle import conditions as ocond
+    from oracle.structures import find_dimers
+    dist.init_process_group('gloo', init_method='tcp://127.0.0.1:%d' % port, rank=rank, world_size=world)
+    ocond.PCR_P.set(dict(Na=50e-3, Mg=3e-3, dNTP=0.3e-3, DNA=1e-10, DMSO=0.0, PCR_T=40.0))
+    b, e = D.shard_pairs(len(pairs), world, rank)
+    rec = np.zeros(e - b, dtype=[('pair', '<u4'), ('n', '<u4'), ('min_dG', '<f8')])
+    for k, (i, j) in enumerate(pairs[b:e]):
+        dimers = find_dimers(seqs[i], seqs[j])[0]
+        rec[k] = (b + k, len(dimers), min((d.dG for d in dimers), default=0.0))
+    allr = D.all_gather_records(rec)
+    np.save(os.path.join(out_dir, 'pairs%d.npy' % rank), allr[np.argsort(allr['pair'])])
+    dist.destroy_process_group()
+
+
+def test_sharded_dimer_pairs_equal_whole(tmp_path):
+    """N3 shards by sequence pair: two ranks, each its slice (the oracle stands in for dp_find_dimers), one
+    variable-length gather; every rank ends up with the records of all pairs."""
+    from degenprimer_b200 import distributed as D
+    from oracle import conditions as ocond
+    from oracle.structures import find_dimers
+    for n, w in ((7, 2), (8, 3), (2, 4), (0, 2)):
+        cuts = [D.shard_pairs(n, w, r) for r in range(w)]
+        assert cuts[0][0] == 0 and cuts[-1][1] == n and all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
+        assert max(e - b for b, e in cuts) - min(e - b for b, e in cuts) <= 1
+    rng = np.random.default_rng(3)
+    seqs = [''.join(rng.choice(list('ACGT'), size=int(n))) for n in rng.integers(12, 30, size=9)]
+    seqs += ['GGGAAATTTCCCGGGAAATTTCCC', 'GCGGCCGCTTTTGCGGCCGC']
+    pairs = [(i, j) for i in range(len(seqs)) for j in range(i, len(seqs))][:41]
+    port = _free_port()
+    mp.spawn(_pairs_worker, args=(2, port, seqs, pairs, str(tmp_path)), nprocs=2, join=True)
+    ocond.PCR_P.set(dict(Na=50e-3, Mg=3e-3, dNTP=0.3e-3, DNA=1e-10, DMSO=0.0, PCR_T=40.0))
+    want = [(k, len(find_dimers(seqs[i], seqs[j])[0])) for k, (i, j) in enumerate(pairs)]
+    for rank in range(2):
+        got = np.load(os.path.join(str(tmp_path), 'pairs%d.npy' % rank))
+        assert [(int(r['pair']), int(r['n'])) for r in got] == want
+    assert sum(n for _, n in want) > 5
