@@ -29,6 +29,7 @@ What is rewritten (the complete list; everything else is the reference's code):
         (A2) a class defining `__nonzero__` also gets `__bool__` (DP/SecStructures.py:103,257: `if dup:`)
         (A3) class-body `__metaclass__ = M` -> `class C(..., metaclass=M)` (DP/PCR_Parameters.py:67)
         (A4) `d.keys()/values()/items()` -> list(...)  (DP/UnifiedNN.py:214 mutates while iterating)
+        (A5) a class defining `__div__` / `__idiv__` also answers `/` and `/=` (DP/UnifiedNN.py:65-74: Pars)
   names (N1) module globals `map`, `filter`, `zip`, `range` return lists; `xrange`, `basestring`, `unicode`,
              `long`, `reduce`, `raw_input` exist.
   deps  (D1) Biopython stand-ins `Bio.Seq.Seq`, `Bio.SeqRecord.SeqRecord`, `Bio.Alphabet.IUPAC`, `Bio.SeqIO`
@@ -196,7 +197,7 @@ class _Py2Semantics(ast.NodeTransformer):
             for n in ast.walk(load):
                 if hasattr(n, 'ctx'):
                     n.ctx = ast.Load()
-            call = ast.Call(func=ast.Name(id='__py2div__', ctx=ast.Load()), args=[load, node.value], keywords=[])
+            call = ast.Call(func=ast.Name(id='__py2idiv__', ctx=ast.Load()), args=[load, node.value], keywords=[])
             return ast.copy_location(ast.Assign(targets=[node.target], value=call), node)
         return node
 
@@ -207,6 +208,9 @@ class _Py2Semantics(ast.NodeTransformer):
             if isinstance(stmt, ast.FunctionDef) and stmt.name == '__nonzero__':                        # A2
                 extra.append(ast.Assign(targets=[ast.Name(id='__bool__', ctx=ast.Store())],
                                         value=ast.Name(id='__nonzero__', ctx=ast.Load())))
+            if isinstance(stmt, ast.FunctionDef) and stmt.name in ('__div__', '__idiv__', '__rdiv__'):   # A5
+                extra.append(ast.Assign(targets=[ast.Name(id=stmt.name.replace('div', 'truediv'), ctx=ast.Store())],
+                                        value=ast.Name(id=stmt.name, ctx=ast.Load())))
             if (isinstance(stmt, ast.Assign) and len(stmt.targets) == 1 and isinstance(stmt.targets[0], ast.Name)
                     and stmt.targets[0].id == '__metaclass__'):                                         # A3
                 node.keywords.append(ast.keyword(arg='metaclass', value=stmt.value))
@@ -238,6 +242,14 @@ def _py2div(a, b):
     return a / b
 
 
+def _py2idiv(a, b):
+    """Python-2 `a /= b`: the object's own `__idiv__` (in place) when it has one, else `a = a / b`."""
+    own = getattr(type(a), '__idiv__', None)
+    if own is not None:
+        return own(a, b)
+    return _py2div(a, b)
+
+
 def _py2list(x):
     # dict views become lists; anything else that happens to have a .keys()/.values()/.items() method and already
     # returns a list/dict/proxy is passed through untouched
@@ -260,7 +272,7 @@ def _py2_map(fn, *seqs):
 
 
 _NAMES = {
-    '__py2div__': _py2div, '__py2list__': _py2list,
+    '__py2div__': _py2div, '__py2idiv__': _py2idiv, '__py2list__': _py2list,
     'map': _py2_map, 'filter': _listing(builtins.filter), 'zip': _listing(builtins.zip),
     'range': _listing(builtins.range), 'xrange': builtins.range,
     'basestring': str, 'unicode': str, 'long': int, 'reduce': functools.reduce, 'raw_input': input,

@@ -154,10 +154,21 @@ def main():
                                                ('dmso_hot', PRIMERS[2], 4, 14, 6000, 14),
                                                ('cold', LONG35, 4, 15, 6000, 10),
                                                ('test_ipcr', BIG, 3, 16, 3000, 3),
-                                               ('cold', SHORT18, 4, 17, 30000, 12)):
+                                               ('cold', SHORT18, 4, 17, 30000, 12),
+                                               # ambiguous template letters INSIDE the annealing windows: the NN
+                                               # parameters of those stacks are averages over the expansions
+                                               # (UnifiedNN.int_dPar_37, DP/UnifiedNN.py:224-246)
+                                               ('readme', PRIMERS[1], 3, 18, 6000, 24),
+                                               ('test_ipcr', PRIMERS[0], 4, 19, 6000, 24)):
         print('duplex', cname, master, flush=True)
         tdf.PCR_P.set(CONDS[cname])
         t = make_template(seed, n, *FEW_N, [master], k, n_plant)
+        if seed in (18, 19):
+            rng = np.random.default_rng(seed + 100)
+            chars = list(t)
+            for at in rng.choice(len(chars), size=len(chars) // 25, replace=False):
+                chars[at] = 'NRYSWKMBDHV'[int(rng.integers(11))]
+            t = ''.join(chars)
         pr = primer(master)
         r = eng._find(WC(), record(t), pr, len(t), len(master), k)
         mp = None

@@ -95,6 +95,15 @@ def main():
     gold['texts'] = {'str': str(a), 'pretty': a.pretty_print(), 'pretty_no_name_no_3': a.pretty_print(False, False),
                      'region': str(rp.Region('x', 3, 9, False)), 'fwd_ids': a.fwd_ids,
                      'fwd_template': [a.fwd_template.start, a.fwd_template.end]}
+    # the reference's own Product smoke test (Tests/DegenPrimer_Tests/Test_Product.py:27-39): two duplexes of
+    # DEGENERATE primers with their reverse complements (NN parameters averaged over the expansions)
+    tdf.PCR_P.set(CONDS['default'])
+    rcomp, Duplex = ns.SecStructures.reverse_complement, ns.SecStructures.Duplex
+    fp, rp_ = 'ATARTCTYCGAMGGCTATCC', 'NAAGGYTTAGAKGCGGAAG'
+    d1, d2 = Duplex(fp, rcomp(fp)), Duplex(rp_, rcomp(rp_))
+    tp = rp.Product('test_template', 50, 150, (d1,), (d2,))
+    gold['test_product'] = {'cond': 'default', 'fwd': fp, 'rev': rp_, 'str': str(tp), 'pretty': tp.pretty_print(),
+                            'dG': [d1.dG, d2.dG]}
     out = os.path.join(HERE, 'reference_mixture.json.gz')
     with open(out, 'wb') as raw, gzip.GzipFile(fileobj=raw, mode='wb', mtime=0, filename='') as fh:
         fh.write(json.dumps(gold, separators=(',', ':'), default=lambda o: o.item()).encode())

@@ -260,3 +260,19 @@ def test_product_text_equals_reference():
     assert a.pretty_print(False, False) == want['pretty_no_name_no_3']
     assert str(Region('x', 3, 9, False)) == want['region'] and a.fwd_ids == want['fwd_ids']
     assert [a.fwd_template.start, a.fwd_template.end] == want['fwd_template']
+
+
+def test_reference_product_smoke_test():
+    """Tests/DegenPrimer_Tests/Test_Product.py:27-39 — the one assertion the reference's tests make on this
+    side of the path: a Product of two duplexes survives save/load with the same text.  Here also: that text
+    equals the reference's (recorded), with the oracle's Duplex (degenerate primers: averaged NN parameters)."""
+    from oracle.sequtils import reverse_complement
+    from oracle.structures import Duplex
+    want = REF['test_product']
+    ocond.PCR_P.set(REF['conds'][want['cond']])
+    d1 = Duplex(want['fwd'], reverse_complement(want['fwd']))
+    d2 = Duplex(want['rev'], reverse_complement(want['rev']))
+    assert [d1.dG, d2.dG] == want['dG']
+    p = Product('test_template', 50, 150, (d1,), (d2,))
+    p1 = pickle.loads(pickle.dumps(p))
+    assert str(p) == str(p1) == want['str'] and p.pretty_print() == p1.pretty_print() == want['pretty']

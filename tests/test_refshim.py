@@ -50,13 +50,20 @@ def test_py2_semantics():
         "    __metaclass__ = M",
         "    def __init__(self, n): self.n = n",
         "    def __nonzero__(self): return self.n > 0",
+        "class P(object):",
+        "    def __init__(self, v): self.v = v",
+        "    def __div__(self, d): return P(self.v / d)",
+        "    def __idiv__(self, d):",
+        "        self.v /= d",
+        "        return self",
+        "p = P(9); q = p; p /= 2; r = (P(7.0) / 2).v; same = p is q and p.v == 4",
         "a = 7/2; b = 7/2.0; c = 9; c /= 2; d = -7/2",
         "e = map(lambda x: x/2, range(4)); f = zip('ab', 'cd')",
         "t = {'x': 1, 'y': 2}",
         "for k in t.keys(): t[k+k] = 0",
         "z = (bool(A(0)), bool(A(1)), A.tagged)"]), '<t>')
     exec(code, ns)
-    assert (ns['a'], ns['b'], ns['c'], ns['d']) == (3, 3.5, 4, -4)
+    assert (ns['a'], ns['b'], ns['c'], ns['d']) == (3, 3.5, 4, -4) and ns['same'] and ns['r'] == 3.5
     assert ns['e'] == [0, 0, 1, 1] and ns['f'] == [('a', 'c'), ('b', 'd')]
     assert sorted(ns['t']) == ['x', 'xx', 'y', 'yy'] and ns['z'] == (False, True, True)
 
