@@ -296,3 +296,68 @@ def test_host_mirrors_equal_reference():
         assert [list(x.fwd_matches) for x in dm.alternatives] == case['alternatives']
     for case in REF['scan']:
         assert hashlib.sha1(g_rc(case['template']).encode()).hexdigest() == case['rev_seq_sha1']
+
+
+def test_device_tables_reproduce_reference_dG_on_ambiguous_windows():
+    """The flattened NN tables the kernels index (UnifiedNN.device_tables: stack / rstack averaged over the
+    expansions of an ambiguous template letter, loop_dS, terminal terms) walked in Python exactly as
+    dp_dimer_dg_device walks them (offset 0: left-aligned primer/window duplexes) give the reference's dG for
+    every dimer of the duplex cases whose windows contain N / IUPAC letters — no GPU involved."""
+    from degenprimer_b200 import _native as nat
+    from degenprimer_b200.UnifiedNN import UnifiedNN
+    T = UnifiedNN.device_tables()
+    letter = {c: i for i, c in enumerate(nat.LETTERS)}
+    comp = [2, 3, 0, 1, 5, 4, 6, 7, 9, 8, 13, 12, 11, 10, 14]
+
+    def stack(tab, x, y, w):
+        return tab[(x * 4 + y) * 15 + w]
+
+    def dimer_dg(s, r, mask, PCR_T, Na_eq_log):
+        L = len(s)
+        fm = [i for i in range(L) if mask >> i & 1]
+        f0, f1 = fm[0], fm[-1]
+        dG, dH, dS = 0.0, T.ini_dH, T.ini_dS
+        if f0 == 0:
+            if s[0] in (0, 2):
+                dH += T.ter_dH
+                dS += T.ter_dS
+        else:
+            dG += T.terminal_mismatch
+        if f1 < L - 1:
+            dG += T.terminal_mismatch
+        elif s[L - 1] in (0, 2):
+            dH += T.ter_dH
+            dS += T.ter_dS
+        for a, b in zip(fm, fm[1:]):
+            gap = b - a
+            if gap < 4:
+                assert r[a] == comp[s[a]]
+                dH += stack(T.stack_dH, s[a], s[a + 1], r[a + 1])
+                dS += stack(T.stack_dS, s[a], s[a + 1], r[a + 1])
+                if gap > 1:
+                    dH += stack(T.rstack_dH, s[b - 1], s[b], r[b - 1])
+                    dS += stack(T.rstack_dS, s[b - 1], s[b], r[b - 1])
+            else:
+                dS += T.loop_dS[gap - 1]
+        dS += T.dS_Na * (f1 - f0) * Na_eq_log
+        return dG + dH - (PCR_T - T.K0) * dS / 1000.0
+
+    checked = ambiguous = 0
+    for case in REF['duplex'][-2:]:
+        ocond.PCR_P.set(CONDS[case['cond']])
+        p = OPrimer(OSeqRecord(case['master'], id='P'), 1e-6)
+        variants = dict(zip([r.id for r in p.seq_records], p.str_sequences))
+        t, L = case['template'], len(case['master'])
+        rc = reverse_complement(t)
+        for strand, lst in enumerate(case['serial']):
+            for pos, dups in lst or []:
+                window = t[pos - L:pos] if strand == 0 else rc[len(t) + 1 - pos - L:len(t) + 1 - pos]
+                ambiguous += any(c not in 'ACGT' for c in window)
+                r = [comp[letter[c]] for c in window]                     # 3'->5' complement strand under the primer
+                for name, _, _, _, dimers in dups:
+                    s = [letter[c] for c in variants[name]]
+                    for mask, offset, dG, _, _ in dimers:
+                        assert offset == 0
+                        assert dimer_dg(s, r, mask, ocond.PCR_P.PCR_T, ocond.PCR_P.Na_eq_log) == dG
+                        checked += 1
+    assert checked > 300 and ambiguous >= 10
