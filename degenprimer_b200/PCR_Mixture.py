@@ -4,9 +4,9 @@ The step right after the hot path: annealing sites of both strands (the `(positi
 SearchEngine.compile_duplexes[_mp] returns) are split into sites that can prime a product and sites
 that cannot, and forward / reverse sites are paired into products of [min_amplicon, max_amplicon].
 This is host code on purpose: the pairing loop of the reference carries state from one forward site
-to the next (see `create_PCR_mixture`), so its exact result is a sequential walk over two sorted lists
-— microseconds of work for the site counts the scan produces — and everything else is object
-bookkeeping that PCR_Simulation reads (`reaction_id, annealings, templates, products`).
+to the next (see `create_PCR_mixture`), so its exact result is a sequential walk over two sorted lists,
+and nearly all of its time is object bookkeeping that PCR_Simulation reads (`reaction_id, annealings,
+templates, products`): 674 sites -> 3393 products take 139 ms here, 173 ms in the reference (same box).
 """
 from . import tmpStorage
 from .Product import Product, Region
