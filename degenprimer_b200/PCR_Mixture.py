@@ -126,7 +126,7 @@ class MixtureFactory(object):
         """Pair forward and reverse sites into products (:194-249).  Returns a PCR_Mixture, or None when
         there is no product.
 
-        The inner loop is kept as the reference has it, including what looks like two slips, because
+        The inner loop is kept as the reference has it, including what look like slips, because
         the products it reports depend on them:
           * `rev_start = rev_pi` stores an index into the SLICED list `good[0][rev_start:]`, so the
             window start can move backwards;

@@ -12,8 +12,14 @@ TEXT_WIDTH = 80      # BioUtils/Tools/Text.py:16
 
 
 def hr(text='', symbol='-', width=TEXT_WIDTH):
-    """Centered horizontal rule for short captions (BioUtils/Tools/Text.py:22-26)."""
-    return (' %s ' % text).center(width, symbol) + '\n\n'
+    """Centered horizontal rule (BioUtils/Tools/Text.py:22-26): an empty caption gives just the blank
+    lines; captions longer than the line are wrapped first."""
+    if len(text) > TEXT_WIDTH - 4:
+        import textwrap
+        lines = textwrap.wrap(' '.join(text.split()), TEXT_WIDTH * 3 // 4)
+    else:
+        lines = [text]
+    return '\n'.join((' %s ' % l).center(width, symbol) for l in lines if l) + '\n\n'
 
 
 def format_concentration(quantity, unit='M'):

@@ -528,8 +528,8 @@ def find_hairpins_batch(dimer_sets, return_ms=False):
 
 class SecStructures(object):
     """Self-dimers and hairpins of one sequence, or cross-dimers of two
-    (DegenPrimer/SecStructures.py:389-605): same constructor, same attributes and query methods;
-    the report formatting (`_format_*`, :720-871) stays with the reference's reporters.
+    (DegenPrimer/SecStructures.py:389-871): same constructor, same attributes, query methods and report
+    text (`str()`, `formatFull()`, `formatShort()`).
     `SecStructures.batch(records, pairs)` builds many of them from two kernel launches."""
 
     def __init__(self, seq_rec1, seq_rec2=None, _dimer_set=None, _hairpin_set=None):
@@ -647,3 +647,122 @@ class SecStructures(object):
 
     def hairpinMin_3prim_dG(self):
         return self._min_3prim_hairpin_dG if self._min_3prim_hairpin_dG else None
+
+    # ---- report text (SecStructures.py:528-567,718-871) -----------------------------------------
+    def formatFull(self):
+        return self._format_str(full=True)
+
+    def formatShort(self):
+        return self._format_str(full=False)
+
+    def __str__(self):
+        return self._format_str()
+
+    def _format_str(self, full=True):
+        """All structures (`full`) or counts, minimum dG and the most stable ones; cross-dimers for two
+        sequences, self-dimers and hairpins for one."""
+        from .Product import hr
+        show_dimers = self._format_dimers if full else self._format_dimers_short
+        show_hairpins = self._format_hairpins if full else self._format_hairpins_short
+        by_dG = lambda table: sorted(table.values(), key=lambda x: x.dG)
+        seq1 = str(self._seq1)
+        out = ['\n']
+        if self._seq2:
+            out.append(hr(' %s vs %s cross-dimers ' % (self._seq_rec1.id, self._seq_rec2.id), symbol='='))
+            out.append(show_dimers(by_dG(self._cross_dimers), seq1, str(self._seq2)))
+        else:
+            out.append(hr(' %s: %s ' % (self._seq_rec1.id, seq1), symbol='='))
+            out.append(hr(' self-dimers '))
+            out.append(show_dimers(by_dG(self._seq1_dimers), seq1, seq1))
+            out.append(hr(' hairpins '))
+            out.append(show_hairpins(by_dG(self._seq1_hairpins), seq1))
+        out.append(hr('', symbol='='))
+        return ''.join(out)
+
+    @staticmethod
+    def _is_3prim_dimer(dimer, seq1):
+        return dimer.fwd_matches[-1] > len(seq1) - 4 or dimer.rev_min < 3
+
+    @classmethod
+    def _format_dimer(cls, dimer, seq1, seq2):
+        text = Duplex.print_dimer(str(seq1), str(seq2), dimer)
+        if cls._is_3prim_dimer(dimer, seq1):
+            text += "(3'-dimer)\n"
+        return text + '\n'
+
+    def _format_dimers_header(self, dimers):
+        if not dimers:
+            return 'No dimers found.\n\n'
+        lines = ['Dimers count: %d' % len(dimers)]
+        if self._3prim_dimers:
+            lines.append("3'-dimers count: %d" % self._3prim_dimers)
+        lines.append('Most stable dimer: %.2f kcal/mol' % self.dimerMin_dG())
+        if self._3prim_dimers:
+            lines.append("Most stable 3' dimer: %.2f kcal/mol" % self.dimerMin_3prim_dG())
+        return '\n'.join(lines) + '\n\n'
+
+    def _format_dimers(self, dimers, seq1, seq2):
+        if not dimers:
+            return 'No dimers found.\n\n'
+        return self._format_dimers_header(dimers) + ''.join(self._format_dimer(d, seq1, seq2) for d in dimers)
+
+    def _format_dimers_short(self, dimers, seq1, seq2):
+        """Header, the most stable dimer and the most stable 3' dimer (once, if they are the same)."""
+        if not dimers:
+            return 'No dimers found.\n\n'
+        text = self._format_dimers_header(dimers)
+        if self.dimerMin_dG() and dimers[0] != self._min_3prim_dimer:
+            text += self._format_dimer(dimers[0], seq1, seq2)
+        if self.dimerMin_3prim_dG():
+            text += self._format_dimer(self._min_3prim_dimer, seq1, seq2)
+        return text
+
+    @classmethod
+    def _format_hairpin(cls, hairpin, seq):
+        """The folded sequence drawn as two rows joined at the loop (SecStructures.py:779-829)."""
+        seq = str(seq)
+        fm, rm = hairpin.fwd_matches, hairpin.rev_matches
+        loop = rm[-1] - fm[-1] - 1
+        odd = loop % 2
+        half = (loop - odd) // 2
+        fwd_tail, rev_tail = fm[0], len(seq) - rm[0] - 1
+        turn = fm[-1] + half + 1                       # first base of the lower row (after the middle base, if any)
+        bars = '|'
+        for a, b in zip(fm, fm[1:]):
+            bars += ' ' * (b - a - 1) + '|'
+        shift = abs(fwd_tail - rev_tail)
+        pad_top, pad_bottom = ('', ' ' * shift) if fwd_tail > rev_tail else (' ' * shift, '')
+        text = "%s5' %s\n" % (pad_top, seq[:turn])
+        text += '%s%s%s%s\n' % (' ' * (max(fwd_tail, rev_tail) + 3), bars, ' ' * half, seq[turn] if odd else ']')
+        text += "%s3' %s\n" % (pad_bottom, seq[turn + odd:][::-1])
+        if hairpin.dG is not None:
+            text += 'dG(%.1fC) = %.2f kcal/mol\n' % (tdf.PCR_P.PCR_T, hairpin.dG)
+        if hairpin.conversion_degree is not None:
+            text += 'conversion degree = %.4f%%\n' % (hairpin.conversion_degree * 100)
+        if rm[0] > len(seq) - 4:
+            text += "(3'-hairpin)\n"
+        return text + '\n'
+
+    def _format_hairpins_header(self, hairpins):
+        lines = ['Hairpins count: %d' % len(hairpins)]
+        if self._3prim_hairpins:
+            lines.append("3'-hairpins count: %d" % self._3prim_hairpins)
+        lines.append('Most stable hairpin: %.2f kcal/mol' % self.hairpinMin_dG())
+        if self._3prim_hairpins:
+            lines.append("Most stable 3' hairpin: %.2f kcal/mol" % self.hairpinMin_3prim_dG())
+        return '\n'.join(lines) + '\n\n'
+
+    def _format_hairpins(self, hairpins, seq):
+        if not hairpins:
+            return 'No hairpins found\n\n'
+        return self._format_hairpins_header(hairpins) + ''.join(self._format_hairpin(h, seq) for h in hairpins)
+
+    def _format_hairpins_short(self, hairpins, seq):
+        if not hairpins:
+            return 'No hairpins found\n\n'
+        text = self._format_hairpins_header(hairpins)
+        if self.hairpinMin_dG() and hairpins[0] is not self._min_3prim_hairpin:
+            text += self._format_hairpin(hairpins[0], seq)
+        if self.hairpinMin_3prim_dG():
+            text += self._format_hairpin(self._min_3prim_hairpin, seq)
+        return text

@@ -6,6 +6,7 @@ oracle/refshim.py — SURVEY §8(f) N3.  See make_reference_golden.py for how th
 usage: python tests/golden/make_reference_dimers.py
 """
 import gzip
+import hashlib
 import json
 import os
 import sys
@@ -53,6 +54,9 @@ def main():
                     'n_3prim': s._3prim_dimers, 'min_3prim_dG': s._min_3prim_dimer_dG,
                     'hairpins': [[list(h.fwd_matches), list(h.rev_matches), h.dG] for h in s._seq1_hairpins.values()],
                     'n_3prim_hairpins': s._3prim_hairpins}
+            case['text_sha1'] = [hashlib.sha1(x.encode()).hexdigest() for x in (str(s), s.formatShort())]
+            if i < 6 and cname == 'readme':
+                case['text'] = [str(s), s.formatShort()]
             seeds = s._find_dimers(s._seq1, s._seq1)['hairpins']
             case['fronts'] = [[mask_of(x.fwd_matches), x.offset] for x in seeds.values()]
             gold['cases'].append(case)
@@ -63,7 +67,9 @@ def main():
                     continue
                 c = SS(rec(a, i), rec(b, j))
                 gold['cases'].append({'cond': cname, 'a': i, 'b': j, 'dimers': dump_dimers(c._cross_dimers),
-                                      'n_3prim': c._3prim_dimers, 'min_3prim_dG': c._min_3prim_dimer_dG})
+                                      'n_3prim': c._3prim_dimers, 'min_3prim_dG': c._min_3prim_dimer_dG,
+                                      'text_sha1': [hashlib.sha1(x.encode()).hexdigest()
+                                                    for x in (str(c), c.formatShort())]})
     out = os.path.join(HERE, 'reference_dimers.json.gz')
     with open(out, 'wb') as raw, gzip.GzipFile(fileobj=raw, mode='wb', mtime=0, filename='') as fh:
         fh.write(json.dumps(gold, separators=(',', ':'), default=lambda o: o.item()).encode())

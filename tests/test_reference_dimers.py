@@ -187,3 +187,57 @@ def test_gpu_find_hairpins_equals_oracle_on_random_sequences():
         assert hs.n_3prim_hairpins == n3
         total += len(hairpins)
     assert total > 40
+
+
+def _facade_from_oracle(cond, a, b):
+    """degenprimer_b200.SecStructures.SecStructures filled with the ORACLE's structures (no GPU): what the
+    kernels deliver, routed through the same DimerSet / HairpinSet hand-off."""
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200 import SecStructures as S
+    from degenprimer_b200.SeqUtils import SeqRecord, Seq
+    from oracle.structures import find_hairpins as o_find_hairpins
+    ocond.PCR_P.set(cond)
+    tdf.PCR_P.set(cond)
+    sa, sb = SEQS[a], SEQS[b]
+    dimers, fronts, n3, min3 = o_find_dimers(sa, sb)
+    ds = S.DimerSet(sa, sb)
+    for d in dimers:
+        x = S.Dimer(d.fwd_matches, d.offset)
+        x.dG = d.dG
+        ds.dimers.append(x)
+        if x.fwd_matches[-1] > len(sa) - 4 or x.rev_min < 3:
+            ds.n_3prim_dimers += 1
+            if ds.min_3prim_dimer_dG is None or ds.min_3prim_dimer_dG > x.dG:
+                ds.min_3prim_dimer_dG, ds.min_3prim_dimer = x.dG, x
+    assert ds.n_3prim_dimers == n3
+    hs = None
+    if a == b:
+        hs = S.HairpinSet(sa)
+        hairpins, hn3, _ = o_find_hairpins(fronts, sa)
+        for h in hairpins:
+            y = S.Hairpin(h.fwd_matches, h.rev_matches)
+            y.dG = h.dG
+            hs.hairpins.append(y)
+            if y.rev_matches[0] > len(sa) - 4:
+                hs.n_3prim_hairpins += 1
+                if hs.min_3prim_hairpin_dG is None or hs.min_3prim_hairpin_dG > y.dG:
+                    hs.min_3prim_hairpin_dG, hs.min_3prim_hairpin = y.dG, y
+        assert hs.n_3prim_hairpins == hn3
+    ra, rb = SeqRecord(Seq(sa), id='s%d' % a), SeqRecord(Seq(sb), id='s%d' % b)
+    return S.SecStructures(ra, None if a == b else rb, _dimer_set=ds, _hairpin_set=hs)
+
+
+def test_secstructures_report_text_equals_reference():
+    import hashlib
+    n_text = n = 0
+    for case in REF['cases']:
+        obj = _facade_from_oracle(REF['conds'][case['cond']], case['a'], case['b'])
+        full, short = str(obj), obj.formatShort()
+        if 'text' in case:
+            assert [full, short] == case['text']
+            n_text += 1
+        assert [hashlib.sha1(x.encode()).hexdigest() for x in (full, short)] == case['text_sha1'], \
+            (case['cond'], case['a'], case['b'])
+        assert obj.formatFull() == full
+        n += 1
+    assert n_text >= 5 and n == len(REF['cases'])
