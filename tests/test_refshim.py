@@ -117,3 +117,77 @@ def test_live_reference_reproduces_fixtures():
         except ProcessLookupError:
             pass
     assert b'LIVE-OK' in out, out.decode(errors='replace')[-2000:]
+
+
+_LIVE_MIXTURE = r'''
+import sys, warnings, random
+warnings.simplefilter('ignore')
+sys.path.insert(0, %(root)r)
+from oracle import refshim
+ns = refshim.load()
+import DegenPrimer.PCR_Mixture as ref_pm
+from multiprocessing import Event
+from degenprimer_b200.PCR_Mixture import MixtureFactory
+from degenprimer_b200.WorkCounter import WorkCounter
+
+class D(object):
+    def __init__(self, name, seq, ok3):
+        self.name, self.fwd_seq, self.fwd_len, self.have_3_matches = name, seq, len(seq), ok3
+    def __hash__(self): return hash((self.name, self.fwd_seq))
+    def __eq__(self, o): return hash(self) == hash(o)
+class P(object):
+    def __init__(self, seqs): self.seqs = set(seqs)
+    def __contains__(self, s): return str(s) in self.seqs
+
+def dump(mix):
+    if mix is None: return None
+    reg = lambda r: (r.name, r.start, r.end, bool(r.forward))
+    return (sorted((p.start, p.end, tuple(p.fwd_ids), tuple(p.rev_ids), reg(p.fwd_template), reg(p.rev_template))
+                   for p in mix.products.values()),
+            [reg(r) for r in mix.templates[1]], [reg(r) for r in mix.templates[0]],
+            [(reg(t), tuple(d.name for d in dups)) for dups, t in mix.annealings])
+
+rnd = random.Random(7)
+n_products = n_none = 0
+for trial in range(300):
+    variants = ['ACGT' * 5 + 'ACGT'[:rnd.randint(0, 3)] + str(v) for v in range(rnd.randint(1, 4))]
+    primers = [P(variants[:rnd.randint(1, len(variants))])]
+    def sites(n):
+        out = []
+        for _ in range(n):
+            pos = rnd.randint(30, 900)
+            dups = tuple(D('v%%d' %% rnd.randint(0, 5), rnd.choice(variants + ['FOREIGN' * 3]), rnd.random() < 0.7)
+                         for _ in range(rnd.randint(1, 3)))
+            out.append((pos, dups))
+        return out
+    fwd, rev = sites(rnd.randint(0, 12)), sites(rnd.randint(0, 12))
+    lo = rnd.choice([1, 10, 50, 200]); hi = lo + rnd.choice([0, 50, 300, 2000])
+    exo, side = rnd.random() < 0.3, rnd.random() < 0.5
+    a = ref_pm.MixtureFactory(Event(), primers, lo, hi, exo, side).create_PCR_mixture(
+        ns.WorkCounter.WorkCounter(), 'hit=/x', list(fwd), list(rev))
+    b = MixtureFactory(Event(), primers, lo, hi, exo, side).create_PCR_mixture(WorkCounter(), 'hit=/x', list(fwd), list(rev))
+    assert dump(a) == dump(b), trial
+    if a is None: n_none += 1
+    else: n_products += len(a.products)
+assert n_products > 300 and n_none > 20, (n_products, n_none)
+print('LIVE-OK', n_products, n_none)
+'''
+
+
+@pytest.mark.skipif(not refshim.available(), reason='reference sources only exist in the build container')
+def test_live_mixture_factory_equals_reference_on_random_systems():
+    """300 random site sets (overlapping sites, equal positions, foreign duplexes, 3' mismatches, narrow and
+    wide amplicon windows) through the reference's MixtureFactory and the mirror: same products, regions, annealings."""
+    proc = subprocess.Popen([sys.executable, '-c', _LIVE_MIXTURE % {'root': ROOT}], stdout=subprocess.PIPE,
+                            stderr=subprocess.STDOUT, start_new_session=True)
+    try:
+        out, _ = proc.communicate(timeout=180)
+    except subprocess.TimeoutExpired:
+        os.killpg(proc.pid, signal.SIGKILL)
+        raise
+    finally:
+        try:
+            os.killpg(proc.pid, signal.SIGKILL)
+        except ProcessLookupError:
+            pass
+    assert b'LIVE-OK' in out, out.decode(errors='replace')[-3000:]
