@@ -191,3 +191,134 @@ def test_live_mixture_factory_equals_reference_on_random_systems():
         except ProcessLookupError:
             pass
     assert b'LIVE-OK' in out, out.decode(errors='replace')[-3000:]
+
+
+_LIVE_RANDOM = r'''
+import sys, warnings, random
+warnings.simplefilter('ignore')
+sys.path.insert(0, %(root)r)
+import numpy as np
+from oracle import refshim
+ns = refshim.load()
+from multiprocessing import Event
+from oracle import conditions as ocond, search_o1 as o1, search_o2 as o2, thermo
+from oracle.primer import Primer as OPrimer, SeqRecord as OSeqRecord
+from oracle.structures import Dimer as ODimer, find_dimers, find_hairpins
+from oracle.sequtils import reverse_complement as o_rc
+tdf, SS = ns.tdf, ns.SecStructures
+eng = ns.SearchEngine.SearchEngine(Event()); WC = ns.WorkCounter.WorkCounter
+rnd = random.Random(2026)
+IUPAC = 'ACGTRYSWKMBDHVN'
+
+def rand_seq(n, alphabet='ACGT', weights=None):
+    return ''.join(rnd.choices(alphabet, weights=weights, k=n))
+
+def set_cond():
+    c = dict(Na=rnd.uniform(0.01, 0.2), Mg=rnd.uniform(0.5e-3, 5e-3), dNTP=rnd.uniform(0, 0.4e-3), DNA=10 ** rnd.uniform(-10, -8),
+             DMSO=rnd.choice([0.0, 0.0, 2.5]), PCR_T=rnd.uniform(30, 72))
+    tdf.PCR_P.set(c); ocond.PCR_P.set(c)
+
+# 1. scan: random IUPAC primers, templates with IUPAC noise, every k
+n_hits = 0
+for trial in range(60):
+    L = rnd.randint(4, 35)
+    master = rand_seq(L, IUPAC, [6] * 4 + [1] * 11)
+    if 4 ** sum(c not in 'ACGT' for c in master) > 4096: continue
+    t = list(rand_seq(rnd.randint(L, 3000), 'ACGTN' + IUPAC, [30] * 4 + [2] + [1] * 15))
+    for _ in range(rnd.randint(0, 6)):                      # plant near-matches on either strand
+        v = ''.join(rnd.choice({'R': 'AG', 'Y': 'CT', 'S': 'GC', 'W': 'AT', 'K': 'GT', 'M': 'AC', 'B': 'CGT', 'D': 'AGT',
+                                'H': 'ACT', 'V': 'ACG', 'N': 'ACGT'}.get(c, c)) for c in master)
+        if rnd.random() < 0.5: v = o_rc(v)
+        at = rnd.randint(0, max(0, len(t) - L))
+        t[at:at + L] = list(v)[:len(t) - at]
+    t = ''.join(t)
+    k = rnd.randint(0, min(6, L))
+    p = ns.Primer.Primer(ns.SeqRecord(ns.Seq(master), id='P'), 1e-6, True)
+    r = eng._find(WC(), ns.SeqRecord(ns.Seq(t), id='T'), p, len(t), L, k)
+    a, b = o1.find_serial(t, master, k), o2.find(t, master, k)
+    assert r[5].tolist() == a[4].tolist() == b[4].tolist() and r[6].tolist() == a[5].tolist() == b[5].tolist(), (master, k)
+    n_hits += len(r[5]) + len(r[6])
+    # 2. duplexes of the first hits under random conditions
+    set_cond()
+    op = OPrimer(OSeqRecord(master, id='P'), 1e-6)
+    sub = (r[0], r[1], r[2], r[3], r[4], r[5][:3], r[6][:3])
+    ref = eng.compile_duplexes(WC(), *sub)
+    mine = o1.compile_duplexes(a[0], a[1], op, a[2], a[3], a[4][:3], a[5][:3], mp_order=False)
+    assert (ref is None) == (mine is None), (master, k)
+    if ref is not None:
+        for x, y in zip(ref, mine):
+            assert (x is None) == (y is None)
+            for (p1, d1), (p2, d2) in zip(x or [], y or []):
+                assert p1 == p2 and [(d.name, [(m.fwd_matches, m.dG, m.K) for m in d.dimers], str(d)) for d in d1] == \
+                    [(d.name, [(m.fwd_matches, m.dG, m.K) for m in d.dimers], str(d)) for d in d2]
+assert n_hits > 100, n_hits
+
+# 3. dimers with offsets / dangling ends, self- and cross-dimers, hairpins: random unequal lengths
+n_d = n_h = 0
+for trial in range(150):
+    set_cond()
+    gc = rnd.random()
+    w = [(1 - gc) / 2, gc / 2, gc / 2, (1 - gc) / 2]
+    a = rand_seq(rnd.randint(1, 64), 'ACGT', w)
+    b = a if trial %% 3 == 0 else rand_seq(rnd.randint(1, 64), 'ACGT', w)
+    if trial %% 5 == 0 and len(a) > 12:
+        a = a[:len(a) // 2] + 'TTTT' + o_rc(a[:len(a) // 2])           # a stem-loop
+        b = a if trial %% 3 == 0 else b
+    ra, rb = ns.SeqRecord(ns.Seq(a), id='a'), ns.SeqRecord(ns.Seq(b), id='b')
+    s = SS.SecStructures(ra) if a == b else SS.SecStructures(ra, rb)
+    want = s._seq1_dimers if a == b else s._cross_dimers
+    dimers, fronts, n3, min3 = find_dimers(a, b)
+    assert [(d.fwd_matches, d.offset, d.dG) for d in want.values()] == [(d.fwd_matches, d.offset, d.dG) for d in dimers], (a, b)
+    assert s._3prim_dimers == n3 and s._min_3prim_dimer_dG == min3
+    n_d += len(dimers)
+    if a == b:
+        hp, hn3, _ = find_hairpins(fronts, a)
+        assert [(h.fwd_matches, h.rev_matches, h.dG) for h in s._seq1_hairpins.values()] == \
+            [(h.fwd_matches, h.rev_matches, h.dG) for h in hp], a
+        assert s._3prim_hairpins == hn3
+        n_h += len(hp)
+    off = rnd.randint(-len(b) + 1, len(a) - 1)
+    try:
+        dm = SS.Dimer.from_sequences(a, SS.reverse_complement(b), off)
+    except IndexError:       # the reference's own range runs past `forward` for some negative offsets of unequal strands
+        continue
+    om = ODimer.from_sequences(a, o_rc(b), off)
+    assert dm.fwd_matches == om.fwd_matches
+    if dm:
+        assert tdf.dimer_dG_corrected(dm, a, b) == thermo.dimer_dG_corrected(om, a, b)
+assert n_d > 150 and n_h > 20, (n_d, n_h)
+
+# 4. per-variant Tm
+for trial in range(20):
+    set_cond()
+    master = rand_seq(rnd.randint(8, 30), 'ACGTRYKMSWN', [8] * 4 + [1] * 7)
+    if 4 ** sum(c not in 'ACGT' for c in master) > 1024: continue
+    conc = 10 ** rnd.uniform(-7, -5)
+    p = ns.Primer.Primer(ns.SeqRecord(ns.Seq(master), id='P'), conc, True)
+    op = OPrimer(OSeqRecord(master, id='P'), conc)
+    if not p.calculate_Tms():
+        continue
+    assert op.calculate_Tms() and (p.Tm_min, p.Tm_max, p.Tm_mean) == (op.Tm_min, op.Tm_max, op.Tm_mean)
+    assert [str(x) for x in p.sequences] == op.str_sequences
+print('LIVE-OK', n_hits, n_d, n_h)
+'''
+
+
+@pytest.mark.skipif(not refshim.available(), reason='reference sources only exist in the build container')
+def test_live_oracle_equals_reference_on_random_inputs():
+    """Beyond the committed fixtures: the oracle against the reference run live on seeded random inputs — scan
+    (random IUPAC primers, noisy templates, k = 0..6), duplexes under random conditions, self-/cross-dimers with
+    unequal lengths 1..64 (every dangling-end branch), hairpins, per-variant Tm.  Everything compared with `==`."""
+    proc = subprocess.Popen([sys.executable, '-c', _LIVE_RANDOM % {'root': ROOT}], stdout=subprocess.PIPE,
+                            stderr=subprocess.STDOUT, start_new_session=True)
+    try:
+        out, _ = proc.communicate(timeout=400)
+    except subprocess.TimeoutExpired:
+        os.killpg(proc.pid, signal.SIGKILL)
+        raise
+    finally:
+        try:
+            os.killpg(proc.pid, signal.SIGKILL)
+        except ProcessLookupError:
+            pass
+    assert b'LIVE-OK' in out, out.decode(errors='replace')[-3000:]
