@@ -420,6 +420,13 @@ def find_dimers_batch(seqs, pairs, return_ms=False):
     strs = [str(s).upper() for s in seqs]
     pairs = np.asarray(list(pairs), dtype=np.uint32).reshape(-1, 2)
     rec, ms = tdf._ctx().find_dimers(strs, pairs, tdf.conditions())
+    out = _dimer_sets_from_records(strs, pairs, rec)
+    return (out, ms) if return_ms else out
+
+
+def _dimer_sets_from_records(strs, pairs, rec):
+    """Host half of `find_dimers_batch`: the dense [pair][front] records of dp_find_dimers -> DimerSet objects
+    (de-duplication by the reference's structure key, hairpin seeds of self pairs, 3'-dimer bookkeeping)."""
     if np.isnan(rec['best_dG']).any():
         raise ValueError('UnifiedNN.int_dPar_37: sequence is not in the database')
     la = np.array([len(s) for s in strs], dtype=np.int64)
@@ -457,7 +464,7 @@ def find_dimers_batch(seqs, pairs, return_ms=False):
             if ds.min_3prim_dimer_dG is None or ds.min_3prim_dimer_dG > d.dG:
                 ds.min_3prim_dimer_dG = d.dG
                 ds.min_3prim_dimer = d
-    return (out, ms) if return_ms else out
+    return out
 
 
 def find_dimers(seq1, seq2=None):
@@ -478,10 +485,9 @@ def trim_hairpin_seed(fwd_matches):
     return m[:k - t], m[t:]
 
 
-def find_hairpins_batch(dimer_sets, return_ms=False):
-    """SecStructures._find_hairpins for the self-dimer seeds (`DimerSet.fronts`) of many sequences in
-    ONE kernel launch (dp_find_hairpins: one warp per seed).  Returns a list of HairpinSet."""
-    seqs = [ds.seq1 for ds in dimer_sets]
+def _hairpin_seeds(dimer_sets):
+    """(seed_seq, seed_mask, seed_offset) for dp_find_hairpins: every hairpin seed of every self-dimer set,
+    trimmed (SecStructures.py:684-690,695)."""
     seed_seq, seed_mask, seed_off = [], [], []
     for si, ds in enumerate(dimer_sets):
         L = len(ds.seq1)
@@ -494,35 +500,52 @@ def find_hairpins_batch(dimer_sets, return_ms=False):
                 m |= 1 << f
             seed_seq.append(si)
             seed_mask.append(m)
-            seed_off.append(fwd[0] - (L - 1 - rev[-1]))                       # SecStructures.py:695
+            seed_off.append(fwd[0] - (L - 1 - rev[-1]))
+    return seed_seq, seed_mask, seed_off
+
+
+def _hairpin_sets_from_records(seqs, seed_seq, seed_off, rec):
+    """Host half of `find_hairpins_batch`: the per-seed records of dp_find_hairpins -> HairpinSet objects
+    (de-duplication by structure key, 3'-hairpin bookkeeping, SecStructures.py:700-714)."""
     out = [HairpinSet(s) for s in seqs]
-    ms = 0.0
+    if not len(seed_seq):
+        return out
+    if np.isnan(rec['best_dG']).any():
+        raise ValueError('UnifiedNN.int_dPar_37: sequence is not in the database')
+    seen, last = None, -1
+    for si, off, bm, dG in zip(seed_seq, seed_off, rec['best_mask'].tolist(), rec['best_dG'].tolist()):
+        if si != last:
+            seen, last = set(), si
+        if not bm:
+            continue
+        hs = out[si]
+        L = len(hs.seq)
+        fm = mask_to_matches(bm)
+        h = Hairpin(fm, [L - 1 - (f - off) for f in fm])
+        h.dG = dG
+        key = h.fwd_matches + h.rev_matches                               # _structure_hash: concatenation
+        if key in seen:
+            continue
+        seen.add(key)
+        hs.hairpins.append(h)
+        if h.rev_matches[0] > L - 4:
+            hs.n_3prim_hairpins += 1
+            if hs.min_3prim_hairpin_dG is None or hs.min_3prim_hairpin_dG > dG:
+                hs.min_3prim_hairpin_dG = dG
+                hs.min_3prim_hairpin = h
+    return out
+
+
+def find_hairpins_batch(dimer_sets, return_ms=False):
+    """SecStructures._find_hairpins for the self-dimer seeds (`DimerSet.fronts`) of many sequences in
+    ONE kernel launch (dp_find_hairpins: one warp per seed).  Returns a list of HairpinSet."""
+    seqs = [ds.seq1 for ds in dimer_sets]
+    seed_seq, seed_mask, seed_off = _hairpin_seeds(dimer_sets)
+    rec, ms = None, 0.0
     if seed_seq:
         rec, ms = tdf._ctx_with_hairpin_tables().find_hairpins(seqs, seed_seq, seed_mask, seed_off, tdf.conditions(),
                                                                max_hairpin_dG)
-        if np.isnan(rec['best_dG']).any():
-            raise ValueError('UnifiedNN.int_dPar_37: sequence is not in the database')
-        seen, last = None, -1
-        for si, off, bm, dG in zip(seed_seq, seed_off, rec['best_mask'].tolist(), rec['best_dG'].tolist()):
-            if si != last:
-                seen, last = set(), si
-            if not bm:
-                continue
-            hs = out[si]
-            L = len(hs.seq)
-            fm = mask_to_matches(bm)
-            h = Hairpin(fm, [L - 1 - (f - off) for f in fm])
-            h.dG = dG
-            key = h.fwd_matches + h.rev_matches                               # _structure_hash: concatenation
-            if key in seen:
-                continue
-            seen.add(key)
-            hs.hairpins.append(h)
-            if h.rev_matches[0] > L - 4:                                      # SecStructures.py:707-713
-                hs.n_3prim_hairpins += 1
-                if hs.min_3prim_hairpin_dG is None or hs.min_3prim_hairpin_dG > dG:
-                    hs.min_3prim_hairpin_dG = dG
-                    hs.min_3prim_hairpin = h
+    out = _hairpin_sets_from_records(seqs, seed_seq, seed_off, rec)
     return (out, ms) if return_ms else out
 
 

@@ -241,3 +241,74 @@ def test_secstructures_report_text_equals_reference():
         assert obj.formatFull() == full
         n += 1
     assert n_text >= 5 and n == len(REF['cases'])
+
+
+def _kernel_model_dimers(strs, pairs):
+    """What dp_find_dimers writes ([pair][front] = full mask, best mask, best dG), computed with the oracle's
+    pieces: the contract of include/degenprimer_b200.h restated on the CPU for the host-side tests."""
+    from degenprimer_b200 import _native as nat
+    from oracle import thermo
+    from oracle.sequtils import reverse_complement
+    from oracle.structures import Dimer
+    stride = max(len(strs[i]) + len(strs[j]) - 1 for i, j in pairs)
+    rec = np.zeros((len(pairs), stride), dtype=nat.FRONT_DIMER_DTYPE)
+    for p, (i, j) in enumerate(pairs):
+        a, b = strs[i], strs[j]
+        rc = reverse_complement(b)
+        la, lb = len(a), len(b)
+        for front in range(la + lb - 1):
+            off = max(0, la - front - 1) - max(0, front - la + 1)
+            m = [f for f in range(la) if 0 <= f - off < lb and a[f] == rc[f - off]]
+            if not m:
+                continue
+            d = Dimer(m, off)
+            rec[p, front]['full_mask'] = mask_of(m)
+            best, best_dG = None, -3
+            for x in [d] + d.alternatives:
+                g = thermo.dimer_dG_corrected(x, a, b)
+                if best_dG > g:
+                    best, best_dG = x, g
+            if best is not None:
+                rec[p, front]['best_mask'] = mask_of(best.fwd_matches)
+                rec[p, front]['best_dG'] = best_dG
+    return rec
+
+
+def _kernel_model_hairpins(seqs, seed_seq, seed_mask, seed_off):
+    from degenprimer_b200 import _native as nat
+    from oracle import thermo
+    from oracle.structures import Dimer, Hairpin
+    rec = np.zeros(len(seed_seq), dtype=nat.BEST_STRUCTURE_DTYPE)
+    for k, (si, mask, off) in enumerate(zip(seed_seq, seed_mask, seed_off)):
+        s = seqs[si]
+        d = Dimer([i for i in range(64) if mask >> i & 1], off)
+        best, best_dG = None, 3
+        for x in [d] + d.alternatives:
+            h = Hairpin(x.fwd_matches, [len(s) - 1 - (f - off) for f in x.fwd_matches])
+            g = thermo.hairpin_dG_corrected(h, s)
+            if best_dG > g:
+                best, best_dG = x, g
+        if best is not None:
+            rec[k] = (mask_of(best.fwd_matches), best_dG)
+    return rec
+
+
+@pytest.mark.parametrize('cname', sorted(REF['conds']))
+def test_host_halves_of_the_batch_calls_equal_reference(cname):
+    """`_dimer_sets_from_records`, `_hairpin_seeds`, `_hairpin_sets_from_records` (everything find_dimers_batch /
+    find_hairpins_batch do around the two kernel launches) fed with a CPU model of the kernels' output."""
+    from degenprimer_b200 import SecStructures as S
+    ocond.PCR_P.set(REF['conds'][cname])
+    cases = [c for c in REF['cases'] if c['cond'] == cname]
+    pairs = np.array([(c['a'], c['b']) for c in cases], dtype=np.uint32)
+    sets = S._dimer_sets_from_records(SEQS, pairs, _kernel_model_dimers(SEQS, pairs))
+    assert _check_gpu(cases, sets) == sum(len(c['dimers']) for c in cases)
+    selfs = [(c, ds) for c, ds in zip(cases, sets) if 'hairpins' in c]
+    seqs = [ds.seq1 for _, ds in selfs]
+    seed_seq, seed_mask, seed_off = S._hairpin_seeds([ds for _, ds in selfs])
+    hsets = S._hairpin_sets_from_records(seqs, seed_seq, seed_off,
+                                         _kernel_model_hairpins(seqs, seed_seq, seed_mask, seed_off))
+    for (c, _), hs in zip(selfs, hsets):
+        assert [[list(h.fwd_matches), list(h.rev_matches), h.dG] for h in hs.hairpins] == c['hairpins']
+        assert hs.n_3prim_hairpins == c['n_3prim_hairpins']
+    assert S._hairpin_sets_from_records(['ACGT'], [], [], None)[0].hairpins == []
