@@ -17,16 +17,35 @@ max_hairpin_dG = 3                   # SecStructures.py:31
 min_K = tdf.min_K                    # 100, SecStructures.py:32
 
 
+# bit positions of every byte value at every byte offset of a 64-bit mask, and every byte value with a
+# zero bit interleaved between its bits (bit b -> bit 2b): table-driven forms of the two inner loops below
+_BYTE_BITS = [[tuple(8 * k + b for b in range(8) if v >> b & 1) for v in range(256)] for k in range(8)]
+_BYTE_SPREAD = [sum(1 << (2 * b) for b in range(8) if v >> b & 1) for v in range(256)]
+
+
 def mask_to_matches(mask):
+    """Sorted tuple of the set bit positions of a match mask (<= 64 bits)."""
     mask = int(mask)
-    out = []
-    i = 0
+    out = ()
+    k = 0
     while mask:
-        if mask & 1:
-            out.append(i)
-        mask >>= 1
-        i += 1
-    return tuple(out)
+        out += _BYTE_BITS[k][mask & 255]
+        mask >>= 8
+        k += 1
+    return out
+
+
+def _structure_key_of_mask(mask, offset):
+    """`structure_key` as ONE integer: bit (2f - offset + 64) set for every match f.  Equal integers <=> equal
+    key tuples (both list the same increasing values), so it de-duplicates exactly like the tuple does."""
+    mask = int(mask)
+    spread = 0
+    shift = 0
+    while mask:
+        spread |= _BYTE_SPREAD[mask & 255] << shift
+        mask >>= 8
+        shift += 16
+    return spread << (64 - offset)
 
 
 class Dimer(object):
@@ -430,34 +449,35 @@ def _dimer_sets_from_records(strs, pairs, rec):
     if np.isnan(rec['best_dG']).any():
         raise ValueError('UnifiedNN.int_dPar_37: sequence is not in the database')
     la = np.array([len(s) for s in strs], dtype=np.int64)
-    out = [DimerSet(strs[i], strs[j]) for i, j in pairs]
-    is_self = np.array([strs[i] == strs[j] for i, j in pairs], dtype=bool) if len(pairs) else np.zeros(0, bool)
+    plist = pairs.tolist()                                   # plain ints: numpy scalars are slow list indices
+    out = [DimerSet(strs[i], strs[j]) for i, j in plist]
+    is_self = np.array([strs[i] == strs[j] for i, j in plist], dtype=bool) if plist else np.zeros(0, bool)
     # only the entries that lead to an object are visited: stable structures, and the seeds of self pairs
     want = (rec['best_mask'] != 0) | ((rec['full_mask'] != 0) & is_self[:, None])
     pp, ff = np.nonzero(want)                                # row-major: pair by pair, fronts ascending
     fwd_len = la[pairs[pp, 0]] if len(pp) else np.zeros(0, np.int64)
     offsets = np.maximum(0, fwd_len - ff - 1) - np.maximum(0, ff - fwd_len + 1)
     full, best, dGs = rec['full_mask'][pp, ff], rec['best_mask'][pp, ff], rec['best_dG'][pp, ff]
+    self_list = is_self.tolist()
     seen, seen_fronts, last = None, None, -1
     for p, offset, fm, bm, dG, flen in zip(pp.tolist(), offsets.tolist(), full.tolist(), best.tolist(),
                                            dGs.tolist(), fwd_len.tolist()):
         if p != last:
             seen, seen_fronts, last = set(), set(), p
         ds = out[p]
-        if is_self[p]:
-            seed = Dimer(mask_to_matches(fm), offset)
-            key = structure_key(seed)
+        if self_list[p]:
+            key = _structure_key_of_mask(fm, offset)
             if key not in seen_fronts:                                        # SecStructures.py:643-645
                 seen_fronts.add(key)
-                ds.fronts.append(seed)
+                ds.fronts.append(Dimer(mask_to_matches(fm), offset))
         if not bm:
             continue
-        d = Dimer(mask_to_matches(bm), offset)
-        d.dG = dG
-        key = structure_key(d)
+        key = _structure_key_of_mask(bm, offset)
         if key in seen:
             continue
         seen.add(key)
+        d = Dimer(mask_to_matches(bm), offset)
+        d.dG = dG
         ds.dimers.append(d)
         if d.fwd_matches[-1] > flen - 4 or d.rev_min < 3:                     # SecStructures.py:660-667
             ds.n_3prim_dimers += 1
