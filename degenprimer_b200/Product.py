@@ -11,12 +11,28 @@ from math import log
 TEXT_WIDTH = 80      # BioUtils/Tools/Text.py:16
 
 
+def wrap_text(text, width=TEXT_WIDTH):
+    """Greedy word wrap of BioUtils/Tools/Text.py:33-55: runs of blanks collapse, a line holds at most
+    width-1 characters, a word longer than `width` is cut into hyphenated pieces; ends with a newline."""
+    limit = width - 1
+    lines, cur = [], ''
+    for word in text.split():
+        if cur and len(cur) + len(word) > limit:
+            lines.append(cur)
+            cur = ''
+        while not cur and len(word) > width:
+            lines.append(word[:limit] + '-')
+            word = word[limit:]
+        cur = cur + ' ' + word if cur else word
+    lines.append(cur)
+    return '\n'.join(lines) + '\n'
+
+
 def hr(text='', symbol='-', width=TEXT_WIDTH):
     """Centered horizontal rule (BioUtils/Tools/Text.py:22-26): an empty caption gives just the blank
-    lines; captions longer than the line are wrapped first."""
+    lines; captions longer than the line are wrapped to 3/4 of it first."""
     if len(text) > TEXT_WIDTH - 4:
-        import textwrap
-        lines = textwrap.wrap(' '.join(text.split()), TEXT_WIDTH * 3 // 4)
+        lines = wrap_text(text, TEXT_WIDTH * 3 // 4).split('\n')
     else:
         lines = [text]
     return '\n'.join((' %s ' % l).center(width, symbol) for l in lines if l) + '\n\n'

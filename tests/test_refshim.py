@@ -170,6 +170,17 @@ for trial in range(300):
     if a is None: n_none += 1
     else: n_products += len(a.products)
 assert n_products > 300 and n_none > 20, (n_products, n_none)
+# the caption helpers the reports are built with (BioUtils/Tools/Text.py:22-55)
+import BioUtils.Tools.Text as ref_text
+from degenprimer_b200 import Product as mine
+for trial in range(1000):
+    words = [''.join(rnd.choices('abcXYZ-:', k=rnd.choice([1, 3, 8, 20, 59, 60, 61, 79, 80, 81, 130])))
+             for _ in range(rnd.randint(0, 12))]
+    text = (' ' * rnd.randint(0, 2)).join(w + ' ' * rnd.randint(1, 3) for w in words)
+    for width in (None, 60, 10):
+        assert ref_text.wrap_text(text, width) == mine.wrap_text(text, width or 80), (text, width)
+    for symbol in '-=':
+        assert ref_text.hr(text, symbol=symbol) == mine.hr(text, symbol=symbol), text
 print('LIVE-OK', n_products, n_none)
 '''
 
