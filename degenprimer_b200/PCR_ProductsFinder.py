@@ -74,21 +74,21 @@ class PCR_ProductsFinder(MixtureFactory):
         return mixture.save()          # like the reference, this raises when no product was found
 
     def find(self, counter, template, mismatches):
-        """{template name: path of the saved mixture}, or None (:94-112)."""
-        all_annealings = []
-        counter.set_subwork(self._num_p + 1, self._p_weights + [0.01 * self._pw_sum])
-        for i, primer in enumerate(self._primers):
-            if self.aborted():
-                return None
-            annealings = self._searcher.find(counter[i], template, primer, mismatches)
-            if annealings is None:
-                continue
-            all_annealings.append(annealings)
+        """{template name: path of the saved mixture}, or None (:94-112).  The reference runs
+        `SearchEngine.find` once per primer (one template pass and one temp file each); here all
+        primers of the system are ONE device pass (SearchEngine.find_all) and the annealings stay in
+        memory."""
+        counter.set_subwork(2, [self._pw_sum, 0.01 * self._pw_sum])
+        if self.aborted():
+            return None
+        found = self._searcher.find_all(counter[0], [template], self._primers, mismatches)
+        if found is None:
+            return None
+        all_annealings = [pair for pair in found[template.id] if pair is not None]
         if not all_annealings:
             return None
         tname = pretty_rec_name(template)
-        mixture = self.create_PCR_mixture(counter[-1], tname, *self._extract_annealings(*all_annealings))
-        cleanup_files(all_annealings)
+        mixture = self.create_PCR_mixture(counter[-1], tname, *self._combine_annealings(*all_annealings))
         counter.done()
         if not mixture:
             return None

@@ -21,7 +21,7 @@ import numpy as np
 
 from . import TD_Functions as tdf
 from . import _native as nat
-from .SecStructures import DuplexTable, SiteDuplexes
+from .SecStructures import DuplexTable, LazyWindows, SiteDuplexes, SiteList
 from .SeqView import ResidentRecord, StrandView
 from .WorkCounter import WorkCounter
 from .tmpStorage import to_shelf
@@ -87,8 +87,12 @@ class SearchEngine(object):
 
     _max_chunk_size = 2 ** 12     # the reference's FFT chunk; meaningless here, kept for set_max_chunk
 
-    def __init__(self, abort_event=None):
+    def __init__(self, abort_event=None, jit=None):
+        """jit: compile the scan kernel for every primer set this engine meets (NVRTC, ~0.3 s once
+        per set and process; pays for Gbp templates and repeated searches).  None: the
+        DEGENPRIMER_B200_JIT environment variable decides (default off)."""
         self._abort_event = abort_event if abort_event is not None else DummyEvent()
+        self._jit = jit
         self.last_stats = {}
 
     # ---- plumbing the reference exposes ----------------------------------------------
@@ -283,6 +287,97 @@ class SearchEngine(object):
         duplexes = self.find_duplexes(counter, template, primer, mismatches)
         return to_shelf(duplexes) if duplexes else None
 
+    # ---- all primers x all records of a resident template in ONE device pass --------------------
+    def find_all(self, counter, templates, primers, mismatches):
+        """`find` for every (template, primer) pair at once: the templates must be records of one
+        resident template (a loaded SeqView, ResidentRecords); the scan of all primers over all of
+        them and the duplex stage of every site are ONE dp_find submission instead of the
+        per-primer, per-template loop of DegenPrimer/PCR_ProductsFinder.py:94-111,114-141.
+        Returns {template.id: [(fwd_results, rev_results) or None, one per primer]} with the lists
+        of `find_duplexes` (sorted by position), or None when aborted."""
+        templates = list(templates)
+        primers = list(primers)
+        if not templates or not primers:
+            return {}
+        native = [resident(t) for t in templates]
+        tmpl = native[0][0]
+        if any(n[0] is not tmpl for n in native):
+            raise ValueError('find_all: the templates must be records of one resident template')
+        recs = [n[1] for n in native]
+        for t in templates:
+            for p in primers:
+                self._check_length_inequality(len(t), len(p))
+        counter.set_work(len(templates) * len(primers))
+        if self.aborted():
+            return None
+        query, var_lists, name_lists = _primers_query(tmpl.ctx, primers, int(mismatches), self._jit)
+        begin = min(tmpl.starts[r] for r in recs)
+        end = max(tmpl.starts[r] + ((tmpl.lengths[r] + 31) // 32) * 32 for r in recs)
+        if len(set(recs)) == tmpl.n_records:
+            begin, end = 0, 2 ** 64 - 1
+        with tdf.AcquireParameters():       # the snapshot is the by-value conditions block
+            cond = tdf.conditions()
+            T = tdf.PCR_P.PCR_T
+        try:
+            hits, dimers, st, dst = tmpl.ctx.find(tmpl, query, cond=cond, seg_begin=begin, seg_end=end)
+        except nat.Aborted:
+            return None
+        self.last_stats['scan'] = st
+        self.last_stats['dg'] = dst
+        if self.aborted():
+            return None
+        out = self._split_results(tmpl, templates, recs, primers, hits, dimers, var_lists, name_lists, T)
+        counter.done()
+        return out
+
+    @staticmethod
+    def _split_results(tmpl, templates, recs, primers, hits, dimers, var_lists, name_lists, T):
+        """hits sorted by (primer, strand, record, pos), dimers grouped by hit -> per (template,
+        primer) a pair of SiteLists; no per-site Python work."""
+        n_p = len(primers)
+        p_lens = np.array([len(p) for p in primers], dtype=np.int64)
+        windows = LazyWindows(tmpl, hits, p_lens)
+        tables = [DuplexTable(dimers, windows, var_lists[i], name_lists[i], T) for i in range(n_p)]
+        out = {t.id: [None] * n_p for t in templates}
+        if not len(hits):
+            return out
+        bounds = np.searchsorted(dimers['hit'], np.arange(len(hits) + 1))
+        keep = np.flatnonzero(bounds[1:] > bounds[:-1])            # sites with a stable duplex
+        if not len(keep):
+            return out
+        kh = hits[keep]
+        L = p_lens[kh['primer']]
+        pos = kh['pos'].astype(np.int64)
+        t_len = np.asarray(tmpl.lengths, dtype=np.int64)[kh['record']]
+        site = np.where(kh['strand'] == 0, pos + L, t_len + 1 - (pos + L))
+        lo, hi = bounds[keep], bounds[keep + 1]
+        n_r = tmpl.n_records
+        key = (kh['primer'].astype(np.int64) * 2 + kh['strand']) * n_r + kh['record']
+        cut = np.flatnonzero(np.diff(key)) + 1
+        starts = np.concatenate(([0], cut))
+        ends = np.concatenate((cut, [len(key)]))
+        by_rec = {}
+        for t, r in zip(templates, recs):
+            by_rec.setdefault(r, []).append(t.id)
+        for a, b in zip(starts, ends):
+            k0 = int(key[a])
+            r = k0 % n_r
+            ids = by_rec.get(r)
+            if not ids:
+                continue
+            p_i, strand = (k0 // n_r) // 2, (k0 // n_r) % 2
+            sl = slice(a, b) if strand == 0 else slice(b - 1, a - 1 if a else None, -1)   # ascending position
+            lst = SiteList(tables[p_i], keep[sl], site[sl], lo[sl], hi[sl])
+            for tid in ids:
+                pair = out[tid][p_i]
+                if pair is None:
+                    pair = out[tid][p_i] = [SiteList(tables[p_i], keep[:0], site[:0], lo[:0], hi[:0]),
+                                            SiteList(tables[p_i], keep[:0], site[:0], lo[:0], hi[:0])]
+                pair[strand] = lst
+        for tid, pairs in out.items():
+            out[tid] = [tuple(p) if p is not None else None for p in pairs]
+        return out
+
     def _batch_find(self, template, primer, p_len, mismatches):
         """DegenPrimer/SearchEngine.py:388-394 (serial orderings)."""
         self._check_length_inequality(len(template), p_len)
@@ -324,6 +419,24 @@ def _primer_query(primer, mismatches):
     try:
         primer._dp_query_cache = (key, value)
     except AttributeError:          # a foreign Primer class with __slots__
+        pass
+    return value
+
+
+def _primers_query(ctx, primers, mismatches, jit=None):
+    """(native Query over all primers, variant strings per primer, variant names per primer),
+    cached on the first primer object by the masters of the set."""
+    masters = [str(p.master_sequence.seq) for p in primers]
+    key = (tuple(masters), mismatches, tuple(p.num_components for p in primers), bool(jit))
+    cache = getattr(primers[0], '_dp_set_cache', None)
+    if cache is not None and cache[0] == key:
+        return cache[1]
+    var_lists = [[str(r.seq) for r in p.seq_records] for p in primers]
+    name_lists = [[r.id for r in p.seq_records] for p in primers]
+    value = (ctx.prepare(masters, mismatches, var_lists, jit=jit), var_lists, name_lists)
+    try:
+        primers[0]._dp_set_cache = (key, value)
+    except AttributeError:
         pass
     return value
 

@@ -345,6 +345,103 @@ class SiteDuplexes(object):
         return (tuple, (list(self._materialise()),))
 
 
+class LazyWindows(object):
+    """hit index -> window string (strand orientation), fetched from HBM in ONE dp_hit_windows
+    call on first use and kept for every table that shares the hits."""
+
+    def __init__(self, tmpl, hits, primer_lens):
+        self._tmpl, self._hits, self._lens = tmpl, hits, list(primer_lens)
+        self._w = None
+
+    def _fetch(self):
+        if self._w is None:
+            self._w = self._tmpl.ctx.hit_windows(self._tmpl, self._hits, self._lens)
+            self._tmpl = None
+        return self._w
+
+    def __getitem__(self, h):
+        return self._fetch()[h]
+
+    def __len__(self):
+        return len(self._hits)
+
+
+def _rebuild_site_list(positions, counts, rows, windows, variants, names, T):
+    table = DuplexTable(rows, windows, variants, names, T)
+    hi = np.cumsum(counts)
+    return SiteList(table, np.arange(len(positions)), positions, hi - counts, hi)
+
+
+class SiteList(object):
+    """List-like `[(position, duplexes), ...]` of one primer on one strand of one template — the
+    fwd_results / rev_results of DegenPrimer/SearchEngine.py:120-157 — kept as arrays: the
+    (position, SiteDuplexes) pairs are made when the list is iterated or indexed, Duplex objects only
+    when a SiteDuplexes is looked into.  Pickles as arrays (what `find` puts on the shelf)."""
+    __slots__ = ['_table', '_hits', '_pos', '_lo', '_hi']
+
+    def __init__(self, table, hits, positions, lo, hi):
+        self._table = table
+        self._hits = np.asarray(hits)
+        self._pos = np.asarray(positions)
+        self._lo, self._hi = np.asarray(lo), np.asarray(hi)
+
+    def __len__(self):
+        return len(self._pos)
+
+    def __bool__(self):
+        return len(self._pos) > 0
+
+    def _item(self, i):
+        return (int(self._pos[i]), SiteDuplexes(self._table, int(self._hits[i]), int(self._lo[i]), int(self._hi[i])))
+
+    def __iter__(self):
+        for i in range(len(self._pos)):
+            yield self._item(i)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return SiteList(self._table, self._hits[i], self._pos[i], self._lo[i], self._hi[i])
+        if i < 0:
+            i += len(self._pos)
+        if not 0 <= i < len(self._pos):
+            raise IndexError('SiteList index out of range')
+        return self._item(i)
+
+    @property
+    def positions(self):
+        return self._pos
+
+    def sort(self, key=None, reverse=False):
+        """Order by position (the only order the callers ask for, SearchEngine.py:153-154)."""
+        order = np.argsort(self._pos, kind='stable')
+        if reverse:
+            order = order[::-1]
+        self._hits, self._pos = self._hits[order], self._pos[order]
+        self._lo, self._hi = self._lo[order], self._hi[order]
+
+    def __eq__(self, other):
+        return list(self) == list(other)
+
+    def __ne__(self, other):
+        return not self == other
+
+    __hash__ = None
+
+    def __add__(self, other):
+        return list(self) + list(other)
+
+    def __repr__(self):
+        return 'SiteList(%d sites)' % len(self)
+
+    def __reduce__(self):
+        t = self._table
+        counts = (self._hi - self._lo).astype(np.int64)
+        rows = (np.concatenate([t.dimers[a:b] for a, b in zip(self._lo, self._hi)])
+                if len(counts) else t.dimers[:0].copy())
+        windows = [t.windows[int(h)] for h in self._hits]
+        return (_rebuild_site_list, (np.array(self._pos), counts, rows, windows, t.variants, t.names, t.T))
+
+
 # ---------------------------------------------------------------------------------------------
 # SURVEY §8(f) N3: self-dimers, cross-dimers and hairpins of primer variants
 # (DegenPrimer/SecStructures.py:389-716).  Two kernels: dp_find_dimers (one warp per sequence pair and

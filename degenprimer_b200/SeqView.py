@@ -166,6 +166,19 @@ class ResidentRecord(object):
         return 'ResidentRecord(id=%r, len=%d)' % (self.id, len(self))
 
 
+def source_identity(path):
+    """What a packed cache remembers about the file it was made from."""
+    st = os.stat(path)
+    return '%s|%d|%d' % (os.path.abspath(path), st.st_size, st.st_mtime_ns)
+
+
+def _cache_origin(cache):
+    try:
+        return nat.packed_info(cache)['origin']
+    except (ValueError, OSError):
+        return None
+
+
 class SeqView(object):
     def __init__(self, upper=False):
         self.upper = upper           # kept for signature parity: input is always case-folded
@@ -220,10 +233,13 @@ class SeqView(object):
         ctx = nat.context(device)
         for i, f in enumerate(valid):
             # `dbname` is the reference's on-disk index (SeqIO.index_db, BioUtils/SeqUtils.py:160-172);
-            # here it names the packed-template cache: used when it is newer than the
-            # FASTA file, (re)written otherwise.
+            # here it names the packed-template cache.  The cache records what it was
+            # packed from (absolute path, size, mtime in ns -- inside the file, under its checksum) and
+            # is used only when that still describes the source file; SeqIO.index_db likewise refuses an
+            # index whose file list differs (BioUtils/SeqUtils.py:169).  Anything else is rebuilt.
             cache = None if not dbname else (dbname if len(valid) == 1 else '%s.%d' % (dbname, i))
-            if cache and os.path.isfile(cache) and os.path.getmtime(cache) >= os.path.getmtime(f):
+            origin = source_identity(f)
+            if cache and os.path.isfile(cache) and _cache_origin(cache) == origin:
                 t = ctx.template_load(cache)
             else:
                 if schema == 'fasta':
@@ -238,6 +254,7 @@ class SeqView(object):
                     t = ctx.template_from_sequences([r[2] for r in recs])
                     t.set_record_names([r[0] for r in recs], [r[1] for r in recs])
                 if cache:
+                    t.origin = origin
                     t.save(cache)
             self._templates.append(t)
             for r, rid in enumerate(t.ids):

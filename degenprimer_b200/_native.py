@@ -127,6 +127,11 @@ def _declare(lib):
         'dp_template_set_record_name': (i32, [vp, u32, cp, cp]),
         'dp_template_save': (i32, [vp, vp, cp]),
         'dp_template_load': (i32, [vp, cp, P(vp)]),
+        'dp_template_image_size': (i32, [vp, P(u64)]),
+        'dp_template_save_mem': (i32, [vp, vp, C.c_void_p, u64]),
+        'dp_template_load_mem': (i32, [vp, C.c_void_p, u64, i32, P(vp)]),
+        'dp_template_set_origin': (i32, [vp, cp]),
+        'dp_template_origin': (cp, [vp]),
         'dp_template_free': (None, [vp]),
         'dp_template_get_info': (i32, [vp, P(dp_template_info)]),
         'dp_template_record': (i32, [vp, u32, P(u64), P(u64), P(cp), P(cp)]),
@@ -152,6 +157,7 @@ def _declare(lib):
         'dp_comm_destroy': (i32, [vp]),
         'dp_comm_gathered': (i32, [vp, i32, P(vp), P(u64), P(i32)]),
         'dp_comm_hits': (i32, [vp, i32, P(vp), P(u64)]),
+        'dp_comm_set_layout': (i32, [vp, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
         'dp_stream': (vp, [vp]),
         'dp_synchronize': (i32, [vp]),
         'dp_hit_windows': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p]),
@@ -174,9 +180,9 @@ def _declare(lib):
 
 EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy dp_last_error dp_free '
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
-           'dp_template_from_fasta dp_template_set_record_name dp_template_save dp_template_load dp_template_free dp_template_get_info dp_template_record '
+           'dp_template_from_fasta dp_template_set_record_name dp_template_save dp_template_load dp_template_image_size dp_template_save_mem dp_template_load_mem dp_template_set_origin dp_template_origin dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
-           'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_stream dp_synchronize '
+           'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_comm_set_layout dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
 
 
@@ -245,6 +251,26 @@ class Template(object):
         """dp_template_save: planes + run table + record table as they sit in HBM."""
         self.ctx._check(self.ctx.lib.dp_template_save(self.ctx._h, self._h, os.fsencode(path)))
         return path
+
+    @property
+    def image_bytes(self):
+        n = C.c_uint64()
+        self.ctx._check(self.ctx.lib.dp_template_image_size(self._h, C.byref(n)))
+        return n.value
+
+    def save_image(self, address, capacity):
+        """dp_template_save_mem: the packed-file image into caller-owned host memory
+        (pin it, and Context.template_load_image brings it back with three DMA transfers)."""
+        self.ctx._check(self.ctx.lib.dp_template_save_mem(self.ctx._h, self._h, C.c_void_p(address), int(capacity)))
+        return self.image_bytes
+
+    @property
+    def origin(self):
+        return (self.ctx.lib.dp_template_origin(self._h) or b'').decode(errors='replace')
+
+    @origin.setter
+    def origin(self, text):
+        self.ctx._check(self.ctx.lib.dp_template_set_origin(self._h, text.encode()))
 
     def close(self):
         if self._h is not None and self.ctx._h is not None:
@@ -377,6 +403,14 @@ class Context(object):
         self._check(self.lib.dp_template_load(self._h, os.fsencode(path), C.byref(out)))
         return Template(self, out.value)
 
+    def template_load_image(self, address, nbytes, verify=True):
+        """dp_template_load_mem: a packed image (Template.save_image, or a cache file read or
+        mmap()ed into memory) -> resident template.  verify=False skips the checksum pass."""
+        out = C.c_void_p()
+        self._check(self.lib.dp_template_load_mem(self._h, C.c_void_p(address), int(nbytes), 1 if verify else 0,
+                                                  C.byref(out)))
+        return Template(self, out.value)
+
     # ---- scan ---------------------------------------------------------------------
     def scan(self, template, masters, mismatches, seg_begin=0, seg_end=2 ** 64 - 1,
              strands=DP_STRAND_BOTH, algo=DP_ALGO_AUTO):
@@ -497,6 +531,21 @@ class Context(object):
     def comm_destroy(self):
         self._check(self.lib.dp_comm_destroy(self._h))
 
+    def comm_set_layout(self, base, local_start, offset, record, record_len):
+        """dp_comm_set_layout: where every rank's local records were cut from, so that
+        gathered_hits() returns whole-genome coordinates.  base=None switches it off."""
+        if base is None:
+            self._check(self.lib.dp_comm_set_layout(self._h, None, None, None, None, None))
+            return
+        b = np.ascontiguousarray(base, dtype=np.uint32)
+        ls = np.ascontiguousarray(local_start, dtype=np.uint64)
+        of = np.ascontiguousarray(offset, dtype=np.uint64)
+        rc = np.ascontiguousarray(record, dtype=np.uint32)
+        rl = np.ascontiguousarray(record_len, dtype=np.uint64)
+        if len(b) != self._gather_world + 1 or not (len(ls) == len(of) == len(rc) == len(rl) == int(b[-1])):
+            raise ValueError('layout tables do not match the world size / entry count')
+        self._check(self.lib.dp_comm_set_layout(self._h, _ptr(b), _ptr(ls), _ptr(of), _ptr(rc), _ptr(rl)))
+
     def gathered_hits(self, age=0):
         """Hits of every rank for a call (one segment per rank: record = sender rank,
         positions in that segment), sorted.  age 0 = the newest call (waits for the
@@ -518,8 +567,9 @@ class Context(object):
         world, slot, cap = w.value, slot_b.value, self._gather_max
         raw = (C.c_uint8 * (slot * world)).from_address(ptr.value)
         buf = np.frombuffer(raw, dtype=np.uint8).reshape(world, slot)
-        counts = (buf[:, :8].copy().view(np.uint64)[:, 0] & np.uint64(0xFFFFFFFF)).astype(np.int64)
-        if int(counts.max()) > cap:
+        head = buf[:, :64].copy().view(np.uint64)
+        counts = (head[:, 0] & np.uint64(0xFFFFFFFF)).astype(np.int64)
+        if int(counts.max()) > cap or (head[:, 4] & np.uint64(2)).any():     # a slot overflowed or is truncated
             return None
         recs = buf[:, WIRE_HEADER_BYTES:].view(WIRE_DTYPE)            # (world, cap) view of pinned memory
         keep = np.arange(cap)[None, :] < counts[:, None]
@@ -656,9 +706,9 @@ assert PACK_HEADER.itemsize == 64 and PACK_RECORD.itemsize == 24 and PACK_RUN.it
 
 
 def pack_checksum(*chunks):
-    """The checksum of a packed-template file (dp_pack_sum in csrc/dp_template.cu): the six sections
-    (record table, names, run table, plane lo, plane hi, plane exc), each zero-padded to a multiple of 8
-    bytes, form one sequence of little-endian 64-bit words; word i goes to lane i & 3 (h_l starts at
+    """The checksum of a packed-template file (dp_pack_sum in csrc/dp_template.cu): the header with its
+    checksum field zeroed and the six sections (record table, names + origin, run table, plane lo, plane hi,
+    plane exc), each zero-padded to a multiple of 8 bytes, form one sequence of little-endian 64-bit words; word i goes to lane i & 3 (h_l starts at
     SEED + l; h = (h ^ w) * P; h ^= h >> 29) and the four lanes are folded at the end."""
     mask = (1 << 64) - 1
     prime = 0x100000001B3
@@ -688,8 +738,8 @@ def packed_info(path):
         h = np.frombuffer(raw, dtype=PACK_HEADER)[0]
         if bytes(h['magic']) != PACK_MAGIC:
             raise ValueError('%s: not a packed template (bad magic)' % path)
-        if int(h['version']) != 2:
-            raise ValueError('%s: packed-template version %d, expected 2' % (path, int(h['version'])))
+        if int(h['version']) != 3:
+            raise ValueError('%s: packed-template version %d, expected 3' % (path, int(h['version'])))
         n = int(h['n_records'])
         recs = np.frombuffer(fh.read(24 * n), dtype=PACK_RECORD)
         names = fh.read(int(h['names_bytes']))
@@ -701,7 +751,8 @@ def packed_info(path):
         descr = names[p:p + int(r['descr_len'])].decode()
         p += int(r['descr_len'])
         out.append((rid, descr, int(r['start']), int(r['len'])))
-    return {'n_records': n, 'total_bases': int(h['total_bases']), 'n_words': int(h['n_words']),
+    origin = names[p:].decode(errors='replace')
+    return {'origin': origin, 'n_records': n, 'total_bases': int(h['total_bases']), 'n_words': int(h['n_words']),
             'n_runs': int(h['n_runs']), 'checksum': int(h['checksum']), 'records': out,
             'expected_bytes': want, 'bytes': size}
 

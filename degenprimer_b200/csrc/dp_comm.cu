@@ -42,6 +42,8 @@ void dp_comm_release(dp_ctx* ctx) {
   ctx->comm_world = ctx->comm_rank = 0;
   ctx->comm_slot_bytes = 0;
   ctx->comm_seq = 0;
+  ctx->comm_layout.clear();
+  ctx->comm_layout_base.clear();
 }
 
 // (length, strand, primer) of the patterns of `call`, for the kernel that converts its hits
@@ -124,6 +126,9 @@ int dp_comm_export(dp_ctx* ctx, int world, int rank, uint32_t max_hits, char han
   if (world < 1 || world > DP_MAX_RANKS || rank < 0 || rank >= world)
     return dp_set_error(ctx, DP_ERR_ARG, "world %d / rank %d out of range (at most %d ranks)", world, rank, DP_MAX_RANKS);
   if (sizeof(cudaIpcMemHandle_t) != 64) return dp_set_error(ctx, DP_ERR_STATE, "unexpected IPC handle size");
+  // a slot never holds more than the first attempt of a call can produce (the hit workspace starts
+  // at 2^20 records; a call that overflows it re-runs locally and flags its slot as truncated)
+  if (max_hits > (1u << 20)) return dp_set_error(ctx, DP_ERR_ARG, "max_hits %u: a slot holds at most %u hits", max_hits, 1u << 20);
   dp_comm_release(ctx);
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
   const uint64_t slot = 64 + (uint64_t)std::max<uint32_t>(1, max_hits) * sizeof(dp_raw_hit);
@@ -188,6 +193,28 @@ int dp_comm_gathered(dp_ctx* ctx, int age, const void** host_ptr, uint64_t* slot
   return DP_OK;
 }
 
+int dp_comm_set_layout(dp_ctx* ctx, const uint32_t* base, const uint64_t* local_start, const uint64_t* offset,
+                       const uint32_t* record, const uint64_t* record_len) {
+  if (!ctx) return DP_ERR_ARG;
+  if (!ctx->comm_world) return dp_set_error(ctx, DP_ERR_STATE, "dp_comm_set_layout: dp_comm_export first");
+  ctx->comm_layout.clear();
+  ctx->comm_layout_base.clear();
+  if (!base) return DP_OK;                       // back to one segment per rank
+  if (!local_start || !offset || !record || !record_len) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  const int W = ctx->comm_world;
+  for (int r = 0; r < W; ++r)
+    if (base[r + 1] < base[r]) return dp_set_error(ctx, DP_ERR_ARG, "dp_comm_set_layout: base[] must not decrease");
+  ctx->comm_layout_base.assign(base, base + W + 1);
+  ctx->comm_layout.resize(base[W]);
+  for (uint32_t e = 0; e < base[W]; ++e) {
+    ctx->comm_layout[e].local_start = local_start[e];
+    ctx->comm_layout[e].offset = offset[e];
+    ctx->comm_layout[e].record = record[e];
+    ctx->comm_layout[e].record_len = record_len[e];
+  }
+  return DP_OK;
+}
+
 int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
   if (!ctx || !hits_out || !n_out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
   *hits_out = nullptr;
@@ -196,11 +223,12 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
   uint64_t call = 0;
   int rc = comm_collect(ctx, age, &s, &call);
   if (rc) return rc;
+  const bool mapped = !ctx->comm_layout_base.empty();
   // the kernel that brought the slots to the host has converted and sorted them already
   // (one segment per rank, not too many hits): just take its array
   const uint64_t* sorted = ctx->h_sorted[s];
   const char* force = getenv("DEGENPRIMER_B200_EXCHANGE_SORT");      // "host": test hook for the path below
-  if (sorted[1] == 1 && sorted[2] == call + 1 && sorted[0] <= DP_EXCHANGE_SORT_MAX && !(force && force[0] == 'h')) {
+  if (!mapped && sorted[1] == 1 && sorted[2] == call + 1 && sorted[0] <= DP_EXCHANGE_SORT_MAX && !(force && force[0] == 'h')) {
     const uint64_t n = sorted[0];
     dp_hit* out = (dp_hit*)dp_result_alloc(std::max<uint64_t>(1, n) * sizeof(dp_hit));
     if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu hits", (unsigned long long)n);
@@ -221,31 +249,36 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
     // now, the misses then overlap instead of being taken one by one in the loops below
     for (uint64_t off = 64; off < 64 + std::min(n, cap) * sizeof(dp_raw_hit); off += 64)
       __builtin_prefetch((const char*)h + off);
-    if (n > cap) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "rank %d had %llu hits, a slot holds %llu", r,
-                                     (unsigned long long)n, (unsigned long long)cap);
-    if (h[6] != 1) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "rank %d scanned a template of %llu records; "
-                                       "dp_comm_hits handles one segment per rank", r, (unsigned long long)h[6]);
+    if (n > cap || (h[DP_C_SATURATED] & 2ull))
+      return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "rank %d had %llu hits, its slot holds fewer", r, (unsigned long long)n);
+    if (!mapped && h[6] != 1) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "rank %d scanned a template of %llu records; "
+                                       "dp_comm_hits handles one segment per rank unless dp_comm_set_layout was called", r, (unsigned long long)h[6]);
+    if (mapped && h[6] != ctx->comm_layout_base[r + 1] - ctx->comm_layout_base[r])
+      return dp_set_error(ctx, DP_ERR_STATE, "rank %d scanned %llu records, the layout says %u", r, (unsigned long long)h[6],
+                          ctx->comm_layout_base[r + 1] - ctx->comm_layout_base[r]);
     total += n;
   }
   dp_hit* out = (dp_hit*)dp_result_alloc(std::max<uint64_t>(1, total) * sizeof(dp_hit));
   if (!out) return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu hits", (unsigned long long)total);
   // output order (primer, strand, record, pos): patterns are numbered in (primer, strand)
-  // order and record = sender rank, so a counting sort over (pattern, rank) buckets leaves
-  // only the positions inside a bucket to sort
-  const int W = ctx->comm_world;
+  // order, so a counting sort over patterns (x rank, when record = sender rank) leaves only
+  // (record, pos) inside a bucket to sort
+  const int W = mapped ? 1 : ctx->comm_world;
   static thread_local std::vector<uint64_t> bucket;
   bucket.assign((size_t)DP_MAX_PATTERNS * W + 1, 0);
-  for (int r = 0; r < W; ++r) {
+  for (int r = 0; r < ctx->comm_world; ++r) {
     const char* base = recv + (size_t)r * slot;
     const uint64_t n = (uint32_t)((const uint64_t*)base)[0];
     const dp_raw_hit* raw = (const dp_raw_hit*)(base + 64);
+    const uint32_t n_local = mapped ? ctx->comm_layout_base[r + 1] - ctx->comm_layout_base[r] : 1u;
     for (uint64_t i = 0; i < n; ++i) {
-      if (raw[i].pattern >= DP_MAX_PATTERNS) return dp_result_free(out), dp_set_error(ctx, DP_ERR_STATE, "exchange: corrupt slot of rank %d", r);
-      ++bucket[(size_t)raw[i].pattern * W + r + 1];
+      if (raw[i].pattern >= DP_MAX_PATTERNS || raw[i].record >= n_local)
+        return dp_result_free(out), dp_set_error(ctx, DP_ERR_STATE, "exchange: corrupt slot of rank %d", r);
+      ++bucket[(size_t)raw[i].pattern * W + (mapped ? 0 : r) + 1];
     }
   }
   for (size_t i = 1; i < bucket.size(); ++i) bucket[i] += bucket[i - 1];
-  for (int r = 0; r < W; ++r) {
+  for (int r = 0; r < ctx->comm_world; ++r) {
     const char* base = recv + (size_t)r * slot;
     const uint64_t* h = (const uint64_t*)base;
     const uint64_t n = (uint32_t)h[0], rec_len = h[5];
@@ -254,9 +287,17 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
       const uint32_t pat = raw[i].pattern;
       const uint32_t L = plan.pat_len[pat];
       const uint32_t strand = plan.pat_strand[pat];
-      dp_hit& o = out[bucket[(size_t)pat * W + r]++];
-      o.pos = strand ? rec_len - L - raw[i].g : raw[i].g;     // record 0 starts at padded position 0
-      o.record = (uint32_t)r;
+      dp_hit& o = out[bucket[(size_t)pat * W + (mapped ? 0 : r)]++];
+      if (mapped) {
+        // sender's local record -> the record of the whole genome it was cut from
+        const dp_comm_piece& pc = ctx->comm_layout[ctx->comm_layout_base[r] + raw[i].record];
+        const uint64_t fwd = pc.offset + (raw[i].g - pc.local_start);
+        o.pos = strand ? pc.record_len - L - fwd : fwd;
+        o.record = pc.record;
+      } else {
+        o.pos = strand ? rec_len - L - raw[i].g : raw[i].g;     // record 0 starts at padded position 0
+        o.record = (uint32_t)r;
+      }
       o.primer = plan.pat_primer[pat];
       o.strand = (uint8_t)strand;
       o.score3 = (uint8_t)raw[i].score3;
@@ -266,7 +307,10 @@ int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits_out, uint64_t* n_out) {
   uint64_t lo = 0;
   for (size_t j = 0; j + 1 < bucket.size(); ++j) {
     const uint64_t hi = bucket[j];
-    if (hi - lo > 1) std::sort(out + lo, out + hi, [](const dp_hit& a, const dp_hit& b) { return a.pos < b.pos; });
+    if (hi - lo > 1)
+      std::sort(out + lo, out + hi, [](const dp_hit& a, const dp_hit& b) {
+        return a.record != b.record ? a.record < b.record : a.pos < b.pos;
+      });
     lo = hi;
   }
   *hits_out = out;

@@ -40,7 +40,10 @@ struct dp_template {
   std::vector<dp_exc_run> runs;
   dp_exc_run* d_runs;
   uint64_t device_bytes;
+  std::string origin;          // free text saved with the packed image: what it was packed from
+  uint64_t uid;                // process-wide serial number; dp_template_alive(uid) is false once freed
 };
+bool dp_template_alive(uint64_t uid);
 
 // one surviving dimer as written by the duplex kernel; (hit, variant) are
 // implied by the pair directory
@@ -61,6 +64,14 @@ struct dp_dg_plan {
   uint32_t var_off[DP_MAX_PRIMERS];      // byte offset of the primer's variants in d_codes
 };
 
+
+// dp_comm_set_layout: local record of a sender -> where it was cut from
+struct dp_comm_piece {
+  uint64_t local_start;   // padded start of the local record in the sender's template
+  uint64_t offset;        // first base of the piece inside the whole record
+  uint32_t record;        // index of the whole record
+  uint64_t record_len;    // its length
+};
 
 struct dp_ctx {
   int device;
@@ -113,6 +124,8 @@ struct dp_ctx {
   uint64_t* h_sorted[2];       // the same calls converted to dp_hit and sorted by the kernel (32-byte header first)
   unsigned long long* comm_err;         // pinned host flag (device-visible): a wait for a peer timed out
   uint64_t comm_slot_bytes;             // bytes per rank in a receive buffer: 64-byte header + raw hits
+  std::vector<dp_comm_piece> comm_layout;      // multi-record shards (dp_comm_set_layout); empty: one segment per rank
+  std::vector<uint32_t> comm_layout_base;      // entries of rank r: [base[r], base[r+1])
   dp_dg_plan comm_plan[4];     // (length, strand, primer) of the patterns of the last calls (call & 3)
   bool wire_owned;
   dp_dg_plan last_plan;        // (length, strand, primer) of the patterns of the last scan

@@ -184,7 +184,7 @@ __device__ void dp_exchange_to_host(const dp_exchange_args& X, uint64_t call) {
     for (int r = 0; r < X.world; ++r) {
       const volatile uint64_t* h = (const volatile uint64_t*)(X.recv_prev + r * X.slot_bytes);
       const uint64_t n = (uint32_t)h[DP_C_HITS];
-      if (n > X.slot_hits || h[6] != 1) ok = 0;
+      if (n > X.slot_hits || h[6] != 1 || (h[DP_C_SATURATED] & 2ull)) ok = 0;
       first[r] = total;
       total += (uint32_t)min(n, X.slot_hits);
     }
@@ -259,8 +259,11 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
       for (int r = 0; r < P.X.world; ++r) {
         uint64_t* dst = (uint64_t*)(P.X.peers[r] + (uint64_t)P.X.rank * P.X.slot_bytes);
         for (uint64_t i = threadIdx.x; i < n_wire * 3; i += blockDim.x) dst[8 + i] = P.hits[i];
+        // word 4 bit 1: the slot carries fewer records than word 0 says (receivers fall back)
         if (threadIdx.x < 7)
-          dst[threadIdx.x] = threadIdx.x == 5 ? P.X.rec0_len : threadIdx.x == 6 ? P.X.n_records : c[threadIdx.x];
+          dst[threadIdx.x] = threadIdx.x == 5 ? P.X.rec0_len : threadIdx.x == 6 ? P.X.n_records :
+                             threadIdx.x == DP_C_SATURATED ? (c[DP_C_SATURATED] & 1ull) | ((uint64_t)(uint32_t)c[DP_C_HITS] > n_wire ? 2ull : 0ull)
+                                                           : c[threadIdx.x];
       }
     }
   }
@@ -493,7 +496,7 @@ static int scan_prepare(dp_ctx* ctx, const dp_template* t, uint32_t n_primers, c
     hit->job = J;
     hit->used = ++cache_clock;
   }
-  if (t->records.size() == 1 && t->records[0].len < J.max_len)
+  if (t->records.size() == 1 && t->records[0].len < J.max_len && !ctx->comm_world)
     return dp_set_error(ctx, DP_ERR_LENGTH, "template (%llu) is shorter than the primer (%u)",
                         (unsigned long long)t->records[0].len, J.max_len);
   dp_scan_args& A = J.A;
@@ -1042,6 +1045,7 @@ extern "C" int dp_scan(dp_ctx* ctx, const dp_template* t, uint32_t n_primers,
 struct dp_find_pending {
   bool active = false;
   const dp_template* t = nullptr;
+  uint64_t t_uid = 0;                 // dp_find_again: the template must still be alive
   dp_scan_job J;
   dp_dg_launch DL;
   dp_pipeline_state P;
@@ -1099,6 +1103,7 @@ extern "C" int dp_find_begin(dp_ctx* ctx, const dp_template* t, uint32_t n_prime
   }
   F.var_count.assign(var_count, var_count + n_primers);
   F.t = t;
+  F.t_uid = t->uid;
   pipeline_init(F.P);
   rc = pipeline_reserve(ctx, true);
   if (rc) return rc;
@@ -1168,6 +1173,10 @@ extern "C" int dp_find_again(dp_ctx* ctx, const dp_conditions* cond, dp_dimer** 
                                            "(another call used the context, or there was none)");
   if (ctx->abort_flag) return dp_set_error(ctx, DP_ERR_ABORTED, "aborted");
   dp_find_pending& F = *Fp;
+  if (!dp_template_alive(F.t_uid)) {
+    F.resident = false;
+    return dp_set_error(ctx, DP_ERR_STATE, "dp_find_again: the template of the last dp_find has been freed");
+  }
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
   F.DL.PCR_T = cond->PCR_T;
   F.DL.Na_eq_log = cond->Na_eq_log;

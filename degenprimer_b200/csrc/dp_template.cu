@@ -7,6 +7,7 @@
 // buffer when that is already pinned) and packed there; the host never touches
 // a base twice.
 #include <algorithm>
+#include <stdexcept>
 #include <stdlib.h>
 #include <string.h>
 
@@ -354,8 +355,34 @@ int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
   return DP_OK;
 }
 
+// live templates by serial number: a context that keeps the hits of its last dp_find resident
+// (dp_find_again) must not touch a template that has been freed since
+#include <mutex>
+#include <unordered_set>
+static std::mutex g_live_mutex;
+static std::unordered_set<uint64_t> g_live;
+static uint64_t g_next_uid = 1;
+
+bool dp_template_alive(uint64_t uid) {
+  std::lock_guard<std::mutex> lock(g_live_mutex);
+  return g_live.count(uid) != 0;
+}
+
+static void delete_template(dp_template* t) {
+  {
+    std::lock_guard<std::mutex> lock(g_live_mutex);
+    g_live.erase(t->uid);
+  }
+  delete t;
+}
+
 static dp_template* new_template(dp_ctx* ctx, uint32_t n_records) {
   dp_template* t = new dp_template();
+  {
+    std::lock_guard<std::mutex> lock(g_live_mutex);
+    t->uid = g_next_uid++;
+    g_live.insert(t->uid);
+  }
   t->ctx = ctx;
   t->n_words = t->n_words_alloc = 0;
   t->d_lo = t->d_hi = t->d_exc = nullptr;
@@ -380,7 +407,7 @@ int dp_template_from_records(dp_ctx* ctx, uint32_t n_records, const char* const*
     t->records[r].id = name;
   }
   int rc = dp_upload_and_pack(ctx, t, n_records, seqs, lens);
-  if (rc) { free_template_device(t); delete t; return rc; }
+  if (rc) { free_template_device(t); delete_template(t); return rc; }
   *out = t;
   return DP_OK;
 }
@@ -446,7 +473,7 @@ int dp_template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out) {
     t->records[r].descr = recs[r].descr;
   }
   int rc = dp_upload_and_pack(ctx, t, nr, seqs.data(), lens.data());
-  if (rc) { free_template_device(t); delete t; return rc; }
+  if (rc) { free_template_device(t); delete_template(t); return rc; }
   *out = t;
   return DP_OK;
 }
@@ -455,7 +482,7 @@ void dp_template_free(dp_template* t) {
   if (!t) return;
   if (t->ctx) cudaSetDevice(t->ctx->device);
   free_template_device(t);
-  delete t;
+  delete_template(t);
 }
 
 int dp_template_get_info(const dp_template* t, dp_template_info* info) {
@@ -514,7 +541,7 @@ int dp_template_unpack(dp_ctx* ctx, const dp_template* t, uint32_t r, uint64_t b
 //   planes       : lo, hi, exc — n_words_alloc little-endian u32 each (tail guard included)
 // 0.375 B/bp instead of >= 1 B/bp of text, nothing to parse, and the load is one H2D stream.
 #define DP_PACK_MAGIC "DPB200PK"
-#define DP_PACK_VERSION 2u
+#define DP_PACK_VERSION 3u
 
 struct dp_pack_header {
   char magic[8];
@@ -564,27 +591,19 @@ struct dp_pack_sum {
   uint64_t value() const { uint64_t r = h[0]; for (int l = 1; l < 4; ++l) r = (r * DP_PACK_PRIME) ^ h[l]; return r; }
 };
 
-extern "C" int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* path) {
-  if (!ctx || !t || !path) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+// Builds the file image of a template: header, tables and (when `planes` is given) the three planes
+// copied from the device straight to their place.  `image` must hold dp_template_image_size() bytes.
+static uint64_t image_bytes(const dp_template* t) {
+  uint64_t names = 0;
+  for (const dp_record& x : t->records) names += x.id.size() + x.descr.size();
+  names += t->origin.size();
+  return sizeof(dp_pack_header) + t->records.size() * sizeof(dp_pack_record) + names +
+         t->runs.size() * sizeof(dp_exc_run) + 3ull * t->n_words_alloc * 4ull;
+}
+
+static int template_save_to(dp_ctx* ctx, const dp_template* t, char* image) {
   DP_CUDA(ctx, cudaSetDevice(ctx->device));
   const uint32_t nrec = (uint32_t)t->records.size();
-  std::vector<dp_pack_record> recs(nrec);
-  std::string names;
-  for (uint32_t r = 0; r < nrec; ++r) {
-    const dp_record& x = t->records[r];
-    recs[r].start = x.start;
-    recs[r].len = x.len;
-    recs[r].id_len = (uint32_t)x.id.size();
-    recs[r].descr_len = (uint32_t)x.descr.size();
-    names += x.id;
-    names += x.descr;
-  }
-  const size_t plane_words = (size_t)t->n_words_alloc;
-  std::vector<uint32_t> planes(3 * plane_words);
-  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  DP_CUDA(ctx, cudaMemcpy(planes.data(), t->d_lo, plane_words * 4, cudaMemcpyDeviceToHost));
-  DP_CUDA(ctx, cudaMemcpy(planes.data() + plane_words, t->d_hi, plane_words * 4, cudaMemcpyDeviceToHost));
-  DP_CUDA(ctx, cudaMemcpy(planes.data() + 2 * plane_words, t->d_exc, plane_words * 4, cudaMemcpyDeviceToHost));
   dp_pack_header h;
   memset(&h, 0, sizeof h);
   memcpy(h.magic, DP_PACK_MAGIC, 8);
@@ -594,21 +613,75 @@ extern "C" int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* p
   h.n_words_alloc = t->n_words_alloc;
   h.total_bases = t->total_bases;
   h.n_runs = t->runs.size();
-  h.names_bytes = names.size();
+  char* p = image + sizeof h;
+  dp_pack_record* recs = (dp_pack_record*)p;
+  p += nrec * sizeof(dp_pack_record);
+  char* names = p;
+  for (uint32_t r = 0; r < nrec; ++r) {
+    const dp_record& x = t->records[r];
+    dp_pack_record pr;
+    memset(&pr, 0, sizeof pr);
+    pr.start = x.start;
+    pr.len = x.len;
+    pr.id_len = (uint32_t)x.id.size();
+    pr.descr_len = (uint32_t)x.descr.size();
+    memcpy(&recs[r], &pr, sizeof pr);
+    memcpy(p, x.id.data(), x.id.size());
+    p += x.id.size();
+    memcpy(p, x.descr.data(), x.descr.size());
+    p += x.descr.size();
+  }
+  // the origin string (what the image was packed from) rides behind the record names
+  memcpy(p, t->origin.data(), t->origin.size());
+  p += t->origin.size();
+  h.names_bytes = (uint64_t)(p - names);
+  char* runs = p;
+  if (!t->runs.empty()) memcpy(runs, t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
+  p += t->runs.size() * sizeof(dp_exc_run);
+  const size_t plane_bytes = (size_t)t->n_words_alloc * 4;
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  DP_CUDA(ctx, cudaMemcpy(p, t->d_lo, plane_bytes, cudaMemcpyDeviceToHost));
+  DP_CUDA(ctx, cudaMemcpy(p + plane_bytes, t->d_hi, plane_bytes, cudaMemcpyDeviceToHost));
+  DP_CUDA(ctx, cudaMemcpy(p + 2 * plane_bytes, t->d_exc, plane_bytes, cudaMemcpyDeviceToHost));
   dp_pack_sum c;
-  c.mix(recs.data(), recs.size() * sizeof(dp_pack_record));
-  c.mix(names.data(), names.size());
-  c.mix(t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
-  for (int pl = 0; pl < 3; ++pl) c.mix(planes.data() + pl * plane_words, plane_words * 4);   // one section per plane
+  c.mix(&h, sizeof h);                                      // checksum field still zero
+  c.mix(recs, nrec * sizeof(dp_pack_record));
+  c.mix(names, (size_t)h.names_bytes);
+  c.mix(runs, t->runs.size() * sizeof(dp_exc_run));
+  for (int pl = 0; pl < 3; ++pl) c.mix(p + (size_t)pl * plane_bytes, plane_bytes);   // one section per plane
   h.checksum = c.value();
+  memcpy(image, &h, sizeof h);
+  return DP_OK;
+}
+
+extern "C" int dp_template_image_size(const dp_template* t, uint64_t* bytes) {
+  if (!t || !bytes) return DP_ERR_ARG;
+  *bytes = image_bytes(t);
+  return DP_OK;
+}
+
+extern "C" int dp_template_save_mem(dp_ctx* ctx, const dp_template* t, void* image, uint64_t capacity) {
+  if (!ctx || !t || !image) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  if (capacity < image_bytes(t))
+    return dp_set_error(ctx, DP_ERR_ARG, "image buffer holds %llu bytes, the template needs %llu",
+                        (unsigned long long)capacity, (unsigned long long)image_bytes(t));
+  return template_save_to(ctx, t, (char*)image);
+}
+
+extern "C" int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* path) {
+  if (!ctx || !t || !path) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  std::vector<char> image;
+  try {
+    image.resize((size_t)image_bytes(t));
+  } catch (const std::exception&) {
+    return dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for the %llu-byte image of the template", (unsigned long long)image_bytes(t));
+  }
+  int rc = template_save_to(ctx, t, image.data());
+  if (rc) return rc;
   std::string tmp = std::string(path) + ".tmp";
   FILE* fh = fopen(tmp.c_str(), "wb");
   if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot create %s", tmp.c_str());
-  bool ok = fwrite(&h, sizeof h, 1, fh) == 1;
-  ok = ok && (recs.empty() || fwrite(recs.data(), sizeof(dp_pack_record), recs.size(), fh) == recs.size());
-  ok = ok && (names.empty() || fwrite(names.data(), 1, names.size(), fh) == names.size());
-  ok = ok && (t->runs.empty() || fwrite(t->runs.data(), sizeof(dp_exc_run), t->runs.size(), fh) == t->runs.size());
-  ok = ok && fwrite(planes.data(), 4, planes.size(), fh) == planes.size();
+  bool ok = fwrite(image.data(), 1, image.size(), fh) == image.size();
   ok = (fclose(fh) == 0) && ok;
   if (!ok || rename(tmp.c_str(), path) != 0) {
     remove(tmp.c_str());
@@ -617,38 +690,64 @@ extern "C" int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* p
   return DP_OK;
 }
 
-extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out) {
-  if (!ctx || !path || !out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
-  *out = nullptr;
-  FILE* fh = fopen(path, "rb");
-  if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot open %s", path);
-  struct closer { FILE* f; ~closer() { if (f) fclose(f); } } guard{fh};
+// A packed template is read from a file or from an image of that file in host memory
+// (dp_template_load_mem: the cache kept resident by a long-running caller, or mmap()ed).
+struct dp_pack_source {
+  FILE* fh;                  // file source, or
+  const char* mem;           // memory source
+  uint64_t size, at;
+  const char* name;
+  bool read(void* dst, size_t n) {
+    if (n > size - at) return false;
+    if (fh) { if (n && fread(dst, 1, n, fh) != n) return false; }
+    else if (n) memcpy(dst, mem + at, n);
+    at += n;
+    return true;
+  }
+};
+
+// header arithmetic on untrusted input: every term is bounded before it is used as a size
+static bool pack_expected_size(const dp_pack_header& h, uint64_t* want) {
+  uint64_t a, b, c, total = sizeof(dp_pack_header);
+  if (__builtin_mul_overflow((uint64_t)h.n_records, (uint64_t)sizeof(dp_pack_record), &a)) return false;
+  if (__builtin_mul_overflow(h.n_runs, (uint64_t)sizeof(dp_exc_run), &b)) return false;
+  if (__builtin_mul_overflow(h.n_words_alloc, (uint64_t)12, &c)) return false;
+  if (__builtin_add_overflow(total, a, &total) || __builtin_add_overflow(total, h.names_bytes, &total) ||
+      __builtin_add_overflow(total, b, &total) || __builtin_add_overflow(total, c, &total))
+    return false;
+  *want = total;
+  return true;
+}
+
+static int template_load_from(dp_ctx* ctx, dp_pack_source& S, int verify, dp_template** out) {
+  const char* path = S.name;
   dp_pack_header h;
-  if (fread(&h, sizeof h, 1, fh) != 1) return dp_set_error(ctx, DP_ERR_IO, "%s: shorter than a packed-template header", path);
+  if (!S.read(&h, sizeof h)) return dp_set_error(ctx, DP_ERR_IO, "%s: shorter than a packed-template header", path);
   if (memcmp(h.magic, DP_PACK_MAGIC, 8) != 0) return dp_set_error(ctx, DP_ERR_IO, "%s: not a packed template (bad magic)", path);
   if (h.version != DP_PACK_VERSION) return dp_set_error(ctx, DP_ERR_UNSUPPORTED, "%s: packed-template version %u, expected %u", path, h.version, DP_PACK_VERSION);
-  if (h.n_words_alloc != h.n_words + DP_GUARD_WORDS || h.total_bases > h.n_words * 32)
+  if (h.n_words > (1ull << 58) || h.n_words_alloc != h.n_words + DP_GUARD_WORDS || h.total_bases > h.n_words * 32)
     return dp_set_error(ctx, DP_ERR_IO, "%s: inconsistent header", path);
-  fseek(fh, 0, SEEK_END);
-  const uint64_t fsize = (uint64_t)ftell(fh);
-  const uint64_t want = sizeof h + (uint64_t)h.n_records * sizeof(dp_pack_record) + h.names_bytes +
-                        h.n_runs * sizeof(dp_exc_run) + 3ull * h.n_words_alloc * 4ull;
-  if (fsize != want) return dp_set_error(ctx, DP_ERR_IO, "%s: %llu bytes, header says %llu (truncated?)", path,
-                                         (unsigned long long)fsize, (unsigned long long)want);
-  fseek(fh, sizeof h, SEEK_SET);
+  uint64_t want = 0;
+  if (!pack_expected_size(h, &want) || S.size != want)
+    return dp_set_error(ctx, DP_ERR_IO, "%s: %llu bytes, header says %llu (truncated?)", path,
+                        (unsigned long long)S.size, (unsigned long long)want);
+  // from here on every table size is bounded by the size of the source
   std::vector<dp_pack_record> recs(h.n_records);
   std::string names((size_t)h.names_bytes, '\0');
   dp_template* t = new_template(ctx, h.n_records);
   struct dropper {     // error paths: no copy may still be writing into planes that go back to the pool
     dp_template* t;
-    ~dropper() { if (t) { cudaStreamSynchronize(t->ctx->copy_stream); free_template_device(t); delete t; } }
+    ~dropper() { if (t) { cudaStreamSynchronize(t->ctx->copy_stream); free_template_device(t); delete_template(t); } }
   } drop{t};
   t->runs.resize((size_t)h.n_runs);
-  if ((h.n_records && fread(recs.data(), sizeof(dp_pack_record), recs.size(), fh) != recs.size()) ||
-      (h.names_bytes && fread(&names[0], 1, names.size(), fh) != names.size()) ||
-      (h.n_runs && fread(t->runs.data(), sizeof(dp_exc_run), t->runs.size(), fh) != t->runs.size()))
+  if (!S.read(recs.data(), recs.size() * sizeof(dp_pack_record)) || !S.read(&names[0], names.size()) ||
+      !S.read(t->runs.data(), t->runs.size() * sizeof(dp_exc_run)))
     return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
   dp_pack_sum c;
+  // the header (without its checksum field) is covered too
+  dp_pack_header hc = h;
+  hc.checksum = 0;
+  c.mix(&hc, sizeof hc);
   c.mix(recs.data(), recs.size() * sizeof(dp_pack_record));
   c.mix(names.data(), names.size());
   c.mix(t->runs.data(), t->runs.size() * sizeof(dp_exc_run));
@@ -656,7 +755,8 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
   uint64_t prev_end = 0;
   for (uint32_t r = 0; r < h.n_records; ++r) {
     const dp_pack_record& x = recs[r];
-    if ((x.start & 31) || x.start < prev_end || x.start + x.len > h.n_words * 32 || np + x.id_len + x.descr_len > names.size())
+    if ((x.start & 31) || x.start < prev_end || x.len > h.n_words * 32 || x.start > h.n_words * 32 - x.len ||
+        (uint64_t)x.id_len + x.descr_len > names.size() - np)
       return dp_set_error(ctx, DP_ERR_IO, "%s: record table is inconsistent at record %u", path, r);
     prev_end = x.start + x.len;
     t->records[r].start = x.start;
@@ -666,8 +766,10 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
     t->records[r].descr = names.substr(np, x.descr_len);
     np += x.descr_len;
   }
+  t->origin = names.substr(np);
   for (size_t i = 0; i < t->runs.size(); ++i)
-    if (t->runs[i].end <= t->runs[i].start || t->runs[i].end > h.n_words * 32 || (i && t->runs[i].start < t->runs[i - 1].end))
+    if (t->runs[i].end <= t->runs[i].start || t->runs[i].end > h.n_words * 32 || (i && t->runs[i].start < t->runs[i - 1].end) ||
+        t->runs[i].letter < 4 || t->runs[i].letter > 14)
       return dp_set_error(ctx, DP_ERR_IO, "%s: exception-run table is inconsistent at run %zu", path, i);
   t->n_words = h.n_words;
   t->n_words_alloc = h.n_words_alloc;
@@ -683,36 +785,59 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
   DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[0], ctx->stream));
   DP_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->stage_ev[0], 0));
   uint32_t* dst[3] = {t->d_lo, t->d_hi, t->d_exc};
-  bool slot_busy[2] = {false, false};
-  int slot = 0;
-  for (int pl = 0; pl < 3; ++pl) {
-    size_t done = 0;
-    while (done < plane_bytes) {
-      const size_t n = std::min<size_t>(DP_STAGE_BYTES, plane_bytes - done);
-      if (slot_busy[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_copied[slot]));   // pinned slot free again
-      if (fread(ctx->h_stage[slot], 1, n, fh) != n) return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
-      c.mix(ctx->h_stage[slot], n);              // DP_STAGE_BYTES is a multiple of 32: only a plane's last chunk has a tail
-      DP_CUDA(ctx, cudaMemcpyAsync((char*)dst[pl] + done, ctx->h_stage[slot], n, cudaMemcpyHostToDevice, ctx->copy_stream));
-      DP_CUDA(ctx, cudaEventRecord(ctx->stage_copied[slot], ctx->copy_stream));
-      slot_busy[slot] = true;
-      slot ^= 1;
-      done += n;
+  if (S.mem && is_pinned(S.mem)) {
+    // an image in pinned host memory: the planes go out as three DMA transfers, the host touches
+    // them only when asked to verify the checksum (which then overlaps the copies)
+    for (int pl = 0; pl < 3; ++pl)
+      DP_CUDA(ctx, cudaMemcpyAsync(dst[pl], S.mem + S.at + (size_t)pl * plane_bytes, plane_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    if (verify)
+      for (int pl = 0; pl < 3; ++pl) c.mix(S.mem + S.at + (size_t)pl * plane_bytes, plane_bytes);
+    S.at += 3 * plane_bytes;
+  } else {
+    bool slot_busy[2] = {false, false};
+    int slot = 0;
+    for (int pl = 0; pl < 3; ++pl) {
+      size_t done = 0;
+      while (done < plane_bytes) {
+        const size_t n = std::min<size_t>(DP_STAGE_BYTES, plane_bytes - done);
+        if (slot_busy[slot]) DP_CUDA(ctx, cudaEventSynchronize(ctx->stage_copied[slot]));   // pinned slot free again
+        if (!S.read(ctx->h_stage[slot], n)) return dp_set_error(ctx, DP_ERR_IO, "short read on %s", path);
+        if (verify) c.mix(ctx->h_stage[slot], n);  // DP_STAGE_BYTES is a multiple of 32: only a plane's last chunk has a tail
+        DP_CUDA(ctx, cudaMemcpyAsync((char*)dst[pl] + done, ctx->h_stage[slot], n, cudaMemcpyHostToDevice, ctx->copy_stream));
+        DP_CUDA(ctx, cudaEventRecord(ctx->stage_copied[slot], ctx->copy_stream));
+        slot_busy[slot] = true;
+        slot ^= 1;
+        done += n;
+      }
     }
   }
-  DP_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
-  if (c.value() != h.checksum) return dp_set_error(ctx, DP_ERR_IO, "%s: checksum mismatch (file is corrupt)", path);
+  if (verify && c.value() != h.checksum) {
+    DP_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+    return dp_set_error(ctx, DP_ERR_IO, "%s: checksum mismatch (file is corrupt)", path);
+  }
   const size_t nr = t->runs.size();
   const uint32_t nrec = h.n_records;
-  std::vector<uint64_t> starts(nrec), rl(nrec);
+  // small tables go through the pinned result area (async copies from pageable memory would block)
+  const size_t tab_bytes = nr * sizeof(dp_exc_run) + 2 * (size_t)nrec * sizeof(uint64_t);
+  rc = dp_ws_pinned(ctx, tab_bytes + 64);
+  if (rc) return rc;
+  DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));       // nothing queued earlier still reads the pinned area
+  uint64_t* starts = (uint64_t*)ctx->h_res;
+  uint64_t* rl = starts + nrec;
+  dp_exc_run* hruns = (dp_exc_run*)(rl + nrec);
   for (uint32_t r = 0; r < nrec; ++r) { starts[r] = t->records[r].start; rl[r] = t->records[r].len; }
+  if (nr) memcpy(hruns, t->runs.data(), nr * sizeof(dp_exc_run));
   DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_runs, std::max<size_t>(1, nr) * sizeof(dp_exc_run)));
   DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_rec_start, std::max<size_t>(1, nrec) * sizeof(uint64_t)));
   DP_CUDA(ctx, dp_pool_alloc(ctx, (void**)&t->d_rec_len, std::max<size_t>(1, nrec) * sizeof(uint64_t)));
-  if (nr) DP_CUDA(ctx, cudaMemcpyAsync(t->d_runs, t->runs.data(), nr * sizeof(dp_exc_run), cudaMemcpyHostToDevice, ctx->stream));
+  if (nr) DP_CUDA(ctx, cudaMemcpyAsync(t->d_runs, hruns, nr * sizeof(dp_exc_run), cudaMemcpyHostToDevice, ctx->stream));
   if (nrec) {
-    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_start, starts.data(), nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
-    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_len, rl.data(), nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_start, starts, nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+    DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_len, rl, nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
   }
+  // later kernels on ctx->stream wait for the planes on the device, the host waits once
+  DP_CUDA(ctx, cudaEventRecord(ctx->stage_copied[0], ctx->copy_stream));
+  DP_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->stage_copied[0], 0));
   DP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   t->device_bytes = 3 * plane_bytes + nr * sizeof(dp_exc_run) + 2 * nrec * sizeof(uint64_t);
   drop.t = nullptr;
@@ -720,8 +845,44 @@ extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out
   return DP_OK;
 }
 
+extern "C" int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out) {
+  if (!ctx || !path || !out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *out = nullptr;
+  FILE* fh = fopen(path, "rb");
+  if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot open %s", path);
+  struct closer { FILE* f; ~closer() { if (f) fclose(f); } } guard{fh};
+  fseek(fh, 0, SEEK_END);
+  const long fsize = ftell(fh);
+  fseek(fh, 0, SEEK_SET);
+  dp_pack_source S{fh, nullptr, fsize > 0 ? (uint64_t)fsize : 0, 0, path};
+  try {
+    return template_load_from(ctx, S, 1, out);
+  } catch (const std::exception& e) {
+    return dp_set_error(ctx, DP_ERR_NOMEM, "%s: %s", path, e.what());
+  }
+}
+
+extern "C" int dp_template_load_mem(dp_ctx* ctx, const void* image, uint64_t bytes, int verify, dp_template** out) {
+  if (!ctx || !image || !out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
+  *out = nullptr;
+  dp_pack_source S{nullptr, (const char*)image, bytes, 0, "packed image"};
+  try {
+    return template_load_from(ctx, S, verify, out);
+  } catch (const std::exception& e) {
+    return dp_set_error(ctx, DP_ERR_NOMEM, "packed image: %s", e.what());
+  }
+}
+
 // id / description of a record (records made by dp_template_from_records are named record_<r>):
 // what a GenBank / EMBL loader calls after it has handed the sequences over.  Host-side only.
+extern "C" int dp_template_set_origin(dp_template* t, const char* origin) {
+  if (!t) return DP_ERR_ARG;
+  t->origin = origin ? origin : "";
+  return DP_OK;
+}
+
+extern "C" const char* dp_template_origin(const dp_template* t) { return t ? t->origin.c_str() : ""; }
+
 extern "C" int dp_template_set_record_name(dp_template* t, uint32_t r, const char* id, const char* descr) {
   if (!t || r >= t->records.size() || !id) return DP_ERR_ARG;
   t->records[r].id = id;

@@ -227,3 +227,114 @@ class ShardedTemplate(object):
         if gather:
             hits = sort_hits(all_gather_records(hits, group))
         return hits, stats
+
+
+class GenomeLayout(object):
+    """A genome of several records cut into `world` contiguous ranges of its padded
+    concatenation (every record starts on a 32-base word), one range per rank — the
+    strong-scaling split of SURVEY §8e.  Rank g owns the window STARTS in
+    [ranges[g][0], ranges[g][1]); the bases it uploads are the pieces of the records that
+    intersect that range, the last piece extended by a (max_primer_len - 1) halo so that every
+    owned window is complete.  Only the last piece of a rank can carry a halo (the records
+    behind it start past the range), so the owned starts of a rank are one interval
+    [0, seg_end) of ITS padded concatenation — exactly what dp_find's seg_begin / seg_end take."""
+
+    def __init__(self, lengths, world, max_primer_len):
+        self.lengths = np.asarray(lengths, dtype=np.int64)
+        words = (self.lengths + 31) // 32
+        self.starts = (np.concatenate(([0], np.cumsum(words)[:-1])) * 32).astype(np.int64)
+        self.n_words = int(words.sum())
+        self.world = int(world)
+        self.halo = int(max_primer_len) - 1
+        per = -(-self.n_words // self.world) if self.n_words else 0
+        self.ranges = [(min(self.n_words, g * per) * 32, min(self.n_words, (g + 1) * per) * 32)
+                       for g in range(self.world)]
+        self.pieces = [self._pieces(g) for g in range(self.world)]
+
+    def _pieces(self, g):
+        """[(record, offset, length, owned)]: bases [offset, offset+length) of the record are
+        uploaded, window starts [offset, offset+owned) of it belong to rank g."""
+        b, e = self.ranges[g]
+        out = []
+        for r in range(len(self.lengths)):
+            s, n = int(self.starts[r]), int(self.lengths[r])
+            lo, hi = max(0, b - s), min(n, e - s)
+            if hi <= lo:
+                continue
+            out.append((r, lo, min(n, hi + self.halo) - lo, hi - lo))
+        return out
+
+    def records_of(self, g):
+        return sorted({p[0] for p in self.pieces[g]})
+
+    def local_starts(self, g):
+        n = np.array([p[2] for p in self.pieces[g]], dtype=np.int64)
+        return (np.concatenate(([0], np.cumsum((n + 31) // 32)[:-1])) * 32).astype(np.int64) if len(n) else n
+
+    def seg_end(self, g):
+        """Window starts of rank g's template that it owns: [0, seg_end)."""
+        if not self.pieces[g]:
+            return 0
+        return int(self.local_starts(g)[-1]) + self.pieces[g][-1][3]
+
+    def exchange_tables(self):
+        """(base, local_start, offset, record, record_len) for Context.comm_set_layout."""
+        base, ls, off, rec, rl = [0], [], [], [], []
+        for g in range(self.world):
+            starts = self.local_starts(g)
+            for j, (r, o, _n, _own) in enumerate(self.pieces[g]):
+                ls.append(int(starts[j]))
+                off.append(o)
+                rec.append(r)
+                rl.append(int(self.lengths[r]))
+            base.append(len(ls))
+        return base, ls, off, rec, rl
+
+    def to_global(self, hits, g, primer_lens):
+        """Hits of rank g's template (record = piece index) in whole-genome coordinates."""
+        out = hits.copy()
+        if not len(hits):
+            return out
+        pc = self.pieces[g]
+        rec = np.array([p[0] for p in pc], dtype=np.int64)[hits['record']]
+        off = np.array([p[1] for p in pc], dtype=np.int64)[hits['record']]
+        ln = np.array([p[2] for p in pc], dtype=np.int64)[hits['record']]
+        L = np.asarray(primer_lens, dtype=np.int64)[hits['primer']]
+        pos = hits['pos'].astype(np.int64)
+        fwd = np.where(hits['strand'] == 0, pos, ln - L - pos) + off
+        out['pos'] = np.where(hits['strand'] == 0, fwd, self.lengths[rec] - L - fwd).astype(np.uint64)
+        out['record'] = rec.astype(np.uint32)
+        return out
+
+
+class ShardedGenome(object):
+    """This rank's part of a multi-record genome, resident on its GPU (GenomeLayout)."""
+
+    def __init__(self, ctx, layout, rank, record_source):
+        """record_source(r) -> the bytes of whole record r: a pinned uint8 torch tensor / numpy
+        array (sliced without a copy) or bytes."""
+        self.ctx, self.layout, self.rank = ctx, layout, rank
+        self._keep, srcs = [], []
+        for r, off, n, _own in layout.pieces[rank]:
+            src = record_source(r)
+            if hasattr(src, 'data_ptr'):                      # torch tensor
+                srcs.append((src.data_ptr() + off, n))
+            elif isinstance(src, np.ndarray):
+                srcs.append((src.ctypes.data + off, n))
+            else:
+                srcs.append(bytes(src[off:off + n]))
+            self._keep.append(src)
+        self.sources = srcs
+        self.template = ctx.template_from_sequences(srcs)
+        self.seg_end = layout.seg_end(rank)
+
+    def attach(self, exchange):
+        """Tells a HitExchange where the pieces of every rank come from: collect_hits() then
+        returns the hits of the WHOLE genome in whole-genome coordinates."""
+        exchange.ctx.comm_set_layout(*self.layout.exchange_tables())
+
+    def find(self, query, cond, ctx=None, algo=0):
+        """dp_find over the owned window starts.  Returns (local hits, dimers, stats, dG stats);
+        GenomeLayout.to_global() translates the hits."""
+        c = ctx or self.ctx
+        return c.find(self.template, query, cond=cond, seg_begin=0, seg_end=self.seg_end, algo=algo)

@@ -99,19 +99,37 @@ void dp_template_free(dp_template* t);
  * together with parsing and packing the text: the file holds the three bit-planes, the
  * exception-run table and the record table (ids, descriptions) exactly as they sit in
  * HBM — 0.375 B/bp, nothing to parse, one H2D stream through pinned staging.
- * Layout (little endian): 64-byte header {magic "DPB200PK", u32 version = 2,
+ * Layout (little endian): 64-byte header {magic "DPB200PK", u32 version = 3,
  * u32 n_records, u64 n_words, u64 n_words_alloc, u64 total_bases, u64 n_runs,
- * u64 names_bytes, u64 checksum of the six sections after the header (four interleaved
- * multiply-xor lanes over their 64-bit words, see dp_pack_sum)}; n_records x
- * {u64 start, u64 len, u32 id_len, u32 descr_len}; the id and description bytes;
+ * u64 names_bytes, u64 checksum of the header (checksum field zero) and the six sections
+ * after it (four interleaved multiply-xor lanes over their 64-bit words, see dp_pack_sum)};
+ * n_records x {u64 start, u64 len, u32 id_len, u32 descr_len}; the id and description
+ * bytes, followed by the origin string (names_bytes covers both);
  * n_runs x {u64 start, u64 end, u32 letter, u32 pad}; planes lo, hi, exc of
- * n_words_alloc u32 each.  dp_template_load checks magic, version, sizes, the tables'
- * consistency and the checksum (DP_ERR_IO / DP_ERR_UNSUPPORTED otherwise). */
+ * n_words_alloc u32 each.  dp_template_load checks magic, version, sizes (overflow-safe), the
+ * tables' consistency (run letters included) and the checksum (DP_ERR_IO /
+ * DP_ERR_UNSUPPORTED otherwise; DP_ERR_NOMEM instead of an exception across the ABI). */
 /* id / description of record r (dp_template_from_records names them record_<r>); host-side,
  * used by loaders of formats other than FASTA (GenBank, EMBL) before dp_template_save. */
 int dp_template_set_record_name(dp_template* t, uint32_t r, const char* id, const char* descr);
 int dp_template_save(dp_ctx* ctx, const dp_template* t, const char* path);
 int dp_template_load(dp_ctx* ctx, const char* path, dp_template** out);
+/* The same image in host memory instead of a file: a long-running caller keeps its genomes
+ * packed in (pinned) host memory, 0.375 B/bp, and brings one to the device with three DMA
+ * transfers -- the counterpart of the reference holding SeqRecords in RAM
+ * (BioUtils/BioUtils/SeqUtils.py:216-225) at 1 B/bp and re-encoding them on every search
+ * (DegenPrimer/SearchEngine.py:287-290,333-336).  dp_template_save_mem writes
+ * dp_template_image_size() bytes.  dp_template_load_mem: `verify` != 0 checks the checksum
+ * (one pass of the host over the image); an image that is not pinned is staged like a file. */
+int dp_template_image_size(const dp_template* t, uint64_t* bytes);
+int dp_template_save_mem(dp_ctx* ctx, const dp_template* t, void* image, uint64_t capacity);
+int dp_template_load_mem(dp_ctx* ctx, const void* image, uint64_t bytes, int verify, dp_template** out);
+/* Free text stored with the image (covered by its checksum): what the template was packed
+ * from.  degenprimer_b200/SeqView.py records path, size and mtime of the source file there and
+ * rebuilds a cache whose origin differs -- the reference's SeqIO.index_db raises when the
+ * file list of an index differs (BioUtils/BioUtils/SeqUtils.py:169). */
+int dp_template_set_origin(dp_template* t, const char* origin);
+const char* dp_template_origin(const dp_template* t);
 
 typedef struct dp_template_info {
   uint32_t n_records;
@@ -360,7 +378,8 @@ int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes);
  *          the conversion overlaps the kernels of the call in flight.
  * dp_comm_gathered() gives `world` slots of `slot_bytes`, slot r = rank r's hits
  * of that call.  A slot holds max_hits records; header[0] tells when a rank had
- * more (then fall back to a host-side gather).  dp_comm_destroy only after every
+ * more, and bit 1 of header[4] says that the slot carries fewer records than header[0]
+ * (then fall back to a host-side gather).  max_hits <= 2^20.  dp_comm_destroy only after every
  * rank has collected its last call (barrier on the host side). */
 int dp_comm_export(dp_ctx* ctx, int world, int rank, uint32_t max_hits, char handles[128]);
 int dp_comm_attach(dp_ctx* ctx, const char* all_handles);
@@ -373,6 +392,15 @@ int dp_comm_gathered(dp_ctx* ctx, int age, const void** host_ptr, uint64_t* slot
  * and record count.  DP_ERR_UNSUPPORTED if a slot overflowed or a rank scanned a
  * multi-record template (use dp_comm_gathered then). */
 int dp_comm_hits(dp_ctx* ctx, int age, dp_hit** hits, uint64_t* n_hits);
+/* Shards of a multi-record genome (one contiguous range of the padded concatenation per
+ * rank, cut inside records where it has to be): tells dp_comm_hits where every rank's LOCAL
+ * records come from, so that it returns hits in whole-genome coordinates -- record = index
+ * of the whole record, pos on that record (strand 1: on its reverse complement).  Rank r's
+ * local record j is entry e = base[r] + j: it starts at local_start[e] of r's padded
+ * concatenation and holds the bases from offset[e] on of record record[e], which is
+ * record_len[e] long.  base has world+1 entries.  NULL base: back to one segment per rank. */
+int dp_comm_set_layout(dp_ctx* ctx, const uint32_t* base, const uint64_t* local_start,
+                       const uint64_t* offset, const uint32_t* record, const uint64_t* record_len);
 
 /* The duplex stage of the LAST dp_find / dp_find_end of this context again under
  * other conditions (the optimiser's inner loop, DegenPrimer/PCR_Optimizer.py:

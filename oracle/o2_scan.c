@@ -13,6 +13,9 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 static int base_index(unsigned char c) {
   switch (c) { case 'A': return 0; case 'C': return 1; case 'G': return 2; case 'T': return 3; default: return -1; }
@@ -55,18 +58,52 @@ static int64_t scan_strand(const unsigned char* t, int64_t T, const unsigned cha
   const int thr = 3 * need - 1;
   const int64_t n = T - L + 1;
   if (n <= 0) return 0;
-  unsigned char* flag = (unsigned char*)calloc((size_t)n, 1);
-  if (!flag) return -2;
-#pragma omp parallel for schedule(static)
-  for (int64_t q = 0; q < n; ++q) {
-    int s = 0;
-    for (int j = 0; j < L; ++j) s += lut[j][t[q + j]];
-    flag[q] = s >= thr;
-  }
+  /* every thread scans one contiguous stretch of window starts and keeps its own ascending hit
+   * list; the lists are concatenated in thread order */
   int64_t found = 0;
-  for (int64_t q = 0; q < n; ++q)
-    if (flag[q]) { if (found < cap) out[found] = q; ++found; }
-  free(flag);
+  int failed = 0;
+#pragma omp parallel
+  {
+#ifdef _OPENMP
+    const int nt = omp_get_num_threads(), me = omp_get_thread_num();
+#else
+    const int nt = 1, me = 0;
+#endif
+    const int64_t lo = n * me / nt, hi = n * (me + 1) / nt;
+    int64_t cap_l = 1024, n_l = 0;
+    int64_t* mine = (int64_t*)malloc(sizeof(int64_t) * (size_t)cap_l);
+    for (int64_t q = lo; mine && q < hi; ++q) {
+      /* plain sum over the window; gives up once even full scores for the rest cannot reach thr */
+      int s = 0, left = 3 * L;
+      for (int j = 0; j < L; ++j) {
+        s += lut[j][t[q + j]];
+        left -= 3;
+        if (s + left < thr) break;
+      }
+      if (s >= thr) {
+        if (n_l == cap_l) {
+          cap_l *= 2;
+          int64_t* grown = (int64_t*)realloc(mine, sizeof(int64_t) * (size_t)cap_l);
+          if (!grown) { free(mine); mine = NULL; break; }
+          mine = grown;
+        }
+        mine[n_l++] = q;
+      }
+    }
+    if (!mine) {
+#pragma omp atomic write
+      failed = 1;
+    }
+    /* ordered hand-over: thread i appends after threads 0..i-1 */
+    for (int turn = 0; turn < nt; ++turn) {
+      if (turn == me && mine) {
+        for (int64_t i = 0; i < n_l; ++i) { if (found < cap) out[found] = mine[i]; ++found; }
+      }
+#pragma omp barrier
+    }
+    free(mine);
+  }
+  if (failed) return -2;
   return found;
 }
 
@@ -76,11 +113,16 @@ int o2_scan(const unsigned char* fwd, int64_t T, const unsigned char* primer, in
             int64_t* rev_out, int64_t rev_cap, int64_t* n_rev) {
   unsigned char* rev = (unsigned char*)malloc((size_t)(T > 0 ? T : 1));
   if (!rev) return -2;
+  unsigned char comp[256];
+  for (int c = 0; c < 256; ++c) comp[c] = complement((unsigned char)c);
+  int bad = 0;
+#pragma omp parallel for schedule(static) reduction(|:bad)
   for (int64_t i = 0; i < T; ++i) {
-    unsigned char c = complement(fwd[T - 1 - i]);
-    if (!c) { free(rev); return -1; }
+    unsigned char c = comp[fwd[T - 1 - i]];
+    if (!c) bad = 1;
     rev[i] = c;
   }
+  if (bad) { free(rev); return -1; }
   int64_t a = scan_strand(fwd, T, primer, L, k, fwd_out, fwd_cap);
   int64_t b = a < 0 ? a : scan_strand(rev, T, primer, L, k, rev_out, rev_cap);
   free(rev);

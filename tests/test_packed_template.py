@@ -26,11 +26,11 @@ def _write_packed(path, records, n_runs=2, corrupt=None):
         runs[i] = (10 * i + 3, 10 * i + 7, 14, 0)
     planes = np.arange(3 * (n_words + guard), dtype='<u4') * np.uint32(2654435761)
     h = np.zeros(1, dtype=nat.PACK_HEADER)
-    h['magic'], h['version'], h['n_records'] = nat.PACK_MAGIC, 2, len(records)
+    h['magic'], h['version'], h['n_records'] = nat.PACK_MAGIC, 3, len(records)
     h['n_words'], h['n_words_alloc'] = n_words, n_words + guard
     h['total_bases'], h['n_runs'], h['names_bytes'] = sum(r[2] for r in records), n_runs, len(names)
     pb = planes.tobytes()
-    h['checksum'] = nat.pack_checksum(recs.tobytes(), names, runs.tobytes(), pb[:len(pb) // 3],
+    h['checksum'] = nat.pack_checksum(h.tobytes(), recs.tobytes(), names, runs.tobytes(), pb[:len(pb) // 3],
                                       pb[len(pb) // 3:2 * len(pb) // 3], pb[2 * len(pb) // 3:])
     blob = h.tobytes() + recs.tobytes() + names + runs.tobytes() + planes.tobytes()
     if corrupt is not None:
@@ -115,10 +115,11 @@ def test_packed_template_round_trip(tmp_path):
     assert info['total_bases'] == sum(len(s) for s in seqs.values())
     raw = open(cache, 'rb').read()
     o_names = 64 + 24 * 3
-    o_runs = o_names + sum(len(r[0]) + len(r[1]) for r in info['records'])
+    o_runs = o_names + sum(len(r[0]) + len(r[1]) for r in info['records']) + len(info['origin'].encode())
     o_planes = o_runs + 24 * info['n_runs']
     pb = (len(raw) - o_planes) // 3
-    assert nat.pack_checksum(raw[64:o_names], raw[o_names:o_runs], raw[o_runs:o_planes], raw[o_planes:o_planes + pb],
+    assert info['origin'].startswith(os.path.abspath(fa) + '|')
+    assert nat.pack_checksum(raw[:56] + b'\0' * 8, raw[64:o_names], raw[o_names:o_runs], raw[o_runs:o_planes], raw[o_planes:o_planes + pb],
                              raw[o_planes + pb:o_planes + 2 * pb], raw[o_planes + 2 * pb:]) == info['checksum']                                                       # C writer == Python reader
     t0 = a._templates[0]
     b = SeqView(upper=True)
@@ -141,10 +142,13 @@ def test_packed_template_round_trip(tmp_path):
             fh.write(blob)
         with pytest.raises(nat.NativeError, match=msg):
             SeqView(upper=True).load_packed(str(tmp_path / name))
-    # a cache older than the FASTA file is rebuilt
+    # the cache remembers size and mtime of its source: a touched FASTA file makes it stale and it is rebuilt
     os.utime(cache, (1, 1))
     d = SeqView(upper=True)
-    assert d.load(fa, dbname=cache) and os.path.getmtime(cache) > 1 and hits(d) == want
+    assert d.load(fa, dbname=cache) and os.path.getmtime(cache) == 1 and hits(d) == want     # still valid: reused
+    os.utime(fa, (2_000_000_000, 2_000_000_000))
+    e = SeqView(upper=True)
+    assert e.load(fa, dbname=cache) and os.path.getmtime(cache) > 1 and hits(e) == want
 
 
 GENBANK = '''LOCUS       SCU49845     120 bp    DNA             PLN       21-JUN-1999

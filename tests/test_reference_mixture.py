@@ -203,6 +203,10 @@ class _OracleSearcher(object):
         res = self._compile(self.find_matches(counter, template, primer, mismatches), True)
         return to_shelf(res) if res else None
 
+    def find_all(self, counter, templates, primers, mismatches):
+        return {t.id: [self._compile(self.find_matches(counter, t, p, mismatches), True) for p in primers]
+                for t in templates}
+
 
 @pytest.mark.parametrize('idx', [0, 2, 5])
 def test_products_finder_composition(idx):
