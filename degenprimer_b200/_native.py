@@ -152,6 +152,7 @@ def _declare(lib):
         'dp_find_again': (i32, [vp, vp, P(vp), P(u64), vp]),
         'dp_scan_prepare_kernels': (i32, [vp, u32, P(C.c_char_p), P(i32), i32]),
         'dp_jit_selftest': (i32, [u32, P(C.c_char_p), P(i32), i32, C.c_char_p, C.c_char_p]),
+        'dp_jit_describe': (i32, [u32, P(C.c_char_p), P(i32), i32, C.c_char_p, u64]),
         'dp_comm_export': (i32, [vp, i32, i32, u32, C.c_char_p]),
         'dp_comm_attach': (i32, [vp, C.c_char_p]),
         'dp_comm_destroy': (i32, [vp]),
@@ -182,7 +183,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_abort_requested dp_device_info dp_template_from_records dp_template_from_ascii '
            'dp_template_from_fasta dp_template_set_record_name dp_template_save dp_template_load dp_template_image_size dp_template_save_mem dp_template_load_mem dp_template_set_origin dp_template_origin dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
-           'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_comm_set_layout dp_stream dp_synchronize '
+           'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_jit_describe dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_comm_set_layout dp_stream dp_synchronize '
            'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
 
 
@@ -208,6 +209,30 @@ def load():
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def jit_plan(masters, mismatches, strands=DP_STRAND_BOTH):
+    """dp_jit_describe: the prefilter plan of the specialised scan kernel of a primer set —
+    [dict(pattern, K, need, p_alive, groups=[[window positions], ...])], mode.  No GPU needed."""
+    lib = load()
+    n = len(masters)
+    m = (C.c_char_p * n)(*[s.encode('ascii') for s in masters])
+    if isinstance(mismatches, int):
+        mismatches = [mismatches] * n
+    k = (C.c_int32 * n)(*[int(x) for x in mismatches])
+    buf = C.create_string_buffer(1 << 20)
+    rc = lib.dp_jit_describe(n, m, k, int(strands), buf, len(buf))
+    if rc < 0:
+        raise NativeError(rc, lib.dp_last_error(None).decode(errors='replace'))
+    plans, mode = [], None
+    for line in buf.value.decode().splitlines():
+        f = line.split()
+        if f[1] == 'mode':
+            mode = f[2]
+            continue
+        plans.append(dict(pattern=int(f[2]), K=int(f[4]), need=int(f[6]), p_alive=float(f[8]),
+                          groups=[[int(x) for x in g.split(',')] for g in f[10:]]))
+    return plans, mode
 
 
 class Template(object):

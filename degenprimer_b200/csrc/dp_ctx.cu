@@ -33,21 +33,36 @@ struct block_header { size_t bytes; size_t magic; };          // in front of eve
 const size_t kMagic = 0x44504253554C5453ull;
 }  // namespace
 
+const size_t kMagicPinned = 0x44504250494E4E44ull;      // block came from cudaHostAlloc
+
 void* dp_result_alloc(size_t bytes) {
   if (bytes == 0) bytes = 1;
   if (bytes >= kBigBlock) {
-    std::lock_guard<std::mutex> lock(g_blocks_mutex);
-    int best = -1;
-    for (int i = 0; i < 4; ++i)
-      if (g_blocks[i].p && g_blocks[i].bytes >= bytes && g_blocks[i].bytes <= 2 * bytes + kBigBlock &&
-          (best < 0 || g_blocks[i].bytes < g_blocks[best].bytes))
-        best = i;
-    if (best >= 0) {
-      void* p = g_blocks[best].p;
-      g_blocks[best].p = nullptr;
-      g_blocks[best].bytes = 0;
-      return (char*)p + sizeof(block_header);
+    {
+      std::lock_guard<std::mutex> lock(g_blocks_mutex);
+      int best = -1;
+      for (int i = 0; i < 4; ++i)
+        if (g_blocks[i].p && g_blocks[i].bytes >= bytes && g_blocks[i].bytes <= 2 * bytes + kBigBlock &&
+            (best < 0 || g_blocks[i].bytes < g_blocks[best].bytes))
+          best = i;
+      if (best >= 0) {
+        void* p = g_blocks[best].p;
+        g_blocks[best].p = nullptr;
+        g_blocks[best].bytes = 0;
+        return (char*)p + sizeof(block_header);
+      }
     }
+    // big blocks are page-locked: the device writes results straight into them (no staging copy);
+    // they are recycled, so the cost of locking the pages is paid once
+    void* raw = nullptr;
+    const size_t want = bytes + bytes / 8;                  // a little slack: the next result of the loop fits too
+    if (cudaHostAlloc(&raw, sizeof(block_header) + want, cudaHostAllocDefault) == cudaSuccess) {
+      block_header* h = (block_header*)raw;
+      h->bytes = want;
+      h->magic = kMagicPinned;
+      return (char*)h + sizeof(block_header);
+    }
+    cudaGetLastError();
   }
   block_header* h = (block_header*)malloc(sizeof(block_header) + bytes);
   if (!h) return nullptr;
@@ -56,10 +71,21 @@ void* dp_result_alloc(size_t bytes) {
   return (char*)h + sizeof(block_header);
 }
 
+bool dp_result_is_pinned(const void* p) {
+  if (!p) return false;
+  const block_header* h = (const block_header*)((const char*)p - sizeof(block_header));
+  return h->magic == kMagicPinned;
+}
+
+static void block_release(block_header* h) {
+  if (h->magic == kMagicPinned) cudaFreeHost(h);
+  else free(h);
+}
+
 void dp_result_free(void* p) {
   if (!p) return;
   block_header* h = (block_header*)((char*)p - sizeof(block_header));
-  if (h->magic != kMagic) { free(p); return; }               // not ours: plain malloc
+  if (h->magic != kMagic && h->magic != kMagicPinned) { free(p); return; }               // not ours: plain malloc
   if (h->bytes >= kBigBlock) {
     std::lock_guard<std::mutex> lock(g_blocks_mutex);
     int slot = -1;
@@ -67,14 +93,14 @@ void dp_result_free(void* p) {
     if (slot < 0) {                                            // evict the smallest parked block
       slot = 0;
       for (int i = 1; i < 4; ++i) if (g_blocks[i].bytes < g_blocks[slot].bytes) slot = i;
-      if (g_blocks[slot].bytes >= h->bytes) { free(h); return; }
-      free(g_blocks[slot].p);
+      if (g_blocks[slot].bytes >= h->bytes) { block_release(h); return; }
+      block_release((block_header*)g_blocks[slot].p);
     }
     g_blocks[slot].p = h;
     g_blocks[slot].bytes = h->bytes;
     return;
   }
-  free(h);
+  block_release(h);
 }
 
 cudaError_t dp_pool_alloc(dp_ctx* ctx, void** p, size_t bytes) {

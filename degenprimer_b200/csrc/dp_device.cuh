@@ -150,10 +150,10 @@ __device__ __forceinline__ void dp_emit_hit(const dp_scan_args& A, uint64_t g, u
   }
 }
 
-// exact verify of window g against pattern P (index pat); with_exc = false leaves
-// windows that touch a non-ACGT base to the run-boundary pass
-__device__ __forceinline__ void dp_verify_window(const dp_scan_args& A, const dp_pattern& P, uint64_t g,
-                                                 uint32_t pat, bool with_exc) {
+// exact thirds score of window g against pattern P; with_exc = false leaves windows that touch
+// a non-ACGT base to the run-boundary pass.  True iff the window reaches the threshold.
+__device__ __forceinline__ bool dp_score_window(const dp_scan_args& A, const dp_pattern& P, uint64_t g,
+                                                bool with_exc, uint32_t* score) {
   const uint64_t wi = g >> 5;
   const int sh = (int)(g & 31);
   uint32_t whi[2], wlo[2], wex[2];
@@ -165,9 +165,113 @@ __device__ __forceinline__ void dp_verify_window(const dp_scan_args& A, const dp
     const uint32_t e0 = __ldg(A.exc + wi), e1 = __ldg(A.exc + wi + 1), e2 = __ldg(A.exc + wi + 2);
     wex[0] = __funnelshift_r(e0, e1, sh); wex[1] = __funnelshift_r(e1, e2, sh);
   }
-  if (!with_exc && ((wex[0] & P.lmask[0]) | (wex[1] & P.lmask[1]))) return;
+  if (!with_exc && ((wex[0] & P.lmask[0]) | (wex[1] & P.lmask[1]))) return false;
   const uint32_t s = dp_score3<2>(P, whi, wlo, wex);
-  if (s >= P.thr3) dp_emit_hit(A, g, pat, P.len, s, P.n_var);
+  *score = s;
+  return s >= P.thr3;
+}
+
+__device__ __forceinline__ void dp_verify_window(const dp_scan_args& A, const dp_pattern& P, uint64_t g,
+                                                 uint32_t pat, bool with_exc) {
+  uint32_t s;
+  if (dp_score_window(A, P, g, with_exc, &s)) dp_emit_hit(A, g, pat, P.len, s, P.n_var);
+}
+
+// ---- deferred exact verify of the run-time specialised kernels ------------------------------
+// The prefilter leaves ~1e-4 of the windows alive.  Verifying them where they are found costs a
+// whole warp ~250 issue slots per candidate (31 lanes idle).  Instead every warp parks its
+// candidates in a small shared-memory queue and verifies 32 of them at once, one per lane; the
+// hits of such a batch take ONE atomic (slot and pair index handed out by ballot / prefix sum).
+#define DP_Q_CAP 64
+
+// every lane of a converged warp calls this; lanes with `hit` append a record
+__device__ __forceinline__ void dp_emit_hits_warp(const dp_scan_args& A, bool hit, uint64_t g, uint32_t r,
+                                                  uint32_t pat, uint32_t score, uint32_t n_var) {
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t m = __ballot_sync(0xFFFFFFFFu, hit);
+  if (!m) return;
+  const uint32_t v = hit ? n_var : 0u;
+  uint32_t incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t x = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= (uint32_t)o) incl += x;
+  }
+  const uint32_t total_var = __shfl_sync(0xFFFFFFFFu, incl, 31);
+  const int leader = __ffs(m) - 1;
+  unsigned long long old = 0;
+  if ((int)lane == leader) {
+    const unsigned long long seen = *(volatile unsigned long long*)&A.counters[DP_C_HITS];
+    if ((uint32_t)seen > 0xF0000000u || (seen >> 32) > 0xF0000000ull) {
+      A.counters[DP_C_SATURATED] = 1ull;
+      old = ~0ull;
+    } else {
+      old = atomicAdd(&A.counters[DP_C_HITS], (unsigned long long)__popc(m) | ((unsigned long long)total_var << 32));
+    }
+  }
+  old = __shfl_sync(0xFFFFFFFFu, old, leader);
+  if (old == ~0ull || !hit) return;
+  // slot and pair_base both grow with the lane number: pair_base stays monotone in slot
+  const uint32_t slot = (uint32_t)old + __popc(m & ((1u << lane) - 1u));
+  if (slot < A.hits_cap) {
+    dp_raw_hit h;
+    h.g = g; h.record = r; h.pattern = (uint16_t)pat; h.score3 = (uint16_t)score;
+    h.pair_base = (uint32_t)(old >> 32) + (incl - v); h.reserved = 0;
+    A.hits[slot] = h;
+  }
+}
+
+// one queued candidate per lane (entry = g << 8 | slot in `pats`); `valid` lanes verify theirs
+static __device__ __noinline__ void dp_verify_warp(const dp_scan_args& A, const dp_pattern* pats, const uint8_t* pattern_of,
+                                            unsigned long long entry, bool valid) {
+  bool hit = false;
+  uint64_t g = 0;
+  uint32_t r = 0, slot = 0, score = 0, n_var = 0;
+  if (valid) {
+    g = entry >> 8;
+    slot = (uint32_t)(entry & 0xFFull);
+    const dp_pattern& P = pats[slot];
+    if (dp_score_window(A, P, g, false, &score)) {
+      r = dp_find_record(A.rec_start, A.n_records, g);
+      hit = g - A.rec_start[r] + P.len <= A.rec_len[r];        // a window must not run past its record
+      n_var = P.n_var;
+    }
+  }
+  dp_emit_hits_warp(A, hit, g, r, pattern_of[slot], score, n_var);
+}
+
+// Appends the alive windows of word w (bit b = window 32w+b) of pattern `slot` to the warp's
+// queue q (n entries held, n < 32 on entry) and verifies a batch when 32 are there.  Called by
+// all lanes of the warp together; returns the new n.
+static __device__ __noinline__ uint32_t dp_queue_push(const dp_scan_args& A, const dp_pattern* pats, const uint8_t* pattern_of,
+                                               unsigned long long* q, uint32_t n, uint32_t alive, uint64_t w,
+                                               uint32_t slot, unsigned long long& n_cand) {
+  const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+  while (__any_sync(0xFFFFFFFFu, alive != 0u)) {
+    bool mine = false;
+    unsigned long long e = 0ull;
+    if (alive) {
+      const int b = __ffs(alive) - 1;
+      alive &= alive - 1u;
+      ++n_cand;
+      const uint64_t g = w * 32 + b;
+      if (g >= A.seg_begin && g < A.seg_end) { mine = true; e = (g << 8) | slot; }
+    }
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, mine);
+    if (mine) q[n + __popc(m & below)] = e;
+    n += __popc(m);
+    __syncwarp();
+    if (n >= 32u) {
+      dp_verify_warp(A, pats, pattern_of, q[lane], true);
+      __syncwarp();
+      const unsigned long long moved = lane + 32u < n ? q[lane + 32u] : 0ull;
+      __syncwarp();
+      if (lane + 32u < n) q[lane] = moved;
+      n -= 32u;
+      __syncwarp();
+    }
+  }
+  return n;
 }
 
 // ---- bit-sliced population count of N one-bit planes ----------------------------

@@ -28,8 +28,18 @@ __device__ __forceinline__ double f64_mul(double a, double b) { return __dmul_rn
 // s: seq1 letters (5'->3'), s_len; r: seq2 reversed = 3'->5' letters, r_len;
 // mask: matched seq1 indices; off: Dimer.offset.  Returns NaN where the
 // reference would raise (a table key that does not exist).
-__device__ double dp_dimer_dg_device(const dp_dg_args& A, const uint8_t* s, int s_len,
-                                     const uint8_t* r, int r_len, uint64_t mask, int off) {
+// The two strands are anything indexable: byte arrays, or dp_seq_planes (a variant kept as two
+// 64-bit planes in registers).
+struct dp_seq_planes {
+  uint64_t hi, lo;
+  __device__ __forceinline__ uint32_t operator[](int i) const {
+    return (uint32_t)((hi >> i) & 1ull) * 2u + (uint32_t)((lo >> i) & 1ull);
+  }
+};
+
+template <typename SeqS, typename SeqR>
+__device__ double dp_dimer_dg_device(const dp_dg_args& A, const SeqS& s, int s_len,
+                                     const SeqR& r, int r_len, uint64_t mask, int off) {
   const dp_nn_tables& T = *A.T;
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
   if (!mask) return nan;
@@ -150,7 +160,7 @@ struct dp_duplex_args {
   const uint32_t* exc;
   const dp_exc_run* runs;
   uint64_t n_runs;
-  const dp_raw_hit* hits;
+  dp_raw_hit* hits;             // .reserved receives the number of dimers of the hit
   uint64_t hits_cap;
   const uint8_t* codes;
   uint64_t* dir;
@@ -162,16 +172,14 @@ struct dp_duplex_args {
 
 #define DP_DUPLEX_WARPS 4
 #define DP_DUPLEX_THREADS (32 * DP_DUPLEX_WARPS)
-#define DP_DUPLEX_LIST 128     // survivors one warp can rank in shared memory
+#define DP_LANE_LIST 16        // survivors one lane keeps in shared memory (>= 5 mismatch runs overflow)
 
-// per-warp scratch: the two strands of the duplex, its run table, surviving dimers
+// per-warp scratch: the window's complement strand and every lane's list of surviving dimers
+// ([entry][lane]: a lane's accesses stay in its own bank)
 struct dp_duplex_scratch {
-  uint8_t s[DP_WIN];
   uint8_t r[DP_WIN];
-  uint8_t run_start[32];
-  uint8_t run_end[32];
-  double kdg[DP_DUPLEX_LIST];
-  uint64_t kmask[DP_DUPLEX_LIST];
+  double kdg[DP_LANE_LIST * 32];
+  uint64_t kmask[DP_LANE_LIST * 32];
 };
 
 // d-th dimer of [full, alternatives...] in the reference's construction order
@@ -192,18 +200,44 @@ __device__ __forceinline__ uint64_t dp_nth_dimer(uint64_t M, int n, uint32_t d, 
   return M & lo_m & hi_m;
 }
 
-// One WARP per (hit, variant) pair: lanes read the window letters in parallel,
-// a ballot gives the match mask, then lane d evaluates the d-th dimer, the
-// survivors are ranked by dG (stable) in shared memory and written to one
-// atomically reserved output range.  Latency of a small call is one dimer
-// evaluation, not the sum over sites.
+// Calls f(sub) for every dimer of [full, alternatives...] of match mask M, in that construction
+// order, walking the run boundaries with bit tricks (no run table).
+template <typename F>
+__device__ __forceinline__ void dp_for_each_dimer(uint64_t M, F&& f) {
+  f(M);
+  const uint64_t S = M & ~(M << 1);                      // first index of every run
+  const uint64_t E = M & ~(M >> 1);                      // last index of every run
+  const int n = __popcll(S);
+  uint64_t Sl = S;
+  for (int l = 0; l + 1 < n; ++l) {
+    const int start_l = __ffsll((long long)Sl) - 1;
+    Sl &= Sl - 1ull;
+    const int start_l1 = __ffsll((long long)Sl) - 1;
+    const uint64_t lo_m = ~0ull << start_l;
+    uint64_t Er = E & ~(1ull << (63 - __clzll((long long)E)));      // ends of runs 0..n-2
+    for (int r = n - 1; r > l; --r) {                     // runs [l, r): ends with run r-1
+      const int e = 63 - __clzll((long long)Er);
+      Er &= ~(1ull << e);
+      f(M & lo_m & ((2ull << e) - 1ull));
+    }
+    f(M & (~0ull << start_l1));                           // runs [l+1, n)
+  }
+}
+
+// One WARP per hit, one LANE per variant (SecStructures.py:294-324 for every Duplex of the site):
+// the window is decoded once into two 64-bit planes + the complement strand in shared memory; a
+// lane builds its variant's planes from the code bytes, gets the match mask with four 64-bit
+// logic ops, walks [full, alternatives...] in the reference's order, evaluates each dimer's dG
+// and keeps the survivors sorted by dG (stable insertion) in its column of shared memory.  One
+// atomic per 32 variants reserves the output range; a directory entry offset << 16 | count per
+// (hit, variant) lets host or device reassemble them in order.  No search for the hit of a pair,
+// no re-decoding of the window per variant, all 32 lanes busy for degenerate primers.
 __global__ void __launch_bounds__(DP_DUPLEX_THREADS)
 dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant__ dp_dg_plan plan) {
   const unsigned long long packed = A.counters[DP_C_HITS];
   const uint64_t n_hits = (uint32_t)packed;
-  const uint64_t n_pairs = packed >> 32;
   if (n_hits > A.hits_cap) return;                       // the host grows the buffer and rescans
-  if ((uint64_t)blockIdx.x * DP_DUPLEX_WARPS >= n_pairs) return;
+  if ((uint64_t)blockIdx.x * DP_DUPLEX_WARPS >= n_hits) return;
   __shared__ dp_nn_tables sT;                            // 10 KB: NN tables next to the lanes
   __shared__ dp_duplex_scratch sW[DP_DUPLEX_WARPS];
   {
@@ -215,144 +249,130 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
   dp_dg_args G = A.dg;
   G.T = &sT;
   const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t lt_mask = (1u << lane) - 1u;
   dp_duplex_scratch& W = sW[threadIdx.x >> 5];
+  double* const kdg = W.kdg + lane;
+  uint64_t* const kmask = W.kmask + lane;
   unsigned long long n_tried = 0;
   const uint64_t n_warps = (uint64_t)gridDim.x * DP_DUPLEX_WARPS;
-  for (uint64_t pair = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); pair < n_pairs; pair += n_warps) {
-    // hit of this pair: last slot whose pair_base <= pair (monotone in slot); 32-ary search
-    uint64_t lo = 0, hi = n_hits;
-    while (hi - lo > 1) {
-      const uint64_t step = (hi - lo + 31) / 32;
-      const uint64_t idx = lo + (uint64_t)(lane + 1) * step;
-      const bool ok = idx < hi && (uint64_t)A.hits[idx].pair_base <= pair;
-      const uint32_t c = __popc(__ballot_sync(0xFFFFFFFFu, ok));
-      lo += (uint64_t)c * step;
-      hi = min(hi, lo + step);
-    }
-    const dp_raw_hit hit = A.hits[lo];
-    const uint32_t v = (uint32_t)(pair - hit.pair_base);
+  for (uint64_t hi_ = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); hi_ < n_hits; hi_ += n_warps) {
+    const dp_raw_hit hit = A.hits[hi_];
     const int L = plan.pat_len[hit.pattern];
     const int strand = plan.pat_strand[hit.pattern];
     const uint32_t primer = plan.pat_primer[hit.pattern];
-    const uint8_t* vc = A.codes + plan.var_off[primer] + (uint64_t)v * L;
-    // the two strands: s = variant, r = complement(window) (3'->5'), match = plain equality
-    uint64_t M = 0;
+    const uint32_t V = plan.var_count[primer];
+    const uint8_t* codes = A.codes + plan.var_off[primer];
+    // the window as the reference's strand string shows it: two planes for its ACGT letters,
+    // W.r = its complement strand (3'->5') as letter indices (IUPAC letters included)
+    uint64_t whi = 0, wlo = 0, wbase = 0;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       const int i = (int)lane + 32 * half;
-      bool match = false;
+      uint32_t w = 15u;
       if (i < L) {
         const uint64_t g = hit.g + (strand ? (uint64_t)(L - 1 - i) : (uint64_t)i);
-        uint32_t w = dp_letter_at(A.lo, A.hi, A.exc, A.runs, A.n_runs, g);
+        w = dp_letter_at(A.lo, A.hi, A.exc, A.runs, A.n_runs, g);
         if (strand) w = dp_letter_complement(w);
-        const uint8_t sv = vc[i];
-        W.s[i] = sv;
         W.r[i] = (uint8_t)dp_letter_complement(w);
-        match = (w == sv);
       }
-      M |= (uint64_t)__ballot_sync(0xFFFFFFFFu, match) << (32 * half);
-    }
-    if (!M) {                                            // no dimer at all
-      if (lane == 0 && pair < A.dir_cap) A.dir[pair] = 0;
-      __syncwarp();
-      continue;
-    }
-    const uint64_t S = M & ~(M << 1);                    // first index of every run
-    const uint64_t Eb = M & ~(M >> 1);                   // last index of every run
-    const int n = __popcll(S);
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      const int i = (int)lane + 32 * half;
-      const uint64_t below = (1ull << i) - 1ull;
-      if ((S >> i) & 1ull) W.run_start[__popcll(S & below)] = (uint8_t)i;
-      if ((Eb >> i) & 1ull) W.run_end[__popcll(Eb & below)] = (uint8_t)i;
+      whi |= (uint64_t)__ballot_sync(0xFFFFFFFFu, w < 4u && (w & 2u)) << (32 * half);
+      wlo |= (uint64_t)__ballot_sync(0xFFFFFFFFu, w < 4u && (w & 1u)) << (32 * half);
+      wbase |= (uint64_t)__ballot_sync(0xFFFFFFFFu, w < 4u) << (32 * half);
     }
     __syncwarp();
-    const uint32_t n_dimers = (uint32_t)(n * (n + 1) / 2);
-    uint32_t kept = 0;
-    for (uint32_t base = 0; base < n_dimers; base += 32) {
-      const uint32_t d = base + lane;
-      bool keep = false;
-      uint64_t sub = 0;
-      double dG = 0.0;
-      if (d < n_dimers) {
-        sub = dp_nth_dimer(M, n, d, W.run_start, W.run_end);
-        dG = dp_dimer_dg_device(G, W.s, L, W.r, L, sub, 0);
-        keep = !(dG > G.max_dimer_dG) && (dG <= G.max_dG_for_K);   // SecStructures.py:302-304
-      }
-      const uint32_t kb = __ballot_sync(0xFFFFFFFFu, keep);
-      const uint32_t pos = kept + __popc(kb & lt_mask);
-      if (keep && pos < DP_DUPLEX_LIST) { W.kdg[pos] = dG; W.kmask[pos] = sub; }
-      kept += __popc(kb);
-    }
-    if (lane == 0) n_tried += n_dimers;
-    __syncwarp();
-    uint64_t off = 0;
-    if (kept) {
-      if (lane == 0) off = atomicAdd(&A.counters[DP_C_DIMERS], (unsigned long long)kept);
-      off = __shfl_sync(0xFFFFFFFFu, off, 0);
-      if (off + kept <= A.out_cap) {
-        if (kept <= DP_DUPLEX_LIST) {
-          // the list is in construction order; rank = stable position by dG
-          for (uint32_t e = lane; e < kept; e += 32) {
-            const double x = W.kdg[e];
-            uint32_t rank = 0;
-            for (uint32_t f = 0; f < kept; ++f) {
-              const double y = W.kdg[f];
-              rank += (y < x || (y == x && f < e)) ? 1u : 0u;
+    uint32_t hit_dimers = 0;
+    for (uint32_t v0 = 0; v0 < V; v0 += 32) {
+      const uint32_t v = v0 + lane;
+      uint32_t kept = 0;
+      uint64_t M = 0;
+      dp_seq_planes sv;
+      sv.hi = sv.lo = 0;
+      if (v < V) {
+        const uint8_t* vc = codes + (uint64_t)v * L;
+        for (int i = 0; i < L; ++i) {
+          const uint32_t c = vc[i];
+          sv.hi |= (uint64_t)(c >> 1) << i;
+          sv.lo |= (uint64_t)(c & 1u) << i;
+        }
+        M = ~(sv.hi ^ whi) & ~(sv.lo ^ wlo) & wbase;     // plain equality of letters
+        if (M) {
+          dp_for_each_dimer(M, [&](uint64_t sub) {
+            const double dG = dp_dimer_dg_device(G, sv, L, W.r, L, sub, 0);
+            ++n_tried;
+            if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;        // SecStructures.py:302-304
+            if (kept < DP_LANE_LIST) {
+              // stable insertion by dG: behind every entry that is not larger
+              uint32_t pos = kept;
+              while (pos > 0 && kdg[32 * (pos - 1)] > dG) {
+                kdg[32 * pos] = kdg[32 * (pos - 1)];
+                kmask[32 * pos] = kmask[32 * (pos - 1)];
+                --pos;
+              }
+              kdg[32 * pos] = dG;
+              kmask[32 * pos] = sub;
             }
-            A.out[off + rank].match_mask = W.kmask[e];
-            A.out[off + rank].dG = x;
-          }
-        } else if (lane == 0) {
-          // more survivors than the list holds (>= 16 mismatch runs): one lane re-runs
-          // the enumeration and inserts straight into the reserved range
-          dp_raw_dimer* dst = A.out + off;
-          uint32_t m = 0;
-          for (uint32_t d = 0; d < n_dimers; ++d) {
-            const uint64_t sub = dp_nth_dimer(M, n, d, W.run_start, W.run_end);
-            const double dG = dp_dimer_dg_device(G, W.s, L, W.r, L, sub, 0);
-            if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) continue;
-            uint32_t pos = m;
-            while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
-            dst[pos].match_mask = sub;
-            dst[pos].dG = dG;
-            ++m;
-          }
+            ++kept;
+          });
         }
       }
+      // output range of these 32 variants: one atomic, offsets by prefix sum
+      uint32_t incl = kept;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t x = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= (uint32_t)o) incl += x;
+      }
+      const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+      hit_dimers += total;
+      unsigned long long base = 0;
+      if (total) {
+        if (lane == 0) base = atomicAdd(&A.counters[DP_C_DIMERS], (unsigned long long)total);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+      }
+      if (v < V) {
+        const uint64_t off = base + (incl - kept);
+        if (kept && off + kept <= A.out_cap) {
+          dp_raw_dimer* dst = A.out + off;
+          if (kept <= DP_LANE_LIST) {
+            for (uint32_t e = 0; e < kept; ++e) {
+              dst[e].match_mask = kmask[32 * e];
+              dst[e].dG = kdg[32 * e];
+            }
+          } else {
+            // more survivors than the list holds: enumerate again, insert straight into the range
+            uint32_t m = 0;
+            dp_for_each_dimer(M, [&](uint64_t sub) {
+              const double dG = dp_dimer_dg_device(G, sv, L, W.r, L, sub, 0);
+              if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;
+              uint32_t pos = m;
+              while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
+              dst[pos].match_mask = sub;
+              dst[pos].dG = dG;
+              ++m;
+            });
+          }
+        }
+        const uint64_t pair = (uint64_t)hit.pair_base + v;
+        if (pair < A.dir_cap) A.dir[pair] = kept ? (off << 16) | (uint64_t)kept : 0ull;
+      }
+      __syncwarp();
     }
-    if (lane == 0 && pair < A.dir_cap) A.dir[pair] = (off << 16) | (uint64_t)kept;
-    __syncwarp();                                        // scratch is reused by the next pair
+    if (lane == 0) A.hits[hi_].reserved = hit_dimers;
+    __syncwarp();                                        // W.r is rewritten for the next hit
   }
-  if (n_tried) atomicAdd(&A.counters[DP_C_TRIED], n_tried);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n_tried += __shfl_xor_sync(0xFFFFFFFFu, n_tried, o);
+  if (lane == 0 && n_tried) atomicAdd(&A.counters[DP_C_TRIED], n_tried);
 }
 
 // ---- large results: final dp_dimer records are laid out by the device -----------------
-// (a) dimers per hit slot, (b) after the host has sorted the hits and turned the
-// counts into output offsets: every pair's dimers copied to their final place with
-// (hit rank, variant) filled in.  One warp per hit slot, lanes over variants.
+// The duplex kernel leaves the dimers per hit slot in the hit records; after the host has
+// sorted the hits and turned the counts into output offsets, every pair's dimers are copied to
+// their final place with (hit rank, variant) filled in.  One warp per hit slot, lanes over variants.
 struct dp_slot_info {
   uint64_t final_off;   // first output record of this hit
   uint32_t rank;        // index of the hit in the sorted hit list
-  uint32_t count;       // in: dimers of the hit (written by the count kernel)
+  uint32_t count;       // dimers of the hit
 };
-
-__global__ void __launch_bounds__(128)
-dp_hit_count_kernel(const dp_raw_hit* __restrict__ hits, uint64_t n_hits, const uint64_t* __restrict__ dir,
-                    const __grid_constant__ dp_dg_plan plan, dp_slot_info* __restrict__ info) {
-  const uint64_t slot = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const uint32_t lane = threadIdx.x & 31u;
-  if (slot >= n_hits) return;
-  const dp_raw_hit h = hits[slot];
-  const uint32_t V = plan.var_count[plan.pat_primer[h.pattern]];
-  uint32_t c = 0;
-  for (uint32_t v = lane; v < V; v += 32) c += (uint32_t)(dir[(uint64_t)h.pair_base + v] & 0xFFFFu);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
-  if (lane == 0) info[slot].count = c;
-}
 
 __global__ void __launch_bounds__(128)
 dp_dimer_gather_kernel(const dp_raw_hit* __restrict__ hits, uint64_t n_hits, const uint64_t* __restrict__ dir,
@@ -389,15 +409,6 @@ dp_dimer_gather_kernel(const dp_raw_hit* __restrict__ hits, uint64_t n_hits, con
   }
 }
 
-int dp_dg_hit_counts(dp_ctx* ctx, const dp_dg_plan& plan, uint64_t n_hits, void* d_info) {
-  if (!n_hits) return DP_OK;
-  const uint64_t threads = n_hits * 32;
-  dp_hit_count_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, ctx->stream>>>(
-      ctx->d_hits, n_hits, ctx->d_dir, plan, (dp_slot_info*)d_info);
-  DP_CUDA(ctx, cudaGetLastError());
-  return DP_OK;
-}
-
 int dp_dg_gather(dp_ctx* ctx, const dp_dg_plan& plan, uint64_t n_hits, const void* d_info, dp_dimer* d_out) {
   if (!n_hits) return DP_OK;
   const uint64_t threads = n_hits * 32;
@@ -427,7 +438,7 @@ int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint
   A.counters = ctx->d_counters;
   // pair count unknown on the host (fused call): a persistent grid, most blocks
   // leave at once when there are few pairs
-  uint64_t blocks = (uint64_t)ctx->sm_count * 8;
+  uint64_t blocks = (uint64_t)ctx->sm_count * 5;           // 43 KB of shared memory per block: 5 fit an SM
   if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS);
   dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, 0, ctx->stream>>>(A, L.plan);
   DP_CUDA(ctx, cudaGetLastError());

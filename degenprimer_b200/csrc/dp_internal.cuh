@@ -199,6 +199,7 @@ int dp_upload_and_pack(dp_ctx* ctx, dp_template* t, uint32_t n_records,
 // host memory of result arrays handed to the caller (released with dp_free)
 void* dp_result_alloc(size_t bytes);
 void dp_result_free(void* p);
+bool dp_result_is_pinned(const void* p);     // big blocks are page-locked: D2H copies go straight in
 
 // stream-ordered allocation from the context's pool (no cudaMalloc on hot calls)
 cudaError_t dp_pool_alloc(dp_ctx* ctx, void** p, size_t bytes);
@@ -238,8 +239,8 @@ struct dp_dg_launch {
   double PCR_T, Na_eq_log, max_dimer_dG, max_dG_for_K;
 };
 int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches);
-// large results: per-hit dimer counts into d_info[slot].count, then the gather of every
-// pair's dimers to d_info[slot].final_off with (rank, variant) filled in (dp_dg.cu)
+// large results: the duplex kernel leaves the number of dimers of every hit in the hit record
+// (dp_raw_hit.reserved); the gather copies every pair's dimers to d_info[slot].final_off with
+// (rank, variant) filled in (dp_dg.cu)
 struct dp_slot_info_host { uint64_t final_off; uint32_t rank; uint32_t count; };
-int dp_dg_hit_counts(dp_ctx* ctx, const dp_dg_plan& plan, uint64_t n_hits, void* d_info);
 int dp_dg_gather(dp_ctx* ctx, const dp_dg_plan& plan, uint64_t n_hits, const void* d_info, dp_dimer* d_out);

@@ -130,7 +130,7 @@ dp_jit_kernel* dp_jit_lookup(const std::string& source) {
   return it == g_jit_kernels.end() ? nullptr : it->second;
 }
 
-int dp_jit_compile(dp_ctx* ctx, const std::string& source, dp_jit_kernel** out) {
+int dp_jit_compile(dp_ctx* ctx, const std::string& source, int threads, dp_jit_kernel** out) {
   *out = nullptr;
   {
     std::lock_guard<std::mutex> lock(g_jit_mutex);
@@ -145,6 +145,7 @@ int dp_jit_compile(dp_ctx* ctx, const std::string& source, dp_jit_kernel** out) 
   k->fn = nullptr;
   k->per_sm = 0;
   k->regs = 0;
+  k->threads = threads;
   std::string cubin = nvrtc_compile(source, k->log);
   if (!cubin.empty()) {
     cudaError_t e = cudaLibraryLoadData(&k->lib, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
@@ -157,10 +158,10 @@ int dp_jit_compile(dp_ctx* ctx, const std::string& source, dp_jit_kernel** out) 
       cudaFuncAttributes attr;
       if (cudaFuncGetAttributes(&attr, (const void*)k->fn) == cudaSuccess) k->regs = attr.numRegs;
       int per_sm = 0;
-      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k->fn, DP_JIT_THREADS, 0) == cudaSuccess && per_sm > 0)
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k->fn, threads, 0) == cudaSuccess && per_sm > 0)
         k->per_sm = per_sm;
       else
-        k->per_sm = k->regs ? std::max(1, std::min(8, 65536 / (k->regs * DP_JIT_THREADS))) : 4;
+        k->per_sm = k->regs ? std::max(1, std::min(8, 65536 / (k->regs * threads))) : 4;
       cudaGetLastError();
     }
   }
@@ -182,13 +183,27 @@ int dp_jit_compile(dp_ctx* ctx, const std::string& source, dp_jit_kernel** out) 
 // All offsets are window positions: bit b of the thread's word w is the window that
 // starts at base 32w+b, position j of it sits at bit b of the text shifted right by j.
 //
-// Two prefilters, chosen per pattern by instruction count (both are necessary
-// conditions for a hit, K = hard mismatches a hit can have):
-//   EXACT  K+1 disjoint sets of positions; a hit matches at least one set completely
-//          (pigeonhole).  A set is an AND chain, one LOP3 per position:
-//          acc = acc & f(h_j, l_j).  ~9 positions per set keep the verify rate low.
-//   ADDER  the generic kernel's anchor: J = 8+2K positions, bit-sliced count >= J-K
-//          (one LOP3 per plane + ~1.8 per adder input).
+// The prefilter of a pattern (K = hard mismatches a hit can have) is a GROUP COUNT: some
+// of its positions are dealt into G disjoint groups; a group matches iff every one of its
+// positions matches.  K mismatches spoil at most K groups, so a hit has at least G-K
+// matching groups -- a necessary condition, evaluated for 32 windows at once:
+//   group i   = AND of the match planes of its positions
+//   alive     = [number of matching groups >= G-K]   (carry-save adders + a small comparator)
+// G = K+1 is the pigeonhole filter (alive = OR of the groups), groups of one position are the
+// plain mismatch count; in between lies the cheapest form for K >= 2: e.g. L = 18, K = 3 ->
+// 6 groups of 3 positions, alive = "at least 3 of 6" = 12 LOP3 per pattern and 32 windows
+// against 14 planes + a 14-input adder (~42) for the anchor count.  The generator picks G and
+// the positions per pattern by estimated instruction count (hot path + expected verify work).
+//
+// Match planes: the plane of (position j, letter set S) is one LOP3 of the two shifted code
+// words (h_j, l_j).  With many patterns (a multiplex) every plane that is used is computed
+// ONCE per word and kept in a register ("shared planes"): a group of three positions is then
+// a single 3-input AND.  With few patterns the planes are folded into the AND chain
+// (acc &= f(h_j, l_j): one LOP3 per position, nothing kept).
+//
+// Alive windows are not verified where they are found: they go to a per-warp queue and are
+// verified 32 at a time (dp_queue_push / dp_verify_warp in dp_device.cuh).
+//
 // The integer pipe (LOP3/SHF, 16 lanes per SM sub-partition and clock) is what bounds
 // this kernel.  Moving the funnel shifts to the FMA pipe as multiply-adds
 // (hi32(h0 * 2^(32-j)) + lo32(hn * 2^(32-j)), multiplier from a kernel parameter so that
@@ -212,141 +227,220 @@ static std::string plane_expr(uint32_t set, const std::string& h, const std::str
 
 static double set_fraction(uint32_t set) { return __builtin_popcount(set & 15u) / 4.0; }
 
-// expected instructions per word spent in the out-of-line verify for a prefilter that
-// lets a random window through with probability p
-static double cold_cost(double p) {
-  const double any = 1.0 - pow(1.0 - std::min(p, 0.5), 1024.0);   // some lane of the warp, some bit of its word
-  return 250.0 * any;
-}
-
-// EXACT: K+1 disjoint position sets within the first `span` positions.  Returns the
-// estimated instructions per word (sets + verify), or a negative number if infeasible.
-static double choose_exact(const std::vector<uint8_t>& lt, int K, int span, std::vector<std::vector<int>>& sets) {
-  const int L = std::min<int>((int)lt.size(), span);
-  std::vector<int> order;
-  for (int j = 0; j < L; ++j)
-    if (set_fraction(dp_letter_set(lt[j])) < 1.0) order.push_back(j);
-  std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
-    return set_fraction(dp_letter_set(lt[x])) < set_fraction(dp_letter_set(lt[y]));
-  });
-  double best = -1.0;
-  std::vector<std::vector<int>> best_sets;
-  // deal the most selective positions round-robin; try every common depth
-  for (int depth = 6; depth * (K + 1) <= (int)order.size() && depth <= 12; ++depth) {
-    std::vector<std::vector<int>> g(K + 1);
-    for (int i = 0; i < depth * (K + 1); ++i) g[i % (K + 1)].push_back(order[i]);
-    double p = 0.0;
-    for (auto& v : g) {
-      double q = 1.0;
-      for (int j : v) q *= set_fraction(dp_letter_set(lt[j]));
-      p += q;
-    }
-    const double cost = depth * (K + 1) + K + cold_cost(p);
-    if (best < 0 || cost < best) {
-      best = cost;
-      best_sets = g;
-    }
-  }
-  if (best >= 0) {
-    for (auto& v : best_sets) std::sort(v.begin(), v.end());
-    sets = best_sets;
-  }
-  return best;
-}
-
-static double adder_cost(const std::vector<uint8_t>& lt, const dp_jit_entry& e) {
-  const int J = 8 + 2 * e.K;
-  // alive probability as in dp_bitslice_make_plan
-  std::vector<double> d(e.K + 2, 0.0);
-  d[0] = 1.0;
-  for (int j = 0; j < J; ++j) {
-    const double pm = set_fraction(dp_letter_set(lt[e.anchor + j]));
-    for (int m = e.K + 1; m >= 0; --m) {
-      double stay = m == e.K + 1 ? d[m] : d[m] * pm;
-      double from = m > 0 ? d[m - 1] * (1.0 - pm) : 0.0;
-      d[m] = stay + from;
-    }
-  }
-  double p = 0.0;
-  for (int m = 0; m <= e.K; ++m) p += d[m];
-  return 2.8 * J + 5.0 + cold_cost(p);
-}
-
-struct unit_pattern {
-  dp_jit_entry e;
-  bool exact;
-  std::vector<std::vector<int>> sets;     // EXACT
-};
-
 static int jit_env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return v && *v ? atoi(v) : dflt;
 }
 
+// expected instructions per word and pattern spent on alive windows: the warp-wide vote and
+// queue push when any of the warp's 1024 windows is alive, plus the batched verify per candidate
+static double cold_cost(double p) {
+  const double any = 1.0 - pow(1.0 - std::min(p, 0.5), 1024.0);
+  return 30.0 * any + 1024.0 * p * 14.0;
+}
+
+// Emits the threshold function [x_0 + ... + x_{n-1} >= T] over one-bit planes as C statements.
+// Full adders reduce three planes of one weight to a sum and a carry; with the sums W and the
+// carries C of one level,  [sum >= T] = OR_j ([C-count >= j] & [W-count >= T - 2j]), which
+// recurses on two shorter lists.  Unused sums are dead code for the compiler.
+struct thr_emitter {
+  std::string code, indent, prefix;
+  int n_tmp = 0, ops = 0;
+  std::map<std::string, std::string> memo;
+
+  std::string tmp(const std::string& expr, int cost = 1) {
+    auto it = memo.find(expr);
+    if (it != memo.end()) return it->second;
+    const std::string name = prefix + std::to_string(n_tmp++);
+    code += indent + "const uint32_t " + name + " = " + expr + ";\n";
+    ops += cost;
+    memo[expr] = name;
+    return name;
+  }
+  static std::string join(const std::vector<std::string>& x, const char* op) {
+    std::string s = "(";
+    for (size_t i = 0; i < x.size(); ++i) s += (i ? std::string(" ") + op + " " : std::string()) + x[i];
+    return s + ")";
+  }
+  std::string ge(const std::vector<std::string>& x, int T) {
+    const int n = (int)x.size();
+    if (T <= 0) return "0xffffffffu";
+    if (T > n) return "0u";
+    if (n == 1) return x[0];
+    if (T == 1) return tmp(join(x, "|"), n / 2);
+    if (T == n) return tmp(join(x, "&"), n / 2);
+    if (n == 3) return tmp("((" + x[0] + " & " + x[1] + ") | (" + x[2] + " & (" + x[0] + " | " + x[1] + ")))");
+    std::vector<std::string> W, C;
+    for (int i = 0; i + 3 <= n; i += 3) {
+      const std::string &a = x[i], &b = x[i + 1], &c = x[i + 2];
+      W.push_back(tmp("(" + a + " ^ " + b + " ^ " + c + ")"));
+      C.push_back(tmp("((" + a + " & " + b + ") | (" + c + " & (" + a + " | " + b + ")))"));
+    }
+    for (int i = n - n % 3; i < n; ++i) W.push_back(x[i]);
+    std::vector<std::string> terms;
+    for (int j = 0; j <= (int)C.size(); ++j) {
+      const int t1 = T - 2 * j;
+      if (t1 > (int)W.size()) continue;
+      const std::string cj = ge(C, j);
+      if (cj == "0u") break;
+      if (t1 <= 0) { terms.push_back(cj); break; }            // larger j are implied by this term
+      const std::string wj = ge(W, t1);
+      if (wj == "0u") continue;
+      terms.push_back(cj == "0xffffffffu" ? wj : "(" + cj + " & " + wj + ")");
+    }
+    if (terms.empty()) return "0u";
+    if (terms.size() == 1 && terms[0][0] != '(') return terms[0];
+    return tmp(join(terms, "|"), (int)terms.size());
+  }
+};
+
+// P(at least `need` of the independent events q[] happen)
+static double tail_probability(const std::vector<double>& q, int need) {
+  std::vector<double> d(q.size() + 1, 0.0);
+  d[0] = 1.0;
+  for (size_t i = 0; i < q.size(); ++i)
+    for (size_t m = i + 1; m-- > 0;) {
+      d[m + 1] += d[m] * q[i];
+      d[m] *= 1.0 - q[i];
+    }
+  double s = 0.0;
+  for (size_t m = (size_t)std::max(0, need); m < d.size(); ++m) s += d[m];
+  return s;
+}
+
+struct unit_pattern {
+  dp_jit_entry e;
+  std::vector<std::vector<int>> groups;     // window positions of every group
+  double p_alive;
+};
+
+// Chooses the groups of one pattern.  shared: planes come from registers (a group of d positions
+// costs (d-1)/2 rounded up three-input ANDs), else one LOP3 per position.
+static bool choose_groups(const std::vector<uint8_t>& lt, int K, bool shared, unit_pattern& out) {
+  std::vector<int> order;
+  for (int j = 0; j < (int)lt.size() && j < 64; ++j)
+    if (set_fraction(dp_letter_set(lt[j])) < 1.0) order.push_back(j);
+  std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
+    return set_fraction(dp_letter_set(lt[x])) < set_fraction(dp_letter_set(lt[y]));
+  });
+  const int n_avail = (int)order.size();
+  double best = -1.0;
+  for (int G = K + 1; G <= std::min(n_avail, 16); ++G) {
+    thr_emitter dry;
+    std::vector<std::string> names;
+    for (int i = 0; i < G; ++i) names.push_back("g" + std::to_string(i));
+    dry.ge(names, G - K);
+    for (int n_use = G; n_use <= n_avail; ++n_use) {
+      std::vector<std::vector<int>> g(G);
+      for (int i = 0; i < n_use; ++i) g[i % G].push_back(order[i]);
+      std::vector<double> q;
+      double hot = dry.ops;
+      for (auto& v : g) {
+        double x = 1.0;
+        for (int j : v) x *= set_fraction(dp_letter_set(lt[j]));
+        q.push_back(x);
+        hot += shared ? (double)(v.size() / 2) : (double)v.size();
+      }
+      const double p = tail_probability(q, G - K);
+      const double cost = hot + cold_cost(p);
+      if (best < 0 || cost < best - 1e-9) {
+        best = cost;
+        out.groups = g;
+        out.p_alive = p;
+      }
+    }
+  }
+  if (best < 0) return false;
+  for (auto& v : out.groups) std::sort(v.begin(), v.end());
+  return out.p_alive <= 0.02;           // a filter that lets more through is not worth a launch
+}
+
+static std::string plane_name(int j, uint32_t set) { return "p" + std::to_string(j) + "_" + std::to_string(set & 15u); }
+
+static int jit_threads() {
+  const int t = jit_env_int("DEGENPRIMER_B200_JIT_THREADS", DP_JIT_THREADS);
+  return (t == 64 || t == 128 || t == 256 || t == 512) ? t : DP_JIT_THREADS;
+}
+
 static std::string unit_source(const std::vector<dp_pattern>& pats, const std::vector<std::vector<uint8_t>>& letters,
                                const std::vector<dp_jit_entry>& entries) {
-  const int use_exact = jit_env_int("DEGENPRIMER_B200_JIT_EXACT", 1);
+  (void)pats;
+  const int shared_from = jit_env_int("DEGENPRIMER_B200_JIT_SHARED_FROM", 12);
+  const bool shared = (int)entries.size() >= shared_from;
   std::vector<unit_pattern> ups;
   bool used[64] = {false};
+  std::map<std::string, std::pair<int, uint32_t>> planes;       // shared planes by name
   for (const dp_jit_entry& e : entries) {
     unit_pattern u;
     u.e = e;
-    u.exact = false;
+    u.p_alive = 1.0;
     const std::vector<uint8_t>& lt = letters[e.pattern];
-    if (use_exact) {
-      std::vector<std::vector<int>> sets;
-      const double ce = choose_exact(lt, e.K, 24, sets);
-      if (ce >= 0 && ce < adder_cost(lt, e)) {
-        u.exact = true;
-        u.sets = sets;
+    if (!choose_groups(lt, e.K, shared, u)) {
+      // cannot happen for patterns the plan accepted (they have a selective anchor); keep the
+      // kernel correct anyway: one group per position of the anchor
+      u.groups.clear();
+      for (int j = 0; j < 8 + 2 * e.K; ++j) u.groups.push_back(std::vector<int>(1, (int)e.anchor + j));
+    }
+    for (auto& v : u.groups)
+      for (int j : v) {
+        used[j] = true;
+        if (shared) planes[plane_name(j, dp_letter_set(lt[j]))] = std::make_pair(j, dp_letter_set(lt[j]));
       }
-    }
-    if (u.exact) {
-      for (auto& v : u.sets)
-        for (int j : v) used[j] = true;
-    } else {
-      for (int j = 0; j < 8 + 2 * e.K; ++j) used[e.anchor + j] = true;
-    }
     ups.push_back(u);
   }
   int max_off = 0;
   for (int j = 1; j < 64; ++j)
     if (used[j]) max_off = j;
   const bool three = max_off >= 32;        // positions 32..63 need the third word
+  const int min_blocks = jit_env_int("DEGENPRIMER_B200_JIT_MIN_BLOCKS", shared ? 1 : 3);
 
   std::string s;
-  s.reserve(4096 + 1024 * entries.size());
+  s.reserve(8192 + 1024 * entries.size());
+  // the plan, readable by dp_jit_describe and by whoever looks at the source
+  for (const unit_pattern& u : ups) {
+    char head[96];
+    snprintf(head, sizeof head, "//PLAN pattern %u K %d need %d p_alive %.3g groups", u.e.pattern, u.e.K,
+             (int)u.groups.size() - u.e.K, u.p_alive);
+    s += head;
+    for (auto& v : u.groups) {
+      s += " ";
+      for (size_t t = 0; t < v.size(); ++t) s += (t ? "," : "") + std::to_string(v[t]);
+    }
+    s += "\n";
+  }
+  s += std::string("//PLAN mode ") + (shared ? "shared-planes" : "folded-planes") + "\n";
   s += "#include \"dp_device.cuh\"\n";
   s += "static_assert(sizeof(dp_pattern) == " + std::to_string(sizeof(dp_pattern)) + ", \"dp_pattern layout\");\n";
   s += "static_assert(sizeof(dp_scan_args) == " + std::to_string(sizeof(dp_scan_args)) + ", \"dp_scan_args layout\");\n";
   s += "static_assert(sizeof(dp_raw_hit) == " + std::to_string(sizeof(dp_raw_hit)) + ", \"dp_raw_hit layout\");\n";
   s += "#define NP " + std::to_string(entries.size()) + "\n";
-  // cold path, kept out of line so that the word loop stays small
-  s += "__device__ __noinline__ void dp_jit_alive(const dp_scan_args& A, const dp_pattern* pats, uint32_t slot,\n"
-       "                                          uint32_t pattern, uint32_t alive, uint64_t w,\n"
-       "                                          unsigned long long& n_cand) {\n"
-       "  while (alive) {\n"
-       "    const int b = __ffs(alive) - 1;\n"
-       "    alive &= alive - 1;\n"
-       "    ++n_cand;\n"
-       "    const uint64_t g = w * 32 + b;\n"
-       "    if (g < A.seg_begin || g >= A.seg_end) continue;\n"
-       "    dp_verify_window(A, pats[slot], g, pattern, false);\n"
-       "  }\n"
-       "}\n";
-  s += "extern \"C\" __global__ void __launch_bounds__(" + std::to_string(DP_JIT_THREADS) + ", 3)\n"
+  s += "#define NT " + std::to_string(jit_threads()) + "\n";
+  s += "__device__ const uint8_t dp_jit_pattern_of[NP] = {";
+  for (size_t i = 0; i < ups.size(); ++i) s += (i ? ", " : "") + std::to_string(ups[i].e.pattern);
+  s += "};\n";
+  s += "extern \"C\" __global__ void __launch_bounds__(NT, " + std::to_string(min_blocks) + ")\n"
        "dp_jit_scan(const __grid_constant__ dp_scan_args A, const __grid_constant__ dp_pattern_set<NP> PS) {\n"
-       "  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;\n"
+       "  // patterns and the candidate queues of the block's warps\n"
+       "  __shared__ dp_pattern s_pat[NP];\n"
+       "  __shared__ unsigned long long s_queue[NT / 32][DP_Q_CAP];\n"
+       "  for (uint32_t i = threadIdx.x; i < NP * (uint32_t)(sizeof(dp_pattern) / 4); i += NT)\n"
+       "    reinterpret_cast<uint32_t*>(s_pat)[i] = reinterpret_cast<const uint32_t*>(PS.pat)[i];\n"
+       "  __syncthreads();\n"
+       "  unsigned long long* const q = s_queue[threadIdx.x >> 5];\n"
+       "  uint32_t qn = 0;\n"
+       "  const uint64_t stride = (uint64_t)gridDim.x * NT;\n"
        "  const uint64_t w_end = A.word_end;\n"
        "  unsigned long long n_cand = 0;\n"
-       "  uint64_t w = A.word_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;\n"
+       "  uint64_t w = A.word_begin + (uint64_t)blockIdx.x * NT + threadIdx.x;\n"
        "  uint32_t h0 = 0, hn = 0, hm = 0, l0 = 0, ln = 0, lm = 0;\n"
        "  if (w < w_end) {\n"
        "    h0 = __ldg(A.hi + w); hn = __ldg(A.hi + w + 1);\n"
        "    l0 = __ldg(A.lo + w); ln = __ldg(A.lo + w + 1);\n";
   if (three) s += "    hm = __ldg(A.hi + w + 2); lm = __ldg(A.lo + w + 2);\n";
   s += "  }\n"
-       "  while (w < w_end) {\n"
+       "  // the loop is uniform over the warp (its first lane decides): the queue is warp-collective\n"
+       "  while (w - (threadIdx.x & 31u) < w_end) {\n"
+       "    const uint32_t live = w < w_end ? 0xffffffffu : 0u;\n"
        "    const uint64_t wn = w + stride;\n"
        "    uint32_t ph0 = 0, phn = 0, phm = 0, pl0 = 0, pln = 0, plm = 0;\n"
        "    if (wn < w_end) {\n"
@@ -363,10 +457,15 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
     }
     const std::string x0 = j < 32 ? "0" : "n", x1 = j < 32 ? "n" : "m";
     const int sh = j & 31;
-      s += "    const uint32_t h" + n + " = __funnelshift_r(h" + x0 + ", h" + x1 + ", " + std::to_string(sh) + "), l" + n +
-           " = __funnelshift_r(l" + x0 + ", l" + x1 + ", " + std::to_string(sh) + ");\n";
+    s += "    const uint32_t h" + n + " = __funnelshift_r(h" + x0 + ", h" + x1 + ", " + std::to_string(sh) + "), l" + n +
+         " = __funnelshift_r(l" + x0 + ", l" + x1 + ", " + std::to_string(sh) + ");\n";
   }
-  // patterns in chunks of 8: one branch per chunk on the hot path
+  if (shared)
+    for (auto& kv : planes) {
+      const std::string n = std::to_string(kv.second.first);
+      s += "    const uint32_t " + kv.first + " = " + plane_expr(kv.second.second, "h" + n, "l" + n) + ";\n";
+    }
+  // patterns in chunks of 8: one vote + branch per chunk on the hot path
   for (size_t c0 = 0; c0 < ups.size(); c0 += 8) {
     const size_t c1 = std::min(ups.size(), c0 + 8);
     s += "    {\n";
@@ -374,59 +473,47 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
       const unit_pattern& u = ups[i];
       const std::vector<uint8_t>& lt = letters[u.e.pattern];
       const std::string v = "alive" + std::to_string(i);
-      if (u.exact) {
-        s += "      uint32_t " + v + ";\n      {\n";
-        for (size_t g = 0; g < u.sets.size(); ++g) {
-          const std::string acc = "e" + std::to_string(g);
+      s += "      uint32_t " + v + ";\n      {\n";
+      std::vector<std::string> gnames;
+      for (size_t g = 0; g < u.groups.size(); ++g) {
+        const std::string acc = "g" + std::to_string(g);
+        gnames.push_back(acc);
+        if (shared) {
+          std::string e;
+          for (size_t t = 0; t < u.groups[g].size(); ++t) {
+            const int j = u.groups[g][t];
+            e += (t ? " & " : "") + plane_name(j, dp_letter_set(lt[j]));
+          }
+          s += "        const uint32_t " + acc + " = " + e + ";\n";
+        } else {
           bool first = true;
-          for (int j : u.sets[g]) {
+          for (int j : u.groups[g]) {
             const std::string n = std::to_string(j);
             const std::string pe = plane_expr(dp_letter_set(lt[j]), "h" + n, "l" + n);
             s += first ? "        uint32_t " + acc + " = " + pe + ";\n" : "        " + acc + " &= " + pe + ";\n";
             first = false;
           }
         }
-        s += "        " + v + " = e0";
-        for (size_t g = 1; g < u.sets.size(); ++g) s += " | e" + std::to_string(g);
-        s += ";\n      }\n";
-      } else {
-        const int J = 8 + 2 * u.e.K, THR = J - u.e.K;
-        // fresh names for the shifted words behind an empty asm: keeps the compiler from
-        // computing every plane of every pattern up front and holding them in registers
-        s += "      uint32_t " + v + ";\n      {\n        uint32_t";
-        for (int j = 0; j < J; ++j) {
-          const std::string n = std::to_string(j), o = std::to_string(u.e.anchor + j);
-          s += (j ? ", a" : " a") + n + " = h" + o + ", b" + n + " = l" + o;
-        }
-        s += ";\n";
-        for (int j0 = 0; j0 < J; j0 += 8) {
-          s += "        asm volatile(\"\" :";
-          for (int j = j0; j < std::min(J, j0 + 8); ++j) {
-            const std::string n = std::to_string(j);
-            s += (j > j0 ? ", \"+r\"(a" : " \"+r\"(a") + n + "), \"+r\"(b" + n + ")";
-          }
-          s += ");\n";
-        }
-        s += "        const uint32_t x[" + std::to_string(J) + "] = {";
-        for (int j = 0; j < J; ++j) {
-          const std::string n = std::to_string(j);
-          s += (j ? ", " : "") + plane_expr(dp_letter_set(lt[u.e.anchor + j]), "a" + n, "b" + n);
-        }
-        s += "};\n";
-        s += "        " + v + " = dp_count_ge<" + std::to_string(J) + ", " + std::to_string(THR) + ">(x);\n      }\n";
       }
+      thr_emitter em;
+      em.indent = "        ";
+      em.prefix = "t";
+      const std::string res = em.ge(gnames, (int)u.groups.size() - u.e.K);
+      s += em.code;
+      s += "        " + v + " = " + res + " & live;\n      }\n";
     }
-    s += "      if (alive" + std::to_string(c0);
+    s += "      if (__any_sync(0xffffffffu, (alive" + std::to_string(c0);
     for (size_t i = c0 + 1; i < c1; ++i) s += " | alive" + std::to_string(i);
-    s += ") {\n";
+    s += ") != 0u)) {\n";
     for (size_t i = c0; i < c1; ++i)
-      s += "        if (alive" + std::to_string(i) + ") dp_jit_alive(A, PS.pat, " + std::to_string(i) + "u, " +
-           std::to_string(ups[i].e.pattern) + "u, alive" + std::to_string(i) + ", w, n_cand);\n";
+      s += "        if (__any_sync(0xffffffffu, alive" + std::to_string(i) + " != 0u)) qn = dp_queue_push(A, s_pat, dp_jit_pattern_of, q, qn, alive" +
+           std::to_string(i) + ", w, " + std::to_string(i) + "u, n_cand);\n";
     s += "      }\n    }\n";
   }
   s += "    w = wn;\n"
        "    h0 = ph0; hn = phn; hm = phm; l0 = pl0; ln = pln; lm = plm;\n"
        "  }\n"
+       "  if (qn) dp_verify_warp(A, s_pat, dp_jit_pattern_of, q[threadIdx.x & 31u], (threadIdx.x & 31u) < qn);\n"
        "  if (n_cand) atomicAdd(&A.counters[DP_C_CAND], n_cand);\n"
        "}\n";
   return s;
@@ -442,6 +529,7 @@ void dp_jit_make_units(const std::vector<dp_pattern>& pats, const std::vector<st
     std::vector<dp_jit_entry> part(entries.begin() + at, entries.begin() + std::min(entries.size(), at + per));
     dp_jit_unit u;
     u.source = unit_source(pats, letters, part);
+    u.threads = jit_threads();
     for (const dp_jit_entry& e : part) u.patterns.push_back(e.pattern);
     u.kernel = nullptr;
     units.push_back(u);
@@ -454,9 +542,9 @@ int dp_jit_launch(dp_ctx* ctx, const dp_scan_args& A, const std::vector<dp_patte
   set.resize(unit.patterns.size());
   for (size_t i = 0; i < unit.patterns.size(); ++i) set[i] = pats[unit.patterns[i]];
   const uint64_t words = A.word_end - A.word_begin;
-  const unsigned blocks = (unsigned)std::min<uint64_t>((words + DP_JIT_THREADS - 1) / DP_JIT_THREADS,
-                                                       (uint64_t)ctx->sm_count * unit.kernel->per_sm);
+  const uint64_t nt = (uint64_t)unit.kernel->threads;
+  const unsigned blocks = (unsigned)std::min<uint64_t>((words + nt - 1) / nt, (uint64_t)ctx->sm_count * unit.kernel->per_sm);
   void* args[] = {(void*)&A, (void*)set.data()};
-  DP_CUDA(ctx, cudaLaunchKernel((const void*)unit.kernel->fn, dim3(blocks), dim3(DP_JIT_THREADS), args, 0, ctx->stream));
+  DP_CUDA(ctx, cudaLaunchKernel((const void*)unit.kernel->fn, dim3(blocks), dim3((unsigned)nt), args, 0, ctx->stream));
   return DP_OK;
 }

@@ -5,8 +5,7 @@
 
 #include "dp_scan.cuh"
 
-#define DP_JIT_THREADS 256
-#define DP_JIT_AUTO_MAX_PATTERNS 16 // DP_ALGO_AUTO: larger sets stay on the generic kernel
+#define DP_JIT_THREADS 256         // default block size; DEGENPRIMER_B200_JIT_THREADS overrides (tuning)
 #define DP_JIT_MAX_PATTERNS 48     // per launch: bounds code size and the parameter block
 
 struct dp_jit_kernel {
@@ -14,6 +13,7 @@ struct dp_jit_kernel {
   cudaKernel_t fn;       // null: the compile failed, `log` says why
   int per_sm;            // resident CTAs per SM
   int regs;
+  int threads;           // block size the source was generated for
   std::string log;
 };
 
@@ -29,6 +29,7 @@ struct dp_jit_entry {
 struct dp_jit_unit {
   std::string source;
   std::vector<uint32_t> patterns;
+  int threads;               // block size (NT of the source)
   dp_jit_kernel* kernel;     // null until compiled / found in the cache
 };
 
@@ -37,5 +38,5 @@ void dp_jit_make_units(const std::vector<dp_pattern>& pats, const std::vector<st
                        const std::vector<dp_jit_entry>& entries, std::vector<dp_jit_unit>& units);
 std::string dp_jit_compile_only(const std::string& source, std::string& log);
 dp_jit_kernel* dp_jit_lookup(const std::string& source);
-int dp_jit_compile(dp_ctx* ctx, const std::string& source, dp_jit_kernel** out);
+int dp_jit_compile(dp_ctx* ctx, const std::string& source, int threads, dp_jit_kernel** out);
 int dp_jit_launch(dp_ctx* ctx, const dp_scan_args& A, const std::vector<dp_pattern>& pats, const dp_jit_unit& unit);

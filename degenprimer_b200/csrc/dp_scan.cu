@@ -397,7 +397,7 @@ static int jit_attach(dp_ctx* ctx, dp_scan_job& J, bool compile) {
   for (dp_jit_unit& u : J.core->jit) {
     if (!u.kernel || !u.kernel->fn) {
       if (compile) {
-        int rc = dp_jit_compile(ctx, u.source, &u.kernel);
+        int rc = dp_jit_compile(ctx, u.source, u.threads, &u.kernel);
         if (rc) {
           J.jit_ready = false;
           return rc;
@@ -434,10 +434,7 @@ static int job_build(dp_ctx* ctx, uint32_t n_primers, const char* const* masters
     for (const dp_bitslice_group& g : J.core->plan.groups)
       for (const dp_bs_pattern& bp : g.pats) entries.push_back(dp_jit_entry{bp.pattern, bp.anchor, g.K});
     std::sort(entries.begin(), entries.end(), [](const dp_jit_entry& a, const dp_jit_entry& b) { return a.pattern < b.pattern; });
-    // with many patterns the generic kernel wins: it fetches a term's plane with an LDS,
-    // the specialised one computes it with a LOP3 on the integer pipe that bounds both
-    // (20-plex, K = 3: 13.7 ms against 15.3 ms), so AUTO leaves those to the generic kernel
-    if (algo == DP_ALGO_JIT || entries.size() <= DP_JIT_AUTO_MAX_PATTERNS) {
+    {
       dp_jit_make_units(J.core->pats, J.core->letters, entries, J.core->jit);
       rc = jit_attach(ctx, J, compile || algo == DP_ALGO_JIT);
       if (rc) return rc;
@@ -746,15 +743,29 @@ static int hits_to_abi(dp_ctx* ctx, const dp_template* t, const dp_scan_job& J, 
     tmp[i].score3 = (uint8_t)h.score3;
   }
   std::vector<uint32_t> order(n);
-  for (uint64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
-  std::sort(order.begin(), order.end(), [&tmp](uint32_t x, uint32_t y) {
-    const dp_hit& a = tmp[x];
-    const dp_hit& b = tmp[y];
-    if (a.primer != b.primer) return a.primer < b.primer;
-    if (a.strand != b.strand) return a.strand < b.strand;
-    if (a.record != b.record) return a.record < b.record;
-    return a.pos < b.pos;
-  });
+  bool packable = true;                // (primer, strand, record, pos) fits one 64-bit key
+  for (uint64_t i = 0; i < n && packable; ++i)
+    packable = tmp[i].primer < 64 && tmp[i].record < (1u << 17) && tmp[i].pos < (1ull << 39);
+  if (packable) {
+    struct keyed { uint64_t key; uint32_t idx; };
+    std::vector<keyed> ks(n);
+    for (uint64_t i = 0; i < n; ++i) {
+      ks[i].key = ((uint64_t)tmp[i].primer << 57) | ((uint64_t)tmp[i].strand << 56) | ((uint64_t)tmp[i].record << 39) | tmp[i].pos;
+      ks[i].idx = (uint32_t)i;
+    }
+    std::sort(ks.begin(), ks.end(), [](const keyed& a, const keyed& b) { return a.key < b.key; });
+    for (uint64_t i = 0; i < n; ++i) order[i] = ks[i].idx;
+  } else {
+    for (uint64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+    std::sort(order.begin(), order.end(), [&tmp](uint32_t x, uint32_t y) {
+      const dp_hit& a = tmp[x];
+      const dp_hit& b = tmp[y];
+      if (a.primer != b.primer) return a.primer < b.primer;
+      if (a.strand != b.strand) return a.strand < b.strand;
+      if (a.record != b.record) return a.record < b.record;
+      return a.pos < b.pos;
+    });
+  }
   for (uint64_t i = 0; i < n; ++i) out[i] = tmp[order[i]];
   *out_p = out;
   if (order_p) order_p->swap(order);
@@ -794,37 +805,44 @@ static int dimers_to_abi(dp_ctx* ctx, const dp_host_results& R, const dp_sizes& 
   return DP_OK;
 }
 
-// Large results: the device counts the dimers of every hit, the host turns the counts
-// into output offsets in sorted-hit order, the device writes final dp_dimer records,
-// one copy brings them back.  order[i] = raw slot of output hit i.
+// Large results: the duplex kernel left the number of dimers of every hit in the raw hit
+// records; the host turns them into output offsets in sorted-hit order, the device writes final
+// dp_dimer records, ONE copy brings them back -- straight into the (page-locked, recycled) block
+// that is handed to the caller.  order[i] = raw slot of output hit i; raw = the raw hits on the
+// host (null: fetched here).
 static int dimers_large(dp_ctx* ctx, const dp_dg_plan& plan, const std::vector<uint32_t>& order, const dp_sizes& S,
-                        dp_dimer** out_p, uint64_t* n_out_p) {
+                        const dp_raw_hit* raw, dp_dimer** out_p, uint64_t* n_out_p) {
   const uint64_t n = order.size();
   cudaStream_t st = ctx->stream;
+  std::vector<dp_raw_hit> fetched;
+  if (!raw) {
+    fetched.resize(n);
+    DP_CUDA(ctx, cudaMemcpyAsync(fetched.data(), ctx->d_hits, n * sizeof(dp_raw_hit), cudaMemcpyDeviceToHost, st));
+    DP_CUDA(ctx, cudaStreamSynchronize(st));
+    raw = fetched.data();
+  }
+  // `raw` usually points into the pinned staging area that is reused (and may be re-allocated)
+  // below: read it first
+  std::vector<dp_slot_info_host> info(n);
+  uint64_t run = 0;
+  for (uint64_t i = 0; i < n; ++i) {
+    dp_slot_info_host& x = info[order[i]];
+    x.count = raw[order[i]].reserved;
+    x.final_off = run;
+    x.rank = (uint32_t)i;
+    run += x.count;
+  }
+  if (run != S.n_dimers)
+    return dp_set_error(ctx, DP_ERR_STATE, "internal: per-hit dimer counts (%llu) disagree with the total (%llu)",
+                        (unsigned long long)run, (unsigned long long)S.n_dimers);
+  int rc = dp_ws_pinned(ctx, n * sizeof(dp_slot_info_host));
+  if (rc) return rc;
+  dp_slot_info_host* h = (dp_slot_info_host*)ctx->h_res;
+  memcpy(h, info.data(), n * sizeof(dp_slot_info_host));
   void* d_info = nullptr;
   dp_dimer* d_final = nullptr;
-  DP_CUDA(ctx, dp_pool_alloc(ctx, &d_info, n * sizeof(dp_slot_info_host)));
-  int rc = dp_dg_hit_counts(ctx, plan, n, d_info);
-  if (rc == DP_OK) rc = dp_ws_pinned(ctx, n * sizeof(dp_slot_info_host));
-  if (rc) { dp_pool_free(ctx, d_info); return rc; }
-  dp_slot_info_host* h = (dp_slot_info_host*)ctx->h_res;
-  cudaError_t e = cudaMemcpyAsync(h, d_info, n * sizeof(dp_slot_info_host), cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  uint64_t run = 0;
-  if (e == cudaSuccess) {
-    for (uint64_t i = 0; i < n; ++i) {
-      dp_slot_info_host& x = h[order[i]];
-      x.final_off = run;
-      x.rank = (uint32_t)i;
-      run += x.count;
-    }
-    if (run != S.n_dimers) {
-      dp_pool_free(ctx, d_info);
-      return dp_set_error(ctx, DP_ERR_STATE, "internal: per-hit dimer counts (%llu) disagree with the total (%llu)",
-                          (unsigned long long)run, (unsigned long long)S.n_dimers);
-    }
-    e = cudaMemcpyAsync(d_info, h, n * sizeof(dp_slot_info_host), cudaMemcpyHostToDevice, st);
-  }
+  DP_CUDA(ctx, dp_pool_alloc(ctx, &d_info, std::max<uint64_t>(1, n) * sizeof(dp_slot_info_host)));
+  cudaError_t e = cudaMemcpyAsync(d_info, h, n * sizeof(dp_slot_info_host), cudaMemcpyHostToDevice, st);
   if (e == cudaSuccess) e = dp_pool_alloc(ctx, (void**)&d_final, std::max<uint64_t>(1, run) * sizeof(dp_dimer));
   dp_dimer* out = nullptr;
   if (e == cudaSuccess) {
@@ -834,13 +852,8 @@ static int dimers_large(dp_ctx* ctx, const dp_dg_plan& plan, const std::vector<u
       if (!out) rc = dp_set_error(ctx, DP_ERR_NOMEM, "out of host memory for %llu dimers", (unsigned long long)run);
     }
     const size_t bytes = run * sizeof(dp_dimer);
-    if (rc == DP_OK && run && bytes <= (256u << 20)) {
-      // through pinned memory at PCIe speed, then one host memcpy into the (recycled) block
-      rc = dp_ws_pinned(ctx, bytes);
-      if (rc == DP_OK) e = cudaMemcpyAsync(ctx->h_res, d_final, bytes, cudaMemcpyDeviceToHost, st);
-      if (rc == DP_OK && e == cudaSuccess) e = cudaStreamSynchronize(st);
-      if (rc == DP_OK && e == cudaSuccess) memcpy(out, ctx->h_res, bytes);
-    } else if (rc == DP_OK && run) {
+    if (rc == DP_OK && run) {
+      // the caller's block is page-locked when it is big (dp_result_alloc): DMA straight into it
       e = cudaMemcpyAsync(out, d_final, bytes, cudaMemcpyDeviceToHost, st);
       if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     }
@@ -1137,7 +1150,7 @@ extern "C" int dp_find_end(dp_ctx* ctx, dp_hit** hits_out, uint64_t* n_hits_out,
   const dp_hit* hits = *hits_out;
   const std::vector<uint32_t>& vc = F.var_count;
   if (results_are_large(true, S))
-    rc = dimers_large(ctx, F.DL.plan, order, S, dimers_out, n_dimers_out);
+    rc = dimers_large(ctx, F.DL.plan, order, S, R.hits, dimers_out, n_dimers_out);
   else
     rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return vc[hits[i].primer]; }, dimers_out, n_dimers_out);
   if (rc) { dp_result_free(*hits_out); *hits_out = nullptr; *n_hits_out = 0; return rc; }
@@ -1199,7 +1212,7 @@ extern "C" int dp_find_again(dp_ctx* ctx, const dp_conditions* cond, dp_dimer** 
   const std::vector<uint16_t>& primer_of = F.primer_of;
   const std::vector<uint32_t>& vc = F.var_count;
   if (results_are_large(true, S))
-    rc = dimers_large(ctx, F.DL.plan, F.order, S, dimers_out, n_dimers_out);
+    rc = dimers_large(ctx, F.DL.plan, F.order, S, R.hits, dimers_out, n_dimers_out);
   else
     rc = dimers_to_abi(ctx, R, S, F.order, [&](size_t i) { return vc[primer_of[i]]; }, dimers_out, n_dimers_out);
   if (rc) return rc;
@@ -1279,6 +1292,38 @@ extern "C" int dp_jit_selftest(uint32_t n_primers, const char* const* masters, c
       if (f) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
     }
   }
+  return (int)J.core->jit.size();
+}
+
+// The prefilter plan of a primer set as text (one "//PLAN" line per pattern: K, groups needed,
+// estimated alive probability, the window positions of every group).  No device needed.
+extern "C" int dp_jit_describe(uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
+                               int strand_mask, char* out, uint64_t capacity) {
+  if (!masters || !out || !capacity) return DP_ERR_ARG;
+  out[0] = 0;
+  dp_scan_job J;
+  J.core = std::make_shared<dp_job_core>();
+  int rc = build_patterns(nullptr, n_primers, masters, max_mismatches, strand_mask, nullptr, J.core->pats, J.core->letters);
+  if (rc) return rc;
+  if (!dp_bitslice_make_plan(J.core->pats, J.core->letters, J.core->plan)) return 0;
+  std::vector<dp_jit_entry> entries;
+  for (const dp_bitslice_group& g : J.core->plan.groups)
+    for (const dp_bs_pattern& bp : g.pats) entries.push_back(dp_jit_entry{bp.pattern, bp.anchor, g.K});
+  std::sort(entries.begin(), entries.end(), [](const dp_jit_entry& a, const dp_jit_entry& b) { return a.pattern < b.pattern; });
+  dp_jit_make_units(J.core->pats, J.core->letters, entries, J.core->jit);
+  std::string text;
+  for (const dp_jit_unit& u : J.core->jit) {
+    size_t at = 0;
+    while (at < u.source.size()) {
+      size_t eol = u.source.find('\n', at);
+      if (eol == std::string::npos) eol = u.source.size();
+      if (u.source.compare(at, 6, "//PLAN") == 0) text += u.source.substr(at, eol - at) + "\n";
+      else break;
+      at = eol + 1;
+    }
+  }
+  if (text.size() + 1 > capacity) return dp_set_error(nullptr, DP_ERR_ARG, "dp_jit_describe: %zu bytes needed", text.size() + 1);
+  memcpy(out, text.c_str(), text.size() + 1);
   return (int)J.core->jit.size();
 }
 
@@ -1393,7 +1438,7 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
   std::vector<uint32_t> order(n_hits);
   for (uint64_t i = 0; i < n_hits; ++i) order[i] = (uint32_t)i;
   if (results_are_large(true, S)) {
-    rc = dimers_large(ctx, DL.plan, order, S, dimers_out, n_dimers_out);
+    rc = dimers_large(ctx, DL.plan, order, S, nullptr, dimers_out, n_dimers_out);
   } else {
     // small: directory + dimers already sit in the published prefix; the raw hits are
     // still in the pinned staging area behind it

@@ -215,6 +215,14 @@ int dp_scan_prepare_kernels(dp_ctx* ctx, uint32_t n_primers, const char* const* 
 int dp_jit_selftest(uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
                     int strand_mask, const char* source_path, const char* cubin_path);
 
+/* The prefilter plan of the specialised kernel of a primer set, as text: one line
+ *   //PLAN pattern <i> K <k> need <t> p_alive <p> groups <j,j,..> <j,j,..> ...
+ * per (primer, strand) pattern (window positions of every group; a hit has at least `need`
+ * groups that match completely), then "//PLAN mode ...".  Host-only (tests, documentation).
+ * Returns the number of launch units or a negative DP_ERR code. */
+int dp_jit_describe(uint32_t n_primers, const char* const* masters, const int32_t* max_mismatches,
+                    int strand_mask, char* out, uint64_t capacity);
+
 /* seg_begin/seg_end restrict window STARTS to [seg_begin, seg_end) of the
  * padded concatenation (multi-GPU sharding); pass 0, UINT64_MAX for
  * everything.  `stats` may be NULL. */

@@ -164,7 +164,7 @@ def test_search_engine_surface():
 def test_specialised_scan_kernel_compiles_without_a_device(native_lib, tmp_path):
     """dp_jit_selftest: source generation + NVRTC compile of the run-time specialised scan
     kernel (sm_100a) for a plain pair, a degenerate pair and a 20-plex; the source has one
-    block per (primer, strand) pattern and no shared memory."""
+    group-count prefilter per (primer, strand) pattern, feeding the warp's candidate queue."""
     lib = ctypes.CDLL(native_lib)
     lib.dp_last_error.restype = ctypes.c_char_p
     from degenprimer_b200.synthetic import TP53_F, TP53_R, P27F_D128, P1492R_D128, multiplex_primers
@@ -177,8 +177,8 @@ def test_specialised_scan_kernel_compiles_without_a_device(native_lib, tmp_path)
             pytest.skip('NVRTC is not installed here')
         assert rc == units, lib.dp_last_error(None)
         text = open(src).read()
-        assert text.count('dp_jit_alive(A, PS.pat') == 2 * len(masters)      # one prefilter per (primer, strand)
-        assert ('dp_count_ge<' in text) == (k == 3)                          # K <= 1: exact position sets, else adders
-        assert '__shared__' not in text
+        assert text.count('qn = dp_queue_push(A, s_pat') == 2 * len(masters)   # one prefilter per (primer, strand)
+        assert text.count('//PLAN pattern') == 2 * len(masters)
+        assert ('shared-planes' in text) == (len(masters) == 20)               # a multiplex keeps its match planes in registers
     bad = (ctypes.c_char_p * 1)(b'ACGTZ')
     assert lib.dp_jit_selftest(1, bad, (ctypes.c_int32 * 1)(0), 3, None, None) < 0

@@ -54,8 +54,7 @@ def main():
     tdf.PCR_P.set(COND)
     ctx = tdf._ctx()
     cond = tdf.conditions()
-    host = [torch.from_numpy(r).pin_memory() for r in wl['records']]
-    srcs = [(h.data_ptr(), h.numel()) for h in host]
+    srcs = [(r.ctypes.data, len(r)) for r in wl['records']]
     t0 = time.perf_counter()
     tmpl = ctx.template_from_sequences(srcs)
     t_up = time.perf_counter() - t0
