@@ -697,12 +697,14 @@ def run_ours(args):
             'note': 'canonical = 16 int32 ops incl. 2 POPC per window (SURVEY 8d); the bit-sliced prefilter issues '
                     'far fewer, so a fraction above 1 means "faster than the per-window popcount roof"',
         }
-        if entry and entry.get('warp_inst_per_word') and ms_main > 0:
-            # instructions actually issued (ncu smsp__inst_executed.sum of the committed capture, per plane
-            # word scanned) x 32 lanes against the calibrated LOP3 rate
-            words = shard_bp / 32.0
-            introof['warp_inst_per_word'] = entry['warp_inst_per_word']
-            introof['frac_issued'] = entry['warp_inst_per_word'] * words * 32.0 / (ms_main * 1e-3) / lop3
+        if entry and entry.get('warp_inst_per_bp') and ms_main > 0:
+            # instructions actually issued (ncu smsp__inst_executed.sum of the committed capture, per
+            # template base) x 32 lanes / this run's kernel time, against the LOP3 rate calibrated in this run;
+            # every instruction counts, so a kernel that sits on the ALU pipe reads close to (or a little
+            # above) 1: its few non-ALU instructions issue on other pipes
+            introof['warp_inst_per_launch'] = entry['warp_inst_per_bp'] * shard_bp
+            introof['frac_issued'] = entry['warp_inst_per_bp'] * shard_bp * 32.0 / (ms_main * 1e-3) / lop3
+            introof['alu_pipe_pct_ncu'] = entry.get('alu_pipe_pct')
             introof['frac_issued_source'] = entry.get('source')
         return roof, introof
 
