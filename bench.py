@@ -65,7 +65,7 @@ def parse_args():
     ap.add_argument('--parity-mbp', type=float, default=50.0)
     ap.add_argument('--cpu-repeats', type=int, default=2)
     ap.add_argument('--host-threads', type=int, default=2, help='host threads that queue and collect the calls')
-    ap.add_argument('--in-flight', type=int, default=2,
+    ap.add_argument('--in-flight', type=int, default=4,
                     help='calls in flight on the GPU (one context per call); 1 = strictly sequential')
     return ap.parse_args()
 
@@ -575,7 +575,7 @@ def run_ours(args):
         latency and kernel durations that no other lane's kernels stretch)."""
         queries = [c.prepare(p.primers, p.k, p.var_lists, jit=not args.no_jit) for c in lanes]
         n_threads = max(1, min(args.host_threads, n_lanes))
-        timed_region(queries, max(W, 2 * n_lanes), n_lanes, n_threads)
+        timed_region(queries, max(W, 3 * n_lanes), n_lanes, n_threads)     # every lane: workspaces, page-locked result blocks
         elapsed, wall, acc = timed_region(queries, K, n_lanes, n_threads)
         ks = max(3, min(K, 10))
         seq_elapsed, _w, seq = timed_region(queries, ks, 1, 1)
@@ -587,7 +587,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     main = measure(plan, K, W)
-    ns = measure(ns_plan, max(3, min(K, 10)), 3) if ns_plan is not None else None
+    ns = measure(ns_plan, K, W) if ns_plan is not None else None
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- parity, outside the timed regions ----------------------------------------------------

@@ -5,17 +5,34 @@ Same constructor and method names, argument order and return values (paths of sa
 when aborted or when nothing was found); the reference's Manager wrappers (:144-168) are not needed — there
 is no process fan-out to coordinate, the GPU grid is the fan-out.
 """
+import numpy as np
+
+from . import TD_Functions as tdf
+from . import _native as nat
 from .PCR_Mixture import MixtureFactory
-from .SearchEngine import SearchEngine
+from .SearchEngine import SearchEngine, StrandView, _primers_query, resident
 from .SeqUtils import pretty_rec_name
 from .WorkCounter import WorkCounter
 from .tmpStorage import cleanup_files, from_shelf
+
+
+class ResidentMatches(list):
+    """What `find_matches` returns: the reference's list of 7-tuples, one per primer
+    (DegenPrimer/PCR_ProductsFinder.py:83-92), plus a handle on the same hits still sitting in HBM on a
+    context of their own.  `matches_to_mixture` re-evaluates them there under the conditions of the
+    moment (dp_find_again) — the optimiser calls it once per trial point
+    (DegenPrimer/PCR_Optimizer.py:162-214) — instead of uploading the positions again per primer and step."""
+
+    def __init__(self, tuples, state):
+        list.__init__(self, tuples)
+        self._state = state          # dict(ctx, tmpl, rec, template, hits, var_lists, name_lists) or None
 
 
 class PCR_ProductsFinder(MixtureFactory):
     def __init__(self, abort_event, *args, **kwargs):
         MixtureFactory.__init__(self, abort_event, *args, **kwargs)
         self._searcher = SearchEngine(self._abort_event)
+        self._resident_ctx = None
         self._p_weights = [p.num_components for p in self._primers]
         self._pw_sum = sum(self._p_weights)
         self._num_p = len(self._primers)
@@ -45,7 +62,70 @@ class PCR_ProductsFinder(MixtureFactory):
         return cls._pool(from_shelf(path) for path in paths)
 
     def find_matches(self, counter, template, mismatches):
-        """Scan only: one 7-tuple per primer (:83-92)."""
+        """Scan only: one 7-tuple per primer (:83-92).  All primers are ONE device pass; the hits stay
+        resident for `matches_to_mixture` (ResidentMatches)."""
+        if isinstance(self._searcher, SearchEngine):
+            return self._find_matches_resident(counter, template, mismatches)
+        return self._find_matches_per_primer(counter, template, mismatches)
+
+    def _find_matches_resident(self, counter, template, mismatches):
+        for primer in self._primers:
+            self._searcher._check_length_inequality(len(template), len(primer))
+        counter.set_work(self._pw_sum)
+        if self.aborted():
+            return None
+        tmpl, rec = resident(template)
+        if self._resident_ctx is None or self._resident_ctx.device != tmpl.ctx.device:
+            self._resident_ctx = tdf.new_context(tmpl.ctx.device)     # nobody else's calls drop these hits
+        ctx = self._resident_ctx
+        query, var_lists, name_lists = _primers_query(ctx, self._primers, int(mismatches), self._searcher._jit)
+        begin = tmpl.starts[rec]
+        end = begin + ((tmpl.lengths[rec] + 31) // 32) * 32
+        if tmpl.n_records == 1:
+            begin, end = 0, 2 ** 64 - 1
+        with tdf.AcquireParameters():
+            cond = tdf.conditions()
+        try:
+            hits, _dimers, st, dst = ctx.find(tmpl, query, cond=cond, seg_begin=begin, seg_end=end)
+        except nat.Aborted:
+            return None
+        self._searcher.last_stats['scan'], self._searcher.last_stats['dg'] = st, dst
+        if self.aborted():
+            return None
+        counter.done()
+        t_len = len(template)
+        text = getattr(tmpl, 'host_text', None)
+        fwd_seq, rev_seq = StrandView(tmpl, rec, False, text), StrandView(tmpl, rec, True)
+        tuples = []
+        for i, primer in enumerate(self._primers):
+            h = hits[(hits['primer'] == i) & (hits['record'] == rec)]
+            tuples.append((fwd_seq, rev_seq, primer, t_len, len(primer),
+                           h['pos'][h['strand'] == 0].astype(np.int64), h['pos'][h['strand'] == 1].astype(np.int64)))
+        return ResidentMatches(tuples, dict(ctx=ctx, tmpl=tmpl, rec=rec, template=template, hits=hits,
+                                            var_lists=var_lists, name_lists=name_lists))
+
+    def _matches_to_annealings_resident(self, matches_list):
+        """(fwd, rev) annealing lists of every primer from the resident hits, or None when they are gone
+        (another search used the context, the template was closed): the caller then goes per primer."""
+        st = getattr(matches_list, '_state', None)
+        if st is None or len(matches_list) != self._num_p:
+            return None
+        with tdf.AcquireParameters():
+            cond = tdf.conditions()
+            T = tdf.PCR_P.PCR_T
+        try:
+            dimers, dst = st['ctx'].find_again(cond)
+        except nat.NativeError as e:
+            if e.code != nat.DP_ERR_STATE:
+                raise
+            matches_list._state = None
+            return None
+        self._searcher.last_stats['dg'] = dst
+        found = SearchEngine._split_results(st['tmpl'], [st['template']], [st['rec']], self._primers, st['hits'],
+                                            dimers, st['var_lists'], st['name_lists'], T)
+        return found[st['template'].id]          # one entry per primer; None = no stable duplex for that primer
+
+    def _find_matches_per_primer(self, counter, template, mismatches):
         all_matches = []
         counter.set_subwork(self._num_p, self._p_weights)
         for i, primer in enumerate(self._primers):
@@ -58,10 +138,20 @@ class PCR_ProductsFinder(MixtureFactory):
         return all_matches
 
     def matches_to_mixture(self, counter, tname, matches_list):
-        """Duplex stage + pairing for matches found earlier — the optimiser's inner loop (:67-81)."""
+        """Duplex stage + pairing for matches found earlier — the optimiser's inner loop (:67-81).  Matches
+        that came from `find_matches` are re-evaluated where they are, on the device (dp_find_again)."""
         all_annealings = []
         weights = [len(m) for m in matches_list]
         counter.set_subwork(len(matches_list) + 1, weights + [0.01 * sum(weights)])
+        if self.aborted():
+            return None
+        resident_annealings = self._matches_to_annealings_resident(matches_list)
+        if resident_annealings is not None:
+            if any(pair is None for pair in resident_annealings):
+                return None              # the reference gives up when one primer has no annealing (:74-75)
+            mixture = self.create_PCR_mixture(counter[-1], tname, *self._combine_annealings(*resident_annealings))
+            counter.done()
+            return mixture.save()
         for i, matches in enumerate(matches_list):
             if self.aborted():
                 return None

@@ -333,3 +333,94 @@ def test_sharded_genome_on_one_gpu(ctx, world):
         sh.template.close()
     got = sort_hits(np.concatenate(parts))
     assert len(want) > 50 and np.array_equal(got, want) and n_dimers == len(d)
+
+
+def test_matches_to_mixture_on_resident_hits_ten_conditions():
+    """SURVEY §8f N2 through the facade: PCR_ProductsFinder.find_matches keeps the hits of all primers on the
+    device, matches_to_mixture re-evaluates them with dp_find_again under every new set of conditions.  Ten
+    trial points: annealings (positions, duplexes, every dimer's structure and dG) == the ORACLE's under the same
+    conditions, and the mixture == the one the same factory builds from the oracle's annealings."""
+    import json
+    from degenprimer_b200 import TD_Functions as tdf
+    from degenprimer_b200.PCR_Mixture import MixtureFactory, load_mixture
+    from degenprimer_b200.PCR_ProductsFinder import PCR_ProductsFinder, ResidentMatches
+    from degenprimer_b200.Primer import Primer
+    from degenprimer_b200.SeqUtils import Seq, SeqRecord
+    from degenprimer_b200.WorkCounter import WorkCounter
+    from tests.test_reference_mixture import dump
+    from tests.util import random_dna
+    from oracle.sequtils import reverse_complement
+    rng = np.random.default_rng(77)
+    masters = [('F', 'GAASGCRAAKATYGGGAAC'), ('R', 'ATATTCTACRACGGCTATCC')]
+    t = list(random_dna(rng, 40000))
+    sites = []
+    for i in range(10):                                   # amplicons: F site, R site (as reverse complement) 300-900 bp downstream
+        at = 1500 + 3500 * i
+        f = masters[0][1].replace('S', 'G').replace('R', 'A').replace('K', 'T').replace('Y', 'C')
+        r = reverse_complement(masters[1][1].replace('R', 'G'))
+        if i % 3 == 1:
+            f = f[:4] + ('A' if f[4] != 'A' else 'C') + f[5:]          # one mismatch
+        gap = 300 + 60 * i
+        t[at:at + len(f)] = f
+        t[at + gap:at + gap + len(r)] = r
+        sites.append(at)
+    text = ''.join(t)
+    k = 2
+    gprimers, oprimers = [], []
+    for pid, m in masters:
+        p = Primer(SeqRecord(Seq(m), id=pid), 1e-6)
+        p.generate_components()
+        gprimers.append(p)
+        oprimers.append(OPrimer(OSeqRecord(m, id=pid), 1e-6))
+    ppf = PCR_ProductsFinder(threading.Event(), gprimers, 50, 3000, with_exonuclease=False, include_side_annealings=True)
+    mirror = MixtureFactory(threading.Event(), oprimers, 50, 3000, with_exonuclease=False, include_side_annealings=True)
+    rec = SeqRecord(Seq(text), id='T', description='T synthetic')
+    tdf.PCR_P.set(COND)
+    matches = ppf.find_matches(WorkCounter(), rec, k)
+    assert isinstance(matches, ResidentMatches) and len(matches) == 2 and matches[0][2] is gprimers[0]
+    oracle_matches = [o1.find_matches(text, m, k, workers=0) for _, m in masters]
+    for got, want in zip(matches, oracle_matches):
+        assert np.array_equal(got[5], want[4]) and np.array_equal(got[6], want[5])
+    n_dimers = 0
+    for step in range(10):
+        cond = dict(COND, PCR_T=52.0 + 2.0 * step, Na=(30 + 10 * step) * 1e-3, Mg=(1.0 + 0.4 * step) * 1e-3,
+                    DMSO=float(step % 3))
+        tdf.PCR_P.set(cond)
+        ocond.PCR_P.set(cond)
+        want_ann = [o1.compile_duplexes(m[0], m[1], p, m[2], m[3], m[4], m[5], mp_order=True)
+                    for m, p in zip(oracle_matches, oprimers)]
+        got_ann = ppf._matches_to_annealings_resident(matches)
+        assert got_ann is not None and matches._state is not None                # evaluated on the resident hits
+        for g, w in zip(got_ann, want_ann):
+            assert (g is None) == (w is None)
+            if g is None:
+                continue
+            for strand in (0, 1):
+                assert [x[0] for x in g[strand]] == [x[0] for x in w[strand]]
+                for (_, gd), (_, wd) in zip(g[strand], w[strand]):
+                    assert [d.name for d in gd] == [d.name for d in wd]
+                    for a, b in zip(gd, wd):
+                        assert [x.fwd_matches for x in a.dimers] == [x.fwd_matches for x in b.dimers]
+                        assert [x.dG for x in a.dimers] == [x.dG for x in b.dimers]          # bit for bit
+                        n_dimers += len(a.dimers)
+        path = ppf.matches_to_mixture(WorkCounter(), 'synthetic', matches)
+        if any(w is None for w in want_ann):
+            assert path is None
+            continue
+        fwd, rev = [], []
+        for w in want_ann:
+            fwd.extend(w[0])
+            rev.extend(w[1])
+        want_mix = mirror.create_PCR_mixture(WorkCounter(), 'synthetic', fwd, rev)
+        got = json.loads(json.dumps(dump(load_mixture(path))))
+        assert got == json.loads(json.dumps(dump(want_mix))) and len(got['products']) >= 5
+    assert n_dimers > 200
+    # hits that are gone (another search on that context) fall back to the per-primer path, same result
+    ppf._resident_ctx.scan(matches._state['tmpl'], [masters[0][1]], 0)
+    path = ppf.matches_to_mixture(WorkCounter(), 'synthetic', matches)
+    assert matches._state is None and json.loads(json.dumps(dump(load_mixture(path)))) == got
+    # a template that was closed must not be touched (ADVICE r1: use after free in dp_find_again)
+    m2 = ppf.find_matches(WorkCounter(), rec, k)
+    m2._state['tmpl'].close()
+    with pytest.raises(Exception):
+        m2._state['ctx'].find_again(tdf.conditions())
