@@ -24,13 +24,32 @@ def _nvcc():
     return exe
 
 
-def _stale():
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
+STAMP = LIB + '.sources'
+
+
+def _source_digest():
+    """Digest of everything the library is built from.  File times do not survive the copy to a GPU box
+    (and eight ranks starting at once must not all decide to rebuild), so staleness is decided by content."""
+    import hashlib
+    h = hashlib.sha256()
+    deps = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC))
     deps.append(os.path.join(os.path.dirname(HERE), 'include', 'degenprimer_b200.h'))
-    return any(os.path.getmtime(d) > t for d in deps)
+    for d in deps:
+        h.update(os.path.basename(d).encode() + b'\0')
+        with open(d, 'rb') as fh:
+            h.update(fh.read())
+    h.update(' '.join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
+def _stale():
+    if not os.path.exists(LIB) or not os.path.exists(STAMP):
+        return True
+    try:
+        with open(STAMP) as fh:
+            return fh.read().strip() != _source_digest()
+    except OSError:
+        return True
 
 
 def _embed_device_header(objdir):
@@ -48,9 +67,21 @@ def build_native(force=False, verbose=False):
     """Compile every CUDA source into one shared library.  Returns its path."""
     if not force and not _stale():
         return LIB
-    nvcc = _nvcc()
+    import fcntl
     objdir = os.path.join(HERE, 'build')
     os.makedirs(objdir, exist_ok=True)
+    with open(os.path.join(objdir, '.lock'), 'w') as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)          # one builder at a time (ranks of one node share the tree)
+        try:
+            if not force and not _stale():        # somebody else built it while this process waited
+                return LIB
+            return _build_locked(objdir, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(objdir, verbose):
+    nvcc = _nvcc()
     _embed_device_header(objdir)
     procs = []
     for src in SOURCES:
@@ -72,6 +103,9 @@ def build_native(force=False, verbose=False):
     if r.returncode:
         raise RuntimeError('link failed:\n%s' % r.stdout.decode())
     os.replace(tmp, LIB)
+    with open(STAMP + '.tmp', 'w') as fh:
+        fh.write(_source_digest() + '\n')
+    os.replace(STAMP + '.tmp', STAMP)
     return LIB
 
 

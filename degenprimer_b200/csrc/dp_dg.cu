@@ -180,6 +180,8 @@ struct dp_duplex_scratch {
   uint8_t r[DP_WIN];
   double kdg[DP_LANE_LIST * 32];
   uint64_t kmask[DP_LANE_LIST * 32];
+  uint16_t kd[DP_LANE_LIST * 32];        // construction index of the entry (ties keep that order)
+  uint16_t kn[32];                       // survivors of every lane in this pass
 };
 
 // d-th dimer of [full, alternatives...] in the reference's construction order
@@ -224,14 +226,17 @@ __device__ __forceinline__ void dp_for_each_dimer(uint64_t M, F&& f) {
   }
 }
 
-// One WARP per hit, one LANE per variant (SecStructures.py:294-324 for every Duplex of the site):
-// the window is decoded once into two 64-bit planes + the complement strand in shared memory; a
-// lane builds its variant's planes from the code bytes, gets the match mask with four 64-bit
-// logic ops, walks [full, alternatives...] in the reference's order, evaluates each dimer's dG
-// and keeps the survivors sorted by dG (stable insertion) in its column of shared memory.  One
-// atomic per 32 variants reserves the output range; a directory entry offset << 16 | count per
-// (hit, variant) lets host or device reassemble them in order.  No search for the hit of a pair,
-// no re-decoding of the window per variant, all 32 lanes busy for degenerate primers.
+// One WARP per hit (SecStructures.py:294-324 for every Duplex of the site): the window is decoded
+// once into two 64-bit planes + the complement strand in shared memory.  The 32 lanes are dealt over
+// (variant, share of its dimers): with V >= 32 variants a lane owns a variant, with fewer a group
+// of J = 32 / V' lanes shares one (lane j of the group evaluates the dimers d = j mod J of
+// [full, alternatives...]), so a non-degenerate primer's handful of dimers is evaluated side by
+// side instead of one after the other.  A lane builds its variant's planes from the code bytes,
+// gets the match mask with four 64-bit logic ops, walks the dimers in the reference's order,
+// evaluates its share and parks the survivors in its column of shared memory; the final place
+// of a survivor is its rank by (dG, construction index) among the group's survivors (the
+// reference's stable sort).  One atomic per pass reserves the output range; a directory entry
+// offset << 16 | count per (hit, variant) lets host or device reassemble them in order.
 __global__ void __launch_bounds__(DP_DUPLEX_THREADS)
 dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant__ dp_dg_plan plan) {
   const unsigned long long packed = A.counters[DP_C_HITS];
@@ -250,8 +255,6 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
   G.T = &sT;
   const uint32_t lane = threadIdx.x & 31u;
   dp_duplex_scratch& W = sW[threadIdx.x >> 5];
-  double* const kdg = W.kdg + lane;
-  uint64_t* const kmask = W.kmask + lane;
   unsigned long long n_tried = 0;
   const uint64_t n_warps = (uint64_t)gridDim.x * DP_DUPLEX_WARPS;
   for (uint64_t hi_ = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); hi_ < n_hits; hi_ += n_warps) {
@@ -261,6 +264,11 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
     const uint32_t primer = plan.pat_primer[hit.pattern];
     const uint32_t V = plan.var_count[primer];
     const uint8_t* codes = A.codes + plan.var_off[primer];
+    // lanes per variant: 32, 16, 8, 4, 2 or 1 (V = 1, 2, 3-4, 5-8, 9-16, more)
+    uint32_t J = 1;
+    while (J < 32u && J * 2u * V <= 32u) J *= 2u;
+    const uint32_t per_pass = 32u / J;                   // variants per pass
+    const uint32_t j = lane & (J - 1u), first = lane & ~(J - 1u);
     // the window as the reference's strand string shows it: two planes for its ACGT letters,
     // W.r = its complement strand (3'->5') as letter indices (IUPAC letters included)
     uint64_t whi = 0, wlo = 0, wbase = 0;
@@ -280,8 +288,8 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
     }
     __syncwarp();
     uint32_t hit_dimers = 0;
-    for (uint32_t v0 = 0; v0 < V; v0 += 32) {
-      const uint32_t v = v0 + lane;
+    for (uint32_t v0 = 0; v0 < V; v0 += per_pass) {
+      const uint32_t v = v0 + lane / J;
       uint32_t kept = 0;
       uint64_t M = 0;
       dp_seq_planes sv;
@@ -295,26 +303,24 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
         }
         M = ~(sv.hi ^ whi) & ~(sv.lo ^ wlo) & wbase;     // plain equality of letters
         if (M) {
+          uint32_t d = 0;
           dp_for_each_dimer(M, [&](uint64_t sub) {
+            const uint32_t mine = d++;
+            if ((mine & (J - 1u)) != j) return;
             const double dG = dp_dimer_dg_device(G, sv, L, W.r, L, sub, 0);
             ++n_tried;
             if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;        // SecStructures.py:302-304
             if (kept < DP_LANE_LIST) {
-              // stable insertion by dG: behind every entry that is not larger
-              uint32_t pos = kept;
-              while (pos > 0 && kdg[32 * (pos - 1)] > dG) {
-                kdg[32 * pos] = kdg[32 * (pos - 1)];
-                kmask[32 * pos] = kmask[32 * (pos - 1)];
-                --pos;
-              }
-              kdg[32 * pos] = dG;
-              kmask[32 * pos] = sub;
+              W.kdg[32 * kept + lane] = dG;
+              W.kmask[32 * kept + lane] = sub;
+              W.kd[32 * kept + lane] = (uint16_t)mine;
             }
             ++kept;
           });
         }
       }
-      // output range of these 32 variants: one atomic, offsets by prefix sum
+      __syncwarp();
+      // output range of this pass: one atomic, offsets by prefix sum over the lanes
       uint32_t incl = kept;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -328,31 +334,52 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
         if (lane == 0) base = atomicAdd(&A.counters[DP_C_DIMERS], (unsigned long long)total);
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
       }
-      if (v < V) {
-        const uint64_t off = base + (incl - kept);
-        if (kept && off + kept <= A.out_cap) {
-          dp_raw_dimer* dst = A.out + off;
-          if (kept <= DP_LANE_LIST) {
-            for (uint32_t e = 0; e < kept; ++e) {
-              dst[e].match_mask = kmask[32 * e];
-              dst[e].dG = kdg[32 * e];
+      // the group of a variant: its range starts where its first lane's does
+      const uint32_t g_excl = __shfl_sync(0xFFFFFFFFu, incl - kept, first);
+      const uint32_t g_total = __shfl_sync(0xFFFFFFFFu, incl, first + J - 1u) - g_excl;
+      const uint32_t big = __ballot_sync(0xFFFFFFFFu, kept > DP_LANE_LIST);
+      const uint32_t g_mask = J == 32u ? 0xFFFFFFFFu : ((1u << J) - 1u) << first;
+      const uint64_t off = base + g_excl;
+      const bool fits = off + g_total <= A.out_cap;
+      W.kn[lane] = (uint16_t)min(kept, (uint32_t)DP_LANE_LIST);
+      __syncwarp();
+      if (v < V && g_total && fits) {
+        dp_raw_dimer* dst = A.out + off;
+        if (!(big & g_mask)) {
+          // place = rank by (dG, construction index) among the survivors of the group
+          for (uint32_t e = 0; e < kept; ++e) {
+            const double x = W.kdg[32 * e + lane];
+            const uint32_t xd = W.kd[32 * e + lane];
+            uint32_t rank = 0;
+#pragma unroll 1
+            for (uint32_t l = 0; l < J; ++l) {
+              const uint32_t n_l = W.kn[first + l];
+              for (uint32_t f = 0; f < n_l; ++f) {
+                const double y = W.kdg[32 * f + first + l];
+                rank += (y < x || (y == x && W.kd[32 * f + first + l] < xd)) ? 1u : 0u;
+              }
             }
-          } else {
-            // more survivors than the list holds: enumerate again, insert straight into the range
-            uint32_t m = 0;
-            dp_for_each_dimer(M, [&](uint64_t sub) {
-              const double dG = dp_dimer_dg_device(G, sv, L, W.r, L, sub, 0);
-              if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;
-              uint32_t pos = m;
-              while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
-              dst[pos].match_mask = sub;
-              dst[pos].dG = dG;
-              ++m;
-            });
+            dst[rank].match_mask = W.kmask[32 * e + lane];
+            dst[rank].dG = x;
           }
+        } else if (j == 0) {
+          // more survivors than a lane's list holds (>= 5 mismatch runs): the group's first lane
+          // enumerates again and inserts straight into the reserved range (stable)
+          uint32_t m = 0;
+          dp_for_each_dimer(M, [&](uint64_t sub) {
+            const double dG = dp_dimer_dg_device(G, sv, L, W.r, L, sub, 0);
+            if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;
+            uint32_t pos = m;
+            while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
+            dst[pos].match_mask = sub;
+            dst[pos].dG = dG;
+            ++m;
+          });
         }
+      }
+      if (v < V && j == 0) {
         const uint64_t pair = (uint64_t)hit.pair_base + v;
-        if (pair < A.dir_cap) A.dir[pair] = kept ? (off << 16) | (uint64_t)kept : 0ull;
+        if (pair < A.dir_cap) A.dir[pair] = g_total ? (off << 16) | (uint64_t)g_total : 0ull;
       }
       __syncwarp();
     }
@@ -438,7 +465,7 @@ int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint
   A.counters = ctx->d_counters;
   // pair count unknown on the host (fused call): a persistent grid, most blocks
   // leave at once when there are few pairs
-  uint64_t blocks = (uint64_t)ctx->sm_count * 5;           // 43 KB of shared memory per block: 5 fit an SM
+  uint64_t blocks = (uint64_t)ctx->sm_count * 4;           // 47 KB of shared memory per block: 4 fit an SM
   if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS);
   dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, 0, ctx->stream>>>(A, L.plan);
   DP_CUDA(ctx, cudaGetLastError());
