@@ -173,6 +173,8 @@ struct dp_duplex_args {
 #define DP_DUPLEX_WARPS 4
 #define DP_DUPLEX_THREADS (32 * DP_DUPLEX_WARPS)
 #define DP_LANE_LIST 16        // survivors one lane keeps in shared memory (>= 5 mismatch runs overflow)
+#define DP_DUPLEX_TABLE_BYTES ((sizeof(dp_nn_tables) + 15) / 16 * 16)
+#define DP_DUPLEX_SMEM (DP_DUPLEX_TABLE_BYTES + DP_DUPLEX_WARPS * sizeof(dp_duplex_scratch))
 
 // per-warp scratch: the window's complement strand and every lane's list of surviving dimers
 // ([entry][lane]: a lane's accesses stay in its own bank)
@@ -182,7 +184,57 @@ struct dp_duplex_scratch {
   uint64_t kmask[DP_LANE_LIST * 32];
   uint16_t kd[DP_LANE_LIST * 32];        // construction index of the entry (ties keep that order)
   uint16_t kn[32];                       // survivors of every lane in this pass
+  uint8_t idx[DP_WIN * 32];              // [position][lane]: NN-table index of the stack (s[i] s[i+1] / r[i+1])
 };
+
+// dimer_dG_corrected (TD_Functions.py:124-206) for a primer-template Duplex: both strands have
+// the primer's length and offset 0, so no dangling end is reachable and the end terms reduce to
+// "terminal AT" or "terminal mismatch"; the stack of two adjacent positions is looked up through
+// the lane's precomputed table index.  Same additions in the same order as dp_dimer_dg_device.
+__device__ __forceinline__ double dp_duplex_dimer_dg(const dp_dg_args& A, const dp_seq_planes& s, const uint8_t* r,
+                                                     const uint8_t* idx /* stride 32 */, int L, uint64_t mask) {
+  const dp_nn_tables& T = *A.T;
+  const double* sdH = &T.stack_dH[0][0][0];
+  const double* sdS = &T.stack_dS[0][0][0];
+  const int f0 = __ffsll((long long)mask) - 1;
+  const int f1 = 63 - __clzll((long long)mask);
+  double dG = 0.0, dH = T.ini_dH, dS = T.ini_dS;
+  if (f0 == 0) {                                         // left end, TD_Functions.py:140-158
+    const uint32_t x = s[0];
+    if (x == 0 || x == 2) { dH = f64_add(dH, T.ter_dH); dS = f64_add(dS, T.ter_dS); }
+  } else {
+    dG = f64_add(dG, T.terminal_mismatch);
+  }
+  if (f1 == L - 1) {                                     // right end, :160-178
+    const uint32_t x = s[L - 1];
+    if (x == 0 || x == 2) { dH = f64_add(dH, T.ter_dH); dS = f64_add(dS, T.ter_dS); }
+  } else {
+    dG = f64_add(dG, T.terminal_mismatch);
+  }
+  uint64_t m = mask & (mask - 1);                        // stacks, |x|, |xx|, loops, :180-202
+  int a = f0;
+  while (m) {
+    const int b = __ffsll((long long)m) - 1;
+    m &= m - 1;
+    const int gap = b - a;
+    if (gap < 4) {
+      const uint32_t i = idx[32 * a];
+      dH = f64_add(dH, sdH[i]);
+      dS = f64_add(dS, sdS[i]);
+      if (gap > 1) {
+        const uint32_t x2 = s[b - 1], y2 = s[b], w2 = r[b - 1];
+        dH = f64_add(dH, T.rstack_dH[x2][y2][w2]);
+        dS = f64_add(dS, T.rstack_dS[x2][y2][w2]);
+      }
+    } else {
+      dS = f64_add(dS, T.loop_dS[gap - 1]);
+    }
+    a = b;
+  }
+  dS = f64_add(dS, f64_mul(f64_mul(T.dS_Na, (double)(f1 - f0)), A.Na_eq_log));      // :204-205
+  const double tds = __ddiv_rn(f64_mul(f64_add(A.PCR_T, -T.K0), dS), 1000.0);
+  return f64_add(f64_add(dG, dH), -tds);
+}
 
 // d-th dimer of [full, alternatives...] in the reference's construction order
 // (Dimer.alternatives, SecStructures.py:126-152): M split into n maximal runs of
@@ -243,8 +295,9 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
   const uint64_t n_hits = (uint32_t)packed;
   if (n_hits > A.hits_cap) return;                       // the host grows the buffer and rescans
   if ((uint64_t)blockIdx.x * DP_DUPLEX_WARPS >= n_hits) return;
-  __shared__ dp_nn_tables sT;                            // 10 KB: NN tables next to the lanes
-  __shared__ dp_duplex_scratch sW[DP_DUPLEX_WARPS];
+  extern __shared__ __align__(16) unsigned char dp_duplex_smem[];     // NN tables (10 KB) + one scratch per warp
+  dp_nn_tables& sT = *reinterpret_cast<dp_nn_tables*>(dp_duplex_smem);
+  dp_duplex_scratch* sW = reinterpret_cast<dp_duplex_scratch*>(dp_duplex_smem + DP_DUPLEX_TABLE_BYTES);
   {
     const uint64_t* src = reinterpret_cast<const uint64_t*>(A.dg.T);
     uint64_t* dst = reinterpret_cast<uint64_t*>(&sT);
@@ -296,10 +349,13 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
       sv.hi = sv.lo = 0;
       if (v < V) {
         const uint8_t* vc = codes + (uint64_t)v * L;
+        uint32_t c = vc[0];
         for (int i = 0; i < L; ++i) {
-          const uint32_t c = vc[i];
           sv.hi |= (uint64_t)(c >> 1) << i;
           sv.lo |= (uint64_t)(c & 1u) << i;
+          const uint32_t cn = i + 1 < L ? vc[i + 1] : 0u;
+          if (i + 1 < L) W.idx[32 * i + lane] = (uint8_t)((c * 4u + cn) * 15u + W.r[i + 1]);
+          c = cn;
         }
         M = ~(sv.hi ^ whi) & ~(sv.lo ^ wlo) & wbase;     // plain equality of letters
         if (M) {
@@ -307,7 +363,7 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
           dp_for_each_dimer(M, [&](uint64_t sub) {
             const uint32_t mine = d++;
             if ((mine & (J - 1u)) != j) return;
-            const double dG = dp_dimer_dg_device(G, sv, L, W.r, L, sub, 0);
+            const double dG = dp_duplex_dimer_dg(G, sv, W.r, W.idx + lane, L, sub);
             ++n_tried;
             if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;        // SecStructures.py:302-304
             if (kept < DP_LANE_LIST) {
@@ -367,7 +423,7 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
           // enumerates again and inserts straight into the reserved range (stable)
           uint32_t m = 0;
           dp_for_each_dimer(M, [&](uint64_t sub) {
-            const double dG = dp_dimer_dg_device(G, sv, L, W.r, L, sub, 0);
+            const double dG = dp_duplex_dimer_dg(G, sv, W.r, W.idx + lane, L, sub);
             if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;
             uint32_t pos = m;
             while (pos > 0 && dst[pos - 1].dG > dG) { dst[pos] = dst[pos - 1]; --pos; }
@@ -465,9 +521,14 @@ int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint
   A.counters = ctx->d_counters;
   // pair count unknown on the host (fused call): a persistent grid, most blocks
   // leave at once when there are few pairs
-  uint64_t blocks = (uint64_t)ctx->sm_count * 4;           // 47 KB of shared memory per block: 4 fit an SM
+  static bool configured[16] = {false};                    // per device: opt in to > 48 KB of shared memory
+  if (!configured[ctx->device & 15]) {
+    DP_CUDA(ctx, cudaFuncSetAttribute(dp_duplex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DP_DUPLEX_SMEM));
+    configured[ctx->device & 15] = true;
+  }
+  uint64_t blocks = (uint64_t)ctx->sm_count * 4;           // 56 KB of shared memory per block: 4 fit an SM
   if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS);
-  dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, 0, ctx->stream>>>(A, L.plan);
+  dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, DP_DUPLEX_SMEM, ctx->stream>>>(A, L.plan);
   DP_CUDA(ctx, cudaGetLastError());
   ++*launches;
   return DP_OK;
