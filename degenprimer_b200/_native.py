@@ -164,6 +164,8 @@ def _declare(lib):
         'dp_hit_windows': (i32, [vp, vp, C.c_void_p, u64, u32, C.c_void_p, C.c_void_p]),
         'dp_calibrate': (i32, [vp, i32, i32, P(C.c_double), P(C.c_double)]),
         'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
+        'dp_variant_tm_static': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
+        'dp_variant_tm_static_limits': (i32, [P(u32), P(u64), P(u64)]),
         'dp_dimer_dg': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_void_p, P(dp_conditions), C.c_void_p]),
         'dp_hairpin_tables_load': (i32, [vp, P(dp_hairpin_tables)]),
@@ -184,7 +186,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_template_from_fasta dp_template_set_record_name dp_template_save dp_template_load dp_template_image_size dp_template_save_mem dp_template_load_mem dp_template_set_origin dp_template_origin dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
            'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_jit_describe dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_comm_set_layout dp_stream dp_synchronize '
-           'dp_hit_windows dp_variant_tm dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
+           'dp_hit_windows dp_variant_tm dp_variant_tm_static dp_variant_tm_static_limits dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
 
 
 def load():

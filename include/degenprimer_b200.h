@@ -435,6 +435,23 @@ int dp_variant_tm(dp_ctx* ctx, uint32_t n, uint32_t len, const char* seqs,
                   double concentration, double conversion_degree,
                   const dp_conditions* cond, double* tm);
 
+/* dp_variant_tm for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments, results bit-identical
+ * to dp_variant_tm; the staging memory dp_variant_tm takes from the context's pool is ONE
+ * file-scope `static __device__` array of 296 KiB (csrc/dp_static.cu) that every GPU which loads
+ * the library holds until the process exits.  Limits per call: n <= 4096 sequences and
+ * n * len <= 262144 bytes (dp_variant_tm_static_limits reports them); larger calls are refused
+ * with DP_ERR_UNSUPPORTED and a message naming the limits.  The call makes no cudaMalloc /
+ * cudaFree / stream-ordered or pool allocation and no host allocation on its success path.
+ * All calls on a device share the array, which keeps the last call's contents (the call clears
+ * what must start clean): calls that OVERLAP on one GPU -- two contexts, two threads -- race on
+ * it; issue them one after the other. */
+int dp_variant_tm_static(dp_ctx* ctx, uint32_t n, uint32_t len, const char* seqs,
+                         double concentration, double conversion_degree,
+                         const dp_conditions* cond, double* tm);
+int dp_variant_tm_static_limits(uint32_t* max_seqs, uint64_t* max_seq_bytes, uint64_t* scratch_bytes);
+
 /* dimer_dG_corrected for arbitrary dimers (offset != 0, unequal lengths:
  * dangling ends reachable) — DegenPrimer/TD_Functions.py:124-206.
  * Dimer i: seq1 = s1 + off1[i] (len1[i] bytes, 5'->3'), seq2 likewise,
