@@ -11,6 +11,7 @@ from . import TD_Functions as tdf
 from . import _native as nat
 from .PCR_Mixture import MixtureFactory
 from .SearchEngine import SearchEngine, StrandView, _primers_query, resident
+from .SecStructures import SiteList, SitePool
 from .SeqUtils import pretty_rec_name
 from .WorkCounter import WorkCounter
 from .tmpStorage import cleanup_files, from_shelf
@@ -44,7 +45,12 @@ class PCR_ProductsFinder(MixtureFactory):
     @staticmethod
     def _pool(results):
         """One forward and one reverse list out of the (fwd_results, rev_results) pairs of several primers."""
-        pooled = ([], [])
+        results = list(results)
+        lists = [pair[strand] for pair in results if pair for strand in (0, 1) if pair[strand]]
+        if lists and all(isinstance(x, SiteList) for x in lists):
+            pooled = (SitePool(), SitePool())          # device results stay arrays: MixtureFactory joins them on the GPU
+        else:
+            pooled = ([], [])
         for pair in results:
             for strand in (0, 1):
                 if pair and pair[strand]:

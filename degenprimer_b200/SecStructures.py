@@ -366,6 +366,49 @@ class LazyWindows(object):
         return len(self._hits)
 
 
+class SitePool(object):
+    """The annealing sites of several primers on one strand, pooled (PCR_ProductsFinder._combine_annealings,
+    DegenPrimer/PCR_ProductsFinder.py:57-65) but kept as the SiteLists they came in: list-like for every
+    consumer of `[(position, duplexes), ...]`, structure-of-arrays for MixtureFactory's device join."""
+
+    def __init__(self, parts=()):
+        self.parts = [p for p in parts if len(p)]
+
+    def extend(self, part):
+        if len(part):
+            self.parts.append(part)
+
+    def __len__(self):
+        return sum(len(p) for p in self.parts)
+
+    def __bool__(self):
+        return bool(self.parts)
+
+    def __iter__(self):
+        for p in self.parts:
+            for item in p:
+                yield item
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return list(self)[i]
+        if i < 0:
+            i += len(self)
+        for p in self.parts:
+            if i < len(p):
+                return p[i]
+            i -= len(p)
+        raise IndexError('SitePool index out of range')
+
+    def __eq__(self, other):
+        return list(self) == list(other)
+
+    __hash__ = None
+
+    def __reduce__(self):
+        return (SitePool, (self.parts,))
+
+
 def _rebuild_site_list(positions, counts, rows, windows, variants, names, T):
     table = DuplexTable(rows, windows, variants, names, T)
     hi = np.cumsum(counts)
@@ -432,6 +475,26 @@ class SiteList(object):
 
     def __repr__(self):
         return 'SiteList(%d sites)' % len(self)
+
+    def duplex_flags(self):
+        """Per duplex ((site, variant) group of dimer rows) of this list, as arrays and without building any
+        object: (site index in this list, variant index, has a dimer whose 3' end is annealed).  The last one is
+        Duplex.have_3_matches (SecStructures.py:326-339: some dimer with fwd_max == fwd_len - 1)."""
+        t = self._table
+        n = (self._hi - self._lo).astype(np.int64)
+        if not len(n) or not int(n.sum()):
+            z = np.zeros(0, dtype=np.int64)
+            return z, z, np.zeros(0, dtype=bool)
+        site = np.repeat(np.arange(len(n)), n)
+        first = np.concatenate(([0], np.cumsum(n)[:-1]))
+        rows = np.repeat(self._lo.astype(np.int64) - first, n) + np.arange(int(n.sum()))
+        variant = t.dimers['variant'][rows].astype(np.int64)
+        p_len = len(t.variants[0])
+        bit = ((t.dimers['match_mask'][rows] >> np.uint64(p_len - 1)) & np.uint64(1)).astype(bool)
+        new = np.ones(len(rows), dtype=bool)
+        new[1:] = (site[1:] != site[:-1]) | (variant[1:] != variant[:-1])
+        starts = np.flatnonzero(new)
+        return site[starts], variant[starts], np.logical_or.reduceat(bit, starts)
 
     def __reduce__(self):
         t = self._table

@@ -103,6 +103,7 @@ BEST_STRUCTURE_DTYPE = np.dtype([('best_mask', '<u8'), ('best_dG', '<f8')], alig
 FRONT_DIMER_DTYPE = np.dtype([('full_mask', '<u8'), ('best_mask', '<u8'), ('best_dG', '<f8')], align=True)
 assert HIT_DTYPE.itemsize == 16 and DIMER_DTYPE.itemsize == 24 and WIRE_DTYPE.itemsize == 24
 assert FRONT_DIMER_DTYPE.itemsize == 24
+PAIR_DTYPE = np.dtype([('fwd', '<u4'), ('rev', '<u4')])
 
 _lib = None
 _lock = threading.Lock()
@@ -166,6 +167,7 @@ def _declare(lib):
         'dp_variant_tm': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
         'dp_variant_tm_static': (i32, [vp, u32, u32, C.c_void_p, C.c_double, C.c_double, P(dp_conditions), C.c_void_p]),
         'dp_variant_tm_static_limits': (i32, [P(u32), P(u64), P(u64)]),
+        'dp_pair_products': (i32, [vp, u32, C.c_void_p, u32, C.c_void_p, C.c_int64, C.c_int64, P(vp), P(u64), C.c_void_p]),
         'dp_dimer_dg': (i32, [vp, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_void_p, P(dp_conditions), C.c_void_p]),
         'dp_hairpin_tables_load': (i32, [vp, P(dp_hairpin_tables)]),
@@ -186,7 +188,7 @@ EXPORTS = ('dp_abi_version dp_device_count dp_create dp_create_error dp_destroy 
            'dp_template_from_fasta dp_template_set_record_name dp_template_save dp_template_load dp_template_image_size dp_template_save_mem dp_template_load_mem dp_template_set_origin dp_template_origin dp_template_free dp_template_get_info dp_template_record '
            'dp_template_unpack dp_scan dp_tables_load dp_duplex_dg dp_find dp_find_begin dp_find_end '
            'dp_set_wire dp_set_timing dp_find_again dp_scan_prepare_kernels dp_jit_selftest dp_jit_describe dp_comm_export dp_comm_attach dp_comm_destroy dp_comm_gathered dp_comm_hits dp_comm_set_layout dp_stream dp_synchronize '
-           'dp_hit_windows dp_variant_tm dp_variant_tm_static dp_variant_tm_static_limits dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
+           'dp_hit_windows dp_variant_tm dp_variant_tm_static dp_variant_tm_static_limits dp_pair_products dp_dimer_dg dp_find_dimers dp_hairpin_tables_load dp_find_hairpins dp_calibrate').split()
 
 
 def load():
@@ -630,6 +632,19 @@ class Context(object):
                                           C.byref(cond), C.byref(out), C.byref(n_out), C.byref(st)))
         arr = self._take(out, n_out.value, DIMER_DTYPE)
         return arr, st
+
+    def pair_products(self, fwd_pos, rev_pos, min_amplicon, max_amplicon):
+        """dp_pair_products: the pairing loop of MixtureFactory.create_PCR_mixture on the device.
+        Returns (pairs as an (n, 2) uint32 array of (forward index, reverse index) in the reference's
+        order, rev_start per forward site)."""
+        f = np.ascontiguousarray(fwd_pos, dtype=np.int64)
+        r = np.ascontiguousarray(rev_pos, dtype=np.int64)
+        rs = np.zeros(len(f), dtype=np.uint32)
+        out, n = C.c_void_p(), C.c_uint64()
+        self._check(self.lib.dp_pair_products(self._h, len(f), _ptr(f), len(r), _ptr(r), int(min_amplicon),
+                                              int(max_amplicon), C.byref(out), C.byref(n), _ptr(rs)))
+        pairs = self._take(out, n.value, PAIR_DTYPE)
+        return pairs, rs
 
     def calibrate(self, which, reps=5):
         """Lane-ops/s of a pipe: 'lop3', 'popc' or 'lds'."""

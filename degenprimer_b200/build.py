@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libdegenprimer_b200.so')
-SOURCES = ['dp_ctx.cu', 'dp_template.cu', 'dp_scan.cu', 'dp_dg.cu', 'dp_comm.cu', 'dp_jit.cu', 'dp_calib.cu', 'dp_static.cu']
+SOURCES = ['dp_ctx.cu', 'dp_template.cu', 'dp_scan.cu', 'dp_dg.cu', 'dp_comm.cu', 'dp_jit.cu', 'dp_calib.cu', 'dp_static.cu', 'dp_mixture.cu']
 NVCC_FLAGS = ['-std=c++17', '-O3', '-gencode', 'arch=compute_100a,code=sm_100a',
               '-lineinfo', '-Xcompiler', '-fPIC']
 

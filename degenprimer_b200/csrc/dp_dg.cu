@@ -170,9 +170,12 @@ struct dp_duplex_args {
   unsigned long long* counters;
 };
 
-#define DP_DUPLEX_WARPS 4
+// two warps per block: a block then needs ~5K registers and 33 KB of shared memory and fits on an SM NEXT TO
+// the resident blocks of a scan kernel of another call in flight (which leave ~8K registers free), so the
+// duplex stage of one call overlaps the scan of the next instead of waiting for a gap
+#define DP_DUPLEX_WARPS 2
 #define DP_DUPLEX_THREADS (32 * DP_DUPLEX_WARPS)
-#define DP_LANE_LIST 16        // survivors one lane keeps in shared memory (>= 5 mismatch runs overflow)
+#define DP_LANE_LIST 8         // dimers one lane's column of shared memory holds (more: a slow path, same results)
 #define DP_DUPLEX_TABLE_BYTES ((sizeof(dp_nn_tables) + 15) / 16 * 16)
 #define DP_DUPLEX_SMEM (DP_DUPLEX_TABLE_BYTES + DP_DUPLEX_WARPS * sizeof(dp_duplex_scratch))
 
@@ -278,12 +281,32 @@ __device__ __forceinline__ void dp_for_each_dimer(uint64_t M, F&& f) {
   }
 }
 
-// One WARP per hit (SecStructures.py:294-324 for every Duplex of the site): the window is decoded
-// once into two 64-bit planes + the complement strand in shared memory.  The 32 lanes are dealt over
-// (variant, share of its dimers): with V >= 32 variants a lane owns a variant, with fewer a group
-// of J = 32 / V' lanes shares one (lane j of the group evaluates the dimers d = j mod J of
-// [full, alternatives...]), so a non-degenerate primer's handful of dimers is evaluated side by
-// side instead of one after the other.  A lane builds its variant's planes from the code bytes,
+// lanes that share one variant of a primer with V variants, and the passes a hit of it needs
+__host__ __device__ __forceinline__ uint32_t dp_lanes_per_variant(uint32_t V) {
+  uint32_t J = 1u;                                       // 32, 16, 8, 4, 2, 1 for V = 1, 2, 3-4, 5-8, 9-16, more
+  while (J < 32u && J * 2u * V <= 32u) J *= 2u;
+  return J;
+}
+__host__ __device__ __forceinline__ uint32_t dp_passes(uint32_t V) {
+  const uint32_t per_pass = 32u / dp_lanes_per_variant(V);
+  return V ? (V + per_pass - 1u) / per_pass : 0u;
+}
+
+// dimers per hit are summed over the hit's passes: start from zero (the hits may be resident ones
+// that have been through the duplex stage before, dp_find_again)
+__global__ void __launch_bounds__(128)
+dp_duplex_clear_kernel(dp_raw_hit* __restrict__ hits, uint64_t hits_cap, const unsigned long long* __restrict__ counters) {
+  const uint64_t n = min((uint64_t)(uint32_t)counters[DP_C_HITS], hits_cap);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    hits[i].reserved = 0u;
+}
+
+// One WARP per (hit, pass) (SecStructures.py:294-324 for every Duplex of the site): the window is
+// decoded into two 64-bit planes + the complement strand in shared memory.  The 32 lanes are dealt
+// over (variant, share of its dimers): J = 32 ... 1 lanes share one variant (V = 1 ... > 16; lane j
+// of the group evaluates the dimers d = j mod J of [full, alternatives...]), so the handful of dimers
+// of a non-degenerate duplex is evaluated side by side instead of one after the other, and the
+// variants of a degenerate primer are spread over passes of 32 variants that different warps take.  A lane builds its variant's planes from the code bytes,
 // gets the match mask with four 64-bit logic ops, walks the dimers in the reference's order,
 // evaluates its share and parks the survivors in its column of shared memory; the final place
 // of a survivor is its rank by (dG, construction index) among the group's survivors (the
@@ -294,7 +317,13 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
   const unsigned long long packed = A.counters[DP_C_HITS];
   const uint64_t n_hits = (uint32_t)packed;
   if (n_hits > A.hits_cap) return;                       // the host grows the buffer and rescans
-  if ((uint64_t)blockIdx.x * DP_DUPLEX_WARPS >= n_hits) return;
+  // work item = (hit, pass): a pass covers 32 / J variants of the hit, J lanes each (dp_lanes_per_variant);
+  // every hit gets PP = passes of the most degenerate primer of the call, the surplus items leave at once
+  uint32_t v_max = 1;
+  for (int p = 0; p < DP_MAX_PRIMERS; ++p) v_max = max(v_max, plan.var_count[p]);
+  const uint32_t PP = dp_passes(v_max);
+  const uint64_t n_items = n_hits * PP;
+  if ((uint64_t)blockIdx.x * DP_DUPLEX_WARPS >= n_items) return;
   extern __shared__ __align__(16) unsigned char dp_duplex_smem[];     // NN tables (10 KB) + one scratch per warp
   dp_nn_tables& sT = *reinterpret_cast<dp_nn_tables*>(dp_duplex_smem);
   dp_duplex_scratch* sW = reinterpret_cast<dp_duplex_scratch*>(dp_duplex_smem + DP_DUPLEX_TABLE_BYTES);
@@ -310,16 +339,17 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
   dp_duplex_scratch& W = sW[threadIdx.x >> 5];
   unsigned long long n_tried = 0;
   const uint64_t n_warps = (uint64_t)gridDim.x * DP_DUPLEX_WARPS;
-  for (uint64_t hi_ = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); hi_ < n_hits; hi_ += n_warps) {
+  for (uint64_t item = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); item < n_items; item += n_warps) {
+    const uint64_t hi_ = item / PP;
+    const uint32_t pass = (uint32_t)(item % PP);
     const dp_raw_hit hit = A.hits[hi_];
     const int L = plan.pat_len[hit.pattern];
     const int strand = plan.pat_strand[hit.pattern];
     const uint32_t primer = plan.pat_primer[hit.pattern];
     const uint32_t V = plan.var_count[primer];
+    if (pass >= dp_passes(V)) continue;                  // uniform over the warp
     const uint8_t* codes = A.codes + plan.var_off[primer];
-    // lanes per variant: 32, 16, 8, 4, 2 or 1 (V = 1, 2, 3-4, 5-8, 9-16, more)
-    uint32_t J = 1;
-    while (J < 32u && J * 2u * V <= 32u) J *= 2u;
+    const uint32_t J = dp_lanes_per_variant(V);
     const uint32_t per_pass = 32u / J;                   // variants per pass
     const uint32_t j = lane & (J - 1u), first = lane & ~(J - 1u);
     // the window as the reference's strand string shows it: two planes for its ACGT letters,
@@ -341,7 +371,8 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
     }
     __syncwarp();
     uint32_t hit_dimers = 0;
-    for (uint32_t v0 = 0; v0 < V; v0 += per_pass) {
+    {
+      const uint32_t v0 = pass * per_pass;
       const uint32_t v = v0 + lane / J;
       uint32_t kept = 0;
       uint64_t M = 0;
@@ -358,21 +389,64 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
           c = cn;
         }
         M = ~(sv.hi ^ whi) & ~(sv.lo ^ wlo) & wbase;     // plain equality of letters
-        if (M) {
-          uint32_t d = 0;
+      }
+      // Phase 1 (cheap, lanes diverge): every lane walks [full, alternatives...] of its variant and
+      // notes the masks of ITS share (d = j mod J) in its column.  Phase 2 (the expensive part, lanes
+      // converged): share t of every lane is evaluated in the same instruction stream -- evaluating
+      // inside the walk would serialise the lanes of a group, each at its own dimer index.
+      uint32_t mine_n = 0;
+      bool overflow = false;                             // the lane's column does not hold the group's dimers / survivors
+      if (v < V && M) {
+        if (J == 1u) {
+          // a lane per variant: every lane is busy anyway, evaluate inside the walk
           dp_for_each_dimer(M, [&](uint64_t sub) {
-            const uint32_t mine = d++;
-            if ((mine & (J - 1u)) != j) return;
             const double dG = dp_duplex_dimer_dg(G, sv, W.r, W.idx + lane, L, sub);
             ++n_tried;
             if (dG > G.max_dimer_dG || !(dG <= G.max_dG_for_K)) return;        // SecStructures.py:302-304
             if (kept < DP_LANE_LIST) {
               W.kdg[32 * kept + lane] = dG;
               W.kmask[32 * kept + lane] = sub;
-              W.kd[32 * kept + lane] = (uint16_t)mine;
+              W.kd[32 * kept + lane] = (uint16_t)kept;    // already in construction order
             }
             ++kept;
           });
+          overflow = kept > DP_LANE_LIST;
+        } else {
+          const uint64_t S = M & ~(M << 1);
+          const uint32_t n_runs = (uint32_t)__popcll(S);
+          if (n_runs * (n_runs + 1u) / 2u <= DP_LANE_LIST * J) {
+            uint32_t d = 0;
+            dp_for_each_dimer(M, [&](uint64_t sub) {
+              const uint32_t idx_d = d++;
+              if ((idx_d & (J - 1u)) == j) W.kmask[32 * (mine_n++) + lane] = sub;
+            });
+          } else if (j == 0) {
+            // too many dimers for the group's columns: its first lane counts the survivors alone
+            dp_for_each_dimer(M, [&](uint64_t sub) {
+              const double dG = dp_duplex_dimer_dg(G, sv, W.r, W.idx + lane, L, sub);
+              ++n_tried;
+              if (!(dG > G.max_dimer_dG) && dG <= G.max_dG_for_K) ++kept;
+            });
+            overflow = true;
+          }
+        }
+      }
+      if (J > 1u) {
+        uint32_t most = mine_n;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) most = max(most, __shfl_xor_sync(0xFFFFFFFFu, most, o));
+        for (uint32_t t = 0; t < most; ++t) {
+          if (t < mine_n) {
+            const uint64_t sub = W.kmask[32 * t + lane];
+            const double dG = dp_duplex_dimer_dg(G, sv, W.r, W.idx + lane, L, sub);
+            ++n_tried;
+            if (!(dG > G.max_dimer_dG) && dG <= G.max_dG_for_K) {               // SecStructures.py:302-304
+              W.kdg[32 * kept + lane] = dG;               // kept <= t: in place
+              W.kmask[32 * kept + lane] = sub;
+              W.kd[32 * kept + lane] = (uint16_t)(t * J + j);                   // construction index
+              ++kept;
+            }
+          }
         }
       }
       __syncwarp();
@@ -393,7 +467,7 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
       // the group of a variant: its range starts where its first lane's does
       const uint32_t g_excl = __shfl_sync(0xFFFFFFFFu, incl - kept, first);
       const uint32_t g_total = __shfl_sync(0xFFFFFFFFu, incl, first + J - 1u) - g_excl;
-      const uint32_t big = __ballot_sync(0xFFFFFFFFu, kept > DP_LANE_LIST);
+      const uint32_t big = __ballot_sync(0xFFFFFFFFu, overflow);
       const uint32_t g_mask = J == 32u ? 0xFFFFFFFFu : ((1u << J) - 1u) << first;
       const uint64_t off = base + g_excl;
       const bool fits = off + g_total <= A.out_cap;
@@ -439,8 +513,8 @@ dp_duplex_kernel(const __grid_constant__ dp_duplex_args A, const __grid_constant
       }
       __syncwarp();
     }
-    if (lane == 0) A.hits[hi_].reserved = hit_dimers;
-    __syncwarp();                                        // W.r is rewritten for the next hit
+    if (lane == 0 && hit_dimers) atomicAdd(&A.hits[hi_].reserved, hit_dimers);    // cleared by dp_duplex_clear_kernel
+    __syncwarp();                                        // W.r is rewritten for the next item
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) n_tried += __shfl_xor_sync(0xFFFFFFFFu, n_tried, o);
@@ -526,11 +600,12 @@ int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint
     DP_CUDA(ctx, cudaFuncSetAttribute(dp_duplex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DP_DUPLEX_SMEM));
     configured[ctx->device & 15] = true;
   }
-  uint64_t blocks = (uint64_t)ctx->sm_count * 4;           // 56 KB of shared memory per block: 4 fit an SM
+  uint64_t blocks = (uint64_t)ctx->sm_count * 8;           // 23 KB of shared memory and 5K registers per block
   if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS);
+  dp_duplex_clear_kernel<<<ctx->sm_count, 128, 0, ctx->stream>>>(A.hits, A.hits_cap, A.counters);
   dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, DP_DUPLEX_SMEM, ctx->stream>>>(A, L.plan);
   DP_CUDA(ctx, cudaGetLastError());
-  ++*launches;
+  *launches += 2;                                          // clear + duplex
   return DP_OK;
 }
 
@@ -574,6 +649,8 @@ __global__ void dp_dimer_dg_kernel(dp_dg_args A, uint32_t n, const uint8_t* __re
   out[i] = dp_dimer_dg_device(A, s, sl, r, rl, mask[i], offset[i]);
 }
 
+#define DP_FD_WARPS 4                    // warps per block of the primer-dimer / hairpin kernels
+#define DP_FD_THREADS (32 * DP_FD_WARPS)
 // ---- self / cross dimers of primer pairs -------------------------------
 // SecStructures._find_dimers, DegenPrimer/SecStructures.py:609-668: slide seq2 (as its reverse
 // complement) along seq1; at every relative position ("front", fwd_len+rev_len-1 of them) the
@@ -588,13 +665,13 @@ struct dp_fd_scratch {
   uint8_t run_end[32];
 };
 
-__global__ void __launch_bounds__(DP_DUPLEX_THREADS)
+__global__ void __launch_bounds__(DP_FD_THREADS)
 dp_find_dimers_kernel(dp_dg_args A, const uint8_t* __restrict__ codes, const uint64_t* __restrict__ seq_off,
                       const uint8_t* __restrict__ seq_len, const uint32_t* __restrict__ pair_a,
                       const uint32_t* __restrict__ pair_b, uint32_t n_pairs, uint32_t stride,
                       dp_front_dimer* __restrict__ out) {
   __shared__ dp_nn_tables sT;
-  __shared__ dp_fd_scratch sW[DP_DUPLEX_WARPS];
+  __shared__ dp_fd_scratch sW[DP_FD_WARPS];
   {
     const uint64_t* src = reinterpret_cast<const uint64_t*>(A.T);
     uint64_t* dst = reinterpret_cast<uint64_t*>(&sT);
@@ -606,9 +683,9 @@ dp_find_dimers_kernel(dp_dg_args A, const uint8_t* __restrict__ codes, const uin
   const uint32_t lane = threadIdx.x & 31u;
   dp_fd_scratch& W = sW[threadIdx.x >> 5];
   const uint64_t n_items = (uint64_t)n_pairs * stride;
-  const uint64_t n_warps = (uint64_t)gridDim.x * DP_DUPLEX_WARPS;
+  const uint64_t n_warps = (uint64_t)gridDim.x * DP_FD_WARPS;
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
-  for (uint64_t item = (uint64_t)blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); item < n_items; item += n_warps) {
+  for (uint64_t item = (uint64_t)blockIdx.x * DP_FD_WARPS + (threadIdx.x >> 5); item < n_items; item += n_warps) {
     const uint32_t pair = (uint32_t)(item / stride);
     const int front = (int)(item % stride);
     const uint32_t ia = pair_a[pair], ib = pair_b[pair];
@@ -774,14 +851,14 @@ __device__ double dp_hairpin_dg_device(const dp_dg_args& A, const dp_hairpin_tab
 // SecStructures._find_hairpins, DegenPrimer/SecStructures.py:676-716, the part after the seed has been
 // trimmed (a few set operations, done by the caller): of [stem] + stem.alternatives the hairpin with
 // the lowest dG strictly below max_hairpin_dG.  One WARP per seed, lane d evaluates candidate d.
-__global__ void __launch_bounds__(DP_DUPLEX_THREADS)
+__global__ void __launch_bounds__(DP_FD_THREADS)
 dp_find_hairpins_kernel(dp_dg_args A, const dp_hairpin_tables* __restrict__ H, double max_hairpin_dG,
                         const uint8_t* __restrict__ codes, const uint64_t* __restrict__ seq_off,
                         const uint8_t* __restrict__ seq_len, const uint32_t* __restrict__ seed_seq,
                         const uint64_t* __restrict__ seed_mask, const int32_t* __restrict__ seed_offset,
                         uint32_t n_seeds, dp_best_structure* __restrict__ out) {
   __shared__ dp_nn_tables sT;
-  __shared__ dp_fd_scratch sW[DP_DUPLEX_WARPS];
+  __shared__ dp_fd_scratch sW[DP_FD_WARPS];
   {
     const uint64_t* src = reinterpret_cast<const uint64_t*>(A.T);
     uint64_t* dst = reinterpret_cast<uint64_t*>(&sT);
@@ -792,9 +869,9 @@ dp_find_hairpins_kernel(dp_dg_args A, const dp_hairpin_tables* __restrict__ H, d
   G.T = &sT;
   const uint32_t lane = threadIdx.x & 31u;
   dp_fd_scratch& W = sW[threadIdx.x >> 5];
-  const uint32_t n_warps = gridDim.x * DP_DUPLEX_WARPS;
+  const uint32_t n_warps = gridDim.x * DP_FD_WARPS;
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
-  for (uint32_t seed = blockIdx.x * DP_DUPLEX_WARPS + (threadIdx.x >> 5); seed < n_seeds; seed += n_warps) {
+  for (uint32_t seed = blockIdx.x * DP_FD_WARPS + (threadIdx.x >> 5); seed < n_seeds; seed += n_warps) {
     const uint32_t si = seed_seq[seed];
     const int L = seq_len[si];
     const uint64_t M = seed_mask[seed];
@@ -1041,10 +1118,10 @@ extern "C" int dp_find_dimers(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, co
     DP_CUDA(ctx, cudaEventRecord(e0, st));
   }
   // one warp per (pair, front), grid-stride; 16 resident blocks of 4 warps per SM
-  const uint64_t blocks_needed = (n_items + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS;
+  const uint64_t blocks_needed = (n_items + DP_FD_WARPS - 1) / DP_FD_WARPS;
   const unsigned grid = (unsigned)std::min<uint64_t>(blocks_needed, (uint64_t)ctx->sm_count * 16);
   dp_dg_args A = make_args(ctx, cond);
-  dp_find_dimers_kernel<<<grid, DP_DUPLEX_THREADS, 0, st>>>(A, d_codes.p, d_off.p, d_len.p, d_a.p, d_b.p, n_pairs, stride, d_out.p);
+  dp_find_dimers_kernel<<<grid, DP_FD_THREADS, 0, st>>>(A, d_codes.p, d_off.p, d_len.p, d_a.p, d_b.p, n_pairs, stride, d_out.p);
   cudaError_t le = cudaGetLastError();
   if (ms_kernel && le == cudaSuccess) le = cudaEventRecord(e1, st);
   if (le == cudaSuccess) le = cudaMemcpyAsync(out, d_out.p, n_items * sizeof(dp_front_dimer), cudaMemcpyDeviceToHost, st);
@@ -1120,10 +1197,10 @@ extern "C" int dp_find_hairpins(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, 
     DP_CUDA(ctx, cudaEventCreate(&e1));
     DP_CUDA(ctx, cudaEventRecord(e0, st));
   }
-  const uint64_t blocks_needed = ((uint64_t)n_seeds + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS;
+  const uint64_t blocks_needed = ((uint64_t)n_seeds + DP_FD_WARPS - 1) / DP_FD_WARPS;
   const unsigned grid = (unsigned)std::min<uint64_t>(blocks_needed, (uint64_t)ctx->sm_count * 16);
   dp_dg_args A = make_args(ctx, cond);
-  dp_find_hairpins_kernel<<<grid, DP_DUPLEX_THREADS, 0, st>>>(A, ctx->d_hp_tables, max_hairpin_dG, d_codes.p, d_off.p, d_len.p,
+  dp_find_hairpins_kernel<<<grid, DP_FD_THREADS, 0, st>>>(A, ctx->d_hp_tables, max_hairpin_dG, d_codes.p, d_off.p, d_len.p,
                                                               d_seq.p, d_mask.p, d_so.p, n_seeds, d_out.p);
   cudaError_t le = cudaGetLastError();
   if (ms_kernel && le == cudaSuccess) le = cudaEventRecord(e1, st);

@@ -114,6 +114,10 @@ dp_scan_runs_kernel(const __grid_constant__ dp_scan_args A, const __grid_constan
   }
 }
 
+// One small block: 128 threads x <= 64 registers fit on an SM next to the resident blocks of another call's
+// scan kernel, so the publish (and the exchange it carries) does not wait for a gap between scans.
+#define DP_PUBLISH_THREADS 128
+
 // ---- kernel 4: publish -------------------------------------------------------------
 // Last kernel of a call: one block writes the counters and the first few result
 // records straight into pinned host memory (zero-copy over PCIe: a few KB) and
@@ -197,48 +201,50 @@ __device__ void dp_exchange_to_host(const dp_exchange_args& X, uint64_t call) {
     return;
   }
   const uint32_t total = first[X.world];
-  // at most two records per thread
-  uint64_t key[2] = {0, 0}, pos[2] = {0, 0};
-  uint32_t meta[2] = {0, 0};
-  for (int e = 0; e < 2; ++e) {
-    const uint32_t i = threadIdx.x + e * blockDim.x;
-    if (i >= total) break;
+  // key, position and the packed rest of record i of the landed call
+  auto record = [&](uint32_t i, uint64_t& key, uint64_t& pos, uint32_t& meta) {
     int r = 0;
     while (i >= first[r + 1]) ++r;
     const volatile uint64_t* h = (const volatile uint64_t*)(X.recv_prev + r * X.slot_bytes);
     const uint64_t g = h[8 + 3 * (i - first[r])], w1 = h[8 + 3 * (i - first[r]) + 1];
     const uint32_t pat = (uint32_t)(w1 >> 32) & 0xFFFFu, score3 = (uint32_t)(w1 >> 48);
     const uint32_t strand = X.prev_strand[pat & (DP_MAX_PATTERNS - 1)];
-    pos[e] = strand ? h[5] - X.prev_len[pat & (DP_MAX_PATTERNS - 1)] - g : g;   // record 0 starts at padded position 0
-    key[e] = ((uint64_t)pat << 56) | ((uint64_t)r << 48) | (pos[e] & 0xFFFFFFFFFFFFull);
-    meta[e] = (uint32_t)r | ((uint32_t)X.prev_primer[pat & (DP_MAX_PATTERNS - 1)] << 8) | (strand << 16) | ((score3 & 0xFFu) << 17);
-    keys[i] = key[e];
+    pos = strand ? h[5] - X.prev_len[pat & (DP_MAX_PATTERNS - 1)] - g : g;   // record 0 starts at padded position 0
+    key = ((uint64_t)pat << 56) | ((uint64_t)r << 48) | (pos & 0xFFFFFFFFFFFFull);
+    meta = (uint32_t)r | ((uint32_t)X.prev_primer[pat & (DP_MAX_PATTERNS - 1)] << 8) | (strand << 16) | ((score3 & 0xFFu) << 17);
+  };
+  for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) {
+    uint64_t key, pos;
+    uint32_t meta;
+    record(i, key, pos, meta);
+    keys[i] = key;
   }
   __syncthreads();
-  for (int e = 0; e < 2; ++e) {
-    const uint32_t i = threadIdx.x + e * blockDim.x;
-    if (i >= total) break;
+  for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) {
+    uint64_t key, pos;
+    uint32_t meta;
+    record(i, key, pos, meta);
     uint32_t rank = 0;
-    for (uint32_t j = 0; j < total; ++j) rank += keys[j] < key[e];       // keys are distinct
+    for (uint32_t j = 0; j < total; ++j) rank += keys[j] < key;       // keys are distinct
     // dp_hit {pos u64; record u32; primer u16; strand u8; score3 u8}
-    X.h_sorted[4 + 2 * rank] = pos[e];
-    X.h_sorted[4 + 2 * rank + 1] = (uint64_t)(meta[e] & 0xFFu) | ((uint64_t)((meta[e] >> 8) & 0xFFu) << 32) |
-                                   ((uint64_t)((meta[e] >> 16) & 1u) << 48) | ((uint64_t)(meta[e] >> 17) << 56);
+    X.h_sorted[4 + 2 * rank] = pos;
+    X.h_sorted[4 + 2 * rank + 1] = (uint64_t)(meta & 0xFFu) | ((uint64_t)((meta >> 8) & 0xFFu) << 32) |
+                                   ((uint64_t)((meta >> 16) & 1u) << 48) | ((uint64_t)(meta >> 17) << 56);
   }
   if (threadIdx.x == 0) { X.h_sorted[0] = total; X.h_sorted[1] = 1; X.h_sorted[2] = call + 1; }
 }
 
 // standalone drain: brings the slots of the LAST call to the host (dp_comm_hits with age 0)
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(DP_PUBLISH_THREADS)
 dp_exchange_drain_kernel(const __grid_constant__ dp_exchange_args X) {
   if (dp_exchange_wait(X, X.seq)) dp_exchange_to_host(X, X.seq);
 }
 
 void dp_exchange_drain_launch(const dp_exchange_args& X, cudaStream_t st) {
-  dp_exchange_drain_kernel<<<1, 1024, 0, st>>>(X);
+  dp_exchange_drain_kernel<<<1, DP_PUBLISH_THREADS, 0, st>>>(X);
 }
 
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(DP_PUBLISH_THREADS)
 dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
   __shared__ unsigned long long c[8];
   if (threadIdx.x < 8) c[threadIdx.x] = P.counters[threadIdx.x];
@@ -648,7 +654,7 @@ static int publish_enqueue(dp_ctx* ctx, bool with_dg, bool exchange = false) {
   if (ctx->wire_bytes < 64) P.wire = nullptr;
   P.rec0_len = ctx->last_rec0_len;
   P.n_records = ctx->last_n_records;
-  dp_publish_kernel<<<1, 1024, 0, st>>>(P);
+  dp_publish_kernel<<<1, DP_PUBLISH_THREADS, 0, st>>>(P);
   DP_CUDA(ctx, cudaGetLastError());
   DP_EVENT(ctx, ev5, st);
   return DP_OK;
@@ -1149,8 +1155,10 @@ extern "C" int dp_find_end(dp_ctx* ctx, dp_hit** hits_out, uint64_t* n_hits_out,
   *n_hits_out = S.n_hits;
   const dp_hit* hits = *hits_out;
   const std::vector<uint32_t>& vc = F.var_count;
-  if (results_are_large(true, S))
+  if (results_are_large(true, S)) {
     rc = dimers_large(ctx, F.DL.plan, order, S, R.hits, dimers_out, n_dimers_out);
+    ++F.P.dg_launches;                                     // the gather kernel
+  }
   else
     rc = dimers_to_abi(ctx, R, S, order, [&](size_t i) { return vc[hits[i].primer]; }, dimers_out, n_dimers_out);
   if (rc) { dp_result_free(*hits_out); *hits_out = nullptr; *n_hits_out = 0; return rc; }

@@ -517,6 +517,25 @@ int dp_find_hairpins(dp_ctx* ctx, uint32_t n_seqs, const char* seqs, const uint6
                      const dp_conditions* cond, double max_hairpin_dG,
                      dp_best_structure* out, float* ms_kernel);
 
+/* SURVEY §8(f) N1 — product pairing: the forward/reverse windowed join of
+ * MixtureFactory.create_PCR_mixture (DegenPrimer/PCR_Mixture.py:216-236).  fwd_pos / rev_pos:
+ * the positions (1-based 3' ends, as SearchEngine reports them) of the sites that can be
+ * extended, each sorted ascending.  Returns every (forward site, reverse site) pair the
+ * reference's loop turns into a product -- start = fwd_pos+1, end = rev_pos-1,
+ * min_amplicon <= end-start+1 <= max_amplicon -- in the loop's order (forward index, then
+ * reverse index), INCLUDING its quirks: the scan of reverse sites starts at `rev_start`, which the
+ * reference sets to an index RELATIVE to the previous slice, and a first candidate shorter than
+ * min_amplicon ends the scan for that forward site.  rev_start (optional, n_fwd entries) receives
+ * the slice start used for every forward site: the reference remembers reverse annealings by
+ * rev - rev_start.  The recurrence is walked by one device thread, everything else is parallel. */
+typedef struct dp_pair {
+  uint32_t fwd;   /* index into fwd_pos */
+  uint32_t rev;   /* index into rev_pos */
+} dp_pair;
+int dp_pair_products(dp_ctx* ctx, uint32_t n_fwd, const int64_t* fwd_pos, uint32_t n_rev,
+                     const int64_t* rev_pos, int64_t min_amplicon, int64_t max_amplicon,
+                     dp_pair** pairs, uint64_t* n_pairs, uint32_t* rev_start);
+
 /* ---- roofline calibration -------------------------------------------------------
  * Measured issue rate of the pipes the scan kernels live on (the
  * integer roofline's denominators must be measured on the box).
