@@ -64,8 +64,8 @@ def parse_args():
     ap.add_argument('--no-jit', action='store_true', help='generic scan kernel instead of the run-time specialised one')
     ap.add_argument('--parity-mbp', type=float, default=50.0)
     ap.add_argument('--cpu-repeats', type=int, default=2)
-    ap.add_argument('--host-threads', type=int, default=2, help='host threads that queue and collect the calls')
-    ap.add_argument('--in-flight', type=int, default=4,
+    ap.add_argument('--host-threads', type=int, default=3, help='host threads that queue and collect the calls')
+    ap.add_argument('--in-flight', type=int, default=6,
                     help='calls in flight on the GPU (one context per call); 1 = strictly sequential')
     return ap.parse_args()
 
@@ -510,6 +510,7 @@ def run_ours(args):
             acc['ms_main'] += st['ms_main']
             acc['ms_scan'] += st['ms_scan']
             acc['ms_dg'] += dst['ms_kernel']
+            acc['ms_total'] += st['ms_total']
             acc['launches'] += st['launches'] + dst['launches'] + 1        # + the publish kernel
             acc['dimers'] += len(dimers)
             acc['duplexes'] += dst['duplexes']
@@ -529,7 +530,7 @@ def run_ours(args):
         (F = T = 1: strictly one call after the other on the main thread)."""
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         T = max(1, min(T, F))
-        accs = [dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, launches=0, hits=0, own_hits=0, dimers=0, duplexes=0,
+        accs = [dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, ms_total=0.0, launches=0, hits=0, own_hits=0, dimers=0, duplexes=0,
                      cand=0, windows=0, algo=0) for _ in range(T)]
         shares = [K // T + (1 if t < K % T else 0) for t in range(T)]
         groups = [list(range(t, F, T)) for t in range(T)]
@@ -566,7 +567,7 @@ def run_ours(args):
             elapsed, wall = float(tt[0].item()), float(tt[1].item())
         acc = accs[0]
         for o in accs[1:]:
-            for key in ('ms_main', 'ms_scan', 'ms_dg', 'launches', 'hits', 'own_hits', 'dimers', 'duplexes', 'cand'):
+            for key in ('ms_main', 'ms_scan', 'ms_dg', 'ms_total', 'launches', 'hits', 'own_hits', 'dimers', 'duplexes', 'cand'):
                 acc[key] += o[key]
         return elapsed, wall, acc
 
@@ -717,6 +718,7 @@ def run_ours(args):
             'hits_per_step': acc['hits'] / Kb, 'duplexes_per_step': world * acc['duplexes'] / Kb if world == 1 else None,
             'dimers_per_step_rank0': acc['dimers'] / Kb, 'candidates_per_step_rank0': acc['cand'] / Kb,
             'ms_scan_kernels': seq['ms_scan'] / ks, 'ms_dg_kernels': seq['ms_dg'] / ks,
+            'ms_call_on_device': seq['ms_total'] / ks,
             'sequential_ms_per_step': m['seq_elapsed'] / ks * 1e3,
             'dg_duplexes_per_s': (seq['duplexes'] / ks) / (seq['ms_dg'] / ks * 1e-3) if seq['ms_dg'] > 0 else None,
             'gpu_launches': acc['launches'],
@@ -741,7 +743,7 @@ def run_ours(args):
         'duplexes_per_step': mb['duplexes_per_step'], 'candidates_per_step': mb['candidates_per_step_rank0'],
         'ms_scan_kernels': mb['ms_scan_kernels'], 'ms_dg_kernels': mb['ms_dg_kernels'],
         'dg_duplexes_per_s': mb['dg_duplexes_per_s'], 'gpu_launches': mb['gpu_launches'],
-        'sequential': {'ms_per_step': mb['sequential_ms_per_step'],
+        'sequential': {'ms_per_step': mb['sequential_ms_per_step'], 'ms_call_on_device': mb['ms_call_on_device'],
                        'note': 'the same step with one call in flight (per-call latency); the kernel durations of the '
                                'roofline are taken here'},
         'roofline': roofline, 'int_roofline': int_roofline, 'clocks': clocks, 'parity': parity,

@@ -13,6 +13,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libdegenprimer_b200.so')
+_LIB_OVERRIDE = os.environ.get('DEGENPRIMER_B200_LIB')      # tuning: a library built with other kernel parameters
 
 DP_OK = 0
 DP_ERR_CUDA, DP_ERR_ARG, DP_ERR_ALPHABET, DP_ERR_LENGTH, DP_ERR_UNSUPPORTED = -1, -2, -3, -4, -5
@@ -197,6 +198,11 @@ def load():
     with _lock:
         if _lib is None:
             from .build import build_native, _stale
+            if _LIB_OVERRIDE:
+                lib = C.CDLL(_LIB_OVERRIDE)
+                _declare(lib)
+                _lib = lib
+                return _lib
             if _stale():              # sources newer than the .so: rebuild (seconds) or fail loudly
                 build_native()
             if not os.path.exists(LIB_PATH):

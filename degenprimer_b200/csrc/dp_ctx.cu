@@ -27,7 +27,8 @@ int dp_set_error(dp_ctx* ctx, int code, const char* fmt, ...) {
 namespace {
 struct result_block { void* p; size_t bytes; };
 std::mutex g_blocks_mutex;
-result_block g_blocks[4] = {{nullptr, 0}, {nullptr, 0}, {nullptr, 0}, {nullptr, 0}};
+const int kParked = 16;                   // blocks kept for reuse: two per call in flight and then some
+result_block g_blocks[kParked] = {};
 const size_t kBigBlock = 1u << 20;
 struct block_header { size_t bytes; size_t magic; };          // in front of every block
 const size_t kMagic = 0x44504253554C5453ull;
@@ -41,7 +42,7 @@ void* dp_result_alloc(size_t bytes) {
     {
       std::lock_guard<std::mutex> lock(g_blocks_mutex);
       int best = -1;
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < kParked; ++i)
         if (g_blocks[i].p && g_blocks[i].bytes >= bytes && g_blocks[i].bytes <= 2 * bytes + kBigBlock &&
             (best < 0 || g_blocks[i].bytes < g_blocks[best].bytes))
           best = i;
@@ -89,10 +90,10 @@ void dp_result_free(void* p) {
   if (h->bytes >= kBigBlock) {
     std::lock_guard<std::mutex> lock(g_blocks_mutex);
     int slot = -1;
-    for (int i = 0; i < 4; ++i) if (!g_blocks[i].p) { slot = i; break; }
+    for (int i = 0; i < kParked; ++i) if (!g_blocks[i].p) { slot = i; break; }
     if (slot < 0) {                                            // evict the smallest parked block
       slot = 0;
-      for (int i = 1; i < 4; ++i) if (g_blocks[i].bytes < g_blocks[slot].bytes) slot = i;
+      for (int i = 1; i < kParked; ++i) if (g_blocks[i].bytes < g_blocks[slot].bytes) slot = i;
       if (g_blocks[slot].bytes >= h->bytes) { block_release(h); return; }
       block_release((block_header*)g_blocks[slot].p);
     }

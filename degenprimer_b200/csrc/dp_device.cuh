@@ -177,6 +177,47 @@ __device__ __forceinline__ void dp_verify_window(const dp_scan_args& A, const dp
   if (dp_score_window(A, P, g, with_exc, &s)) dp_emit_hit(A, g, pat, P.len, s, P.n_var);
 }
 
+// ---- windows that touch non-ACGT bases, for a set of prefiltered patterns --------------------
+// A window belongs to the run that holds its FIRST unknown base: for run [start, end) with the previous run
+// ending at prev_end, starts in [max(prev_end, start-(L-1)), start) reach into the run from the left, starts in
+// [max(start, end-emax), end) begin inside it (a window with more than emax = (3L - thr3)/2 unknown bases cannot
+// reach thr3).  Items (run, candidate start) are dealt to threads `first, first + stride, ...`.
+__device__ __forceinline__ void dp_scan_runs_device(const dp_scan_args& A, const dp_pattern* pats, const uint8_t* pattern_of,
+                                                    uint32_t n_pats, uint64_t first, uint64_t stride) {
+  if (!A.n_runs) return;
+  uint32_t left = 0, emax = 0;
+  for (uint32_t p = 0; p < n_pats; ++p) {
+    left = max(left, (uint32_t)pats[p].len - 1u);
+    emax = max(emax, (3u * pats[p].len - pats[p].thr3) / 2u);
+  }
+  emax = max(1u, min(emax, left + 1u));
+  const uint32_t span = left + emax;
+  const uint64_t n_items = A.n_runs * (uint64_t)span;
+  for (uint64_t idx = first; idx < n_items; idx += stride) {
+    const uint64_t r = idx / span;
+    const uint32_t j = (uint32_t)(idx % span);
+    const uint64_t start = A.runs[r].start, end = A.runs[r].end;
+    const uint64_t prev_end = r ? A.runs[r - 1].end : 0;
+    uint64_t g;
+    if (j < left) {
+      const uint64_t d = left - j;                 // 1 .. Lmax-1 bases in front of the run
+      if (start < d) continue;
+      g = start - d;
+      if (g < prev_end) continue;                  // an earlier run owns this window
+    } else {
+      const uint64_t d = emax - (j - left);        // 1 .. emax bases before the run's end
+      if (end - start < d) continue;
+      g = end - d;
+    }
+    for (uint32_t p = 0; p < n_pats; ++p) {
+      const dp_pattern& P = pats[p];
+      if (g < start && g + P.len <= start) continue;          // does not reach the run
+      if (g >= start && 2ull * min((unsigned long long)(end - g), (unsigned long long)P.len) > 3ull * P.len - P.thr3) continue;
+      dp_verify_window(A, P, g, pattern_of[p], true);
+    }
+  }
+}
+
 // ---- deferred exact verify of the run-time specialised kernels ------------------------------
 // The prefilter leaves ~1e-4 of the windows alive.  Verifying them where they are found costs a
 // whole warp ~250 issue slots per candidate (31 lanes idle).  Instead every warp parks its

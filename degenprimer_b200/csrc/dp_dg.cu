@@ -170,12 +170,20 @@ struct dp_duplex_args {
   unsigned long long* counters;
 };
 
-// two warps per block: a block then needs ~5K registers and 33 KB of shared memory and fits on an SM NEXT TO
-// the resident blocks of a scan kernel of another call in flight (which leave ~8K registers free), so the
-// duplex stage of one call overlaps the scan of the next instead of waiting for a gap
-#define DP_DUPLEX_WARPS 2
+// Geometry (measured on B200, tools/dg_variants.sh / n8_variants.sh): 4 warps per block, 16-entry columns, 4 blocks
+// per SM.  Two-warp blocks (5K registers, 23 KB shared memory) fit on an SM NEXT TO the resident block of another
+// call's scan kernel, but the overlap bought nothing measurable while the smaller columns overflow more often:
+// config 4 0.228 vs 0.173 ms, and 0.152 vs 0.075 ms on a 1/8 shard.
+#ifndef DP_DUPLEX_WARPS
+#define DP_DUPLEX_WARPS 4
+#endif
 #define DP_DUPLEX_THREADS (32 * DP_DUPLEX_WARPS)
-#define DP_LANE_LIST 8         // dimers one lane's column of shared memory holds (more: a slow path, same results)
+#ifndef DP_LANE_LIST
+#define DP_LANE_LIST 16        // dimers one lane's column of shared memory holds (more: a slow path, same results)
+#endif
+#ifndef DP_DUPLEX_BLOCKS_PER_SM
+#define DP_DUPLEX_BLOCKS_PER_SM 4
+#endif
 #define DP_DUPLEX_TABLE_BYTES ((sizeof(dp_nn_tables) + 15) / 16 * 16)
 #define DP_DUPLEX_SMEM (DP_DUPLEX_TABLE_BYTES + DP_DUPLEX_WARPS * sizeof(dp_duplex_scratch))
 
@@ -575,7 +583,8 @@ int dp_dg_gather(dp_ctx* ctx, const dp_dg_plan& plan, uint64_t n_hits, const voi
   return DP_OK;
 }
 
-int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches) {
+int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches,
+                  bool hits_fresh) {
   dp_duplex_args A;
   A.dg.T = ctx->d_tables;
   A.dg.PCR_T = L.PCR_T;
@@ -600,12 +609,12 @@ int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint
     DP_CUDA(ctx, cudaFuncSetAttribute(dp_duplex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DP_DUPLEX_SMEM));
     configured[ctx->device & 15] = true;
   }
-  uint64_t blocks = (uint64_t)ctx->sm_count * 8;           // 23 KB of shared memory and 5K registers per block
+  uint64_t blocks = (uint64_t)ctx->sm_count * DP_DUPLEX_BLOCKS_PER_SM;   // 56 KB of shared memory per block
   if (n_pairs_hint) blocks = std::min<uint64_t>(blocks, (n_pairs_hint + DP_DUPLEX_WARPS - 1) / DP_DUPLEX_WARPS);
-  dp_duplex_clear_kernel<<<ctx->sm_count, 128, 0, ctx->stream>>>(A.hits, A.hits_cap, A.counters);
+  if (!hits_fresh) dp_duplex_clear_kernel<<<ctx->sm_count, 128, 0, ctx->stream>>>(A.hits, A.hits_cap, A.counters);
   dp_duplex_kernel<<<(unsigned)blocks, DP_DUPLEX_THREADS, DP_DUPLEX_SMEM, ctx->stream>>>(A, L.plan);
   DP_CUDA(ctx, cudaGetLastError());
-  *launches += 2;                                          // clear + duplex
+  *launches += hits_fresh ? 1 : 2;                         // [clear +] duplex
   return DP_OK;
 }
 

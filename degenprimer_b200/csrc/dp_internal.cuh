@@ -238,7 +238,8 @@ struct dp_dg_launch {
   dp_dg_plan plan;
   double PCR_T, Na_eq_log, max_dimer_dG, max_dG_for_K;
 };
-int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches);
+int dp_dg_enqueue(dp_ctx* ctx, const dp_template* t, const dp_dg_launch& L, uint64_t n_pairs_hint, uint32_t* launches,
+                  bool hits_fresh);     // hits_fresh: straight from a scan / an upload, dimer counts are zero
 // large results: the duplex kernel leaves the number of dimers of every hit in the hit record
 // (dp_raw_hit.reserved); the gather copies every pair's dimers to d_info[slot].final_off with
 // (rank, variant) filled in (dp_dg.cu)

@@ -515,6 +515,9 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
        "  }\n"
        "  if (qn) dp_verify_warp(A, s_pat, dp_jit_pattern_of, q[threadIdx.x & 31u], (threadIdx.x & 31u) < qn);\n"
        "  if (n_cand) atomicAdd(&A.counters[DP_C_CAND], n_cand);\n"
+       "  // windows that touch a non-ACGT base (the prefilter skips them): enumerated from the exception-run table\n"
+       "  // for this unit's patterns, as dp_scan_runs_kernel does for the generic kernel -- no extra launch\n"
+       "  dp_scan_runs_device(A, s_pat, dp_jit_pattern_of, NP, (uint64_t)blockIdx.x * NT + threadIdx.x, stride);\n"
        "}\n";
   return s;
 }

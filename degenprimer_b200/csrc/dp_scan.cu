@@ -114,9 +114,29 @@ dp_scan_runs_kernel(const __grid_constant__ dp_scan_args A, const __grid_constan
   }
 }
 
-// One small block: 128 threads x <= 64 registers fit on an SM next to the resident blocks of another call's
-// scan kernel, so the publish (and the exchange it carries) does not wait for a gap between scans.
-#define DP_PUBLISH_THREADS 128
+// One block of 1024 threads (a 128-thread block that fits next to a resident scan block was tried: no gain, and
+// the exchange at 8 ranks is latency bound on this kernel).
+#ifndef DP_PUBLISH_THREADS
+#define DP_PUBLISH_THREADS 1024
+#define DP_PUBLISH_MIN_BLOCKS 1
+#endif
+
+// Block-wide copy of 64-bit words with eight independent loads in flight per thread: the copies of the publish
+// kernel are latency bound (L2 / NVLink / PCIe round trips), not bandwidth bound.  `src` may be memory a peer GPU
+// has just written: it is read with volatile loads.
+__device__ __forceinline__ void dp_block_copy(uint64_t* __restrict__ dst, const uint64_t* src, uint64_t n) {
+  const volatile uint64_t* s = (const volatile uint64_t*)src;
+  const uint64_t step = blockDim.x;
+  uint64_t i = threadIdx.x;
+  for (; i + 7 * step < n; i += 8 * step) {
+    uint64_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = s[i + k * step];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) dst[i + k * step] = v[k];
+  }
+  for (; i < n; i += step) dst[i] = s[i];
+}
 
 // ---- kernel 4: publish -------------------------------------------------------------
 // Last kernel of a call: one block writes the counters and the first few result
@@ -180,7 +200,7 @@ __device__ void dp_exchange_to_host(const dp_exchange_args& X, uint64_t call) {
     const volatile uint64_t* src = (const volatile uint64_t*)(X.recv_prev + r * X.slot_bytes);
     uint64_t* dst = (uint64_t*)(X.h_prev + r * X.slot_bytes);
     const uint64_t n = min((uint64_t)(uint32_t)src[DP_C_HITS], X.slot_hits);
-    for (uint64_t i = threadIdx.x; i < 8 + 3 * n; i += blockDim.x) dst[i] = src[i];
+    dp_block_copy(dst, (const uint64_t*)src, 8 + 3 * n);
   }
   if (threadIdx.x == 0) {
     uint32_t total = 0;
@@ -235,7 +255,7 @@ __device__ void dp_exchange_to_host(const dp_exchange_args& X, uint64_t call) {
 }
 
 // standalone drain: brings the slots of the LAST call to the host (dp_comm_hits with age 0)
-__global__ void __launch_bounds__(DP_PUBLISH_THREADS)
+__global__ void __launch_bounds__(DP_PUBLISH_THREADS, DP_PUBLISH_MIN_BLOCKS)
 dp_exchange_drain_kernel(const __grid_constant__ dp_exchange_args X) {
   if (dp_exchange_wait(X, X.seq)) dp_exchange_to_host(X, X.seq);
 }
@@ -244,7 +264,7 @@ void dp_exchange_drain_launch(const dp_exchange_args& X, cudaStream_t st) {
   dp_exchange_drain_kernel<<<1, DP_PUBLISH_THREADS, 0, st>>>(X);
 }
 
-__global__ void __launch_bounds__(DP_PUBLISH_THREADS)
+__global__ void __launch_bounds__(DP_PUBLISH_THREADS, DP_PUBLISH_MIN_BLOCKS)
 dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
   __shared__ unsigned long long c[8];
   if (threadIdx.x < 8) c[threadIdx.x] = P.counters[threadIdx.x];
@@ -264,7 +284,7 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
       const uint64_t n_wire = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), P.X.slot_hits);
       for (int r = 0; r < P.X.world; ++r) {
         uint64_t* dst = (uint64_t*)(P.X.peers[r] + (uint64_t)P.X.rank * P.X.slot_bytes);
-        for (uint64_t i = threadIdx.x; i < n_wire * 3; i += blockDim.x) dst[8 + i] = P.hits[i];
+        dp_block_copy(dst + 8, P.hits, n_wire * 3);
         // word 4 bit 1: the slot carries fewer records than word 0 says (receivers fall back)
         if (threadIdx.x < 7)
           dst[threadIdx.x] = threadIdx.x == 5 ? P.X.rec0_len : threadIdx.x == 6 ? P.X.n_records :
@@ -274,16 +294,16 @@ dp_publish_kernel(const __grid_constant__ dp_publish_args P) {
     }
   }
   const uint64_t n_hits = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), (uint64_t)P.spec_hits);
-  for (uint64_t i = threadIdx.x; i < n_hits * 3; i += blockDim.x) P.h_hits[i] = P.hits[i];
+  dp_block_copy(P.h_hits, P.hits, n_hits * 3);
   if (P.with_dg) {
     const uint64_t n_pairs = min(min((uint64_t)(c[DP_C_HITS] >> 32), P.dir_cap), (uint64_t)P.spec_pairs);
     const uint64_t n_dim = min(min((uint64_t)c[DP_C_DIMERS], P.dimers_cap), (uint64_t)P.spec_dimers);
-    for (uint64_t i = threadIdx.x; i < n_pairs; i += blockDim.x) P.h_dir[i] = P.dir[i];
-    for (uint64_t i = threadIdx.x; i < n_dim * 2; i += blockDim.x) P.h_dimers[i] = P.dimers[i];
+    dp_block_copy(P.h_dir, P.dir, n_pairs);
+    dp_block_copy(P.h_dimers, P.dimers, n_dim * 2);
   }
   if (P.wire) {
     const uint64_t n_wire = min(min((uint64_t)(uint32_t)c[DP_C_HITS], P.hits_cap), P.wire_hits);
-    for (uint64_t i = threadIdx.x; i < n_wire * 3; i += blockDim.x) P.wire[8 + i] = P.hits[i];
+    dp_block_copy(P.wire + 8, P.hits, n_wire * 3);
     if (threadIdx.x < 8)
       P.wire[threadIdx.x] = threadIdx.x == 5 ? P.rec0_len : threadIdx.x == 6 ? P.n_records : c[threadIdx.x];
   }
@@ -580,7 +600,7 @@ static int scan_enqueue(dp_ctx* ctx, dp_scan_job& J, uint32_t* launches) {
         if (rc) return rc;
       }
       DP_EVENT(ctx, ev3, ctx->stream);
-      if (A.n_runs) {
+      if (A.n_runs && !J.jit_ready) {               // (the specialised kernels do this at their end themselves)
         // windows touching non-ACGT bases, for the prefiltered patterns
         uint32_t left = 0, emax = 0;
         for (size_t p = 0; p < J.core->pats.size(); ++p) {
@@ -974,7 +994,7 @@ static int pipeline_enqueue(dp_ctx* ctx, const dp_template* t, dp_scan_job& J, c
     DP_EVENT(ctx, ev2, ctx->stream);
   }
   if (dg) {
-    rc = dp_dg_enqueue(ctx, t, *dg, 0, &P.dg_launches);
+    rc = dp_dg_enqueue(ctx, t, *dg, 0, &P.dg_launches, /*hits_fresh=*/P.need_scan);
     if (rc) return rc;
   }
   DP_EVENT(ctx, ev4, ctx->stream);
@@ -1426,7 +1446,7 @@ extern "C" int dp_duplex_dg(dp_ctx* ctx, const dp_template* t, const dp_hit* hit
     DP_CUDA(ctx, cudaMemcpyAsync(ctx->d_counters, hc, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
     ctx->counters_clean = false;
     DP_EVENT(ctx, ev2, st);
-    rc = dp_dg_enqueue(ctx, t, DL, pairs, &launches);
+    rc = dp_dg_enqueue(ctx, t, DL, pairs, &launches, /*hits_fresh=*/true);      // uploaded with reserved = 0
     if (rc) return rc;
     DP_EVENT(ctx, ev4, st);
     // only directory + dimers are wanted back; the hit prefix copy is harmless
