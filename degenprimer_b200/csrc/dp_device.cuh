@@ -40,6 +40,7 @@ enum {
   DP_C_DIMERS = 2,    // dimer slots wanted
   DP_C_TRIED = 3,     // dimers whose dG was computed
   DP_C_SATURATED = 4, // the packed hit counter came close to 2^32
+  DP_C_CHUNK0 = 5,    // 5..7: next chunk of words of launch unit 0..2 of the specialised scan kernel
   DP_C_PACK0 = 8,     // pack kernel: boundary entries wanted
   DP_C_PACK1 = 9      // pack kernel: first foreign byte
 };
@@ -224,6 +225,7 @@ __device__ __forceinline__ void dp_scan_runs_device(const dp_scan_args& A, const
 // candidates in a small shared-memory queue and verifies 32 of them at once, one per lane; the
 // hits of such a batch take ONE atomic (slot and pair index handed out by ballot / prefix sum).
 #define DP_Q_CAP 64
+#define DP_JIT_CHUNK 16       // words per thread and chunk of the specialised scan kernels
 
 // every lane of a converged warp calls this; lanes with `hit` append a record
 __device__ __forceinline__ void dp_emit_hits_warp(const dp_scan_args& A, bool hit, uint64_t g, uint32_t r,

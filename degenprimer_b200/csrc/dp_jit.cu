@@ -363,7 +363,7 @@ static int jit_threads() {
 }
 
 static std::string unit_source(const std::vector<dp_pattern>& pats, const std::vector<std::vector<uint8_t>>& letters,
-                               const std::vector<dp_jit_entry>& entries) {
+                               const std::vector<dp_jit_entry>& entries, int unit_index) {
   (void)pats;
   const int shared_from = jit_env_int("DEGENPRIMER_B200_JIT_SHARED_FROM", 12);
   const bool shared = (int)entries.size() >= shared_from;
@@ -429,9 +429,23 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
        "  unsigned long long* const q = s_queue[threadIdx.x >> 5];\n"
        "  uint32_t qn = 0;\n"
        "  const uint64_t stride = (uint64_t)gridDim.x * NT;\n"
-       "  const uint64_t w_end = A.word_end;\n"
        "  unsigned long long n_cand = 0;\n"
-       "  uint64_t w = A.word_begin + (uint64_t)blockIdx.x * NT + threadIdx.x;\n"
+       "  // Work is handed out per WARP in chunks of DP_JIT_CHUNK x 32 consecutive words from a counter in\n"
+       "  // global memory (zeroed by the previous call's publish kernel), not by a fixed stride: a block that\n"
+       "  // starts late -- its SM was still held by a small kernel of another call in flight -- then simply\n"
+       "  // takes fewer chunks instead of stretching the whole launch by its full share.  No block barrier:\n"
+       "  // with one resident block per SM a barrier per chunk would idle the integer pipe.\n"
+       "  const uint32_t lane = threadIdx.x & 31u;\n"
+       "  const uint64_t n_words = A.word_end > A.word_begin ? A.word_end - A.word_begin : 0;\n"
+       "  const uint64_t chunk_words = (uint64_t)DP_JIT_CHUNK * 32u;\n"
+       "  const uint64_t n_chunks = (n_words + chunk_words - 1) / chunk_words;\n"
+       "  for (;;) {\n"
+       "  unsigned long long chunk = 0;\n"
+       "  if (lane == 0) chunk = atomicAdd(&A.counters[DP_C_CHUNK0 + " + std::to_string(unit_index) + "], 1ull);\n"
+       "  chunk = __shfl_sync(0xffffffffu, chunk, 0);\n"
+       "  if (chunk >= n_chunks) break;\n"
+       "  const uint64_t w_end = min(A.word_end, A.word_begin + (chunk + 1) * chunk_words);\n"
+       "  uint64_t w = A.word_begin + chunk * chunk_words + lane;\n"
        "  uint32_t h0 = 0, hn = 0, hm = 0, l0 = 0, ln = 0, lm = 0;\n"
        "  if (w < w_end) {\n"
        "    h0 = __ldg(A.hi + w); hn = __ldg(A.hi + w + 1);\n"
@@ -441,7 +455,7 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
        "  // the loop is uniform over the warp (its first lane decides): the queue is warp-collective\n"
        "  while (w - (threadIdx.x & 31u) < w_end) {\n"
        "    const uint32_t live = w < w_end ? 0xffffffffu : 0u;\n"
-       "    const uint64_t wn = w + stride;\n"
+       "    const uint64_t wn = w + 32u;\n"
        "    uint32_t ph0 = 0, phn = 0, phm = 0, pl0 = 0, pln = 0, plm = 0;\n"
        "    if (wn < w_end) {\n"
        "      ph0 = __ldg(A.hi + wn); phn = __ldg(A.hi + wn + 1);\n"
@@ -513,6 +527,7 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
   s += "    w = wn;\n"
        "    h0 = ph0; hn = phn; hm = phm; l0 = pl0; ln = pln; lm = plm;\n"
        "  }\n"
+       "  }\n"
        "  if (qn) dp_verify_warp(A, s_pat, dp_jit_pattern_of, q[threadIdx.x & 31u], (threadIdx.x & 31u) < qn);\n"
        "  if (n_cand) atomicAdd(&A.counters[DP_C_CAND], n_cand);\n"
        "  // windows that touch a non-ACGT base (the prefilter skips them): enumerated from the exception-run table\n"
@@ -531,7 +546,7 @@ void dp_jit_make_units(const std::vector<dp_pattern>& pats, const std::vector<st
   for (size_t at = 0; at < entries.size(); at += per) {
     std::vector<dp_jit_entry> part(entries.begin() + at, entries.begin() + std::min(entries.size(), at + per));
     dp_jit_unit u;
-    u.source = unit_source(pats, letters, part);
+    u.source = unit_source(pats, letters, part, (int)units.size());
     u.threads = jit_threads();
     for (const dp_jit_entry& e : part) u.patterns.push_back(e.pattern);
     u.kernel = nullptr;

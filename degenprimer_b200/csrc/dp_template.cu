@@ -418,9 +418,21 @@ int dp_template_from_ascii(dp_ctx* ctx, const char* seq, uint64_t len, dp_templa
   return dp_template_from_records(ctx, 1, seqs, lens, out);
 }
 
+static int template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out);
+
 int dp_template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out) {
   if (!ctx || !path || !out) return dp_set_error(ctx, DP_ERR_ARG, "null argument");
   *out = nullptr;
+  try {                                   // no C++ exception may cross the C ABI (a file larger than memory ...)
+    return template_from_fasta(ctx, path, out);
+  } catch (const std::exception& e) {
+    return dp_set_error(ctx, DP_ERR_NOMEM, "%s: %s", path, e.what());
+  }
+}
+
+}  // extern "C"
+
+static int template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out) {
   FILE* fh = fopen(path, "rb");
   if (!fh) return dp_set_error(ctx, DP_ERR_IO, "cannot open %s", path);
   fseek(fh, 0, SEEK_END);
@@ -477,6 +489,8 @@ int dp_template_from_fasta(dp_ctx* ctx, const char* path, dp_template** out) {
   *out = t;
   return DP_OK;
 }
+
+extern "C" {
 
 void dp_template_free(dp_template* t) {
   if (!t) return;
