@@ -108,7 +108,7 @@ class Plan(object):
 # ---- clocks -------------------------------------------------------------------------
 class ClockSampler(object):
     """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md) through
-    NVML in a background thread (every 2 ms; the nvidia-smi CLI takes longer to start than the
+    NVML in a background thread (every 5 ms; the nvidia-smi CLI takes longer to start than the
     timed region lasts)."""
     REASONS = (('hw_slowdown', 0x8), ('hw_thermal_slowdown', 0x40), ('sw_thermal_slowdown', 0x20),
                ('sw_power_cap', 0x4))
@@ -143,7 +143,7 @@ class ClockSampler(object):
                         self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
                     except Exception:
                         pass
-                time.sleep(0.002)
+                time.sleep(0.005)
         self.thread = threading.Thread(target=loop, daemon=True)
         self.thread.start()
 
@@ -158,6 +158,39 @@ class ClockSampler(object):
                        samples=len(self.samples))
         out['reasons'] = [name for name, bit in self.REASONS if self.bits & bit]
         return out
+
+
+class HostThreads(object):
+    """A few long-lived host threads, each running the callables handed to it one after the other."""
+
+    def __init__(self, n):
+        import queue
+        self.todo = [queue.Queue() for _ in range(n)]
+        self.done = queue.Queue()
+        self.threads = [threading.Thread(target=self._loop, args=(i,), daemon=True) for i in range(n)]
+        for th in self.threads:
+            th.start()
+
+    def _loop(self, i):
+        while True:
+            fn, a = self.todo[i].get()
+            if fn is None:
+                return
+            try:
+                fn(*a)
+            finally:
+                self.done.put(i)
+
+    def run(self, i, fn, *a):
+        self.todo[i].put((fn, a))
+
+    def wait(self, n):
+        for _ in range(n):
+            self.done.get()
+
+    def close(self):
+        for q in self.todo:
+            q.put((None, ()))
 
 
 # ---- CPU arm: the reference algorithm (oracle O1) on the host cores -------------------------
@@ -489,9 +522,13 @@ def run_ours(args):
         F = len(my)
         made = [0] * F
 
+        clock = time.perf_counter
+
         def begin(i):
             j = i % F
+            t = clock()
             lanes[my[j]].find_begin(tmpl, queries[my[j]], cond, seg_begin=0, seg_end=shard.seg_end, algo=args.algo)
+            acc['host_begin'] += clock() - t
             made[j] += 1
 
         for i in range(min(F - 1, n_steps)):
@@ -501,9 +538,13 @@ def run_ours(args):
                 begin(i + F - 1)
             j = i % F
             lane = my[j]
+            t = clock()
             if exchs[lane] is not None and made[j] >= 3:
                 acc['hits'] += len(exchs[lane].collect_hits(2))
+            t1 = clock()
             hits, dimers, st, dst = lanes[lane].find_end()
+            acc['host_collect'] += t1 - t
+            acc['host_end'] += clock() - t1
             if exchs[lane] is None:
                 acc['hits'] += len(hits)
             acc['own_hits'] += len(hits)
@@ -525,13 +566,15 @@ def run_ours(args):
                 if made[j] >= 1:
                     acc['hits'] += len(exchs[lane].collect_hits(0))
 
+    helpers = HostThreads(max(0, min(args.host_threads, n_lanes) - 1))
+
     def timed_region(queries, K, F, T):
         """K steps with F calls in flight (one per lane), queued and collected by T host threads
         (F = T = 1: strictly one call after the other on the main thread)."""
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         T = max(1, min(T, F))
         accs = [dict(ms_main=0.0, ms_scan=0.0, ms_dg=0.0, ms_total=0.0, launches=0, hits=0, own_hits=0, dimers=0, duplexes=0,
-                     cand=0, windows=0, algo=0) for _ in range(T)]
+                     cand=0, windows=0, algo=0, host_begin=0.0, host_collect=0.0, host_end=0.0) for _ in range(T)]
         shares = [K // T + (1 if t < K % T else 0) for t in range(T)]
         groups = [list(range(t, F, T)) for t in range(T)]
         for c in lanes:
@@ -547,12 +590,12 @@ def run_ours(args):
         sync_all()
         t0 = time.perf_counter()
         ev0.record(kstream)
-        threads = [threading.Thread(target=work, args=(t,)) for t in range(1, T)]
-        for th in threads:
-            th.start()
+        # the host threads live as long as the bench (a caller's thread pool): a NEW thread pays the
+        # CUDA runtime's per-thread set-up on its first call, ~10 ms next to 7 other ranks doing the same
+        for t in range(1, T):
+            helpers.run(t - 1, work, t)
         work(0)
-        for th in threads:
-            th.join()
+        helpers.wait(T - 1)
         if errors:
             raise errors[0]
         for c in lanes:
@@ -567,7 +610,8 @@ def run_ours(args):
             elapsed, wall = float(tt[0].item()), float(tt[1].item())
         acc = accs[0]
         for o in accs[1:]:
-            for key in ('ms_main', 'ms_scan', 'ms_dg', 'ms_total', 'launches', 'hits', 'own_hits', 'dimers', 'duplexes', 'cand'):
+            for key in ('ms_main', 'ms_scan', 'ms_dg', 'ms_total', 'launches', 'hits', 'own_hits', 'dimers', 'duplexes', 'cand',
+                        'host_begin', 'host_collect', 'host_end'):
                 acc[key] += o[key]
         return elapsed, wall, acc
 
@@ -722,6 +766,9 @@ def run_ours(args):
             'sequential_ms_per_step': m['seq_elapsed'] / ks * 1e3,
             'dg_duplexes_per_s': (seq['duplexes'] / ks) / (seq['ms_dg'] / ks * 1e-3) if seq['ms_dg'] > 0 else None,
             'gpu_launches': acc['launches'],
+            # where the host threads of rank 0 spent the pipelined region (summed over the threads, per step)
+            'host_ms_per_step': {'find_begin': acc['host_begin'] / Kb * 1e3, 'collect_gathered': acc['host_collect'] / Kb * 1e3,
+                                 'find_end_incl_wait': acc['host_end'] / Kb * 1e3},
         }
 
     mb = block(plan, main)
@@ -738,7 +785,8 @@ def run_ours(args):
                       if plane_bytes > 1.5 * L2_BYTES else 'input planes per rank %.0f MB: NOT larger than L2' % (plane_bytes / 1e6),
                 'sharding': 'one genome, %d contiguous ranges of the padded concatenation, halo %d bases, hit set of the '
                             'whole genome on every rank after every step' % (world, max_len - 1) if world > 1 else 'single GPU',
-                'gpu': info['name'], 'sms': info['sm_count'], 's_generate': s_generate, 's_upload_pack': s_upload},
+                'gpu': info['name'], 'sms': info['sm_count'], 's_generate': s_generate, 's_upload_pack': s_upload,
+                'host_ms_per_step': mb['host_ms_per_step'], 'host_cores': os.cpu_count()},
         'hits_per_step': mb['hits_per_step'], 'dimers_per_step': mb['dimers_per_step_rank0'],
         'duplexes_per_step': mb['duplexes_per_step'], 'candidates_per_step': mb['candidates_per_step_rank0'],
         'ms_scan_kernels': mb['ms_scan_kernels'], 'ms_dg_kernels': mb['ms_dg_kernels'],
@@ -778,9 +826,14 @@ def run_e2e(args, plan, shard, lanes, sync_all, rank, world):
     from degenprimer_b200.SeqUtils import Seq, SeqRecord
     from degenprimer_b200.SeqView import ResidentRecord
     from degenprimer_b200.WorkCounter import WorkCounter
+    from degenprimer_b200 import _native as nat
     n_img = shard.template.image_bytes
     image = torch.empty(n_img, dtype=torch.uint8).pin_memory()
     shard.template.save_image(image.data_ptr(), n_img)
+    # an unverified load from pinned memory moves the tables and two of the three planes: the exception
+    # plane is rebuilt on the device from the tables (dp_exc_records_kernel / dp_exc_runs_kernel)
+    head = np.frombuffer(image.numpy()[:64].tobytes(), dtype=nat.PACK_HEADER)[0]
+    n_h2d = n_img - 4 * int(head['n_words_alloc'])
     gprimers = []
     for i, p in enumerate(plan.primers):
         g = Primer(SeqRecord(Seq(p), id='primer%d' % i), 1.5e-6)
@@ -812,15 +865,14 @@ def run_e2e(args, plan, shard, lanes, sync_all, rank, world):
                     e2e_step(w)
             except BaseException as e:          # noqa: surfaced on the main thread below
                 errors.append(e)
-        threads = [threading.Thread(target=work, args=(w,)) for w in range(1, n_workers)]
-        for th in threads:
-            th.start()
+        for w in range(1, n_workers):
+            helpers.run(w - 1, work, w)
         work(0)
-        for th in threads:
-            th.join()
+        helpers.wait(n_workers - 1)
         if errors:
             raise errors[0]
 
+    helpers = HostThreads(n_workers - 1)           # long-lived, as in run_ours
     for w in range(n_workers):
         e2e_step(w)
     e2e_run(2 * n_workers)
@@ -834,10 +886,12 @@ def run_e2e(args, plan, shard, lanes, sync_all, rank, world):
         tt = torch.tensor([elapsed], dtype=torch.float64, device='cuda')
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         elapsed = float(tt.item())
-    return {'value': plan.bp * plan.n_var / (elapsed / steps), 'unit': UNIT, 'h2d_bytes_per_step': int(n_img),
+    helpers.close()
+    return {'value': plan.bp * plan.n_var / (elapsed / steps), 'unit': UNIT, 'h2d_bytes_per_step': int(n_h2d), 'image_bytes': int(n_img),
             'd2h_bytes_per_step': int(d2h_last[0]), 'ms_per_step': elapsed / steps * 1e3, 'steps': steps,
             'workers': n_workers, 'sites_per_step': int(sites_last[0]),
-            'path': 'packed genome image (0.375 B/bp) in pinned host memory -> dp_template_load_mem (H2D) -> '
+            'path': 'packed genome image (0.375 B/bp) in pinned host memory -> dp_template_load_mem (H2D of the tables and '
+                    'the two base planes, 0.25 B/bp; the exception plane is rebuilt on the device) -> '
                     'SearchEngine.find_all (all primers x all records, one dp_find) -> per (record, primer) '
                     '(fwd_results, rev_results) on the host, as SearchEngine.find puts them on its shelf; Duplex '
                     'objects are built when a site is looked into, the temp files of `find` are not written '

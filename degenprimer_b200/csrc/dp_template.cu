@@ -104,6 +104,48 @@ __global__ void dp_fill_guard_kernel(uint32_t* lo, uint32_t* hi, uint32_t* exc, 
   if (w < to) { lo[w] = 0; hi[w] = 0; exc[w] = 0xFFFFFFFFu; }
 }
 
+// ---- exception plane from the tables ----------------------------------------------
+// The exception plane is redundant with the record table and the exception-run table: a bit is set
+// where the position lies outside every record (padding, spacers, tail guard) or inside a run of
+// non-ACGT letters.  dp_template_load_mem rebuilds it here for an image in page-locked memory instead
+// of moving it over PCIe (a third of the image).
+__global__ void __launch_bounds__(256)
+dp_exc_records_kernel(uint32_t* __restrict__ exc, uint64_t n_words_alloc, const uint64_t* __restrict__ rec_start,
+                      const uint64_t* __restrict__ rec_len, uint32_t n_records) {
+  const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= n_words_alloc) return;
+  const uint64_t g = w * 32;
+  uint32_t a = 0, b = n_records;            // records with start <= g
+  while (a < b) {
+    const uint32_t m = (a + b) >> 1;
+    if (rec_start[m] <= g) a = m + 1; else b = m;
+  }
+  uint32_t mask = 0xFFFFFFFFu;
+  if (a) {
+    const uint64_t end = rec_start[a - 1] + rec_len[a - 1];      // records start on word boundaries
+    if (g + 32 <= end) mask = 0u;
+    else if (g < end) mask = 0xFFFFFFFFu << (uint32_t)(end - g);
+  }
+  exc[w] = mask;
+}
+
+// one warp per run; whole words are stored, the two edge words are OR-ed in (a neighbouring run or
+// the end of the record may share them)
+__global__ void __launch_bounds__(256)
+dp_exc_runs_kernel(uint32_t* __restrict__ exc, const dp_exc_run* __restrict__ runs, uint64_t n_runs) {
+  const uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= n_runs) return;
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint64_t s = runs[r].start, e = runs[r].end;           // [s, e)
+  const uint64_t w0 = s >> 5, w1 = (e - 1) >> 5;
+  for (uint64_t w = w0 + lane; w <= w1; w += 32) {
+    uint32_t mask = 0xFFFFFFFFu;
+    if (w == w0) mask &= 0xFFFFFFFFu << (uint32_t)(s & 31);
+    if (w == w1) mask &= 0xFFFFFFFFu >> (31u - (uint32_t)((e - 1) & 31));
+    if (mask == 0xFFFFFFFFu) exc[w] = mask; else atomicOr(exc + w, mask);
+  }
+}
+
 // ---- unpack kernel ------------------------------------------------------------
 __device__ __forceinline__ uint32_t dp_run_letter(const dp_exc_run* runs, uint64_t n_runs, uint64_t g) {
   uint64_t a = 0, b = n_runs;            // last run with start <= g
@@ -799,10 +841,14 @@ static int template_load_from(dp_ctx* ctx, dp_pack_source& S, int verify, dp_tem
   DP_CUDA(ctx, cudaEventRecord(ctx->stage_ev[0], ctx->stream));
   DP_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->stage_ev[0], 0));
   uint32_t* dst[3] = {t->d_lo, t->d_hi, t->d_exc};
+  bool rebuild_exc = false;
   if (S.mem && is_pinned(S.mem)) {
     // an image in pinned host memory: the planes go out as three DMA transfers, the host touches
     // them only when asked to verify the checksum (which then overlaps the copies)
-    for (int pl = 0; pl < 3; ++pl)
+    // Unverified, the exception plane does not travel: it is rebuilt on the device from the tables
+    // below (dp_exc_records_kernel / dp_exc_runs_kernel) while the other two planes are on their way.
+    rebuild_exc = !verify;
+    for (int pl = 0; pl < (rebuild_exc ? 2 : 3); ++pl)
       DP_CUDA(ctx, cudaMemcpyAsync(dst[pl], S.mem + S.at + (size_t)pl * plane_bytes, plane_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
     if (verify)
       for (int pl = 0; pl < 3; ++pl) c.mix(S.mem + S.at + (size_t)pl * plane_bytes, plane_bytes);
@@ -848,6 +894,15 @@ static int template_load_from(dp_ctx* ctx, dp_pack_source& S, int verify, dp_tem
   if (nrec) {
     DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_start, starts, nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
     DP_CUDA(ctx, cudaMemcpyAsync(t->d_rec_len, rl, nrec * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  if (rebuild_exc) {
+    dp_exc_records_kernel<<<(unsigned)((h.n_words_alloc + 255) / 256), 256, 0, ctx->stream>>>(
+        t->d_exc, h.n_words_alloc, t->d_rec_start, t->d_rec_len, nrec);
+    DP_CUDA(ctx, cudaGetLastError());
+    if (nr) {
+      dp_exc_runs_kernel<<<(unsigned)((nr * 32 + 255) / 256), 256, 0, ctx->stream>>>(t->d_exc, t->d_runs, nr);
+      DP_CUDA(ctx, cudaGetLastError());
+    }
   }
   // later kernels on ctx->stream wait for the planes on the device, the host waits once
   DP_CUDA(ctx, cudaEventRecord(ctx->stage_copied[0], ctx->copy_stream));

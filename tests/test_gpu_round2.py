@@ -199,8 +199,10 @@ def test_packed_image_round_trip(ctx):
     rng = np.random.default_rng(5)
     master, k = 'GAASGCRAAKATYGGGAAC', 2
     seqs = []
-    for n in (50001, 33, 0, 4096):
+    for n in (50001, 33, 0, 4096, 64, 1):
         t = random_dna(rng, n, 'ACGTN', [0.2475] * 4 + [0.01])
+        if n == 50001:                    # long runs: whole words, word edges, a run that ends the record
+            t = t[:1000] + 'N' * 300 + t[1300:2000] + 'R' * 32 + t[2032:4064] + 'Y' * 33 + t[4097:49990] + 'N' * 11
         if n > 1000:
             t, _ = plant_sites(rng, t, [master], k, 8)
         seqs.append(t)
@@ -220,6 +222,11 @@ def test_packed_image_round_trip(ctx):
         got, _ = ctx.scan(t1, [master], k)
         assert np.array_equal(got, want) and len(want) >= 8
         assert t1.unpack(0, 100, 200) == seqs[0][100:300].upper()
+        # the device state is the same bit for bit -- also the exception plane, which the unverified
+        # load from pinned memory does not copy but rebuilds from the record and run tables
+        again = np.zeros(n, dtype=np.uint8)
+        assert t1.save_image(again.ctypes.data, n) == n
+        assert np.array_equal(again, buf[:n])
         t1.close()
     bad = buf[:n].copy()
     bad[n // 2] ^= 4
