@@ -750,6 +750,10 @@ def run_ours(args):
             introof['warp_inst_per_launch'] = entry['warp_inst_per_bp'] * shard_bp
             introof['frac_issued'] = entry['warp_inst_per_bp'] * shard_bp * 32.0 / (ms_main * 1e-3) / lop3
             introof['alu_pipe_pct_ncu'] = entry.get('alu_pipe_pct')
+            if entry.get('alu_pipe_pct') and entry.get('ms_under_ncu'):
+                # the pipe this kernel is bound by: utilisation in the committed capture, scaled by that
+                # capture's kernel time over this run's (same kernel, same input)
+                introof['frac_alu_pipe'] = entry['alu_pipe_pct'] / 100.0 * entry['ms_under_ncu'] / ms_main
             introof['frac_issued_source'] = entry.get('source')
         return roof, introof
 

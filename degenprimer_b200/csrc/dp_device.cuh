@@ -225,7 +225,8 @@ __device__ __forceinline__ void dp_scan_runs_device(const dp_scan_args& A, const
 // candidates in a small shared-memory queue and verifies 32 of them at once, one per lane; the
 // hits of such a batch take ONE atomic (slot and pair index handed out by ballot / prefix sum).
 #define DP_Q_CAP 64
-#define DP_JIT_CHUNK 16       // words per thread and chunk of the specialised scan kernels
+#define DP_JIT_CHUNK 16       // words per thread and chunk of the specialised scan kernels ...
+#define DP_JIT_CHUNK_TAIL 4   // ... and in the last sixteenth of a launch
 
 // every lane of a converged warp calls this; lanes with `hit` append a record
 __device__ __forceinline__ void dp_emit_hits_warp(const dp_scan_args& A, bool hit, uint64_t g, uint32_t r,

@@ -430,22 +430,30 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
        "  uint32_t qn = 0;\n"
        "  const uint64_t stride = (uint64_t)gridDim.x * NT;\n"
        "  unsigned long long n_cand = 0;\n"
-       "  // Work is handed out per WARP in chunks of DP_JIT_CHUNK x 32 consecutive words from a counter in\n"
-       "  // global memory (zeroed by the previous call's publish kernel), not by a fixed stride: a block that\n"
-       "  // starts late -- its SM was still held by a small kernel of another call in flight -- then simply\n"
+       "  // Work is handed out per WARP in chunks of consecutive words from a counter in global memory\n"
+       "  // (zeroed by the previous call's publish kernel), not by a fixed stride: a block that starts\n"
+       "  // late -- its SM was still held by a small kernel of another call in flight -- then simply\n"
        "  // takes fewer chunks instead of stretching the whole launch by its full share.  No block barrier:\n"
-       "  // with one resident block per SM a barrier per chunk would idle the integer pipe.\n"
+       "  // with one resident block per SM a barrier per chunk would idle the integer pipe.  The first\n"
+       "  // 15/16 of the words go out in chunks of DP_JIT_CHUNK x 32, the rest in chunks of\n"
+       "  // DP_JIT_CHUNK_TAIL x 32, so that the warps finish within a few microseconds of each other;\n"
+       "  // the index of the next chunk is asked for before the current one is worked on.\n"
        "  const uint32_t lane = threadIdx.x & 31u;\n"
        "  const uint64_t n_words = A.word_end > A.word_begin ? A.word_end - A.word_begin : 0;\n"
-       "  const uint64_t chunk_words = (uint64_t)DP_JIT_CHUNK * 32u;\n"
-       "  const uint64_t n_chunks = (n_words + chunk_words - 1) / chunk_words;\n"
-       "  for (;;) {\n"
+       "  const uint64_t big_words = (uint64_t)DP_JIT_CHUNK * 32u, small_words = (uint64_t)DP_JIT_CHUNK_TAIL * 32u;\n"
+       "  const uint64_t n_big = (n_words - n_words / 16) / big_words;\n"
+       "  const uint64_t big_total = n_big * big_words;\n"
+       "  const uint64_t n_chunks = n_big + (n_words - big_total + small_words - 1) / small_words;\n"
+       "  unsigned long long* const next_chunk = &A.counters[DP_C_CHUNK0 + " + std::to_string(unit_index) + "];\n"
        "  unsigned long long chunk = 0;\n"
-       "  if (lane == 0) chunk = atomicAdd(&A.counters[DP_C_CHUNK0 + " + std::to_string(unit_index) + "], 1ull);\n"
+       "  if (lane == 0) chunk = atomicAdd(next_chunk, 1ull);\n"
        "  chunk = __shfl_sync(0xffffffffu, chunk, 0);\n"
-       "  if (chunk >= n_chunks) break;\n"
-       "  const uint64_t w_end = min(A.word_end, A.word_begin + (chunk + 1) * chunk_words);\n"
-       "  uint64_t w = A.word_begin + chunk * chunk_words + lane;\n"
+       "  while (chunk < n_chunks) {\n"
+       "  unsigned long long after = 0;\n"
+       "  if (lane == 0) after = atomicAdd(next_chunk, 1ull);        // in flight while this chunk is scanned\n"
+       "  const uint64_t c_begin = chunk < n_big ? chunk * big_words : big_total + (chunk - n_big) * small_words;\n"
+       "  const uint64_t w_end = min(A.word_end, A.word_begin + c_begin + (chunk < n_big ? big_words : small_words));\n"
+       "  uint64_t w = A.word_begin + c_begin + lane;\n"
        "  uint32_t h0 = 0, hn = 0, hm = 0, l0 = 0, ln = 0, lm = 0;\n"
        "  if (w < w_end) {\n"
        "    h0 = __ldg(A.hi + w); hn = __ldg(A.hi + w + 1);\n"
@@ -527,6 +535,7 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
   s += "    w = wn;\n"
        "    h0 = ph0; hn = phn; hm = phm; l0 = pl0; ln = pln; lm = plm;\n"
        "  }\n"
+       "  chunk = __shfl_sync(0xffffffffu, after, 0);\n"
        "  }\n"
        "  if (qn) dp_verify_warp(A, s_pat, dp_jit_pattern_of, q[threadIdx.x & 31u], (threadIdx.x & 31u) < qn);\n"
        "  if (n_cand) atomicAdd(&A.counters[DP_C_CAND], n_cand);\n"
