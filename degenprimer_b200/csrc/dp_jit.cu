@@ -470,23 +470,53 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
        "      pl0 = __ldg(A.lo + wn); pln = __ldg(A.lo + wn + 1);\n";
   if (three) s += "      phm = __ldg(A.hi + wn + 2); plm = __ldg(A.lo + wn + 2);\n";
   s += "    }\n";
-  for (int j = 1; j < 64; ++j) {
-    if (!used[j]) continue;
-    const std::string n = std::to_string(j);
-    if (j == 32) {
-      s += "    const uint32_t h32 = hn, l32 = ln;\n";
-      continue;
+  // Shared planes, "letter planes first" (default): the plane of letter set S is made ONCE per template word
+  // (one LOP3 on the unshifted code words of this word and of the next) and the plane of (position j, S) is one
+  // funnel shift of those -- instead of two funnel shifts per position (both code words) plus one LOP3 per plane.
+  const bool shift_planes = shared && jit_env_int("DEGENPRIMER_B200_JIT_SHIFT_PLANES", 1) != 0;
+  if (!shift_planes)
+    for (int j = 1; j < 64; ++j) {
+      if (!used[j]) continue;
+      const std::string n = std::to_string(j);
+      if (j == 32) {
+        s += "    const uint32_t h32 = hn, l32 = ln;\n";
+        continue;
+      }
+      const std::string x0 = j < 32 ? "0" : "n", x1 = j < 32 ? "n" : "m";
+      const int sh = j & 31;
+      s += "    const uint32_t h" + n + " = __funnelshift_r(h" + x0 + ", h" + x1 + ", " + std::to_string(sh) + "), l" + n +
+           " = __funnelshift_r(l" + x0 + ", l" + x1 + ", " + std::to_string(sh) + ");\n";
     }
-    const std::string x0 = j < 32 ? "0" : "n", x1 = j < 32 ? "n" : "m";
-    const int sh = j & 31;
-    s += "    const uint32_t h" + n + " = __funnelshift_r(h" + x0 + ", h" + x1 + ", " + std::to_string(sh) + "), l" + n +
-         " = __funnelshift_r(l" + x0 + ", l" + x1 + ", " + std::to_string(sh) + ");\n";
-  }
-  if (shared)
+  if (shared && !shift_planes)
     for (auto& kv : planes) {
       const std::string n = std::to_string(kv.second.first);
       s += "    const uint32_t " + kv.first + " = " + plane_expr(kv.second.second, "h" + n, "l" + n) + ";\n";
     }
+  if (shift_planes) {
+    std::map<uint32_t, int> sets;           // letter set -> highest word it is needed in (0, 1 = next, 2 = third)
+    for (auto& kv : planes) {
+      const int j = kv.second.first;
+      int& top = sets[kv.second.second];
+      top = std::max(top, j == 0 ? 0 : j <= 32 ? 1 : 2);
+    }
+    for (auto& kv : sets) {
+      const std::string n = "s" + std::to_string(kv.first);
+      s += "    const uint32_t " + n + "_0 = " + plane_expr(kv.first, "h0", "l0");
+      if (kv.second >= 1) s += ", " + n + "_n = " + plane_expr(kv.first, "hn", "ln");
+      if (kv.second >= 2) s += ", " + n + "_m = " + plane_expr(kv.first, "hm", "lm");
+      s += ";\n";
+    }
+    for (auto& kv : planes) {
+      const int j = kv.second.first;
+      const std::string n = "s" + std::to_string(kv.second.second);
+      std::string e;
+      if (j == 0) e = n + "_0";
+      else if (j < 32) e = "__funnelshift_r(" + n + "_0, " + n + "_n, " + std::to_string(j) + ")";
+      else if (j == 32) e = n + "_n";
+      else e = "__funnelshift_r(" + n + "_n, " + n + "_m, " + std::to_string(j - 32) + ")";
+      s += "    const uint32_t " + kv.first + " = " + e + ";\n";
+    }
+  }
   // patterns in chunks of 8: one vote + branch per chunk on the hot path
   for (size_t c0 = 0; c0 < ups.size(); c0 += 8) {
     const size_t c1 = std::min(ups.size(), c0 + 8);
@@ -522,14 +552,16 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
       em.prefix = "t";
       const std::string res = em.ge(gnames, (int)u.groups.size() - u.e.K);
       s += em.code;
-      s += "        " + v + " = " + res + " & live;\n      }\n";
+      s += "        " + v + " = " + res + ";\n      }\n";
     }
-    s += "      if (__any_sync(0xffffffffu, (alive" + std::to_string(c0);
+    s += "      if (__any_sync(0xffffffffu, ((alive" + std::to_string(c0);
     for (size_t i = c0 + 1; i < c1; ++i) s += " | alive" + std::to_string(i);
-    s += ") != 0u)) {\n";
+    // lanes past the end of the chunk hold zeros, not template words: their bits are dropped here, once per
+    // group of patterns, and again where a pattern's word is handed to the queue
+    s += ") & live) != 0u)) {\n";
     for (size_t i = c0; i < c1; ++i)
-      s += "        if (__any_sync(0xffffffffu, alive" + std::to_string(i) + " != 0u)) qn = dp_queue_push(A, s_pat, dp_jit_pattern_of, q, qn, alive" +
-           std::to_string(i) + ", w, " + std::to_string(i) + "u, n_cand);\n";
+      s += "        if (__any_sync(0xffffffffu, (alive" + std::to_string(i) + " & live) != 0u)) qn = dp_queue_push(A, s_pat, dp_jit_pattern_of, q, qn, alive" +
+           std::to_string(i) + " & live, w, " + std::to_string(i) + "u, n_cand);\n";
     s += "      }\n    }\n";
   }
   s += "    w = wn;\n"
