@@ -376,6 +376,10 @@ int dp_set_wire(dp_ctx* ctx, void* device_ptr, uint64_t bytes);
  * epilogue of the compute, there is no separate collective launch.  All ranks
  * must make the same sequence of calls; ranks run at most one call apart (a call
  * first waits, with a 2 s timeout, until every peer's previous call has landed).
+ * After a timeout (a rank made fewer calls -- e.g. it failed before it queued one)
+ * the ranks' sequence numbers no longer agree: every later dp_comm_gathered /
+ * dp_comm_hits of this ctx returns DP_ERR_STATE until the exchange is set up again
+ * (dp_comm_destroy, dp_comm_export, dp_comm_attach on every rank).
  * The gathered hits are fetched with `age`:
  *   age 0  the call that just returned (one small kernel waits for the slowest
  *          rank's slot),
