@@ -747,14 +747,21 @@ def run_ours(args):
             # template base) x 32 lanes / this run's kernel time, against the LOP3 rate calibrated in this run;
             # every instruction counts, so a kernel that sits on the ALU pipe reads close to (or a little
             # above) 1: its few non-ALU instructions issue on other pipes
-            introof['warp_inst_per_launch'] = entry['warp_inst_per_bp'] * shard_bp
-            introof['frac_issued'] = entry['warp_inst_per_bp'] * shard_bp * 32.0 / (ms_main * 1e-3) / lop3
             introof['alu_pipe_pct_ncu'] = entry.get('alu_pipe_pct')
-            if entry.get('alu_pipe_pct') and entry.get('ms_under_ncu'):
-                # the pipe this kernel is bound by: utilisation in the committed capture, scaled by that
-                # capture's kernel time over this run's (same kernel, same input)
-                introof['frac_alu_pipe'] = entry['alu_pipe_pct'] / 100.0 * entry['ms_under_ncu'] / ms_main
             introof['frac_issued_source'] = entry.get('source')
+            captured_ms = float(entry.get('ms_under_ncu') or 0.0)
+            if captured_ms and ms_main < 0.95 * captured_ms:
+                # this run's kernel is clearly shorter than the captured one: the kernel has changed since the
+                # capture (fewer instructions), so the capture's instruction count no longer describes it
+                introof['counters_stale'] = ('kernel time %.3f ms against %.3f ms in the committed capture: the '
+                                             'instruction count of that capture is not this kernel\'s' % (ms_main, captured_ms))
+            else:
+                introof['warp_inst_per_launch'] = entry['warp_inst_per_bp'] * shard_bp
+                introof['frac_issued'] = entry['warp_inst_per_bp'] * shard_bp * 32.0 / (ms_main * 1e-3) / lop3
+                if entry.get('alu_pipe_pct') and captured_ms:
+                    # the pipe this kernel is bound by: utilisation in the committed capture, scaled by that
+                    # capture's kernel time over this run's (same kernel, same input)
+                    introof['frac_alu_pipe'] = entry['alu_pipe_pct'] / 100.0 * captured_ms / ms_main
         return roof, introof
 
     def block(p, m):

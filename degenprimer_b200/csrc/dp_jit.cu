@@ -269,12 +269,12 @@ struct thr_emitter {
     if (n == 1) return x[0];
     if (T == 1) return tmp(join(x, "|"), n / 2);
     if (T == n) return tmp(join(x, "&"), n / 2);
-    if (n == 3) return tmp("((" + x[0] + " & " + x[1] + ") | (" + x[2] + " & (" + x[0] + " | " + x[1] + ")))");
+    if (n == 3) return tmp("dp_maj(" + x[0] + ", " + x[1] + ", " + x[2] + ")");
     std::vector<std::string> W, C;
     for (int i = 0; i + 3 <= n; i += 3) {
       const std::string &a = x[i], &b = x[i + 1], &c = x[i + 2];
-      W.push_back(tmp("(" + a + " ^ " + b + " ^ " + c + ")"));
-      C.push_back(tmp("((" + a + " & " + b + ") | (" + c + " & (" + a + " | " + b + ")))"));
+      W.push_back(tmp("dp_xor3(" + a + ", " + b + ", " + c + ")"));
+      C.push_back(tmp("dp_maj(" + a + ", " + b + ", " + c + ")"));
     }
     for (int i = n - n % 3; i < n; ++i) W.push_back(x[i]);
     std::vector<std::string> terms;
@@ -410,6 +410,17 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
   }
   s += std::string("//PLAN mode ") + (shared ? "shared-planes" : "folded-planes") + "\n";
   s += "#include \"dp_device.cuh\"\n";
+  // The three-input functions of the group / threshold network as explicit LOP3: left to itself the compiler
+  // re-associates the and/or/xor trees of a 40-pattern kernel into more instructions than the source has statements
+  // (713 -> 524 LOP3 in the word loop of config 4).  DEGENPRIMER_B200_JIT_LOP3=0: the same functions in plain C.
+  if (jit_env_int("DEGENPRIMER_B200_JIT_LOP3", 1) != 0)
+    s += "#define DP_LOP3(name, lut) __device__ __forceinline__ uint32_t name(uint32_t a, uint32_t b, uint32_t c) { \\\n"
+         "  uint32_t r; asm(\"lop3.b32 %0, %1, %2, %3, \" #lut \";\" : \"=r\"(r) : \"r\"(a), \"r\"(b), \"r\"(c)); return r; }\n"
+         "DP_LOP3(dp_and3, 0x80)\nDP_LOP3(dp_xor3, 0x96)\nDP_LOP3(dp_maj, 0xE8)\n";
+  else
+    s += "__device__ __forceinline__ uint32_t dp_and3(uint32_t a, uint32_t b, uint32_t c) { return a & b & c; }\n"
+         "__device__ __forceinline__ uint32_t dp_xor3(uint32_t a, uint32_t b, uint32_t c) { return a ^ b ^ c; }\n"
+         "__device__ __forceinline__ uint32_t dp_maj(uint32_t a, uint32_t b, uint32_t c) { return (a & b) | (c & (a | b)); }\n";
   s += "static_assert(sizeof(dp_pattern) == " + std::to_string(sizeof(dp_pattern)) + ", \"dp_pattern layout\");\n";
   s += "static_assert(sizeof(dp_scan_args) == " + std::to_string(sizeof(dp_scan_args)) + ", \"dp_scan_args layout\");\n";
   s += "static_assert(sizeof(dp_raw_hit) == " + std::to_string(sizeof(dp_raw_hit)) + ", \"dp_raw_hit layout\");\n";
@@ -510,9 +521,11 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
       const int j = kv.second.first;
       const std::string n = "s" + std::to_string(kv.second.second);
       std::string e;
-      if (j == 0) e = n + "_0";
+      // (an unshifted plane takes the live-lane mask along: as a two-input function of the code words ptxas would
+      // otherwise re-derive it inside every group that uses it -- one more LOP3 per pattern)
+      if (j == 0) e = n + "_0 & live";
       else if (j < 32) e = "__funnelshift_r(" + n + "_0, " + n + "_n, " + std::to_string(j) + ")";
-      else if (j == 32) e = n + "_n";
+      else if (j == 32) e = n + "_n & live";
       else e = "__funnelshift_r(" + n + "_n, " + n + "_m, " + std::to_string(j - 32) + ")";
       s += "    const uint32_t " + kv.first + " = " + e + ";\n";
     }
@@ -531,10 +544,17 @@ static std::string unit_source(const std::vector<dp_pattern>& pats, const std::v
         const std::string acc = "g" + std::to_string(g);
         gnames.push_back(acc);
         if (shared) {
+          std::vector<std::string> in;
+          for (int j : u.groups[g]) in.push_back(plane_name(j, dp_letter_set(lt[j])));
           std::string e;
-          for (size_t t = 0; t < u.groups[g].size(); ++t) {
-            const int j = u.groups[g][t];
-            e += (t ? " & " : "") + plane_name(j, dp_letter_set(lt[j]));
+          if (shift_planes) {
+            // chains of explicit three-input ANDs; an even number of planes leaves one input free and the
+            // live-lane mask fills it
+            if (in.size() % 2 == 0) in.push_back("live");
+            e = in[0];
+            for (size_t t = 1; t + 1 < in.size(); t += 2) e = "dp_and3(" + e + ", " + in[t] + ", " + in[t + 1] + ")";
+          } else {
+            for (size_t t = 0; t < in.size(); ++t) e += (t ? " & " : "") + in[t];
           }
           s += "        const uint32_t " + acc + " = " + e + ";\n";
         } else {

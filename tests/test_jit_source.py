@@ -4,9 +4,11 @@ The hot loop of the generated CUDA source is straight-line code over six 32-bit 
 letter-set planes, funnel shifts, group ANDs and the "at least `need` of G groups" network.  Those statements are
 plain C bit operations, so this test runs them in Python on random templates and checks every `alive` bit against
 the plan's own definition (tests/test_jit_plan.py::_alive): bit b of pattern i is set iff at least `need` position
-groups of the window that starts at base b match completely.  No GPU; NVRTC is only needed because
+groups of the window that starts at base b match completely.  (dp_and3 / dp_xor3 / dp_maj are explicit LOP3 in the
+kernel -- inline PTX with the truth tables 0x80 / 0x96 / 0xE8, checked below -- and plain Python here.)  No GPU; NVRTC is only needed because
 dp_jit_selftest compiles the source it writes."""
 import ctypes
+import os
 import re
 
 import numpy as np
@@ -111,7 +113,9 @@ def _check(native_lib, masters, k, tmp_path, seed, trials):
             text = text[:at] + ''.join(site) + text[at + len(site):]
             text = text[:96]
         (l0, h0), (ln, hn), (lm, hm) = _planes(text)
-        env = dict(h0=h0, hn=hn, hm=hm, l0=l0, ln=ln, lm=lm, live=M32, __funnelshift_r=_funnelshift_r)
+        env = dict(h0=h0, hn=hn, hm=hm, l0=l0, ln=ln, lm=lm, live=M32, __funnelshift_r=_funnelshift_r,
+                   dp_and3=lambda a, b, c: a & b & c, dp_xor3=lambda a, b, c: a ^ b ^ c,
+                   dp_maj=lambda a, b, c: (a & b) | (c & (a | b)))
         exec(program, env)
         for slot, plan in enumerate(plans):
             got = env['alive%d' % slot] & M32
@@ -124,6 +128,23 @@ def _check(native_lib, masters, k, tmp_path, seed, trials):
             assert got == want, (masters, slot, plan, text, bin(got), bin(want))
             near += bin(want).count('1')
     assert near >= trials // 8            # the planted near-hits did light bits up
+
+
+def test_lop3_truth_tables(native_lib, tmp_path):
+    """The immediates of the explicit LOP3 helpers are the truth tables of and / xor / majority of three inputs
+    (bit (a << 2 | b << 1 | c) of the table = f(a, b, c); all three functions are symmetric)."""
+    src = _source(native_lib, CASES[0][0], CASES[0][1], tmp_path)
+    found = dict(re.findall(r'DP_LOP3\((dp_\w+), (0x[0-9A-Fa-f]+)\)', src))
+    if not found and os.environ.get('DEGENPRIMER_B200_JIT_LOP3') == '0':
+        pytest.skip('the plain-C helpers were asked for')
+    assert set(found) == {'dp_and3', 'dp_xor3', 'dp_maj'}
+    fn = {'dp_and3': lambda a, b, c: a & b & c, 'dp_xor3': lambda a, b, c: a ^ b ^ c,
+          'dp_maj': lambda a, b, c: (a & b) | (c & (a | b))}
+    for name, lut in found.items():
+        table = 0
+        for i in range(8):
+            table |= fn[name]((i >> 2) & 1, (i >> 1) & 1, i & 1) << i
+        assert table == int(lut, 16), name
 
 
 def nat_sets(ch):
