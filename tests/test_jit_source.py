@@ -158,6 +158,17 @@ def test_generated_prefilter_is_the_plan(native_lib, tmp_path, case):
     _check(native_lib, masters, k, tmp_path, 500 + case, 60)
 
 
+@pytest.mark.parametrize('case', range(len(CASES)))
+def test_generated_prefilter_with_shared_planes(native_lib, tmp_path, case, monkeypatch):
+    """The same primer sets forced into the multiplex form (planes kept in registers, letter planes shifted per
+    position, explicit three-input ANDs): covers degenerate letter sets and the third template word (35-mer) there."""
+    monkeypatch.setenv('DEGENPRIMER_B200_JIT_SHARED_FROM', '1')
+    masters, k = CASES[case]
+    src = _source(native_lib, masters, k, tmp_path)
+    assert '//PLAN mode shared-planes' in src
+    _check(native_lib, masters, k, tmp_path, 900 + case, 40)
+
+
 def test_generated_prefilter_of_the_multiplex(native_lib, tmp_path):
     """config 4: 40 patterns, shared planes made from letter-set planes by funnel shifts."""
     from degenprimer_b200.synthetic import multiplex_primers
